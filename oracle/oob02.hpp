@@ -1,0 +1,549 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see ojson.hpp header).
+//
+// CPU restatement of the OB02 mesh-optimisation steps (paths relative to
+// /root/reference/js_iteration_2/):
+//   make_neighbour_faces_of_vertex   mesh_algorithms.hpp:178-209
+//   make_edge_lookup                 mesh_algorithms.hpp:50-110   (32-bit ids / 64-bit keys)
+//   build_faces_of_faces             mesh_algorithms.hpp:111-131
+//   compute_centroids                implicit_vectorised_algorithms.hpp:161-171
+//   produce_facet_normals            implicit_vectorised_algorithms.hpp:52-133
+//   normalize_1111 / normalise_inplace   vectorised_algorithms/normalise_inplace.hpp:19-70
+//   kij / wi / vertex_resampling_VV1 vertex_resampling.hpp:47-141
+//   process2_vertex_resampling_relaxation_v1  vertex_resampling.hpp:152-225
+//   compute_average_edge_length      centroids_projection.cpp:70-82  (accumulator initialised to 0 here)
+//   make_alpha_list                  centroids_projection.cpp:144-194
+//   create_directions_bundle         centroids_projection.cpp:197-362
+//   set_centers_on_surface           centroids_projection.cpp:421-1214
+//   bisection                        polygoniser/bisection.hpp:117-459 (iteration cap added: the reference loops forever
+//                                    when the interval collapses before |f|<=tol)
+//   vertex_apply_qem / get_A_b       qem.hpp:256-599  (Eigen JacobiSVD of the symmetric PSD 3x3 restated as a cyclic
+//                                    Jacobi eigen-decomposition; Eigen is not in this image — tolerance parity only)
+//   make_random_pm1                  vectorised_algorithms/make_random_pm1.hpp:15-28 (boost mt11213b + uniform_01<float>
+//                                    restated from the published algorithm; unpinned)
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <map>
+#include <vector>
+#include "oshapes.hpp"
+
+namespace oracle {
+
+const REAL ROOT_TOLERANCE = 0.001 / 10.0;          // configs.hpp:33
+const REAL MILLIMETER = 1.0;                        // configs.hpp:38-48: every step is a REAL constexpr
+const REAL MICROMETER = MILLIMETER / 1000.0;
+const REAL NANOMETER = MICROMETER / 1000.0;
+const REAL MIN_AREA = (30 * NANOMETER) * (30 * NANOMETER);
+const REAL min_gradient_len = 0.000001;            // configs.hpp:57
+const int BISECTION_MAX_ITER = 100;                // ours
+
+struct Stats {
+    long projection_by_type[7] = {0, 0, 0, 0, 0, 0, 0};   // centroids resolved by direction type k
+    long projection_failed = 0;
+    long bisection_capped = 0;
+    long bisected = 0;
+};
+
+inline REAL norm_2(REAL x, REAL y, REAL z) { return std::sqrt(x * x + y * y + z * z); }
+
+typedef std::vector<std::vector<int>> umbrella_t;
+
+inline umbrella_t make_neighbour_faces_of_vertex(const std::vector<int>& faces, int num_verts) {
+    umbrella_t nb(num_verts);
+    int nf = (int)(faces.size() / 3);
+    for (int fi = 0; fi < nf; fi++)
+        for (int s = 0; s < 3; s++) nb[faces[fi * 3 + s]].push_back(fi);
+    return nb;
+}
+
+// make_edge_lookup + build_faces_of_faces -> faces_of_faces[nf][3]
+inline std::vector<int> build_faces_of_faces(const std::vector<int>& faces) {
+    int nf = (int)(faces.size() / 3);
+    int num_edges = (nf * 3) / 2;
+    std::vector<int> eof((size_t)nf * 3, 0);
+    std::vector<int> foe;                      // grows by 2 per edge; zero-initialised like multi_array
+    foe.reserve((size_t)num_edges * 2);
+    std::map<int64_t, int> lookup;
+    int64_t modulo = (int64_t)num_edges;
+    for (int fi = 0; fi < nf; fi++)
+        for (int vj = 0; vj < 3; vj++) {
+            int v2j = (vj + 1) % 3;
+            int64_t e1 = faces[fi * 3 + vj], e2 = faces[fi * 3 + v2j];
+            int64_t key = (e2 > e1) ? (e1 + e2 * modulo) : (e2 + e1 * modulo);
+            // NOTE: with modulo = num_edges the reference key is only unique when vertex ids < num_edges
+            // (true for closed meshes: Nv ~ Nf/2); restated as written.
+            auto it = lookup.find(key);
+            if (it == lookup.end()) {
+                int e_id = (int)(foe.size() / 2);
+                foe.push_back(fi);
+                foe.push_back(0);
+                eof[fi * 3 + vj] = e_id;
+                lookup.insert(std::make_pair(key, e_id));
+            } else {
+                int e_id = it->second;
+                eof[fi * 3 + vj] = e_id;
+                foe[e_id * 2 + 1] = fi;
+            }
+        }
+    std::vector<int> fof((size_t)nf * 3);
+    for (int face = 0; face < nf; face++)
+        for (int edge = 0; edge < 3; edge++) {
+            int e = eof[face * 3 + edge];
+            fof[face * 3 + edge] = (foe[e * 2] != face) ? foe[e * 2] : foe[e * 2 + 1];
+        }
+    return fof;
+}
+
+inline void compute_centroids(const std::vector<int>& faces, const vects& verts, vects& centroids) {
+    int nt = (int)(faces.size() / 3);
+    for (int j = 0; j < nt; j++) {
+        const int f0 = faces[j * 3], f1 = faces[j * 3 + 1], f2 = faces[j * 3 + 2];
+        for (int di = 0; di < 3; di++) centroids[j][di] = (verts[f0][di] + verts[f1][di] + verts[f2][di]) / (REAL)(3.0);
+    }
+}
+
+inline void normalize_1111(vects& A) {
+    for (size_t i = 0; i < A.n(); i++) {
+        REAL norm = norm_2(A[i][0], A[i][1], A[i][2]);
+        for (int j = 0; j < 3; j++) A[i][j] = A[i][j] / norm;
+    }
+}
+inline void normalise_inplace(vects& A, REAL minimum_acceptable_norm) {
+    for (size_t i = 0; i < A.n(); i++) {
+        REAL norm = norm_2(A[i][0], A[i][1], A[i][2]);
+        norm = (norm < minimum_acceptable_norm) ? 1.0 : norm;
+        REAL factor = 1.0 / norm;
+        A[i][0] = A[i][0] * factor;
+        A[i][1] = A[i][1] * factor;
+        A[i][2] = A[i][2] * factor;
+    }
+}
+
+inline vects produce_facet_normals(const std::vector<int>& faces, const vects& verts, bool force_normalisation) {
+    const REAL min_norm_sq = MIN_AREA * MIN_AREA;
+    const REAL osqrt3 = 1.0 / std::sqrt((REAL)3.0);
+    int nf = (int)(faces.size() / 3);
+    vects out(nf);
+    for (int fi = 0; fi < nf; ++fi) {
+        int f0 = faces[fi * 3], f1 = faces[fi * 3 + 1], f2 = faces[fi * 3 + 2];
+        REAL x1 = verts[f1][0] - verts[f0][0], y1 = verts[f1][1] - verts[f0][1], z1 = verts[f1][2] - verts[f0][2];
+        REAL x2 = verts[f2][0] - verts[f0][0], y2 = verts[f2][1] - verts[f0][1], z2 = verts[f2][2] - verts[f0][2];
+        REAL x = y1 * z2 - z1 * y2;
+        REAL y = z1 * x2 - x1 * z2;
+        REAL z = x1 * y2 - y1 * x2;
+        if (force_normalisation) {
+            REAL n2 = x * x + y * y + z * z;
+            if (n2 < min_norm_sq) { x = osqrt3; y = osqrt3; z = osqrt3; }
+            else { REAL n = std::sqrt(n2); x = x / n; y = y / n; z = z / n; }
+        }
+        out[fi][0] = x; out[fi][1] = y; out[fi][2] = z;
+    }
+    return out;
+}
+
+// ---- vertex_resampling.hpp --------------------------------------------------------------------
+inline REAL kij(int i, int j, const vects& c, const vects& nrm) {
+    REAL mimj = nrm[i][0] * nrm[j][0] + nrm[i][1] * nrm[j][1] + nrm[i][2] * nrm[j][2];
+    if (mimj > 1.0) mimj = 1.0;
+    if (mimj < -1.0) mimj = -1.0;
+    REAL pipj = norm_2(c[i][0] - c[j][0], c[i][1] - c[j][1], c[i][2] - c[j][2]);
+    if (pipj == 0) return 0;
+    return std::acos(mimj) / pipj;
+}
+inline REAL wi(int i, const std::vector<int>& fof, const vects& c, const vects& nrm, float cc) {
+    REAL ki = 0;
+    for (int j = 0; j < 3; j++) ki += kij(i, fof[i * 3 + j], c, nrm);
+    REAL w = 1.0 + cc * ki;
+    return w;
+}
+
+inline void vertex_resampling(const implicit_function& object, float c, std::vector<REAL>& result_verts,
+                              const std::vector<int>& faces) {
+    int nv = (int)(result_verts.size() / 3), nf = (int)(faces.size() / 3);
+    vects verts(nv);
+    verts.d = result_verts;
+    vects centroids(nf);
+    compute_centroids(faces, verts, centroids);
+    vects nrm(nf);
+    object.eval_gradient(centroids, &nrm);
+    normalize_1111(nrm);
+    umbrella_t nb = make_neighbour_faces_of_vertex(faces, nv);
+    std::vector<int> fof = build_faces_of_faces(faces);
+    scalars w(nf);
+    for (int i = 0; i < nf; i++) w[i] = wi(i, fof, centroids, nrm, c);
+    for (int i = 0; i < nv; i++) {
+        const std::vector<int>& um = nb[i];
+        REAL sum_w = 0;
+        for (size_t j = 0; j < um.size(); j++) sum_w += w[um[j]];
+        REAL nx = 0, ny = 0, nz = 0;
+        for (size_t j = 0; j < um.size(); j++) {
+            REAL wj = w[um[j]] / sum_w;
+            nx += wj * centroids[um[j]][0];
+            ny += wj * centroids[um[j]][1];
+            nz += wj * centroids[um[j]][2];
+        }
+        result_verts[i * 3] = nx; result_verts[i * 3 + 1] = ny; result_verts[i * 3 + 2] = nz;
+    }
+}
+
+// ---- centroids_projection.cpp -----------------------------------------------------------------
+inline REAL compute_average_edge_length(const std::vector<int>& faces, const vects& verts) {
+    int nfaces = (int)(faces.size() / 3);
+    REAL edge_length = 0;   // uninitialised in the reference (:72)
+    for (int j = 0; j < nfaces; j++) {
+        int f0 = faces[j * 3], f1 = faces[j * 3 + 1], f2 = faces[j * 3 + 2];
+        edge_length += norm_2(verts[f0][0] - verts[f1][0], verts[f0][1] - verts[f1][1], verts[f0][2] - verts[f1][2]);
+        edge_length += norm_2(verts[f0][0] - verts[f2][0], verts[f0][1] - verts[f2][1], verts[f0][2] - verts[f2][2]);
+        edge_length += norm_2(verts[f2][0] - verts[f1][0], verts[f2][1] - verts[f1][1], verts[f2][2] - verts[f1][2]);
+    }
+    return edge_length / (3. * nfaces);
+}
+
+inline std::vector<REAL> make_alpha_list(REAL initial_step_size, REAL min_step_size, REAL max_dist, int max_iter) {
+    REAL unit_of_length = max_dist;
+    std::vector<REAL> alpha_list;
+    REAL step_size = initial_step_size;
+    while (step_size > min_step_size) {
+        step_size = step_size * 0.5;
+        int total_steps = (int)(std::floor(max_dist / std::abs(step_size) + 0.001));
+        int max_steps = std::min(max_iter, total_steps);
+        for (int i = 1; i < max_steps + 1; i += 2) {
+            REAL alpha = ((REAL)i) * step_size;
+            alpha_list.push_back(alpha / unit_of_length);
+            alpha_list.push_back(-alpha / unit_of_length);
+        }
+    }
+    return alpha_list;
+}
+
+// boost::random::mt11213b (published parameters) + boost::random::uniform_01<float>
+struct mt11213b {
+    static const int N = 351, M = 175;
+    uint32_t x[N];
+    int i;
+    explicit mt11213b(uint32_t seed) {
+        x[0] = seed;
+        for (int k = 1; k < N; k++) x[k] = 1812433253u * (x[k - 1] ^ (x[k - 1] >> 30)) + (uint32_t)k;
+        i = N;
+    }
+    void twist() {
+        const uint32_t upper = ~0u << 19, lower = ~upper;
+        for (int k = 0; k < N; k++) {
+            uint32_t y = (x[k] & upper) | (x[(k + 1) % N] & lower);
+            x[k] = x[(k + M) % N] ^ (y >> 1) ^ ((y & 1) ? 0xccab8ee7u : 0u);
+        }
+        i = 0;
+    }
+    uint32_t operator()() {
+        if (i >= N) twist();
+        uint32_t z = x[i++];
+        z ^= (z >> 11);
+        z ^= (z << 7) & 0x31b6ab00u;
+        z ^= (z << 15) & 0xffe50000u;
+        z ^= (z >> 17);
+        return z;
+    }
+};
+inline float uniform_01f(mt11213b& eng) {
+    for (;;) {
+        float factor = 1.0f / ((float)0xffffffffu + 1.0f);
+        float r = (float)eng() * factor;
+        if (r < 1.0f) return r;
+    }
+}
+inline vects make_random_pm1(int n, REAL amplitude) {
+    vects r(n);
+    mt11213b rng(12);
+    for (int i = 0; i < n; ++i) {
+        r[i][0] = (uniform_01f(rng) * 2.0 - 1.0) * amplitude;
+        r[i][1] = (uniform_01f(rng) * 2.0 - 1.0) * amplitude;
+        r[i][2] = (uniform_01f(rng) * 2.0 - 1.0) * amplitude;
+    }
+    return r;
+}
+inline void cross_product(const vects& A, const vects& B, vects& C) {
+    for (size_t i = 0; i < A.n(); i++) {
+        const REAL x1 = A[i][0], y1 = A[i][1], z1 = A[i][2], x2 = B[i][0], y2 = B[i][1], z2 = B[i][2];
+        C[i][0] = y1 * z2 - z1 * y2;
+        C[i][1] = z1 * x2 - x1 * z2;
+        C[i][2] = x1 * y2 - y1 * x2;
+    }
+}
+
+inline REAL sign_tol(REAL v) { return (v > ROOT_TOLERANCE) ? +1.0f : (v < -ROOT_TOLERANCE) ? -1.0f : 0.0f; }
+
+inline scalars eval_on(const implicit_function& object, const vects& X, const std::vector<int>& idx) {
+    vects xa(idx.size());
+    for (size_t j = 0; j < idx.size(); j++) { xa[j][0] = X[idx[j]][0]; xa[j][1] = X[idx[j]][1]; xa[j][2] = X[idx[j]][2]; }
+    scalars f(idx.size());
+    if (!idx.empty()) object.eval_implicit(xa, &f);
+    return f;
+}
+
+inline void bisection(const implicit_function& object, vects& res, vects& x1, vects& x2, Stats* st) {
+    int n = (int)x1.n();
+    std::vector<int> active(n);
+    for (int i = 0; i < n; i++) active[i] = i;
+    int iteration = 1;
+    while (!active.empty()) {
+        int m = (int)active.size();
+        vects mid(m);
+        for (int i = 0; i < m; i++)
+            for (int d = 0; d < 3; d++) mid[i][d] = (x1[active[i]][d] + x2[active[i]][d]) / 2.;
+        scalars v(m);
+        object.eval_implicit(mid, &v);
+        std::vector<int> next;
+        for (int i = 0; i < m; i++) {
+            int g = active[i];
+            if (std::abs(v[i]) <= ROOT_TOLERANCE || iteration >= BISECTION_MAX_ITER) {
+                if (std::abs(v[i]) > ROOT_TOLERANCE && st) st->bisection_capped++;
+                for (int d = 0; d < 3; d++) res[g][d] = mid[i][d];
+            } else {
+                if (v[i] > +ROOT_TOLERANCE) for (int d = 0; d < 3; d++) x2[g][d] = mid[i][d];
+                if (v[i] < -ROOT_TOLERANCE) for (int d = 0; d < 3; d++) x1[g][d] = mid[i][d];
+                next.push_back(g);
+            }
+        }
+        active.swap(next);
+        iteration++;
+    }
+}
+
+inline void set_centers_on_surface(const implicit_function& object, const vects& centroids, const REAL average_edge,
+                                   const vects& facet_normals, vects& centroids_output, Stats* st) {
+    const int max_iter = 20;
+    const vects& X = centroids;
+    REAL max_dist = average_edge;
+    const int n = (int)X.n();
+    scalars fc_a(n);
+    object.eval_implicit(centroids, &fc_a);
+    vects g_a(n);
+    object.eval_gradient(X, &g_a);
+    normalise_inplace(g_a, min_gradient_len);
+    scalars signs_c(n);
+    for (int i = 0; i < n; i++) signs_c[i] = sign_tol(fc_a[i]);
+    for (int i = 0; i < n; i++)
+        if (signs_c[i] < 0.0) { g_a[i][0] = -g_a[i][0]; g_a[i][1] = -g_a[i][1]; g_a[i][2] = -g_a[i][2]; }
+    vects dx0(n);
+    for (int i = 0; i < n; i++) {
+        dx0[i][0] = -g_a[i][0] * signs_c[i];
+        dx0[i][1] = -g_a[i][1] * signs_c[i];
+        dx0[i][2] = -g_a[i][2] * signs_c[i];
+    }
+    const REAL length_factor = max_dist;
+    REAL initial_step_size = max_dist * 1.0;
+    REAL scale_min_len = 1.0;
+    std::vector<REAL> alpha_full = make_alpha_list(initial_step_size, 0.001 * scale_min_len, max_dist, max_iter);
+    if (alpha_full.size() < 10) { fprintf(stderr, "oracle: alpha list shorter than 10 (average edge %g too small)\n", (double)average_edge); abort(); }
+    std::vector<REAL> alpha10(alpha_full.begin(), alpha_full.begin() + 10);
+
+    vects best(n);
+    for (int i = 0; i < n; i++) { best[i][0] = -10.0; best[i][1] = -10.0; best[i][2] = -10.0; }
+    std::vector<int> still(n);
+    for (int i = 0; i < n; i++) still[i] = i;
+    std::vector<char> already(n, 0);
+    vects dxc(n);
+    for (int iter_type = 0; iter_type < 7 && !still.empty(); iter_type++) {
+        const std::vector<REAL>* alphas = &alpha10;
+        if (iter_type == 0) { dxc = dx0; alphas = &alpha_full; }
+        else if (iter_type == 1) { dxc = facet_normals; }
+        else if (iter_type == 2) {
+            vects perturb = make_random_pm1(n, 0.000001);     // add_inplace takes copies: perturb stays pure noise
+            vects z(n);
+            cross_product(facet_normals, perturb, z);
+            normalize_1111(z);
+            dxc = z;
+        } else if (iter_type == 3) {
+            vects z2(n);                                       // replace_zero_normals...: never triggers on unit normals
+            cross_product(facet_normals, dxc, z2);
+            normalise_inplace(z2, min_gradient_len);
+            dxc = z2;
+        } else {
+            int dimi = iter_type - 4;
+            for (int i = 0; i < n; i++) { dxc[i][0] = dimi == 0; dxc[i][1] = dimi == 1; dxc[i][2] = dimi == 2; }
+        }
+        for (size_t ai = 0; ai < alphas->size() && !still.empty(); ai++) {
+            REAL alpha = (*alphas)[ai];
+            REAL c = (length_factor * alpha) * 4.0 / 4.0;
+            vects x1(n);
+            for (int j = 0; j < n; j++) {
+                x1[j][0] = X[j][0] + c * dxc[j][0];
+                x1[j][1] = X[j][1] + c * dxc[j][1];
+                x1[j][2] = X[j][2] + c * dxc[j][2];
+            }
+            scalars f_a = eval_on(object, x1, still);
+            std::vector<int> next;
+            for (size_t k = 0; k < still.size(); k++) {
+                int j = still[k];
+                bool success = (sign_tol(f_a[k]) * signs_c[j]) <= 0;
+                if (success) {
+                    best[j][0] = x1[j][0]; best[j][1] = x1[j][1]; best[j][2] = x1[j][2];
+                    already[j] = 1;
+                    if (st) st->projection_by_type[iter_type]++;
+                } else {
+                    next.push_back(j);
+                }
+            }
+            still.swap(next);
+        }
+    }
+    if (st) st->projection_failed += (long)still.size();
+    for (int j : still) { best[j][0] = centroids[j][0]; best[j][1] = centroids[j][1]; best[j][2] = centroids[j][2]; }
+
+    scalars f2(n);
+    object.eval_implicit(best, &f2);
+    std::vector<char> zeros1(n), zeros12(n);
+    for (int i = 0; i < n; i++) {
+        bool z2 = std::abs(f2[i]) <= ROOT_TOLERANCE;
+        zeros1[i] = std::abs(fc_a[i]) <= ROOT_TOLERANCE;
+        if (zeros1[i]) { best[i][0] = centroids[i][0]; best[i][1] = centroids[i][1]; best[i][2] = centroids[i][2]; }
+        zeros12[i] = z2 || zeros1[i];
+    }
+    std::vector<int> rel;
+    for (int i = 0; i < n; i++)
+        if (already[i] && !zeros12[i]) rel.push_back(i);
+    int m = (int)rel.size();
+    vects x1r(m), x2r(m);
+    for (int i = 0; i < m; i++)
+        for (int d = 0; d < 3; d++) { x1r[i][d] = centroids[rel[i]][d]; x2r[i][d] = best[rel[i]][d]; }
+    scalars f2r(m);
+    if (m) object.eval_implicit(x2r, &f2r);
+    for (int i = 0; i < m; i++)
+        if (f2r[i] < -ROOT_TOLERANCE)
+            for (int d = 0; d < 3; d++) std::swap(x2r[i][d], x1r[i][d]);
+    vects xb(m);
+    bisection(object, xb, x1r, x2r, st);
+    if (st) st->bisected += m;
+    vects out = centroids;
+    for (int i = 0; i < m; i++)
+        for (int d = 0; d < 3; d++) out[rel[i]][d] = xb[i][d];
+    for (int i = 0; i < n; i++)
+        if (zeros12[i])
+            for (int d = 0; d < 3; d++) out[i][d] = best[i][d];
+    centroids_output = out;
+}
+
+// ---- qem.hpp ----------------------------------------------------------------------------------
+// eigen-decomposition of a symmetric 3x3 by cyclic Jacobi, double accumulation of rotations kept in
+// float like the data; eigenvalues sorted descending.
+inline void sym_eig3(const REAL Ain[3][3], REAL w[3], REAL V[3][3]) {
+    REAL A[3][3];
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) { A[i][j] = Ain[i][j]; V[i][j] = (i == j) ? 1.0f : 0.0f; }
+    for (int sweep = 0; sweep < 12; sweep++) {
+        REAL off = std::fabs(A[0][1]) + std::fabs(A[0][2]) + std::fabs(A[1][2]);
+        if (off == 0.0f) break;
+        for (int p = 0; p < 2; p++)
+            for (int q = p + 1; q < 3; q++) {
+                if (A[p][q] == 0.0f) continue;
+                REAL theta = (A[q][q] - A[p][p]) / (2.0f * A[p][q]);
+                REAL t = (theta >= 0 ? 1.0f : -1.0f) / (std::fabs(theta) + std::sqrt(theta * theta + 1.0f));
+                REAL c = 1.0f / std::sqrt(t * t + 1.0f), s = t * c;
+                for (int k = 0; k < 3; k++) {
+                    REAL akp = A[k][p], akq = A[k][q];
+                    A[k][p] = c * akp - s * akq;
+                    A[k][q] = s * akp + c * akq;
+                }
+                for (int k = 0; k < 3; k++) {
+                    REAL apk = A[p][k], aqk = A[q][k];
+                    A[p][k] = c * apk - s * aqk;
+                    A[q][k] = s * apk + c * aqk;
+                }
+                for (int k = 0; k < 3; k++) {
+                    REAL vkp = V[k][p], vkq = V[k][q];
+                    V[k][p] = c * vkp - s * vkq;
+                    V[k][q] = s * vkp + c * vkq;
+                }
+            }
+    }
+    for (int i = 0; i < 3; i++) w[i] = A[i][i];
+    for (int i = 0; i < 2; i++)
+        for (int j = i + 1; j < 3; j++)
+            if (w[j] > w[i]) {
+                std::swap(w[i], w[j]);
+                for (int k = 0; k < 3; k++) std::swap(V[k][i], V[k][j]);
+            }
+}
+
+inline void vertex_apply_qem(vects& verts, const vects& centroids, const umbrella_t& nb, const vects& cn,
+                             REAL maximum_displacement_distance) {
+    const REAL tau = 680.0;
+    const REAL svd_threshold = 1.0 / tau;
+    int nverts = (int)verts.n();
+    for (int vi = 0; vi < nverts; vi++) {
+        REAL o[3] = {verts[vi][0], verts[vi][1], verts[vi][2]};
+        REAL A[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}}, b[3] = {0, 0, 0};
+        for (int ni : nb[vi]) {                                                     // get_A_b :256-316
+            REAL Nx = cn[ni][0], Ny = cn[ni][1], Nz = cn[ni][2];
+            REAL Px = centroids[ni][0] - o[0], Py = centroids[ni][1] - o[1], Pz = centroids[ni][2] - o[2];
+            REAL nn00 = Nx * Nx, nn01 = Nx * Ny, nn02 = Nx * Nz, nn11 = Ny * Ny, nn12 = Ny * Nz, nn22 = Nz * Nz;
+            A[0][0] += nn00; A[0][1] += nn01; A[0][2] += nn02;
+            A[1][0] += nn01; A[1][1] += nn11; A[1][2] += nn12;
+            A[2][2] += nn22; A[2][0] += nn02; A[2][1] += nn12;
+            b[0] -= nn00 * Px + nn01 * Py + nn02 * Pz;
+            b[1] -= nn01 * Px + nn11 * Py + nn12 * Pz;
+            b[2] -= nn02 * Px + nn12 * Py + nn22 * Pz;
+        }
+        REAL S[3], V[3][3];
+        sym_eig3(A, S, V);
+        for (int i = 0; i < 3; i++) if (S[i] < 0) S[i] = 0;                        // singular values of a PSD matrix
+        // Eigen rank(): sigma_i >= max(sigma_0 * threshold, realmin)
+        REAL thr = std::max(S[0] * svd_threshold, std::numeric_limits<REAL>::min());
+        int rank = 0;
+        while (rank < 3 && !(S[rank] < thr)) rank++;
+        REAL nx[3] = {o[0], o[1], o[2]};
+        REAL acc[3] = {0, 0, 0};
+        for (int i = 0; i < rank; i++) {
+            REAL utb = -(V[0][i] * b[0] + V[1][i] * b[1] + V[2][i] * b[2]);
+            REAL y = utb / S[i];
+            for (int d = 0; d < 3; d++) acc[d] += V[d][i] * y;
+        }
+        for (int d = 0; d < 3; d++) nx[d] = acc[d] + o[d];
+        if (maximum_displacement_distance > 0) {
+            REAL dx = nx[0] - verts[vi][0], dy = nx[1] - verts[vi][1], dz = nx[2] - verts[vi][2];
+            REAL dist2 = norm_squared(dx, dy, dz);
+            if (dist2 <= maximum_displacement_distance * maximum_displacement_distance) {
+                verts[vi][0] = nx[0]; verts[vi][1] = nx[1]; verts[vi][2] = nx[2];
+            } else {
+                REAL dist = std::sqrt(dist2);
+                REAL displacement_len = maximum_displacement_distance * 1.5;
+                if (displacement_len > dist) displacement_len = dist;
+                verts[vi][0] += dx / dist * displacement_len;
+                verts[vi][1] += dy / dist * displacement_len;
+                verts[vi][2] += dz / dist * displacement_len;
+            }
+        } else {
+            verts[vi][0] = nx[0]; verts[vi][1] = nx[1]; verts[vi][2] = nx[2];
+        }
+    }
+}
+
+struct ProjectionDebug {           // what the reference keeps in point_set_set (pre/post_p_centroids)
+    vects centroids_before, centroids_after, centroid_normals;
+    REAL average_edge = 0;
+};
+
+inline void centroids_projection(const implicit_function& object, std::vector<REAL>& result_verts, const std::vector<int>& faces,
+                                 bool enable_qem, Stats* st, ProjectionDebug* dbg = nullptr) {
+    int nv = (int)(result_verts.size() / 3), nf = (int)(faces.size() / 3);
+    vects verts(nv);
+    verts.d = result_verts;
+    REAL average_edge = compute_average_edge_length(faces, verts);
+    vects centroids(nf);
+    compute_centroids(faces, verts, centroids);
+    if (dbg) { dbg->centroids_before = centroids; dbg->average_edge = average_edge; }
+    vects facet_normals = produce_facet_normals(faces, verts, true);
+    vects projected(nf);
+    set_centers_on_surface(object, centroids, average_edge, facet_normals, projected, st);
+    centroids = projected;
+    umbrella_t nb = make_neighbour_faces_of_vertex(faces, nv);
+    vects cg(nf);
+    object.eval_gradient(centroids, &cg);
+    normalize_1111(cg);
+    if (dbg) { dbg->centroids_after = centroids; dbg->centroid_normals = cg; }
+    if (enable_qem) {
+        vertex_apply_qem(verts, centroids, nb, cg, average_edge);
+        result_verts = verts.d;
+    }
+}
+
+}  // namespace oracle

@@ -1,0 +1,472 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see ojson.hpp header).
+//
+// CPU restatement of the reference's implicit-function tree, statement by statement,
+// in binary32 with the reference's evaluation order (compile with -ffp-contract=off).
+// Paths are relative to /root/reference/js_iteration_2/.
+//   invert_matrix            basic_functions.hpp:77-128   (uBLAS lu_factorize/lu_substitute restated;
+//                            Boost is not in this image, so this elimination order DEFINES the oracle)
+//   matrix_vector_product    basic_functions.hpp:140-177
+//   prepare_inner_vectors    basic_functions.hpp:361-379
+//   egg                      implicit_function/egg.hpp:93-128
+//   scylinder                implicit_function/scylinder.hpp:97-176
+//   cube                     implicit_function/cube.hpp:199-210 (analytic), :215-270 (HEAD SDF grid), :291-315 (gradient)
+//   scone                    implicit_function/scone.hpp:81-166
+//   meta_ball_Rydgard        implicit_function/meta_balls_Rydgard.hpp:49-59,89-144,292-432
+//   transformed_union/intersection/subtract  implicit_function/transformed_*.hpp
+//   object_factory           object_factory.hpp:21-30,56-173,537-673,741-758
+#pragma once
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <memory>
+#include <string>
+#include <vector>
+#include "ojson.hpp"
+
+namespace oracle {
+
+typedef float REAL;
+
+struct vects {            // N x 3, AoS (boost::multi_array<REAL,2> in the reference)
+    std::vector<REAL> d;
+    vects() {}
+    explicit vects(size_t n) : d(n * 3, 0.0f) {}
+    size_t n() const { return d.size() / 3; }
+    REAL* operator[](size_t i) { return &d[i * 3]; }
+    const REAL* operator[](size_t i) const { return &d[i * 3]; }
+};
+typedef std::vector<REAL> scalars;
+
+// ---- basic_functions.hpp:77-128 -------------------------------------------------------------
+// Returns false (and leaves inv untouched) when a zero pivot is met, like lu_factorize != 0.
+inline bool invert_matrix(const REAL in12[12], REAL inv12[12]) {
+    REAL A[4][4], B[4][4];
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 4; j++) A[i][j] = in12[i * 4 + j];
+    A[3][0] = 0.f; A[3][1] = 0.f; A[3][2] = 0.f; A[3][3] = 1.f;
+    int pm[4] = {0, 1, 2, 3};
+    int singular = 0;
+    // lu_factorize: partial pivoting, reciprocal scaling, rank-1 trailing update
+    for (int i = 0; i < 4; i++) {
+        int p = i;
+        REAL best = std::fabs(A[i][i]);
+        for (int k = i + 1; k < 4; k++) {             // index_norm_inf: first maximum
+            REAL a = std::fabs(A[k][i]);
+            if (a > best) { best = a; p = k; }
+        }
+        if (A[p][i] != 0.0f) {
+            if (p != i) {
+                pm[i] = p;
+                for (int j = 0; j < 4; j++) std::swap(A[i][j], A[p][j]);
+            }
+            REAL r = 1.0f / A[i][i];
+            for (int k = i + 1; k < 4; k++) A[k][i] *= r;
+        } else if (singular == 0) {
+            singular = i + 1;
+        }
+        for (int k = i + 1; k < 4; k++)
+            for (int j = i + 1; j < 4; j++) A[k][j] -= A[k][i] * A[i][j];
+    }
+    if (singular != 0) return false;
+    for (int i = 0; i < 4; i++)
+        for (int j = 0; j < 4; j++) B[i][j] = (i == j) ? 1.0f : 0.0f;
+    // lu_substitute: swap_rows(pm, B)
+    for (int i = 0; i < 4; i++)
+        if (pm[i] != i)
+            for (int j = 0; j < 4; j++) std::swap(B[i][j], B[pm[i]][j]);
+    // inplace_solve(unit_lower): column-oriented forward substitution
+    for (int n = 0; n < 4; n++)
+        for (int l = 0; l < 4; l++) {
+            REAL t = B[n][l];
+            if (t != 0.0f)
+                for (int m = n + 1; m < 4; m++) B[m][l] -= A[m][n] * t;
+        }
+    // inplace_solve(upper): column-oriented back substitution
+    for (int n = 3; n >= 0; n--)
+        for (int l = 3; l >= 0; l--) {
+            REAL t = B[n][l] /= A[n][n];
+            if (t != 0.0f)
+                for (int m = n - 1; m >= 0; m--) B[m][l] -= A[m][n] * t;
+        }
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 4; j++) inv12[i * 4 + j] = B[i][j];
+    return true;
+}
+
+// ---- basic_functions.hpp:140-177 ------------------------------------------------------------
+inline void matrix_vector_product(const REAL m[12], vects& v) {
+    for (size_t i = 0, n = v.n(); i < n; ++i) {
+        const REAL x = v[i][0], y = v[i][1], z = v[i][2];
+        v[i][0] = m[0] * x + m[1] * y + m[2] * z + m[3];
+        v[i][1] = m[4] * x + m[5] * y + m[6] * z + m[7];
+        v[i][2] = m[8] * x + m[9] * y + m[10] * z + m[11];
+    }
+}
+inline vects prepare_inner_vectors(const REAL inv[12], const vects& x) {
+    vects c = x;
+    matrix_vector_product(inv, c);
+    return c;
+}
+
+// how "cube" evaluates f: HEAD looks up a hard-coded SDF grid (cube.hpp:215-270), the
+// analytic six-plane form is what the class name, its gradient and its bounding box mean
+// (cube.hpp:199-210, commented out at HEAD).  SURVEY F3.
+enum CubeMode { CUBE_ANALYTIC = 0, CUBE_HEAD_SDFGRID = 1 };
+
+struct SdfGrid {   // supplied by the test harness from a fixture (never compiled in)
+    int nx = 0, ny = 0, nz = 0;
+    float h = 0, ox = 0, oy = 0, oz = 0;
+    std::vector<float> v;
+};
+
+struct Env {
+    CubeMode cube_mode = CUBE_ANALYTIC;
+    const SdfGrid* sdf = nullptr;
+};
+
+struct implicit_function {
+    REAL M[12], Minv[12];
+    virtual ~implicit_function() {}
+    virtual void eval_implicit(const vects& x, scalars* f) const = 0;
+    virtual void eval_gradient(const vects& x, vects* g) const = 0;
+    void set_matrix(const REAL m[12]) {
+        for (int i = 0; i < 12; i++) { M[i] = m[i]; Minv[i] = 0.0f; }   // reference: uninitialised heap if singular
+        invert_matrix(M, Minv);
+    }
+    // (M^-1)^T_{3x3} g, e.g. egg.hpp:124-126
+    void back(REAL g0, REAL g1, REAL g2, REAL* out) const {
+        out[0] = Minv[0] * g0 + Minv[4] * g1 + Minv[8] * g2;
+        out[1] = Minv[1] * g0 + Minv[5] * g1 + Minv[9] * g2;
+        out[2] = Minv[2] * g0 + Minv[6] * g1 + Minv[10] * g2;
+    }
+};
+
+inline REAL squared(REAL x) { return x * x; }
+inline REAL norm_squared(REAL x, REAL y, REAL z) { return x * x + y * y + z * z; }
+
+// ---- egg.hpp ----------------------------------------------------------------------------------
+struct egg : implicit_function {
+    REAL a = 0.5f, b = 0.5f, c = 0.5f, x0 = 0.f, y0 = 0.f, z0 = 0.f;
+    explicit egg(const REAL m[12]) { set_matrix(m); }
+    void eval_implicit(const vects& x, scalars* f) const override {
+        vects lx = x;
+        matrix_vector_product(Minv, lx);
+        for (size_t i = 0; i < lx.n(); i++)
+            (*f)[i] = 1 - norm_squared((lx[i][0] - x0) / a, (lx[i][1] - y0) / b, (lx[i][2] - z0) / c);
+    }
+    void eval_gradient(const vects& x, vects* out) const override {
+        vects lx = x;
+        matrix_vector_product(Minv, lx);
+        const REAL a2 = squared(a), b2 = squared(b), c2 = squared(c);
+        for (size_t i = 0; i < lx.n(); i++) {
+            REAL g0 = -2. * (lx[i][0] - x0) / a2;      // double intermediate, single rounding (Appendix E)
+            REAL g1 = -2. * (lx[i][1] - y0) / b2;
+            REAL g2 = -2. * (lx[i][2] - z0) / c2;
+            back(g0, g1, g2, (*out)[i]);
+        }
+    }
+};
+
+// ---- scylinder.hpp ----------------------------------------------------------------------------
+struct scylinder : implicit_function {
+    REAL x = 0.f, y = 0.f, z = -0.5f, w[3] = {0.f, 0.f, 1.f}, c_len = 1.0f, radius_u = 0.5f;
+    explicit scylinder(const REAL m[12]) { set_matrix(m); }
+    void eval_implicit(const vects& xx, scalars* f) const override {
+        vects lx = xx;
+        matrix_vector_product(Minv, lx);
+        for (size_t i = 0; i < lx.n(); i++) {
+            REAL i0 = lx[i][0], i1 = lx[i][1], i2 = lx[i][2];
+            REAL w0 = w[0], w1 = w[1], w2 = w[2];
+            REAL t0 = (i0 - x) * w0 + (i1 - y) * w1 + (i2 - z) * w2;
+            REAL t1 = c_len - t0;
+            REAL r_ = radius_u - std::sqrt((i0 - w0 * t0 - x) * (i0 - w0 * t0 - x) +
+                                           (i1 - w1 * t0 - y) * (i1 - w1 * t0 - y) + (i2 - w2 * t0 - z) * (i2 - w2 * t0 - z));
+            (*f)[i] = std::min(t0, std::min(t1, r_));
+        }
+    }
+    void eval_gradient(const vects& xx, vects* out) const override {
+        vects lx = xx;
+        matrix_vector_product(Minv, lx);
+        for (size_t i = 0; i < lx.n(); i++) {
+            REAL i0 = lx[i][0], i1 = lx[i][1], i2 = lx[i][2];
+            REAL w0 = w[0], w1 = w[1], w2 = w[2];
+            REAL t0 = (i0 - x) * w0 + (i1 - y) * w1 + (i2 - z) * w2;
+            REAL t1 = c_len - t0;
+            REAL r_ = radius_u - std::sqrt((i0 - w0 * t0 - x) * (i0 - w0 * t0 - x) +
+                                           (i1 - w1 * t0 - y) * (i1 - w1 * t0 - y) + (i2 - w2 * t0 - z) * (i2 - w2 * t0 - z));
+            bool c_t0 = 0, c_t1 = 0, c_r = 0;
+            if (t0 <= t1 && t0 <= r_) c_t0 = 1;
+            if (t1 <= t0 && t1 <= r_) c_t1 = 1;
+            if (r_ <= t0 && r_ <= t1) c_r = 1;
+            REAL g0 = c_t0 * w0 + c_t1 * (-w0) + c_r * (w0 * t0 + x - i0);
+            REAL g1 = c_t0 * w1 + c_t1 * (-w1) + c_r * (w1 * t0 + y - i1);
+            REAL g2 = c_t0 * w2 + c_t1 * (-w2) + c_r * (w2 * t0 + z - i2);
+            back(g0, g1, g2, (*out)[i]);
+        }
+    }
+};
+
+// ---- cube.hpp ---------------------------------------------------------------------------------
+struct cube : implicit_function {
+    REAL p[18];
+    REAL x = 0.f, y = 0.f, z = 0.f;
+    Env env;
+    cube(const REAL m[12], const Env& e) : env(e) {
+        for (int i = 0; i < 18; i++) p[i] = 0;
+        p[0] = 0.5f; p[3] = -0.5f; p[7] = 0.5f; p[10] = -0.5f; p[14] = 0.5f; p[17] = -0.5f;
+        set_matrix(m);
+    }
+    // one plane term of cube.hpp:204-209 / :296-300, formed in double like the source
+    double plane(int k, REAL i1, REAL i2, REAL i3) const {
+        return (i1 - x - p[0 + k * 3]) * p[0 + k * 3] * (-2.) + (i2 - y - p[1 + k * 3]) * p[1 + k * 3] * (-2.) +
+               (i3 - z - p[2 + k * 3]) * p[2 + k * 3] * (-2.);
+    }
+    void eval_implicit(const vects& xx, scalars* f) const override {
+        vects lx = xx;
+        matrix_vector_product(Minv, lx);
+        for (size_t i = 0; i < lx.n(); i++) {
+            if (env.cube_mode == CUBE_ANALYTIC) {
+                REAL i1 = lx[i][0], i2 = lx[i][1], i3 = lx[i][2];
+                // min(...) of the six plane terms; every term is exactly representable in binary32
+                REAL m5 = (REAL)plane(5, i1, i2, i3);
+                REAL m4 = std::min((REAL)plane(4, i1, i2, i3), m5);
+                REAL m3 = std::min((REAL)plane(3, i1, i2, i3), m4);
+                REAL m2 = std::min((REAL)plane(2, i1, i2, i3), m3);
+                REAL m1 = std::min((REAL)plane(1, i1, i2, i3), m2);
+                (*f)[i] = std::min((REAL)plane(0, i1, i2, i3), m1);
+            } else {
+                const SdfGrid& g = *env.sdf;
+                const float px = lx[i][0], py = lx[i][1], pz = lx[i][2];
+                float res = 10000;
+                if (g.ox + g.h * g.nx < px || px < g.ox) {
+                } else if (g.oy + g.h * g.ny < py || py < g.oy) {
+                } else if (g.oz + g.h * g.nz < pz || pz < g.oz) {
+                } else {
+                    int xc = (px - g.ox) / g.h, yc = (py - g.oy) / g.h, zc = (pz - g.oz) / g.h;
+                    float xl = g.ox + xc * g.h, yl = g.oy + yc * g.h, zl = g.oz + zc * g.h;
+                    float xd = (px - xl) / g.h, yd = (py - yl) / g.h, zd = (pz - zl) / g.h;
+                    auto at = [&](int a, int b, int c) {
+                        size_t idx = (size_t)a + (size_t)b * g.nx + (size_t)c * g.nx * g.ny;
+                        return idx < g.v.size() ? g.v[idx] : 0.0f;   // reference reads past the table here (UB)
+                    };
+                    float c00 = at(xc, yc, zc) * (1 - xd) + at(xc + 1, yc, zc) * xd;
+                    float c01 = at(xc, yc, zc + 1) * (1 - xd) + at(xc + 1, yc, zc + 1) * xd;
+                    float c10 = at(xc, yc + 1, zc) * (1 - xd) + at(xc + 1, yc + 1, zc) * xd;
+                    float c11 = at(xc, yc + 1, zc + 1) * (1 - xd) + at(xc + 1, yc + 1, zc + 1) * xd;
+                    float c0 = c00 * (1 - yd) + c10 * yd;
+                    float c1 = c01 * (1 - yd) + c11 * yd;
+                    res = c0 * (1 - zd) + c1 * (zd);
+                }
+                (*f)[i] = -res;
+            }
+        }
+    }
+    void eval_gradient(const vects& xx, vects* out) const override {
+        vects lx = xx;
+        matrix_vector_product(Minv, lx);
+        for (size_t i = 0; i < lx.n(); i++) {
+            REAL i1 = lx[i][0], i2 = lx[i][1], i3 = lx[i][2];
+            int index = 0;
+            REAL mn = plane(0, i1, i2, i3);
+            for (int k = 0; k < 6; k++)
+                if (plane(k, i1, i2, i3) < mn) { index = k; mn = plane(k, i1, i2, i3); }
+            back(-p[index * 3 + 0], -p[index * 3 + 1], -p[index * 3 + 2], (*out)[i]);
+        }
+    }
+};
+
+// ---- scone.hpp --------------------------------------------------------------------------------
+struct scone : implicit_function {
+    REAL h = 1.f, r1 = 0.0f, r2 = 0.5f, x0 = 0.f, y0 = 0.f, z0 = 0.5f;
+    explicit scone(const REAL m[12]) { set_matrix(m); }
+    void eval_implicit(const vects& xx, scalars* f) const override {
+        const vects lx = prepare_inner_vectors(Minv, xx);
+        const REAL a2 = squared(r2 / h);
+        for (size_t i = 0; i < lx.n(); i++) {
+            REAL x = lx[i][0], y = lx[i][1], z = lx[i][2];
+            REAL fv = -std::sqrt((x - x0) * (x - x0) + (y - y0) * (y - y0)) + std::sqrt((z - z0) * (z - z0) * a2);
+            REAL uperside = -(z - z0) - r1;
+            REAL lowerside = (z - z0) + h;
+            (*f)[i] = std::min(fv, std::min(uperside, lowerside));
+        }
+    }
+    void eval_gradient(const vects& xx, vects* out) const override {
+        const vects lx = prepare_inner_vectors(Minv, xx);
+        const REAL a2 = squared(r2 / h);
+        for (size_t i = 0; i < lx.n(); i++) {
+            REAL x = lx[i][0], y = lx[i][1], z = lx[i][2];
+            REAL fv = -(x - x0) * (x - x0) / a2 - (y - y0) * (y - y0) / a2 + (z - z0) * (z - z0);
+            REAL uperside = -(z - z0) - r1;
+            REAL lowerside = (z - z0) + h;
+            REAL gx, gy, gz;
+            if (uperside < fv && uperside < lowerside) { gx = 0.; gy = 0.; gz = -1.; }
+            else if (lowerside < fv && lowerside < uperside) { gx = 0.; gy = 0.; gz = +1.; }
+            else { gx = -2 * (x - x0) / a2; gy = -2 * (y - y0) / a2; gz = 2 * (z - z0); }
+            back(gx, gy, gz, (*out)[i]);
+        }
+    }
+};
+
+// ---- meta_balls_Rydgard.hpp -------------------------------------------------------------------
+struct meta_balls : implicit_function {
+    struct ball_t { REAL ballx, bally, ballz, strength, subtract, scale; };
+    std::vector<ball_t> balls;
+    meta_balls(const REAL m[12], int num_blobs, REAL time, REAL scale) {
+        int numblobs = num_blobs;
+        for (int ball_i = 0; ball_i < numblobs; ball_i++) {          // :49-59, host double math
+            REAL x0 = 0.5, y0 = 0.5, z0 = 0.5;
+            REAL D = 1;
+            REAL ballx = sin(ball_i + 1.26 * time * (1.03 + 0.5 * cos(0.21 * ball_i))) * 0.27 * D + 0.5 - x0;
+            REAL bally = std::abs(cos(ball_i + 1.12 * time * cos(1.22 + 0.1424 * ball_i))) * 0.77 * D - y0;
+            REAL ballz = cos(ball_i + 1.32 * time * 0.1 * sin((0.92 + 0.53 * ball_i))) * 0.27 * D + 0.5 - z0;
+            REAL subtract = 12;
+            REAL strength = 1.2 / ((sqrt(numblobs) - 1) / 4 + 1);
+            balls.push_back(ball_t{ballx, bally, ballz, strength, subtract, scale});
+        }
+        set_matrix(m);
+    }
+    void eval_implicit(const vects& x, scalars* f) const override {
+        for (size_t i = 0; i < x.n(); i++) (*f)[i] = 0.0;
+        const vects lx = prepare_inner_vectors(Minv, x);
+        for (const ball_t& b : balls)
+            for (size_t i = 0; i < lx.n(); i++) {
+                REAL fx = lx[i][0] - b.ballx; REAL fx2 = fx * fx;
+                REAL fy = lx[i][1] - b.bally; REAL fy2 = fy * fy;
+                REAL fz = lx[i][2] - b.ballz; REAL fz2 = fz * fz;
+                REAL h = ((REAL)0.000001 + fx2 + fy2 + fz2);
+                REAL hinv = 1.0 / h;
+                REAL val = b.strength * hinv - b.subtract;
+                (*f)[i] += val / 100;
+            }
+    }
+    void eval_gradient(const vects& x, vects* out) const override {
+        const vects lx = prepare_inner_vectors(Minv, x);
+        for (size_t i = 0; i < lx.n(); i++) {
+            REAL gx = 0, gy = 0, gz = 0;
+            for (const ball_t& b : balls) {
+                REAL fz = lx[i][2] - b.ballz; REAL fz2 = fz * fz;
+                REAL fy = lx[i][1] - b.bally; REAL fy2 = fy * fy;
+                REAL fx = lx[i][0] - b.ballx; REAL fx2 = fx * fx;
+                REAL h = 0.000001 + fx2 + fy2 + fz2;          // double literal: summed in double (:118-136)
+                REAL hinv = 1.0 / h;
+                REAL gradx = b.strength * (-2 * fx * hinv * hinv) / 100;
+                REAL grady = b.strength * (-2 * fy * hinv * hinv) / 100;
+                REAL gradz = b.strength * (-2 * fz * hinv * hinv) / 100;
+                gx += gradx; gy += grady; gz += gradz;
+            }
+            back(gx, gy, gz, (*out)[i]);
+        }
+    }
+};
+
+// ---- transformed_union / intersection / subtract ----------------------------------------------
+enum CsgOp { OP_UNION, OP_INTERSECTION, OP_SUBTRACT };
+struct csg_node : implicit_function {
+    CsgOp op;
+    const implicit_function* a;
+    const implicit_function* b;
+    csg_node(CsgOp op_, const implicit_function* a_, const implicit_function* b_, const REAL m[12]) : op(op_), a(a_), b(b_) {
+        set_matrix(m);
+    }
+    void eval_implicit(const vects& x, scalars* f) const override {
+        const size_t n = x.n();
+        const vects lx = prepare_inner_vectors(Minv, x);
+        scalars f1(n), f2(n);
+        a->eval_implicit(lx, &f1);
+        b->eval_implicit(lx, &f2);
+        for (size_t i = 0; i < n; i++) {
+            switch (op) {
+                case OP_UNION:        (*f)[i] = (f1[i] > f2[i]) ? f1[i] : f2[i]; break;     // transformed_union.hpp:47
+                case OP_INTERSECTION: (*f)[i] = (f1[i] > f2[i]) ? f2[i] : f1[i]; break;     // transformed_intersection.hpp:49
+                case OP_SUBTRACT:     (*f)[i] = (f1[i] < -f2[i]) ? f1[i] : -f2[i]; break;   // transformed_subtract.hpp:52
+            }
+        }
+    }
+    void eval_gradient(const vects& x, vects* out) const override {
+        const size_t n = x.n();
+        scalars f1(n), f2(n);
+        vects g1(n), g2(n);
+        const vects lx = prepare_inner_vectors(Minv, x);
+        a->eval_implicit(lx, &f1);
+        b->eval_implicit(lx, &f2);
+        a->eval_gradient(lx, &g1);
+        b->eval_gradient(lx, &g2);
+        if (op == OP_SUBTRACT)
+            for (size_t i = 0; i < n * 3; i++) g2.d[i] = -g2.d[i];
+        for (size_t i = 0; i < n; i++) {
+            bool first;
+            switch (op) {
+                case OP_UNION:        first = (f1[i] > f2[i]); break;
+                case OP_INTERSECTION: first = !(f1[i] > f2[i]); break;
+                default:              first = (f1[i] < -f2[i]); break;
+            }
+            const REAL* g = first ? g1[i] : g2[i];
+            back(g[0], g[1], g[2], (*out)[i]);
+        }
+    }
+};
+
+// ---- object_factory.hpp -----------------------------------------------------------------------
+struct Shape {                       // owns every node (object_collector.hpp:10-32)
+    std::vector<std::unique_ptr<implicit_function>> pool;
+    const implicit_function* root = nullptr;
+    template <class T> T* keep(T* p) { pool.emplace_back(p); return p; }
+};
+
+inline void getMatrix12(REAL m[12], const ojson::Node& node) {        // :21-30 (reads 16, UB; we stop at 12)
+    const ojson::Node* mat = node.child("matrix");
+    if (!mat) { fprintf(stderr, "oracle: node without \"matrix\"\n"); abort(); }
+    int i = 0;
+    for (auto& kv : mat->kids) {
+        if (i >= 12) break;
+        float v = 0;
+        if (!kv.second.as_float(&v)) { fprintf(stderr, "oracle: bad matrix entry\n"); abort(); }
+        m[i++] = v;
+    }
+    if (i < 12) { fprintf(stderr, "oracle: matrix needs 12 entries\n"); abort(); }
+}
+inline void copy_eye(REAL m[12]) {
+    const REAL eye[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+    for (int j = 0; j < 12; j++) m[j] = eye[j];
+}
+
+inline const implicit_function* object_factory(Shape& S, const ojson::Node& node, bool ignore_root_matrix, const Env& env) {
+    const ojson::Node* t = node.child("type");
+    std::string name = t ? t->text : std::string();
+    REAL m[12];
+    auto matrix = [&]() { getMatrix12(m, node); if (ignore_root_matrix) copy_eye(m); };
+    if (name == "icube" || name == "cube") { matrix(); return S.keep(new cube(m, env)); }
+    if (name == "icylinder" || name == "cylinder") { matrix(); return S.keep(new scylinder(m)); }
+    if (name == "iellipsoid" || name == "ellipsoid") { matrix(); return S.keep(new egg(m)); }
+    if (name == "icone" || name == "cone") { matrix(); return S.keep(new scone(m)); }
+    if (name == "meta_balls") {                                                          // :654-673
+        matrix();
+        REAL time = node.get_float("time", 0.1);
+        return S.keep(new meta_balls(m, 4, time, 1.0));
+    }
+    if (name == "Union" || name == "Intersection" || name == "Difference") {
+        matrix();
+        const ojson::Node* ch = node.child("children");
+        size_t nch = ch ? ch->kids.size() : 0;
+        if (name == "Union") {                                                           // :537-580 left fold
+            if (nch < 2) { fprintf(stderr, "oracle: Union needs >= 2 children (reference returns an uninitialised pointer)\n"); abort(); }
+            const REAL eye[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+            const implicit_function* a = object_factory(S, ch->kids[0].second, false, env);
+            for (size_t i = 1; i < nch; i++) {
+                const implicit_function* b = object_factory(S, ch->kids[i].second, false, env);
+                bool last = (i + 1 == nch);
+                a = S.keep(new csg_node(OP_UNION, a, b, last ? m : eye));
+            }
+            return a;
+        }
+        if (nch != 2) { fprintf(stderr, "oracle: %s needs exactly 2 children\n", name.c_str()); abort(); }
+        const implicit_function* a = object_factory(S, ch->kids[0].second, false, env);
+        const implicit_function* b = object_factory(S, ch->kids[1].second, false, env);
+        return S.keep(new csg_node(name == "Intersection" ? OP_INTERSECTION : OP_SUBTRACT, a, b, m));
+    }
+    fprintf(stderr, "Invalid object you asked for: \"%s\"\n", name.c_str());              // :731-733
+    abort();
+}
+
+}  // namespace oracle
