@@ -1,0 +1,333 @@
+// Evaluator for the flattened CSG program (see program.hpp): value mode (f only, P points per thread) and
+// gradient mode (f and grad f, one pass).
+//
+// Arithmetic follows the reference's implicit_function classes operation by operation in binary32, with no FMA
+// contraction (this file must be compiled with -fmad=false; on the host with -ffp-contract=off), so field values are
+// bit-identical to the reference's eval_implicit / eval_gradient (paths relative to
+// /root/reference/js_iteration_2/implicit_function/):
+//   affine        basic_functions.hpp:140-177  ((m0*x + m1*y) + m2*z) + m3
+//   egg           egg.hpp:93-128               radii 0.5, centre 0 (object_factory.hpp:134-143 only builds this one)
+//   scylinder     scylinder.hpp:97-176         w=(0,0,1), base z=-0.5, length 1, radius 0.5
+//   scone         scone.hpp:81-166             h=1, r1=0, r2=0.5, apex z0=+0.5
+//   cube          cube.hpp:199-210 (six planes, analytic), :291-315 (gradient); HEAD's SDF-grid lookup :215-270
+//   metaballs     meta_balls_Rydgard.hpp:89-144,292-432
+//   union / intersection / subtract   transformed_union.hpp:47,76  transformed_intersection.hpp:49,78
+//                                     transformed_subtract.hpp:52,76-85
+// Where the factory's fixed parameters make an operation exact (x-0, x/0.5, x*0+..) it is folded; every folded form
+// is bit-equal to the written one for finite inputs (checked against the oracle in tests/test_program_emulation.py).
+//
+// The same code compiles for the host (ISD_HD) so the flattening and the interpreter can be checked against the
+// oracle without a GPU; the host build is a test fixture, never a fallback of the product.
+#pragma once
+#include <stdint.h>
+#include <math.h>
+#include "program.hpp"
+
+#if defined(__CUDACC__)
+#define ISD_HD __host__ __device__ __forceinline__
+#else
+#define ISD_HD inline
+#endif
+
+namespace isd {
+
+struct SdfGridView {          // HEAD-literal cube (cube.hpp:65-72): table lives in global memory
+    const float* v;
+    int nx, ny, nz;
+    float h, ox, oy, oz;
+};
+
+ISD_HD float as_float(uint32_t w) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(w);
+#else
+    float f; memcpy(&f, &w, 4); return f;
+#endif
+}
+
+// std::min as the reference calls it: (b < a) ? b : a
+ISD_HD float ref_min(float a, float b) { return (b < a) ? b : a; }
+
+template <class Prog>
+struct Mat12 {
+    float m[12];
+    ISD_HD void load(const Prog& prog, int at) {
+#pragma unroll
+        for (int i = 0; i < 12; ++i) m[i] = as_float(prog[at + i]);
+    }
+    ISD_HD void apply(float x, float y, float z, float& ox, float& oy, float& oz) const {
+        ox = m[0] * x + m[1] * y + m[2] * z + m[3];
+        oy = m[4] * x + m[5] * y + m[6] * z + m[7];
+        oz = m[8] * x + m[9] * y + m[10] * z + m[11];
+    }
+    // (M^-1)^T_{3x3} g   e.g. egg.hpp:124-126
+    ISD_HD void back(float g0, float g1, float g2, float& o0, float& o1, float& o2) const {
+        o0 = m[0] * g0 + m[4] * g1 + m[8] * g2;
+        o1 = m[1] * g0 + m[5] * g1 + m[9] * g2;
+        o2 = m[2] * g0 + m[6] * g1 + m[10] * g2;
+    }
+};
+
+// ---- primitives, local coordinates (x,y,z) already in the primitive's frame -----------------------------------
+ISD_HD float prim_ellipsoid(float x, float y, float z) {
+    // 1 - ((x/0.5)^2 + (y/0.5)^2 + (z/0.5)^2); scaling by 2 and 4 is exact
+    const float X = x + x, Y = y + y, Z = z + z;
+    return 1 - (X * X + Y * Y + Z * Z);
+}
+ISD_HD void grad_ellipsoid(float x, float y, float z, float& g0, float& g1, float& g2) {
+    g0 = -8.0f * x; g1 = -8.0f * y; g2 = -8.0f * z;      // (-2*x)/0.25, exact
+}
+ISD_HD void cyl_terms(float i0, float i1, float i2, float& t0, float& t1, float& r_) {
+    // t0 = (i0-0)*0 + (i1-0)*0 + (i2+0.5)*1 == i2+0.5 ;  i - w*t0 - c  with w=(0,0,1), c=(0,0,-0.5)
+    t0 = i2 + 0.5f;
+    t1 = 1.0f - t0;
+    const float d2 = i2 - t0 + 0.5f;
+    r_ = 0.5f - sqrtf(i0 * i0 + i1 * i1 + d2 * d2);
+}
+ISD_HD float prim_cylinder(float x, float y, float z) {
+    float t0, t1, r_;
+    cyl_terms(x, y, z, t0, t1, r_);
+    return ref_min(t0, ref_min(t1, r_));
+}
+ISD_HD void grad_cylinder(float i0, float i1, float i2, float& g0, float& g1, float& g2) {
+    float t0, t1, r_;
+    cyl_terms(i0, i1, i2, t0, t1, r_);
+    const float c_t0 = (t0 <= t1 && t0 <= r_) ? 1.0f : 0.0f;
+    const float c_t1 = (t1 <= t0 && t1 <= r_) ? 1.0f : 0.0f;
+    const float c_r = (r_ <= t0 && r_ <= t1) ? 1.0f : 0.0f;
+    const float w0 = 0.0f, w1 = 0.0f, w2 = 1.0f, cx = 0.0f, cy = 0.0f, cz = -0.5f;
+    g0 = c_t0 * w0 + c_t1 * (-w0) + c_r * (w0 * t0 + cx - i0);
+    g1 = c_t0 * w1 + c_t1 * (-w1) + c_r * (w1 * t0 + cy - i1);
+    g2 = c_t0 * w2 + c_t1 * (-w2) + c_r * (w2 * t0 + cz - i2);
+}
+ISD_HD float prim_cone(float x, float y, float z) {
+    const float dz = z - 0.5f;
+    const float f = -sqrtf(x * x + y * y) + sqrtf(dz * dz * 0.25f);
+    const float uperside = -dz - 0.0f;
+    const float lowerside = dz + 1.0f;
+    return ref_min(f, ref_min(uperside, lowerside));
+}
+ISD_HD void grad_cone(float x, float y, float z, float& gx, float& gy, float& gz) {
+    const float dz = z - 0.5f;
+    // -(x*x)/a2 - (y*y)/a2 + dz*dz with a2 = 0.25: the divisions are exact scalings by 4
+    const float f = -(x * x) * 4.0f - (y * y) * 4.0f + dz * dz;
+    const float uperside = -dz - 0.0f;
+    const float lowerside = dz + 1.0f;
+    if (uperside < f && uperside < lowerside) { gx = 0.f; gy = 0.f; gz = -1.f; }
+    else if (lowerside < f && lowerside < uperside) { gx = 0.f; gy = 0.f; gz = +1.f; }
+    else { gx = -8.0f * x; gy = -8.0f * y; gz = 2.0f * dz; }
+}
+ISD_HD float prim_cube(float x, float y, float z) {
+    // the six plane terms ((X-C-p).p)(-2) are exactly 0.5 -/+ coordinate
+    const float t0 = 0.5f - x, t1 = x + 0.5f, t2 = 0.5f - y, t3 = y + 0.5f, t4 = 0.5f - z, t5 = z + 0.5f;
+    return ref_min(t0, ref_min(t1, ref_min(t2, ref_min(t3, ref_min(t4, t5)))));
+}
+ISD_HD void grad_cube(float x, float y, float z, float& g0, float& g1, float& g2) {
+    const float t[6] = {0.5f - x, x + 0.5f, 0.5f - y, y + 0.5f, 0.5f - z, z + 0.5f};
+    int index = 0;
+    float mn = t[0];
+#pragma unroll
+    for (int k = 1; k < 6; ++k)
+        if (t[k] < mn) { index = k; mn = t[k]; }
+    // -p[index], including the signed zeros of the other two components
+    g0 = (index == 0) ? -0.5f : (index == 1) ? 0.5f : -0.0f;
+    g1 = (index == 2) ? -0.5f : (index == 3) ? 0.5f : -0.0f;
+    g2 = (index == 4) ? -0.5f : (index == 5) ? 0.5f : -0.0f;
+}
+ISD_HD float prim_cube_sdf(const SdfGridView& g, float px, float py, float pz) {
+    float res = 10000;
+    if (g.ox + g.h * g.nx < px || px < g.ox) {
+    } else if (g.oy + g.h * g.ny < py || py < g.oy) {
+    } else if (g.oz + g.h * g.nz < pz || pz < g.oz) {
+    } else {
+        const int xc = (int)((px - g.ox) / g.h), yc = (int)((py - g.oy) / g.h), zc = (int)((pz - g.oz) / g.h);
+        const float xl = g.ox + xc * g.h, yl = g.oy + yc * g.h, zl = g.oz + zc * g.h;
+        const float xd = (px - xl) / g.h, yd = (py - yl) / g.h, zd = (pz - zl) / g.h;
+        const long total = (long)g.nx * g.ny * g.nz;
+        // the reference indexes one past the table at the upper faces (UB); out-of-table reads give 0 here
+#define ISD_AT(a, b, c) (((long)(a) + (long)(b) * g.nx + (long)(c) * g.nx * g.ny) < total ? g.v[(long)(a) + (long)(b) * g.nx + (long)(c) * g.nx * g.ny] : 0.0f)
+        const float c00 = ISD_AT(xc, yc, zc) * (1 - xd) + ISD_AT(xc + 1, yc, zc) * xd;
+        const float c01 = ISD_AT(xc, yc, zc + 1) * (1 - xd) + ISD_AT(xc + 1, yc, zc + 1) * xd;
+        const float c10 = ISD_AT(xc, yc + 1, zc) * (1 - xd) + ISD_AT(xc + 1, yc + 1, zc) * xd;
+        const float c11 = ISD_AT(xc, yc + 1, zc + 1) * (1 - xd) + ISD_AT(xc + 1, yc + 1, zc + 1) * xd;
+#undef ISD_AT
+        const float c0 = c00 * (1 - yd) + c10 * yd;
+        const float c1 = c01 * (1 - yd) + c11 * yd;
+        res = c0 * (1 - zd) + c1 * (zd);
+    }
+    return -res;
+}
+
+// ---- value mode -------------------------------------------------------------------------------------------------
+// Evaluates the program at P points held in registers; cur* are clobbered.
+template <int P, class Prog>
+ISD_HD void eval_values(const Prog& prog, const SdfGridView& sdf, float (&cx)[P], float (&cy)[P], float (&cz)[P], float (&out)[P]) {
+    float vs[kMaxValueStack][P];
+    float fs[kMaxFrameStack][3][P];
+    int sp = 0, fp = 0, pc = 0;
+    for (;;) {
+        const uint32_t word = prog[pc];
+        const uint32_t op = word & OP_MASK;
+        if (op == OP_END) break;
+        if (op == OP_SAVE) {
+#pragma unroll
+            for (int p = 0; p < P; ++p) { fs[fp][0][p] = cx[p]; fs[fp][1][p] = cy[p]; fs[fp][2][p] = cz[p]; }
+            ++fp; ++pc;
+            continue;
+        }
+        if (op == OP_RESTORE) {
+            --fp;
+#pragma unroll
+            for (int p = 0; p < P; ++p) { cx[p] = fs[fp][0][p]; cy[p] = fs[fp][1][p]; cz[p] = fs[fp][2][p]; }
+            ++pc;
+            continue;
+        }
+        Mat12<Prog> M;
+        M.load(prog, pc + 1);
+        pc += 13;
+        if (op == OP_XFORM) {
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                float x, y, z;
+                M.apply(cx[p], cy[p], cz[p], x, y, z);
+                cx[p] = x; cy[p] = y; cz[p] = z;
+            }
+        } else if (op >= OP_UNION) {
+            --sp;
+            const bool swapped = (word & OP_FLAG_SWAPPED) != 0;
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                const float top = vs[sp][p], below = vs[sp - 1][p];
+                const float f1 = swapped ? top : below, f2 = swapped ? below : top;
+                float r;
+                if (op == OP_UNION) r = (f1 > f2) ? f1 : f2;
+                else if (op == OP_INTERSECT) r = (f1 > f2) ? f2 : f1;
+                else r = (f1 < -f2) ? f1 : -f2;
+                vs[sp - 1][p] = r;
+            }
+        } else {
+            if (op == OP_METABALLS) {
+                const int nb = (int)prog[pc];
+                ++pc;
+                float acc[P], lx[P], ly[P], lz[P];
+#pragma unroll
+                for (int p = 0; p < P; ++p) { M.apply(cx[p], cy[p], cz[p], lx[p], ly[p], lz[p]); acc[p] = 0.0f; }
+                for (int b = 0; b < nb; ++b) {
+                    const float bx = as_float(prog[pc]), by = as_float(prog[pc + 1]), bz = as_float(prog[pc + 2]);
+                    const float strength = as_float(prog[pc + 3]), subtract = as_float(prog[pc + 4]);
+                    pc += 5;
+#pragma unroll
+                    for (int p = 0; p < P; ++p) {
+                        const float fx = lx[p] - bx, fx2 = fx * fx;
+                        const float fy = ly[p] - by, fy2 = fy * fy;
+                        const float fz = lz[p] - bz, fz2 = fz * fz;
+                        const float h = 0.000001f + fx2 + fy2 + fz2;
+                        const float hinv = 1.0f / h;
+                        const float val = strength * hinv - subtract;
+                        acc[p] += val / 100.0f;
+                    }
+                }
+#pragma unroll
+                for (int p = 0; p < P; ++p) vs[sp][p] = acc[p];
+            } else {
+#pragma unroll
+                for (int p = 0; p < P; ++p) {
+                    float x, y, z;
+                    M.apply(cx[p], cy[p], cz[p], x, y, z);
+                    float f;
+                    if (op == OP_ELLIPSOID) f = prim_ellipsoid(x, y, z);
+                    else if (op == OP_CYLINDER) f = prim_cylinder(x, y, z);
+                    else if (op == OP_CONE) f = prim_cone(x, y, z);
+                    else if (op == OP_CUBE) f = prim_cube(x, y, z);
+                    else f = prim_cube_sdf(sdf, x, y, z);
+                    vs[sp][p] = f;
+                }
+            }
+            ++sp;
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < P; ++p) out[p] = vs[0][p];
+}
+
+// ---- gradient mode: f and grad f in one pass (identical to the reference's O(depth^2) recursion) ----
+template <class Prog>
+ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, float cx, float cy, float cz, float& f_out, float& g0_out,
+                                float& g1_out, float& g2_out) {
+    float vs[kMaxValueStack][4];
+    float fs[kMaxFrameStack][3];
+    int sp = 0, fp = 0, pc = 0;
+    for (;;) {
+        const uint32_t word = prog[pc];
+        const uint32_t op = word & OP_MASK;
+        if (op == OP_END) break;
+        if (op == OP_SAVE) { fs[fp][0] = cx; fs[fp][1] = cy; fs[fp][2] = cz; ++fp; ++pc; continue; }
+        if (op == OP_RESTORE) { --fp; cx = fs[fp][0]; cy = fs[fp][1]; cz = fs[fp][2]; ++pc; continue; }
+        Mat12<Prog> M;
+        M.load(prog, pc + 1);
+        pc += 13;
+        if (op == OP_XFORM) {
+            float x, y, z;
+            M.apply(cx, cy, cz, x, y, z);
+            cx = x; cy = y; cz = z;
+        } else if (op >= OP_UNION) {
+            --sp;
+            const bool swapped = (word & OP_FLAG_SWAPPED) != 0;
+            const int i1 = swapped ? sp : sp - 1, i2 = swapped ? sp - 1 : sp;
+            const float f1 = vs[i1][0], f2 = vs[i2][0];
+            bool first;
+            float r;
+            if (op == OP_UNION) { first = (f1 > f2); r = first ? f1 : f2; }
+            else if (op == OP_INTERSECT) { first = !(f1 > f2); r = (f1 > f2) ? f2 : f1; }
+            else { first = (f1 < -f2); r = first ? f1 : -f2; }
+            float a0, a1, a2;
+            if (first) { a0 = vs[i1][1]; a1 = vs[i1][2]; a2 = vs[i1][3]; }
+            else if (op == OP_SUBTRACT) { a0 = -vs[i2][1]; a1 = -vs[i2][2]; a2 = -vs[i2][3]; }
+            else { a0 = vs[i2][1]; a1 = vs[i2][2]; a2 = vs[i2][3]; }
+            float o0, o1, o2;
+            M.back(a0, a1, a2, o0, o1, o2);
+            vs[sp - 1][0] = r; vs[sp - 1][1] = o0; vs[sp - 1][2] = o1; vs[sp - 1][3] = o2;
+        } else {
+            float x, y, z;
+            M.apply(cx, cy, cz, x, y, z);
+            float f, g0, g1, g2;
+            if (op == OP_METABALLS) {
+                const int nb = (int)prog[pc];
+                ++pc;
+                f = 0.0f; g0 = 0.0f; g1 = 0.0f; g2 = 0.0f;
+                for (int b = 0; b < nb; ++b) {
+                    const float bx = as_float(prog[pc]), by = as_float(prog[pc + 1]), bz = as_float(prog[pc + 2]);
+                    const float strength = as_float(prog[pc + 3]), subtract = as_float(prog[pc + 4]);
+                    pc += 5;
+                    const float fx = x - bx, fx2 = fx * fx;
+                    const float fy = y - by, fy2 = fy * fy;
+                    const float fz = z - bz, fz2 = fz * fz;
+                    {   // implicit_ball :89-100: float literal, float sum
+                        const float h = 0.000001f + fx2 + fy2 + fz2;
+                        const float hinv = 1.0f / h;
+                        const float val = strength * hinv - subtract;
+                        f += val / 100.0f;
+                    }
+                    {   // gradient_ball :118-136: the literal is a double, h is summed in double then rounded
+                        const float h = (float)(0.000001 + (double)fx2 + (double)fy2 + (double)fz2);
+                        const float hinv = 1.0f / h;
+                        g0 += strength * (-2.0f * fx * hinv * hinv) / 100.0f;
+                        g1 += strength * (-2.0f * fy * hinv * hinv) / 100.0f;
+                        g2 += strength * (-2.0f * fz * hinv * hinv) / 100.0f;
+                    }
+                }
+            } else if (op == OP_ELLIPSOID) { f = prim_ellipsoid(x, y, z); grad_ellipsoid(x, y, z, g0, g1, g2); }
+            else if (op == OP_CYLINDER) { f = prim_cylinder(x, y, z); grad_cylinder(x, y, z, g0, g1, g2); }
+            else if (op == OP_CONE) { f = prim_cone(x, y, z); grad_cone(x, y, z, g0, g1, g2); }
+            else if (op == OP_CUBE) { f = prim_cube(x, y, z); grad_cube(x, y, z, g0, g1, g2); }
+            else { f = prim_cube_sdf(sdf, x, y, z); grad_cube(x, y, z, g0, g1, g2); }
+            float o0, o1, o2;
+            M.back(g0, g1, g2, o0, o1, o2);
+            vs[sp][0] = f; vs[sp][1] = o0; vs[sp][2] = o1; vs[sp][3] = o2;
+            ++sp;
+        }
+    }
+    f_out = vs[0][0]; g0_out = vs[0][1]; g1_out = vs[0][2]; g2_out = vs[0][3];
+}
+
+}  // namespace isd

@@ -1,0 +1,320 @@
+// Shape spec (JSON) -> CSG tree -> flat device bytecode ("program").
+//
+// Host-side replacement for the reference's object_factory (object_factory.hpp:56-758) and the
+// per-node matrix inversion done in every implicit_function constructor
+// (implicit_function/transformed.hpp:16-26, egg.hpp:38-57, ... -> invert_matrix,
+// basic_functions.hpp:77-128).  The reference nests transforms (every node applies its OWN inverse
+// matrix to the points handed down by its parent, basic_functions.hpp:361-379) and never composes
+// them, so the program carries one 3x4 inverse per node and the device applies them in the same
+// order — required for bit-identical field values.
+//
+// Program = array of 32-bit words.  Instruction = opcode word (+ payload floats):
+//   XFORM  m[12]            cur <- m * cur                 (entering a CSG node)
+//   SAVE / RESTORE          push / pop cur on the frame stack (only around a CSG child that is itself a CSG node
+//                           and is not evaluated last)
+//   ELLIPSOID|CYLINDER|CONE|CUBE|CUBE_SDF  m[12]      push f(m * cur)         (primitives apply their own inverse)
+//   METABALLS m[12] nb {bx,by,bz,strength,subtract}*nb
+//   UNION|INTERSECT|SUBTRACT (+SWAPPED flag)  m[12]    pop two values, push the selected one; m is the node's own
+//                           inverse, used only in gradient mode to map the selected child's gradient back
+//   END
+// Children are ordered so the deeper child is evaluated last (no frame to keep while descending), which keeps the
+// frame stack empty and the value stack at one float per level for the left-deep chains the factory builds.
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+#include "json_min.hpp"
+
+namespace isd {
+
+enum Opcode : uint32_t {
+    OP_END = 0,
+    OP_XFORM = 1,
+    OP_SAVE = 2,
+    OP_RESTORE = 3,
+    OP_ELLIPSOID = 4,
+    OP_CYLINDER = 5,
+    OP_CONE = 6,
+    OP_CUBE = 7,
+    OP_CUBE_SDF = 8,
+    OP_METABALLS = 9,
+    OP_UNION = 10,
+    OP_INTERSECT = 11,
+    OP_SUBTRACT = 12,
+    OP_MASK = 0xff,
+    OP_FLAG_SWAPPED = 0x100,     // value stack holds (second child, first child)
+};
+
+constexpr int kMaxValueStack = 64;     // device limits (csg_eval.cuh)
+constexpr int kMaxFrameStack = 16;
+constexpr int kMaxProgramWords = 14336;   // 56 KB of __constant__
+
+// ---- 3x4 affine inverse -------------------------------------------------------------------------------------
+// Restates what invert_matrix gets from uBLAS lu_factorize + lu_substitute on the 4x4 [M; 0 0 0 1] in binary32:
+// partial pivoting by largest |a_ki| (first maximum), column scaled by the reciprocal of the pivot, rank-1 trailing
+// update, then row swaps on the identity, unit-lower forward and upper backward substitution, column by column.
+// Boost is not available here and the reference pins no version, so this order defines the result.
+// Returns false on a zero pivot, leaving `inv` untouched like the reference.
+inline bool affine_inverse(const float m12[12], float inv[12]) {
+    float lu[16];
+    memcpy(lu, m12, 12 * sizeof(float));
+    lu[12] = 0.f; lu[13] = 0.f; lu[14] = 0.f; lu[15] = 1.f;
+    int swap_with[4];
+    for (int c = 0; c < 4; ++c) {
+        int piv = c;
+        float big = fabsf(lu[c * 4 + c]);
+        for (int r = c + 1; r < 4; ++r) {
+            float v = fabsf(lu[r * 4 + c]);
+            if (v > big) { big = v; piv = r; }
+        }
+        swap_with[c] = piv;
+        if (lu[piv * 4 + c] == 0.0f) return false;
+        if (piv != c)
+            for (int k = 0; k < 4; ++k) { float t = lu[c * 4 + k]; lu[c * 4 + k] = lu[piv * 4 + k]; lu[piv * 4 + k] = t; }
+        const float recip = 1.0f / lu[c * 4 + c];
+        for (int r = c + 1; r < 4; ++r) lu[r * 4 + c] *= recip;
+        for (int r = c + 1; r < 4; ++r)
+            for (int k = c + 1; k < 4; ++k) lu[r * 4 + k] -= lu[r * 4 + c] * lu[c * 4 + k];
+    }
+    float x[16];
+    for (int i = 0; i < 16; ++i) x[i] = (i % 5 == 0) ? 1.0f : 0.0f;
+    for (int c = 0; c < 4; ++c)
+        if (swap_with[c] != c)
+            for (int k = 0; k < 4; ++k) { float t = x[c * 4 + k]; x[c * 4 + k] = x[swap_with[c] * 4 + k]; x[swap_with[c] * 4 + k] = t; }
+    for (int n = 0; n < 4; ++n)                 // L y = P b   (unit diagonal)
+        for (int col = 0; col < 4; ++col) {
+            const float t = x[n * 4 + col];
+            if (t != 0.0f)
+                for (int r = n + 1; r < 4; ++r) x[r * 4 + col] -= lu[r * 4 + n] * t;
+        }
+    for (int n = 3; n >= 0; --n)                // U x = y
+        for (int col = 3; col >= 0; --col) {
+            const float t = (x[n * 4 + col] /= lu[n * 4 + n]);
+            if (t != 0.0f)
+                for (int r = n - 1; r >= 0; --r) x[r * 4 + col] -= lu[r * 4 + n] * t;
+        }
+    memcpy(inv, x, 12 * sizeof(float));
+    return true;
+}
+
+// ---- tree -----------------------------------------------------------------------------------------------------
+struct ShapeNode {
+    Opcode op = OP_END;
+    float m[12], minv[12];
+    std::vector<float> params;                       // metaballs: nb*5
+    std::unique_ptr<ShapeNode> a, b;                 // CSG children (reference order)
+    bool is_csg() const { return op >= OP_UNION; }
+    int depth() const { return is_csg() ? 1 + std::max(a->depth(), b->depth()) : 0; }
+};
+
+struct ShapeOptions {
+    int cube_mode = 0;
+};
+
+class ShapeCompiler {
+public:
+    explicit ShapeCompiler(const ShapeOptions& o) : opt_(o) {}
+
+    // object_factory(const char*, bool)  object_factory.hpp:741-758
+    std::unique_ptr<ShapeNode> parse(const char* shape_json, bool ignore_root_matrix) {
+        JsonDoc doc(shape_json);
+        return build(doc, doc.root(), ignore_root_matrix);
+    }
+
+    struct Program {
+        std::vector<uint32_t> words;
+        int value_depth = 0, frame_depth = 0, num_nodes = 0;
+        bool uses_sdf_grid = false;
+        double flops_per_point = 0;          // mul and add counted separately
+    };
+
+    Program compile(const ShapeNode& root) {
+        Program p;
+        vs_ = fs_ = 0;
+        emit_node(root, /*preserve=*/false, p);
+        p.words.push_back(OP_END);
+        if (p.value_depth > kMaxValueStack || p.frame_depth > kMaxFrameStack) {
+            fprintf(stderr, "implisolid_b200: shape tree too deep for the device evaluator (value stack %d > %d or frame stack %d > %d)\n",
+                    p.value_depth, kMaxValueStack, p.frame_depth, kMaxFrameStack);
+            abort();
+        }
+        if ((int)p.words.size() > kMaxProgramWords) {
+            fprintf(stderr, "implisolid_b200: shape program too large (%zu words > %d)\n", p.words.size(), kMaxProgramWords);
+            abort();
+        }
+        return p;
+    }
+
+private:
+    ShapeOptions opt_;
+    int vs_ = 0, fs_ = 0;
+
+    static void read_matrix12(const JsonDoc& d, int node, bool ignore_root_matrix, float m[12]) {
+        // getMatrix12 (object_factory.hpp:21-30) copies every entry it finds (16 -> overruns REAL[12]); we stop at 12.
+        int mat = d.child(node, "matrix");
+        if (mat < 0) { fprintf(stderr, "implisolid_b200: shape node without \"matrix\"\n"); abort(); }
+        int i = 0;
+        for (int c = d.first_child(mat); c >= 0 && i < 12; c = d.next(c)) {
+            float v;
+            if (!d.to_float(c, &v)) { fprintf(stderr, "implisolid_b200: bad matrix entry\n"); abort(); }
+            m[i++] = v;
+        }
+        if (i < 12) { fprintf(stderr, "implisolid_b200: \"matrix\" needs at least 12 entries\n"); abort(); }
+        if (ignore_root_matrix) {   // copy_eye, object_factory.hpp:47
+            static const float eye[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+            memcpy(m, eye, sizeof(eye));
+        }
+    }
+    static void set_matrix(ShapeNode& n, const float m[12]) {
+        memcpy(n.m, m, sizeof(n.m));
+        memset(n.minv, 0, sizeof(n.minv));     // the reference leaves heap garbage when the matrix is singular
+        if (!affine_inverse(n.m, n.minv)) fprintf(stderr, "implisolid_b200: warning: singular shape matrix\n");
+    }
+    static std::unique_ptr<ShapeNode> leaf(Opcode op, const float m[12]) {
+        std::unique_ptr<ShapeNode> n(new ShapeNode());
+        n->op = op;
+        set_matrix(*n, m);
+        return n;
+    }
+    static std::unique_ptr<ShapeNode> csg(Opcode op, std::unique_ptr<ShapeNode> a, std::unique_ptr<ShapeNode> b, const float m[12]) {
+        std::unique_ptr<ShapeNode> n(new ShapeNode());
+        n->op = op;
+        set_matrix(*n, m);
+        n->a = std::move(a);
+        n->b = std::move(b);
+        return n;
+    }
+
+    std::unique_ptr<ShapeNode> build(const JsonDoc& d, int node, bool ignore_root_matrix) {
+        int t = d.child(node, "type");
+        std::string name = t >= 0 ? d.text(t) : std::string();
+        float m[12];
+        if (name == "icube" || name == "cube") {                                      // object_factory.hpp:110-120
+            read_matrix12(d, node, ignore_root_matrix, m);
+            return leaf(opt_.cube_mode ? OP_CUBE_SDF : OP_CUBE, m);
+        }
+        if (name == "icylinder" || name == "cylinder") {                              // :121-133
+            read_matrix12(d, node, ignore_root_matrix, m);
+            return leaf(OP_CYLINDER, m);
+        }
+        if (name == "iellipsoid" || name == "ellipsoid") {                            // :134-143
+            read_matrix12(d, node, ignore_root_matrix, m);
+            return leaf(OP_ELLIPSOID, m);
+        }
+        if (name == "icone" || name == "cone") {                                      // :144-152
+            read_matrix12(d, node, ignore_root_matrix, m);
+            return leaf(OP_CONE, m);
+        }
+        if (name == "meta_balls") {                                                   // :654-673
+            read_matrix12(d, node, ignore_root_matrix, m);
+            float time = 0.1f;
+            d.to_float(d.child(node, "time"), &time);
+            std::unique_ptr<ShapeNode> n = leaf(OP_METABALLS, m);
+            metaball_centres(4, time, n->params);
+            return n;
+        }
+        if (name == "Union" || name == "Intersection" || name == "Difference") {
+            read_matrix12(d, node, ignore_root_matrix, m);
+            int kids = d.child(node, "children");
+            int nkids = kids >= 0 ? d.count_children(kids) : 0;
+            if (name == "Union") {
+                // left fold of binary unions; inner ones carry the identity, the last one the node matrix
+                // (object_factory.hpp:537-580).  One child leaves the reference with an uninitialised pointer: rejected.
+                if (nkids < 2) { fprintf(stderr, "implisolid_b200: Union needs at least two children\n"); abort(); }
+                static const float eye[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+                int c = d.first_child(kids);
+                std::unique_ptr<ShapeNode> acc = build(d, c, false);
+                int idx = 1;
+                for (c = d.next(c); c >= 0; c = d.next(c), ++idx) {
+                    std::unique_ptr<ShapeNode> rhs = build(d, c, false);
+                    acc = csg(OP_UNION, std::move(acc), std::move(rhs), (idx + 1 == nkids) ? m : eye);
+                }
+                return acc;
+            }
+            if (nkids != 2) {   // :581-653 mis-builds with != 2 children
+                fprintf(stderr, "implisolid_b200: %s needs exactly two children\n", name.c_str());
+                abort();
+            }
+            int c0 = d.first_child(kids), c1 = d.next(c0);
+            std::unique_ptr<ShapeNode> a = build(d, c0, false);
+            std::unique_ptr<ShapeNode> b = build(d, c1, false);
+            return csg(name == "Intersection" ? OP_INTERSECT : OP_SUBTRACT, std::move(a), std::move(b), m);
+        }
+        fprintf(stderr, "Invalid object you asked for: \"%s\"\n", name.c_str());      // :731-733
+        abort();
+    }
+
+    // meta_ball_Rydgard constructor, implicit_function/meta_balls_Rydgard.hpp:49-59 (double math on the host,
+    // each result rounded once to binary32)
+    static void metaball_centres(int numblobs, float time, std::vector<float>& out) {
+        for (int ball_i = 0; ball_i < numblobs; ++ball_i) {
+            float x0 = 0.5, y0 = 0.5, z0 = 0.5;
+            float D = 1;
+            float ballx = sin(ball_i + 1.26 * time * (1.03 + 0.5 * cos(0.21 * ball_i))) * 0.27 * D + 0.5 - x0;
+            float bally = std::abs(cos(ball_i + 1.12 * time * cos(1.22 + 0.1424 * ball_i))) * 0.77 * D - y0;
+            float ballz = cos(ball_i + 1.32 * time * 0.1 * sin((0.92 + 0.53 * ball_i))) * 0.27 * D + 0.5 - z0;
+            float subtract = 12;
+            float strength = 1.2 / ((sqrt((double)numblobs) - 1) / 4 + 1);
+            out.push_back(ballx); out.push_back(bally); out.push_back(ballz);
+            out.push_back(strength); out.push_back(subtract);
+        }
+    }
+
+    static void put_matrix(Program& p, const float m[12]) {
+        for (int i = 0; i < 12; ++i) { uint32_t w; memcpy(&w, &m[i], 4); p.words.push_back(w); }
+    }
+    void push_value(Program& p) { if (++vs_ > p.value_depth) p.value_depth = vs_; }
+
+    void emit_node(const ShapeNode& n, bool preserve, Program& p) {
+        p.num_nodes++;
+        if (!n.is_csg()) {
+            p.words.push_back(n.op);
+            put_matrix(p, n.minv);
+            p.flops_per_point += 18;
+            switch (n.op) {
+                case OP_ELLIPSOID: p.flops_per_point += 9; break;
+                case OP_CYLINDER: p.flops_per_point += 14; break;
+                case OP_CONE: p.flops_per_point += 14; break;
+                case OP_CUBE: p.flops_per_point += 11; break;
+                case OP_CUBE_SDF: p.flops_per_point += 40; p.uses_sdf_grid = true; break;
+                case OP_METABALLS: {
+                    uint32_t nb = (uint32_t)(n.params.size() / 5);
+                    p.words.push_back(nb);
+                    for (float v : n.params) { uint32_t w; memcpy(&w, &v, 4); p.words.push_back(w); }
+                    p.flops_per_point += 12.0 * nb;
+                    break;
+                }
+                default: break;
+            }
+            push_value(p);
+            return;
+        }
+        if (preserve) {
+            p.words.push_back(OP_SAVE);
+            if (++fs_ > p.frame_depth) p.frame_depth = fs_;
+        }
+        p.words.push_back(OP_XFORM);
+        put_matrix(p, n.minv);
+        p.flops_per_point += 18 + 1;
+        // deeper child last; ties keep the reference order
+        const bool b_first = n.b->depth() < n.a->depth();
+        const ShapeNode& first = b_first ? *n.b : *n.a;
+        const ShapeNode& second = b_first ? *n.a : *n.b;
+        emit_node(first, /*preserve=*/first.is_csg(), p);
+        emit_node(second, /*preserve=*/false, p);
+        p.words.push_back((uint32_t)n.op | (b_first ? (uint32_t)OP_FLAG_SWAPPED : 0u));
+        put_matrix(p, n.minv);
+        vs_ -= 1;   // pops two, pushes one
+        if (preserve) {
+            p.words.push_back(OP_RESTORE);
+            --fs_;
+        }
+    }
+};
+
+}  // namespace isd

@@ -1,0 +1,96 @@
+// Polygonizer settings: the mc_parameters_json string of build_geometry().
+//
+// Same keys, defaults and abort conditions as the reference's mc_settings /
+// parse_mc_properties_json (polygoniser_settings.hpp:8-34 struct, :70-84 defaults, :101-141
+// read_bool_from_json, :147-305 parser).  Booleans are JSON integers 0/1 there (get<int>); a JSON
+// true/false is not an int and silently yields the default — kept.  Extra keys under "gpu" are ours
+// and are ignored by the reference parser.
+#pragma once
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <limits>
+#include "json_min.hpp"
+
+namespace isd {
+
+struct Box { float xmin, xmax, ymin, ymax, zmin, zmax; };
+
+struct McSettings {
+    Box box;
+    int resolution;
+    bool ignore_root_matrix;
+    int overall_repeats;
+    int vresampl_iters;
+    float vresampl_c;
+    bool qem_enabled, projection_enabled, subdiv_enabled;
+    float post_subdiv_noise;
+    // ---- ours ("gpu": {...}) ----
+    int cube_mode;        // 0: analytic six-plane cube (default), 1: HEAD-literal SDF grid (needs isd_set_sdf_grid)
+    int fast_math;        // 0: exact (no FMA contraction; parity mode), 1: contraction allowed
+    int verbose;
+};
+
+inline bool settings_bool(const JsonDoc& d, const char* field, bool dflt, const char* forbidden, bool* needs_abort) {
+    const int kUnset = -1;
+    int v = d.get_int(field, kUnset);
+    bool val = (v == kUnset) ? dflt : (v != 0);
+    const int kMagic = 9123456;
+    if (d.get_int(forbidden, kMagic) != kMagic) {
+        fprintf(stderr, "Error: Use %s instead of using%s. Aborting! \n", field, forbidden);
+        *needs_abort = true;
+    }
+    return val;
+}
+
+inline McSettings parse_mc_settings(const char* json) {
+    JsonDoc d(json);
+    McSettings s;
+    bool needs_abort = false;
+    const float nan = std::numeric_limits<float>::quiet_NaN();
+    float b[6] = {d.get_float("box.xmin", nan), d.get_float("box.xmax", nan), d.get_float("box.ymin", nan),
+                  d.get_float("box.ymax", nan), d.get_float("box.zmin", nan), d.get_float("box.zmax", nan)};
+    for (float v : b)
+        if (std::isnan(v)) needs_abort = true;
+    if (needs_abort) fprintf(stderr, "Error: missing or incorrect values in mc_parameters_json\n");
+    s.box = Box{b[0], b[1], b[2], b[3], b[4], b[5]};
+
+    float res_real = d.get_float("resolution", -1.0f);
+    int res_int = (int)res_real;
+    if (res_int == -1) res_int = 28;
+    if ((float)res_int != res_real) {      // also hit when "resolution" is absent (28 != -1), as in the reference
+        fprintf(stderr, "Error: resolution must be integer: %g != %g\n", (double)res_int, (double)res_real);
+        needs_abort = true;
+    }
+    s.resolution = res_int;
+    if (s.resolution <= 2) {
+        fprintf(stderr, "Error: missing or incorrect values in mc_parameters_json\n");
+        needs_abort = true;
+    }
+    if (s.resolution > 65535 - 5) {        // dim_t is uint16 in the reference (mcc2.cpp:68)
+        fprintf(stderr, "Error: resolution too large\n");
+        needs_abort = true;
+    }
+    s.vresampl_c = d.get_float("vresampl.c", 1.0f);
+    s.vresampl_iters = d.get_int("vresampl.iters", 0);
+    s.projection_enabled = settings_bool(d, "projection.enabled", false, "projection.enable", &needs_abort);
+    s.qem_enabled = settings_bool(d, "qem.enabled", false, "qem.enable", &needs_abort);
+    s.subdiv_enabled = settings_bool(d, "subdiv.enabled", true, "subdiv.enable", &needs_abort);
+    s.post_subdiv_noise = d.get_float("debug.post_subdiv_noise", 0.01f);
+    s.overall_repeats = d.get_int("overall_repeats", 1);
+    s.ignore_root_matrix = d.get_bool("ignore_root_matrix", false);
+    s.cube_mode = d.get_int("gpu.cube_mode", 0);
+    s.fast_math = d.get_int("gpu.fast_math", 0);
+    s.verbose = d.get_int("gpu.verbose", 0);
+    if (s.qem_enabled && !s.projection_enabled) {
+        fprintf(stderr, "Invalid settings: QEM will not be applied if centroid projection is disabled\n");
+        needs_abort = true;
+    }
+    if (needs_abort) {
+        fprintf(stderr, "Aborting because of a problem in mc_settings_from_json.\n");
+        abort();
+    }
+    return s;
+}
+
+}  // namespace isd

@@ -1,0 +1,120 @@
+"""Synthetic shape specs and polygonizer settings for the BASELINE configs.
+
+Pure data generators: they build the two JSON strings the geometry API takes.  Matrices are row-major 4x4
+(`[R|t]` in the first 12 entries) exactly as the reference's mp5 documents carry them
+(/root/reference/js_iteration_2/examples/js/example_objects.js:39).
+"""
+import json
+import numpy as np
+
+EYE = [1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1]
+
+
+def _mat(R, t):
+    m = np.eye(4)
+    m[:3, :3] = R
+    m[:3, 3] = t
+    # round-trip through float32 text so every consumer parses the same binary32 values
+    return [float(np.float32(v)) for v in m.reshape(-1)]
+
+
+def _rot_axis(axis, deg):
+    axis = np.asarray(axis, dtype=np.float64)
+    axis = axis / np.linalg.norm(axis)
+    a = np.deg2rad(deg)
+    K = np.array([[0, -axis[2], axis[1]], [axis[2], 0, -axis[0]], [-axis[1], axis[0], 0]])
+    return np.eye(3) + np.sin(a) * K + (1 - np.cos(a)) * (K @ K)
+
+
+def box(h):
+    return {"xmin": -h, "xmax": h, "ymin": -h, "ymax": h, "zmin": -h, "zmax": h}
+
+
+def mc_settings(resolution, half, iters=0, c=1.0, projection=0, qem=0, repeats=1, **gpu):
+    s = {"resolution": int(resolution), "box": box(half), "ignore_root_matrix": 0, "subdiv": {"enabled": 0},
+         "overall_repeats": int(repeats), "vresampl": {"iters": int(iters), "c": float(c)},
+         "projection": {"enabled": int(projection)}, "qem": {"enabled": int(qem)}}
+    if gpu:
+        s["gpu"] = gpu
+    return json.dumps(s)
+
+
+def c1_sphere():
+    """C1: sphere r=0.5 requested as an ellipsoid."""
+    return json.dumps({"type": "ellipsoid", "matrix": EYE})
+
+
+def c2_cube_minus_cylinder():
+    """C2: Difference[cube, cylinder(diag(0.6,0.6,1.4))] under Rot((1,1,0),30deg)*0.9 + t."""
+    R = _rot_axis([1, 1, 0], 30.0) * 0.9
+    node = _mat(R, [0.05, -0.03, 0.02])
+    cyl = _mat(np.diag([0.6, 0.6, 1.4]), [0, 0, 0])
+    return json.dumps({"type": "Difference", "matrix": node,
+                       "children": [{"type": "cube", "matrix": EYE}, {"type": "cylinder", "matrix": cyl}]})
+
+
+def c3_metaballs():
+    """C3(i): Union of 16 meta_balls nodes (4 blobs each) on a 4x2x2 lattice, spacing 0.4."""
+    kids = []
+    i = 0
+    for ix in range(4):
+        for iy in range(2):
+            for iz in range(2):
+                t = [(ix - 1.5) * 0.4, (iy - 0.5) * 0.4, (iz - 0.5) * 0.4]
+                kids.append({"type": "meta_balls", "time": float(np.float32(0.1 + 0.37 * i)), "matrix": _mat(np.eye(3), t)})
+                i += 1
+    return json.dumps({"type": "Union", "matrix": EYE, "children": kids})
+
+
+def c4_deep_chain(n_prims=32, seed=1234):
+    """C4: left-deep chain of n_prims transformed primitives, ops cycle [Union x3, Difference x1]."""
+    rng = np.random.default_rng(seed)
+    types = ["ellipsoid", "cylinder", "cone", "ellipsoid"]
+    ops = ["Union", "Union", "Union", "Difference"]
+
+    def prim(k):
+        q, _ = np.linalg.qr(rng.normal(size=(3, 3)))
+        R = q * rng.uniform(0.15, 0.35)
+        t = rng.uniform(-0.7, 0.7, size=3)
+        return {"type": types[k % 4], "matrix": _mat(R, t)}
+
+    def small_affine():
+        axis = rng.normal(size=3)
+        R = _rot_axis(axis, rng.uniform(-10, 10)) * rng.uniform(0.95, 1.05)
+        return _mat(R, [0, 0, 0])
+
+    node = prim(0)
+    for k in range(1, n_prims):
+        node = {"type": ops[(k - 1) % 4], "matrix": small_affine(), "children": [node, prim(k)]}
+    return json.dumps(node)
+
+
+def demo_moon():
+    """MOON demo (nested Difference of cylinders), examples/js/example_objects.js:22-70, scaled to a unit box."""
+    s = 1.0 / 60.0
+    def sc(m):
+        m = np.array(m, dtype=np.float64).reshape(4, 4)
+        return [float(np.float32(v)) for v in m.reshape(-1)]
+    inner = {"type": "Difference", "matrix": sc([2.38, 0, 0, 0.36, 0, 2.38, 0, 0.56, 0, 0, 2.38, 6.9, 0, 0, 0, 1]),
+             "children": [{"type": "cylinder", "matrix": sc([10, 0, 0, 0, 0, 10, 0, 0, 0, 0, 10, 0, 0, 0, 0, 1])},
+                          {"type": "cylinder", "matrix": sc([10, 0, 0, 0.66, 0, 10, 0, 6.22, 0, 0, 10, 0.00001, 0, 0, 0, 1])}]}
+    return json.dumps({"type": "Difference", "matrix": sc([1, 0, 0, 0.33, 0, 1, 0, 0.156, 0, 0, 1, 0.000000000000014, 0, 0, 0, 1]),
+                       "children": [{"type": "cylinder", "matrix": sc([42.5, 0, 0, 0, 0, 49.6, 0, 0, 0, 0, 10, 0, 0, 0, 0, 1])}, inner]})
+
+
+def simple_cone():
+    """SIMPLE_CONE demo, examples/js/example_objects.js:79 (icone, matrix diag 8) scaled to 0.8."""
+    return json.dumps({"type": "icone", "matrix": [0.8, 0, 0, 0, 0, 0.8, 0, 0, 0, 0, 0.8, 0, 0, 0, 0, 1]})
+
+
+def bushy_tree(seed=7):
+    """A balanced CSG tree (both children are CSG nodes) to exercise the SAVE/RESTORE frame stack."""
+    rng = np.random.default_rng(seed)
+    def prim(kind):
+        q, _ = np.linalg.qr(rng.normal(size=(3, 3)))
+        return {"type": kind, "matrix": _mat(q * rng.uniform(0.3, 0.6), rng.uniform(-0.3, 0.3, size=3))}
+    def aff():
+        return _mat(_rot_axis(rng.normal(size=3), rng.uniform(-20, 20)) * rng.uniform(0.9, 1.1), rng.uniform(-0.05, 0.05, size=3))
+    l = {"type": "Union", "matrix": aff(), "children": [prim("cube"), prim("cylinder"), prim("ellipsoid")]}
+    r = {"type": "Intersection", "matrix": aff(), "children": [prim("cone"), {"type": "Difference", "matrix": aff(), "children": [prim("ellipsoid"), prim("cube")]}]}
+    return json.dumps({"type": "Difference", "matrix": aff(), "children": [l, r]})
