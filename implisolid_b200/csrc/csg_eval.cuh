@@ -160,10 +160,15 @@ ISD_HD float prim_cube_sdf(const SdfGridView& g, float px, float py, float pz) {
 
 // ---- value mode -------------------------------------------------------------------------------------------------
 // Evaluates the program at P points held in registers; cur* are clobbered.
+// The two newest values of the stack live in registers (t0 = top, t1 = below); older ones spill to a per-thread
+// array (local memory, L1-resident).  Stack depth is a property of the program, hence uniform across the grid.
 template <int P, class Prog>
 ISD_HD void eval_values(const Prog& prog, const SdfGridView& sdf, float (&cx)[P], float (&cy)[P], float (&cz)[P], float (&out)[P]) {
-    float vs[kMaxValueStack][P];
+    float spill[kMaxValueStack][P];
     float fs[kMaxFrameStack][3][P];
+    float t0[P], t1[P];
+#pragma unroll
+    for (int p = 0; p < P; ++p) { t0[p] = 0.0f; t1[p] = 0.0f; }
     int sp = 0, fp = 0, pc = 0;
     for (;;) {
         const uint32_t word = prog[pc];
@@ -193,25 +198,30 @@ ISD_HD void eval_values(const Prog& prog, const SdfGridView& sdf, float (&cx)[P]
                 cx[p] = x; cy[p] = y; cz[p] = z;
             }
         } else if (op >= OP_UNION) {
-            --sp;
             const bool swapped = (word & OP_FLAG_SWAPPED) != 0;
 #pragma unroll
             for (int p = 0; p < P; ++p) {
-                const float top = vs[sp][p], below = vs[sp - 1][p];
+                const float top = t0[p], below = t1[p];
                 const float f1 = swapped ? top : below, f2 = swapped ? below : top;
                 float r;
                 if (op == OP_UNION) r = (f1 > f2) ? f1 : f2;
                 else if (op == OP_INTERSECT) r = (f1 > f2) ? f2 : f1;
                 else r = (f1 < -f2) ? f1 : -f2;
-                vs[sp - 1][p] = r;
+                t0[p] = r;
+            }
+            --sp;
+            if (sp >= 2) {
+#pragma unroll
+                for (int p = 0; p < P; ++p) t1[p] = spill[sp - 2][p];
             }
         } else {
+            float f[P];
             if (op == OP_METABALLS) {
                 const int nb = (int)prog[pc];
                 ++pc;
-                float acc[P], lx[P], ly[P], lz[P];
+                float lx[P], ly[P], lz[P];
 #pragma unroll
-                for (int p = 0; p < P; ++p) { M.apply(cx[p], cy[p], cz[p], lx[p], ly[p], lz[p]); acc[p] = 0.0f; }
+                for (int p = 0; p < P; ++p) { M.apply(cx[p], cy[p], cz[p], lx[p], ly[p], lz[p]); f[p] = 0.0f; }
                 for (int b = 0; b < nb; ++b) {
                     const float bx = as_float(prog[pc]), by = as_float(prog[pc + 1]), bz = as_float(prog[pc + 2]);
                     const float strength = as_float(prog[pc + 3]), subtract = as_float(prog[pc + 4]);
@@ -224,30 +234,33 @@ ISD_HD void eval_values(const Prog& prog, const SdfGridView& sdf, float (&cx)[P]
                         const float h = 0.000001f + fx2 + fy2 + fz2;
                         const float hinv = 1.0f / h;
                         const float val = strength * hinv - subtract;
-                        acc[p] += val / 100.0f;
+                        f[p] += val / 100.0f;
                     }
                 }
-#pragma unroll
-                for (int p = 0; p < P; ++p) vs[sp][p] = acc[p];
             } else {
 #pragma unroll
                 for (int p = 0; p < P; ++p) {
                     float x, y, z;
                     M.apply(cx[p], cy[p], cz[p], x, y, z);
-                    float f;
-                    if (op == OP_ELLIPSOID) f = prim_ellipsoid(x, y, z);
-                    else if (op == OP_CYLINDER) f = prim_cylinder(x, y, z);
-                    else if (op == OP_CONE) f = prim_cone(x, y, z);
-                    else if (op == OP_CUBE) f = prim_cube(x, y, z);
-                    else f = prim_cube_sdf(sdf, x, y, z);
-                    vs[sp][p] = f;
+                    if (op == OP_ELLIPSOID) f[p] = prim_ellipsoid(x, y, z);
+                    else if (op == OP_CYLINDER) f[p] = prim_cylinder(x, y, z);
+                    else if (op == OP_CONE) f[p] = prim_cone(x, y, z);
+                    else if (op == OP_CUBE) f[p] = prim_cube(x, y, z);
+                    else f[p] = prim_cube_sdf(sdf, x, y, z);
                 }
             }
+            // push
+            if (sp >= 2) {
+#pragma unroll
+                for (int p = 0; p < P; ++p) spill[sp - 2][p] = t1[p];
+            }
+#pragma unroll
+            for (int p = 0; p < P; ++p) { t1[p] = t0[p]; t0[p] = f[p]; }
             ++sp;
         }
     }
 #pragma unroll
-    for (int p = 0; p < P; ++p) out[p] = vs[0][p];
+    for (int p = 0; p < P; ++p) out[p] = t0[p];
 }
 
 // ---- gradient mode: f and grad f in one pass (identical to the reference's O(depth^2) recursion) ----

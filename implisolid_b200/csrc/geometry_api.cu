@@ -1,0 +1,936 @@
+// libimplisolid_b200.so — the reference's extern "C" geometry API (mcc2.cpp:88-134) on one B200, plus isd_* extensions.
+//
+// Host side of the hot path: what mcc2.cpp's grand_algorithm (:309-444), mc_start (:222-249), the polygonizer state
+// machine (polygonizer_algorithm_ob02.hpp:14-176) and the direct-evaluation service (mcc2.cpp:699-911) do, restated
+// as: parse the two JSON strings (settings.hpp, program.hpp), flatten the CSG tree to a device program, then launch
+//   K1 eval_field -> K2 mc_classify -> K3 scan -> [z-slab: ncclAllGather of {nv,nf}] -> K4 mc_emit
+//   -> overall_repeats x { vresampl.iters x (K5,K6,K7) ; projection (K5,K8) ; qem (K9) }
+// on one stream.  Only the three scan totals cross back to the host before the mesh itself.  There is no CPU
+// fallback: every compute entry point aborts if no CUDA device is usable.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <chrono>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/implisolid_b200.h"
+#include "device_util.hpp"
+#include "field_kernel.cuh"
+#include "mc_kernels.cuh"
+#include "ob02_kernels.cuh"
+#include "settings.hpp"
+
+using namespace isd;
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------------------------------
+// NCCL, bound at run time (the library has no link-time dependency on it)
+// ---------------------------------------------------------------------------------------------------------------------
+struct NcclApi {
+    void* lib = nullptr;
+    typedef struct { char internal[128]; } unique_id;
+    int (*GetUniqueId)(unique_id*) = nullptr;
+    int (*CommInitRank)(void**, int, unique_id, int) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+    int (*Broadcast)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    bool load() {
+        if (lib) return true;
+        const char* names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char* n : names) {
+            lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+            if (lib) break;
+        }
+        if (!lib) { fprintf(stderr, "implisolid_b200: cannot load libnccl.so.2: %s\n", dlerror()); return false; }
+#define ISD_NCCL_SYM(field, name)                                             \
+    *(void**)(&field) = dlsym(lib, name);                                     \
+    if (!field) { fprintf(stderr, "implisolid_b200: NCCL symbol %s missing\n", name); return false; }
+        ISD_NCCL_SYM(GetUniqueId, "ncclGetUniqueId");
+        ISD_NCCL_SYM(CommInitRank, "ncclCommInitRank");
+        ISD_NCCL_SYM(AllGather, "ncclAllGather");
+        ISD_NCCL_SYM(Broadcast, "ncclBroadcast");
+        ISD_NCCL_SYM(GroupStart, "ncclGroupStart");
+        ISD_NCCL_SYM(GroupEnd, "ncclGroupEnd");
+        ISD_NCCL_SYM(CommDestroy, "ncclCommDestroy");
+        ISD_NCCL_SYM(GetErrorString, "ncclGetErrorString");
+#undef ISD_NCCL_SYM
+        return true;
+    }
+    void check(int rc, const char* what) {
+        if (rc != 0) {
+            fprintf(stderr, "implisolid_b200: NCCL error in %s: %s\n", what, GetErrorString ? GetErrorString(rc) : "?");
+            abort();
+        }
+    }
+};
+constexpr int kNcclInt64 = 4, kNcclFloat32 = 7, kNcclInt32 = 2;   // ncclDataType_t values (nccl.h)
+
+// ---------------------------------------------------------------------------------------------------------------------
+// process-wide state (the reference keeps one global state_t _state, mcc2.cpp:165-193)
+// ---------------------------------------------------------------------------------------------------------------------
+enum { T_FIELD = 0, T_CLASSIFY, T_EMIT, T_RESAMPLE, T_PROJECT, T_QEM, T_COPY, T_TOTAL, T_COUNT };
+
+struct Context {
+    bool ready = false;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[16];
+
+    // geometry state
+    bool active = false;          // state_t::active
+    long long nv = 0, nf = 0;     // mesh held on this GPU (a slab's part in sharded mode until gathered)
+    bool host_valid = false;      // pinned mirrors hold the current mesh
+    DeviceBuffer d_verts, d_faces;
+    PinnedBuffer h_verts, h_faces;
+
+    // field + marching cubes scratch
+    DeviceBuffer d_field, d_counts, d_offsets, d_active, d_partials, d_totals, d_cases;
+    PinnedBuffer h_small;         // totals and other small read-backs
+    GridDesc grid{};
+    McDesc mc{};
+    bool keep_field = false, have_cases = false;
+    int S = 0;
+
+    // OB02 scratch
+    DeviceBuffer d_cen, d_nrm, d_deg, d_uoff, d_uitems, d_cursor, d_fof, d_w, d_len3, d_best, d_fc, d_state, d_proj, d_pnrm,
+        d_noise, d_scal, d_counters, d_upartials;
+    bool adjacency_valid = false, fof_valid_ = false;
+    float average_edge = 0.f;
+    long long proj_n = 0;
+
+    // HEAD-literal cube table
+    DeviceBuffer d_sdf;
+    SdfGridView sdf{nullptr, 0, 0, 0, 0.f, 0.f, 0.f, 0.f};
+
+    // stats
+    float timings[T_COUNT] = {0};
+    int64_t counters[16] = {0};
+    int launches = 0;
+
+    // z-slab sharding
+    int rank = 0, world = 1;
+    bool emulate = false;
+    long long emu_voff = 0, emu_foff = 0;
+    NcclApi nccl;
+    void* comm = nullptr;
+    DeviceBuffer d_gather;
+    int64_t slab[8] = {0};
+    bool gathered = false;
+
+    // direct evaluation service (mcc2.cpp:699-705)
+    bool svc_object = false;
+    std::vector<uint32_t> svc_program;
+    bool svc_uses_sdf = false;
+    bool svc_x = false;
+    int svc_n = 0;
+    DeviceBuffer d_svc_x, d_svc_f, d_svc_g;
+    PinnedBuffer h_svc_f, h_svc_g;
+} g;
+
+void ensure_init(int device = -1) {
+    if (g.ready) return;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        fprintf(stderr, "implisolid_b200: no CUDA device available (%s); this library has no CPU path\n",
+                e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+        abort();
+    }
+    if (device < 0) {
+        const char* s = getenv("ISD_DEVICE");
+        if (!s) s = getenv("LOCAL_RANK");
+        device = s ? atoi(s) : 0;
+        if (device >= count) device = device % count;
+    }
+    ISD_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    ISD_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) {
+        fprintf(stderr, "implisolid_b200: device %d is sm_%d%d; this build is sm_100a only\n", device, prop.major, prop.minor);
+        abort();
+    }
+    g.device = device;
+    ISD_CUDA(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
+    for (auto& ev : g.ev) ISD_CUDA(cudaEventCreate(&ev));
+    // tables derived from the reference's own (mc_tables.h)
+    uint16_t info[256];
+    for (int i = 0; i < 256; ++i) info[i] = (uint16_t)(ISD_MC_NTRI[i] | (ISD_MC_OWNED[i] << 8));
+    ISD_CUDA(cudaMemcpyToSymbol(c_case_info, info, sizeof(info)));
+    ISD_CUDA(cudaMemcpyToSymbol(c_tri_table, ISD_MC_TRI, sizeof(ISD_MC_TRI)));
+    g.h_small.reserve(4096);
+    g.ready = true;
+}
+
+inline void launched() { g.launches++; }
+#define ISD_LAUNCH_CHECK() do { ISD_CUDA(cudaGetLastError()); launched(); } while (0)
+
+void upload_program(const std::vector<uint32_t>& words) {
+    ISD_CUDA(cudaMemcpyToSymbolAsync(c_program, words.data(), words.size() * sizeof(uint32_t), 0, cudaMemcpyHostToDevice, g.stream));
+}
+
+ShapeCompiler::Program compile_shape(const char* shape_json, bool ignore_root_matrix, int cube_mode) {
+    ShapeOptions opt;
+    opt.cube_mode = cube_mode;
+    ShapeCompiler compiler(opt);
+    std::unique_ptr<ShapeNode> tree = compiler.parse(shape_json, ignore_root_matrix);
+    ShapeCompiler::Program p = compiler.compile(*tree);
+    if (p.uses_sdf_grid && g.sdf.v == nullptr) {
+        fprintf(stderr, "implisolid_b200: \"gpu.cube_mode\":1 needs isd_set_sdf_grid() first\n");
+        abort();
+    }
+    return p;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// marching cubes stage
+// ---------------------------------------------------------------------------------------------------------------------
+void slab_layers(int S, int rank, int world, int* z_begin, int* z_end) {
+    const long long layers = S - 3;                       // cube layers z in [1, S-2)
+    *z_begin = 1 + (int)((long long)rank * layers / world);
+    *z_end = 1 + (int)((long long)(rank + 1) * layers / world);
+}
+
+void setup_grid(const McSettings& s) {
+    const int S = s.resolution + 5;                       // skip_count_l + skip_count_h, marching_cubes.hpp:178-181
+    GridDesc& gd = g.grid;
+    gd.S = S;
+    gd.pitch = (S + 3) & ~3;
+    gd.plane = (long long)gd.pitch * S;
+    gd.xmin = s.box.xmin; gd.ymin = s.box.ymin; gd.zmin = s.box.zmin;
+    gd.wx = (s.box.xmax - s.box.xmin) / (float)s.resolution;
+    gd.wy = (s.box.ymax - s.box.ymin) / (float)s.resolution;
+    gd.wz = (s.box.zmax - s.box.zmin) / (float)s.resolution;
+    gd.two_wx = 2 * gd.wx; gd.two_wy = 2 * gd.wy; gd.two_wz = 2 * gd.wz;
+    gd.xi0 = s.box.xmin / gd.wx - 2; gd.yi0 = s.box.ymin / gd.wy - 2; gd.zi0 = s.box.zmin / gd.wz - 2;
+    int zb, ze;
+    slab_layers(S, g.rank, g.world, &zb, &ze);
+    McDesc& m = g.mc;
+    m.emit_z0 = zb;
+    m.zc_end = ze;
+    m.scan_z0 = (zb > 1) ? zb - 1 : zb;
+    if (g.world == 1) { gd.z0 = 0; gd.nz = S; }
+    else { gd.z0 = zb - 1; gd.nz = (ze - zb) + 2; }
+    m.NX = S - 3;
+    m.K = (m.NX + 31) / 32;
+    m.n_chunks = (long long)(ze - m.scan_z0) * m.NX * m.K;
+    m.ghost_chunks = (long long)(zb - m.scan_z0) * m.NX * m.K;
+    m.g = gd;
+    g.S = S;
+}
+
+void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog) {
+    setup_grid(s);
+    const GridDesc& gd = g.grid;
+    McDesc& m = g.mc;
+    const size_t field_bytes = (size_t)gd.plane * gd.nz * sizeof(float);
+    g.d_field.reserve(field_bytes);
+    const long long n_chunks = m.n_chunks;
+    const long long padded = (n_chunks + kScanTile - 1) / kScanTile * kScanTile;
+    g.d_counts.reserve(padded * sizeof(uint16_t));
+    g.d_offsets.reserve((n_chunks + 1) * sizeof(uint2));
+    g.d_active.reserve(n_chunks * sizeof(unsigned));
+    const int scan_blocks = (int)(padded / kScanTile);
+    g.d_partials.reserve((size_t)scan_blocks * sizeof(Triple));
+    g.d_totals.reserve(64);
+    uint8_t* dbg_cases = nullptr;
+    g.have_cases = false;
+    if (s.debug_cases) {
+        g.d_cases.reserve((size_t)(m.zc_end - m.scan_z0) * m.NX * m.NX);
+        dbg_cases = g.d_cases.as<uint8_t>();
+        g.have_cases = true;
+    }
+
+    ISD_CUDA(cudaEventRecord(g.ev[0], g.stream));
+    {   // K1
+        const long long quads = (long long)(gd.pitch / 4) * gd.S * gd.nz;
+        const long long blocks = (quads + kFieldThreads - 1) / kFieldThreads;
+        k_eval_field<<<(unsigned)blocks, kFieldThreads, 0, g.stream>>>(gd, g.sdf, g.d_field.as<float>());
+        ISD_LAUNCH_CHECK();
+    }
+    ISD_CUDA(cudaEventRecord(g.ev[1], g.stream));
+    {   // K2
+        const int layers = m.zc_end - m.scan_z0;
+        dim3 grid(m.K, (m.NX + kTY - 1) / kTY, (layers + kTZ - 1) / kTZ);
+        k_mc_classify<<<grid, 256, 0, g.stream>>>(m, g.d_field.as<float>(), g.d_counts.as<uint16_t>(), dbg_cases);
+        ISD_LAUNCH_CHECK();
+    }
+    {   // K3
+        k_scan_reduce<<<scan_blocks, kScanThreads, 0, g.stream>>>(g.d_counts.as<uint16_t>(), n_chunks, g.d_partials.as<Triple>());
+        ISD_LAUNCH_CHECK();
+        k_scan_partials<<<1, kScanThreads, 0, g.stream>>>(g.d_partials.as<Triple>(), scan_blocks, g.d_totals.as<unsigned>());
+        ISD_LAUNCH_CHECK();
+        k_scan_apply<<<scan_blocks, kScanThreads, 0, g.stream>>>(g.d_counts.as<uint16_t>(), n_chunks, g.d_partials.as<Triple>(),
+                                                                g.d_offsets.as<uint2>(), g.d_active.as<unsigned>());
+        ISD_LAUNCH_CHECK();
+    }
+    // totals (and the ghost layer's share) back to the host: the only read-back before the mesh
+    unsigned* h = g.h_small.as<unsigned>();
+    ISD_CUDA(cudaMemcpyAsync(h, g.d_totals.ptr, 3 * sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));
+    h[4] = 0; h[5] = 0;
+    if (m.ghost_chunks > 0)
+        ISD_CUDA(cudaMemcpyAsync(h + 4, g.d_offsets.as<uint2>() + m.ghost_chunks, sizeof(uint2), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaEventRecord(g.ev[2], g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    const long long scan_v = h[0], scan_f = h[1];
+    const unsigned n_active = h[2];
+    const long long ghost_v = h[4], ghost_f = h[5];
+    const long long nv = scan_v - ghost_v, nf = scan_f - ghost_f;
+
+    long long voff = 0, foff = 0, gnv = nv, gnf = nf;
+    if (g.world > 1) {
+        if (g.emulate) {
+            voff = g.emu_voff; foff = g.emu_foff;
+        } else {
+            // the one collective of the path: {nv, nf} of every slab (16 bytes per rank)
+            g.d_gather.reserve((size_t)g.world * 2 * sizeof(int64_t) + 64);
+            int64_t* dg = g.d_gather.as<int64_t>();
+            int64_t* hs = reinterpret_cast<int64_t*>(g.h_small.as<char>() + 256);
+            hs[0] = nv; hs[1] = nf;
+            ISD_CUDA(cudaMemcpyAsync(dg + 2 * g.world, hs, 2 * sizeof(int64_t), cudaMemcpyHostToDevice, g.stream));
+            g.nccl.check(g.nccl.AllGather(dg + 2 * g.world, dg, 2, kNcclInt64, g.comm, g.stream), "ncclAllGather");
+            ISD_CUDA(cudaMemcpyAsync(hs + 2, dg, (size_t)g.world * 2 * sizeof(int64_t), cudaMemcpyDeviceToHost, g.stream));
+            ISD_CUDA(cudaStreamSynchronize(g.stream));
+            gnv = 0; gnf = 0;
+            for (int r = 0; r < g.world; ++r) {
+                if (r == g.rank) { voff = gnv; foff = gnf; }
+                gnv += hs[2 + 2 * r]; gnf += hs[3 + 2 * r];
+            }
+        }
+    }
+    if (gnv >= (1ll << 31) || gnf >= (1ll << 31)) {
+        fprintf(stderr, "implisolid_b200: mesh too large for 32-bit indices (%lld vertices, %lld faces)\n", gnv, gnf);
+        abort();
+    }
+    g.d_verts.reserve((size_t)(nv > 0 ? nv : 1) * 3 * sizeof(float));
+    g.d_faces.reserve((size_t)(nf > 0 ? nf : 1) * 3 * sizeof(int));
+    if (n_active > 0) {   // K4
+        EmitArgs ea;
+        ea.vbase = voff - ghost_v; ea.fbase = foff - ghost_f;
+        ea.v_local0 = ghost_v; ea.f_local0 = ghost_f;
+        const unsigned blocks = (n_active + kEmitWarps - 1) / kEmitWarps;
+        k_mc_emit<<<blocks, kEmitWarps * 32, 0, g.stream>>>(m, ea, g.d_field.as<float>(), g.d_offsets.as<uint2>(), g.d_active.as<unsigned>(),
+                                                            n_active, g.d_verts.as<float>(), g.d_faces.as<int>());
+        ISD_LAUNCH_CHECK();
+    }
+    ISD_CUDA(cudaEventRecord(g.ev[3], g.stream));
+    g.nv = nv; g.nf = nf;
+    g.gathered = false;
+    g.slab[0] = m.emit_z0; g.slab[1] = m.zc_end; g.slab[2] = voff; g.slab[3] = foff;
+    g.slab[4] = nv; g.slab[5] = nf; g.slab[6] = gnv; g.slab[7] = gnf;
+    g.counters[0] = (int64_t)gd.S * gd.S * gd.nz;
+    g.counters[1] = (int64_t)(m.zc_end - m.emit_z0) * m.NX * m.NX;
+    g.counters[2] = n_active;
+    g.counters[14] = (int64_t)field_bytes;
+    g.counters[15] = g.counters[0];
+    (void)prog;
+}
+
+// all ranks end up with the whole stitched mesh (vertices of rank r at [voff_r, voff_r + nv_r))
+void gather_mesh() {
+    if (g.world == 1 || g.gathered || g.emulate) return;
+    int64_t* hs = reinterpret_cast<int64_t*>(g.h_small.as<char>() + 256);
+    const long long gnv = g.slab[6], gnf = g.slab[7];
+    DeviceBuffer all_v, all_f;
+    all_v.reserve((size_t)(gnv > 0 ? gnv : 1) * 3 * sizeof(float));
+    all_f.reserve((size_t)(gnf > 0 ? gnf : 1) * 3 * sizeof(int));
+    g.nccl.check(g.nccl.GroupStart(), "ncclGroupStart");
+    long long vo = 0, fo = 0;
+    for (int r = 0; r < g.world; ++r) {
+        const long long rv = hs[2 + 2 * r], rf = hs[3 + 2 * r];
+        if (rv > 0)
+            g.nccl.check(g.nccl.Broadcast(g.d_verts.ptr, all_v.as<float>() + vo * 3, (size_t)rv * 3, kNcclFloat32, r, g.comm, g.stream), "ncclBroadcast");
+        if (rf > 0)
+            g.nccl.check(g.nccl.Broadcast(g.d_faces.ptr, all_f.as<int>() + fo * 3, (size_t)rf * 3, kNcclInt32, r, g.comm, g.stream), "ncclBroadcast");
+        vo += rv; fo += rf;
+    }
+    g.nccl.check(g.nccl.GroupEnd(), "ncclGroupEnd");
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    g.d_verts.release(); g.d_faces.release();
+    g.d_verts = all_v; g.d_faces = all_f;
+    g.nv = gnv; g.nf = gnf;
+    g.gathered = true;
+    g.host_valid = false;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// OB02 stages
+// ---------------------------------------------------------------------------------------------------------------------
+void exclusive_scan_u32(const unsigned* in, long long n, unsigned* out /* n + 1 */) {
+    const int blocks = (int)((n + kUScanTile - 1) / kUScanTile);
+    g.d_upartials.reserve((size_t)(blocks > 0 ? blocks : 1) * sizeof(unsigned));
+    if (blocks == 0) { ISD_CUDA(cudaMemsetAsync(out, 0, sizeof(unsigned), g.stream)); return; }
+    k_uscan_reduce<<<blocks, kUScanThreads, 0, g.stream>>>(in, n, g.d_upartials.as<unsigned>());
+    ISD_LAUNCH_CHECK();
+    k_uscan_partials<<<1, kUScanThreads, 0, g.stream>>>(g.d_upartials.as<unsigned>(), blocks);
+    ISD_LAUNCH_CHECK();
+    k_uscan_apply<<<blocks, kUScanThreads, 0, g.stream>>>(in, n, g.d_upartials.as<unsigned>(), out);
+    ISD_LAUNCH_CHECK();
+}
+
+inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
+
+// umbrella CSR (always) and faces-of-faces (resampling only); the face list does not change between OB02 steps
+void build_adjacency(bool need_fof) {
+    const int nv = (int)g.nv, nf = (int)g.nf;
+    if (!g.adjacency_valid) {
+        g.d_deg.reserve((size_t)(nv + 1) * sizeof(unsigned));
+        g.d_cursor.reserve((size_t)(nv + 1) * sizeof(unsigned));
+        g.d_uoff.reserve((size_t)(nv + 2) * sizeof(unsigned));
+        g.d_uitems.reserve((size_t)nf * 3 * sizeof(int) + 16);
+        ISD_CUDA(cudaMemsetAsync(g.d_deg.ptr, 0, (size_t)(nv + 1) * sizeof(unsigned), g.stream));
+        ISD_CUDA(cudaMemsetAsync(g.d_cursor.ptr, 0, (size_t)(nv + 1) * sizeof(unsigned), g.stream));
+        k_vertex_degree<<<blocks_for((long long)nf * 3, 256), 256, 0, g.stream>>>(g.d_faces.as<int>(), nf, g.d_deg.as<unsigned>());
+        ISD_LAUNCH_CHECK();
+        exclusive_scan_u32(g.d_deg.as<unsigned>(), nv, g.d_uoff.as<unsigned>());
+        k_umbrella_fill<<<blocks_for((long long)nf * 3, 256), 256, 0, g.stream>>>(g.d_faces.as<int>(), nf, g.d_uoff.as<unsigned>(),
+                                                                                 g.d_cursor.as<unsigned>(), g.d_uitems.as<int>());
+        ISD_LAUNCH_CHECK();
+        k_umbrella_sort<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>());
+        ISD_LAUNCH_CHECK();
+        g.adjacency_valid = true;
+        g.fof_valid_ = false;
+    }
+    if (need_fof && !g.fof_valid_) {
+        g.d_fof.reserve((size_t)nf * 3 * sizeof(int) + 16);
+        k_faces_of_faces<<<blocks_for((long long)nf * 3, 256), 256, 0, g.stream>>>(g.d_faces.as<int>(), nf, g.d_uoff.as<unsigned>(),
+                                                                                  g.d_uitems.as<int>(), g.d_fof.as<int>());
+        ISD_LAUNCH_CHECK();
+        g.fof_valid_ = true;
+    }
+}
+
+void compute_centroids() {
+    const int nf = (int)g.nf;
+    g.d_cen.reserve((size_t)nf * 3 * sizeof(float) + 16);
+    k_centroids<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>());
+    ISD_LAUNCH_CHECK();
+}
+
+// polygonize_step_1 (polygonizer_algorithm_ob02.hpp:94-106) -> process2_vertex_resampling_relaxation_v1
+void vertex_resampling_step(float c) {
+    const int nv = (int)g.nv, nf = (int)g.nf;
+    if (nf == 0) return;
+    build_adjacency(true);
+    compute_centroids();
+    g.d_nrm.reserve((size_t)nf * 3 * sizeof(float) + 16);
+    g.d_w.reserve((size_t)nf * sizeof(float) + 16);
+    k_unit_gradients<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, g.d_cen.as<float>(), nf, g.d_nrm.as<float>());
+    ISD_LAUNCH_CHECK();
+    k_face_weights<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.d_cen.as<float>(), g.d_nrm.as<float>(), g.d_fof.as<int>(), nf, c, g.d_w.as<float>());
+    ISD_LAUNCH_CHECK();
+    k_resample<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(), g.d_w.as<float>(), g.d_cen.as<float>(),
+                                                          g.d_verts.as<float>());
+    ISD_LAUNCH_CHECK();
+}
+
+// make_alpha_list (centroids_projection.cpp:144-194)
+std::vector<float> make_alpha_list(float initial_step_size, float min_step_size, float max_dist, int max_iter) {
+    const float unit_of_length = max_dist;
+    std::vector<float> alphas;
+    float step_size = initial_step_size;
+    while (step_size > min_step_size) {
+        step_size = step_size * 0.5;
+        const int total_steps = (int)(std::floor(max_dist / std::abs(step_size) + 0.001));
+        const int max_steps = std::min(max_iter, total_steps);
+        for (int i = 1; i < max_steps + 1; i += 2) {
+            const float alpha = ((float)i) * step_size;
+            alphas.push_back(alpha / unit_of_length);
+            alphas.push_back(-alpha / unit_of_length);
+        }
+    }
+    return alphas;
+}
+
+// boost::random::mt11213b(seed 12) + uniform_01<float>, as make_random_pm1 uses them
+// (vectorised_algorithms/make_random_pm1.hpp:15-28); published Matsumoto-Nishimura parameters.
+struct Mt11213b {
+    enum { N = 351, M = 175 };
+    uint32_t x[N];
+    int i;
+    explicit Mt11213b(uint32_t seed) {
+        x[0] = seed;
+        for (int k = 1; k < N; ++k) x[k] = 1812433253u * (x[k - 1] ^ (x[k - 1] >> 30)) + (uint32_t)k;
+        i = N;
+    }
+    uint32_t next() {
+        if (i >= N) {
+            const uint32_t upper = ~0u << 19, lower = ~upper;
+            for (int k = 0; k < N; ++k) {
+                const uint32_t y = (x[k] & upper) | (x[(k + 1) % N] & lower);
+                x[k] = x[(k + M) % N] ^ (y >> 1) ^ ((y & 1u) ? 0xccab8ee7u : 0u);
+            }
+            i = 0;
+        }
+        uint32_t z = x[i++];
+        z ^= (z >> 11);
+        z ^= (z << 7) & 0x31b6ab00u;
+        z ^= (z << 15) & 0xffe50000u;
+        z ^= (z >> 17);
+        return z;
+    }
+    float uniform01() {
+        for (;;) {
+            const float factor = 1.0f / ((float)0xffffffffu + 1.0f);
+            const float r = (float)next() * factor;
+            if (r < 1.0f) return r;
+        }
+    }
+};
+
+// polygonize_step_2 (polygonizer_algorithm_ob02.hpp:108-116) -> centroids_projection (centroids_projection.cpp:1219-1311)
+void projection_step(bool enable_qem, bool exact_reduce) {
+    const int nv = (int)g.nv, nf = (int)g.nf;
+    if (nf == 0) return;
+    ISD_CUDA(cudaEventRecord(g.ev[6], g.stream));
+    g.d_len3.reserve((size_t)nf * 3 * sizeof(float) + 16);
+    g.d_scal.reserve(64);
+    g.d_counters.reserve(sizeof(Ob02Counters));
+    float* d_avg = g.d_scal.as<float>();
+    double* d_acc = reinterpret_cast<double*>(g.d_scal.as<char>() + 16);
+    k_edge_lengths<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_len3.as<float>());
+    ISD_LAUNCH_CHECK();
+    if (exact_reduce) {
+        k_sum_serial_float<<<1, 32, 0, g.stream>>>(g.d_len3.as<float>(), (long long)nf * 3, nf, d_avg);
+        ISD_LAUNCH_CHECK();
+    } else {
+        ISD_CUDA(cudaMemsetAsync(d_acc, 0, sizeof(double), g.stream));
+        k_sum_double<<<296, 256, 0, g.stream>>>(g.d_len3.as<float>(), (long long)nf * 3, d_acc);
+        ISD_LAUNCH_CHECK();
+        k_finish_average<<<1, 1, 0, g.stream>>>(d_acc, nf, d_avg);
+        ISD_LAUNCH_CHECK();
+    }
+    float* h_avg = reinterpret_cast<float*>(g.h_small.as<char>() + 1024);
+    ISD_CUDA(cudaMemcpyAsync(h_avg, d_avg, sizeof(float), cudaMemcpyDeviceToHost, g.stream));
+    compute_centroids();
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    const float average_edge = *h_avg;
+    g.average_edge = average_edge;
+    std::vector<float> alphas = make_alpha_list(average_edge, 0.001f, average_edge, 20);
+    if (alphas.size() < 10) {   // the reference slices begin()+10 out of range here (centroids_projection.cpp:211)
+        fprintf(stderr, "implisolid_b200: average edge %g too small for the projection's alpha list\n", (double)average_edge);
+        abort();
+    }
+    if (alphas.size() > (size_t)kMaxAlphas) alphas.resize(kMaxAlphas);
+    ISD_CUDA(cudaMemcpyToSymbolAsync(c_alpha, alphas.data(), alphas.size() * sizeof(float), 0, cudaMemcpyHostToDevice, g.stream));
+
+    g.d_best.reserve((size_t)nf * 3 * sizeof(float) + 16);
+    g.d_fc.reserve((size_t)nf * sizeof(float) + 16);
+    g.d_state.reserve((size_t)nf + 16);
+    g.d_proj.reserve((size_t)nf * 3 * sizeof(float) + 16);
+    g.d_pnrm.reserve((size_t)nf * 3 * sizeof(float) + 16);
+    ISD_CUDA(cudaMemsetAsync(g.d_counters.ptr, 0, sizeof(Ob02Counters), g.stream));
+    ProjectArgs a;
+    a.verts = g.d_verts.as<float>(); a.faces = g.d_faces.as<int>(); a.cen = g.d_cen.as<float>(); a.noise = nullptr;
+    a.avg_edge = d_avg; a.best = g.d_best.as<float>(); a.fc = g.d_fc.as<float>(); a.state = g.d_state.as<unsigned char>();
+    a.out = g.d_proj.as<float>(); a.nrm_out = g.d_pnrm.as<float>(); a.counters = g.d_counters.as<Ob02Counters>();
+    a.n = nf; a.n_alpha_full = (int)alphas.size();
+    k_project_search<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a, 0);
+    ISD_LAUNCH_CHECK();
+    Ob02Counters* hc = reinterpret_cast<Ob02Counters*>(g.h_small.as<char>() + 2048);
+    ISD_CUDA(cudaMemcpyAsync(hc, g.d_counters.ptr, sizeof(Ob02Counters), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    if (hc->c[10] > 0) {
+        // rare: direction types 2..6 for the left-overs; type 2 needs make_random_pm1(n, 1e-6), centroid i <- draws 3i..3i+2
+        std::vector<float> noise((size_t)nf * 3);
+        Mt11213b rng(12);
+        const float amplitude = 0.000001f;
+        for (size_t i = 0; i < noise.size(); ++i) noise[i] = (float)((rng.uniform01() * 2.0 - 1.0) * amplitude);
+        g.d_noise.reserve(noise.size() * sizeof(float));
+        ISD_CUDA(cudaMemcpyAsync(g.d_noise.ptr, noise.data(), noise.size() * sizeof(float), cudaMemcpyHostToDevice, g.stream));
+        a.noise = g.d_noise.as<float>();
+        k_project_search<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a, 1);
+        ISD_LAUNCH_CHECK();
+        ISD_CUDA(cudaStreamSynchronize(g.stream));   // noise lives on the host stack frame until the copy is done
+    }
+    k_project_finish<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a);
+    ISD_LAUNCH_CHECK();
+    ISD_CUDA(cudaMemcpyAsync(hc, g.d_counters.ptr, sizeof(Ob02Counters), cudaMemcpyDeviceToHost, g.stream));
+    g.proj_n = nf;
+    ISD_CUDA(cudaEventRecord(g.ev[7], g.stream));
+    if (enable_qem) {   // centroids_projection.cpp:1272-1310: the mesh only changes when QEM is on
+        build_adjacency(false);
+        k_qem<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(), g.d_proj.as<float>(),
+                                                        g.d_pnrm.as<float>(), d_avg, g.d_verts.as<float>());
+        ISD_LAUNCH_CHECK();
+    }
+    ISD_CUDA(cudaEventRecord(g.ev[8], g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    for (int i = 0; i < 7; ++i) g.counters[3 + i] += (int64_t)hc->c[i];
+    g.counters[10] += (int64_t)hc->c[7];
+    g.counters[11] += (int64_t)hc->c[8];
+    g.counters[12] += (int64_t)hc->c[9];
+    float ms = 0;
+    ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[6], g.ev[7]));
+    g.timings[T_PROJECT] += ms;
+    ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[7], g.ev[8]));
+    g.timings[T_QEM] += ms;
+}
+
+void copy_mesh_to_host() {
+    if (g.host_valid) return;
+    g.h_verts.reserve((size_t)(g.nv > 0 ? g.nv : 1) * 3 * sizeof(float));
+    g.h_faces.reserve((size_t)(g.nf > 0 ? g.nf : 1) * 3 * sizeof(int));
+    ISD_CUDA(cudaEventRecord(g.ev[9], g.stream));
+    if (g.nv) ISD_CUDA(cudaMemcpyAsync(g.h_verts.ptr, g.d_verts.ptr, (size_t)g.nv * 3 * sizeof(float), cudaMemcpyDeviceToHost, g.stream));
+    if (g.nf) ISD_CUDA(cudaMemcpyAsync(g.h_faces.ptr, g.d_faces.ptr, (size_t)g.nf * 3 * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaEventRecord(g.ev[10], g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    float ms = 0;
+    ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[9], g.ev[10]));
+    g.timings[T_COPY] = ms;
+    g.host_valid = true;
+}
+
+// grand_algorithm (mcc2.cpp:309-444)
+void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out) {
+    if (g.active) {
+        fprintf(stderr, "Error: There are non-deallocated geometry resources. Call finit_geometry() first. Not doing anything.");
+        fprintf(stderr, "build_geometry() called in a bad state.");
+        return;
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    for (float& t : g.timings) t = 0;
+    for (int64_t& c : g.counters) c = 0;
+    g.launches = 0;
+    g.host_valid = false;
+    g.adjacency_valid = false;
+    g.fof_valid_ = false;
+    g.proj_n = 0;
+    ShapeCompiler::Program prog = compile_shape(shape_json, s.ignore_root_matrix, s.cube_mode);
+    upload_program(prog.words);
+    g.keep_field = true;
+    run_marching_cubes(s, prog);                                   // polygonize_step_0
+    const bool any_ob02 = s.overall_repeats > 0 && (s.vresampl_iters > 0 || s.projection_enabled);
+    if (any_ob02 && g.world > 1 && !g.emulate) gather_mesh();      // OB02 runs on the stitched mesh, replicated
+    for (int overall_iter = 0; overall_iter < s.overall_repeats; ++overall_iter) {
+        if (s.vresampl_iters > 0) {
+            ISD_CUDA(cudaEventRecord(g.ev[4], g.stream));
+            for (int i = 0; i < s.vresampl_iters; ++i) vertex_resampling_step(s.vresampl_c);   // polygonize_step_1
+            ISD_CUDA(cudaEventRecord(g.ev[5], g.stream));
+            ISD_CUDA(cudaStreamSynchronize(g.stream));
+            float ms = 0;
+            ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[4], g.ev[5]));
+            g.timings[T_RESAMPLE] += ms;
+        }
+        if (s.projection_enabled) projection_step(s.qem_enabled, s.exact_reduce != 0);     // polygonize_step_2
+        const bool is_last = overall_iter == s.overall_repeats - 1;
+        if (s.subdiv_enabled && (s.overall_repeats <= 1 || is_last) && s.verbose)
+            fprintf(stderr, "implisolid_b200: subdivision (polygonize_step_3) is outside this library's scope; skipped\n");
+    }
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    float ms = 0;
+    ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[0], g.ev[1])); g.timings[T_FIELD] = ms;
+    ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[1], g.ev[2])); g.timings[T_CLASSIFY] = ms;
+    ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[2], g.ev[3])); g.timings[T_EMIT] = ms;
+    if (copy_out) copy_mesh_to_host();
+    g.active = true;                                               // polygonize_terminate
+    g.counters[13] = g.launches;
+    g.timings[T_TOTAL] = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+
+}  // namespace
+
+// =====================================================================================================================
+extern "C" {
+
+int isd_init(int device) { ensure_init(device); return 0; }
+void isd_shutdown(void) {
+    if (!g.ready) return;
+    cudaStreamSynchronize(g.stream);
+    if (g.comm) { g.nccl.CommDestroy(g.comm); g.comm = nullptr; }
+}
+uint64_t isd_stream(void) { ensure_init(); return (uint64_t)(uintptr_t)g.stream; }
+
+void build_geometry(const char* shape_parameters_json, const char* mc_parameters_json) {
+    const McSettings s = parse_mc_settings(mc_parameters_json);
+    ensure_init();
+    grand_algorithm(shape_parameters_json, s, /*copy_out=*/true);
+}
+void build_geometry_u(const char* shape_parameters_json, const char* mc_parameters_json, const char* /*call_specs*/) {
+    build_geometry(shape_parameters_json, mc_parameters_json);
+}
+void isd_build_geometry_device(const char* shape_parameters_json, const char* mc_parameters_json) {
+    const McSettings s = parse_mc_settings(mc_parameters_json);
+    ensure_init();
+    grand_algorithm(shape_parameters_json, s, /*copy_out=*/false);
+}
+const REAL* isd_device_verts(void) { return g.d_verts.as<float>(); }
+const int* isd_device_faces(void) { return g.d_faces.as<int>(); }
+
+int get_f_size(void) { return (int)g.nf; }
+int get_v_size(void) { return (int)g.nv; }
+void get_v(REAL* v_out, int vcount) {
+    if (g.ready) copy_mesh_to_host();
+    const size_t n = (size_t)g.nv * 3;
+    if (n) memcpy(v_out, g.h_verts.ptr, n * sizeof(float));
+    if ((long long)vcount * 3 != (long long)n) fprintf(stderr, "sizes dont match: %g %d\n", n / 3., vcount);
+}
+void get_f(int* f_out, int fcount) {
+    if (g.ready) copy_mesh_to_host();
+    const size_t n = (size_t)g.nf * 3;
+    if (n) memcpy(f_out, g.h_faces.ptr, n * sizeof(int));
+    if ((long long)fcount * 3 != (long long)n) fprintf(stderr, "sizes dont match: %g %d\n", n / 3., fcount);
+}
+void* get_v_ptr(void) {
+    if (!g.ready) return nullptr;
+    copy_mesh_to_host();
+    return g.h_verts.ptr;
+}
+void* get_f_ptr(void) {
+    if (!g.ready) return nullptr;
+    copy_mesh_to_host();
+    return g.h_faces.ptr;
+}
+void finish_geometry(void) { g.active = false; }
+
+// ---- direct evaluation ------------------------------------------------------------------------------------------------
+int set_object(const char* shape_parameters_json, bool ignore_root_matrix) {
+    if (g.svc_object) {
+        fprintf(stderr, "Error: You cannot unset() the object before a set_object(json).\n");
+        return 0;
+    }
+    ensure_init();
+    ShapeCompiler::Program p = compile_shape(shape_parameters_json, ignore_root_matrix, 0);
+    g.svc_program = p.words;
+    g.svc_object = true;
+    return 1;
+}
+bool unset_object(int id) {
+    if (!g.svc_object) {
+        fprintf(stderr, "Error: You cannot unset() the object before a set_object(json).\n");
+        return false;
+    }
+    if (id <= 0) { fprintf(stderr, "Incorrect ID: use the same id returned by set_object(json).\n"); return false; }
+    if (id != 1) { fprintf(stderr, "Incorrect ID. For now, The only id is 1\n"); return false; }
+    g.svc_program.clear();
+    g.svc_object = false;
+    return true;
+}
+bool set_x(void* verts, int n) {
+    if (g.svc_x) {
+        fprintf(stderr, "Error: You set() before unset()ing the previous set().\n");
+        return false;
+    }
+    if (n < 0 || n >= 10000 * 5) {
+        fprintf(stderr, "Error: n is outside [0, 50000].\n");
+        return false;
+    }
+    ensure_init();
+    const size_t n3 = (size_t)(n > 0 ? n : 1) * 3 * sizeof(float);
+    g.d_svc_x.reserve(n3); g.d_svc_f.reserve(n3 / 3); g.d_svc_g.reserve(n3);
+    g.h_svc_f.reserve(n3 / 3); g.h_svc_g.reserve(n3);
+    memset(g.h_svc_f.ptr, 0, n3 / 3);
+    memset(g.h_svc_g.ptr, 0, n3);
+    if (n > 0) {
+        ISD_CUDA(cudaMemcpyAsync(g.d_svc_x.ptr, verts, (size_t)n * 3 * sizeof(float), cudaMemcpyHostToDevice, g.stream));
+        ISD_CUDA(cudaStreamSynchronize(g.stream));      // the caller's buffer is copied, like the reference does (:781-785)
+    }
+    g.svc_n = n;
+    g.svc_x = true;
+    return true;
+}
+void unset_x(void) {
+    if (!g.svc_x) {
+        fprintf(stderr, "Error: You cannot unset() before a set().\n");
+        return;
+    }
+    g.svc_x = false;
+    g.svc_n = 0;
+}
+static void svc_eval(int mode) {
+    if (g.svc_n == 0) return;
+    upload_program(g.svc_program);
+    k_eval_points<<<blocks_for(g.svc_n, 128), 128, 0, g.stream>>>(g.sdf, g.d_svc_x.as<float>(), g.svc_n, g.d_svc_f.as<float>(),
+                                                                 g.d_svc_g.as<float>(), mode);
+    ISD_LAUNCH_CHECK();
+    if (mode & 1) ISD_CUDA(cudaMemcpyAsync(g.h_svc_f.ptr, g.d_svc_f.ptr, (size_t)g.svc_n * sizeof(float), cudaMemcpyDeviceToHost, g.stream));
+    if (mode & 2) ISD_CUDA(cudaMemcpyAsync(g.h_svc_g.ptr, g.d_svc_g.ptr, (size_t)g.svc_n * 3 * sizeof(float), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+}
+void calculate_implicit_values(void) {
+    if (!g.svc_x || !g.svc_object) {
+        fprintf(stderr, "Error: You need to set_x() and set_object() first.\n");
+        return;
+    }
+    svc_eval(1);
+}
+void* get_values_ptr(void) { return g.h_svc_f.ptr; }
+int get_values_size(void) { return g.svc_n; }
+void calculate_implicit_gradients(bool normalize_and_invert) {
+    if (!g.svc_x || !g.svc_object) {
+        fprintf(stderr, "Error: You need to set_x() and set_object() first.\n");
+        return;
+    }
+    svc_eval(2 | (normalize_and_invert ? 4 : 0));
+}
+void* get_gradients_ptr(void) {
+    if (!g.svc_x || !g.svc_object) {
+        fprintf(stderr, "Error: You need to set_x() and set_object() first.\n");
+        return nullptr;
+    }
+    return g.h_svc_g.ptr;
+}
+int get_gradients_size(void) {
+    if (!g.svc_x || !g.svc_object) {
+        fprintf(stderr, "Error: You need to set_x() and set_object() first.\n");
+        return 0;
+    }
+    return g.svc_n * 3;
+}
+
+void* get_pointset_ptr(char*) { return nullptr; }
+int get_pointset_size(char*) { return 0; }
+void about(void) {
+    fprintf(stderr, "Build Info: \n%s %s\n", __DATE__, __TIME__);
+    fprintf(stderr, "implisolid_b200: sm_100a CUDA implementation of the ImpliSolid polygonization path (field eval, marching cubes, OB02)\n");
+    fprintf(stderr, "CONFIG: ROOT_TOLERANCE=%g \n", (double)kRootTolerance);
+}
+
+// ---- extensions -----------------------------------------------------------------------------------------------------
+int isd_last_timings(float* out_ms, int cap) {
+    int n = cap < (int)T_COUNT ? cap : (int)T_COUNT;
+    for (int i = 0; i < n; ++i) out_ms[i] = g.timings[i];
+    return n;
+}
+int isd_last_counters(int64_t* out, int cap) {
+    int n = cap < 16 ? cap : 16;
+    for (int i = 0; i < n; ++i) out[i] = g.counters[i];
+    return n;
+}
+int isd_grid_size(void) { return g.S; }
+int isd_get_field(float* out, int64_t count) {
+    if (!g.ready || g.S == 0 || g.world != 1) return 1;
+    const int S = g.S;
+    if (count != (int64_t)S * S * S) return 2;
+    ISD_CUDA(cudaMemcpy2DAsync(out, (size_t)S * sizeof(float), g.d_field.ptr, (size_t)g.grid.pitch * sizeof(float), (size_t)S * sizeof(float),
+                               (size_t)S * S, cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    return 0;
+}
+int isd_get_case_codes(uint8_t* out, int64_t count) {
+    if (!g.ready || !g.have_cases) return 1;
+    const int64_t n = (int64_t)(g.mc.zc_end - g.mc.scan_z0) * g.mc.NX * g.mc.NX;
+    if (count != n) return 2;
+    ISD_CUDA(cudaMemcpyAsync(out, g.d_cases.ptr, (size_t)n, cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    return 0;
+}
+float isd_average_edge(void) { return g.average_edge; }
+int isd_get_projected_centroids(float* out, int64_t count) {
+    if (!g.ready || g.proj_n == 0 || count != g.proj_n * 3) return 1;
+    ISD_CUDA(cudaMemcpyAsync(out, g.d_proj.ptr, (size_t)count * sizeof(float), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    return 0;
+}
+int isd_get_centroid_normals(float* out, int64_t count) {
+    if (!g.ready || g.proj_n == 0 || count != g.proj_n * 3) return 1;
+    ISD_CUDA(cudaMemcpyAsync(out, g.d_pnrm.ptr, (size_t)count * sizeof(float), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    return 0;
+}
+
+void isd_set_sdf_grid(int nx, int ny, int nz, float h, float ox, float oy, float oz, const float* values) {
+    ensure_init();
+    const size_t n = (size_t)nx * ny * nz;
+    g.d_sdf.reserve(n * sizeof(float));
+    ISD_CUDA(cudaMemcpy(g.d_sdf.ptr, values, n * sizeof(float), cudaMemcpyHostToDevice));
+    g.sdf = SdfGridView{g.d_sdf.as<float>(), nx, ny, nz, h, ox, oy, oz};
+}
+
+static void load_mesh(const float* verts, int nv, const int* faces, int nf) {
+    g.d_verts.reserve((size_t)(nv > 0 ? nv : 1) * 3 * sizeof(float));
+    g.d_faces.reserve((size_t)(nf > 0 ? nf : 1) * 3 * sizeof(int));
+    if (verts && nv) ISD_CUDA(cudaMemcpyAsync(g.d_verts.ptr, verts, (size_t)nv * 3 * sizeof(float), cudaMemcpyHostToDevice, g.stream));
+    if (nf) ISD_CUDA(cudaMemcpyAsync(g.d_faces.ptr, faces, (size_t)nf * 3 * sizeof(int), cudaMemcpyHostToDevice, g.stream));
+    g.nv = nv; g.nf = nf;
+    g.adjacency_valid = false; g.fof_valid_ = false; g.host_valid = false;
+}
+
+void isd_ob02_on_mesh(const char* shape_parameters_json, float* verts, int nv, const int* faces, int nf, int resample_iters, float c,
+                      int projection, int qem) {
+    ensure_init();
+    ShapeCompiler::Program p = compile_shape(shape_parameters_json, false, 0);
+    upload_program(p.words);
+    for (int64_t& v : g.counters) v = 0;
+    load_mesh(verts, nv, faces, nf);
+    for (int i = 0; i < resample_iters; ++i) vertex_resampling_step(c);
+    if (projection) projection_step(qem != 0, true);
+    ISD_CUDA(cudaMemcpyAsync(verts, g.d_verts.ptr, (size_t)nv * 3 * sizeof(float), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+}
+void isd_faces_of_faces(const int* faces, int nf, int nv, int* out_3nf) {
+    ensure_init();
+    load_mesh(nullptr, nv, faces, nf);
+    build_adjacency(true);
+    ISD_CUDA(cudaMemcpyAsync(out_3nf, g.d_fof.ptr, (size_t)nf * 3 * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+}
+void isd_umbrella(const int* faces, int nf, int nv, int* offsets_nv1, int* items_3nf) {
+    ensure_init();
+    load_mesh(nullptr, nv, faces, nf);
+    build_adjacency(false);
+    ISD_CUDA(cudaMemcpyAsync(offsets_nv1, g.d_uoff.ptr, (size_t)(nv + 1) * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaMemcpyAsync(items_3nf, g.d_uitems.ptr, (size_t)nf * 3 * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+}
+
+void isd_eval_points(const char* shape_parameters_json, int ignore_root_matrix, const float* xyz, int64_t n, float* f_out, float* grad_out) {
+    ensure_init();
+    if (n <= 0) return;
+    ShapeCompiler::Program p = compile_shape(shape_parameters_json, ignore_root_matrix != 0, 0);
+    upload_program(p.words);
+    DeviceBuffer dx, df, dg;
+    dx.reserve((size_t)n * 3 * sizeof(float)); df.reserve((size_t)n * sizeof(float)); dg.reserve((size_t)n * 3 * sizeof(float));
+    ISD_CUDA(cudaMemcpyAsync(dx.ptr, xyz, (size_t)n * 3 * sizeof(float), cudaMemcpyHostToDevice, g.stream));
+    k_eval_points<<<blocks_for(n, 128), 128, 0, g.stream>>>(g.sdf, dx.as<float>(), n, df.as<float>(), dg.as<float>(), grad_out ? 3 : 1);
+    ISD_LAUNCH_CHECK();
+    ISD_CUDA(cudaMemcpyAsync(f_out, df.ptr, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, g.stream));
+    if (grad_out) ISD_CUDA(cudaMemcpyAsync(grad_out, dg.ptr, (size_t)n * 3 * sizeof(float), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    dx.release(); df.release(); dg.release();
+}
+
+// ---- z-slab sharding ----------------------------------------------------------------------------------------------------
+int isd_dist_unique_id(uint8_t* id128) {
+    if (!g.nccl.load()) return 1;
+    NcclApi::unique_id id;
+    g.nccl.check(g.nccl.GetUniqueId(&id), "ncclGetUniqueId");
+    memcpy(id128, &id, 128);
+    return 0;
+}
+int isd_dist_init(int rank, int world, const uint8_t* id128) {
+    ensure_init();
+    if (world <= 1) { g.rank = 0; g.world = 1; return 0; }
+    if (!g.nccl.load()) abort();
+    NcclApi::unique_id id;
+    memcpy(&id, id128, 128);
+    g.nccl.check(g.nccl.CommInitRank(&g.comm, world, id, rank), "ncclCommInitRank");
+    g.rank = rank; g.world = world; g.emulate = false;
+    return 0;
+}
+void isd_dist_finalize(void) {
+    if (g.comm) { g.nccl.CommDestroy(g.comm); g.comm = nullptr; }
+    g.rank = 0; g.world = 1; g.emulate = false;
+}
+int isd_dist_emulate(int rank, int world) {
+    g.rank = rank; g.world = world; g.emulate = world > 1;
+    g.emu_voff = 0; g.emu_foff = 0;
+    return 0;
+}
+void isd_dist_set_offsets(int64_t voff, int64_t foff) { g.emu_voff = voff; g.emu_foff = foff; }
+int isd_dist_last_slab(int64_t* out8) {
+    for (int i = 0; i < 8; ++i) out8[i] = g.slab[i];
+    return 0;
+}
+void isd_dist_gather_mesh(void) { gather_mesh(); }
+
+}  // extern "C"

@@ -1,0 +1,527 @@
+// K5-K9 — the OB02 mesh-optimisation steps on the device-resident mesh.
+//
+// Reference (paths relative to /root/reference/js_iteration_2/):
+//   adjacency            mesh_algorithms.hpp:50-209 (make_edge_lookup, build_faces_of_faces, make_neighbour_faces_of_vertex)
+//   vertex resampling    vertex_resampling.hpp:47-225, apply_v_s_to_mc_buffers.hpp:280-326
+//   centroid projection  centroids_projection.cpp:70-82,144-362,421-1311, polygoniser/bisection.hpp:117-459
+//   QEM                  qem.hpp:256-599
+// The reference runs every step as whole-array passes over shrinking index sets (std::map / vector<vector>
+// adjacency, one eval_implicit call per alpha over all still-active centroids).  Every centroid's search and every
+// vertex's update is independent of the others, so here one thread owns one centroid (or vertex) and walks the whole
+// sequence — direction types, alphas, bisection — in registers, calling the flattened CSG program inline.  Field
+// values are bit-identical to the reference's, so the first alpha that flips the sign is the same one.
+#pragma once
+#include <cuda_runtime.h>
+#include "field_kernel.cuh"
+
+namespace isd {
+
+constexpr float kRootTolerance = (float)(0.001 / 10.0);     // configs.hpp:33
+constexpr float kMinGradientLen = 0.000001f;                 // configs.hpp:57
+constexpr int kBisectionMaxIter = 100;                       // ours: the reference has no cap (bisection.hpp:204,415-437)
+constexpr int kMaxAlphas = 512;
+
+__constant__ float c_alpha[kMaxAlphas];      // make_alpha_list result (host), centroids_projection.cpp:144-194
+
+// counters: [0..6] centroids resolved by direction type, [7] failed, [8] bisection capped, [9] bisected,
+// [10] centroids still unresolved after phase A
+struct Ob02Counters { unsigned long long c[12]; };
+
+__device__ __forceinline__ float norm2f(float x, float y, float z) { return sqrtf(x * x + y * y + z * z); }
+__device__ __forceinline__ float sign_tol(float v) { return (v > kRootTolerance) ? 1.0f : (v < -kRootTolerance) ? -1.0f : 0.0f; }
+
+__device__ __forceinline__ float eval_f(const SdfGridView& sdf, float x, float y, float z) {
+    float cx[1] = {x}, cy[1] = {y}, cz[1] = {z}, out[1];
+    eval_values<1>(ConstProgram(), sdf, cx, cy, cz, out);
+    return out[0];
+}
+
+// ---- generic exclusive scan of a u32 array (three launches) ----------------------------------------------------------
+constexpr int kUScanThreads = 256, kUScanItems = 4, kUScanTile = kUScanThreads * kUScanItems;
+
+__device__ __forceinline__ unsigned block_exclusive_u32(unsigned mine, unsigned* total) {
+    __shared__ unsigned s_w[kUScanThreads / 32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    unsigned inc = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned v = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += v;
+    }
+    if (lane == 31) s_w[w] = inc;
+    __syncthreads();
+    unsigned base = 0, sum = 0;
+#pragma unroll
+    for (int i = 0; i < kUScanThreads / 32; ++i) {
+        if (i < w) base += s_w[i];
+        sum += s_w[i];
+    }
+    __syncthreads();
+    *total = sum;
+    return base + inc - mine;
+}
+__global__ void __launch_bounds__(kUScanThreads) k_uscan_reduce(const unsigned* __restrict__ in, long long n, unsigned* __restrict__ partials) {
+    const long long first = ((long long)blockIdx.x * kUScanThreads + threadIdx.x) * kUScanItems;
+    unsigned s = 0;
+#pragma unroll
+    for (int i = 0; i < kUScanItems; ++i)
+        if (first + i < n) s += in[first + i];
+    unsigned total;
+    block_exclusive_u32(s, &total);
+    if (threadIdx.x == 0) partials[blockIdx.x] = total;
+}
+__global__ void __launch_bounds__(kUScanThreads) k_uscan_partials(unsigned* __restrict__ partials, int nblocks) {
+    unsigned carry = 0;
+    for (int base = 0; base < nblocks; base += kUScanThreads) {
+        const int i = base + threadIdx.x;
+        const unsigned mine = (i < nblocks) ? partials[i] : 0u;
+        unsigned total;
+        const unsigned ex = block_exclusive_u32(mine, &total);
+        if (i < nblocks) partials[i] = carry + ex;
+        carry += total;
+    }
+}
+// out[i] = exclusive prefix; out[n] = total (out has n + 1 entries)
+__global__ void __launch_bounds__(kUScanThreads) k_uscan_apply(const unsigned* __restrict__ in, long long n, const unsigned* __restrict__ partials,
+                                                             unsigned* __restrict__ out) {
+    const long long first = ((long long)blockIdx.x * kUScanThreads + threadIdx.x) * kUScanItems;
+    unsigned v[kUScanItems], s = 0;
+#pragma unroll
+    for (int i = 0; i < kUScanItems; ++i) { v[i] = (first + i < n) ? in[first + i] : 0u; s += v[i]; }
+    unsigned total;
+    unsigned run = partials[blockIdx.x] + block_exclusive_u32(s, &total);
+#pragma unroll
+    for (int i = 0; i < kUScanItems; ++i) {
+        if (first + i < n) out[first + i] = run;
+        run += v[i];
+        if (first + i == n - 1) out[n] = run;
+    }
+}
+
+// ---- K6 adjacency ------------------------------------------------------------------------------------------------
+// make_neighbour_faces_of_vertex (mesh_algorithms.hpp:178-209): faces around a vertex in ascending face index
+__global__ void k_vertex_degree(const int* __restrict__ faces, int nf, unsigned* __restrict__ deg) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nf * 3) return;
+    atomicAdd(&deg[faces[i]], 1u);
+}
+__global__ void k_umbrella_fill(const int* __restrict__ faces, int nf, const unsigned* __restrict__ offsets, unsigned* __restrict__ cursor,
+                                int* __restrict__ items) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nf * 3) return;
+    const int v = faces[i];
+    const unsigned slot = atomicAdd(&cursor[v], 1u);
+    items[offsets[v] + slot] = i / 3;
+}
+__global__ void k_umbrella_sort(int nv, const unsigned* __restrict__ offsets, int* __restrict__ items) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nv) return;
+    const unsigned b = offsets[v], e = offsets[v + 1];
+    for (unsigned i = b + 1; i < e; ++i) {          // insertion sort; umbrellas hold ~6 faces
+        const int key = items[i];
+        unsigned j = i;
+        while (j > b && items[j - 1] > key) { items[j] = items[j - 1]; --j; }
+        items[j] = key;
+    }
+}
+// make_edge_lookup + build_faces_of_faces (mesh_algorithms.hpp:50-131).  The reference's map keeps, per undirected
+// edge, the first face that inserted it and the last face that found it; a face's neighbour across the edge is the
+// first one unless that is the face itself.  Both are read here from the (ascending) umbrella of one end vertex.
+__global__ void k_faces_of_faces(const int* __restrict__ faces, int nf, const unsigned* __restrict__ offsets, const int* __restrict__ items,
+                                 int* __restrict__ fof) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nf * 3) return;
+    const int f = i / 3, j = i - f * 3;
+    const int a = faces[f * 3 + j], b = faces[f * 3 + (j + 1) % 3];
+    int first = -1, last = -1, count = 0, prev = -1;
+    for (unsigned k = offsets[a], e = offsets[a + 1]; k < e; ++k) {
+        const int g = items[k];
+        if (g == prev) continue;        // a face listed twice (repeated vertex) is still one face
+        prev = g;
+        const int g0 = faces[g * 3], g1 = faces[g * 3 + 1], g2 = faces[g * 3 + 2];
+        // does g have the undirected edge {a,b}?  (consecutive corners, cyclically — always true for a triangle holding both)
+        const bool has = (a != b) ? ((g0 == b) || (g1 == b) || (g2 == b)) : false;
+        if (has) {
+            if (first < 0) first = g;
+            last = g;
+            ++count;
+        }
+    }
+    int r;
+    if (count <= 1) r = 0;              // boundary edge: faces_of_edges[e][1] keeps its zero initialisation (:66, :100)
+    else r = (first != f) ? first : last;
+    fof[i] = r;
+}
+
+// ---- K5 centroids and their unit gradients ---------------------------------------------------------------------------
+// compute_centroids (implicit_vectorised_algorithms.hpp:161-171) + eval_gradient + normalize_1111
+// (vectorised_algorithms/normalise_inplace.hpp:60-70)
+__global__ void __launch_bounds__(128) k_centroids(const float* __restrict__ verts, const int* __restrict__ faces, int nf, float* __restrict__ cen) {
+    const int f = blockIdx.x * 128 + threadIdx.x;
+    if (f >= nf) return;
+    const int f0 = faces[f * 3], f1 = faces[f * 3 + 1], f2 = faces[f * 3 + 2];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) cen[f * 3 + d] = (verts[f0 * 3 + d] + verts[f1 * 3 + d] + verts[f2 * 3 + d]) / 3.0f;
+}
+__global__ void __launch_bounds__(128) k_unit_gradients(SdfGridView sdf, const float* __restrict__ pts, int n, float* __restrict__ nrm) {
+    const int i = blockIdx.x * 128 + threadIdx.x;
+    if (i >= n) return;
+    float f, g0, g1, g2;
+    eval_value_gradient(ConstProgram(), sdf, pts[i * 3], pts[i * 3 + 1], pts[i * 3 + 2], f, g0, g1, g2);
+    const float norm = norm2f(g0, g1, g2);
+    nrm[i * 3] = g0 / norm; nrm[i * 3 + 1] = g1 / norm; nrm[i * 3 + 2] = g2 / norm;
+}
+
+// ---- K7 vertex resampling -------------------------------------------------------------------------------------------
+// kij / wi (vertex_resampling.hpp:47-91).  std::acos(float) is glibc's acosf in the reference; here acos is taken in
+// double and rounded, which agrees with a correctly rounded acosf except in rare double-rounding cases.
+__global__ void __launch_bounds__(128) k_face_weights(const float* __restrict__ cen, const float* __restrict__ nrm, const int* __restrict__ fof,
+                                                      int nf, float c, float* __restrict__ w) {
+    const int i = blockIdx.x * 128 + threadIdx.x;
+    if (i >= nf) return;
+    float ki = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        const int o = fof[i * 3 + j];
+        float mimj = nrm[i * 3] * nrm[o * 3] + nrm[i * 3 + 1] * nrm[o * 3 + 1] + nrm[i * 3 + 2] * nrm[o * 3 + 2];
+        if (mimj > 1.0f) mimj = 1.0f;
+        if (mimj < -1.0f) mimj = -1.0f;
+        const float pipj = norm2f(cen[i * 3] - cen[o * 3], cen[i * 3 + 1] - cen[o * 3 + 1], cen[i * 3 + 2] - cen[o * 3 + 2]);
+        float kij = 0.0f;
+        if (pipj != 0.0f) kij = (float)acos((double)mimj) / pipj;
+        ki += kij;
+    }
+    w[i] = (float)(1.0 + (double)(c * ki));     // REAL w = 1.0 + c*ki: the sum is formed in double
+}
+// vertex_resampling_VV1 (vertex_resampling.hpp:93-141)
+__global__ void __launch_bounds__(128) k_resample(int nv, const unsigned* __restrict__ offsets, const int* __restrict__ items, const float* __restrict__ w,
+                                                  const float* __restrict__ cen, float* __restrict__ verts) {
+    const int v = blockIdx.x * 128 + threadIdx.x;
+    if (v >= nv) return;
+    const unsigned b = offsets[v], e = offsets[v + 1];
+    float sum_w = 0.0f;
+    for (unsigned k = b; k < e; ++k) sum_w += w[items[k]];
+    float nx = 0.0f, ny = 0.0f, nz = 0.0f;
+    for (unsigned k = b; k < e; ++k) {
+        const int f = items[k];
+        const float wj = w[f] / sum_w;
+        nx += wj * cen[f * 3]; ny += wj * cen[f * 3 + 1]; nz += wj * cen[f * 3 + 2];
+    }
+    verts[v * 3] = nx; verts[v * 3 + 1] = ny; verts[v * 3 + 2] = nz;
+}
+
+// ---- K8 centroid projection -----------------------------------------------------------------------------------------
+// compute_average_edge_length (centroids_projection.cpp:70-82): three lengths per face
+__global__ void __launch_bounds__(128) k_edge_lengths(const float* __restrict__ verts, const int* __restrict__ faces, int nf, float* __restrict__ len3) {
+    const int j = blockIdx.x * 128 + threadIdx.x;
+    if (j >= nf) return;
+    const int f0 = faces[j * 3], f1 = faces[j * 3 + 1], f2 = faces[j * 3 + 2];
+    const float* a = verts + f0 * 3; const float* b = verts + f1 * 3; const float* c = verts + f2 * 3;
+    len3[j * 3] = norm2f(a[0] - b[0], a[1] - b[1], a[2] - b[2]);
+    len3[j * 3 + 1] = norm2f(a[0] - c[0], a[1] - c[1], a[2] - c[2]);
+    len3[j * 3 + 2] = norm2f(c[0] - b[0], c[1] - b[1], c[2] - b[2]);
+}
+// The reference accumulates the 3*Nf lengths into one float, in order.  "exact" mode repeats that serial sum bit for
+// bit (one warp: coalesced loads, lane 0 adds in order); the default is a pairwise tree in double, which is the
+// better-conditioned value and what large meshes should use (the serial float sum stagnates beyond ~10^7 terms).
+__global__ void __launch_bounds__(32) k_sum_serial_float(const float* __restrict__ v, long long n, int nf, float* __restrict__ out) {
+    const int lane = threadIdx.x;
+    float acc = 0.0f;
+    for (long long base = 0; base < n; base += 32) {
+        const float mine = (base + lane < n) ? v[base + lane] : 0.0f;
+        const int cnt = (n - base < 32) ? (int)(n - base) : 32;
+        for (int l = 0; l < cnt; ++l) {
+            const float t = __shfl_sync(0xffffffffu, mine, l);
+            acc += t;
+        }
+    }
+    if (lane == 0) *out = (float)(acc / (3. * nf));     // edge_length/(3.*nfaces): double division, rounded to REAL
+}
+__global__ void __launch_bounds__(256) k_sum_double(const float* __restrict__ v, long long n, double* __restrict__ acc) {
+    __shared__ double s[8];
+    double t = 0.0;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) t += (double)v[i];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) t += __shfl_xor_sync(0xffffffffu, t, d);
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = t;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double b = 0.0;
+        for (int i = 0; i < 8; ++i) b += s[i];
+        atomicAdd(acc, b);
+    }
+}
+__global__ void k_finish_average(const double* __restrict__ acc, int nf, float* __restrict__ out) { *out = (float)(*acc / (3. * nf)); }
+
+struct ProjectArgs {
+    const float* verts;
+    const int* faces;
+    const float* cen;        // centroids (input)
+    const float* noise;      // make_random_pm1(n, 1e-6) for direction type 2 (phase B only)
+    const float* avg_edge;   // device scalar
+    float* best;             // per centroid: candidate on the other side of the surface
+    float* fc;               // f(centroid)
+    unsigned char* state;    // bit 0: already success; bit 1: still searching after phase A
+    float* out;              // projected centroids
+    float* nrm_out;          // unit gradient at projected centroids
+    Ob02Counters* counters;
+    int n;
+    int n_alpha_full;
+};
+
+// produce_facet_normals(force_normalisation = true)  implicit_vectorised_algorithms.hpp:52-133
+__device__ __forceinline__ void facet_normal(const float* __restrict__ verts, const int* __restrict__ faces, int fi, float& x, float& y, float& z) {
+    const float min_area = (30.0f * ((1.0f / 1000.0f) / 1000.0f)) * (30.0f * ((1.0f / 1000.0f) / 1000.0f));   // configs.hpp:38-48
+    const float min_norm_sq = min_area * min_area;
+    const int f0 = faces[fi * 3], f1 = faces[fi * 3 + 1], f2 = faces[fi * 3 + 2];
+    const float x1 = verts[f1 * 3] - verts[f0 * 3], y1 = verts[f1 * 3 + 1] - verts[f0 * 3 + 1], z1 = verts[f1 * 3 + 2] - verts[f0 * 3 + 2];
+    const float x2 = verts[f2 * 3] - verts[f0 * 3], y2 = verts[f2 * 3 + 1] - verts[f0 * 3 + 1], z2 = verts[f2 * 3 + 2] - verts[f0 * 3 + 2];
+    x = y1 * z2 - z1 * y2;
+    y = z1 * x2 - x1 * z2;
+    z = x1 * y2 - y1 * x2;
+    const float n2 = x * x + y * y + z * z;
+    if (n2 < min_norm_sq) {
+        const float o = 1.0f / sqrtf(3.0f);
+        x = o; y = o; z = o;
+    } else {
+        const float n = sqrtf(n2);
+        x = x / n; y = y / n; z = z / n;
+    }
+}
+
+// tries the alphas of one direction; returns true (and the trial point) at the first sign change  (:604-892)
+__device__ __forceinline__ bool try_direction(const SdfGridView& sdf, float cx, float cy, float cz, float dx, float dy, float dz, float edge,
+                                              int n_alpha, float s_c, float& bx, float& by, float& bz) {
+    for (int ai = 0; ai < n_alpha; ++ai) {
+        const float c = edge * c_alpha[ai];                 // (length_factor * alpha) * 4.0 / 4.0
+        const float x = cx + c * dx, y = cy + c * dy, z = cz + c * dz;
+        const float f = eval_f(sdf, x, y, z);
+        if (sign_tol(f) * s_c <= 0.0f) { bx = x; by = y; bz = z; return true; }
+    }
+    return false;
+}
+
+// set_centers_on_surface, search part.  phase 0: direction types 0 (gradient) and 1 (facet normal);
+// phase 1: types 2..6 for the centroids phase 0 left over (needs the host-generated noise).
+__global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, ProjectArgs a, int phase) {
+    const int i = blockIdx.x * 128 + threadIdx.x;
+    if (i >= a.n) return;
+    const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
+    const float edge = *a.avg_edge;
+    float bx = -10.0f, by = -10.0f, bz = -10.0f;
+    bool ok = false;
+    int type = -1;
+    float s_c;
+    if (phase == 0) {
+        float fc, g0, g1, g2;
+        eval_value_gradient(ConstProgram(), sdf, cx, cy, cz, fc, g0, g1, g2);
+        fc = eval_f(sdf, cx, cy, cz);      // eval_implicit's value (the gradient pass may round metaball sums differently)
+        a.fc[i] = fc;
+        // normalise_inplace(g, min_gradient_len)  normalise_inplace.hpp:19-58
+        float norm = norm2f(g0, g1, g2);
+        norm = (norm < kMinGradientLen) ? 1.0f : norm;
+        const float factor = 1.0f / norm;
+        g0 = g0 * factor; g1 = g1 * factor; g2 = g2 * factor;
+        s_c = sign_tol(fc);
+        if (s_c < 0.0f) { g0 = -g0; g1 = -g1; g2 = -g2; }
+        const float d0 = -g0 * s_c, d1 = -g1 * s_c, d2 = -g2 * s_c;
+        ok = try_direction(sdf, cx, cy, cz, d0, d1, d2, edge, a.n_alpha_full, s_c, bx, by, bz);
+        type = 0;
+        if (!ok) {
+            float nx, ny, nz;
+            facet_normal(a.verts, a.faces, i, nx, ny, nz);
+            ok = try_direction(sdf, cx, cy, cz, nx, ny, nz, edge, 10, s_c, bx, by, bz);
+            type = 1;
+        }
+        if (!ok) atomicAdd(&a.counters->c[10], 1ull);
+    } else {
+        if (!(a.state[i] & 2)) return;
+        s_c = sign_tol(a.fc[i]);
+        float nx, ny, nz;
+        facet_normal(a.verts, a.faces, i, nx, ny, nz);
+        // type 2: facet normal x noise, normalize_1111   (create_directions_bundle :230-262; add_inplace works on copies)
+        const float px = a.noise[i * 3], py = a.noise[i * 3 + 1], pz = a.noise[i * 3 + 2];
+        float zx = ny * pz - nz * py, zy = nz * px - nx * pz, zz = nx * py - ny * px;
+        {
+            const float n = norm2f(zx, zy, zz);
+            zx = zx / n; zy = zy / n; zz = zz / n;
+        }
+        ok = try_direction(sdf, cx, cy, cz, zx, zy, zz, edge, 10, s_c, bx, by, bz);
+        type = 2;
+        if (!ok) {   // type 3: facet normal x previous direction, normalise_inplace
+            float wx = ny * zz - nz * zy, wy = nz * zx - nx * zz, wz = nx * zy - ny * zx;
+            float n = norm2f(wx, wy, wz);
+            n = (n < kMinGradientLen) ? 1.0f : n;
+            const float factor = 1.0f / n;
+            wx = wx * factor; wy = wy * factor; wz = wz * factor;
+            ok = try_direction(sdf, cx, cy, cz, wx, wy, wz, edge, 10, s_c, bx, by, bz);
+            type = 3;
+        }
+        for (int dim = 0; dim < 3 && !ok; ++dim) {
+            ok = try_direction(sdf, cx, cy, cz, dim == 0 ? 1.0f : 0.0f, dim == 1 ? 1.0f : 0.0f, dim == 2 ? 1.0f : 0.0f, edge, 10, s_c, bx, by, bz);
+            type = 4 + dim;
+        }
+    }
+    if (ok) {
+        a.best[i * 3] = bx; a.best[i * 3 + 1] = by; a.best[i * 3 + 2] = bz;
+        a.state[i] = 1;
+        atomicAdd(&a.counters->c[type], 1ull);
+    } else {
+        a.state[i] = 2;
+    }
+}
+
+// set_centers_on_surface, second half (:893-1214): zero tests, bisection between the centroid and the candidate,
+// final assembly; then the unit gradient at the projected centroid (compute_centroid_gradient, :1262).
+__global__ void __launch_bounds__(128) k_project_finish(SdfGridView sdf, ProjectArgs a) {
+    const int i = blockIdx.x * 128 + threadIdx.x;
+    if (i >= a.n) return;
+    const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
+    const bool already = (a.state[i] & 1) != 0;
+    float bx, by, bz;
+    if (already) { bx = a.best[i * 3]; by = a.best[i * 3 + 1]; bz = a.best[i * 3 + 2]; }
+    else {
+        bx = cx; by = cy; bz = cz;
+        atomicAdd(&a.counters->c[7], 1ull);
+    }
+    const float f2 = eval_f(sdf, bx, by, bz);
+    const bool zeros2 = fabsf(f2) <= kRootTolerance;
+    const bool zeros1 = fabsf(a.fc[i]) <= kRootTolerance;
+    if (zeros1) { bx = cx; by = cy; bz = cz; }
+    const bool zeros12 = zeros2 || zeros1;
+    float ox = cx, oy = cy, oz = cz;
+    if (already && !zeros12) {
+        float x1x = cx, x1y = cy, x1z = cz, x2x = bx, x2y = by, x2z = bz;
+        if (f2 < -kRootTolerance) { x1x = bx; x1y = by; x1z = bz; x2x = cx; x2y = cy; x2z = cz; }
+        atomicAdd(&a.counters->c[9], 1ull);
+        for (int it = 1;; ++it) {
+            const float mx = (x1x + x2x) / 2.0f, my = (x1y + x2y) / 2.0f, mz = (x1z + x2z) / 2.0f;
+            const float v = eval_f(sdf, mx, my, mz);
+            if (fabsf(v) <= kRootTolerance || it >= kBisectionMaxIter) {
+                if (fabsf(v) > kRootTolerance) atomicAdd(&a.counters->c[8], 1ull);
+                ox = mx; oy = my; oz = mz;
+                break;
+            }
+            if (v > kRootTolerance) { x2x = mx; x2y = my; x2z = mz; }
+            if (v < -kRootTolerance) { x1x = mx; x1y = my; x1z = mz; }
+        }
+    }
+    if (zeros12) { ox = bx; oy = by; oz = bz; }
+    a.out[i * 3] = ox; a.out[i * 3 + 1] = oy; a.out[i * 3 + 2] = oz;
+    float f, g0, g1, g2;
+    eval_value_gradient(ConstProgram(), sdf, ox, oy, oz, f, g0, g1, g2);
+    const float norm = norm2f(g0, g1, g2);
+    a.nrm_out[i * 3] = g0 / norm; a.nrm_out[i * 3 + 1] = g1 / norm; a.nrm_out[i * 3 + 2] = g2 / norm;
+}
+
+// ---- K9 QEM vertex update ---------------------------------------------------------------------------------------------
+// Eigen's JacobiSVD of the symmetric PSD 3x3 (qem.hpp:397-405) as a cyclic Jacobi eigen-decomposition, operation for
+// operation the same as the oracle's restatement; eigenvalues sorted descending.
+__device__ __forceinline__ void sym_eig3(const float (&Ain)[3][3], float (&w)[3], float (&V)[3][3]) {
+    float A[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) { A[i][j] = Ain[i][j]; V[i][j] = (i == j) ? 1.0f : 0.0f; }
+    for (int sweep = 0; sweep < 12; ++sweep) {
+        const float off = fabsf(A[0][1]) + fabsf(A[0][2]) + fabsf(A[1][2]);
+        if (off == 0.0f) break;
+#pragma unroll
+        for (int p = 0; p < 2; ++p)
+#pragma unroll
+            for (int q = p + 1; q < 3; ++q) {
+                if (A[p][q] == 0.0f) continue;
+                const float theta = (A[q][q] - A[p][p]) / (2.0f * A[p][q]);
+                const float t = (theta >= 0 ? 1.0f : -1.0f) / (fabsf(theta) + sqrtf(theta * theta + 1.0f));
+                const float c = 1.0f / sqrtf(t * t + 1.0f), s = t * c;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const float akp = A[k][p], akq = A[k][q];
+                    A[k][p] = c * akp - s * akq;
+                    A[k][q] = s * akp + c * akq;
+                }
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const float apk = A[p][k], aqk = A[q][k];
+                    A[p][k] = c * apk - s * aqk;
+                    A[q][k] = s * apk + c * aqk;
+                }
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const float vkp = V[k][p], vkq = V[k][q];
+                    V[k][p] = c * vkp - s * vkq;
+                    V[k][q] = s * vkp + c * vkq;
+                }
+            }
+    }
+#pragma unroll
+    for (int i = 0; i < 3; ++i) w[i] = A[i][i];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = i + 1; j < 3; ++j)
+            if (w[j] > w[i]) {
+                const float t = w[i]; w[i] = w[j]; w[j] = t;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) { const float u = V[k][i]; V[k][i] = V[k][j]; V[k][j] = u; }
+            }
+}
+
+// vertex_apply_qem + get_A_b (qem.hpp:256-599)
+__global__ void __launch_bounds__(128) k_qem(int nv, const unsigned* __restrict__ offsets, const int* __restrict__ items, const float* __restrict__ cen,
+                                             const float* __restrict__ nrm, const float* __restrict__ avg_edge, float* __restrict__ verts) {
+    const int vi = blockIdx.x * 128 + threadIdx.x;
+    if (vi >= nv) return;
+    const float maxd = *avg_edge;
+    const float o0 = verts[vi * 3], o1 = verts[vi * 3 + 1], o2 = verts[vi * 3 + 2];
+    float A[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}}, b[3] = {0, 0, 0};
+    for (unsigned k = offsets[vi], e = offsets[vi + 1]; k < e; ++k) {
+        const int ni = items[k];
+        const float Nx = nrm[ni * 3], Ny = nrm[ni * 3 + 1], Nz = nrm[ni * 3 + 2];
+        const float Px = cen[ni * 3] - o0, Py = cen[ni * 3 + 1] - o1, Pz = cen[ni * 3 + 2] - o2;
+        const float nn00 = Nx * Nx, nn01 = Nx * Ny, nn02 = Nx * Nz, nn11 = Ny * Ny, nn12 = Ny * Nz, nn22 = Nz * Nz;
+        A[0][0] += nn00; A[0][1] += nn01; A[0][2] += nn02;
+        A[1][0] += nn01; A[1][1] += nn11; A[1][2] += nn12;
+        A[2][2] += nn22; A[2][0] += nn02; A[2][1] += nn12;
+        b[0] -= nn00 * Px + nn01 * Py + nn02 * Pz;
+        b[1] -= nn01 * Px + nn11 * Py + nn12 * Pz;
+        b[2] -= nn02 * Px + nn12 * Py + nn22 * Pz;
+    }
+    float Sg[3], V[3][3];
+    sym_eig3(A, Sg, V);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) if (Sg[i] < 0) Sg[i] = 0;
+    const float tau = 680.0f;
+    const float svd_threshold = 1.0f / tau;
+    const float thr = fmaxf(Sg[0] * svd_threshold, 1.17549435e-38f);
+    int rank = 0;
+    while (rank < 3 && !(Sg[rank] < thr)) rank++;
+    float acc[3] = {0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        if (i < rank) {
+            const float utb = -(V[0][i] * b[0] + V[1][i] * b[1] + V[2][i] * b[2]);
+            const float y = utb / Sg[i];
+            acc[0] += V[0][i] * y; acc[1] += V[1][i] * y; acc[2] += V[2][i] * y;
+        }
+    }
+    const float n0 = acc[0] + o0, n1 = acc[1] + o1, n2 = acc[2] + o2;
+    if (maxd > 0) {
+        const float dx = n0 - o0, dy = n1 - o1, dz = n2 - o2;
+        const float dist2 = dx * dx + dy * dy + dz * dz;
+        if (dist2 <= maxd * maxd) {
+            verts[vi * 3] = n0; verts[vi * 3 + 1] = n1; verts[vi * 3 + 2] = n2;
+        } else {
+            const float dist = sqrtf(dist2);
+            float dl = maxd * 1.5f;
+            if (dl > dist) dl = dist;
+            verts[vi * 3] = o0 + dx / dist * dl;
+            verts[vi * 3 + 1] = o1 + dy / dist * dl;
+            verts[vi * 3 + 2] = o2 + dz / dist * dl;
+        }
+    } else {
+        verts[vi * 3] = n0; verts[vi * 3 + 1] = n1; verts[vi * 3 + 2] = n2;
+    }
+}
+
+}  // namespace isd

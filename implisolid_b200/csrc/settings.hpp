@@ -29,6 +29,9 @@ struct McSettings {
     int cube_mode;        // 0: analytic six-plane cube (default), 1: HEAD-literal SDF grid (needs isd_set_sdf_grid)
     int fast_math;        // 0: exact (no FMA contraction; parity mode), 1: contraction allowed
     int verbose;
+    int debug_cases;      // 1: keep the dense per-cube case codes for isd_get_case_codes (parity tests)
+    int exact_reduce;     // 1: mean edge length as the reference's serial float sum, bit for bit (slow); 0: pairwise double
+    int prune;            // 1: skip grid tiles proven off-surface by interval bounds (mesh identical, field not dense)
 };
 
 inline bool settings_bool(const JsonDoc& d, const char* field, bool dflt, const char* forbidden, bool* needs_abort) {
@@ -82,6 +85,9 @@ inline McSettings parse_mc_settings(const char* json) {
     s.cube_mode = d.get_int("gpu.cube_mode", 0);
     s.fast_math = d.get_int("gpu.fast_math", 0);
     s.verbose = d.get_int("gpu.verbose", 0);
+    s.debug_cases = d.get_int("gpu.debug_cases", 0);
+    s.exact_reduce = d.get_int("gpu.exact_reduce", 0);
+    s.prune = d.get_int("gpu.prune", 0);
     if (s.qem_enabled && !s.projection_enabled) {
         fprintf(stderr, "Invalid settings: QEM will not be applied if centroid projection is disabled\n");
         needs_abort = true;

@@ -1,0 +1,132 @@
+/* implisolid_b200 — C ABI of libimplisolid_b200.so
+ *
+ * Group 1-3 are, symbol for symbol, the extern "C" block the reference exports from mcc2.cpp and
+ * that its Emscripten/JS layer binds with Module.cwrap (implisolid_main.js:38-59,
+ * js/worker_api.js:121-127).  A maintainer swaps the library, not the callers.  Group 4 ("isd_")
+ * is ours: device-resident results, stage timings, z-slab sharding and parity introspection.
+ *
+ * All entry points are plain C: pointers and sizes, no C++/torch types.  Paths below are relative
+ * to /root/reference/js_iteration_2/.
+ *
+ * Protocol (mcc2.cpp:165-193, :309-319, :540-552): singleton, not re-entrant, one caller thread.
+ *   build_geometry -> get_*_size / get_* / get_*_ptr -> finish_geometry -> next build_geometry.
+ * A second build_geometry without finish_geometry logs and returns without building.  Malformed
+ * settings or an unknown shape type abort() the process after a message on stderr, as the
+ * reference does; a CUDA failure does the same.  There is no CPU fallback: without a usable
+ * sm_100 device every compute entry point aborts with a message.
+ */
+#ifndef IMPLISOLID_B200_H
+#define IMPLISOLID_B200_H
+
+#include <stdbool.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef float REAL; /* basic_data_structures.hpp:60 */
+
+/* ---- group 1: polygonization ------------------------------------------------------------ */
+/* mcc2.cpp:446-464 (decl :89).  shape_parameters_json: one node of an mp5 document
+ * (object_factory.hpp:56-758); mc_parameters_json: mc_settings (polygoniser_settings.hpp:147-305). */
+void build_geometry(const char* shape_parameters_json, const char* mc_parameters_json);
+/* mcc2.cpp:90 (declared, body commented out at :296-302; JS cwraps it, js/worker_api.js:126).
+ * call_specs is accepted and ignored (no progress callbacks natively). */
+void build_geometry_u(const char* shape_parameters_json, const char* mc_parameters_json, const char* call_specs);
+int get_v_size(void);              /* mcc2.cpp:470-473  number of vertices  */
+int get_f_size(void);              /* mcc2.cpp:466-469  number of triangles */
+void get_v(REAL* v_out, int vcount); /* mcc2.cpp:474-492  copies 3*Nv floats; logs on size mismatch */
+void get_f(int* f_out, int fcount);  /* mcc2.cpp:496-511  copies 3*Nf ints;   logs on size mismatch */
+void* get_v_ptr(void);             /* mcc2.cpp:515-519  borrowed, valid until the next build_geometry */
+void* get_f_ptr(void);             /* mcc2.cpp:521-525 */
+void finish_geometry(void);        /* mcc2.cpp:540-552 */
+
+/* ---- group 2: direct evaluation of the implicit function (normals) ------------------------ */
+int set_object(const char* shape_parameters_json, bool ignore_root_matrix); /* mcc2.cpp:726-745, returns id 1 (0 on error) */
+bool unset_object(int id);                                                  /* mcc2.cpp:747-763 */
+bool set_x(void* verts_xyz_f32, int n);                                     /* mcc2.cpp:765-798, rejects n<0 or n>=50000 */
+void unset_x(void);                                                         /* mcc2.cpp:800-812 */
+void calculate_implicit_values(void);                                       /* mcc2.cpp:815-825 */
+void* get_values_ptr(void);                                                 /* mcc2.cpp:827-829, n floats */
+int get_values_size(void);                                                  /* mcc2.cpp:830-832 */
+void calculate_implicit_gradients(bool normalize_and_invert);               /* mcc2.cpp:834-889 */
+void* get_gradients_ptr(void);                                              /* mcc2.cpp:891-900, 3n floats */
+int get_gradients_size(void);                                               /* mcc2.cpp:902-911 */
+
+/* ---- group 3: misc ------------------------------------------------------------------------ */
+void* get_pointset_ptr(char* id);  /* mcc2.cpp:203-208  debug point sets: always NULL here */
+int get_pointset_size(char* id);   /* mcc2.cpp:210-215  always 0 */
+void about(void);                  /* mcc2.cpp:574-617 */
+
+/* ---- group 4: extensions (ours) ------------------------------------------------------------ */
+/* Device selection / lifetime.  isd_init is implicit on first use (device = $ISD_DEVICE or
+ * $LOCAL_RANK or 0).  Returns 0 on success; any failure aborts. */
+int isd_init(int device);
+void isd_shutdown(void);
+/* cudaStream_t all kernels are launched on, as an integer handle (for CUDA-event timing). */
+uint64_t isd_stream(void);
+
+/* build_geometry without the device->host copy of the mesh: results stay in HBM
+ * (isd_device_verts / isd_device_faces).  get_v/get_f/get_*_ptr after this call copy lazily. */
+void isd_build_geometry_device(const char* shape_parameters_json, const char* mc_parameters_json);
+const REAL* isd_device_verts(void); /* device pointer, 3*Nv floats */
+const int* isd_device_faces(void);  /* device pointer, 3*Nf ints   */
+
+/* Per-stage device times of the last build, milliseconds, CUDA events on isd_stream().
+ * out[0]=field eval, [1]=mc classify+scan, [2]=mc emit, [3]=vertex resampling, [4]=projection,
+ * [5]=qem, [6]=device->host mesh copy, [7]=whole build (host wall clock).  Returns entries written. */
+int isd_last_timings(float* out_ms, int cap);
+/* Counters of the last build: [0]=nodes evaluated, [1]=cubes visited, [2]=active chunks,
+ * [3..9]=centroids resolved by projection direction type 0..6, [10]=projection failed,
+ * [11]=bisection capped, [12]=bisected, [13]=kernel launches, [14]=field bytes, [15]=nodes
+ * evaluated with the full program (others were proven off-surface and skipped). */
+int isd_last_counters(int64_t* out, int cap);
+
+/* Parity introspection (needs "gpu":{"keep_field":1} in mc_parameters_json for the field). */
+int isd_grid_size(void);                       /* S = resolution + 5 nodes per axis */
+int isd_get_field(float* out, int64_t count);  /* S^3 floats, x fastest (marching_cubes.hpp:264-268); 0 on success */
+int isd_get_case_codes(uint8_t* out, int64_t count); /* (S-3)^3 cube codes in scan order z,y,x (marching_cubes.hpp:1041-1057) */
+float isd_average_edge(void);                         /* mean edge length used by the last projection */
+int isd_get_projected_centroids(float* out, int64_t count); /* 3*Nf floats of the last projection */
+int isd_get_centroid_normals(float* out, int64_t count);
+
+/* HEAD-literal `cube` (cube.hpp:65-72,215-270): the SDF table it interpolates, supplied by the
+ * caller ("gpu":{"cube_mode":1} selects it). */
+void isd_set_sdf_grid(int nx, int ny, int nz, float h, float ox, float oy, float oz, const float* values);
+
+/* OB02 stages on a caller-supplied mesh (fixtures: mcc2.cpp:254-290 make_a_cube / make_a_square).
+ * verts is updated in place. */
+void isd_ob02_on_mesh(const char* shape_parameters_json, float* verts, int nv, const int* faces, int nf,
+                      int resample_iters, float c, int projection, int qem);
+/* mesh adjacency as the OB02 stages see it (mesh_algorithms.hpp:50-209) */
+void isd_faces_of_faces(const int* faces, int nf, int nv, int* out_3nf);
+void isd_umbrella(const int* faces, int nf, int nv, int* offsets_nv1, int* items_3nf);
+
+/* Points without the 50 000 cap of set_x: f and grad f at n host points (device kernel). */
+void isd_eval_points(const char* shape_parameters_json, int ignore_root_matrix, const float* xyz, int64_t n,
+                     float* f_out, float* grad_out_or_null);
+
+/* ---- z-slab sharding across the GPUs of one box (one process per GPU) ---------------------- */
+/* The library calls NCCL itself (dlopen of libnccl.so.2): one ncclAllGather of {nv,nf} per build.
+ * id128 is an ncclUniqueId made by isd_dist_unique_id on rank 0 and handed to every rank by the
+ * launcher (bench.py broadcasts it with torch.distributed).  After isd_dist_init every
+ * build_geometry evaluates only this rank's z-slab; vertex and face indices are global. */
+int isd_dist_unique_id(uint8_t* id128);
+int isd_dist_init(int rank, int world, const uint8_t* id128);
+void isd_dist_finalize(void);
+/* Test hook: emulate rank `rank` of `world` without NCCL; the caller supplies the gathered counts
+ * global vertex/face offsets of this slab through isd_dist_set_offsets (see tests/test_gpu_slabs.py). */
+int isd_dist_emulate(int rank, int world);
+void isd_dist_set_offsets(int64_t global_vertex_offset, int64_t global_face_offset);
+/* Slab owned by this rank in the last build: out = {first cube layer, end cube layer, global vertex
+ * offset, global face offset, local Nv, local Nf, global Nv, global Nf}. */
+int isd_dist_last_slab(int64_t* out8);
+/* Gather the stitched mesh on every rank (ncclAllGather of padded ranges); afterwards get_v/get_f
+ * return the global mesh on every rank. */
+void isd_dist_gather_mesh(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IMPLISOLID_B200_H */

@@ -1,0 +1,155 @@
+"""Test infrastructure: loads oracle/liboracle.so (CPU restatement of the reference) and tests/emu/libemu.so."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+from implisolid_b200.api import GeometryLibrary
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+EMU_DIR = os.path.join(ROOT, "tests", "emu")
+
+
+class Oracle(GeometryLibrary):
+    def __init__(self, path):
+        super().__init__(path, extensions=False)
+        L = self.lib
+        L.oracle_grid_size.restype = ctypes.c_int
+        L.oracle_field_ptr.restype = ctypes.POINTER(ctypes.c_float)
+        L.oracle_num_cubes.restype = ctypes.c_long
+        L.oracle_case_codes_ptr.restype = ctypes.POINTER(ctypes.c_uint8)
+        L.oracle_vertex_keys_ptr.restype = ctypes.POINTER(ctypes.c_int64)
+        L.oracle_projection_count.restype = ctypes.c_int
+        L.oracle_projected_centroids_ptr.restype = ctypes.POINTER(ctypes.c_float)
+        L.oracle_centroid_normals_ptr.restype = ctypes.POINTER(ctypes.c_float)
+        L.oracle_average_edge.restype = ctypes.c_float
+        L.oracle_alpha_list.restype = ctypes.c_int
+
+    def grid_size(self):
+        return self.lib.oracle_grid_size()
+
+    def get_field(self):
+        S = self.grid_size()
+        return np.ctypeslib.as_array(self.lib.oracle_field_ptr(), shape=(S, S, S)).copy()
+
+    def get_case_codes(self):
+        n = self.grid_size() - 3
+        return np.ctypeslib.as_array(self.lib.oracle_case_codes_ptr(), shape=(n, n, n)).copy()
+
+    def vertex_keys(self):
+        n = self.get_v_size()
+        return np.ctypeslib.as_array(self.lib.oracle_vertex_keys_ptr(), shape=(n,)).copy()
+
+    def stats(self):
+        buf = (ctypes.c_long * 9)()
+        self.lib.oracle_get_stats(buf)
+        return {"projection_by_type": list(buf[0:7]), "projection_failed": buf[7], "bisection_capped": buf[8]}
+
+    def projected_centroids(self):
+        n = self.lib.oracle_projection_count()
+        c = np.ctypeslib.as_array(self.lib.oracle_projected_centroids_ptr(), shape=(n, 3)).copy()
+        nr = np.ctypeslib.as_array(self.lib.oracle_centroid_normals_ptr(), shape=(n, 3)).copy()
+        return c, nr
+
+    def average_edge(self):
+        return float(self.lib.oracle_average_edge())
+
+    def faces_of_faces(self, faces, nv=None):
+        f = np.ascontiguousarray(faces, dtype=np.int32).reshape(-1, 3)
+        out = np.empty_like(f)
+        self.lib.oracle_faces_of_faces(f.ctypes.data_as(ctypes.c_void_p), f.shape[0], out.ctypes.data_as(ctypes.c_void_p))
+        return out
+
+    def umbrella(self, faces, nv):
+        f = np.ascontiguousarray(faces, dtype=np.int32).reshape(-1, 3)
+        off = np.empty(nv + 1, dtype=np.int32)
+        items = np.empty(f.size, dtype=np.int32)
+        self.lib.oracle_umbrella(f.ctypes.data_as(ctypes.c_void_p), f.shape[0], int(nv), off.ctypes.data_as(ctypes.c_void_p),
+                                 items.ctypes.data_as(ctypes.c_void_p))
+        return off, items
+
+    def alpha_list(self, average_edge):
+        buf = np.zeros(1024, dtype=np.float32)
+        n = self.lib.oracle_alpha_list(ctypes.c_float(average_edge), buf.ctypes.data_as(ctypes.c_void_p), 1024)
+        return buf[:n].copy()
+
+    def invert_matrix(self, m12):
+        a = np.ascontiguousarray(m12, dtype=np.float32)
+        out = np.zeros(12, dtype=np.float32)
+        self.lib.oracle_invert_matrix(a.ctypes.data_as(ctypes.c_void_p), out.ctypes.data_as(ctypes.c_void_p))
+        return out
+
+    def random_pm1(self, n, amplitude):
+        out = np.zeros((n, 3), dtype=np.float32)
+        self.lib.oracle_random_pm1(int(n), ctypes.c_float(amplitude), out.ctypes.data_as(ctypes.c_void_p))
+        return out
+
+    def ob02_on_mesh(self, shape_json, verts, faces, resample_iters=0, c=1.0, projection=0, qem=0):
+        v = np.ascontiguousarray(verts, dtype=np.float32).reshape(-1, 3).copy()
+        f = np.ascontiguousarray(faces, dtype=np.int32).reshape(-1, 3)
+        self.lib.oracle_ob02_on_mesh(shape_json.encode(), v.ctypes.data_as(ctypes.c_void_p), v.shape[0], f.ctypes.data_as(ctypes.c_void_p),
+                                     f.shape[0], int(resample_iters), ctypes.c_float(c), int(projection), int(qem))
+        return v
+
+    def set_sdf_grid(self, values, h, origin):
+        v = np.ascontiguousarray(values, dtype=np.float32)
+        nz, ny, nx = v.shape
+        self.lib.oracle_set_sdf_grid(nx, ny, nz, ctypes.c_float(h), ctypes.c_float(origin[0]), ctypes.c_float(origin[1]),
+                                     ctypes.c_float(origin[2]), v.ctypes.data_as(ctypes.c_void_p))
+
+
+def build_oracle():
+    subprocess.run(["make", "-C", ORACLE_DIR], check=True, stdout=subprocess.DEVNULL)
+    return os.path.join(ORACLE_DIR, "liboracle.so")
+
+
+_oracle = None
+
+
+def load_oracle():
+    global _oracle
+    if _oracle is None:
+        _oracle = Oracle(build_oracle())
+    return _oracle
+
+
+class Emu:
+    def __init__(self, path):
+        self.lib = ctypes.CDLL(path)
+        self.lib.emu_compile.restype = ctypes.c_int
+
+    def compile(self, shape_json, ignore_root_matrix=False):
+        words = np.zeros(16384, dtype=np.uint32)
+        stats = np.zeros(4, dtype=np.float64)
+        n = self.lib.emu_compile(shape_json.encode(), int(ignore_root_matrix), words.ctypes.data_as(ctypes.c_void_p), 16384,
+                                 stats.ctypes.data_as(ctypes.c_void_p))
+        return words[:n].copy(), {"value_depth": int(stats[0]), "frame_depth": int(stats[1]), "nodes": int(stats[2]), "flops": stats[3]}
+
+    def eval(self, shape_json, pts, ignore_root_matrix=False):
+        p = np.ascontiguousarray(pts, dtype=np.float32).reshape(-1, 3)
+        n = p.shape[0]
+        f = np.zeros(n, np.float32); f4 = np.zeros(n, np.float32); g = np.zeros((n, 3), np.float32)
+        self.lib.emu_eval(shape_json.encode(), int(ignore_root_matrix), p.ctypes.data_as(ctypes.c_void_p), n,
+                          f.ctypes.data_as(ctypes.c_void_p), f4.ctypes.data_as(ctypes.c_void_p), g.ctypes.data_as(ctypes.c_void_p))
+        return f, f4, g
+
+    def affine_inverse(self, m12):
+        a = np.ascontiguousarray(m12, dtype=np.float32)
+        out = np.zeros(12, dtype=np.float32)
+        self.lib.emu_affine_inverse(a.ctypes.data_as(ctypes.c_void_p), out.ctypes.data_as(ctypes.c_void_p))
+        return out
+
+
+_emu = None
+
+
+def load_emu():
+    global _emu
+    if _emu is None:
+        out = os.path.join(EMU_DIR, "libemu.so")
+        src = os.path.join(EMU_DIR, "emu_eval.cpp")
+        subprocess.run(["g++", "-std=c++17", "-O2", "-fPIC", "-ffp-contract=off", "-shared", "-x", "c++", "-o", out, src], check=True)
+        _emu = Emu(out)
+    return _emu
