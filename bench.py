@@ -1,0 +1,293 @@
+#!/usr/bin/env python
+"""bench.py — voxels/sec of the polygonization hot path (field eval + marching cubes + OB02) on N B200s.
+
+A step = one pass of the path over one synthetic shape spec: build_geometry(shape_json, mc_json) -> mesh.
+  N = 1 : BASELINE.json configs[1] — CSG cube minus cylinder under an affine transform, 256^3, with the OB02 steps the
+          metric names (vresampl 1 iteration, centroid projection, QEM).
+  N > 1 : z-slab sharding of the same shape with the resolution scaled so that every GPU keeps 256^3 voxels
+          (weak scaling); one ncclAllGather of {nv,nf} per step inside the library.
+value  : voxels / s, device-resident (mesh stays in HBM), CUDA events on the library's stream, L2 flushed between steps.
+e2e    : the same through the reference-facing C API with host buffers: JSON strings in, get_v/get_f copies out.
+roofline / cpu_baseline / clocks: see DESIGN.md "Measurement".
+
+`--impl reference` times the reference's own CPU algorithm for the path (the oracle restatement: the reference itself
+needs Boost/Eigen/Emscripten and cannot be built in this image) on the host cores, same workload.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "voxels/sec (eval+MC+OB02)"
+UNIT = "voxels/s"
+BASE_R = 256
+HALF = 0.8
+
+
+def workload(n_gpus):
+    from implisolid_b200 import shapes
+    # weak scaling: voxels per GPU fixed at 256^3 -> R = 256 * N^(1/3), rounded to a multiple of 8
+    R = BASE_R if n_gpus == 1 else int(round(BASE_R * n_gpus ** (1.0 / 3.0) / 8.0)) * 8
+    shape = shapes.c2_cube_minus_cylinder()
+    mc = shapes.mc_settings(R, HALF, iters=1, c=1.0, projection=1, qem=1)
+    name = "C2 cube-minus-cylinder (affine), eval+MC+OB02(resample 1, projection, QEM), R=%d, box +-%.1f" % (R, HALF)
+    return shape, mc, R, name
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+            except ValueError:
+                continue
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        med = sm[len(sm) // 2] if sm else None
+        return {"sm_mhz": med, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d.get("hbm_gbs", 6650.0)), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def fp32_peak_tflops():
+    """Non-tensor FP32 peak of this GPU, measured by tools/fp32_peak (FMUL+FADD separately rounded = exact mode)."""
+    exe = os.path.join(ROOT, "tools", "fp32_peak")
+    try:
+        out = subprocess.run([exe], capture_output=True, text=True, timeout=60).stdout.strip().splitlines()[-1]
+        d = json.loads(out)
+        return d
+    except Exception:
+        return None
+
+
+def run_reference(args):
+    """Reference arm: the reference's CPU algorithm (oracle restatement, single thread like the reference) on rank 0."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from tests.oracle_lib import load_oracle
+    shape, mc, R, name = workload(args.gpus)
+    o = load_oracle()
+    for _ in range(min(args.warmup, 1)):
+        o.polygonize(shape, mc)
+    steps = max(1, min(args.steps, 3))          # each step is the whole workload (~3 s at 256^3); bounded to a few
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        v, f = o.polygonize(shape, mc)
+    dt = (time.perf_counter() - t0) / steps
+    value = R ** 3 / dt
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": min(args.warmup, 1),
+            "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": name, "resolution": R, "nv": int(v.shape[0]), "nf": int(f.shape[0])},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port",
+                             "sample": "whole workload, %d step(s); the reference is single-threaded C++ and cannot be compiled here "
+                                       "(Boost/Eigen/Emscripten absent), so this is the oracle restatement (g++ -O2, no FMA)" % steps},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import numpy as np
+    import torch
+    import implisolid_b200
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU path")
+    torch.cuda.set_device(local_rank)
+    lib = implisolid_b200.load_library()
+    lib.lib.isd_init(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        uid = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            buf = np.zeros(128, dtype=np.uint8)
+            lib.lib.isd_dist_unique_id(buf.ctypes.data)
+            uid = torch.from_numpy(buf)
+        uid = uid.cuda()
+        dist.broadcast(uid, 0)
+        buf = uid.cpu().numpy().copy()
+        lib.lib.isd_dist_init(rank, world, buf.ctypes.data)
+
+    shape, mc, R, name = workload(world)
+    stream = torch.cuda.ExternalStream(lib.lib.isd_stream())
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")      # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def step_device():
+        lib.build_geometry_device(shape, mc)
+        lib.finish_geometry()
+
+    # ---- device-resident throughput ("value") ----
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    stage_sum = {}
+    launches = 0
+    with torch.cuda.stream(stream):
+        for i in range(args.steps):
+            flush.zero_()                      # L2 flush between timed iterations, outside the timed interval
+            starts[i].record(stream)
+            step_device()
+            ends[i].record(stream)
+            for k, v in lib.last_timings().items():
+                stage_sum[k] = stage_sum.get(k, 0.0) + v
+            launches += lib.last_counters()["launches"]
+    barrier()
+    clocks = sampler.stop()
+    ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_per_step = float(t.item()) / args.steps
+    voxels = float(R) ** 3
+    value = voxels / (ms_per_step * 1e-3)
+    counters = lib.last_counters()
+    prog = lib.last_program_stats()
+    slab = lib.last_slab()
+    stages = {k: v / args.steps for k, v in stage_sum.items()}
+
+    # ---- end to end through the reference-facing C API, host buffers in and out ("e2e") ----
+    def step_e2e():
+        lib.build_geometry(shape, mc)          # JSON strings (host) in; mesh copied to pinned host memory inside
+        v = lib.get_v()                        # get_v / get_f copy into caller-owned host arrays (mcc2.cpp:474-511)
+        f = lib.get_f()
+        lib.finish_geometry()
+        return v, f
+    for _ in range(2):
+        v, f = step_e2e()
+    barrier()
+    e2e_steps = max(3, min(args.steps, 10))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        v, f = step_e2e()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = voxels / (float(t.item()) / e2e_steps)
+    h2d = len(shape) + len(mc) + prog["words"] * 4 + 2048
+    d2h = int(v.nbytes + f.nbytes) + 64
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel, measured live (per-stage CUDA events inside the library) ----
+    hbm_peak, hbm_src = measured_peaks()
+    nodes = counters["nodes"]
+    t_field = stages["field"] * 1e-3
+    t_mc = stages["classify_scan"] * 1e-3
+    fp = fp32_peak_tflops()
+    field_tflops = prog["flops_per_point"] * counters["nodes_full_eval"] / t_field / 1e12 if t_field > 0 else 0.0
+    mc_gbs = 4.0 * nodes / t_mc / 1e9 if t_mc > 0 else 0.0
+    dominant = max(stages, key=lambda k: stages[k] if k not in ("total_host", "d2h") else -1.0)
+    roof_field = {"kernel": "k_eval_field", "bound": "fp32", "achieved": field_tflops, "peak": fp["fmul_fadd_tflops"] if fp else None,
+                  "unit": "TFLOP/s", "frac": (field_tflops / fp["fmul_fadd_tflops"]) if fp else None, "traffic": None,
+                  "peak_source": "tools/fp32_peak on this GPU: separately rounded FMUL+FADD (exact mode has no FMA contraction); "
+                                 "FFMA peak %.1f" % (fp["ffma_tflops"] if fp else float("nan")),
+                  "flops_per_node": prog["flops_per_point"], "ms": stages["field"]}
+    roof_mc = {"kernel": "k_mc_classify(+scan)", "bound": "hbm", "achieved": mc_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": mc_gbs / hbm_peak,
+               "traffic": None, "peak_source": hbm_src, "bytes_per_node": 4, "ms": stages["classify_scan"]}
+    roofline = roof_field if dominant == "field" else roof_mc
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": name, "resolution": R, "voxels_per_step": voxels, "nodes_evaluated_per_gpu": nodes, "nv": slab["global_nv"],
+                       "nf": slab["global_nf"], "l2": "flushed between timed steps (256 MB write)", "parallelism": "z-slabs x%d" % world,
+                       "fp_mode": "exact (no FMA contraction)"},
+            "stage_ms": stages, "dominant_stage": dominant, "roofline": roofline, "roofline_field": roof_field, "roofline_mc": roof_mc,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},
+            "gpu_launches": launches, "clocks": clocks}
+    if world == 1 and not args.no_cpu_baseline:
+        from tests.oracle_lib import load_oracle
+        o = load_oracle()
+        t0 = time.perf_counter()
+        ov, of = o.polygonize(shape, mc)
+        cdt = time.perf_counter() - t0
+        line["cpu_baseline"] = {"value": voxels / cdt, "unit": UNIT, "cores": 1, "kind": "port",
+                                "sample": "the whole workload once (%.1f s): oracle restatement of the single-threaded reference" % cdt,
+                                "mesh_matches_gpu": bool(of.shape == f.shape and (of == f).all())}
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -64,6 +64,7 @@ EXT_SIGNATURES = {
     "isd_device_faces": (ctypes.c_void_p, []),
     "isd_last_timings": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "isd_last_counters": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
+    "isd_last_program_stats": (ctypes.c_int, [ctypes.c_void_p]),
     "isd_grid_size": (ctypes.c_int, []),
     "isd_get_field": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int64]),
     "isd_get_case_codes": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int64]),
@@ -204,6 +205,11 @@ class GeometryLibrary:
                 "projection_by_type": [int(x) for x in buf[3:10]], "projection_failed": int(buf[10]),
                 "bisection_capped": int(buf[11]), "bisected": int(buf[12]), "launches": int(buf[13]),
                 "field_bytes": int(buf[14]), "nodes_full_eval": int(buf[15])}
+
+    def last_program_stats(self):
+        buf = np.zeros(4, dtype=np.float64)
+        self.lib.isd_last_program_stats(buf.ctypes.data)
+        return {"flops_per_point": float(buf[0]), "nodes": int(buf[1]), "words": int(buf[2]), "value_depth": int(buf[3])}
 
     def grid_size(self):
         return self.lib.isd_grid_size()

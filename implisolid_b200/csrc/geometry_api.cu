@@ -115,6 +115,7 @@ struct Context {
     float timings[T_COUNT] = {0};
     int64_t counters[16] = {0};
     int launches = 0;
+    double prog_stats[4] = {0, 0, 0, 0};   // flops/point, nodes, words, value-stack depth
 
     // z-slab sharding
     int rank = 0, world = 1;
@@ -607,6 +608,8 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     g.proj_n = 0;
     ShapeCompiler::Program prog = compile_shape(shape_json, s.ignore_root_matrix, s.cube_mode);
     upload_program(prog.words);
+    g.prog_stats[0] = prog.flops_per_point; g.prog_stats[1] = prog.num_nodes; g.prog_stats[2] = (double)prog.words.size();
+    g.prog_stats[3] = prog.value_depth;
     g.keep_field = true;
     run_marching_cubes(s, prog);                                   // polygonize_step_0
     const bool any_ob02 = s.overall_repeats > 0 && (s.vresampl_iters > 0 || s.projection_enabled);
@@ -805,6 +808,10 @@ int isd_last_counters(int64_t* out, int cap) {
     int n = cap < 16 ? cap : 16;
     for (int i = 0; i < n; ++i) out[i] = g.counters[i];
     return n;
+}
+int isd_last_program_stats(double* out4) {
+    for (int i = 0; i < 4; ++i) out4[i] = g.prog_stats[i];
+    return 4;
 }
 int isd_grid_size(void) { return g.S; }
 int isd_get_field(float* out, int64_t count) {

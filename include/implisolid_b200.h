@@ -82,6 +82,9 @@ int isd_last_timings(float* out_ms, int cap);
  * [11]=bisection capped, [12]=bisected, [13]=kernel launches, [14]=field bytes, [15]=nodes
  * evaluated with the full program (others were proven off-surface and skipped). */
 int isd_last_counters(int64_t* out, int cap);
+/* Shape program of the last build: out = {flops per point (mul and add counted separately), tree nodes,
+ * program words, value-stack depth}. */
+int isd_last_program_stats(double* out4);
 
 /* Parity introspection (needs "gpu":{"keep_field":1} in mc_parameters_json for the field). */
 int isd_grid_size(void);                       /* S = resolution + 5 nodes per axis */

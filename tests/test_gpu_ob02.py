@@ -1,0 +1,100 @@
+"""GPU parity: OB02 stages (adjacency, vertex resampling, centroid projection + bisection, QEM) vs the CPU oracle.
+
+Tolerance (north_star): vertex positions within 1e-5 of the bounding-box diagonal.  With "gpu":{"exact_reduce":1} the
+mean edge length is the reference's serial float sum, every f evaluation is bit-identical, and the projection is
+expected to agree far tighter than that (asserted below).
+"""
+import numpy as np
+import pytest
+
+from implisolid_b200 import shapes
+
+pytestmark = pytest.mark.gpu
+
+OCTA_F = np.array([[0, 2, 4], [2, 1, 4], [1, 3, 4], [3, 0, 4], [2, 0, 5], [1, 2, 5], [3, 1, 5], [0, 3, 5]], dtype=np.int32)
+OCTA_V = np.array([[1, 0, 0], [-1, 0, 0], [0, 1, 0], [0, -1, 0], [0, 0, 1], [0, 0, -1]], dtype=np.float32) * 0.45
+
+
+def _tol(half):
+    return 1e-5 * 2 * half * np.sqrt(3.0)
+
+
+def test_adjacency_octahedron_and_mc_mesh(gpu_lib, oracle):
+    off, items = gpu_lib.umbrella(OCTA_F, 6)
+    ooff, oitems = oracle.umbrella(OCTA_F, 6)
+    assert np.array_equal(off, ooff) and np.array_equal(items, oitems)
+    # known answer from mesh_algorithms.hpp:155-175 style: every vertex of an octahedron has 4 faces, ascending
+    assert (np.diff(off) == 4).all()
+    assert np.array_equal(gpu_lib.faces_of_faces(OCTA_F, 6), oracle.faces_of_faces(OCTA_F))
+    v, f = oracle.polygonize(shapes.c2_cube_minus_cylinder(), shapes.mc_settings(40, 0.8))
+    off, items = gpu_lib.umbrella(f, v.shape[0])
+    ooff, oitems = oracle.umbrella(f, v.shape[0])
+    assert np.array_equal(off, ooff) and np.array_equal(items, oitems)
+    assert np.array_equal(gpu_lib.faces_of_faces(f, v.shape[0]), oracle.faces_of_faces(f))
+
+
+@pytest.mark.parametrize("name,shape,R,half", [
+    ("sphere", shapes.c1_sphere, 28, 0.55),
+    ("cube_cyl", shapes.c2_cube_minus_cylinder, 48, 0.8),
+    ("metaballs", shapes.c3_metaballs, 40, 1.2),
+    ("chain", shapes.c4_deep_chain, 56, 1.0),
+    ("bushy", shapes.bushy_tree, 44, 0.9),
+])
+def test_full_pipeline_vs_oracle(gpu_lib, oracle, name, shape, R, half):
+    sj = shape()
+    mc = shapes.mc_settings(R, half, iters=1, c=1.0, projection=1, qem=1, exact_reduce=1)
+    oracle.build_geometry(sj, mc)
+    ov, of = oracle.get_v(), oracle.get_f()
+    oc, on = oracle.projected_centroids()
+    ost = oracle.stats()
+    oedge = oracle.average_edge()
+    oracle.finish_geometry()
+    gpu_lib.build_geometry(sj, mc)
+    gv, gf = gpu_lib.get_v(), gpu_lib.get_f()
+    gc, gn = gpu_lib.projected_centroids()
+    gst = gpu_lib.last_counters()
+    gedge = gpu_lib.average_edge()
+    gpu_lib.finish_geometry()
+    assert np.array_equal(gf, of)
+    assert abs(gedge - oedge) <= 1e-6 * oedge
+    assert gst["projection_by_type"] == ost["projection_by_type"], (gst, ost)
+    assert gst["projection_failed"] == ost["projection_failed"]
+    tol = _tol(half)
+    assert np.abs(gc - oc).max() <= tol, np.abs(gc - oc).max()
+    ok = np.isfinite(on).all(axis=1) & np.isfinite(gn).all(axis=1)
+    assert np.abs(gn[ok] - on[ok]).max() <= 1e-4
+    assert np.abs(gv - ov).max() <= tol, np.abs(gv - ov).max()
+
+
+def test_resampling_only_and_projection_without_qem(gpu_lib, oracle):
+    sj = shapes.c2_cube_minus_cylinder()
+    for kw in (dict(iters=2, c=0.4), dict(iters=0, projection=1, qem=0), dict(iters=1, c=1.0, projection=1, qem=1, repeats=2)):
+        mc = shapes.mc_settings(36, 0.8, exact_reduce=1, **kw)
+        ov, of = oracle.polygonize(sj, mc)
+        gv, gf = gpu_lib.polygonize(sj, mc)
+        assert np.array_equal(gf, of)
+        assert np.abs(gv - ov).max() <= _tol(0.8), (kw, np.abs(gv - ov).max())
+    # projection without QEM leaves the mesh untouched (centroids_projection.cpp:1304-1310)
+    mv, _ = gpu_lib.polygonize(sj, shapes.mc_settings(36, 0.8))
+    pv, _ = gpu_lib.polygonize(sj, shapes.mc_settings(36, 0.8, projection=1, qem=0))
+    assert np.array_equal(mv, pv)
+
+
+def test_ob02_on_fixture_mesh(gpu_lib, oracle):
+    sj = shapes.c1_sphere()
+    got = gpu_lib.ob02_on_mesh(sj, OCTA_V, OCTA_F, resample_iters=1, c=1.0, projection=1, qem=1)
+    want = oracle.ob02_on_mesh(sj, OCTA_V, OCTA_F, resample_iters=1, c=1.0, projection=1, qem=1)
+    assert np.abs(got - want).max() <= 1e-5
+
+
+def test_projected_centroids_lie_on_surface(gpu_lib):
+    sj = shapes.c3_metaballs()
+    gpu_lib.build_geometry(sj, shapes.mc_settings(96, 1.2, projection=1, qem=1))
+    c, _ = gpu_lib.projected_centroids()
+    st = gpu_lib.last_counters()
+    gpu_lib.finish_geometry()
+    f = gpu_lib.eval_points(sj, c)
+    resolved = sum(st["projection_by_type"])
+    assert resolved + st["projection_failed"] == c.shape[0]
+    # |f| <= ROOT_TOLERANCE for every centroid that found the surface and did not hit the bisection cap
+    assert (np.abs(f) > 1.0001e-4).sum() <= st["projection_failed"] + st["bisection_capped"]
