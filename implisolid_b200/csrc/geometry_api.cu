@@ -167,6 +167,8 @@ void ensure_init(int device = -1) {
     for (int i = 0; i < 256; ++i) info[i] = (uint16_t)(ISD_MC_NTRI[i] | (ISD_MC_OWNED[i] << 8));
     ISD_CUDA(cudaMemcpyToSymbol(c_case_info, info, sizeof(info)));
     ISD_CUDA(cudaMemcpyToSymbol(c_tri_table, ISD_MC_TRI, sizeof(ISD_MC_TRI)));
+    ISD_CUDA(cudaMemcpyToSymbol(d_case_info, info, sizeof(info)));
+    ISD_CUDA(cudaMemcpyToSymbol(d_tri_table, ISD_MC_TRI, sizeof(ISD_MC_TRI)));
     g.h_small.reserve(4096);
     g.ready = true;
 }

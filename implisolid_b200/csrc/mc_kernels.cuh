@@ -32,6 +32,9 @@ namespace isd {
 // per case: bits 0-7 triangles, bits 8-15 ISD_MC_OWNED (count + first-appearance order of edges 5,6,10)
 __constant__ uint16_t c_case_info[256];
 __constant__ int8_t c_tri_table[256 * 16];
+// the same tables in global memory for lane-divergent look-ups (constant memory serialises divergent addresses)
+__device__ uint16_t d_case_info[256];
+__device__ int8_t d_tri_table[256 * 16];
 
 struct McDesc {
     GridDesc g;
@@ -216,11 +219,8 @@ __global__ void __launch_bounds__(kEmitWarps * 32) k_mc_emit(McDesc m, EmitArgs 
                                                              const uint2* __restrict__ offsets, const unsigned* __restrict__ active,
                                                              unsigned n_active, float* __restrict__ verts, int* __restrict__ faces) {
     __shared__ float s_f[kEmitWarps][3][3][34];      // [dz+1][dy+1][x - (x0-1)]
-    __shared__ uint16_t s_info[256];
-    __shared__ int8_t s_tri[256 * 16];
-    for (int i = threadIdx.x; i < 256; i += blockDim.x) s_info[i] = c_case_info[i];
-    for (int i = threadIdx.x; i < 256 * 16; i += blockDim.x) s_tri[i] = c_tri_table[i];
-    __syncthreads();
+    const uint16_t* __restrict__ s_info = d_case_info;
+    const int8_t* __restrict__ s_tri = d_tri_table;
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const unsigned slot = blockIdx.x * kEmitWarps + w;
     if (slot >= n_active) return;

@@ -1,0 +1,40 @@
+"""CPU: the product's shape compiler (program.hpp) and program evaluator (csg_eval.cuh, compiled for the host by
+tests/emu) against the oracle's recursive tree, bit for bit."""
+import json
+
+import numpy as np
+import pytest
+
+from implisolid_b200 import shapes
+
+SHAPES = ["c1_sphere", "c2_cube_minus_cylinder", "c3_metaballs", "c4_deep_chain", "demo_moon", "simple_cone", "bushy_tree"]
+
+
+@pytest.mark.parametrize("name", SHAPES)
+def test_values_and_gradients_bit_exact(emu, oracle, name):
+    sj = getattr(shapes, name)()
+    rng = np.random.default_rng(11)
+    pts = np.concatenate([rng.uniform(-1.2, 1.2, (3000, 3)), rng.normal(0, 0.3, (1000, 3))]).astype(np.float32)
+    f1, f4, g = emu.eval(sj, pts)
+    fo = oracle.query_implicit_values(sj, pts)
+    go = oracle.query_normals(sj, pts, normalize_and_invert=False)
+    assert np.array_equal(f1.view(np.uint32), fo.view(np.uint32))
+    assert np.array_equal(f4.view(np.uint32), fo.view(np.uint32))
+    assert np.array_equal(g.view(np.uint32), go.view(np.uint32))
+
+
+def test_inverse_matches_oracle_bitwise(emu, oracle):
+    rng = np.random.default_rng(2)
+    for _ in range(200):
+        m = rng.normal(size=12).astype(np.float32)
+        assert np.array_equal(emu.affine_inverse(m).view(np.uint32), oracle.invert_matrix(m).view(np.uint32))
+
+
+def test_program_shape(emu):
+    words, st = emu.compile(shapes.c4_deep_chain())
+    assert st["nodes"] == 63 and st["frame_depth"] == 0 and st["value_depth"] == 32
+    words, st = emu.compile(shapes.bushy_tree())
+    assert st["frame_depth"] == 1
+    words, st = emu.compile(shapes.c2_cube_minus_cylinder(), ignore_root_matrix=True)
+    eye = np.array([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0], dtype=np.float32).view(np.uint32)
+    assert words[0] == 1 and np.array_equal(words[1:13], eye)       # OP_XFORM with the identity (copy_eye, object_factory.hpp:47)
