@@ -190,11 +190,12 @@ def main():
         lib.finish_geometry()
 
     # ---- device-resident throughput ("value") ----
+    sampler = ClockSampler(local_rank)
+    sampler.start()
     for _ in range(args.warmup):
         step_device()
     barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
+    sampler.rows.clear()
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     stage_sum = {}
@@ -208,6 +209,10 @@ def main():
             for k, v in lib.last_timings().items():
                 stage_sum[k] = stage_sum.get(k, 0.0) + v
             launches += lib.last_counters()["launches"]
+    barrier()
+    t_end = time.perf_counter() + 2.0
+    while len(sampler.rows) < 4 and time.perf_counter() < t_end:      # the timed region is ~25 ms: keep the same load up until
+        step_device()                                                  # nvidia-smi (100 ms period) has a few samples
     barrier()
     clocks = sampler.stop()
     ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))

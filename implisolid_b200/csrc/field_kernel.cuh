@@ -1,13 +1,21 @@
-// K1 — field evaluation over the sampling grid.
+// K1 — field evaluation over the sampling grid, tile by tile, with the sign bits marching cubes needs.
 //
-// Replaces MarchingCubes::prepare_grid + eval_shape + seal_exterior (marching_cubes.hpp:1662-1738, :895-963):
-// the reference materialises a 12 B/node coordinate array and runs the CSG tree over it with two N-sized temporaries
-// per tree node; here the coordinate of a node is computed from its index in registers, the whole flattened program
+// Replaces MarchingCubes::prepare_grid + eval_shape + seal_exterior (marching_cubes.hpp:1662-1738, :895-963): the
+// reference materialises a 12 B/node coordinate array and runs the CSG tree over it with two N-sized temporaries per
+// tree node; here a node's coordinate is computed from its index in registers, the whole flattened program
 // (csg_eval.cuh) runs per thread, and the two outermost node layers get the seal value without being evaluated.
 //
-// Layout in HBM: field[(z - z0) * plane + y * pitch + x], pitch = S rounded up to 4 floats so that every thread's four
-// x-adjacent nodes are one aligned 16-byte store (st.global.v4.f32); plane = pitch * S.
-// Work per node: 4 B written, 0 read; flops = Program::flops_per_point (no FMA contraction in exact mode).
+// Two kernels:
+//   k_tile_bounds : one thread per 8x8x8-node tile.  Interval evaluation of the tree over the tile's box grown by one
+//                   cell (composite transforms, outward margins) proves most tiles entirely inside or entirely outside;
+//                   no cut edge can touch such a tile, so its field values are never read and it only gets sign bits.
+//                   The rest go on a work list.  With pruning off every tile goes on the list (dense field, parity mode).
+//   k_eval_tiles  : persistent blocks walk the work list; 128 threads = 64 rows x 2 quads evaluate 4 x-adjacent nodes
+//                   each (bit-exact arithmetic), store them as one aligned float4, and pack the signs (f < 0,
+//                   marching_cubes.hpp:553-560) into one byte per 8 nodes.
+// Layout in HBM: field[zl * plane + y * pitch + x] (pitch = S rounded up to 8), sign bits as 32-bit words
+// signs[(zl * S + y) * SW + x / 32], bit x % 32; padding bits are 1 ("outside", like the seal).
+// Work per evaluated node: 4 B + 1 bit written, 0 read; flops = Program::flops_per_point.
 #pragma once
 #include <cuda_runtime.h>
 #include "csg_eval.cuh"
@@ -19,15 +27,13 @@ __constant__ uint32_t c_program[kMaxProgramWords];
 struct ConstProgram {
     __device__ __forceinline__ uint32_t operator[](int i) const { return c_program[i]; }
 };
-struct GlobalProgram {     // per-tile shortened programs live in global memory (read through L1, warp-uniform)
-    const uint32_t* w;
-    __device__ __forceinline__ uint32_t operator[](int i) const { return __ldg(w + i); }
-};
 
 struct GridDesc {
     int S;             // nodes per axis = R + 5
     int pitch;         // floats per x-row in HBM
+    int SW;            // sign words per row = ceil(S / 32) + 1 (the last one is padding, all ones)
     int z0, nz;        // node planes [z0, z0 + nz) are resident on this GPU
+    int tx, ty, tz;    // 8x8x8 tiles covering S x S x nz
     float xmin, ymin, zmin;
     float wx, wy, wz;  // (max - min) / R   (marching_cubes.hpp:231-243)
     float two_wx, two_wy, two_wz;   // skip_count_l * width (:1691)
@@ -39,42 +45,196 @@ constexpr float kExteriorValue = -10000000.0f;     // marching_cubes.hpp:1734
 
 // node coordinate exactly as prepare_grid forms it (:1679-1693): ((REAL)i * factor + min) - 2 * width
 __device__ __forceinline__ float node_coord(int i, float w, float mn, float two_w) { return ((float)i * w + mn) - two_w; }
-
 __device__ __forceinline__ bool sealed_index(int i, int S) { return i <= 1 || i >= S - 2; }
 
-constexpr int kFieldThreads = 128;
+// ---- interval evaluation (bounds only) -------------------------------------------------------------------------------
+struct Ival { float lo, hi; };
+__device__ __forceinline__ Ival iv_sq(float c, float r) {      // range of t^2 for t in [c - r, c + r]
+    const float a = fabsf(c);
+    const float mn = fmaxf(a - r, 0.0f), mx = a + r;
+    return Ival{mn * mn, mx * mx};
+}
+__device__ __forceinline__ float fmin3(float a, float b, float c) { return fminf(a, fminf(b, c)); }
 
-__global__ void __launch_bounds__(kFieldThreads) k_eval_field(GridDesc g, SdfGridView sdf, float* __restrict__ field) {
-    const int quads_per_row = g.pitch >> 2;
-    const long long q = (long long)blockIdx.x * kFieldThreads + threadIdx.x;
-    const long long rows = (long long)g.S * g.nz;
-    const long long row = q / quads_per_row;
-    if (row >= rows) return;
-    const int xq = (int)(q - row * quads_per_row);
-    const int zl = (int)(row / g.S);
-    const int y = (int)(row - (long long)zl * g.S);
-    const int z = g.z0 + zl;
-    const int x0 = xq << 2;
-    float4* dst = reinterpret_cast<float4*>(field + (long long)zl * g.plane + (long long)y * g.pitch + x0);
-    const bool row_sealed = sealed_index(y, g.S) || sealed_index(z, g.S);
-    if (row_sealed || x0 + 3 <= 1 || x0 >= g.S - 2) {
-        *dst = make_float4(kExteriorValue, kExteriorValue, kExteriorValue, kExteriorValue);
-        return;
-    }
-    float cx[4], cy[4], cz[4], f[4];
-    const float yy = node_coord(y, g.wy, g.ymin, g.two_wy);
-    const float zz = node_coord(z, g.wz, g.zmin, g.two_wz);
+// Bounds of the CSG function over the axis-aligned box centre (bx,by,bz), half extents (hx,hy,hz), in grid coordinates.
+// Everything is widened outwards: local boxes by a relative+absolute margin that covers the difference between the
+// composite transform used here and the nested float transforms of the exact evaluator; f bounds by a final margin.
+__device__ inline Ival program_bounds(const uint32_t* __restrict__ bp, float bx, float by, float bz, float hx, float hy, float hz) {
+    Ival st[kMaxValueStack];
+    int sp = 0, pc = 0;
+    for (;;) {
+        const uint32_t op = __ldg(bp + pc) & OP_MASK;
+        if (op == OP_END) break;
+        if (op >= OP_UNION) {
+            ++pc;
+            const Ival b = st[--sp], a = st[sp - 1];
+            Ival r;
+            if (op == OP_UNION) r = Ival{fmaxf(a.lo, b.lo), fmaxf(a.hi, b.hi)};
+            else if (op == OP_INTERSECT) r = Ival{fminf(a.lo, b.lo), fminf(a.hi, b.hi)};
+            else r = Ival{fminf(a.lo, -b.hi), fminf(a.hi, -b.lo)};
+            st[sp - 1] = r;
+            continue;
+        }
+        float m[12];
 #pragma unroll
-    for (int p = 0; p < 4; ++p) {
-        cx[p] = node_coord(x0 + p, g.wx, g.xmin, g.two_wx);
-        cy[p] = yy;
-        cz[p] = zz;
+        for (int i = 0; i < 12; ++i) m[i] = __uint_as_float(__ldg(bp + pc + 1 + i));
+        pc += 13;
+        float cx = m[0] * bx + m[1] * by + m[2] * bz + m[3];
+        float cy = m[4] * bx + m[5] * by + m[6] * bz + m[7];
+        float cz = m[8] * bx + m[9] * by + m[10] * bz + m[11];
+        float rx = fabsf(m[0]) * hx + fabsf(m[1]) * hy + fabsf(m[2]) * hz;
+        float ry = fabsf(m[4]) * hx + fabsf(m[5]) * hy + fabsf(m[6]) * hz;
+        float rz = fabsf(m[8]) * hx + fabsf(m[9]) * hy + fabsf(m[10]) * hz;
+        const float mag = fabsf(cx) + fabsf(cy) + fabsf(cz) + rx + ry + rz + fabsf(m[3]) + fabsf(m[7]) + fabsf(m[11]) + 1.0f;
+        const float pad = 1e-3f * mag;
+        rx += pad; ry += pad; rz += pad;
+        Ival r;
+        if (op == OP_ELLIPSOID) {
+            const Ival X = iv_sq(cx, rx), Y = iv_sq(cy, ry), Z = iv_sq(cz, rz);
+            r = Ival{1.0f - 4.0f * (X.hi + Y.hi + Z.hi), 1.0f - 4.0f * (X.lo + Y.lo + Z.lo)};
+        } else if (op == OP_CYLINDER) {
+            const Ival X = iv_sq(cx, rx), Y = iv_sq(cy, ry);
+            const float rho_lo = sqrtf(X.lo + Y.lo), rho_hi = sqrtf(X.hi + Y.hi);
+            const float zl = cz - rz, zh = cz + rz;
+            r = Ival{fmin3(zl + 0.5f, 0.5f - zh, 0.5f - rho_hi), fmin3(zh + 0.5f, 0.5f - zl, 0.5f - rho_lo)};
+        } else if (op == OP_CONE) {
+            const Ival X = iv_sq(cx, rx), Y = iv_sq(cy, ry);
+            const float rho_lo = sqrtf(X.lo + Y.lo), rho_hi = sqrtf(X.hi + Y.hi);
+            const float dl = (cz - 0.5f) - rz, dh = (cz - 0.5f) + rz;
+            const float al = (dl > 0.0f) ? dl : ((dh < 0.0f) ? -dh : 0.0f), ah = fmaxf(fabsf(dl), fabsf(dh));
+            r = Ival{fmin3(-rho_hi + 0.5f * al, -dh, dl + 1.0f), fmin3(-rho_lo + 0.5f * ah, -dl, dh + 1.0f)};
+        } else if (op == OP_CUBE) {
+            const float xl = cx - rx, xh = cx + rx, yl = cy - ry, yh = cy + ry, zl = cz - rz, zh = cz + rz;
+            r = Ival{fminf(fmin3(0.5f - xh, xl + 0.5f, 0.5f - yh), fmin3(yl + 0.5f, 0.5f - zh, zl + 0.5f)),
+                     fminf(fmin3(0.5f - xl, xh + 0.5f, 0.5f - yl), fmin3(yh + 0.5f, 0.5f - zl, zh + 0.5f))};
+        } else if (op == OP_METABALLS) {
+            const int nb = (int)__ldg(bp + pc);
+            ++pc;
+            float lo = 0.0f, hi = 0.0f;
+            for (int b = 0; b < nb; ++b) {
+                const float px = __uint_as_float(__ldg(bp + pc)), py = __uint_as_float(__ldg(bp + pc + 1)), pz = __uint_as_float(__ldg(bp + pc + 2));
+                const float strength = __uint_as_float(__ldg(bp + pc + 3)), subtract = __uint_as_float(__ldg(bp + pc + 4));
+                pc += 5;
+                const Ival X = iv_sq(cx - px, rx), Y = iv_sq(cy - py, ry), Z = iv_sq(cz - pz, rz);
+                const float dmin = 0.000001f + X.lo + Y.lo + Z.lo, dmax = 0.000001f + X.hi + Y.hi + Z.hi;
+                lo += (strength / dmax - subtract) / 100.0f;
+                hi += (strength / dmin - subtract) / 100.0f;
+            }
+            const float slack = 1e-4f * (fabsf(lo) + fabsf(hi) + (float)nb);
+            r = Ival{lo - slack, hi + slack};
+        } else {   // OP_CUBE_SDF: a table look-up, no bound
+            r = Ival{-3.0e38f, 3.0e38f};
+        }
+        st[sp++] = r;
     }
-    eval_values<4>(ConstProgram(), sdf, cx, cy, cz, f);
+    Ival out = st[0];
+    const float slack = 1e-4f * (1.0f + fabsf(out.lo) + fabsf(out.hi));
+    out.lo -= slack; out.hi += slack;
+    return out;
+}
+
+// tile classes
+enum : uint8_t { TILE_OUTSIDE = 0, TILE_INSIDE = 1, TILE_MIXED = 2 };
+
+// One thread per tile.  list_count[0] receives the number of tiles appended to `list`.
+__global__ void __launch_bounds__(128) k_tile_bounds(GridDesc g, const uint32_t* __restrict__ bounds_prog, int prune,
+                                                     uint32_t* __restrict__ signs, unsigned* __restrict__ list, unsigned* __restrict__ list_count) {
+    const int t = blockIdx.x * 128 + threadIdx.x;
+    const int ntiles = g.tx * g.ty * g.tz;
+    uint8_t cls = TILE_MIXED;
+    int tx = 0, ty = 0, tzl = 0;
+    const bool valid = t < ntiles;
+    if (valid) {
+        tx = t % g.tx;
+        const int r = t / g.tx;
+        ty = r % g.ty;
+        tzl = r / g.ty;
+        if (prune) {
+            // node index ranges of the tile, clipped to the grid
+            const int x0 = tx * 8, y0 = ty * 8, z0 = g.z0 + tzl * 8;
+            const int x1 = min(x0 + 7, g.S - 1), y1 = min(y0 + 7, g.S - 1), z1 = min(z0 + 7, g.z0 + g.nz - 1);
+            const bool touches_seal = x0 <= 1 || y0 <= 1 || z0 <= 1 || x1 + 1 >= g.S - 2 || y1 + 1 >= g.S - 2 || z1 + 1 >= g.S - 2;   // the grown box must stay clear of the seal too
+            // box of the tile grown by one cell on every side (+ a hair), in grid coordinates
+            const float ax = node_coord(x0 - 1, g.wx, g.xmin, g.two_wx), bx = node_coord(x1 + 1, g.wx, g.xmin, g.two_wx);
+            const float ay = node_coord(y0 - 1, g.wy, g.ymin, g.two_wy), by = node_coord(y1 + 1, g.wy, g.ymin, g.two_wy);
+            const float az = node_coord(z0 - 1, g.wz, g.zmin, g.two_wz), bz = node_coord(z1 + 1, g.wz, g.zmin, g.two_wz);
+            const Ival b = program_bounds(bounds_prog, 0.5f * (ax + bx), 0.5f * (ay + by), 0.5f * (az + bz), 0.5f * (bx - ax) * 1.001f,
+                                          0.5f * (by - ay) * 1.001f, 0.5f * (bz - az) * 1.001f);
+            if (b.hi < 0.0f) cls = TILE_OUTSIDE;
+            else if (b.lo > 0.0f && !touches_seal) cls = TILE_INSIDE;
+        }
+    }
+    // inside tiles: clear their sign bytes (the array is pre-set to ones = outside)
+    if (valid && cls == TILE_INSIDE) {
+        uint8_t* sb = reinterpret_cast<uint8_t*>(signs);
+        for (int dz = 0; dz < 8; ++dz) {
+            const int zl = tzl * 8 + dz;
+            if (zl >= g.nz) break;
+            for (int dy = 0; dy < 8; ++dy) {
+                const int y = ty * 8 + dy;
+                if (y >= g.S) break;
+                sb[((long long)zl * g.S + y) * (g.SW * 4) + tx] = 0;
+            }
+        }
+    }
+    // mixed tiles -> work list (warp-aggregated append)
+    const bool mixed = valid && cls == TILE_MIXED;
+    const unsigned m = __ballot_sync(0xffffffffu, mixed);
+    if (m) {
+        const int lane = threadIdx.x & 31;
+        unsigned base = 0;
+        if (lane == 0) base = atomicAdd(list_count, (unsigned)__popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (mixed) list[base + __popc(m & ((1u << lane) - 1u))] = (unsigned)t;
+    }
+}
+
+constexpr int kTileThreads = 128;
+
+__global__ void __launch_bounds__(kTileThreads) k_eval_tiles(GridDesc g, SdfGridView sdf, const unsigned* __restrict__ list,
+                                                            const unsigned* __restrict__ list_count, float* __restrict__ field,
+                                                            uint32_t* __restrict__ signs) {
+    const unsigned n = *list_count;
+    const int q = threadIdx.x & 1, row = threadIdx.x >> 1;
+    uint8_t* sb = reinterpret_cast<uint8_t*>(signs);
+    for (unsigned item = blockIdx.x; item < n; item += gridDim.x) {
+        const int t = (int)list[item];
+        const int tx = t % g.tx;
+        const int r = t / g.tx;
+        const int ty = r % g.ty, tzl = r / g.ty;
+        const int x0 = tx * 8 + q * 4, y = ty * 8 + (row & 7), zl = tzl * 8 + (row >> 3);
+        const int z = g.z0 + zl;
+        unsigned nib = 0xfu;
+        const bool in_grid = (y < g.S) && (zl < g.nz) && (x0 < g.pitch);
+        if (in_grid) {
+            float4* dst = reinterpret_cast<float4*>(field + (long long)zl * g.plane + (long long)y * g.pitch + x0);
+            const bool row_sealed = sealed_index(y, g.S) || sealed_index(z, g.S);
+            if (row_sealed || x0 + 3 <= 1 || x0 >= g.S - 2) {
+                *dst = make_float4(kExteriorValue, kExteriorValue, kExteriorValue, kExteriorValue);
+            } else {
+                float cx[4], cy[4], cz[4], f[4];
+                const float yy = node_coord(y, g.wy, g.ymin, g.two_wy);
+                const float zz = node_coord(z, g.wz, g.zmin, g.two_wz);
 #pragma unroll
-    for (int p = 0; p < 4; ++p)
-        if (sealed_index(x0 + p, g.S)) f[p] = kExteriorValue;
-    *dst = make_float4(f[0], f[1], f[2], f[3]);
+                for (int p = 0; p < 4; ++p) {
+                    cx[p] = node_coord(x0 + p, g.wx, g.xmin, g.two_wx);
+                    cy[p] = yy;
+                    cz[p] = zz;
+                }
+                eval_values<4>(ConstProgram(), sdf, cx, cy, cz, f);
+                nib = 0;
+#pragma unroll
+                for (int p = 0; p < 4; ++p) {
+                    if (sealed_index(x0 + p, g.S)) f[p] = kExteriorValue;
+                    nib |= (f[p] < 0.0f ? 1u : 0u) << p;
+                }
+                *dst = make_float4(f[0], f[1], f[2], f[3]);
+            }
+        }
+        // two quads -> one sign byte (lanes 2j, 2j+1 share a row)
+        const unsigned other = __shfl_xor_sync(0xffffffffu, nib, 1);
+        if (q == 0 && y < g.S && zl < g.nz) sb[((long long)zl * g.S + y) * (g.SW * 4) + tx] = (uint8_t)(nib | (other << 4));
+    }
 }
 
 // K10 — f and grad f on an arbitrary point list (mcc2.cpp:815-889 calculate_implicit_values/gradients).

@@ -82,6 +82,7 @@ enum { T_FIELD = 0, T_CLASSIFY, T_EMIT, T_RESAMPLE, T_PROJECT, T_QEM, T_COPY, T_
 struct Context {
     bool ready = false;
     int device = 0;
+    int sm_count = 148;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[16];
 
@@ -93,7 +94,7 @@ struct Context {
     PinnedBuffer h_verts, h_faces;
 
     // field + marching cubes scratch
-    DeviceBuffer d_field, d_counts, d_offsets, d_active, d_partials, d_totals, d_cases;
+    DeviceBuffer d_field, d_signs, d_tile_list, d_bounds, d_counts, d_offsets, d_active, d_partials, d_totals, d_cases;
     PinnedBuffer h_small;         // totals and other small read-backs
     GridDesc grid{};
     McDesc mc{};
@@ -160,13 +161,12 @@ void ensure_init(int device = -1) {
         abort();
     }
     g.device = device;
+    g.sm_count = prop.multiProcessorCount;
     ISD_CUDA(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
     for (auto& ev : g.ev) ISD_CUDA(cudaEventCreate(&ev));
     // tables derived from the reference's own (mc_tables.h)
     uint16_t info[256];
     for (int i = 0; i < 256; ++i) info[i] = (uint16_t)(ISD_MC_NTRI[i] | (ISD_MC_OWNED[i] << 8));
-    ISD_CUDA(cudaMemcpyToSymbol(c_case_info, info, sizeof(info)));
-    ISD_CUDA(cudaMemcpyToSymbol(c_tri_table, ISD_MC_TRI, sizeof(ISD_MC_TRI)));
     ISD_CUDA(cudaMemcpyToSymbol(d_case_info, info, sizeof(info)));
     ISD_CUDA(cudaMemcpyToSymbol(d_tri_table, ISD_MC_TRI, sizeof(ISD_MC_TRI)));
     g.h_small.reserve(4096);
@@ -206,7 +206,8 @@ void setup_grid(const McSettings& s) {
     const int S = s.resolution + 5;                       // skip_count_l + skip_count_h, marching_cubes.hpp:178-181
     GridDesc& gd = g.grid;
     gd.S = S;
-    gd.pitch = (S + 3) & ~3;
+    gd.pitch = (S + 7) & ~7;
+    gd.SW = (S + 31) / 32 + 1;
     gd.plane = (long long)gd.pitch * S;
     gd.xmin = s.box.xmin; gd.ymin = s.box.ymin; gd.zmin = s.box.zmin;
     gd.wx = (s.box.xmax - s.box.xmin) / (float)s.resolution;
@@ -222,8 +223,9 @@ void setup_grid(const McSettings& s) {
     m.scan_z0 = (zb > 1) ? zb - 1 : zb;
     if (g.world == 1) { gd.z0 = 0; gd.nz = S; }
     else { gd.z0 = zb - 1; gd.nz = (ze - zb) + 2; }
+    gd.tx = gd.pitch / 8; gd.ty = (S + 7) / 8; gd.tz = (gd.nz + 7) / 8;
     m.NX = S - 3;
-    m.K = (m.NX + 31) / 32;
+    m.K = (S - 3) / 32 + 1;
     m.n_chunks = (long long)(ze - m.scan_z0) * m.NX * m.K;
     m.ghost_chunks = (long long)(zb - m.scan_z0) * m.NX * m.K;
     m.g = gd;
@@ -252,18 +254,28 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         g.have_cases = true;
     }
 
+    const size_t sign_bytes = (size_t)gd.S * gd.nz * gd.SW * sizeof(uint32_t);
+    const int ntiles = gd.tx * gd.ty * gd.tz;
+    g.d_signs.reserve(sign_bytes);
+    g.d_tile_list.reserve((size_t)ntiles * sizeof(unsigned) + 64);
+    g.d_bounds.reserve(prog.bounds.size() * sizeof(uint32_t));
+    unsigned* tile_count = g.d_totals.as<unsigned>() + 8;
     ISD_CUDA(cudaEventRecord(g.ev[0], g.stream));
-    {   // K1
-        const long long quads = (long long)(gd.pitch / 4) * gd.S * gd.nz;
-        const long long blocks = (quads + kFieldThreads - 1) / kFieldThreads;
-        k_eval_field<<<(unsigned)blocks, kFieldThreads, 0, g.stream>>>(gd, g.sdf, g.d_field.as<float>());
+    {   // K1: bounds -> work list -> tiles
+        ISD_CUDA(cudaMemcpyAsync(g.d_bounds.ptr, prog.bounds.data(), prog.bounds.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, g.stream));
+        ISD_CUDA(cudaMemsetAsync(g.d_signs.ptr, 0xff, sign_bytes, g.stream));
+        ISD_CUDA(cudaMemsetAsync(tile_count, 0, sizeof(unsigned), g.stream));
+        k_tile_bounds<<<(ntiles + 127) / 128, 128, 0, g.stream>>>(gd, g.d_bounds.as<uint32_t>(), s.prune, g.d_signs.as<uint32_t>(),
+                                                                 g.d_tile_list.as<unsigned>(), tile_count);
+        ISD_LAUNCH_CHECK();
+        const int blocks = ntiles < g.sm_count * 8 ? ntiles : g.sm_count * 8;
+        k_eval_tiles<<<blocks, kTileThreads, 0, g.stream>>>(gd, g.sdf, g.d_tile_list.as<unsigned>(), tile_count, g.d_field.as<float>(),
+                                                           g.d_signs.as<uint32_t>());
         ISD_LAUNCH_CHECK();
     }
     ISD_CUDA(cudaEventRecord(g.ev[1], g.stream));
     {   // K2
-        const int layers = m.zc_end - m.scan_z0;
-        dim3 grid(m.K, (m.NX + kTY - 1) / kTY, (layers + kTZ - 1) / kTZ);
-        k_mc_classify<<<grid, 256, 0, g.stream>>>(m, g.d_field.as<float>(), g.d_counts.as<uint16_t>(), dbg_cases);
+        k_mc_classify<<<(unsigned)((n_chunks + 255) / 256), 256, 0, g.stream>>>(m, g.d_signs.as<uint32_t>(), g.d_counts.as<uint16_t>(), dbg_cases);
         ISD_LAUNCH_CHECK();
     }
     {   // K3
@@ -278,6 +290,7 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     // totals (and the ghost layer's share) back to the host: the only read-back before the mesh
     unsigned* h = g.h_small.as<unsigned>();
     ISD_CUDA(cudaMemcpyAsync(h, g.d_totals.ptr, 3 * sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaMemcpyAsync(h + 8, tile_count, sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));
     h[4] = 0; h[5] = 0;
     if (m.ghost_chunks > 0)
         ISD_CUDA(cudaMemcpyAsync(h + 4, g.d_offsets.as<uint2>() + m.ghost_chunks, sizeof(uint2), cudaMemcpyDeviceToHost, g.stream));
@@ -319,9 +332,11 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         EmitArgs ea;
         ea.vbase = voff - ghost_v; ea.fbase = foff - ghost_f;
         ea.v_local0 = ghost_v; ea.f_local0 = ghost_f;
-        const unsigned blocks = (n_active + kEmitWarps - 1) / kEmitWarps;
-        k_mc_emit<<<blocks, kEmitWarps * 32, 0, g.stream>>>(m, ea, g.d_field.as<float>(), g.d_offsets.as<uint2>(), g.d_active.as<unsigned>(),
-                                                            n_active, g.d_verts.as<float>(), g.d_faces.as<int>());
+        unsigned blocks = (n_active + kEmitWarps - 1) / kEmitWarps;
+        if (blocks > (unsigned)g.sm_count * 16u) blocks = (unsigned)g.sm_count * 16u;
+        k_mc_emit<<<blocks, kEmitWarps * 32, 0, g.stream>>>(m, ea, g.d_field.as<float>(), g.d_signs.as<uint32_t>(), g.d_offsets.as<uint2>(),
+                                                            g.d_active.as<unsigned>(), g.d_totals.as<unsigned>() + 2, g.d_verts.as<float>(),
+                                                            g.d_faces.as<int>());
         ISD_LAUNCH_CHECK();
     }
     ISD_CUDA(cudaEventRecord(g.ev[3], g.stream));
@@ -333,7 +348,7 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     g.counters[1] = (int64_t)(m.zc_end - m.emit_z0) * m.NX * m.NX;
     g.counters[2] = n_active;
     g.counters[14] = (int64_t)field_bytes;
-    g.counters[15] = g.counters[0];
+    g.counters[15] = (int64_t)h[8] * 512;
     (void)prog;
 }
 
@@ -518,10 +533,9 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     const float average_edge = *h_avg;
     g.average_edge = average_edge;
     std::vector<float> alphas = make_alpha_list(average_edge, 0.001f, average_edge, 20);
-    if (alphas.size() < 10) {   // the reference slices begin()+10 out of range here (centroids_projection.cpp:211)
-        fprintf(stderr, "implisolid_b200: average edge %g too small for the projection's alpha list\n", (double)average_edge);
-        abort();
-    }
+    // Direction types 1-6 use the first ten alphas (centroids_projection.cpp:211); below an average edge of 0.004 the
+    // list is shorter than that and the reference slices out of range (undefined behaviour).  Here they use what exists.
+    const int n_alpha_short = alphas.size() < 10 ? (int)alphas.size() : 10;
     if (alphas.size() > (size_t)kMaxAlphas) alphas.resize(kMaxAlphas);
     ISD_CUDA(cudaMemcpyToSymbolAsync(c_alpha, alphas.data(), alphas.size() * sizeof(float), 0, cudaMemcpyHostToDevice, g.stream));
 
@@ -535,7 +549,7 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     a.verts = g.d_verts.as<float>(); a.faces = g.d_faces.as<int>(); a.cen = g.d_cen.as<float>(); a.noise = nullptr;
     a.avg_edge = d_avg; a.best = g.d_best.as<float>(); a.fc = g.d_fc.as<float>(); a.state = g.d_state.as<unsigned char>();
     a.out = g.d_proj.as<float>(); a.nrm_out = g.d_pnrm.as<float>(); a.counters = g.d_counters.as<Ob02Counters>();
-    a.n = nf; a.n_alpha_full = (int)alphas.size();
+    a.n = nf; a.n_alpha_full = (int)alphas.size(); a.n_alpha_short = n_alpha_short;
     k_project_search<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a, 0);
     ISD_LAUNCH_CHECK();
     Ob02Counters* hc = reinterpret_cast<Ob02Counters*>(g.h_small.as<char>() + 2048);

@@ -27,6 +27,12 @@ __constant__ float c_alpha[kMaxAlphas];      // make_alpha_list result (host), c
 // [10] centroids still unresolved after phase A
 struct Ob02Counters { unsigned long long c[12]; };
 
+// one atomic per warp instead of one per thread: all counters are bumped by up to every thread of the grid
+__device__ __forceinline__ void count_if(bool pred, unsigned long long* ctr) {
+    const unsigned m = __ballot_sync(__activemask(), pred);
+    if (pred && (threadIdx.x & 31) == (__ffs(m) - 1)) atomicAdd(ctr, (unsigned long long)__popc(m));
+}
+
 __device__ __forceinline__ float norm2f(float x, float y, float z) { return sqrtf(x * x + y * y + z * z); }
 __device__ __forceinline__ float sign_tol(float v) { return (v > kRootTolerance) ? 1.0f : (v < -kRootTolerance) ? -1.0f : 0.0f; }
 
@@ -267,6 +273,7 @@ struct ProjectArgs {
     Ob02Counters* counters;
     int n;
     int n_alpha_full;
+    int n_alpha_short;       // min(10, n_alpha_full): alphas tried by direction types 1-6
 };
 
 // produce_facet_normals(force_normalisation = true)  implicit_vectorised_algorithms.hpp:52-133
@@ -330,10 +337,10 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
         if (!ok) {
             float nx, ny, nz;
             facet_normal(a.verts, a.faces, i, nx, ny, nz);
-            ok = try_direction(sdf, cx, cy, cz, nx, ny, nz, edge, 10, s_c, bx, by, bz);
+            ok = try_direction(sdf, cx, cy, cz, nx, ny, nz, edge, a.n_alpha_short, s_c, bx, by, bz);
             type = 1;
         }
-        if (!ok) atomicAdd(&a.counters->c[10], 1ull);
+        count_if(!ok, &a.counters->c[10]);
     } else {
         if (!(a.state[i] & 2)) return;
         s_c = sign_tol(a.fc[i]);
@@ -346,7 +353,7 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
             const float n = norm2f(zx, zy, zz);
             zx = zx / n; zy = zy / n; zz = zz / n;
         }
-        ok = try_direction(sdf, cx, cy, cz, zx, zy, zz, edge, 10, s_c, bx, by, bz);
+        ok = try_direction(sdf, cx, cy, cz, zx, zy, zz, edge, a.n_alpha_short, s_c, bx, by, bz);
         type = 2;
         if (!ok) {   // type 3: facet normal x previous direction, normalise_inplace
             float wx = ny * zz - nz * zy, wy = nz * zx - nx * zz, wz = nx * zy - ny * zx;
@@ -354,21 +361,22 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
             n = (n < kMinGradientLen) ? 1.0f : n;
             const float factor = 1.0f / n;
             wx = wx * factor; wy = wy * factor; wz = wz * factor;
-            ok = try_direction(sdf, cx, cy, cz, wx, wy, wz, edge, 10, s_c, bx, by, bz);
+            ok = try_direction(sdf, cx, cy, cz, wx, wy, wz, edge, a.n_alpha_short, s_c, bx, by, bz);
             type = 3;
         }
         for (int dim = 0; dim < 3 && !ok; ++dim) {
-            ok = try_direction(sdf, cx, cy, cz, dim == 0 ? 1.0f : 0.0f, dim == 1 ? 1.0f : 0.0f, dim == 2 ? 1.0f : 0.0f, edge, 10, s_c, bx, by, bz);
+            ok = try_direction(sdf, cx, cy, cz, dim == 0 ? 1.0f : 0.0f, dim == 1 ? 1.0f : 0.0f, dim == 2 ? 1.0f : 0.0f, edge, a.n_alpha_short, s_c, bx, by, bz);
             type = 4 + dim;
         }
     }
     if (ok) {
         a.best[i * 3] = bx; a.best[i * 3 + 1] = by; a.best[i * 3 + 2] = bz;
         a.state[i] = 1;
-        atomicAdd(&a.counters->c[type], 1ull);
     } else {
         a.state[i] = 2;
     }
+#pragma unroll
+    for (int t = 0; t < 7; ++t) count_if(ok && type == t, &a.counters->c[t]);
 }
 
 // set_centers_on_surface, second half (:893-1214): zero tests, bisection between the centroid and the candidate,
@@ -382,18 +390,18 @@ __global__ void __launch_bounds__(128) k_project_finish(SdfGridView sdf, Project
     if (already) { bx = a.best[i * 3]; by = a.best[i * 3 + 1]; bz = a.best[i * 3 + 2]; }
     else {
         bx = cx; by = cy; bz = cz;
-        atomicAdd(&a.counters->c[7], 1ull);
     }
+    count_if(!already, &a.counters->c[7]);
     const float f2 = eval_f(sdf, bx, by, bz);
     const bool zeros2 = fabsf(f2) <= kRootTolerance;
     const bool zeros1 = fabsf(a.fc[i]) <= kRootTolerance;
     if (zeros1) { bx = cx; by = cy; bz = cz; }
     const bool zeros12 = zeros2 || zeros1;
     float ox = cx, oy = cy, oz = cz;
+    count_if(already && !zeros12, &a.counters->c[9]);
     if (already && !zeros12) {
         float x1x = cx, x1y = cy, x1z = cz, x2x = bx, x2y = by, x2z = bz;
         if (f2 < -kRootTolerance) { x1x = bx; x1y = by; x1z = bz; x2x = cx; x2y = cy; x2z = cz; }
-        atomicAdd(&a.counters->c[9], 1ull);
         for (int it = 1;; ++it) {
             const float mx = (x1x + x2x) / 2.0f, my = (x1y + x2y) / 2.0f, mz = (x1z + x2z) / 2.0f;
             const float v = eval_f(sdf, mx, my, mz);

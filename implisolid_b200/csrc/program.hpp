@@ -128,6 +128,10 @@ public:
 
     struct Program {
         std::vector<uint32_t> words;
+        // Bounds program (tile pruning, field_kernel.cuh k_tile_bounds): the same tree in plain post-order, every primitive
+        // carrying the COMPOSITE grid->local matrix (product of the nested inverses along its path, formed in double).
+        // Only used to prove a tile is entirely inside or outside; never to produce field values.
+        std::vector<uint32_t> bounds;
         int value_depth = 0, frame_depth = 0, num_nodes = 0;
         bool uses_sdf_grid = false;
         double flops_per_point = 0;          // mul and add counted separately
@@ -138,6 +142,11 @@ public:
         vs_ = fs_ = 0;
         emit_node(root, /*preserve=*/false, p);
         p.words.push_back(OP_END);
+        {
+            double eye[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+            emit_bounds(root, eye, p);
+            p.bounds.push_back(OP_END);
+        }
         if (p.value_depth > kMaxValueStack || p.frame_depth > kMaxFrameStack) {
             fprintf(stderr, "implisolid_b200: shape tree too deep for the device evaluator (value stack %d > %d or frame stack %d > %d)\n",
                     p.value_depth, kMaxValueStack, p.frame_depth, kMaxFrameStack);
@@ -269,6 +278,35 @@ private:
         for (int i = 0; i < 12; ++i) { uint32_t w; memcpy(&w, &m[i], 4); p.words.push_back(w); }
     }
     void push_value(Program& p) { if (++vs_ > p.value_depth) p.value_depth = vs_; }
+
+    // comp = (own inverse) x parent_comp, 4x4 row-major in double
+    static void compose(const float minv[12], const double parent[16], double out[16]) {
+        double a[16];
+        for (int i = 0; i < 12; ++i) a[i] = minv[i];
+        a[12] = 0; a[13] = 0; a[14] = 0; a[15] = 1;
+        for (int r = 0; r < 4; ++r)
+            for (int c = 0; c < 4; ++c) {
+                double t = 0;
+                for (int k = 0; k < 4; ++k) t += a[r * 4 + k] * parent[k * 4 + c];
+                out[r * 4 + c] = t;
+            }
+    }
+    void emit_bounds(const ShapeNode& n, const double parent[16], Program& p) {
+        double comp[16];
+        compose(n.minv, parent, comp);
+        if (!n.is_csg()) {
+            p.bounds.push_back(n.op);
+            for (int i = 0; i < 12; ++i) { float f = (float)comp[i]; uint32_t w; memcpy(&w, &f, 4); p.bounds.push_back(w); }
+            if (n.op == OP_METABALLS) {
+                p.bounds.push_back((uint32_t)(n.params.size() / 5));
+                for (float v : n.params) { uint32_t w; memcpy(&w, &v, 4); p.bounds.push_back(w); }
+            }
+            return;
+        }
+        emit_bounds(*n.a, comp, p);
+        emit_bounds(*n.b, comp, p);
+        p.bounds.push_back(n.op);
+    }
 
     void emit_node(const ShapeNode& n, bool preserve, Program& p) {
         p.num_nodes++;

@@ -31,7 +31,8 @@ struct McSettings {
     int verbose;
     int debug_cases;      // 1: keep the dense per-cube case codes for isd_get_case_codes (parity tests)
     int exact_reduce;     // 1: mean edge length as the reference's serial float sum, bit for bit (slow); 0: pairwise double
-    int prune;            // 1: skip grid tiles proven off-surface by interval bounds (mesh identical, field not dense)
+    int prune;            // 1 (default): skip grid tiles proven off-surface by interval bounds (mesh identical; field values
+                          // exist only in tiles near the surface); 0: evaluate every node (dense field, parity mode)
 };
 
 inline bool settings_bool(const JsonDoc& d, const char* field, bool dflt, const char* forbidden, bool* needs_abort) {
@@ -87,7 +88,7 @@ inline McSettings parse_mc_settings(const char* json) {
     s.verbose = d.get_int("gpu.verbose", 0);
     s.debug_cases = d.get_int("gpu.debug_cases", 0);
     s.exact_reduce = d.get_int("gpu.exact_reduce", 0);
-    s.prune = d.get_int("gpu.prune", 0);
+    s.prune = d.get_int("gpu.prune", 1);
     if (s.qem_enabled && !s.projection_enabled) {
         fprintf(stderr, "Invalid settings: QEM will not be applied if centroid projection is disabled\n");
         needs_abort = true;

@@ -334,8 +334,8 @@ inline void set_centers_on_surface(const implicit_function& object, const vects&
     REAL initial_step_size = max_dist * 1.0;
     REAL scale_min_len = 1.0;
     std::vector<REAL> alpha_full = make_alpha_list(initial_step_size, 0.001 * scale_min_len, max_dist, max_iter);
-    if (alpha_full.size() < 10) { fprintf(stderr, "oracle: alpha list shorter than 10 (average edge %g too small)\n", (double)average_edge); abort(); }
-    std::vector<REAL> alpha10(alpha_full.begin(), alpha_full.begin() + 10);
+    // the reference slices begin()+10 out of range when the list is shorter (average edge < 0.004): clamp instead
+    std::vector<REAL> alpha10(alpha_full.begin(), alpha_full.begin() + std::min<size_t>(10, alpha_full.size()));
 
     vects best(n);
     for (int i = 0; i < n; i++) { best[i][0] = -10.0; best[i][1] = -10.0; best[i][2] = -10.0; }

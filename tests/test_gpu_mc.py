@@ -39,7 +39,7 @@ def test_field_cases_mesh_bit_exact(gpu_lib, oracle, name, shape, R, half):
     ofield, ocases = oracle.get_field(), oracle.get_case_codes()
     oracle.finish_geometry()
 
-    gpu_lib.build_geometry(sj, _mc(R, half, debug_cases=1))
+    gpu_lib.build_geometry(sj, _mc(R, half, debug_cases=1, prune=0))
     gv, gf = gpu_lib.get_v(), gpu_lib.get_f()
     gfield, gcases = gpu_lib.get_field(), gpu_lib.get_case_codes()
     # borrowed views agree with the copies (get_v_ptr / get_f_ptr)
@@ -54,6 +54,38 @@ def test_field_cases_mesh_bit_exact(gpu_lib, oracle, name, shape, R, half):
     assert np.array_equal(gv.view(np.uint32), ov.view(np.uint32)), "vertex positions differ"
     if name.startswith("c1_sphere") and R >= 28:
         assert abs(np.linalg.norm(gv, axis=1) - 0.5).max() < 2e-3
+
+
+@pytest.mark.parametrize("name,shape,R,half", CASES + [("c2_r200", shapes.c2_cube_minus_cylinder, 200, 0.8), ("c4_r160", shapes.c4_deep_chain, 160, 1.0),
+                                                  ("c3_r120", shapes.c3_metaballs, 120, 1.2), ("moon_r130", shapes.demo_moon, 130, 1.0)],
+                         ids=[c[0] for c in CASES] + ["c2_r200", "c4_r160", "c3_r120", "moon_r130"])
+def test_tile_pruning_changes_nothing(gpu_lib, name, shape, R, half):
+    """Interval pruning (the default) must give the same mesh, bit for bit, as evaluating every node; and every tile
+    it does evaluate holds the same field bits."""
+    sj = shape()
+    gpu_lib.build_geometry(sj, _mc(R, half, prune=0, debug_cases=1))
+    v0, f0, field0, cases0 = gpu_lib.get_v(), gpu_lib.get_f(), gpu_lib.get_field(), gpu_lib.get_case_codes()
+    n0 = gpu_lib.last_counters()["nodes_full_eval"]
+    gpu_lib.finish_geometry()
+    gpu_lib.build_geometry(sj, _mc(R, half, prune=1, debug_cases=1))
+    v1, f1, field1, cases1 = gpu_lib.get_v(), gpu_lib.get_f(), gpu_lib.get_field(), gpu_lib.get_case_codes()
+    n1 = gpu_lib.last_counters()["nodes_full_eval"]
+    gpu_lib.finish_geometry()
+    assert np.array_equal(f0, f1) and np.array_equal(v0.view(np.uint32), v1.view(np.uint32))
+    assert np.array_equal(cases0, cases1)
+    assert n1 <= n0
+    if R >= 100:
+        assert n1 < 0.6 * n0, (n1, n0)
+    # field values next to the surface (every node of a cut cube) are present and identical
+    S = field0.shape[0]
+    cut = (cases0 != 0) & (cases0 != 255)
+    zz, yy, xx = np.nonzero(cut)
+    for dz in (0, 1):
+        for dy in (0, 1):
+            for dx in (0, 1):
+                a = field0[zz + 1 + dz, yy + 1 + dy, xx + 1 + dx]
+                b = field1[zz + 1 + dz, yy + 1 + dy, xx + 1 + dx]
+                assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
 
 
 def test_mesh_is_closed_manifold(gpu_lib):
