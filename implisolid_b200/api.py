@@ -201,7 +201,7 @@ class GeometryLibrary:
     def last_counters(self):
         buf = np.zeros(16, dtype=np.int64)
         self.lib.isd_last_counters(buf.ctypes.data, 16)
-        return {"nodes": int(buf[0]), "cubes": int(buf[1]), "active_chunks": int(buf[2]),
+        return {"nodes": int(buf[0]), "cubes": int(buf[1]), "cut_cubes": int(buf[2]),
                 "projection_by_type": [int(x) for x in buf[3:10]], "projection_failed": int(buf[10]),
                 "bisection_capped": int(buf[11]), "bisected": int(buf[12]), "launches": int(buf[13]),
                 "field_bytes": int(buf[14]), "nodes_full_eval": int(buf[15])}

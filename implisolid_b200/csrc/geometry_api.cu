@@ -84,6 +84,9 @@ struct Context {
     int device = 0;
     int sm_count = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;   // device->host copy of the faces overlaps the OB02 stages (faces are final after K4)
+    cudaEvent_t ev_faces;
+    bool faces_in_flight = false;
     cudaEvent_t ev[16];
 
     // geometry state
@@ -94,7 +97,7 @@ struct Context {
     PinnedBuffer h_verts, h_faces;
 
     // field + marching cubes scratch
-    DeviceBuffer d_field, d_signs, d_tile_list, d_bounds, d_counts, d_offsets, d_active, d_partials, d_totals, d_cases;
+    DeviceBuffer d_field, d_signs, d_tile_list, d_bounds, d_counts, d_lane_bits, d_offsets, d_cubes, d_partials, d_totals, d_cases;
     PinnedBuffer h_small;         // totals and other small read-backs
     GridDesc grid{};
     McDesc mc{};
@@ -163,12 +166,15 @@ void ensure_init(int device = -1) {
     g.device = device;
     g.sm_count = prop.multiProcessorCount;
     ISD_CUDA(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
+    ISD_CUDA(cudaStreamCreateWithFlags(&g.copy_stream, cudaStreamNonBlocking));
+    ISD_CUDA(cudaEventCreateWithFlags(&g.ev_faces, cudaEventDisableTiming));
     for (auto& ev : g.ev) ISD_CUDA(cudaEventCreate(&ev));
     // tables derived from the reference's own (mc_tables.h)
     uint16_t info[256];
     for (int i = 0; i < 256; ++i) info[i] = (uint16_t)(ISD_MC_NTRI[i] | (ISD_MC_OWNED[i] << 8));
     ISD_CUDA(cudaMemcpyToSymbol(d_case_info, info, sizeof(info)));
     ISD_CUDA(cudaMemcpyToSymbol(d_tri_table, ISD_MC_TRI, sizeof(ISD_MC_TRI)));
+    ISD_CUDA(cudaMemcpyToSymbol(d_edge_mask, ISD_MC_EDGE_MASK, sizeof(ISD_MC_EDGE_MASK)));
     g.h_small.reserve(4096);
     g.ready = true;
 }
@@ -240,9 +246,9 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     g.d_field.reserve(field_bytes);
     const long long n_chunks = m.n_chunks;
     const long long padded = (n_chunks + kScanTile - 1) / kScanTile * kScanTile;
-    g.d_counts.reserve(padded * sizeof(uint16_t));
+    g.d_counts.reserve(padded * sizeof(uint32_t));
+    g.d_lane_bits.reserve((size_t)n_chunks * 5 * sizeof(uint32_t));
     g.d_offsets.reserve((n_chunks + 1) * sizeof(uint2));
-    g.d_active.reserve(n_chunks * sizeof(unsigned));
     const int scan_blocks = (int)(padded / kScanTile);
     g.d_partials.reserve((size_t)scan_blocks * sizeof(Triple));
     g.d_totals.reserve(64);
@@ -275,29 +281,35 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     }
     ISD_CUDA(cudaEventRecord(g.ev[1], g.stream));
     {   // K2
-        k_mc_classify<<<(unsigned)((n_chunks + 255) / 256), 256, 0, g.stream>>>(m, g.d_signs.as<uint32_t>(), g.d_counts.as<uint16_t>(), dbg_cases);
+        k_mc_classify<<<(unsigned)((n_chunks + 255) / 256), 256, 0, g.stream>>>(m, g.d_signs.as<uint32_t>(), g.d_counts.as<uint32_t>(),
+                                                                                 g.d_lane_bits.as<uint32_t>(), dbg_cases);
         ISD_LAUNCH_CHECK();
     }
-    {   // K3
-        k_scan_reduce<<<scan_blocks, kScanThreads, 0, g.stream>>>(g.d_counts.as<uint16_t>(), n_chunks, g.d_partials.as<Triple>());
+    {   // K3, first half: block sums and their prefix
+        k_scan_reduce<<<scan_blocks, kScanThreads, 0, g.stream>>>(g.d_counts.as<uint32_t>(), n_chunks, g.d_partials.as<Triple>());
         ISD_LAUNCH_CHECK();
         k_scan_partials<<<1, kScanThreads, 0, g.stream>>>(g.d_partials.as<Triple>(), scan_blocks, g.d_totals.as<unsigned>());
         ISD_LAUNCH_CHECK();
-        k_scan_apply<<<scan_blocks, kScanThreads, 0, g.stream>>>(g.d_counts.as<uint16_t>(), n_chunks, g.d_partials.as<Triple>(),
-                                                                g.d_offsets.as<uint2>(), g.d_active.as<unsigned>());
-        ISD_LAUNCH_CHECK();
     }
-    // totals (and the ghost layer's share) back to the host: the only read-back before the mesh
+    // totals back to the host (the only read-back before the mesh): sizes of the vertex, face and cut-cube arrays
     unsigned* h = g.h_small.as<unsigned>();
     ISD_CUDA(cudaMemcpyAsync(h, g.d_totals.ptr, 3 * sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));
     ISD_CUDA(cudaMemcpyAsync(h + 8, tile_count, sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));
-    h[4] = 0; h[5] = 0;
-    if (m.ghost_chunks > 0)
-        ISD_CUDA(cudaMemcpyAsync(h + 4, g.d_offsets.as<uint2>() + m.ghost_chunks, sizeof(uint2), cudaMemcpyDeviceToHost, g.stream));
-    ISD_CUDA(cudaEventRecord(g.ev[2], g.stream));
     ISD_CUDA(cudaStreamSynchronize(g.stream));
+    const unsigned n_cubes = h[2];
+    g.d_cubes.reserve((size_t)(n_cubes > 0 ? n_cubes : 1) * sizeof(unsigned));
+    {   // K3, second half: chunk offsets + the ordered list of cut cubes
+        k_scan_apply<<<scan_blocks, kScanThreads, 0, g.stream>>>(g.d_counts.as<uint32_t>(), n_chunks, g.d_partials.as<Triple>(),
+                                                                g.d_lane_bits.as<uint32_t>(), g.d_offsets.as<uint2>(), g.d_cubes.as<unsigned>());
+        ISD_LAUNCH_CHECK();
+    }
+    h[4] = 0; h[5] = 0;
+    if (m.ghost_chunks > 0) {   // the ghost layer's share of the totals (z-slabs only)
+        ISD_CUDA(cudaMemcpyAsync(h + 4, g.d_offsets.as<uint2>() + m.ghost_chunks, sizeof(uint2), cudaMemcpyDeviceToHost, g.stream));
+        ISD_CUDA(cudaStreamSynchronize(g.stream));
+    }
+    ISD_CUDA(cudaEventRecord(g.ev[2], g.stream));
     const long long scan_v = h[0], scan_f = h[1];
-    const unsigned n_active = h[2];
     const long long ghost_v = h[4], ghost_f = h[5];
     const long long nv = scan_v - ghost_v, nf = scan_f - ghost_f;
 
@@ -328,15 +340,15 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     }
     g.d_verts.reserve((size_t)(nv > 0 ? nv : 1) * 3 * sizeof(float));
     g.d_faces.reserve((size_t)(nf > 0 ? nf : 1) * 3 * sizeof(int));
-    if (n_active > 0) {   // K4
+    if (n_cubes > 0) {   // K4
         EmitArgs ea;
         ea.vbase = voff - ghost_v; ea.fbase = foff - ghost_f;
         ea.v_local0 = ghost_v; ea.f_local0 = ghost_f;
-        unsigned blocks = (n_active + kEmitWarps - 1) / kEmitWarps;
+        unsigned blocks = (n_cubes + kEmitThreads - 1) / kEmitThreads;
         if (blocks > (unsigned)g.sm_count * 16u) blocks = (unsigned)g.sm_count * 16u;
-        k_mc_emit<<<blocks, kEmitWarps * 32, 0, g.stream>>>(m, ea, g.d_field.as<float>(), g.d_signs.as<uint32_t>(), g.d_offsets.as<uint2>(),
-                                                            g.d_active.as<unsigned>(), g.d_totals.as<unsigned>() + 2, g.d_verts.as<float>(),
-                                                            g.d_faces.as<int>());
+        k_mc_emit<<<blocks, kEmitThreads, 0, g.stream>>>(m, ea, g.d_field.as<float>(), g.d_signs.as<uint32_t>(), g.d_offsets.as<uint2>(),
+                                                         g.d_lane_bits.as<uint32_t>(), g.d_cubes.as<unsigned>(), g.d_totals.as<unsigned>() + 2,
+                                                         g.d_verts.as<float>(), g.d_faces.as<int>());
         ISD_LAUNCH_CHECK();
     }
     ISD_CUDA(cudaEventRecord(g.ev[3], g.stream));
@@ -346,7 +358,7 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     g.slab[4] = nv; g.slab[5] = nf; g.slab[6] = gnv; g.slab[7] = gnf;
     g.counters[0] = (int64_t)gd.S * gd.S * gd.nz;
     g.counters[1] = (int64_t)(m.zc_end - m.emit_z0) * m.NX * m.NX;
-    g.counters[2] = n_active;
+    g.counters[2] = n_cubes;
     g.counters[14] = (int64_t)field_bytes;
     g.counters[15] = (int64_t)h[8] * 512;
     (void)prog;
@@ -592,15 +604,28 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     g.timings[T_QEM] += ms;
 }
 
+// faces do not change after marching cubes: start their device->host copy now, on the side stream
+void start_faces_copy() {
+    if (g.nf == 0) return;
+    g.h_faces.reserve((size_t)g.nf * 3 * sizeof(int));
+    ISD_CUDA(cudaEventRecord(g.ev_faces, g.stream));
+    ISD_CUDA(cudaStreamWaitEvent(g.copy_stream, g.ev_faces, 0));
+    ISD_CUDA(cudaMemcpyAsync(g.h_faces.ptr, g.d_faces.ptr, (size_t)g.nf * 3 * sizeof(int), cudaMemcpyDeviceToHost, g.copy_stream));
+    g.faces_in_flight = true;
+}
+
 void copy_mesh_to_host() {
     if (g.host_valid) return;
     g.h_verts.reserve((size_t)(g.nv > 0 ? g.nv : 1) * 3 * sizeof(float));
     g.h_faces.reserve((size_t)(g.nf > 0 ? g.nf : 1) * 3 * sizeof(int));
     ISD_CUDA(cudaEventRecord(g.ev[9], g.stream));
     if (g.nv) ISD_CUDA(cudaMemcpyAsync(g.h_verts.ptr, g.d_verts.ptr, (size_t)g.nv * 3 * sizeof(float), cudaMemcpyDeviceToHost, g.stream));
-    if (g.nf) ISD_CUDA(cudaMemcpyAsync(g.h_faces.ptr, g.d_faces.ptr, (size_t)g.nf * 3 * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
+    if (g.nf && !g.faces_in_flight)
+        ISD_CUDA(cudaMemcpyAsync(g.h_faces.ptr, g.d_faces.ptr, (size_t)g.nf * 3 * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
     ISD_CUDA(cudaEventRecord(g.ev[10], g.stream));
     ISD_CUDA(cudaStreamSynchronize(g.stream));
+    if (g.faces_in_flight) ISD_CUDA(cudaStreamSynchronize(g.copy_stream));
+    g.faces_in_flight = false;
     float ms = 0;
     ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[9], g.ev[10]));
     g.timings[T_COPY] = ms;
@@ -619,6 +644,7 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     for (int64_t& c : g.counters) c = 0;
     g.launches = 0;
     g.host_valid = false;
+    g.faces_in_flight = false;
     g.adjacency_valid = false;
     g.fof_valid_ = false;
     g.proj_n = 0;
@@ -630,6 +656,7 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     run_marching_cubes(s, prog);                                   // polygonize_step_0
     const bool any_ob02 = s.overall_repeats > 0 && (s.vresampl_iters > 0 || s.projection_enabled);
     if (any_ob02 && g.world > 1 && !g.emulate) gather_mesh();      // OB02 runs on the stitched mesh, replicated
+    if (copy_out && any_ob02) start_faces_copy();
     for (int overall_iter = 0; overall_iter < s.overall_repeats; ++overall_iter) {
         if (s.vresampl_iters > 0) {
             ISD_CUDA(cudaEventRecord(g.ev[4], g.stream));

@@ -37,6 +37,8 @@ namespace isd {
 // Global memory (L1-resident): look-ups are lane-divergent, which constant memory would serialise.
 __device__ uint16_t d_case_info[256];
 __device__ int8_t d_tri_table[256 * 16];
+__device__ uint16_t d_edge_mask[256];
+#define ISD_EDGE_MASK(code) ((unsigned)d_edge_mask[code])
 
 struct McDesc {
     GridDesc g;
@@ -69,8 +71,11 @@ __device__ __forceinline__ unsigned case_code(unsigned long long r00, unsigned l
 // ---- K2 ---------------------------------------------------------------------------------------------------------
 constexpr unsigned long long kRowMask = 0x1ffffffffull;
 
-__global__ void __launch_bounds__(256) k_mc_classify(McDesc m, const uint32_t* __restrict__ signs, uint16_t* __restrict__ counts,
-                                                     uint8_t* __restrict__ dbg_cases) {
+// counts[c] = new vertices | triangles << 8 | cut cubes << 16.  For a cut chunk, lane_bits[5c .. 5c+4] hold, bit per
+// lane, the two bits of each cube's vertex count and the three bits of its triangle count, so that K4 can turn any
+// (chunk, lane) into a vertex / face rank with popcounts.
+__global__ void __launch_bounds__(256) k_mc_classify(McDesc m, const uint32_t* __restrict__ signs, uint32_t* __restrict__ counts,
+                                                     uint32_t* __restrict__ lane_bits, uint8_t* __restrict__ dbg_cases) {
     const long long c = (long long)blockIdx.x * 256 + threadIdx.x;
     const bool valid = c < m.n_chunks;
     const int lane = threadIdx.x & 31;
@@ -100,17 +105,25 @@ __global__ void __launch_bounds__(256) k_mc_classify(McDesc m, const uint32_t* _
         const int x = 32 * sk + lane;
         const bool xin = x >= 1 && x <= m.g.S - 3;
         const unsigned code = xin ? case_code(s00, s10, s01, s11, lane) : 0u;
-        unsigned packed = 0;
+        unsigned nv = 0, nt = 0;
         if (code != 0u && code != 255u) {
             const unsigned info = d_case_info[code];
-            packed = ((info >> 8) & 3u) | ((info & 0xffu) << 8);
+            nv = (info >> 8) & 3u;
+            nt = info & 0xffu;
         }
-        const unsigned total = __reduce_add_sync(0xffffffffu, packed);
-        if (lane == src) my_count = total;
+        const unsigned v0 = __ballot_sync(0xffffffffu, nv & 1u), v1 = __ballot_sync(0xffffffffu, nv & 2u);
+        const unsigned t0 = __ballot_sync(0xffffffffu, nt & 1u), t1 = __ballot_sync(0xffffffffu, nt & 2u), t2 = __ballot_sync(0xffffffffu, nt & 4u);
+        if (lane == src) {
+            my_count = (__popc(v0) + 2u * __popc(v1)) | ((__popc(t0) + 2u * __popc(t1) + 4u * __popc(t2)) << 8) | (__popc(t0 | t1 | t2) << 16);
+            if (my_count) {
+                uint32_t* lb = lane_bits + c * 5;
+                lb[0] = v0; lb[1] = v1; lb[2] = t0; lb[3] = t1; lb[4] = t2;
+            }
+        }
         if (dbg_cases != nullptr && xin)
             dbg_cases[((long long)(sz - m.scan_z0) * m.NX + (sy - 1)) * m.NX + (x - 1)] = (uint8_t)code;
     }
-    if (valid) counts[c] = (uint16_t)my_count;
+    if (valid) counts[c] = my_count;
 }
 
 // ---- K3: exclusive scan of the chunk counts -------------------------------------------------------------------------
@@ -146,30 +159,30 @@ __device__ __forceinline__ Triple block_exclusive(Triple mine, Triple* total) {
     return Triple{base.v + inc.v - mine.v, base.f + inc.f - mine.f, base.a + inc.a - mine.a};
 }
 
-__device__ __forceinline__ void load_counts8(const uint16_t* counts, long long first, long long n, unsigned (&c)[kScanItems]) {
+__device__ __forceinline__ void load_counts8(const uint32_t* counts, long long first, long long n, unsigned (&c)[kScanItems]) {
     if (first + kScanItems <= n) {
-        const uint4 raw = *reinterpret_cast<const uint4*>(counts + first);    // first is a multiple of 8: 16-byte aligned
-        c[0] = raw.x & 0xffffu; c[1] = raw.x >> 16; c[2] = raw.y & 0xffffu; c[3] = raw.y >> 16;
-        c[4] = raw.z & 0xffffu; c[5] = raw.z >> 16; c[6] = raw.w & 0xffffu; c[7] = raw.w >> 16;
+        const uint4 a = *reinterpret_cast<const uint4*>(counts + first), b = *reinterpret_cast<const uint4*>(counts + first + 4);
+        c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w; c[4] = b.x; c[5] = b.y; c[6] = b.z; c[7] = b.w;
     } else {
 #pragma unroll
         for (int i = 0; i < kScanItems; ++i) c[i] = (first + i < n) ? counts[first + i] : 0u;
     }
 }
+__device__ __forceinline__ Triple unpack_count(unsigned c) { return Triple{c & 0xffu, (c >> 8) & 0xffu, c >> 16}; }
 
-__global__ void __launch_bounds__(kScanThreads) k_scan_reduce(const uint16_t* __restrict__ counts, long long n, Triple* __restrict__ partials) {
+__global__ void __launch_bounds__(kScanThreads) k_scan_reduce(const uint32_t* __restrict__ counts, long long n, Triple* __restrict__ partials) {
     const long long first = ((long long)blockIdx.x * kScanThreads + threadIdx.x) * kScanItems;
     unsigned c[kScanItems];
     load_counts8(counts, first, n, c);
     Triple t{0, 0, 0};
 #pragma unroll
-    for (int i = 0; i < kScanItems; ++i) { t.v += c[i] & 0xffu; t.f += c[i] >> 8; t.a += (c[i] != 0u); }
+    for (int i = 0; i < kScanItems; ++i) t = t + unpack_count(c[i]);
     Triple total;
     block_exclusive(t, &total);
     if (threadIdx.x == 0) partials[blockIdx.x] = total;
 }
 
-// one block: partials[i] <- exclusive prefix; totals[0..2] <- grand totals
+// one block: partials[i] <- exclusive prefix; totals[0..2] <- grand totals {vertices, triangles, cut cubes}
 __global__ void __launch_bounds__(kScanThreads) k_scan_partials(Triple* __restrict__ partials, int nblocks, unsigned* __restrict__ totals) {
     Triple carry{0, 0, 0};
     for (int base = 0; base < nblocks; base += kScanThreads) {
@@ -183,26 +196,36 @@ __global__ void __launch_bounds__(kScanThreads) k_scan_partials(Triple* __restri
     if (threadIdx.x == 0) { totals[0] = carry.v; totals[1] = carry.f; totals[2] = carry.a; }
 }
 
-__global__ void __launch_bounds__(kScanThreads) k_scan_apply(const uint16_t* __restrict__ counts, long long n, const Triple* __restrict__ partials,
-                                                            uint2* __restrict__ offsets, unsigned* __restrict__ active) {
+// offsets[c] = {first vertex, first triangle} of chunk c; cubes[] = the cut cubes in scan order, as chunk * 32 + lane
+__global__ void __launch_bounds__(kScanThreads) k_scan_apply(const uint32_t* __restrict__ counts, long long n, const Triple* __restrict__ partials,
+                                                            const uint32_t* __restrict__ lane_bits, uint2* __restrict__ offsets,
+                                                            unsigned* __restrict__ cubes) {
     const long long first = ((long long)blockIdx.x * kScanThreads + threadIdx.x) * kScanItems;
     unsigned c[kScanItems];
     load_counts8(counts, first, n, c);
     Triple t{0, 0, 0};
 #pragma unroll
-    for (int i = 0; i < kScanItems; ++i) { t.v += c[i] & 0xffu; t.f += c[i] >> 8; t.a += (c[i] != 0u); }
+    for (int i = 0; i < kScanItems; ++i) t = t + unpack_count(c[i]);
     Triple total;
     Triple run = partials[blockIdx.x] + block_exclusive(t, &total);
 #pragma unroll
     for (int i = 0; i < kScanItems; ++i) {
         if (first + i < n) {
             offsets[first + i] = make_uint2(run.v, run.f);
-            if (c[i] != 0u) active[run.a] = (unsigned)(first + i);
+            if (c[i] != 0u) {
+                const uint32_t* lb = lane_bits + (first + i) * 5;
+                unsigned act = lb[2] | lb[3] | lb[4];
+                unsigned slot = run.a;
+                while (act) {
+                    const int l = __ffs(act) - 1;
+                    act &= act - 1;
+                    cubes[slot++] = (unsigned)((first + i) * 32 + l);
+                }
+            }
         }
-        run.v += c[i] & 0xffu; run.f += c[i] >> 8; run.a += (c[i] != 0u);
+        run = run + unpack_count(c[i]);
     }
 }
-
 
 // ---- K4 ---------------------------------------------------------------------------------------------------------
 // rank of local edge `code` (0: edge 5, 1: edge 6, 2: edge 10) among the vertices a cube with OWNED byte `own`
@@ -223,92 +246,69 @@ struct EmitArgs {
     long long f_local0;
 };
 
-constexpr int kEmitWarps = 8;
-
 // 34 sign bits of one row around chunk k: bit j <-> node x = 32k - 1 + j  (j = 0 is the halo node of the previous word)
 __device__ __forceinline__ unsigned long long row_bits34(const uint32_t* __restrict__ row, int k) {
     const unsigned prev = (k > 0) ? (__ldg(row + k - 1) >> 31) : 1u;
     return (unsigned long long)prev | ((unsigned long long)__ldg(row + k) << 1) | ((unsigned long long)(__ldg(row + k + 1) & 1u) << 33);
 }
 
-__global__ void __launch_bounds__(kEmitWarps * 32) k_mc_emit(McDesc m, EmitArgs ea, const float* __restrict__ field, const uint32_t* __restrict__ signs,
-                                                             const uint2* __restrict__ offsets, const unsigned* __restrict__ active,
-                                                             const unsigned* __restrict__ n_active_ptr, float* __restrict__ verts, int* __restrict__ faces) {
-    const unsigned n_active = *n_active_ptr;
-    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const unsigned lt = (1u << lane) - 1u;
+// first vertex (scan numbering) of the cube at (chunk c, lane l): chunk prefix + vertices of the lanes before it
+__device__ __forceinline__ unsigned cube_vertex_base(const uint2* __restrict__ offsets, const uint32_t* __restrict__ lane_bits, long long c, int l) {
+    const unsigned lt = (1u << l) - 1u;
+    return offsets[c].x + __popc(__ldg(lane_bits + c * 5) & lt) + 2u * __popc(__ldg(lane_bits + c * 5 + 1) & lt);
+}
+
+constexpr int kEmitThreads = 128;
+
+// One thread per cut cube.  Its own new vertices (edges 5, 6, 10) are interpolated from the field; the other nine
+// edges' vertices were introduced by six neighbouring cubes, whose vertex ranks follow from their chunk's prefix and
+// lane bits and their own case code (for the order of their new vertices).
+__global__ void __launch_bounds__(kEmitThreads) k_mc_emit(McDesc m, EmitArgs ea, const float* __restrict__ field, const uint32_t* __restrict__ signs,
+                                                          const uint2* __restrict__ offsets, const uint32_t* __restrict__ lane_bits,
+                                                          const unsigned* __restrict__ cubes, const unsigned* __restrict__ n_cubes_ptr,
+                                                          float* __restrict__ verts, int* __restrict__ faces) {
+    const unsigned n_cubes = *n_cubes_ptr;
     const int S = m.g.S;
-    for (unsigned slot = blockIdx.x * kEmitWarps + w; slot < n_active; slot += gridDim.x * kEmitWarps) {
-        const long long chunk = active[slot];
+    for (unsigned i = blockIdx.x * kEmitThreads + threadIdx.x; i < n_cubes; i += gridDim.x * kEmitThreads) {
+        const unsigned id = cubes[i];
+        const long long chunk = id >> 5;
+        const int lane = (int)(id & 31u);
         const int k = (int)(chunk % m.K);
         const long long row = chunk / m.K;
         const int y = 1 + (int)(row % m.NX);
         const int z = m.scan_z0 + (int)(row / m.NX);
         if (z < m.emit_z0) continue;          // ghost layer: counted here, emitted by the slab below
         const int x = 32 * k + lane;
-        // sign rows (dy, dz) in {-1,0,1}^2, 34 bits each (warp-uniform loads)
-        unsigned long long R[3][3];
+        unsigned long long R[3][3];           // sign rows (dy, dz) in {-1,0,1}^2, 34 bits each
 #pragma unroll
         for (int dz = 0; dz < 3; ++dz)
 #pragma unroll
             for (int dy = 0; dy < 3; ++dy) R[dz][dy] = row_bits34(sign_row(m, signs, y + dy - 1, z + dz - 1), k);
-        const bool xin = (x >= 1 && x <= S - 3);
-        // rows: 0 own (y,z)   1 B (y,z-1)   2 C (y-1,z)   3 A (y-1,z-1); cube at lane -> bit position lane + 1
+        // rows: 0 own (y,z)   1 B (y,z-1)   2 C (y-1,z)   3 A (y-1,z-1); the cube at x sits at bit position lane + 1
         const int rdy[4] = {1, 1, 0, 0}, rdz[4] = {1, 0, 1, 0};
-        unsigned own[4], own_halo[3];
-        long long base[4];
-        unsigned code_self = 0;
+        unsigned code[4], codep[3];
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
-            const int yy = y + rdy[r] - 1, zz = z + rdz[r] - 1;
             const unsigned long long a = R[rdz[r]][rdy[r]], b = R[rdz[r]][rdy[r] + 1], c = R[rdz[r] + 1][rdy[r]], d = R[rdz[r] + 1][rdy[r] + 1];
-            const unsigned code = xin ? case_code(a, b, c, d, lane + 1) : 0u;
-            if (r == 0) code_self = code;
-            const unsigned info = (code != 0u && code != 255u) ? d_case_info[code] : 0u;
-            own[r] = info >> 8;
-            const unsigned n = own[r] & 3u;
-            const unsigned b0 = __ballot_sync(0xffffffffu, n & 1u), b1 = __ballot_sync(0xffffffffu, n & 2u);
-            const unsigned before = __popc(b0 & lt) + 2u * __popc(b1 & lt);
-            long long coff = 0;
-            if (yy >= 1 && zz >= m.scan_z0) coff = offsets[chunk_index(m, zz, yy, k)].x;
-            base[r] = ea.vbase + coff + before;
-            if (r < 3) {
-                // halo cube x = 32k - 1 of the same row (introducer of this chunk's lane-0 edges 3/7/8/11)
-                const unsigned hcode = case_code(a, b, c, d, 0);
-                const unsigned hinfo = (hcode != 0u && hcode != 255u && k > 0) ? d_case_info[hcode] : 0u;
-                own_halo[r] = hinfo >> 8;
-            }
+            code[r] = case_code(a, b, c, d, lane + 1);
+            if (r < 3) codep[r] = (x > 1) ? case_code(a, b, c, d, lane) : 0u;      // the cube at x - 1 (x = 0 is never visited)
         }
-        long long i5[3], i6[4], i10[3], p5[3], p10[3];      // p*: the cube at x-1
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            i6[r] = base[r] + owned_rank(own[r], 1u);
-            if (r < 3) {
-                i5[r] = base[r] + owned_rank(own[r], 0u);
-                i10[r] = base[r] + owned_rank(own[r], 2u);
-                long long q5 = __shfl_up_sync(0xffffffffu, i5[r], 1), q10 = __shfl_up_sync(0xffffffffu, i10[r], 1);
-                if (lane == 0) {
-                    const long long hbase = base[r] - (own_halo[r] & 3u);     // the halo cube's vertices end where this chunk's begin
-                    q5 = hbase + owned_rank(own_halo[r], 0u);
-                    q10 = hbase + owned_rank(own_halo[r], 2u);
-                }
-                p5[r] = q5; p10[r] = q10;
-            }
-        }
-        const unsigned info_self = (code_self != 0u && code_self != 255u) ? d_case_info[code_self] : 0u;
-        const unsigned nt = info_self & 0xffu;
-        // ---- vertices introduced by this cube ---------------------------------------------------------------------
-        const unsigned nv = own[0] & 3u;
+        const unsigned code_self = code[0];
+        const unsigned info_self = d_case_info[code_self];
+        const unsigned nt = info_self & 0xffu, own_self = info_self >> 8, nv = own_self & 3u;
+        const unsigned emask = ISD_EDGE_MASK(code_self);
+        const long long vself = (long long)cube_vertex_base(offsets, lane_bits, chunk, lane);
+        // ---- vertices introduced by this cube -----------------------------------------------------------------------
         if (nv) {
             const float fx = ((float)x + m.g.xi0) * m.g.wx, fy = ((float)y + m.g.yi0) * m.g.wy, fz = ((float)z + m.g.zi0) * m.g.wz;   // :1041-1053
             const float fx2 = fx + m.g.wx, fy2 = fy + m.g.wy, fz2 = fz + m.g.wz;                                                    // :570-576
             const float* p = field + (long long)(z - m.g.z0) * m.g.plane + (long long)y * m.g.pitch + x;
             const float f7 = __ldg(p + m.g.plane + m.g.pitch + 1);
-            const long long vloc = base[0] - ea.vbase - ea.v_local0;
+            const long long vloc = vself - ea.v_local0;
 #pragma unroll
             for (int j = 0; j < 3; ++j) {
                 if ((unsigned)j < nv) {
-                    const unsigned e = (own[0] >> (2 + 2 * j)) & 3u;
+                    const unsigned e = (own_self >> (2 + 2 * j)) & 3u;
                     float px, py, pz;
                     if (e == 0u) {          // edge 5: VIntY(fx2, fy, fz2, field5, field7)  :627-634, :452-457
                         const float f5 = __ldg(p + m.g.plane + 1);
@@ -328,36 +328,60 @@ __global__ void __launch_bounds__(kEmitWarps * 32) k_mc_emit(McDesc m, EmitArgs 
                 }
             }
         }
+        if (nt == 0) continue;
+        // ---- vertex index of every cut edge (SURVEY Appendix A + first-appearance cube) --------------------------------
+        // neighbour cubes: chunk of row r at the same k; the cube at x-1 is lane-1 of it, or lane 31 of chunk k-1
+        const long long crow[3] = {chunk, chunk_index(m, z - 1, y, k), chunk_index(m, z, y - 1, k)};      // own, B, C
+        const long long cA = chunk_index(m, z - 1, y - 1, k);
+        const int lp = (lane > 0) ? lane - 1 : 31;
+        long long ev[12];
+#pragma unroll
+        for (int q = 0; q < 12; ++q) ev[q] = 0;
+        auto vidx = [&](long long c, int l, unsigned cd, unsigned edge_code) -> long long {
+            const unsigned own = d_case_info[cd] >> 8;
+            return ea.vbase + (long long)cube_vertex_base(offsets, lane_bits, c, l) + owned_rank(own, edge_code);
+        };
+        ev[5] = ea.vbase + vself + owned_rank(own_self, 0u);
+        ev[6] = ea.vbase + vself + owned_rank(own_self, 1u);
+        ev[10] = ea.vbase + vself + owned_rank(own_self, 2u);
+        if (emask & 0x001u) ev[0] = vidx(cA, lane, code[3], 1u);                    // x-edge at (x,y,z)    <- cube (x, y-1, z-1) edge 6
+        if (emask & 0x006u) {                                                       // cube (x, y, z-1): edges 5 and 6
+            const long long b = ea.vbase + (long long)cube_vertex_base(offsets, lane_bits, crow[1], lane);
+            const unsigned own = d_case_info[code[1]] >> 8;
+            ev[1] = b + owned_rank(own, 0u);                                        // y-edge at (x+1,y,z)
+            ev[2] = b + owned_rank(own, 1u);                                        // x-edge at (x,y+1,z)
+        }
+        if (emask & 0x210u) {                                                       // cube (x, y-1, z): edges 6 and 10
+            const long long b = ea.vbase + (long long)cube_vertex_base(offsets, lane_bits, crow[2], lane);
+            const unsigned own = d_case_info[code[2]] >> 8;
+            ev[4] = b + owned_rank(own, 1u);                                        // x-edge at (x,y,z+1)
+            ev[9] = b + owned_rank(own, 2u);                                        // z-edge at (x+1,y,z)
+        }
+        const long long dprev = (lane > 0) ? 0 : -1;                                // chunk k-1 of the same row
+        if (emask & 0x008u) ev[3] = vidx(crow[1] + dprev, lp, codep[1], 0u);        // y-edge at (x,y,z)    <- cube (x-1, y, z-1) edge 5
+        if (emask & 0x100u) ev[8] = vidx(crow[2] + dprev, lp, codep[2], 2u);        // z-edge at (x,y,z)    <- cube (x-1, y-1, z) edge 10
+        if (emask & 0x880u) {                                                       // cube (x-1, y, z): edges 5 and 10
+            const long long b = ea.vbase + (long long)cube_vertex_base(offsets, lane_bits, crow[0] + dprev, lp);
+            const unsigned own = d_case_info[codep[0]] >> 8;
+            ev[7] = b + owned_rank(own, 0u);                                        // y-edge at (x,y,z+1)
+            ev[11] = b + owned_rank(own, 2u);                                       // z-edge at (x,y+1,z)
+        }
         // ---- triangles ---------------------------------------------------------------------------------------------------
-        const unsigned t0 = __ballot_sync(0xffffffffu, nt & 1u), t1 = __ballot_sync(0xffffffffu, nt & 2u), t2 = __ballot_sync(0xffffffffu, nt & 4u);
-        if (nt) {
-            const unsigned tbefore = __popc(t0 & lt) + 2u * __popc(t1 & lt) + 4u * __popc(t2 & lt);
-            const long long floc = (long long)offsets[chunk].y + tbefore - ea.f_local0;
-            long long ev[12];            // vertex index per local edge (SURVEY Appendix A + first-appearance cube)
-            ev[0] = i6[3];   // x-edge at (x,y,z)      <- cube (x, y-1, z-1) edge 6
-            ev[1] = i5[1];   // y-edge at (x+1,y,z)    <- cube (x, y, z-1)   edge 5
-            ev[2] = i6[1];   // x-edge at (x,y+1,z)    <- cube (x, y, z-1)   edge 6
-            ev[3] = p5[1];   // y-edge at (x,y,z)      <- cube (x-1, y, z-1) edge 5
-            ev[4] = i6[2];   // x-edge at (x,y,z+1)    <- cube (x, y-1, z)   edge 6
-            ev[5] = i5[0];
-            ev[6] = i6[0];
-            ev[7] = p5[0];   // y-edge at (x,y,z+1)    <- cube (x-1, y, z)   edge 5
-            ev[8] = p10[2];  // z-edge at (x,y,z)      <- cube (x-1, y-1, z) edge 10
-            ev[9] = i10[2];  // z-edge at (x+1,y,z)    <- cube (x, y-1, z)   edge 10
-            ev[10] = i10[0];
-            ev[11] = p10[0]; // z-edge at (x,y+1,z)    <- cube (x-1, y, z)   edge 10
-            const int8_t* tri = d_tri_table + code_self * 16;
-            for (unsigned t = 0; t < nt; ++t) {
-                int* o = faces + (floc + t) * 3;
+        const unsigned ltm = (1u << lane) - 1u;
+        const uint32_t* lb = lane_bits + chunk * 5;
+        const unsigned tbefore = __popc(__ldg(lb + 2) & ltm) + 2u * __popc(__ldg(lb + 3) & ltm) + 4u * __popc(__ldg(lb + 4) & ltm);
+        const long long floc = (long long)offsets[chunk].y + tbefore - ea.f_local0;
+        const int8_t* tri = d_tri_table + code_self * 16;
+        for (unsigned t = 0; t < nt; ++t) {
+            int* o = faces + (floc + t) * 3;
 #pragma unroll
-                for (int c3 = 0; c3 < 3; ++c3) {
-                    const int e = tri[t * 3 + c3];
-                    long long idx = 0;
+            for (int c3 = 0; c3 < 3; ++c3) {
+                const int e = tri[t * 3 + c3];
+                long long idx = 0;
 #pragma unroll
-                    for (int q = 0; q < 12; ++q)
-                        if (e == q) idx = ev[q];
-                    o[c3] = (int)idx;
-                }
+                for (int q = 0; q < 12; ++q)
+                    if (e == q) idx = ev[q];
+                o[c3] = (int)idx;
             }
         }
     }

@@ -77,7 +77,7 @@ const int* isd_device_faces(void);  /* device pointer, 3*Nf ints   */
  * out[0]=field eval, [1]=mc classify+scan, [2]=mc emit, [3]=vertex resampling, [4]=projection,
  * [5]=qem, [6]=device->host mesh copy, [7]=whole build (host wall clock).  Returns entries written. */
 int isd_last_timings(float* out_ms, int cap);
-/* Counters of the last build: [0]=nodes evaluated, [1]=cubes visited, [2]=active chunks,
+/* Counters of the last build: [0]=nodes evaluated, [1]=cubes visited, [2]=cut cubes,
  * [3..9]=centroids resolved by projection direction type 0..6, [10]=projection failed,
  * [11]=bisection capped, [12]=bisected, [13]=kernel launches, [14]=field bytes, [15]=nodes
  * evaluated with the full program (others were proven off-surface and skipped). */

@@ -9,10 +9,10 @@ for R in (200, 256, 512):
         for rep in range(3):
             lib.build_geometry_device(sj, shapes.mc_settings(R, 0.8, **kw)); lib.finish_geometry()
         c = lib.last_counters(); t = lib.last_timings()
-        print(R, bool(kw), c["nodes"], c["nodes_full_eval"], c["active_chunks"], {k: round(v, 4) for k, v in t.items()})
+        print(R, bool(kw), c["nodes"], c["nodes_full_eval"], c["cut_cubes"], {k: round(v, 4) for k, v in t.items()})
 for name, R, half in (("c4_deep_chain", 512, 1.0), ("c3_metaballs", 512, 1.2), ("c4_deep_chain", 1024, 1.0)):
     sj = getattr(shapes, name)()
     for rep in range(2):
         lib.build_geometry_device(sj, shapes.mc_settings(R, half)); lib.finish_geometry()
     c = lib.last_counters(); t = lib.last_timings()
-    print(name, R, c["nodes"], c["nodes_full_eval"], c["active_chunks"], lib.last_slab()["nv"], {k: round(v, 4) for k, v in t.items()})
+    print(name, R, c["nodes"], c["nodes_full_eval"], c["cut_cubes"], lib.last_slab()["nv"], {k: round(v, 4) for k, v in t.items()})
