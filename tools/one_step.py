@@ -1,0 +1,47 @@
+"""One polygonization step for profilers: warm builds outside the capture range, then `--reps` builds between
+cudaProfilerStart/Stop (use `ncu --profile-from-start off`).
+
+  python tools/one_step.py c2 256 [--ob02] [--reps 1] [--gpu key=val ...]
+"""
+import argparse
+import ctypes
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import implisolid_b200
+from implisolid_b200 import shapes
+
+CFG = {"c1": (shapes.c1_sphere, 0.55), "c2": (shapes.c2_cube_minus_cylinder, 0.8), "c3": (shapes.c3_metaballs, 1.2),
+       "c4": (shapes.c4_deep_chain, 1.0)}
+
+ap = argparse.ArgumentParser()
+ap.add_argument("cfg")
+ap.add_argument("R", type=int)
+ap.add_argument("--ob02", action="store_true")
+ap.add_argument("--reps", type=int, default=1)
+ap.add_argument("--warm", type=int, default=2)
+ap.add_argument("--gpu", nargs="*", default=[])
+a = ap.parse_args()
+
+lib = implisolid_b200.load_library()
+fn, half = CFG[a.cfg]
+kw = dict(iters=1, c=1.0, projection=1, qem=1) if a.ob02 else {}
+for kv in a.gpu:
+    k, v = kv.split("=")
+    kw[k] = int(v)
+sj, mc = fn(), shapes.mc_settings(a.R, half, **kw)
+for _ in range(a.warm):
+    lib.build_geometry_device(sj, mc)
+    lib.finish_geometry()
+rt = ctypes.CDLL("libcudart.so.12")
+rt.cudaDeviceSynchronize()
+rt.cudaProfilerStart()
+for _ in range(a.reps):
+    lib.build_geometry_device(sj, mc)
+    lib.finish_geometry()
+rt.cudaDeviceSynchronize()
+rt.cudaProfilerStop()
+c, t, s = lib.last_counters(), lib.last_timings(), lib.last_slab()
+print(a.cfg, a.R, "nodes", c["nodes"], "evaluated", c["nodes_full_eval"], "cut", c["cut_cubes"], "nv", s["nv"], "nf", s["nf"],
+      {k: round(v, 4) for k, v in t.items()})
