@@ -161,25 +161,33 @@ ISD_HD float prim_cube_sdf(const SdfGridView& g, float px, float py, float pz) {
 // ---- value mode -------------------------------------------------------------------------------------------------
 // Evaluates the program at P points held in registers; cur* are clobbered.
 // The two newest values of the stack live in registers (t0 = top, t1 = below); older ones spill to a per-thread
-// array (local memory, L1-resident).  Stack depth is a property of the program, hence uniform across the grid.
-template <int P, class Prog>
-ISD_HD void eval_values(const Prog& prog, const SdfGridView& sdf, float (&cx)[P], float (&cy)[P], float (&cz)[P], float (&out)[P]) {
+// array (local memory, L1-resident).
+//
+// `live(id)` says whether node `id` can influence the result at these points (tile specialisation, field_kernel.cuh:
+// a child of a min/max node that interval bounds prove is never selected over the whole tile is dead).  A dead node is
+// jumped over and pushes nothing; `present` is a bit stack recording, for every node finished so far, whether it left a
+// value, so that a closing CSG instruction knows if it has two operands (select as the reference does), or one (pass it
+// through; a lone second operand of a subtraction is negated: -f2 is what the reference selects there).  A live CSG
+// node always has a live child.  Selecting between the same two floats as the reference, or passing through the one it
+// would select, gives the same bits; AllLive reproduces the reference's full evaluation.
+struct AllLive {
+    ISD_HD bool operator()(uint32_t) const { return true; }
+};
+
+template <int P, class Prog, class Live>
+ISD_HD void eval_values(const Prog& prog, const SdfGridView& sdf, const Live& live, float (&cx)[P], float (&cy)[P], float (&cz)[P],
+                        float (&out)[P]) {
     float spill[kMaxValueStack][P];
     float fs[kMaxFrameStack][3][P];
     float t0[P], t1[P];
 #pragma unroll
     for (int p = 0; p < P; ++p) { t0[p] = 0.0f; t1[p] = 0.0f; }
     int sp = 0, fp = 0, pc = 0;
+    unsigned long long present = 0ull;
     for (;;) {
         const uint32_t word = prog[pc];
         const uint32_t op = word & OP_MASK;
         if (op == OP_END) break;
-        if (op == OP_SAVE) {
-#pragma unroll
-            for (int p = 0; p < P; ++p) { fs[fp][0][p] = cx[p]; fs[fp][1][p] = cy[p]; fs[fp][2][p] = cz[p]; }
-            ++fp; ++pc;
-            continue;
-        }
         if (op == OP_RESTORE) {
             --fp;
 #pragma unroll
@@ -187,32 +195,58 @@ ISD_HD void eval_values(const Prog& prog, const SdfGridView& sdf, float (&cx)[P]
             ++pc;
             continue;
         }
+        if (op >= OP_UNION) {
+            const bool top_there = (present & 1ull) != 0, below_there = (present & 2ull) != 0;
+            present = ((present >> 2) << 1) | 1ull;
+            pc += 13;
+            const bool swapped = (word & OP_FLAG_SWAPPED) != 0;
+            if (top_there && below_there) {
+#pragma unroll
+                for (int p = 0; p < P; ++p) {
+                    const float top = t0[p], below = t1[p];
+                    const float f1 = swapped ? top : below, f2 = swapped ? below : top;
+                    float r;
+                    if (op == OP_UNION) r = (f1 > f2) ? f1 : f2;
+                    else if (op == OP_INTERSECT) r = (f1 > f2) ? f2 : f1;
+                    else r = (f1 < -f2) ? f1 : -f2;
+                    t0[p] = r;
+                }
+                --sp;
+                if (sp >= 2) {
+#pragma unroll
+                    for (int p = 0; p < P; ++p) t1[p] = spill[sp - 2][p];
+                }
+            } else if (op == OP_SUBTRACT) {
+                // the lone operand sits on top; it is f2 when (top is the second-evaluated child) xor swapped
+                const bool lone_is_second_evaluated = top_there;
+                const bool lone_is_f2 = lone_is_second_evaluated != swapped;
+                if (lone_is_f2) {
+#pragma unroll
+                    for (int p = 0; p < P; ++p) t0[p] = -t0[p];
+                }
+            }
+            continue;
+        }
+        // node-opening instruction: XFORM or a primitive
+        if (!live(word >> OP_ID_SHIFT)) {
+            pc = (int)prog[pc + 1];
+            present <<= 1;
+            continue;
+        }
         Mat12<Prog> M;
-        M.load(prog, pc + 1);
-        pc += 13;
+        M.load(prog, pc + 2);
+        pc += 14;
         if (op == OP_XFORM) {
+            if (word & OP_FLAG_SAVE) {
+#pragma unroll
+                for (int p = 0; p < P; ++p) { fs[fp][0][p] = cx[p]; fs[fp][1][p] = cy[p]; fs[fp][2][p] = cz[p]; }
+                ++fp;
+            }
 #pragma unroll
             for (int p = 0; p < P; ++p) {
                 float x, y, z;
                 M.apply(cx[p], cy[p], cz[p], x, y, z);
                 cx[p] = x; cy[p] = y; cz[p] = z;
-            }
-        } else if (op >= OP_UNION) {
-            const bool swapped = (word & OP_FLAG_SWAPPED) != 0;
-#pragma unroll
-            for (int p = 0; p < P; ++p) {
-                const float top = t0[p], below = t1[p];
-                const float f1 = swapped ? top : below, f2 = swapped ? below : top;
-                float r;
-                if (op == OP_UNION) r = (f1 > f2) ? f1 : f2;
-                else if (op == OP_INTERSECT) r = (f1 > f2) ? f2 : f1;
-                else r = (f1 < -f2) ? f1 : -f2;
-                t0[p] = r;
-            }
-            --sp;
-            if (sp >= 2) {
-#pragma unroll
-                for (int p = 0; p < P; ++p) t1[p] = spill[sp - 2][p];
             }
         } else {
             float f[P];
@@ -257,6 +291,7 @@ ISD_HD void eval_values(const Prog& prog, const SdfGridView& sdf, float (&cx)[P]
 #pragma unroll
             for (int p = 0; p < P; ++p) { t1[p] = t0[p]; t0[p] = f[p]; }
             ++sp;
+            present = (present << 1) | 1ull;
         }
     }
 #pragma unroll
@@ -274,12 +309,13 @@ ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, float 
         const uint32_t word = prog[pc];
         const uint32_t op = word & OP_MASK;
         if (op == OP_END) break;
-        if (op == OP_SAVE) { fs[fp][0] = cx; fs[fp][1] = cy; fs[fp][2] = cz; ++fp; ++pc; continue; }
         if (op == OP_RESTORE) { --fp; cx = fs[fp][0]; cy = fs[fp][1]; cz = fs[fp][2]; ++pc; continue; }
         Mat12<Prog> M;
-        M.load(prog, pc + 1);
-        pc += 13;
+        const int hdr = (op >= OP_UNION) ? 1 : 2;      // node-opening instructions carry a skip word (value mode only)
+        M.load(prog, pc + hdr);
+        pc += hdr + 12;
         if (op == OP_XFORM) {
+            if (word & OP_FLAG_SAVE) { fs[fp][0] = cx; fs[fp][1] = cy; fs[fp][2] = cz; ++fp; }
             float x, y, z;
             M.apply(cx, cy, cz, x, y, z);
             cx = x; cy = y; cz = z;

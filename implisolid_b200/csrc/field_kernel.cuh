@@ -59,9 +59,21 @@ __device__ __forceinline__ float fmin3(float a, float b, float c) { return fminf
 // Bounds of the CSG function over the axis-aligned box centre (bx,by,bz), half extents (hx,hy,hz), in grid coordinates.
 // Everything is widened outwards: local boxes by a relative+absolute margin that covers the difference between the
 // composite transform used here and the nested float transforms of the exact evaluator; f bounds by a final margin.
-__device__ inline Ival program_bounds(const uint32_t* __restrict__ bp, float bx, float by, float bz, float hx, float hy, float hz) {
+//
+// With DECIDE, every CSG instruction also records (2 bits, in post-order of the CSG nodes) whether one child can never be
+// selected anywhere in the box: a is the reference's first child (f1), b its second (f2), and the tests mirror the
+// selectors of transformed_union.hpp:47, transformed_intersection.hpp:49, transformed_subtract.hpp:52 with a margin for
+// the rounding of both the bounds and the exact evaluation.
+enum : uint32_t { KEEP_BOTH = 0, KILL_A = 1, KILL_B = 2 };
+__device__ __forceinline__ bool surely_greater(float x, float y) {      // x > y by more than the bounds' uncertainty
+    return x - y > 1e-4f * (1.0f + fabsf(x) + fabsf(y));
+}
+
+template <bool DECIDE>
+__device__ inline Ival program_bounds(const uint32_t* __restrict__ bp, float bx, float by, float bz, float hx, float hy, float hz,
+                                      uint32_t* __restrict__ decisions) {
     Ival st[kMaxValueStack];
-    int sp = 0, pc = 0;
+    int sp = 0, pc = 0, opj = 0;
     for (;;) {
         const uint32_t op = __ldg(bp + pc) & OP_MASK;
         if (op == OP_END) break;
@@ -69,9 +81,24 @@ __device__ inline Ival program_bounds(const uint32_t* __restrict__ bp, float bx,
             ++pc;
             const Ival b = st[--sp], a = st[sp - 1];
             Ival r;
-            if (op == OP_UNION) r = Ival{fmaxf(a.lo, b.lo), fmaxf(a.hi, b.hi)};
-            else if (op == OP_INTERSECT) r = Ival{fminf(a.lo, b.lo), fminf(a.hi, b.hi)};
-            else r = Ival{fminf(a.lo, -b.hi), fminf(a.hi, -b.lo)};
+            uint32_t d = KEEP_BOTH;
+            if (op == OP_UNION) {
+                r = Ival{fmaxf(a.lo, b.lo), fmaxf(a.hi, b.hi)};
+                if (DECIDE) d = surely_greater(a.lo, b.hi) ? KILL_B : (surely_greater(b.lo, a.hi) ? KILL_A : KEEP_BOTH);
+            } else if (op == OP_INTERSECT) {
+                r = Ival{fminf(a.lo, b.lo), fminf(a.hi, b.hi)};
+                if (DECIDE) d = surely_greater(a.lo, b.hi) ? KILL_A : (surely_greater(b.lo, a.hi) ? KILL_B : KEEP_BOTH);
+            } else {
+                r = Ival{fminf(a.lo, -b.hi), fminf(a.hi, -b.lo)};
+                if (DECIDE) d = surely_greater(-b.hi, a.hi) ? KILL_B : (surely_greater(a.lo, -b.lo) ? KILL_A : KEEP_BOTH);
+            }
+            if (DECIDE) {
+                if (d == KILL_A) r = (op == OP_SUBTRACT) ? Ival{-b.hi, -b.lo} : b;      // tighter: the result IS that child
+                else if (d == KILL_B) r = a;
+                if ((opj & 15) == 0) decisions[opj >> 4] = 0u;
+                decisions[opj >> 4] |= d << ((opj & 15) * 2);
+                ++opj;
+            }
             st[sp - 1] = r;
             continue;
         }
@@ -136,12 +163,24 @@ __device__ inline Ival program_bounds(const uint32_t* __restrict__ bp, float bx,
 // tile classes
 enum : uint8_t { TILE_OUTSIDE = 0, TILE_INSIDE = 1, TILE_MIXED = 2 };
 
+// Tile specialisation (SpecDesc::enabled): every work-list tile also gets a liveness mask, one bit per tree node (bit = node id,
+// reverse post-order).  The root is live; a live CSG node passes liveness to the children its decision did not kill.
+struct SpecDesc {
+    int enabled;
+    int num_nodes, num_ops, mask_words;
+    const uint32_t* topo;         // bit i: node id i is a CSG node
+    uint32_t* masks;              // [work-list index][mask_words]
+};
+constexpr int kDecisionWords = kMaxSpecNodes / 2 / 16 + 1;
+
 // One thread per tile.  list_count[0] receives the number of tiles appended to `list`.
-__global__ void __launch_bounds__(128) k_tile_bounds(GridDesc g, const uint32_t* __restrict__ bounds_prog, int prune,
+template <bool SPEC>
+__global__ void __launch_bounds__(128) k_tile_bounds(GridDesc g, const uint32_t* __restrict__ bounds_prog, int prune, SpecDesc spec,
                                                      uint32_t* __restrict__ signs, unsigned* __restrict__ list, unsigned* __restrict__ list_count) {
     const int t = blockIdx.x * 128 + threadIdx.x;
     const int ntiles = g.tx * g.ty * g.tz;
     uint8_t cls = TILE_MIXED;
+    uint32_t decisions[SPEC ? kDecisionWords : 1];
     int tx = 0, ty = 0, tzl = 0;
     const bool valid = t < ntiles;
     if (valid) {
@@ -158,8 +197,8 @@ __global__ void __launch_bounds__(128) k_tile_bounds(GridDesc g, const uint32_t*
             const float ax = node_coord(x0 - 1, g.wx, g.xmin, g.two_wx), bx = node_coord(x1 + 1, g.wx, g.xmin, g.two_wx);
             const float ay = node_coord(y0 - 1, g.wy, g.ymin, g.two_wy), by = node_coord(y1 + 1, g.wy, g.ymin, g.two_wy);
             const float az = node_coord(z0 - 1, g.wz, g.zmin, g.two_wz), bz = node_coord(z1 + 1, g.wz, g.zmin, g.two_wz);
-            const Ival b = program_bounds(bounds_prog, 0.5f * (ax + bx), 0.5f * (ay + by), 0.5f * (az + bz), 0.5f * (bx - ax) * 1.001f,
-                                          0.5f * (by - ay) * 1.001f, 0.5f * (bz - az) * 1.001f);
+            const Ival b = program_bounds<SPEC>(bounds_prog, 0.5f * (ax + bx), 0.5f * (ay + by), 0.5f * (az + bz), 0.5f * (bx - ax) * 1.001f,
+                                                0.5f * (by - ay) * 1.001f, 0.5f * (bz - az) * 1.001f, decisions);
             if (b.hi < 0.0f) cls = TILE_OUTSIDE;
             else if (b.lo > 0.0f && !touches_seal) cls = TILE_INSIDE;
         }
@@ -185,15 +224,47 @@ __global__ void __launch_bounds__(128) k_tile_bounds(GridDesc g, const uint32_t*
         unsigned base = 0;
         if (lane == 0) base = atomicAdd(list_count, (unsigned)__popc(m));
         base = __shfl_sync(0xffffffffu, base, 0);
-        if (mixed) list[base + __popc(m & ((1u << lane) - 1u))] = (unsigned)t;
+        if (mixed) {
+            const unsigned at = base + __popc(m & ((1u << lane) - 1u));
+            list[at] = (unsigned)t;
+            if (SPEC) {
+                uint32_t* out = spec.masks + (size_t)at * spec.mask_words;
+                if (!prune) {
+                    for (int w = 0; w < spec.mask_words; ++w) out[w] = 0xffffffffu;
+                } else {
+                    unsigned long long pending = 1ull;       // stack of liveness flags, top in bit 0 (depth checked on the host)
+                    int opj = spec.num_ops - 1;
+                    uint32_t word = 0u, topo_word = 0u;
+                    for (int i = 0; i < spec.num_nodes; ++i) {
+                        if ((i & 31) == 0) topo_word = __ldg(spec.topo + (i >> 5));
+                        const unsigned long long alive = pending & 1ull;
+                        pending >>= 1;
+                        word |= (uint32_t)alive << (i & 31);
+                        if ((topo_word >> (i & 31)) & 1u) {
+                            const uint32_t d = (decisions[opj >> 4] >> ((opj & 15) * 2)) & 3u;
+                            --opj;
+                            const unsigned long long la = (alive && d != KILL_A) ? 1ull : 0ull, lb = (alive && d != KILL_B) ? 1ull : 0ull;
+                            pending = (pending << 2) | (la << 1) | lb;      // b's subtree comes first in reverse post-order
+                        }
+                        if ((i & 31) == 31 || i + 1 == spec.num_nodes) { out[i >> 5] = word; word = 0u; }
+                    }
+                }
+            }
+        }
     }
 }
 
 constexpr int kTileThreads = 128;
 
+struct TileLive {             // liveness mask of the tile being evaluated (uniform across the block)
+    const uint32_t* mask;
+    __device__ __forceinline__ bool operator()(uint32_t id) const { return (__ldg(mask + (id >> 5)) >> (id & 31)) & 1u; }
+};
+
+template <bool SPEC>
 __global__ void __launch_bounds__(kTileThreads) k_eval_tiles(GridDesc g, SdfGridView sdf, const unsigned* __restrict__ list,
-                                                            const unsigned* __restrict__ list_count, float* __restrict__ field,
-                                                            uint32_t* __restrict__ signs) {
+                                                            const unsigned* __restrict__ list_count, const uint32_t* __restrict__ masks,
+                                                            int mask_words, float* __restrict__ field, uint32_t* __restrict__ signs) {
     const unsigned n = *list_count;
     const int q = threadIdx.x & 1, row = threadIdx.x >> 1;
     uint8_t* sb = reinterpret_cast<uint8_t*>(signs);
@@ -221,7 +292,8 @@ __global__ void __launch_bounds__(kTileThreads) k_eval_tiles(GridDesc g, SdfGrid
                     cy[p] = yy;
                     cz[p] = zz;
                 }
-                eval_values<4>(ConstProgram(), sdf, cx, cy, cz, f);
+                if (SPEC) eval_values<4>(ConstProgram(), sdf, TileLive{masks + (size_t)item * mask_words}, cx, cy, cz, f);
+                else eval_values<4>(ConstProgram(), sdf, AllLive(), cx, cy, cz, f);
                 nib = 0;
 #pragma unroll
                 for (int p = 0; p < 4; ++p) {

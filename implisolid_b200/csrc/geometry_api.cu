@@ -97,8 +97,9 @@ struct Context {
     PinnedBuffer h_verts, h_faces;
 
     // field + marching cubes scratch
-    DeviceBuffer d_field, d_signs, d_tile_list, d_bounds, d_counts, d_lane_bits, d_offsets, d_cubes, d_partials, d_totals, d_cases;
+    DeviceBuffer d_field, d_signs, d_tile_list, d_tile_masks, d_bounds, d_counts, d_lane_bits, d_offsets, d_cubes, d_partials, d_totals, d_cases;
     PinnedBuffer h_small;         // totals and other small read-backs
+    PinnedBuffer h_program;       // staging of the bounds program + topology
     GridDesc grid{};
     McDesc mc{};
     bool keep_field = false, have_cases = false;
@@ -264,20 +265,43 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     const int ntiles = gd.tx * gd.ty * gd.tz;
     g.d_signs.reserve(sign_bytes);
     g.d_tile_list.reserve((size_t)ntiles * sizeof(unsigned) + 64);
-    g.d_bounds.reserve(prog.bounds.size() * sizeof(uint32_t));
+    // bounds program and tree topology share one upload
+    const size_t bounds_words = prog.bounds.size(), topo_words = prog.topo.size();
+    g.d_bounds.reserve((bounds_words + topo_words) * sizeof(uint32_t));
+    SpecDesc spec{};
+    spec.enabled = (s.specialize && prog.can_specialize && prog.num_nodes > 1) ? 1 : 0;
+    spec.num_nodes = prog.num_nodes;
+    spec.num_ops = (prog.num_nodes - 1) / 2;
+    spec.mask_words = (prog.num_nodes + 31) / 32;
+    spec.topo = g.d_bounds.as<uint32_t>() + bounds_words;
+    if (spec.enabled) g.d_tile_masks.reserve((size_t)ntiles * spec.mask_words * sizeof(uint32_t));
+    spec.masks = g.d_tile_masks.as<uint32_t>();
     unsigned* tile_count = g.d_totals.as<unsigned>() + 8;
     ISD_CUDA(cudaEventRecord(g.ev[0], g.stream));
     {   // K1: bounds -> work list -> tiles
-        ISD_CUDA(cudaMemcpyAsync(g.d_bounds.ptr, prog.bounds.data(), prog.bounds.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, g.stream));
+        g.h_program.reserve((bounds_words + topo_words) * sizeof(uint32_t));
+        uint32_t* staged = g.h_program.as<uint32_t>();      // pinned staging: the copy must not read a pageable vector that the
+        memcpy(staged, prog.bounds.data(), bounds_words * sizeof(uint32_t));      // caller may free before the stream gets there
+        memcpy(staged + bounds_words, prog.topo.data(), topo_words * sizeof(uint32_t));
+        ISD_CUDA(cudaMemcpyAsync(g.d_bounds.ptr, staged, (bounds_words + topo_words) * sizeof(uint32_t), cudaMemcpyHostToDevice, g.stream));
         ISD_CUDA(cudaMemsetAsync(g.d_signs.ptr, 0xff, sign_bytes, g.stream));
         ISD_CUDA(cudaMemsetAsync(tile_count, 0, sizeof(unsigned), g.stream));
-        k_tile_bounds<<<(ntiles + 127) / 128, 128, 0, g.stream>>>(gd, g.d_bounds.as<uint32_t>(), s.prune, g.d_signs.as<uint32_t>(),
-                                                                 g.d_tile_list.as<unsigned>(), tile_count);
-        ISD_LAUNCH_CHECK();
         const int blocks = ntiles < g.sm_count * 8 ? ntiles : g.sm_count * 8;
-        k_eval_tiles<<<blocks, kTileThreads, 0, g.stream>>>(gd, g.sdf, g.d_tile_list.as<unsigned>(), tile_count, g.d_field.as<float>(),
-                                                           g.d_signs.as<uint32_t>());
-        ISD_LAUNCH_CHECK();
+        if (spec.enabled) {
+            k_tile_bounds<true><<<(ntiles + 127) / 128, 128, 0, g.stream>>>(gd, g.d_bounds.as<uint32_t>(), s.prune, spec, g.d_signs.as<uint32_t>(),
+                                                                           g.d_tile_list.as<unsigned>(), tile_count);
+            ISD_LAUNCH_CHECK();
+            k_eval_tiles<true><<<blocks, kTileThreads, 0, g.stream>>>(gd, g.sdf, g.d_tile_list.as<unsigned>(), tile_count, spec.masks,
+                                                                     spec.mask_words, g.d_field.as<float>(), g.d_signs.as<uint32_t>());
+            ISD_LAUNCH_CHECK();
+        } else {
+            k_tile_bounds<false><<<(ntiles + 127) / 128, 128, 0, g.stream>>>(gd, g.d_bounds.as<uint32_t>(), s.prune, spec, g.d_signs.as<uint32_t>(),
+                                                                            g.d_tile_list.as<unsigned>(), tile_count);
+            ISD_LAUNCH_CHECK();
+            k_eval_tiles<false><<<blocks, kTileThreads, 0, g.stream>>>(gd, g.sdf, g.d_tile_list.as<unsigned>(), tile_count, nullptr, 0,
+                                                                      g.d_field.as<float>(), g.d_signs.as<uint32_t>());
+            ISD_LAUNCH_CHECK();
+        }
     }
     ISD_CUDA(cudaEventRecord(g.ev[1], g.stream));
     {   // K2

@@ -38,7 +38,7 @@ __device__ __forceinline__ float sign_tol(float v) { return (v > kRootTolerance)
 
 __device__ __forceinline__ float eval_f(const SdfGridView& sdf, float x, float y, float z) {
     float cx[1] = {x}, cy[1] = {y}, cz[1] = {z}, out[1];
-    eval_values<1>(ConstProgram(), sdf, cx, cy, cz, out);
+    eval_values<1>(ConstProgram(), sdf, AllLive(), cx, cy, cz, out);
     return out[0];
 }
 

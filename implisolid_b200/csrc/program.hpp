@@ -8,15 +8,19 @@
 // them, so the program carries one 3x4 inverse per node and the device applies them in the same
 // order — required for bit-identical field values.
 //
-// Program = array of 32-bit words.  Instruction = opcode word (+ payload floats):
-//   XFORM  m[12]            cur <- m * cur                 (entering a CSG node)
-//   SAVE / RESTORE          push / pop cur on the frame stack (only around a CSG child that is itself a CSG node
-//                           and is not evaluated last)
-//   ELLIPSOID|CYLINDER|CONE|CUBE|CUBE_SDF  m[12]      push f(m * cur)         (primitives apply their own inverse)
-//   METABALLS m[12] nb {bx,by,bz,strength,subtract}*nb
+// Program = array of 32-bit words.  Instruction = opcode word (+ payload):
+//   XFORM(+SAVE flag, node id) skip m[12]   entering a CSG node: (push cur on the frame stack when the node is a CSG child
+//                           that is not evaluated last), cur <- m * cur
+//   RESTORE                 pop cur (closes a node entered with the SAVE flag)
+//   ELLIPSOID|CYLINDER|CONE|CUBE|CUBE_SDF (node id) skip m[12]      push f(m * cur)   (primitives apply their own inverse)
+//   METABALLS (node id) skip m[12] nb {bx,by,bz,strength,subtract}*nb
 //   UNION|INTERSECT|SUBTRACT (+SWAPPED flag)  m[12]    pop two values, push the selected one; m is the node's own
 //                           inverse, used only in gradient mode to map the selected child's gradient back
 //   END
+// `skip` is the program counter just past the node's whole code; the opcode word of a node-opening instruction carries
+// the node id in bits 12..31.  Both exist for the tile-specialised field kernel (field_kernel.cuh): per grid tile, interval
+// bounds prove which children of min/max nodes can never be selected, and the evaluator jumps over those nodes.  A node
+// id is the node's index in REVERSE post-order (root = 0), the order in which the liveness pass produces its bits.
 // Children are ordered so the deeper child is evaluated last (no frame to keep while descending), which keeps the
 // frame stack empty and the value stack at one float per level for the left-deep chains the factory builds.
 #pragma once
@@ -48,11 +52,15 @@ enum Opcode : uint32_t {
     OP_SUBTRACT = 12,
     OP_MASK = 0xff,
     OP_FLAG_SWAPPED = 0x100,     // value stack holds (second child, first child)
+    OP_FLAG_SAVE = 0x200,        // XFORM: push cur on the frame stack first
+    OP_ID_SHIFT = 12,
 };
 
 constexpr int kMaxValueStack = 64;     // device limits (csg_eval.cuh)
 constexpr int kMaxFrameStack = 16;
 constexpr int kMaxProgramWords = 14336;   // 56 KB of __constant__
+constexpr int kMaxSpecNodes = 2048;       // tile specialisation: per-tile liveness mask of at most this many bits
+constexpr int kMaxPendingDepth = 64;      // liveness pass: pending-sibling stack held in one 64-bit register
 
 // ---- 3x4 affine inverse -------------------------------------------------------------------------------------
 // Restates what invert_matrix gets from uBLAS lu_factorize + lu_substitute on the 4x4 [M; 0 0 0 1] in binary32:
@@ -132,6 +140,9 @@ public:
         // carrying the COMPOSITE grid->local matrix (product of the nested inverses along its path, formed in double).
         // Only used to prove a tile is entirely inside or outside; never to produce field values.
         std::vector<uint32_t> bounds;
+        // Tree topology for the liveness pass: bit i = node with id i (reverse post-order) is a CSG node.
+        std::vector<uint32_t> topo;
+        bool can_specialize = false;         // nodes <= kMaxSpecNodes and pending depth <= kMaxPendingDepth
         int value_depth = 0, frame_depth = 0, num_nodes = 0;
         bool uses_sdf_grid = false;
         double flops_per_point = 0;          // mul and add counted separately
@@ -140,6 +151,9 @@ public:
     Program compile(const ShapeNode& root) {
         Program p;
         vs_ = fs_ = 0;
+        ids_.clear();
+        int total = count_nodes(root), po = 0;
+        assign_ids(root, total, po);
         emit_node(root, /*preserve=*/false, p);
         p.words.push_back(OP_END);
         {
@@ -147,6 +161,7 @@ public:
             emit_bounds(root, eye, p);
             p.bounds.push_back(OP_END);
         }
+        build_topology(root, total, p);
         if (p.value_depth > kMaxValueStack || p.frame_depth > kMaxFrameStack) {
             fprintf(stderr, "implisolid_b200: shape tree too deep for the device evaluator (value stack %d > %d or frame stack %d > %d)\n",
                     p.value_depth, kMaxValueStack, p.frame_depth, kMaxFrameStack);
@@ -159,9 +174,36 @@ public:
         return p;
     }
 
+    // id of a node of the tree last compiled (reverse post-order index, root = 0)
+    uint32_t id_of(const ShapeNode& n) const {
+        for (const auto& e : ids_) if (e.first == &n) return (uint32_t)e.second;
+        return 0;
+    }
+
 private:
     ShapeOptions opt_;
     int vs_ = 0, fs_ = 0;
+    std::vector<std::pair<const ShapeNode*, int>> ids_;      // node -> id (reverse post-order index)
+
+    static int count_nodes(const ShapeNode& n) { return n.is_csg() ? 1 + count_nodes(*n.a) + count_nodes(*n.b) : 1; }
+    void assign_ids(const ShapeNode& n, int total, int& po) {
+        if (n.is_csg()) { assign_ids(*n.a, total, po); assign_ids(*n.b, total, po); }
+        ids_.push_back({&n, total - 1 - po});
+        ++po;
+    }
+    void build_topology(const ShapeNode& root, int total, Program& p) {
+        p.topo.assign((size_t)(total + 31) / 32, 0u);
+        for (const auto& e : ids_)
+            if (e.first->is_csg()) p.topo[(size_t)e.second >> 5] |= 1u << (e.second & 31);
+        // pending-sibling depth of the liveness pass (walks ids 0..total-1: pop one, a CSG node pushes two)
+        int depth = 1, max_depth = 1;
+        for (int i = 0; i < total; ++i) {
+            --depth;
+            if (p.topo[(size_t)i >> 5] >> (i & 31) & 1u) depth += 2;
+            if (depth > max_depth) max_depth = depth;
+        }
+        p.can_specialize = total <= kMaxSpecNodes && max_depth <= kMaxPendingDepth && total < (1 << (32 - OP_ID_SHIFT));
+    }
 
     static void read_matrix12(const JsonDoc& d, int node, bool ignore_root_matrix, float m[12]) {
         // getMatrix12 (object_factory.hpp:21-30) copies every entry it finds (16 -> overruns REAL[12]); we stop at 12.
@@ -311,7 +353,9 @@ private:
     void emit_node(const ShapeNode& n, bool preserve, Program& p) {
         p.num_nodes++;
         if (!n.is_csg()) {
-            p.words.push_back(n.op);
+            p.words.push_back((uint32_t)n.op | (id_of(n) << OP_ID_SHIFT));
+            const size_t skip_at = p.words.size();
+            p.words.push_back(0u);
             put_matrix(p, n.minv);
             p.flops_per_point += 18;
             switch (n.op) {
@@ -329,14 +373,14 @@ private:
                 }
                 default: break;
             }
+            p.words[skip_at] = (uint32_t)p.words.size();
             push_value(p);
             return;
         }
-        if (preserve) {
-            p.words.push_back(OP_SAVE);
-            if (++fs_ > p.frame_depth) p.frame_depth = fs_;
-        }
-        p.words.push_back(OP_XFORM);
+        if (preserve && ++fs_ > p.frame_depth) p.frame_depth = fs_;
+        p.words.push_back((uint32_t)OP_XFORM | (preserve ? (uint32_t)OP_FLAG_SAVE : 0u) | (id_of(n) << OP_ID_SHIFT));
+        const size_t skip_at = p.words.size();
+        p.words.push_back(0u);
         put_matrix(p, n.minv);
         p.flops_per_point += 18 + 1;
         // deeper child last; ties keep the reference order
@@ -352,6 +396,7 @@ private:
             p.words.push_back(OP_RESTORE);
             --fs_;
         }
+        p.words[skip_at] = (uint32_t)p.words.size();
     }
 };
 

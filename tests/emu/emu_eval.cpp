@@ -46,11 +46,83 @@ void emu_eval(const char* shape_json, int ignore_root_matrix, const float* pts, 
             int j = (i + k < n) ? i + k : n - 1;
             x[k] = pts[j * 3]; y[k] = pts[j * 3 + 1]; z[k] = pts[j * 3 + 2];
         }
-        eval_values<4>(prog, sdf, x, y, z, out);
+        eval_values<4>(prog, sdf, AllLive(), x, y, z, out);
         for (int k = 0; k < 4 && i + k < n; k++) f4_out[i + k] = out[k];
     }
 }
 
 void emu_affine_inverse(const float* in12, float* out12) { affine_inverse(in12, out12); }
 
+}
+
+// ---- tile specialisation: the interpreter's handling of dead nodes ------------------------------------------------------
+// Recursive evaluation of the tree (same primitives, nested transforms) that also records, per point, a liveness mask in
+// which every child NOT selected by its parent's min/max is dead.  eval_values with that mask must return the same bits
+// as the full evaluation: this is the host check of skip offsets, the `present` bit stack and the lone-operand rules.
+namespace {
+struct MaskLive {
+    const uint32_t* m;
+    bool operator()(uint32_t id) const { return (m[id >> 5] >> (id & 31)) & 1u; }
+};
+struct HostMat { const float* w; float operator[](int i) const { return w[i]; } };
+
+float eval_tree(const ShapeCompiler& c, const ShapeNode& n, float x, float y, float z, bool alive, uint32_t* mask) {
+    if (alive) { uint32_t id = c.id_of(n); mask[id >> 5] |= 1u << (id & 31); }
+    const float* m = n.minv;
+    const float lx = m[0] * x + m[1] * y + m[2] * z + m[3];
+    const float ly = m[4] * x + m[5] * y + m[6] * z + m[7];
+    const float lz = m[8] * x + m[9] * y + m[10] * z + m[11];
+    SdfGridView sdf{nullptr, 0, 0, 0, 0, 0, 0, 0};
+    switch (n.op) {
+        case OP_ELLIPSOID: return prim_ellipsoid(lx, ly, lz);
+        case OP_CYLINDER: return prim_cylinder(lx, ly, lz);
+        case OP_CONE: return prim_cone(lx, ly, lz);
+        case OP_CUBE: return prim_cube(lx, ly, lz);
+        case OP_CUBE_SDF: return prim_cube_sdf(sdf, lx, ly, lz);
+        case OP_METABALLS: {
+            float f = 0.0f;
+            for (size_t b = 0; b + 4 < n.params.size(); b += 5) {
+                const float fx = lx - n.params[b], fy = ly - n.params[b + 1], fz = lz - n.params[b + 2];
+                const float h = 0.000001f + fx * fx + fy * fy + fz * fz;
+                const float hinv = 1.0f / h;
+                const float val = n.params[b + 3] * hinv - n.params[b + 4];
+                f += val / 100.0f;
+            }
+            return f;
+        }
+        default: break;
+    }
+    // CSG: evaluate both children unmarked first to learn the selection, then mark the selected one
+    uint32_t scratch[kMaxSpecNodes / 32 + 1];
+    const float f1 = eval_tree(c, *n.a, lx, ly, lz, false, scratch);
+    const float f2 = eval_tree(c, *n.b, lx, ly, lz, false, scratch);
+    bool first;
+    float r;
+    if (n.op == OP_UNION) { first = f1 > f2; r = first ? f1 : f2; }
+    else if (n.op == OP_INTERSECT) { first = !(f1 > f2); r = first ? f1 : f2; }
+    else { first = f1 < -f2; r = first ? f1 : -f2; }
+    if (alive) eval_tree(c, first ? *n.a : *n.b, lx, ly, lz, true, mask);
+    return r;
+}
+}  // namespace
+
+extern "C" int emu_eval_masked(const char* shape_json, const float* pts, int n, float* f_tree, float* f_masked, int* live_nodes) {
+    ShapeOptions o;
+    ShapeCompiler c(o);
+    auto tree = c.parse(shape_json, false);
+    ShapeCompiler::Program p = c.compile(*tree);
+    HostProg prog{p.words.data()};
+    SdfGridView sdf{nullptr, 0, 0, 0, 0, 0, 0, 0};
+    for (int i = 0; i < n; i++) {
+        uint32_t mask[kMaxSpecNodes / 32 + 1];
+        memset(mask, 0, sizeof(mask));
+        f_tree[i] = eval_tree(c, *tree, pts[i * 3], pts[i * 3 + 1], pts[i * 3 + 2], true, mask);
+        float x[1] = {pts[i * 3]}, y[1] = {pts[i * 3 + 1]}, z[1] = {pts[i * 3 + 2]}, out[1];
+        eval_values<1>(prog, sdf, MaskLive{mask}, x, y, z, out);
+        f_masked[i] = out[0];
+        int cnt = 0;
+        for (int k = 0; k < p.num_nodes; k++) cnt += (mask[k >> 5] >> (k & 31)) & 1;
+        live_nodes[i] = cnt;
+    }
+    return p.can_specialize ? p.num_nodes : -p.num_nodes;
 }

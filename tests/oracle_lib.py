@@ -119,6 +119,7 @@ class Emu:
     def __init__(self, path):
         self.lib = ctypes.CDLL(path)
         self.lib.emu_compile.restype = ctypes.c_int
+        self.lib.emu_eval_masked.restype = ctypes.c_int
 
     def compile(self, shape_json, ignore_root_matrix=False):
         words = np.zeros(16384, dtype=np.uint32)
@@ -134,6 +135,15 @@ class Emu:
         self.lib.emu_eval(shape_json.encode(), int(ignore_root_matrix), p.ctypes.data_as(ctypes.c_void_p), n,
                           f.ctypes.data_as(ctypes.c_void_p), f4.ctypes.data_as(ctypes.c_void_p), g.ctypes.data_as(ctypes.c_void_p))
         return f, f4, g
+
+    def eval_masked(self, shape_json, pts):
+        """(tree value, interpreter value with only the selected children live, live node count per point, node count)."""
+        p = np.ascontiguousarray(pts, dtype=np.float32).reshape(-1, 3)
+        n = p.shape[0]
+        ft = np.zeros(n, np.float32); fm = np.zeros(n, np.float32); live = np.zeros(n, np.int32)
+        nodes = self.lib.emu_eval_masked(shape_json.encode(), p.ctypes.data_as(ctypes.c_void_p), n, ft.ctypes.data_as(ctypes.c_void_p),
+                                         fm.ctypes.data_as(ctypes.c_void_p), live.ctypes.data_as(ctypes.c_void_p))
+        return ft, fm, live, nodes
 
     def affine_inverse(self, m12):
         a = np.ascontiguousarray(m12, dtype=np.float32)

@@ -88,6 +88,39 @@ def test_tile_pruning_changes_nothing(gpu_lib, name, shape, R, half):
                 assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
 
 
+SPEC_CASES = [c for c in CASES if c[0] in ("c2_cube_cyl_r100", "c3_metaballs", "c4_chain", "moon", "bushy")] + [
+    ("c4_r160", shapes.c4_deep_chain, 160, 1.0), ("c3_r120", shapes.c3_metaballs, 120, 1.2), ("bushy_r150", shapes.bushy_tree, 150, 0.9),
+    ("c2_r200", shapes.c2_cube_minus_cylinder, 200, 0.8), ("c4_r301", shapes.c4_deep_chain, 301, 1.0)]
+
+
+@pytest.mark.parametrize("name,shape,R,half", SPEC_CASES, ids=[c[0] for c in SPEC_CASES])
+def test_tile_specialisation_changes_nothing(gpu_lib, name, shape, R, half):
+    """Per-tile liveness masks (the default) skip CSG children that interval bounds prove are never selected in a tile.
+    The field must keep the same bits in every node of every tile that holds a cut cube, and the mesh must be identical."""
+    sj = shape()
+    gpu_lib.build_geometry(sj, _mc(R, half, specialize=0, debug_cases=1))
+    v0, f0, field0, cases0 = gpu_lib.get_v(), gpu_lib.get_f(), gpu_lib.get_field(), gpu_lib.get_case_codes()
+    gpu_lib.finish_geometry()
+    gpu_lib.build_geometry(sj, _mc(R, half, specialize=1, debug_cases=1))
+    v1, f1, field1, cases1 = gpu_lib.get_v(), gpu_lib.get_f(), gpu_lib.get_field(), gpu_lib.get_case_codes()
+    gpu_lib.finish_geometry()
+    assert np.array_equal(cases0, cases1)
+    assert np.array_equal(f0, f1) and np.array_equal(v0.view(np.uint32), v1.view(np.uint32))
+    S = field0.shape[0]
+    T = (S + 7) // 8
+    tiles = np.zeros((T, T, T), dtype=bool)
+    cut = (cases0 != 0) & (cases0 != 255)
+    zz, yy, xx = np.nonzero(cut)
+    for dz in (0, 1):
+        for dy in (0, 1):
+            for dx in (0, 1):
+                tiles[(zz + 1 + dz) // 8, (yy + 1 + dy) // 8, (xx + 1 + dx) // 8] = True
+    node_mask = np.repeat(np.repeat(np.repeat(tiles, 8, axis=0), 8, axis=1), 8, axis=2)[:S, :S, :S]
+    assert node_mask.sum() > 0 or f0.shape[0] == 0
+    a, b = field0[node_mask], field1[node_mask]
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), "specialised tiles differ in %d nodes" % int((a.view(np.uint32) != b.view(np.uint32)).sum())
+
+
 def test_mesh_is_closed_manifold(gpu_lib):
     v, f = gpu_lib.polygonize(shapes.c2_cube_minus_cylinder(), _mc(96, 0.8))
     e = np.concatenate([f[:, [0, 1]], f[:, [1, 2]], f[:, [2, 0]]])

@@ -37,4 +37,21 @@ def test_program_shape(emu):
     assert st["frame_depth"] == 1
     words, st = emu.compile(shapes.c2_cube_minus_cylinder(), ignore_root_matrix=True)
     eye = np.array([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0], dtype=np.float32).view(np.uint32)
-    assert words[0] == 1 and np.array_equal(words[1:13], eye)       # OP_XFORM with the identity (copy_eye, object_factory.hpp:47)
+    # OP_XFORM of node id 0 (root), skip word = END's pc, then the identity (copy_eye, object_factory.hpp:47)
+    assert words[0] == 1 and words[1] == len(words) - 1 and np.array_equal(words[2:14], eye)
+
+
+@pytest.mark.parametrize("name", SHAPES)
+def test_dead_children_are_skipped_without_changing_bits(emu, oracle, name):
+    """Tile specialisation, interpreter side: with every unselected child of every min/max node marked dead, the program
+    evaluator must return the same bits as the full tree (skip offsets, operand bookkeeping, -f2 for a lone subtrahend)."""
+    sj = getattr(shapes, name)()
+    rng = np.random.default_rng(5)
+    pts = np.concatenate([rng.uniform(-1.2, 1.2, (1500, 3)), rng.normal(0, 0.3, (500, 3))]).astype(np.float32)
+    ft, fm, live, nodes = emu.eval_masked(sj, pts)
+    fo = oracle.query_implicit_values(sj, pts)
+    assert nodes > 0                                  # every synthetic shape is small enough to specialise
+    assert np.array_equal(ft.view(np.uint32), fo.view(np.uint32))
+    assert np.array_equal(fm.view(np.uint32), fo.view(np.uint32))
+    depth_bound = int(np.ceil(np.log2(nodes + 1))) if name == "bushy_tree" else nodes
+    assert live.max() <= depth_bound and live.min() >= 1
