@@ -48,12 +48,17 @@ ISD_HD float as_float(uint32_t w) {
 // std::min as the reference calls it: (b < a) ? b : a
 ISD_HD float ref_min(float a, float b) { return (b < a) ? b : a; }
 
+struct W4 { uint32_t x, y, z, w; };      // one 128-bit fetch of the program (Prog::load4(word index), index % 4 == 0)
+
 template <class Prog>
 struct Mat12 {
     float m[12];
     ISD_HD void load(const Prog& prog, int at) {
 #pragma unroll
-        for (int i = 0; i < 12; ++i) m[i] = as_float(prog[at + i]);
+        for (int r = 0; r < 3; ++r) {
+            const W4 q = prog.load4(at + 4 * r);
+            m[4 * r] = as_float(q.x); m[4 * r + 1] = as_float(q.y); m[4 * r + 2] = as_float(q.z); m[4 * r + 3] = as_float(q.w);
+        }
     }
     ISD_HD void apply(float x, float y, float z, float& ox, float& oy, float& oz) const {
         ox = m[0] * x + m[1] * y + m[2] * z + m[3];
@@ -185,20 +190,14 @@ ISD_HD void eval_values(const Prog& prog, const SdfGridView& sdf, const Live& li
     int sp = 0, fp = 0, pc = 0;
     unsigned long long present = 0ull;
     for (;;) {
-        const uint32_t word = prog[pc];
+        const W4 hdr = prog.load4(pc);
+        const uint32_t word = hdr.x;
         const uint32_t op = word & OP_MASK;
         if (op == OP_END) break;
-        if (op == OP_RESTORE) {
-            --fp;
-#pragma unroll
-            for (int p = 0; p < P; ++p) { cx[p] = fs[fp][0][p]; cy[p] = fs[fp][1][p]; cz[p] = fs[fp][2][p]; }
-            ++pc;
-            continue;
-        }
         if (op >= OP_UNION) {
             const bool top_there = (present & 1ull) != 0, below_there = (present & 2ull) != 0;
             present = ((present >> 2) << 1) | 1ull;
-            pc += 13;
+            pc += kInstrWords;
             const bool swapped = (word & OP_FLAG_SWAPPED) != 0;
             if (top_there && below_there) {
 #pragma unroll
@@ -218,24 +217,28 @@ ISD_HD void eval_values(const Prog& prog, const SdfGridView& sdf, const Live& li
                 }
             } else if (op == OP_SUBTRACT) {
                 // the lone operand sits on top; it is f2 when (top is the second-evaluated child) xor swapped
-                const bool lone_is_second_evaluated = top_there;
-                const bool lone_is_f2 = lone_is_second_evaluated != swapped;
+                const bool lone_is_f2 = top_there != swapped;
                 if (lone_is_f2) {
 #pragma unroll
                     for (int p = 0; p < P; ++p) t0[p] = -t0[p];
                 }
             }
+            if (word & OP_FLAG_RESTORE) {
+                --fp;
+#pragma unroll
+                for (int p = 0; p < P; ++p) { cx[p] = fs[fp][0][p]; cy[p] = fs[fp][1][p]; cz[p] = fs[fp][2][p]; }
+            }
             continue;
         }
         // node-opening instruction: XFORM or a primitive
         if (!live(word >> OP_ID_SHIFT)) {
-            pc = (int)prog[pc + 1];
+            pc = (int)hdr.y;
             present <<= 1;
             continue;
         }
         Mat12<Prog> M;
-        M.load(prog, pc + 2);
-        pc += 14;
+        M.load(prog, pc + 4);
+        pc += kInstrWords;
         if (op == OP_XFORM) {
             if (word & OP_FLAG_SAVE) {
 #pragma unroll
@@ -251,15 +254,15 @@ ISD_HD void eval_values(const Prog& prog, const SdfGridView& sdf, const Live& li
         } else {
             float f[P];
             if (op == OP_METABALLS) {
-                const int nb = (int)prog[pc];
-                ++pc;
+                const int nb = (int)hdr.z;
                 float lx[P], ly[P], lz[P];
 #pragma unroll
                 for (int p = 0; p < P; ++p) { M.apply(cx[p], cy[p], cz[p], lx[p], ly[p], lz[p]); f[p] = 0.0f; }
                 for (int b = 0; b < nb; ++b) {
-                    const float bx = as_float(prog[pc]), by = as_float(prog[pc + 1]), bz = as_float(prog[pc + 2]);
-                    const float strength = as_float(prog[pc + 3]), subtract = as_float(prog[pc + 4]);
-                    pc += 5;
+                    const W4 q = prog.load4(pc), q2 = prog.load4(pc + 4);
+                    const float bx = as_float(q.x), by = as_float(q.y), bz = as_float(q.z);
+                    const float strength = as_float(q.w), subtract = as_float(q2.x);
+                    pc += 8;
 #pragma unroll
                     for (int p = 0; p < P; ++p) {
                         const float fx = lx[p] - bx, fx2 = fx * fx;
@@ -306,14 +309,13 @@ ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, float 
     float fs[kMaxFrameStack][3];
     int sp = 0, fp = 0, pc = 0;
     for (;;) {
-        const uint32_t word = prog[pc];
+        const W4 hdr = prog.load4(pc);
+        const uint32_t word = hdr.x;
         const uint32_t op = word & OP_MASK;
         if (op == OP_END) break;
-        if (op == OP_RESTORE) { --fp; cx = fs[fp][0]; cy = fs[fp][1]; cz = fs[fp][2]; ++pc; continue; }
         Mat12<Prog> M;
-        const int hdr = (op >= OP_UNION) ? 1 : 2;      // node-opening instructions carry a skip word (value mode only)
-        M.load(prog, pc + hdr);
-        pc += hdr + 12;
+        M.load(prog, pc + 4);
+        pc += kInstrWords;
         if (op == OP_XFORM) {
             if (word & OP_FLAG_SAVE) { fs[fp][0] = cx; fs[fp][1] = cy; fs[fp][2] = cz; ++fp; }
             float x, y, z;
@@ -336,18 +338,19 @@ ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, float 
             float o0, o1, o2;
             M.back(a0, a1, a2, o0, o1, o2);
             vs[sp - 1][0] = r; vs[sp - 1][1] = o0; vs[sp - 1][2] = o1; vs[sp - 1][3] = o2;
+            if (word & OP_FLAG_RESTORE) { --fp; cx = fs[fp][0]; cy = fs[fp][1]; cz = fs[fp][2]; }
         } else {
             float x, y, z;
             M.apply(cx, cy, cz, x, y, z);
             float f, g0, g1, g2;
             if (op == OP_METABALLS) {
-                const int nb = (int)prog[pc];
-                ++pc;
+                const int nb = (int)hdr.z;
                 f = 0.0f; g0 = 0.0f; g1 = 0.0f; g2 = 0.0f;
                 for (int b = 0; b < nb; ++b) {
-                    const float bx = as_float(prog[pc]), by = as_float(prog[pc + 1]), bz = as_float(prog[pc + 2]);
-                    const float strength = as_float(prog[pc + 3]), subtract = as_float(prog[pc + 4]);
-                    pc += 5;
+                    const W4 q = prog.load4(pc), q2 = prog.load4(pc + 4);
+                    const float bx = as_float(q.x), by = as_float(q.y), bz = as_float(q.z);
+                    const float strength = as_float(q.w), subtract = as_float(q2.x);
+                    pc += 8;
                     const float fx = x - bx, fx2 = fx * fx;
                     const float fy = y - by, fy2 = fy * fy;
                     const float fz = z - bz, fz2 = fz * fz;

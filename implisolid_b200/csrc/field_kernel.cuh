@@ -22,10 +22,17 @@
 
 namespace isd {
 
-__constant__ uint32_t c_program[kMaxProgramWords];
+// The program lives in global memory; every thread of a block walks it in step, so its 128-bit fetches are broadcasts
+// served by L1.  (It used to sit in __constant__ memory: the interpreter's program counter is not provably uniform,
+// so every word became an indexed LDC through the address-divergence unit, which ncu showed as the busiest pipe of
+// k_eval_tiles — 12 of them per matrix against 3 LDG.128 now.)
+__device__ uint4 d_program[kMaxProgramWords / 4];
 
 struct ConstProgram {
-    __device__ __forceinline__ uint32_t operator[](int i) const { return c_program[i]; }
+    __device__ __forceinline__ W4 load4(int i) const {
+        const uint4 q = __ldg(&d_program[i >> 2]);
+        return W4{q.x, q.y, q.z, q.w};
+    }
 };
 
 struct GridDesc {
@@ -258,17 +265,32 @@ constexpr int kTileThreads = 128;
 
 struct TileLive {             // liveness mask of the tile being evaluated (uniform across the block)
     const uint32_t* mask;
-    __device__ __forceinline__ bool operator()(uint32_t id) const { return (__ldg(mask + (id >> 5)) >> (id & 31)) & 1u; }
+    unsigned long long first64;       // ids 0..63 in a register pair: no load on the interpreter's critical path
+    __device__ __forceinline__ TileLive(const uint32_t* m, int words) : mask(m) {
+        const uint32_t lo = __ldg(m), hi = words > 1 ? __ldg(m + 1) : 0u;
+        first64 = ((unsigned long long)hi << 32) | lo;
+    }
+    __device__ __forceinline__ bool operator()(uint32_t id) const {
+        if (id < 64u) return (first64 >> id) & 1ull;
+        return (__ldg(mask + (id >> 5)) >> (id & 31)) & 1u;
+    }
 };
 
 template <bool SPEC>
 __global__ void __launch_bounds__(kTileThreads) k_eval_tiles(GridDesc g, SdfGridView sdf, const unsigned* __restrict__ list,
                                                             const unsigned* __restrict__ list_count, const uint32_t* __restrict__ masks,
                                                             int mask_words, float* __restrict__ field, uint32_t* __restrict__ signs) {
-    const unsigned n = *list_count;
+    const unsigned n = list_count[0];
+    unsigned* next_item = const_cast<unsigned*>(list_count) + 1;      // dynamic queue: specialised tiles differ a lot in cost
     const int q = threadIdx.x & 1, row = threadIdx.x >> 1;
     uint8_t* sb = reinterpret_cast<uint8_t*>(signs);
-    for (unsigned item = blockIdx.x; item < n; item += gridDim.x) {
+    __shared__ unsigned s_item;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_item = atomicAdd(next_item, 1u);
+        __syncthreads();
+        const unsigned item = s_item;
+        if (item >= n) break;
         const int t = (int)list[item];
         const int tx = t % g.tx;
         const int r = t / g.tx;
@@ -292,7 +314,7 @@ __global__ void __launch_bounds__(kTileThreads) k_eval_tiles(GridDesc g, SdfGrid
                     cy[p] = yy;
                     cz[p] = zz;
                 }
-                if (SPEC) eval_values<4>(ConstProgram(), sdf, TileLive{masks + (size_t)item * mask_words}, cx, cy, cz, f);
+                if (SPEC) eval_values<4>(ConstProgram(), sdf, TileLive(masks + (size_t)item * mask_words, mask_words), cx, cy, cz, f);
                 else eval_values<4>(ConstProgram(), sdf, AllLive(), cx, cy, cz, f);
                 nib = 0;
 #pragma unroll

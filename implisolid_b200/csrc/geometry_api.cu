@@ -184,7 +184,7 @@ inline void launched() { g.launches++; }
 #define ISD_LAUNCH_CHECK() do { ISD_CUDA(cudaGetLastError()); launched(); } while (0)
 
 void upload_program(const std::vector<uint32_t>& words) {
-    ISD_CUDA(cudaMemcpyToSymbolAsync(c_program, words.data(), words.size() * sizeof(uint32_t), 0, cudaMemcpyHostToDevice, g.stream));
+    ISD_CUDA(cudaMemcpyToSymbolAsync(d_program, words.data(), words.size() * sizeof(uint32_t), 0, cudaMemcpyHostToDevice, g.stream));
 }
 
 ShapeCompiler::Program compile_shape(const char* shape_json, bool ignore_root_matrix, int cube_mode) {
@@ -285,8 +285,14 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         memcpy(staged + bounds_words, prog.topo.data(), topo_words * sizeof(uint32_t));
         ISD_CUDA(cudaMemcpyAsync(g.d_bounds.ptr, staged, (bounds_words + topo_words) * sizeof(uint32_t), cudaMemcpyHostToDevice, g.stream));
         ISD_CUDA(cudaMemsetAsync(g.d_signs.ptr, 0xff, sign_bytes, g.stream));
-        ISD_CUDA(cudaMemsetAsync(tile_count, 0, sizeof(unsigned), g.stream));
-        const int blocks = ntiles < g.sm_count * 8 ? ntiles : g.sm_count * 8;
+        ISD_CUDA(cudaMemsetAsync(tile_count, 0, 2 * sizeof(unsigned), g.stream));      // work-list length, queue head
+        static int resident[2] = {0, 0};      // blocks per SM of the two instantiations (persistent grid = what fits at once)
+        if (!resident[0]) {
+            ISD_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident[0], k_eval_tiles<false>, kTileThreads, 0));
+            ISD_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident[1], k_eval_tiles<true>, kTileThreads, 0));
+        }
+        const int want = g.sm_count * resident[spec.enabled ? 1 : 0];
+        const int blocks = ntiles < want ? ntiles : want;
         if (spec.enabled) {
             k_tile_bounds<true><<<(ntiles + 127) / 128, 128, 0, g.stream>>>(gd, g.d_bounds.as<uint32_t>(), s.prune, spec, g.d_signs.as<uint32_t>(),
                                                                            g.d_tile_list.as<unsigned>(), tile_count);

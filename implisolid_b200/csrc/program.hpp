@@ -8,15 +8,17 @@
 // them, so the program carries one 3x4 inverse per node and the device applies them in the same
 // order — required for bit-identical field values.
 //
-// Program = array of 32-bit words.  Instruction = opcode word (+ payload):
-//   XFORM(+SAVE flag, node id) skip m[12]   entering a CSG node: (push cur on the frame stack when the node is a CSG child
-//                           that is not evaluated last), cur <- m * cur
-//   RESTORE                 pop cur (closes a node entered with the SAVE flag)
-//   ELLIPSOID|CYLINDER|CONE|CUBE|CUBE_SDF (node id) skip m[12]      push f(m * cur)   (primitives apply their own inverse)
-//   METABALLS (node id) skip m[12] nb {bx,by,bz,strength,subtract}*nb
-//   UNION|INTERSECT|SUBTRACT (+SWAPPED flag)  m[12]    pop two values, push the selected one; m is the node's own
-//                           inverse, used only in gradient mode to map the selected child's gradient back
-//   END
+// Program = array of 32-bit words in global memory, every instruction aligned to 16 bytes so that the interpreter
+// fetches it with 128-bit loads (one for the header, three for a 3x4 matrix):
+//   header = {opcode | flags | node id << 12, skip, aux, 0}
+//   XFORM(+SAVE flag) hdr m[12]     entering a CSG node: (push cur on the frame stack when the node is a CSG child that is
+//                                   not evaluated last), cur <- m * cur
+//   ELLIPSOID|CYLINDER|CONE|CUBE|CUBE_SDF hdr m[12]     push f(m * cur)   (primitives apply their own inverse)
+//   METABALLS hdr(aux = nb) m[12] {bx,by,bz,strength, subtract,0,0,0}*nb
+//   UNION|INTERSECT|SUBTRACT (+SWAPPED, +RESTORE flags) hdr m[12]   pop two values, push the selected one; m is the node's
+//                                   own inverse, used only in gradient mode to map the selected child's gradient back;
+//                                   RESTORE: then pop cur (closes a node entered with the SAVE flag)
+//   END hdr
 // `skip` is the program counter just past the node's whole code; the opcode word of a node-opening instruction carries
 // the node id in bits 12..31.  Both exist for the tile-specialised field kernel (field_kernel.cuh): per grid tile, interval
 // bounds prove which children of min/max nodes can never be selected, and the evaluator jumps over those nodes.  A node
@@ -39,8 +41,6 @@ namespace isd {
 enum Opcode : uint32_t {
     OP_END = 0,
     OP_XFORM = 1,
-    OP_SAVE = 2,
-    OP_RESTORE = 3,
     OP_ELLIPSOID = 4,
     OP_CYLINDER = 5,
     OP_CONE = 6,
@@ -53,12 +53,14 @@ enum Opcode : uint32_t {
     OP_MASK = 0xff,
     OP_FLAG_SWAPPED = 0x100,     // value stack holds (second child, first child)
     OP_FLAG_SAVE = 0x200,        // XFORM: push cur on the frame stack first
+    OP_FLAG_RESTORE = 0x400,     // closing CSG instruction: pop cur from the frame stack afterwards
     OP_ID_SHIFT = 12,
 };
 
 constexpr int kMaxValueStack = 64;     // device limits (csg_eval.cuh)
 constexpr int kMaxFrameStack = 16;
-constexpr int kMaxProgramWords = 14336;   // 56 KB of __constant__
+constexpr int kMaxProgramWords = 32768;   // 128 KB of global memory (a __device__ array, field_kernel.cuh)
+constexpr int kInstrWords = 16;           // header (4 words) + 3x4 matrix
 constexpr int kMaxSpecNodes = 2048;       // tile specialisation: per-tile liveness mask of at most this many bits
 constexpr int kMaxPendingDepth = 64;      // liveness pass: pending-sibling stack held in one 64-bit register
 
@@ -155,7 +157,7 @@ public:
         int total = count_nodes(root), po = 0;
         assign_ids(root, total, po);
         emit_node(root, /*preserve=*/false, p);
-        p.words.push_back(OP_END);
+        put_header(p, OP_END, 0u);
         {
             double eye[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
             emit_bounds(root, eye, p);
@@ -316,6 +318,14 @@ private:
         }
     }
 
+    // returns the index of the header's skip word
+    static size_t put_header(Program& p, uint32_t word0, uint32_t aux) {
+        p.words.push_back(word0);
+        p.words.push_back(0u);
+        p.words.push_back(aux);
+        p.words.push_back(0u);
+        return p.words.size() - 3;
+    }
     static void put_matrix(Program& p, const float m[12]) {
         for (int i = 0; i < 12; ++i) { uint32_t w; memcpy(&w, &m[i], 4); p.words.push_back(w); }
     }
@@ -353,9 +363,7 @@ private:
     void emit_node(const ShapeNode& n, bool preserve, Program& p) {
         p.num_nodes++;
         if (!n.is_csg()) {
-            p.words.push_back((uint32_t)n.op | (id_of(n) << OP_ID_SHIFT));
-            const size_t skip_at = p.words.size();
-            p.words.push_back(0u);
+            const size_t skip_at = put_header(p, (uint32_t)n.op | (id_of(n) << OP_ID_SHIFT), (uint32_t)(n.params.size() / 5));
             put_matrix(p, n.minv);
             p.flops_per_point += 18;
             switch (n.op) {
@@ -366,8 +374,10 @@ private:
                 case OP_CUBE_SDF: p.flops_per_point += 40; p.uses_sdf_grid = true; break;
                 case OP_METABALLS: {
                     uint32_t nb = (uint32_t)(n.params.size() / 5);
-                    p.words.push_back(nb);
-                    for (float v : n.params) { uint32_t w; memcpy(&w, &v, 4); p.words.push_back(w); }
+                    for (uint32_t b = 0; b < nb; ++b) {
+                        for (int k = 0; k < 5; ++k) { uint32_t w; memcpy(&w, &n.params[b * 5 + k], 4); p.words.push_back(w); }
+                        for (int k = 5; k < 8; ++k) p.words.push_back(0u);
+                    }
                     p.flops_per_point += 12.0 * nb;
                     break;
                 }
@@ -378,9 +388,7 @@ private:
             return;
         }
         if (preserve && ++fs_ > p.frame_depth) p.frame_depth = fs_;
-        p.words.push_back((uint32_t)OP_XFORM | (preserve ? (uint32_t)OP_FLAG_SAVE : 0u) | (id_of(n) << OP_ID_SHIFT));
-        const size_t skip_at = p.words.size();
-        p.words.push_back(0u);
+        const size_t skip_at = put_header(p, (uint32_t)OP_XFORM | (preserve ? (uint32_t)OP_FLAG_SAVE : 0u) | (id_of(n) << OP_ID_SHIFT), 0u);
         put_matrix(p, n.minv);
         p.flops_per_point += 18 + 1;
         // deeper child last; ties keep the reference order
@@ -389,13 +397,10 @@ private:
         const ShapeNode& second = b_first ? *n.a : *n.b;
         emit_node(first, /*preserve=*/first.is_csg(), p);
         emit_node(second, /*preserve=*/false, p);
-        p.words.push_back((uint32_t)n.op | (b_first ? (uint32_t)OP_FLAG_SWAPPED : 0u));
+        put_header(p, (uint32_t)n.op | (b_first ? (uint32_t)OP_FLAG_SWAPPED : 0u) | (preserve ? (uint32_t)OP_FLAG_RESTORE : 0u), 0u);
         put_matrix(p, n.minv);
         vs_ -= 1;   // pops two, pushes one
-        if (preserve) {
-            p.words.push_back(OP_RESTORE);
-            --fs_;
-        }
+        if (preserve) --fs_;
         p.words[skip_at] = (uint32_t)p.words.size();
     }
 };

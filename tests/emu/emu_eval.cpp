@@ -9,7 +9,7 @@ using namespace isd;
 
 struct HostProg {
     const uint32_t* w;
-    uint32_t operator[](int i) const { return w[i]; }
+    W4 load4(int i) const { return W4{w[i], w[i + 1], w[i + 2], w[i + 3]}; }
 };
 
 extern "C" {
@@ -64,7 +64,6 @@ struct MaskLive {
     const uint32_t* m;
     bool operator()(uint32_t id) const { return (m[id >> 5] >> (id & 31)) & 1u; }
 };
-struct HostMat { const float* w; float operator[](int i) const { return w[i]; } };
 
 float eval_tree(const ShapeCompiler& c, const ShapeNode& n, float x, float y, float z, bool alive, uint32_t* mask) {
     if (alive) { uint32_t id = c.id_of(n); mask[id >> 5] |= 1u << (id & 31); }

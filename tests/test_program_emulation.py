@@ -38,7 +38,8 @@ def test_program_shape(emu):
     words, st = emu.compile(shapes.c2_cube_minus_cylinder(), ignore_root_matrix=True)
     eye = np.array([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0], dtype=np.float32).view(np.uint32)
     # OP_XFORM of node id 0 (root), skip word = END's pc, then the identity (copy_eye, object_factory.hpp:47)
-    assert words[0] == 1 and words[1] == len(words) - 1 and np.array_equal(words[2:14], eye)
+    assert words[0] == 1 and words[1] == len(words) - 4 and np.array_equal(words[4:16], eye)
+    assert len(words) % 4 == 0                                      # every instruction is 16-byte aligned
 
 
 @pytest.mark.parametrize("name", SHAPES)
