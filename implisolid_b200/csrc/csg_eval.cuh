@@ -301,6 +301,135 @@ ISD_HD void eval_values(const Prog& prog, const SdfGridView& sdf, const Live& li
     for (int p = 0; p < P; ++p) out[p] = t0[p];
 }
 
+// ---- value mode over a per-tile instruction list (tile specialisation) ---------------------------------------------
+// spec_entry decides what one program instruction does in a tile whose live nodes are given by `live`:
+//   node-opening instruction : runs iff its node is live;
+//   closing instruction      : runs iff its CSG node is live and it has something to do — select between two live children
+//                              (COMBINE), negate the lone second child of a subtraction (NEGATE: -f2 is what the reference
+//                              selects there), or pop the coordinate frame (RESTORE).
+// Returns 0 when the instruction is skipped.  The list in program order is then run by eval_values_list, which does
+// exactly what eval_values does with the same `live`, minus all the bookkeeping.
+template <class Live>
+ISD_HD uint32_t spec_entry(const W4& it, const Live& live) {
+    if (!live(it.y)) return 0u;
+    if (!(it.x & IT_CLOSING)) return (it.x & IT_PC_MASK) | LE_VALID;
+    const bool la = live(it.z), lb = live(it.w);
+    const uint32_t op = (it.x >> IT_OP_SHIFT) & 3u;
+    uint32_t e = (it.x & (IT_PC_MASK | IT_CLOSING | IT_RESTORE | IT_SWAPPED)) | (op << LE_OP_SHIFT);      // same bit positions as LE_*
+    if (la && lb) e |= LE_COMBINE;
+    else if (op == (uint32_t)OP_SUBTRACT - (uint32_t)OP_UNION && lb) e |= LE_NEGATE;
+    if (!(e & (LE_COMBINE | LE_NEGATE | LE_RESTORE))) return 0u;
+    return e | LE_VALID;
+}
+
+template <int P, class Prog, class List>
+ISD_HD void eval_values_list(const Prog& prog, const SdfGridView& sdf, const List& list, int n_list, float (&cx)[P], float (&cy)[P],
+                             float (&cz)[P], float (&out)[P]) {
+    float spill[kMaxValueStack][P];
+    float fs[kMaxFrameStack][3][P];
+    float t0[P], t1[P];
+#pragma unroll
+    for (int p = 0; p < P; ++p) { t0[p] = 0.0f; t1[p] = 0.0f; }
+    int sp = 0, fp = 0;
+    for (int k = 0; k < n_list; ++k) {
+        const uint32_t e = list[k];
+        int pc = (int)(e & IT_PC_MASK) * 4;
+        if (e & LE_CLOSING) {
+            if (e & LE_COMBINE) {
+                const bool swapped = (e & LE_SWAPPED) != 0;
+                const uint32_t op = (e >> LE_OP_SHIFT) & 3u;
+#pragma unroll
+                for (int p = 0; p < P; ++p) {
+                    const float top = t0[p], below = t1[p];
+                    const float f1 = swapped ? top : below, f2 = swapped ? below : top;
+                    float r;
+                    if (op == 0u) r = (f1 > f2) ? f1 : f2;
+                    else if (op == 1u) r = (f1 > f2) ? f2 : f1;
+                    else r = (f1 < -f2) ? f1 : -f2;
+                    t0[p] = r;
+                }
+                --sp;
+                if (sp >= 2) {
+#pragma unroll
+                    for (int p = 0; p < P; ++p) t1[p] = spill[sp - 2][p];
+                }
+            } else if (e & LE_NEGATE) {
+#pragma unroll
+                for (int p = 0; p < P; ++p) t0[p] = -t0[p];
+            }
+            if (e & LE_RESTORE) {
+                --fp;
+#pragma unroll
+                for (int p = 0; p < P; ++p) { cx[p] = fs[fp][0][p]; cy[p] = fs[fp][1][p]; cz[p] = fs[fp][2][p]; }
+            }
+            continue;
+        }
+        const W4 hdr = prog.load4(pc);
+        const uint32_t word = hdr.x;
+        const uint32_t op = word & OP_MASK;
+        Mat12<Prog> M;
+        M.load(prog, pc + 4);
+        pc += kInstrWords;
+        if (op == OP_XFORM) {
+            if (word & OP_FLAG_SAVE) {
+#pragma unroll
+                for (int p = 0; p < P; ++p) { fs[fp][0][p] = cx[p]; fs[fp][1][p] = cy[p]; fs[fp][2][p] = cz[p]; }
+                ++fp;
+            }
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                float x, y, z;
+                M.apply(cx[p], cy[p], cz[p], x, y, z);
+                cx[p] = x; cy[p] = y; cz[p] = z;
+            }
+            continue;
+        }
+        float f[P];
+        if (op == OP_METABALLS) {
+            const int nb = (int)hdr.z;
+            float lx[P], ly[P], lz[P];
+#pragma unroll
+            for (int p = 0; p < P; ++p) { M.apply(cx[p], cy[p], cz[p], lx[p], ly[p], lz[p]); f[p] = 0.0f; }
+            for (int b = 0; b < nb; ++b) {
+                const W4 q = prog.load4(pc), q2 = prog.load4(pc + 4);
+                const float bx = as_float(q.x), by = as_float(q.y), bz = as_float(q.z);
+                const float strength = as_float(q.w), subtract = as_float(q2.x);
+                pc += 8;
+#pragma unroll
+                for (int p = 0; p < P; ++p) {
+                    const float fx = lx[p] - bx, fx2 = fx * fx;
+                    const float fy = ly[p] - by, fy2 = fy * fy;
+                    const float fz = lz[p] - bz, fz2 = fz * fz;
+                    const float h = 0.000001f + fx2 + fy2 + fz2;
+                    const float hinv = 1.0f / h;
+                    const float val = strength * hinv - subtract;
+                    f[p] += val / 100.0f;
+                }
+            }
+        } else {
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                float x, y, z;
+                M.apply(cx[p], cy[p], cz[p], x, y, z);
+                if (op == OP_ELLIPSOID) f[p] = prim_ellipsoid(x, y, z);
+                else if (op == OP_CYLINDER) f[p] = prim_cylinder(x, y, z);
+                else if (op == OP_CONE) f[p] = prim_cone(x, y, z);
+                else if (op == OP_CUBE) f[p] = prim_cube(x, y, z);
+                else f[p] = prim_cube_sdf(sdf, x, y, z);
+            }
+        }
+        if (sp >= 2) {
+#pragma unroll
+            for (int p = 0; p < P; ++p) spill[sp - 2][p] = t1[p];
+        }
+#pragma unroll
+        for (int p = 0; p < P; ++p) { t1[p] = t0[p]; t0[p] = f[p]; }
+        ++sp;
+    }
+#pragma unroll
+    for (int p = 0; p < P; ++p) out[p] = t0[p];
+}
+
 // ---- gradient mode: f and grad f in one pass (identical to the reference's O(depth^2) recursion) ----
 template <class Prog>
 ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, float cx, float cy, float cz, float& f_out, float& g0_out,

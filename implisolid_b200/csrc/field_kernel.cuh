@@ -276,10 +276,17 @@ struct TileLive {             // liveness mask of the tile being evaluated (unif
     }
 };
 
+// SPEC: before evaluating a tile the block turns its liveness mask into the list of instructions the tile really runs
+// (spec_entry, one instruction per thread, order kept by ballot ranks) in shared memory; eval_values_list then has no
+// liveness tests, no dead-node jumps and no operand bookkeeping left.
 template <bool SPEC>
 __global__ void __launch_bounds__(kTileThreads) k_eval_tiles(GridDesc g, SdfGridView sdf, const unsigned* __restrict__ list,
                                                             const unsigned* __restrict__ list_count, const uint32_t* __restrict__ masks,
-                                                            int mask_words, float* __restrict__ field, uint32_t* __restrict__ signs) {
+                                                            int mask_words, const uint4* __restrict__ itab, int n_instr,
+                                                            float* __restrict__ field, uint32_t* __restrict__ signs) {
+    __shared__ uint32_t s_list[SPEC ? kMaxListEntries : 1];
+    __shared__ int s_warp_count[kTileThreads / 32];
+    __shared__ int s_n_list;
     const unsigned n = list_count[0];
     unsigned* next_item = const_cast<unsigned*>(list_count) + 1;      // dynamic queue: specialised tiles differ a lot in cost
     const int q = threadIdx.x & 1, row = threadIdx.x >> 1;
@@ -291,6 +298,29 @@ __global__ void __launch_bounds__(kTileThreads) k_eval_tiles(GridDesc g, SdfGrid
         __syncthreads();
         const unsigned item = s_item;
         if (item >= n) break;
+        if (SPEC) {
+            const TileLive live(masks + (size_t)item * mask_words, mask_words);
+            const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+            int base = 0;
+            for (int i0 = 0; i0 < n_instr; i0 += kTileThreads) {       // uniform trip count
+                const int i = i0 + (int)threadIdx.x;
+                uint32_t e = 0u;
+                if (i < n_instr) {
+                    const uint4 it = __ldg(itab + i);
+                    e = spec_entry(W4{it.x, it.y, it.z, it.w}, live);
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, e != 0u);
+                if (lane == 0) s_warp_count[warp] = __popc(m);
+                __syncthreads();
+                int before = base;
+                for (int w = 0; w < warp; ++w) before += s_warp_count[w];
+                if (e) s_list[before + __popc(m & ((1u << lane) - 1u))] = e;
+                for (int w = 0; w < kTileThreads / 32; ++w) base += s_warp_count[w];
+                __syncthreads();
+            }
+            if (threadIdx.x == 0) s_n_list = base;
+            __syncthreads();
+        }
         const int t = (int)list[item];
         const int tx = t % g.tx;
         const int r = t / g.tx;
@@ -314,7 +344,7 @@ __global__ void __launch_bounds__(kTileThreads) k_eval_tiles(GridDesc g, SdfGrid
                     cy[p] = yy;
                     cz[p] = zz;
                 }
-                if (SPEC) eval_values<4>(ConstProgram(), sdf, TileLive(masks + (size_t)item * mask_words, mask_words), cx, cy, cz, f);
+                if (SPEC) eval_values_list<4>(ConstProgram(), sdf, s_list, s_n_list, cx, cy, cz, f);
                 else eval_values<4>(ConstProgram(), sdf, AllLive(), cx, cy, cz, f);
                 nib = 0;
 #pragma unroll

@@ -266,24 +266,27 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     g.d_signs.reserve(sign_bytes);
     g.d_tile_list.reserve((size_t)ntiles * sizeof(unsigned) + 64);
     // bounds program and tree topology share one upload
-    const size_t bounds_words = prog.bounds.size(), topo_words = prog.topo.size();
-    g.d_bounds.reserve((bounds_words + topo_words) * sizeof(uint32_t));
+    const size_t itab_words = prog.itab.size(), bounds_words = prog.bounds.size(), topo_words = prog.topo.size();
+    g.d_bounds.reserve((itab_words + bounds_words + topo_words) * sizeof(uint32_t));
     SpecDesc spec{};
     spec.enabled = (s.specialize && prog.can_specialize && prog.num_nodes > 1) ? 1 : 0;
     spec.num_nodes = prog.num_nodes;
     spec.num_ops = (prog.num_nodes - 1) / 2;
     spec.mask_words = (prog.num_nodes + 31) / 32;
-    spec.topo = g.d_bounds.as<uint32_t>() + bounds_words;
+    const uint4* d_itab = g.d_bounds.as<uint4>();                       // [itab | bounds program | topology]
+    const uint32_t* d_bounds_prog = g.d_bounds.as<uint32_t>() + itab_words;
+    spec.topo = d_bounds_prog + bounds_words;
     if (spec.enabled) g.d_tile_masks.reserve((size_t)ntiles * spec.mask_words * sizeof(uint32_t));
     spec.masks = g.d_tile_masks.as<uint32_t>();
     unsigned* tile_count = g.d_totals.as<unsigned>() + 8;
     ISD_CUDA(cudaEventRecord(g.ev[0], g.stream));
     {   // K1: bounds -> work list -> tiles
-        g.h_program.reserve((bounds_words + topo_words) * sizeof(uint32_t));
-        uint32_t* staged = g.h_program.as<uint32_t>();      // pinned staging: the copy must not read a pageable vector that the
-        memcpy(staged, prog.bounds.data(), bounds_words * sizeof(uint32_t));      // caller may free before the stream gets there
-        memcpy(staged + bounds_words, prog.topo.data(), topo_words * sizeof(uint32_t));
-        ISD_CUDA(cudaMemcpyAsync(g.d_bounds.ptr, staged, (bounds_words + topo_words) * sizeof(uint32_t), cudaMemcpyHostToDevice, g.stream));
+        g.h_program.reserve((itab_words + bounds_words + topo_words) * sizeof(uint32_t));
+        uint32_t* staged = g.h_program.as<uint32_t>();      // pinned staging, one copy
+        memcpy(staged, prog.itab.data(), itab_words * sizeof(uint32_t));
+        memcpy(staged + itab_words, prog.bounds.data(), bounds_words * sizeof(uint32_t));
+        memcpy(staged + itab_words + bounds_words, prog.topo.data(), topo_words * sizeof(uint32_t));
+        ISD_CUDA(cudaMemcpyAsync(g.d_bounds.ptr, staged, (itab_words + bounds_words + topo_words) * sizeof(uint32_t), cudaMemcpyHostToDevice, g.stream));
         ISD_CUDA(cudaMemsetAsync(g.d_signs.ptr, 0xff, sign_bytes, g.stream));
         ISD_CUDA(cudaMemsetAsync(tile_count, 0, 2 * sizeof(unsigned), g.stream));      // work-list length, queue head
         static int resident[2] = {0, 0};      // blocks per SM of the two instantiations (persistent grid = what fits at once)
@@ -294,18 +297,19 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         const int want = g.sm_count * resident[spec.enabled ? 1 : 0];
         const int blocks = ntiles < want ? ntiles : want;
         if (spec.enabled) {
-            k_tile_bounds<true><<<(ntiles + 127) / 128, 128, 0, g.stream>>>(gd, g.d_bounds.as<uint32_t>(), s.prune, spec, g.d_signs.as<uint32_t>(),
+            k_tile_bounds<true><<<(ntiles + 127) / 128, 128, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_signs.as<uint32_t>(),
                                                                            g.d_tile_list.as<unsigned>(), tile_count);
             ISD_LAUNCH_CHECK();
             k_eval_tiles<true><<<blocks, kTileThreads, 0, g.stream>>>(gd, g.sdf, g.d_tile_list.as<unsigned>(), tile_count, spec.masks,
-                                                                     spec.mask_words, g.d_field.as<float>(), g.d_signs.as<uint32_t>());
+                                                                     spec.mask_words, d_itab, (int)(itab_words / 4), g.d_field.as<float>(),
+                                                                     g.d_signs.as<uint32_t>());
             ISD_LAUNCH_CHECK();
         } else {
-            k_tile_bounds<false><<<(ntiles + 127) / 128, 128, 0, g.stream>>>(gd, g.d_bounds.as<uint32_t>(), s.prune, spec, g.d_signs.as<uint32_t>(),
+            k_tile_bounds<false><<<(ntiles + 127) / 128, 128, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_signs.as<uint32_t>(),
                                                                             g.d_tile_list.as<unsigned>(), tile_count);
             ISD_LAUNCH_CHECK();
             k_eval_tiles<false><<<blocks, kTileThreads, 0, g.stream>>>(gd, g.sdf, g.d_tile_list.as<unsigned>(), tile_count, nullptr, 0,
-                                                                      g.d_field.as<float>(), g.d_signs.as<uint32_t>());
+                                                                      nullptr, 0, g.d_field.as<float>(), g.d_signs.as<uint32_t>());
             ISD_LAUNCH_CHECK();
         }
     }

@@ -61,6 +61,17 @@ constexpr int kMaxValueStack = 64;     // device limits (csg_eval.cuh)
 constexpr int kMaxFrameStack = 16;
 constexpr int kMaxProgramWords = 32768;   // 128 KB of global memory (a __device__ array, field_kernel.cuh)
 constexpr int kInstrWords = 16;           // header (4 words) + 3x4 matrix
+constexpr int kMaxListEntries = 1024;     // tile specialisation: longest per-tile instruction list kept in shared memory
+
+// Instruction table entry (one uint4 per program instruction, END excluded) and per-tile list entry, tile specialisation:
+//   itab.x = pc / 4 | IT_* flags, itab.y = id of the instruction's node, itab.z / itab.w = ids of a CSG node's children a / b
+//   list entry = pc / 4 | LE_* flags: what the instruction does in THIS tile (see spec_entry, csg_eval.cuh)
+enum : uint32_t {
+    IT_PC_MASK = 0xffffu,
+    IT_CLOSING = 1u << 16, IT_RESTORE = 1u << 17, IT_SWAPPED = 1u << 18, IT_OP_SHIFT = 19,      // op - OP_UNION in 2 bits
+    LE_CLOSING = 1u << 16, LE_RESTORE = 1u << 17, LE_SWAPPED = 1u << 18, LE_OP_SHIFT = 19,
+    LE_COMBINE = 1u << 21, LE_NEGATE = 1u << 22, LE_VALID = 1u << 31,
+};
 constexpr int kMaxSpecNodes = 2048;       // tile specialisation: per-tile liveness mask of at most this many bits
 constexpr int kMaxPendingDepth = 64;      // liveness pass: pending-sibling stack held in one 64-bit register
 
@@ -144,6 +155,9 @@ public:
         std::vector<uint32_t> bounds;
         // Tree topology for the liveness pass: bit i = node with id i (reverse post-order) is a CSG node.
         std::vector<uint32_t> topo;
+        // Instruction table (4 words per instruction, program order): lets a thread block decide in parallel which
+        // instructions a tile executes.
+        std::vector<uint32_t> itab;
         bool can_specialize = false;         // nodes <= kMaxSpecNodes and pending depth <= kMaxPendingDepth
         int value_depth = 0, frame_depth = 0, num_nodes = 0;
         bool uses_sdf_grid = false;
@@ -204,7 +218,8 @@ private:
             if (p.topo[(size_t)i >> 5] >> (i & 31) & 1u) depth += 2;
             if (depth > max_depth) max_depth = depth;
         }
-        p.can_specialize = total <= kMaxSpecNodes && max_depth <= kMaxPendingDepth && total < (1 << (32 - OP_ID_SHIFT));
+        p.can_specialize = total <= kMaxSpecNodes && max_depth <= kMaxPendingDepth && total < (1 << (32 - OP_ID_SHIFT)) &&
+                           p.itab.size() / 4 <= (size_t)kMaxListEntries && p.words.size() / 4 <= (size_t)IT_PC_MASK;
     }
 
     static void read_matrix12(const JsonDoc& d, int node, bool ignore_root_matrix, float m[12]) {
@@ -326,6 +341,9 @@ private:
         p.words.push_back(0u);
         return p.words.size() - 3;
     }
+    static void put_itab(Program& p, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+        p.itab.push_back(x); p.itab.push_back(y); p.itab.push_back(z); p.itab.push_back(w);
+    }
     static void put_matrix(Program& p, const float m[12]) {
         for (int i = 0; i < 12; ++i) { uint32_t w; memcpy(&w, &m[i], 4); p.words.push_back(w); }
     }
@@ -363,6 +381,7 @@ private:
     void emit_node(const ShapeNode& n, bool preserve, Program& p) {
         p.num_nodes++;
         if (!n.is_csg()) {
+            put_itab(p, (uint32_t)(p.words.size() / 4), id_of(n), 0u, 0u);
             const size_t skip_at = put_header(p, (uint32_t)n.op | (id_of(n) << OP_ID_SHIFT), (uint32_t)(n.params.size() / 5));
             put_matrix(p, n.minv);
             p.flops_per_point += 18;
@@ -388,6 +407,7 @@ private:
             return;
         }
         if (preserve && ++fs_ > p.frame_depth) p.frame_depth = fs_;
+        put_itab(p, (uint32_t)(p.words.size() / 4), id_of(n), 0u, 0u);
         const size_t skip_at = put_header(p, (uint32_t)OP_XFORM | (preserve ? (uint32_t)OP_FLAG_SAVE : 0u) | (id_of(n) << OP_ID_SHIFT), 0u);
         put_matrix(p, n.minv);
         p.flops_per_point += 18 + 1;
@@ -397,6 +417,8 @@ private:
         const ShapeNode& second = b_first ? *n.a : *n.b;
         emit_node(first, /*preserve=*/first.is_csg(), p);
         emit_node(second, /*preserve=*/false, p);
+        put_itab(p, (uint32_t)(p.words.size() / 4) | IT_CLOSING | (preserve ? IT_RESTORE : 0u) | (b_first ? IT_SWAPPED : 0u) |
+                        (((uint32_t)n.op - (uint32_t)OP_UNION) << IT_OP_SHIFT), id_of(n), id_of(*n.a), id_of(*n.b));
         put_header(p, (uint32_t)n.op | (b_first ? (uint32_t)OP_FLAG_SWAPPED : 0u) | (preserve ? (uint32_t)OP_FLAG_RESTORE : 0u), 0u);
         put_matrix(p, n.minv);
         vs_ -= 1;   // pops two, pushes one

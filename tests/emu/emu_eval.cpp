@@ -119,6 +119,17 @@ extern "C" int emu_eval_masked(const char* shape_json, const float* pts, int n, 
         float x[1] = {pts[i * 3]}, y[1] = {pts[i * 3 + 1]}, z[1] = {pts[i * 3 + 2]}, out[1];
         eval_values<1>(prog, sdf, MaskLive{mask}, x, y, z, out);
         f_masked[i] = out[0];
+        // the same through the per-tile instruction list (what k_eval_tiles runs); any disagreement poisons the result
+        {
+            std::vector<uint32_t> list;
+            for (size_t k = 0; k + 3 < p.itab.size(); k += 4) {
+                const uint32_t e = spec_entry(W4{p.itab[k], p.itab[k + 1], p.itab[k + 2], p.itab[k + 3]}, MaskLive{mask});
+                if (e) list.push_back(e);
+            }
+            float x2[1] = {pts[i * 3]}, y2[1] = {pts[i * 3 + 1]}, z2[1] = {pts[i * 3 + 2]}, out2[1];
+            eval_values_list<1>(prog, sdf, list.data(), (int)list.size(), x2, y2, z2, out2);
+            if (memcmp(out2, out, 4) != 0) f_masked[i] = __builtin_nanf("");
+        }
         int cnt = 0;
         for (int k = 0; k < p.num_nodes; k++) cnt += (mask[k >> 5] >> (k & 31)) & 1;
         live_nodes[i] = cnt;
