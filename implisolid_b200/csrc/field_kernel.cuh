@@ -76,16 +76,49 @@ __device__ __forceinline__ bool surely_greater(float x, float y) {      // x > y
     return x - y > 1e-4f * (1.0f + fabsf(x) + fabsf(y));
 }
 
-template <bool DECIDE>
+//
+// With MASKED, `in_mask` holds liveness bits proven for an enclosing box (the supertile): dead primitives are not bounded
+// at all and push nothing, `present` tracks which operands exist, and a CSG node with one operand passes it through and
+// records the other as killed — so the masks derived from these decisions are never looser than the enclosing one.
+struct NoMask {
+    __device__ __forceinline__ bool operator()(uint32_t) const { return true; }
+};
+struct WordMask {
+    const uint32_t* m;
+    __device__ __forceinline__ bool operator()(uint32_t id) const { return (__ldg(m + (id >> 5)) >> (id & 31)) & 1u; }
+};
+
+template <bool DECIDE, bool MASKED, class InMask>
 __device__ inline Ival program_bounds(const uint32_t* __restrict__ bp, float bx, float by, float bz, float hx, float hy, float hz,
-                                      uint32_t* __restrict__ decisions) {
+                                      uint32_t* __restrict__ decisions, const InMask& in_mask) {
     Ival st[kMaxValueStack];
     int sp = 0, pc = 0, opj = 0;
+    unsigned long long present = 0ull;
     for (;;) {
-        const uint32_t op = __ldg(bp + pc) & OP_MASK;
+        const uint32_t word = __ldg(bp + pc);
+        const uint32_t op = word & OP_MASK;
         if (op == OP_END) break;
         if (op >= OP_UNION) {
             ++pc;
+            if (MASKED) {
+                const bool b_there = (present & 1ull) != 0, a_there = (present & 2ull) != 0;
+                present = ((present >> 2) << 1) | ((a_there || b_there) ? 1ull : 0ull);
+                if (!(a_there && b_there)) {
+                    uint32_t d = KEEP_BOTH;
+                    if (b_there) {
+                        d = KILL_A;
+                        if (op == OP_SUBTRACT) { const Ival b = st[sp - 1]; st[sp - 1] = Ival{-b.hi, -b.lo}; }
+                    } else if (a_there) {
+                        d = KILL_B;
+                    }
+                    if (DECIDE) {
+                        if ((opj & 15) == 0) decisions[opj >> 4] = 0u;
+                        decisions[opj >> 4] |= d << ((opj & 15) * 2);
+                        ++opj;
+                    }
+                    continue;
+                }
+            }
             const Ival b = st[--sp], a = st[sp - 1];
             Ival r;
             uint32_t d = KEEP_BOTH;
@@ -109,6 +142,13 @@ __device__ inline Ival program_bounds(const uint32_t* __restrict__ bp, float bx,
             st[sp - 1] = r;
             continue;
         }
+        if (MASKED && !in_mask(word >> OP_ID_SHIFT)) {      // dead primitive: no bound needed, nothing pushed
+            pc += 13;
+            if (op == OP_METABALLS) pc += 1 + 5 * (int)__ldg(bp + pc);
+            present <<= 1;
+            continue;
+        }
+        present = (present << 1) | 1ull;
         float m[12];
 #pragma unroll
         for (int i = 0; i < 12; ++i) m[i] = __uint_as_float(__ldg(bp + pc + 1 + i));
@@ -161,7 +201,7 @@ __device__ inline Ival program_bounds(const uint32_t* __restrict__ bp, float bx,
         }
         st[sp++] = r;
     }
-    Ival out = st[0];
+    Ival out = (MASKED && !(present & 1ull)) ? Ival{-1.0f, -1.0f} : st[0];      // (a live root always has a live operand)
     const float slack = 1e-4f * (1.0f + fabsf(out.lo) + fabsf(out.hi));
     out.lo -= slack; out.hi += slack;
     return out;
@@ -177,84 +217,136 @@ struct SpecDesc {
     int num_nodes, num_ops, mask_words;
     const uint32_t* topo;         // bit i: node id i is a CSG node
     uint32_t* masks;              // [work-list index][mask_words]
+    uint32_t* super_masks;        // [supertile-list index][mask_words]
 };
 constexpr int kDecisionWords = kMaxSpecNodes / 2 / 16 + 1;
 
-// One thread per tile.  list_count[0] receives the number of tiles appended to `list`.
+// Liveness masks from the decisions of one program_bounds<DECIDE> call: walk the nodes in reverse post-order (= id order),
+// a stack of pending liveness flags in one register (depth checked on the host).
+__device__ inline void write_live_mask(const SpecDesc& spec, const uint32_t* decisions, uint32_t* __restrict__ out) {
+    unsigned long long pending = 1ull;       // the root is live; top of the stack in bit 0
+    int opj = spec.num_ops - 1;
+    uint32_t word = 0u, topo_word = 0u;
+    for (int i = 0; i < spec.num_nodes; ++i) {
+        if ((i & 31) == 0) topo_word = __ldg(spec.topo + (i >> 5));
+        const unsigned long long alive = pending & 1ull;
+        pending >>= 1;
+        word |= (uint32_t)alive << (i & 31);
+        if ((topo_word >> (i & 31)) & 1u) {
+            const uint32_t d = (decisions[opj >> 4] >> ((opj & 15) * 2)) & 3u;
+            --opj;
+            const unsigned long long la = (alive && d != KILL_A) ? 1ull : 0ull, lb = (alive && d != KILL_B) ? 1ull : 0ull;
+            pending = (pending << 2) | (la << 1) | lb;      // b's subtree comes first in reverse post-order
+        }
+        if ((i & 31) == 31 || i + 1 == spec.num_nodes) { out[i >> 5] = word; word = 0u; }
+    }
+}
+
+// Box of node index ranges [x0,x1] x [y0,y1] x [z0,z1] grown by one cell on every side (+ a hair): class and, with SPEC,
+// the decisions behind it.
+template <bool SPEC, bool MASKED, class InMask>
+__device__ inline uint8_t classify_box(const GridDesc& g, const uint32_t* __restrict__ bounds_prog, int x0, int y0, int z0, int x1, int y1, int z1,
+                                       uint32_t* decisions, const InMask& in_mask) {
+    const bool touches_seal = x0 <= 1 || y0 <= 1 || z0 <= 1 || x1 + 1 >= g.S - 2 || y1 + 1 >= g.S - 2 || z1 + 1 >= g.S - 2;   // the grown box must stay clear of the seal too
+    const float ax = node_coord(x0 - 1, g.wx, g.xmin, g.two_wx), bx = node_coord(x1 + 1, g.wx, g.xmin, g.two_wx);
+    const float ay = node_coord(y0 - 1, g.wy, g.ymin, g.two_wy), by = node_coord(y1 + 1, g.wy, g.ymin, g.two_wy);
+    const float az = node_coord(z0 - 1, g.wz, g.zmin, g.two_wz), bz = node_coord(z1 + 1, g.wz, g.zmin, g.two_wz);
+    const Ival b = program_bounds<SPEC, MASKED>(bounds_prog, 0.5f * (ax + bx), 0.5f * (ay + by), 0.5f * (az + bz), 0.5f * (bx - ax) * 1.001f,
+                                                0.5f * (by - ay) * 1.001f, 0.5f * (bz - az) * 1.001f, decisions, in_mask);
+    if (b.hi < 0.0f) return TILE_OUTSIDE;
+    if (b.lo > 0.0f && !touches_seal) return TILE_INSIDE;
+    return TILE_MIXED;
+}
+
+// Level 1: one thread per supertile (4x4x4 tiles = 32^3 nodes).  Outside supertiles need nothing (the sign array is pre-set
+// to ones); inside and mixed ones go on the supertile list (inside flagged in bit 31), mixed ones with their liveness mask.
+// counters[2] receives the list length.
+constexpr unsigned kSuperInside = 0x80000000u;
 template <bool SPEC>
-__global__ void __launch_bounds__(128) k_tile_bounds(GridDesc g, const uint32_t* __restrict__ bounds_prog, int prune, SpecDesc spec,
-                                                     uint32_t* __restrict__ signs, unsigned* __restrict__ list, unsigned* __restrict__ list_count) {
+__global__ void __launch_bounds__(128) k_super_bounds(GridDesc g, const uint32_t* __restrict__ bounds_prog, int prune, SpecDesc spec,
+                                                      unsigned* __restrict__ super_list, unsigned* __restrict__ counters) {
+    const int stx = (g.tx + 3) / 4, sty = (g.ty + 3) / 4, stz = (g.tz + 3) / 4;
     const int t = blockIdx.x * 128 + threadIdx.x;
-    const int ntiles = g.tx * g.ty * g.tz;
+    const bool valid = t < stx * sty * stz;
     uint8_t cls = TILE_MIXED;
     uint32_t decisions[SPEC ? kDecisionWords : 1];
-    int tx = 0, ty = 0, tzl = 0;
-    const bool valid = t < ntiles;
-    if (valid) {
-        tx = t % g.tx;
-        const int r = t / g.tx;
-        ty = r % g.ty;
-        tzl = r / g.ty;
-        if (prune) {
-            // node index ranges of the tile, clipped to the grid
-            const int x0 = tx * 8, y0 = ty * 8, z0 = g.z0 + tzl * 8;
-            const int x1 = min(x0 + 7, g.S - 1), y1 = min(y0 + 7, g.S - 1), z1 = min(z0 + 7, g.z0 + g.nz - 1);
-            const bool touches_seal = x0 <= 1 || y0 <= 1 || z0 <= 1 || x1 + 1 >= g.S - 2 || y1 + 1 >= g.S - 2 || z1 + 1 >= g.S - 2;   // the grown box must stay clear of the seal too
-            // box of the tile grown by one cell on every side (+ a hair), in grid coordinates
-            const float ax = node_coord(x0 - 1, g.wx, g.xmin, g.two_wx), bx = node_coord(x1 + 1, g.wx, g.xmin, g.two_wx);
-            const float ay = node_coord(y0 - 1, g.wy, g.ymin, g.two_wy), by = node_coord(y1 + 1, g.wy, g.ymin, g.two_wy);
-            const float az = node_coord(z0 - 1, g.wz, g.zmin, g.two_wz), bz = node_coord(z1 + 1, g.wz, g.zmin, g.two_wz);
-            const Ival b = program_bounds<SPEC>(bounds_prog, 0.5f * (ax + bx), 0.5f * (ay + by), 0.5f * (az + bz), 0.5f * (bx - ax) * 1.001f,
-                                                0.5f * (by - ay) * 1.001f, 0.5f * (bz - az) * 1.001f, decisions);
-            if (b.hi < 0.0f) cls = TILE_OUTSIDE;
-            else if (b.lo > 0.0f && !touches_seal) cls = TILE_INSIDE;
-        }
+    if (valid && prune) {
+        const int sx = t % stx, r = t / stx, sy = r % sty, sz = r / sty;
+        const int x0 = sx * 32, y0 = sy * 32, z0 = g.z0 + sz * 32;
+        const int x1 = min(x0 + 31, g.S - 1), y1 = min(y0 + 31, g.S - 1), z1 = min(z0 + 31, g.z0 + g.nz - 1);
+        cls = classify_box<SPEC, false>(g, bounds_prog, x0, y0, z0, x1, y1, z1, decisions, NoMask());
     }
-    // inside tiles: clear their sign bytes (the array is pre-set to ones = outside)
-    if (valid && cls == TILE_INSIDE) {
-        uint8_t* sb = reinterpret_cast<uint8_t*>(signs);
-        for (int dz = 0; dz < 8; ++dz) {
-            const int zl = tzl * 8 + dz;
-            if (zl >= g.nz) break;
-            for (int dy = 0; dy < 8; ++dy) {
-                const int y = ty * 8 + dy;
-                if (y >= g.S) break;
-                sb[((long long)zl * g.S + y) * (g.SW * 4) + tx] = 0;
-            }
-        }
-    }
-    // mixed tiles -> work list (warp-aggregated append)
-    const bool mixed = valid && cls == TILE_MIXED;
-    const unsigned m = __ballot_sync(0xffffffffu, mixed);
+    const bool listed = valid && cls != TILE_OUTSIDE;
+    const unsigned m = __ballot_sync(0xffffffffu, listed);
     if (m) {
         const int lane = threadIdx.x & 31;
         unsigned base = 0;
-        if (lane == 0) base = atomicAdd(list_count, (unsigned)__popc(m));
+        if (lane == 0) base = atomicAdd(counters + 2, (unsigned)__popc(m));
         base = __shfl_sync(0xffffffffu, base, 0);
-        if (mixed) {
+        if (listed) {
             const unsigned at = base + __popc(m & ((1u << lane) - 1u));
-            list[at] = (unsigned)t;
-            if (SPEC) {
-                uint32_t* out = spec.masks + (size_t)at * spec.mask_words;
-                if (!prune) {
-                    for (int w = 0; w < spec.mask_words; ++w) out[w] = 0xffffffffu;
-                } else {
-                    unsigned long long pending = 1ull;       // stack of liveness flags, top in bit 0 (depth checked on the host)
-                    int opj = spec.num_ops - 1;
-                    uint32_t word = 0u, topo_word = 0u;
-                    for (int i = 0; i < spec.num_nodes; ++i) {
-                        if ((i & 31) == 0) topo_word = __ldg(spec.topo + (i >> 5));
-                        const unsigned long long alive = pending & 1ull;
-                        pending >>= 1;
-                        word |= (uint32_t)alive << (i & 31);
-                        if ((topo_word >> (i & 31)) & 1u) {
-                            const uint32_t d = (decisions[opj >> 4] >> ((opj & 15) * 2)) & 3u;
-                            --opj;
-                            const unsigned long long la = (alive && d != KILL_A) ? 1ull : 0ull, lb = (alive && d != KILL_B) ? 1ull : 0ull;
-                            pending = (pending << 2) | (la << 1) | lb;      // b's subtree comes first in reverse post-order
-                        }
-                        if ((i & 31) == 31 || i + 1 == spec.num_nodes) { out[i >> 5] = word; word = 0u; }
-                    }
+            super_list[at] = (unsigned)t | (cls == TILE_INSIDE ? kSuperInside : 0u);
+            if (SPEC && cls == TILE_MIXED) {
+                uint32_t* out = spec.super_masks + (size_t)at * spec.mask_words;
+                if (prune) write_live_mask(spec, decisions, out);
+                else for (int w = 0; w < spec.mask_words; ++w) out[w] = 0xffffffffu;
+            }
+        }
+    }
+}
+
+// Level 2: one 64-thread block per listed supertile (grid-stride), one thread per tile.  Tiles of an inside supertile clear
+// their sign bytes; tiles of a mixed one are bounded again over their own box — only the primitives still live in the
+// supertile are looked at — and the mixed ones go on the work list with their own liveness mask.
+// counters[0] receives the work-list length.
+template <bool SPEC>
+__global__ void __launch_bounds__(64) k_tile_bounds(GridDesc g, const uint32_t* __restrict__ bounds_prog, int prune, SpecDesc spec,
+                                                    const unsigned* __restrict__ super_list, uint32_t* __restrict__ signs,
+                                                    unsigned* __restrict__ list, unsigned* __restrict__ counters) {
+    const unsigned n_super = counters[2];
+    const int stx = (g.tx + 3) / 4, sty = (g.ty + 3) / 4;
+    uint32_t decisions[SPEC ? kDecisionWords : 1];
+    for (unsigned item = blockIdx.x; item < n_super; item += gridDim.x) {
+        const unsigned entry = super_list[item];
+        const int st = (int)(entry & ~kSuperInside);
+        const int sx = st % stx, r = st / stx, sy = r % sty, sz = r / sty;
+        const int tx = sx * 4 + (threadIdx.x & 3), ty = sy * 4 + ((threadIdx.x >> 2) & 3), tzl = sz * 4 + (threadIdx.x >> 4);
+        const bool valid = tx < g.tx && ty < g.ty && tzl < g.tz;
+        uint8_t cls = (entry & kSuperInside) ? TILE_INSIDE : TILE_MIXED;
+        if (valid && cls == TILE_MIXED && prune) {
+            const int x0 = tx * 8, y0 = ty * 8, z0 = g.z0 + tzl * 8;
+            const int x1 = min(x0 + 7, g.S - 1), y1 = min(y0 + 7, g.S - 1), z1 = min(z0 + 7, g.z0 + g.nz - 1);
+            if (SPEC) cls = classify_box<SPEC, true>(g, bounds_prog, x0, y0, z0, x1, y1, z1, decisions, WordMask{spec.super_masks + (size_t)item * spec.mask_words});
+            else cls = classify_box<SPEC, false>(g, bounds_prog, x0, y0, z0, x1, y1, z1, decisions, NoMask());
+        }
+        // inside tiles: clear their sign bytes (the array is pre-set to ones = outside)
+        if (valid && cls == TILE_INSIDE) {
+            uint8_t* sb = reinterpret_cast<uint8_t*>(signs);
+            for (int dz = 0; dz < 8; ++dz) {
+                const int zl = tzl * 8 + dz;
+                if (zl >= g.nz) break;
+                for (int dy = 0; dy < 8; ++dy) {
+                    const int y = ty * 8 + dy;
+                    if (y >= g.S) break;
+                    sb[((long long)zl * g.S + y) * (g.SW * 4) + tx] = 0;
+                }
+            }
+        }
+        // mixed tiles -> work list (warp-aggregated append)
+        const bool mixed = valid && cls == TILE_MIXED;
+        const unsigned m = __ballot_sync(0xffffffffu, mixed);
+        if (m) {
+            const int lane = threadIdx.x & 31;
+            unsigned base = 0;
+            if (lane == 0) base = atomicAdd(counters, (unsigned)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (mixed) {
+                const unsigned at = base + __popc(m & ((1u << lane) - 1u));
+                list[at] = (unsigned)((tzl * g.ty + ty) * g.tx + tx);
+                if (SPEC) {
+                    uint32_t* out = spec.masks + (size_t)at * spec.mask_words;
+                    if (prune) write_live_mask(spec, decisions, out);
+                    else for (int w = 0; w < spec.mask_words; ++w) out[w] = 0xffffffffu;
                 }
             }
         }

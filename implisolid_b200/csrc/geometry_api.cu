@@ -97,7 +97,7 @@ struct Context {
     PinnedBuffer h_verts, h_faces;
 
     // field + marching cubes scratch
-    DeviceBuffer d_field, d_signs, d_tile_list, d_tile_masks, d_bounds, d_counts, d_lane_bits, d_offsets, d_cubes, d_partials, d_totals, d_cases;
+    DeviceBuffer d_field, d_signs, d_tile_list, d_tile_masks, d_super_list, d_super_masks, d_bounds, d_counts, d_lane_bits, d_offsets, d_cubes, d_partials, d_totals, d_cases;
     PinnedBuffer h_small;         // totals and other small read-backs
     PinnedBuffer h_program;       // staging of the bounds program + topology
     GridDesc grid{};
@@ -276,8 +276,14 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     const uint4* d_itab = g.d_bounds.as<uint4>();                       // [itab | bounds program | topology]
     const uint32_t* d_bounds_prog = g.d_bounds.as<uint32_t>() + itab_words;
     spec.topo = d_bounds_prog + bounds_words;
-    if (spec.enabled) g.d_tile_masks.reserve((size_t)ntiles * spec.mask_words * sizeof(uint32_t));
+    const int nsuper = ((gd.tx + 3) / 4) * ((gd.ty + 3) / 4) * ((gd.tz + 3) / 4);      // supertiles: 4x4x4 tiles
+    g.d_super_list.reserve((size_t)nsuper * sizeof(unsigned) + 64);
+    if (spec.enabled) {
+        g.d_tile_masks.reserve((size_t)ntiles * spec.mask_words * sizeof(uint32_t));
+        g.d_super_masks.reserve((size_t)nsuper * spec.mask_words * sizeof(uint32_t));
+    }
     spec.masks = g.d_tile_masks.as<uint32_t>();
+    spec.super_masks = g.d_super_masks.as<uint32_t>();
     unsigned* tile_count = g.d_totals.as<unsigned>() + 8;
     ISD_CUDA(cudaEventRecord(g.ev[0], g.stream));
     {   // K1: bounds -> work list -> tiles
@@ -288,25 +294,30 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         memcpy(staged + itab_words + bounds_words, prog.topo.data(), topo_words * sizeof(uint32_t));
         ISD_CUDA(cudaMemcpyAsync(g.d_bounds.ptr, staged, (itab_words + bounds_words + topo_words) * sizeof(uint32_t), cudaMemcpyHostToDevice, g.stream));
         ISD_CUDA(cudaMemsetAsync(g.d_signs.ptr, 0xff, sign_bytes, g.stream));
-        ISD_CUDA(cudaMemsetAsync(tile_count, 0, 2 * sizeof(unsigned), g.stream));      // work-list length, queue head
+        ISD_CUDA(cudaMemsetAsync(tile_count, 0, 4 * sizeof(unsigned), g.stream));      // work-list length, queue head, supertile-list length
         static int resident[2] = {0, 0};      // blocks per SM of the two instantiations (persistent grid = what fits at once)
         if (!resident[0]) {
             ISD_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident[0], k_eval_tiles<false>, kTileThreads, 0));
             ISD_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident[1], k_eval_tiles<true>, kTileThreads, 0));
         }
+        const int level2_blocks = nsuper < g.sm_count * 32 ? nsuper : g.sm_count * 32;
         const int want = g.sm_count * resident[spec.enabled ? 1 : 0];
         const int blocks = ntiles < want ? ntiles : want;
         if (spec.enabled) {
-            k_tile_bounds<true><<<(ntiles + 127) / 128, 128, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_signs.as<uint32_t>(),
-                                                                           g.d_tile_list.as<unsigned>(), tile_count);
+            k_super_bounds<true><<<(nsuper + 127) / 128, 128, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(), tile_count);
+            ISD_LAUNCH_CHECK();
+            k_tile_bounds<true><<<level2_blocks, 64, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(),
+                                                                   g.d_signs.as<uint32_t>(), g.d_tile_list.as<unsigned>(), tile_count);
             ISD_LAUNCH_CHECK();
             k_eval_tiles<true><<<blocks, kTileThreads, 0, g.stream>>>(gd, g.sdf, g.d_tile_list.as<unsigned>(), tile_count, spec.masks,
                                                                      spec.mask_words, d_itab, (int)(itab_words / 4), g.d_field.as<float>(),
                                                                      g.d_signs.as<uint32_t>());
             ISD_LAUNCH_CHECK();
         } else {
-            k_tile_bounds<false><<<(ntiles + 127) / 128, 128, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_signs.as<uint32_t>(),
-                                                                            g.d_tile_list.as<unsigned>(), tile_count);
+            k_super_bounds<false><<<(nsuper + 127) / 128, 128, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(), tile_count);
+            ISD_LAUNCH_CHECK();
+            k_tile_bounds<false><<<level2_blocks, 64, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(),
+                                                                    g.d_signs.as<uint32_t>(), g.d_tile_list.as<unsigned>(), tile_count);
             ISD_LAUNCH_CHECK();
             k_eval_tiles<false><<<blocks, kTileThreads, 0, g.stream>>>(gd, g.sdf, g.d_tile_list.as<unsigned>(), tile_count, nullptr, 0,
                                                                       nullptr, 0, g.d_field.as<float>(), g.d_signs.as<uint32_t>());

@@ -365,7 +365,7 @@ private:
         double comp[16];
         compose(n.minv, parent, comp);
         if (!n.is_csg()) {
-            p.bounds.push_back(n.op);
+            p.bounds.push_back((uint32_t)n.op | (id_of(n) << OP_ID_SHIFT));
             for (int i = 0; i < 12; ++i) { float f = (float)comp[i]; uint32_t w; memcpy(&w, &f, 4); p.bounds.push_back(w); }
             if (n.op == OP_METABALLS) {
                 p.bounds.push_back((uint32_t)(n.params.size() / 5));
@@ -375,7 +375,7 @@ private:
         }
         emit_bounds(*n.a, comp, p);
         emit_bounds(*n.b, comp, p);
-        p.bounds.push_back(n.op);
+        p.bounds.push_back((uint32_t)n.op | (id_of(n) << OP_ID_SHIFT));
     }
 
     void emit_node(const ShapeNode& n, bool preserve, Program& p) {
