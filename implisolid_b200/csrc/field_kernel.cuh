@@ -295,6 +295,16 @@ __global__ void __launch_bounds__(128) k_super_bounds(GridDesc g, const uint32_t
     }
 }
 
+// Where the work-list tiles are, for marching cubes (mc_kernels.cuh walks the work list, row of tiles by row of tiles):
+// tile_slot[tile] = work-list position; tile_any[tz * ty_count + ty] = 1 if some tile of that row of tiles is listed;
+// tile_bits = one bit per tile, TW words per row of tiles.
+struct TileHints {
+    unsigned* tile_slot;
+    uint8_t* tile_any;
+    uint32_t* tile_bits;
+    int TW;
+};
+
 // Level 2: one 64-thread block per listed supertile (grid-stride), one thread per tile.  Tiles of an inside supertile clear
 // their sign bytes; tiles of a mixed one are bounded again over their own box — only the primitives still live in the
 // supertile are looked at — and the mixed ones go on the work list with their own liveness mask.
@@ -302,7 +312,7 @@ __global__ void __launch_bounds__(128) k_super_bounds(GridDesc g, const uint32_t
 template <bool SPEC>
 __global__ void __launch_bounds__(64) k_tile_bounds(GridDesc g, const uint32_t* __restrict__ bounds_prog, int prune, SpecDesc spec,
                                                     const unsigned* __restrict__ super_list, uint32_t* __restrict__ signs,
-                                                    unsigned* __restrict__ list, unsigned* __restrict__ counters) {
+                                                    unsigned* __restrict__ list, unsigned* __restrict__ counters, TileHints hints) {
     const unsigned n_super = counters[2];
     const int stx = (g.tx + 3) / 4, sty = (g.ty + 3) / 4;
     uint32_t decisions[SPEC ? kDecisionWords : 1];
@@ -342,7 +352,11 @@ __global__ void __launch_bounds__(64) k_tile_bounds(GridDesc g, const uint32_t* 
             base = __shfl_sync(0xffffffffu, base, 0);
             if (mixed) {
                 const unsigned at = base + __popc(m & ((1u << lane) - 1u));
-                list[at] = (unsigned)((tzl * g.ty + ty) * g.tx + tx);
+                const int t = (tzl * g.ty + ty) * g.tx + tx;
+                list[at] = (unsigned)t;
+                hints.tile_slot[t] = at;
+                hints.tile_any[tzl * g.ty + ty] = 1;
+                atomicOr(hints.tile_bits + (long long)(tzl * g.ty + ty) * hints.TW + (tx >> 5), 1u << (tx & 31));
                 if (SPEC) {
                     uint32_t* out = spec.masks + (size_t)at * spec.mask_words;
                     if (prune) write_live_mask(spec, decisions, out);

@@ -97,7 +97,7 @@ struct Context {
     PinnedBuffer h_verts, h_faces;
 
     // field + marching cubes scratch
-    DeviceBuffer d_field, d_signs, d_tile_list, d_tile_masks, d_super_list, d_super_masks, d_bounds, d_counts, d_lane_bits, d_offsets, d_cubes, d_partials, d_totals, d_cases;
+    DeviceBuffer d_field, d_signs, d_tile_list, d_tile_masks, d_super_list, d_super_masks, d_bounds, d_row_tot, d_row_base, d_scan_state, d_tile_hints, d_seg_bits, d_seg_off, d_cubes, d_totals, d_cases;
     PinnedBuffer h_small;         // totals and other small read-backs
     PinnedBuffer h_program;       // staging of the bounds program + topology
     GridDesc grid{};
@@ -232,9 +232,8 @@ void setup_grid(const McSettings& s) {
     else { gd.z0 = zb - 1; gd.nz = (ze - zb) + 2; }
     gd.tx = gd.pitch / 8; gd.ty = (S + 7) / 8; gd.tz = (gd.nz + 7) / 8;
     m.NX = S - 3;
-    m.K = (S - 3) / 32 + 1;
-    m.n_chunks = (long long)(ze - m.scan_z0) * m.NX * m.K;
-    m.ghost_chunks = (long long)(zb - m.scan_z0) * m.NX * m.K;
+    m.n_rows = (long long)(ze - m.scan_z0) * m.NX;
+    m.ghost_rows = (long long)(zb - m.scan_z0) * m.NX;
     m.g = gd;
     g.S = S;
 }
@@ -245,13 +244,11 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     McDesc& m = g.mc;
     const size_t field_bytes = (size_t)gd.plane * gd.nz * sizeof(float);
     g.d_field.reserve(field_bytes);
-    const long long n_chunks = m.n_chunks;
-    const long long padded = (n_chunks + kScanTile - 1) / kScanTile * kScanTile;
-    g.d_counts.reserve(padded * sizeof(uint32_t));
-    g.d_lane_bits.reserve((size_t)n_chunks * 5 * sizeof(uint32_t));
-    g.d_offsets.reserve((n_chunks + 1) * sizeof(uint2));
-    const int scan_blocks = (int)(padded / kScanTile);
-    g.d_partials.reserve((size_t)scan_blocks * sizeof(Triple));
+    const long long n_rows = m.n_rows;
+    const int scan_blocks = (int)((n_rows + kRowScanThreads - 1) / kRowScanThreads);
+    g.d_row_tot.reserve((size_t)n_rows * sizeof(Triple));
+    g.d_row_base.reserve((size_t)n_rows * sizeof(Triple));
+    g.d_scan_state.reserve(((size_t)scan_blocks + 1) * 8 * sizeof(unsigned));
     g.d_totals.reserve(64);
     uint8_t* dbg_cases = nullptr;
     g.have_cases = false;
@@ -284,6 +281,13 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     }
     spec.masks = g.d_tile_masks.as<uint32_t>();
     spec.super_masks = g.d_super_masks.as<uint32_t>();
+    TileHints hints;
+    hints.TW = (gd.tx + 31) / 32;
+    const size_t hint_bits_bytes = (size_t)gd.ty * gd.tz * hints.TW * sizeof(uint32_t), hint_any_bytes = ((size_t)gd.ty * gd.tz + 3) & ~(size_t)3;
+    g.d_tile_hints.reserve(hint_bits_bytes + hint_any_bytes + (size_t)ntiles * sizeof(unsigned));
+    hints.tile_bits = g.d_tile_hints.as<uint32_t>();
+    hints.tile_any = g.d_tile_hints.as<uint8_t>() + hint_bits_bytes;
+    hints.tile_slot = reinterpret_cast<unsigned*>(g.d_tile_hints.as<uint8_t>() + hint_bits_bytes + hint_any_bytes);
     unsigned* tile_count = g.d_totals.as<unsigned>() + 8;
     ISD_CUDA(cudaEventRecord(g.ev[0], g.stream));
     {   // K1: bounds -> work list -> tiles
@@ -294,6 +298,8 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         memcpy(staged + itab_words + bounds_words, prog.topo.data(), topo_words * sizeof(uint32_t));
         ISD_CUDA(cudaMemcpyAsync(g.d_bounds.ptr, staged, (itab_words + bounds_words + topo_words) * sizeof(uint32_t), cudaMemcpyHostToDevice, g.stream));
         ISD_CUDA(cudaMemsetAsync(g.d_signs.ptr, 0xff, sign_bytes, g.stream));
+        ISD_CUDA(cudaMemsetAsync(g.d_tile_hints.ptr, 0, hint_bits_bytes + hint_any_bytes, g.stream));
+        ISD_CUDA(cudaMemsetAsync(g.d_scan_state.ptr, 0, ((size_t)scan_blocks + 1) * 8 * sizeof(unsigned), g.stream));
         ISD_CUDA(cudaMemsetAsync(tile_count, 0, 4 * sizeof(unsigned), g.stream));      // work-list length, queue head, supertile-list length
         static int resident[2] = {0, 0};      // blocks per SM of the two instantiations (persistent grid = what fits at once)
         if (!resident[0]) {
@@ -307,7 +313,7 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
             k_super_bounds<true><<<(nsuper + 127) / 128, 128, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(), tile_count);
             ISD_LAUNCH_CHECK();
             k_tile_bounds<true><<<level2_blocks, 64, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(),
-                                                                   g.d_signs.as<uint32_t>(), g.d_tile_list.as<unsigned>(), tile_count);
+                                                                   g.d_signs.as<uint32_t>(), g.d_tile_list.as<unsigned>(), tile_count, hints);
             ISD_LAUNCH_CHECK();
             k_eval_tiles<true><<<blocks, kTileThreads, 0, g.stream>>>(gd, g.sdf, g.d_tile_list.as<unsigned>(), tile_count, spec.masks,
                                                                      spec.mask_words, d_itab, (int)(itab_words / 4), g.d_field.as<float>(),
@@ -317,7 +323,7 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
             k_super_bounds<false><<<(nsuper + 127) / 128, 128, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(), tile_count);
             ISD_LAUNCH_CHECK();
             k_tile_bounds<false><<<level2_blocks, 64, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(),
-                                                                    g.d_signs.as<uint32_t>(), g.d_tile_list.as<unsigned>(), tile_count);
+                                                                    g.d_signs.as<uint32_t>(), g.d_tile_list.as<unsigned>(), tile_count, hints);
             ISD_LAUNCH_CHECK();
             k_eval_tiles<false><<<blocks, kTileThreads, 0, g.stream>>>(gd, g.sdf, g.d_tile_list.as<unsigned>(), tile_count, nullptr, 0,
                                                                       nullptr, 0, g.d_field.as<float>(), g.d_signs.as<uint32_t>());
@@ -325,33 +331,47 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         }
     }
     ISD_CUDA(cudaEventRecord(g.ev[1], g.stream));
-    {   // K2
-        k_mc_classify<<<(unsigned)((n_chunks + 255) / 256), 256, 0, g.stream>>>(m, g.d_signs.as<uint32_t>(), g.d_counts.as<uint32_t>(),
-                                                                                 g.d_lane_bits.as<uint32_t>(), dbg_cases);
-        ISD_LAUNCH_CHECK();
-    }
-    {   // K3, first half: block sums and their prefix
-        k_scan_reduce<<<scan_blocks, kScanThreads, 0, g.stream>>>(g.d_counts.as<uint32_t>(), n_chunks, g.d_partials.as<Triple>());
-        ISD_LAUNCH_CHECK();
-        k_scan_partials<<<1, kScanThreads, 0, g.stream>>>(g.d_partials.as<Triple>(), scan_blocks, g.d_totals.as<unsigned>());
-        ISD_LAUNCH_CHECK();
-    }
-    // totals back to the host (the only read-back before the mesh): sizes of the vertex, face and cut-cube arrays
+    // Per-segment arrays: sized for every tile when that is small (no read-back), else for the work list (one extra
+    // read-back, negligible at the grid sizes where it happens).
     unsigned* h = g.h_small.as<unsigned>();
-    ISD_CUDA(cudaMemcpyAsync(h, g.d_totals.ptr, 3 * sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));
-    ISD_CUDA(cudaMemcpyAsync(h + 8, tile_count, sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));
+    unsigned n_work = (unsigned)ntiles;
+    if ((size_t)ntiles * 64 * 16 > ((size_t)512 << 20)) {
+        ISD_CUDA(cudaMemcpyAsync(h + 8, tile_count, sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));
+        ISD_CUDA(cudaStreamSynchronize(g.stream));
+        n_work = h[8];
+    }
+    const size_t n_seg = (size_t)(n_work > 0 ? n_work : 1) * 64;
+    g.d_seg_bits.reserve(n_seg * sizeof(unsigned long long));
+    g.d_seg_off.reserve(n_seg * sizeof(uint2));
+    McBuffers mb;
+    mb.list = g.d_tile_list.as<unsigned>();
+    mb.counters = tile_count;
+    mb.tile_slot = hints.tile_slot; mb.tile_any = hints.tile_any; mb.tile_bits = hints.tile_bits; mb.TW = hints.TW;
+    mb.seg_bits = g.d_seg_bits.as<unsigned long long>();
+    mb.seg_off = g.d_seg_off.as<uint2>();
+    mb.row_tot = g.d_row_tot.as<Triple>();
+    mb.row_base = g.d_row_base.as<Triple>();
+    {   // K2, K3 first half
+        if (dbg_cases) {
+            k_debug_cases<<<(unsigned)((n_rows * m.NX + 255) / 256), 256, 0, g.stream>>>(m, g.d_signs.as<uint32_t>(), dbg_cases);
+            ISD_LAUNCH_CHECK();
+        }
+        k_mc_classify_tiles<<<gd.ty * gd.tz, 64, 0, g.stream>>>(m, mb, g.d_signs.as<uint32_t>());
+        ISD_LAUNCH_CHECK();
+        k_row_scan<<<scan_blocks, kRowScanThreads, 0, g.stream>>>(m, mb, g.d_scan_state.as<unsigned>(), g.d_totals.as<unsigned>());
+        ISD_LAUNCH_CHECK();
+    }
+    // totals back to the host: sizes of the vertex, face and cut-cube arrays (+ the ghost layer's share, z-slabs only)
+    ISD_CUDA(cudaMemcpyAsync(h, g.d_totals.ptr, 10 * sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));      // [8] = work-list length
     ISD_CUDA(cudaStreamSynchronize(g.stream));
     const unsigned n_cubes = h[2];
-    g.d_cubes.reserve((size_t)(n_cubes > 0 ? n_cubes : 1) * sizeof(unsigned));
-    {   // K3, second half: chunk offsets + the ordered list of cut cubes
-        k_scan_apply<<<scan_blocks, kScanThreads, 0, g.stream>>>(g.d_counts.as<uint32_t>(), n_chunks, g.d_partials.as<Triple>(),
-                                                                g.d_lane_bits.as<uint32_t>(), g.d_offsets.as<uint2>(), g.d_cubes.as<unsigned>());
+    if (m.ghost_rows == 0) { h[4] = 0; h[5] = 0; }
+    g.d_cubes.reserve((size_t)(n_cubes > 0 ? n_cubes : 1) * sizeof(unsigned long long));
+    if (n_work > 0) {   // K3, second half: absolute segment offsets + the ordered list of cut cubes
+        unsigned blocks = (unsigned)((n_seg + 255) / 256);
+        if (blocks > (unsigned)g.sm_count * 32u) blocks = (unsigned)g.sm_count * 32u;
+        k_seg_apply<<<blocks, 256, 0, g.stream>>>(m, mb, g.d_cubes.as<unsigned long long>());
         ISD_LAUNCH_CHECK();
-    }
-    h[4] = 0; h[5] = 0;
-    if (m.ghost_chunks > 0) {   // the ghost layer's share of the totals (z-slabs only)
-        ISD_CUDA(cudaMemcpyAsync(h + 4, g.d_offsets.as<uint2>() + m.ghost_chunks, sizeof(uint2), cudaMemcpyDeviceToHost, g.stream));
-        ISD_CUDA(cudaStreamSynchronize(g.stream));
     }
     ISD_CUDA(cudaEventRecord(g.ev[2], g.stream));
     const long long scan_v = h[0], scan_f = h[1];
@@ -391,9 +411,9 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         ea.v_local0 = ghost_v; ea.f_local0 = ghost_f;
         unsigned blocks = (n_cubes + kEmitThreads - 1) / kEmitThreads;
         if (blocks > (unsigned)g.sm_count * 16u) blocks = (unsigned)g.sm_count * 16u;
-        k_mc_emit<<<blocks, kEmitThreads, 0, g.stream>>>(m, ea, g.d_field.as<float>(), g.d_signs.as<uint32_t>(), g.d_offsets.as<uint2>(),
-                                                         g.d_lane_bits.as<uint32_t>(), g.d_cubes.as<unsigned>(), g.d_totals.as<unsigned>() + 2,
-                                                         g.d_verts.as<float>(), g.d_faces.as<int>());
+        k_mc_emit<<<blocks, kEmitThreads, 0, g.stream>>>(m, mb, ea, g.d_field.as<float>(), g.d_signs.as<uint32_t>(),
+                                                         g.d_cubes.as<unsigned long long>(), g.d_totals.as<unsigned>() + 2, g.d_verts.as<float>(),
+                                                         g.d_faces.as<int>());
         ISD_LAUNCH_CHECK();
     }
     ISD_CUDA(cudaEventRecord(g.ev[3], g.stream));

@@ -16,14 +16,19 @@
 // indices therefore match the reference exactly, not only after canonical re-ordering.
 //
 // Passes.  The case code is a function of eight sign bits, and K1 already packed those (1 bit/node), so classification
-// never touches the 4 B/node field:
-//   K2 mc_classify : one thread per chunk (32 x-adjacent cubes) reads the 8 sign words around it; a chunk whose 4 rows
-//                    are uniformly 0 or 1 is empty (the common case).  Cut chunks are finished by the whole warp, one
-//                    lane per cube: case code -> {new vertices, triangles}, 2 B / chunk.
-//   K3 scan        : exclusive prefix of the chunk counts in scan order + ordered list of non-empty chunks.
-//   K4 mc_emit     : one warp per non-empty chunk; case codes of its own row and of the three rows that introduced its
-//                    other edges come from the sign words, warp prefix sums become vertex ranks; field values are read
-//                    only at the <= 4 corners each new vertex interpolates between.
+// never touches the 4 B/node field; and a cube can only be cut if its home node (x,y,z) lies in a work-list tile of K1
+// (a tile proven inside or outside over its box grown by one cell has no cut cube), so every pass below walks the work
+// list, never the grid — work and memory are proportional to the surface:
+//   K2 mc_classify_tiles : one 64-thread block per row of tiles (ty,tz) that has work-list tiles, one thread per row of
+//                    cubes (y,z) in it.  The block walks its work-list tiles in x order; a thread reads the 4x9 sign bits
+//                    around its 8-cube segment, turns the 8 case codes into counts and bit planes (new vertices: 2 bits,
+//                    triangles: 3 bits per cube) and keeps a running total along its row, which is the segment's offset
+//                    in the row.  Row totals need no atomics: one thread owns a row.
+//   K3 row_scan    : exclusive prefix of the row totals in scan order (single pass, decoupled look-back); seg_apply makes
+//                    the segment offsets absolute and writes the ordered list of cut cubes.
+//   K4 mc_emit     : one thread per cut cube; case codes of its own cube and of the six cubes that introduced its other
+//                    edges come from the sign bits, popcounts of their segments' bit planes become vertex ranks; field
+//                    values are read only at the <= 4 corners each new vertex interpolates between.
 // Algorithmic HBM bytes: 1 bit/node read (K2) [4 B/node if the field itself were read] + 12 B per vertex + 12 B per
 // triangle written (K4).
 #pragma once
@@ -46,92 +51,132 @@ struct McDesc {
     int emit_z0;      // first cube layer whose geometry this GPU emits
     int zc_end;       // one past the last cube layer
     int NX;           // S - 3 cubes per row / rows per layer (x, y in [1, S-2))
-    int K;            // chunks per row: chunk k holds cubes x in [32k, 32k+32) (aligned with the sign words)
-    long long n_chunks;
-    long long ghost_chunks;     // chunks of the ghost layer (0 or NX * K)
+    long long n_rows;       // (zc_end - scan_z0) * NX rows of cubes, numbered in scan order
+    long long ghost_rows;   // rows of the ghost layer (0 or NX)
 };
 
-__device__ __forceinline__ long long chunk_index(const McDesc& m, int z, int y, int k) {
-    return ((long long)(z - m.scan_z0) * m.NX + (y - 1)) * m.K + k;
-}
+__device__ __forceinline__ long long row_index(const McDesc& m, int y, int z) { return (long long)(z - m.scan_z0) * m.NX + (y - 1); }
 __device__ __forceinline__ const uint32_t* sign_row(const McDesc& m, const uint32_t* signs, int y, int z) {
     return signs + ((long long)(z - m.g.z0) * m.g.S + y) * m.g.SW;
 }
-// sign bits of nodes x = 32k .. 32k+32 (33 bits) of one row
-__device__ __forceinline__ unsigned long long row_bits(const uint32_t* __restrict__ row, int k) {
-    return (unsigned long long)__ldg(row + k) | ((unsigned long long)(__ldg(row + k + 1) & 1u) << 32);
+// sign bits of nodes x0 .. x0+3 of one row (x0 >= 0; the row is padded with a whole word)
+__device__ __forceinline__ unsigned sign_bits4(const uint32_t* __restrict__ row, int x0) {
+    const int w = x0 >> 5;
+    return __funnelshift_r(__ldg(row + w), __ldg(row + w + 1), x0 & 31) & 15u;
 }
-// case code of the cube at bit position `b` given the four 33-bit rows (y,z) (y+1,z) (y,z+1) (y+1,z+1); :553-560
-__device__ __forceinline__ unsigned case_code(unsigned long long r00, unsigned long long r10, unsigned long long r01, unsigned long long r11, int b) {
-    const unsigned a = (unsigned)(r00 >> b) & 3u, c = (unsigned)(r10 >> b) & 3u, d = (unsigned)(r01 >> b) & 3u, e = (unsigned)(r11 >> b) & 3u;
+// sign bits of nodes 8*tx .. 8*tx+8 (9 bits) of one row
+__device__ __forceinline__ unsigned sign_bits9(const uint32_t* __restrict__ row, int tx) {
+    const uint8_t* b = reinterpret_cast<const uint8_t*>(row);
+    return (unsigned)__ldg(b + tx) | (((unsigned)__ldg(b + tx + 1) & 1u) << 8);
+}
+// case code of the cube at bit position `b` given the four sign rows (y,z) (y+1,z) (y,z+1) (y+1,z+1); :553-560
+__device__ __forceinline__ unsigned case_code(unsigned r00, unsigned r10, unsigned r01, unsigned r11, int b) {
+    const unsigned a = (r00 >> b) & 3u, c = (r10 >> b) & 3u, d = (r01 >> b) & 3u, e = (r11 >> b) & 3u;
     // bits: f0 (x,y,z)->1  f1 (x+1,y,z)->2  f3 (x+1,y+1,z)->4  f2 (x,y+1,z)->8  f4->16 f5->32 f7->64 f6->128
     return (a & 1u) | (a & 2u) | ((c & 2u) << 1) | ((c & 1u) << 3) | ((d & 1u) << 4) | ((d & 2u) << 4) | ((e & 2u) << 5) | ((e & 1u) << 7);
 }
 
-// ---- K2 ---------------------------------------------------------------------------------------------------------
-constexpr unsigned long long kRowMask = 0x1ffffffffull;
-
-// counts[c] = new vertices | triangles << 8 | cut cubes << 16.  For a cut chunk, lane_bits[5c .. 5c+4] hold, bit per
-// lane, the two bits of each cube's vertex count and the three bits of its triangle count, so that K4 can turn any
-// (chunk, lane) into a vertex / face rank with popcounts.
-__global__ void __launch_bounds__(256) k_mc_classify(McDesc m, const uint32_t* __restrict__ signs, uint32_t* __restrict__ counts,
-                                                     uint32_t* __restrict__ lane_bits, uint8_t* __restrict__ dbg_cases) {
-    const long long c = (long long)blockIdx.x * 256 + threadIdx.x;
-    const bool valid = c < m.n_chunks;
-    const int lane = threadIdx.x & 31;
-    int k = 0, y = 1, z = m.scan_z0;
-    unsigned long long r00 = 0, r10 = 0, r01 = 0, r11 = 0;
-    bool cut = false;
-    if (valid) {
-        k = (int)(c % m.K);
-        const long long row = c / m.K;
-        y = 1 + (int)(row % m.NX);
-        z = m.scan_z0 + (int)(row / m.NX);
-        r00 = row_bits(sign_row(m, signs, y, z), k);
-        r10 = row_bits(sign_row(m, signs, y + 1, z), k);
-        r01 = row_bits(sign_row(m, signs, y, z + 1), k);
-        r11 = row_bits(sign_row(m, signs, y + 1, z + 1), k);
-        const unsigned long long any = r00 | r10 | r01 | r11, all = r00 & r10 & r01 & r11;
-        cut = !(any == 0ull || all == kRowMask) || dbg_cases != nullptr;
-    }
-    unsigned my_count = 0;
-    unsigned todo = __ballot_sync(0xffffffffu, cut);
-    while (todo) {                         // the warp finishes one cut chunk at a time, one lane per cube
-        const int src = __ffs(todo) - 1;
-        todo &= todo - 1;
-        const unsigned long long s00 = __shfl_sync(0xffffffffu, r00, src), s10 = __shfl_sync(0xffffffffu, r10, src);
-        const unsigned long long s01 = __shfl_sync(0xffffffffu, r01, src), s11 = __shfl_sync(0xffffffffu, r11, src);
-        const int sk = __shfl_sync(0xffffffffu, k, src), sy = __shfl_sync(0xffffffffu, y, src), sz = __shfl_sync(0xffffffffu, z, src);
-        const int x = 32 * sk + lane;
-        const bool xin = x >= 1 && x <= m.g.S - 3;
-        const unsigned code = xin ? case_code(s00, s10, s01, s11, lane) : 0u;
-        unsigned nv = 0, nt = 0;
-        if (code != 0u && code != 255u) {
-            const unsigned info = d_case_info[code];
-            nv = (info >> 8) & 3u;
-            nt = info & 0xffu;
-        }
-        const unsigned v0 = __ballot_sync(0xffffffffu, nv & 1u), v1 = __ballot_sync(0xffffffffu, nv & 2u);
-        const unsigned t0 = __ballot_sync(0xffffffffu, nt & 1u), t1 = __ballot_sync(0xffffffffu, nt & 2u), t2 = __ballot_sync(0xffffffffu, nt & 4u);
-        if (lane == src) {
-            my_count = (__popc(v0) + 2u * __popc(v1)) | ((__popc(t0) + 2u * __popc(t1) + 4u * __popc(t2)) << 8) | (__popc(t0 | t1 | t2) << 16);
-            if (my_count) {
-                uint32_t* lb = lane_bits + c * 5;
-                lb[0] = v0; lb[1] = v1; lb[2] = t0; lb[3] = t1; lb[4] = t2;
-            }
-        }
-        if (dbg_cases != nullptr && xin)
-            dbg_cases[((long long)(sz - m.scan_z0) * m.NX + (sy - 1)) * m.NX + (x - 1)] = (uint8_t)code;
-    }
-    if (valid) counts[c] = my_count;
-}
-
-// ---- K3: exclusive scan of the chunk counts -------------------------------------------------------------------------
-constexpr int kScanThreads = 256, kScanItems = 8;
-constexpr int kScanTile = kScanThreads * kScanItems;
-
 struct Triple { unsigned v, f, a; };
 __device__ __forceinline__ Triple operator+(Triple p, Triple q) { return Triple{p.v + q.v, p.f + q.f, p.a + q.a}; }
+
+// What K1 leaves for marching cubes (field_kernel.cuh, k_tile_bounds) and what the passes share.  A SEGMENT is the 8 cubes
+// of one row (y,z) whose home nodes lie in one work-list tile; segment index = slot * 64 + (lz * 8 + ly).
+//   seg_bits : bits 0-7 / 8-15 the two bit planes of the cubes' new-vertex counts, 16-23 / 24-31 / 32-39 the three bit planes
+//              of their triangle counts, bits 40-63 the cut cubes before the segment in its row
+//   seg_off  : {vertices, triangles} before the segment — in its row after K2, absolute after seg_apply
+struct McBuffers {
+    const unsigned* list;          // work-list: tile index per slot
+    const unsigned* counters;      // [0] work-list length
+    const unsigned* tile_slot;     // tile index -> slot (valid for work-list tiles)
+    const uint8_t* tile_any;       // [tz][ty]: the row of tiles has work-list tiles
+    const uint32_t* tile_bits;     // [tz][ty][TW]: bit per tile
+    int TW;
+    unsigned long long* seg_bits;
+    uint2* seg_off;
+    Triple* row_tot;               // per row of cubes (written for rows inside rows of tiles that have work)
+    Triple* row_base;              // exclusive prefix of row_tot in scan order
+};
+
+__device__ __forceinline__ unsigned planes_v(unsigned long long sb, unsigned below) {      // new vertices of the cubes selected by `below`
+    return __popc((unsigned)sb & 0xffu & below) + 2u * __popc((unsigned)(sb >> 8) & 0xffu & below);
+}
+__device__ __forceinline__ unsigned planes_t(unsigned long long sb, unsigned below) {
+    return __popc((unsigned)(sb >> 16) & 0xffu & below) + 2u * __popc((unsigned)(sb >> 24) & 0xffu & below) +
+           4u * __popc((unsigned)(sb >> 32) & 0xffu & below);
+}
+__device__ __forceinline__ unsigned planes_cut(unsigned long long sb) {      // bit per cube: has triangles
+    return ((unsigned)(sb >> 16) | (unsigned)(sb >> 24) | (unsigned)(sb >> 32)) & 0xffu;
+}
+
+// ---- K2 ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(64) k_mc_classify_tiles(McDesc m, McBuffers mb, const uint32_t* __restrict__ signs) {
+    const int trow = blockIdx.x;
+    if (!mb.tile_any[trow]) return;
+    const int ty = trow % m.g.ty, tz = trow / m.g.ty;
+    const int ly = threadIdx.x & 7, lz = threadIdx.x >> 3;
+    const int y = 8 * ty + ly, z = m.g.z0 + 8 * tz + lz;
+    const bool row_valid = y >= 1 && y <= m.g.S - 3 && z >= m.scan_z0 && z < m.zc_end;
+    const uint32_t *s00 = nullptr, *s10 = nullptr, *s01 = nullptr, *s11 = nullptr;
+    if (row_valid) {
+        s00 = sign_row(m, signs, y, z); s10 = sign_row(m, signs, y + 1, z);
+        s01 = sign_row(m, signs, y, z + 1); s11 = sign_row(m, signs, y + 1, z + 1);
+    }
+    Triple run{0, 0, 0};
+    for (int w = 0; w < mb.TW; ++w) {
+        unsigned bits = __ldg(mb.tile_bits + (long long)trow * mb.TW + w);
+        while (bits) {
+            const int tx = 32 * w + __ffs(bits) - 1;
+            bits &= bits - 1;
+            const long long seg = (long long)__ldg(mb.tile_slot + (long long)trow * m.g.tx + tx) * 64 + threadIdx.x;
+            unsigned long long sb = 0ull;
+            if (row_valid) {
+                const unsigned r00 = sign_bits9(s00, tx), r10 = sign_bits9(s10, tx), r01 = sign_bits9(s01, tx), r11 = sign_bits9(s11, tx);
+                if ((r00 | r10 | r01 | r11) != 0u && (r00 & r10 & r01 & r11) != 0x1ffu) {
+                    unsigned v0 = 0, v1 = 0, t0 = 0, t1 = 0, t2 = 0;
+#pragma unroll
+                    for (int l = 0; l < 8; ++l) {
+                        const int x = 8 * tx + l;
+                        const bool xin = x >= 1 && x <= m.g.S - 3;
+                        const unsigned code = xin ? case_code(r00, r10, r01, r11, l) : 0u;
+                        if (code != 0u && code != 255u) {
+                            const unsigned info = d_case_info[code];
+                            const unsigned nv = (info >> 8) & 3u, nt = info & 0xffu;
+                            v0 |= (nv & 1u) << l; v1 |= ((nv >> 1) & 1u) << l;
+                            t0 |= (nt & 1u) << l; t1 |= ((nt >> 1) & 1u) << l; t2 |= ((nt >> 2) & 1u) << l;
+                        }
+                    }
+                    sb = (unsigned long long)(v0 | (v1 << 8) | (t0 << 16) | (t1 << 24)) | ((unsigned long long)t2 << 32);
+                }
+                if (sb) {
+                    mb.seg_off[seg] = make_uint2(run.v, run.f);
+                    sb |= (unsigned long long)run.a << 40;
+                    run = run + Triple{planes_v(sb, 0xffu), planes_t(sb, 0xffu), (unsigned)__popc(planes_cut(sb))};
+                }
+            }
+            mb.seg_bits[seg] = sb;
+        }
+    }
+    if (row_valid) mb.row_tot[row_index(m, y, z)] = run;
+}
+
+// Debug only (isd_get_case_codes): the dense array of case codes, straight from the sign bits.
+__global__ void __launch_bounds__(256) k_debug_cases(McDesc m, const uint32_t* __restrict__ signs, uint8_t* __restrict__ dbg_cases) {
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i >= m.n_rows * m.NX) return;
+    const int x = 1 + (int)(i % m.NX);
+    const long long row = i / m.NX;
+    const int y = 1 + (int)(row % m.NX), z = m.scan_z0 + (int)(row / m.NX);
+    const unsigned r00 = sign_bits4(sign_row(m, signs, y, z), x), r10 = sign_bits4(sign_row(m, signs, y + 1, z), x);
+    const unsigned r01 = sign_bits4(sign_row(m, signs, y, z + 1), x), r11 = sign_bits4(sign_row(m, signs, y + 1, z + 1), x);
+    dbg_cases[i] = (uint8_t)case_code(r00, r10, r01, r11, 0);
+}
+
+// ---- K3 ---------------------------------------------------------------------------------------------------------
+// Exclusive prefix of the row totals in scan order, one pass: blocks take tickets, publish their aggregate, and look back
+// over their predecessors' aggregates / inclusive prefixes (status 1 / 2).  `scan_state` = {ticket, pad, ...} followed by one
+// {status, v, f, a} per block, zeroed before the launch.  totals[0..2] <- grand totals, totals[4..5] <- vertices / triangles
+// before row `ghost_rows`.
+constexpr int kRowScanThreads = 512;
 
 __device__ __forceinline__ Triple warp_inclusive(Triple t, int lane) {
 #pragma unroll
@@ -141,89 +186,79 @@ __device__ __forceinline__ Triple warp_inclusive(Triple t, int lane) {
     }
     return t;
 }
-// exclusive prefix of `mine` over the block (blockDim = kScanThreads); *total gets the block sum
-__device__ __forceinline__ Triple block_exclusive(Triple mine, Triple* total) {
-    __shared__ Triple s_warp[kScanThreads / 32];
+
+__global__ void __launch_bounds__(kRowScanThreads) k_row_scan(McDesc m, McBuffers mb, unsigned* __restrict__ scan_state, unsigned* __restrict__ totals) {
+    __shared__ Triple s_warp[kRowScanThreads / 32];
+    __shared__ Triple s_prefix;
+    __shared__ unsigned s_ticket;
+    if (threadIdx.x == 0) s_ticket = atomicAdd(scan_state, 1u);
+    __syncthreads();
+    const unsigned blk = s_ticket;
+    const long long row = (long long)blk * kRowScanThreads + threadIdx.x;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    Triple mine{0, 0, 0};
+    if (row < m.n_rows) {
+        const int y = 1 + (int)(row % m.NX), z = m.scan_z0 + (int)(row / m.NX);
+        if (mb.tile_any[((z - m.g.z0) >> 3) * m.g.ty + (y >> 3)]) mine = mb.row_tot[row];
+    }
     const Triple inc = warp_inclusive(mine, lane);
     if (lane == 31) s_warp[w] = inc;
     __syncthreads();
-    Triple base{0, 0, 0}, sum{0, 0, 0};
-#pragma unroll
-    for (int i = 0; i < kScanThreads / 32; ++i) {
-        if (i < w) base = base + s_warp[i];
-        sum = sum + s_warp[i];
-    }
-    __syncthreads();
-    *total = sum;
-    return Triple{base.v + inc.v - mine.v, base.f + inc.f - mine.f, base.a + inc.a - mine.a};
-}
-
-__device__ __forceinline__ void load_counts8(const uint32_t* counts, long long first, long long n, unsigned (&c)[kScanItems]) {
-    if (first + kScanItems <= n) {
-        const uint4 a = *reinterpret_cast<const uint4*>(counts + first), b = *reinterpret_cast<const uint4*>(counts + first + 4);
-        c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w; c[4] = b.x; c[5] = b.y; c[6] = b.z; c[7] = b.w;
-    } else {
-#pragma unroll
-        for (int i = 0; i < kScanItems; ++i) c[i] = (first + i < n) ? counts[first + i] : 0u;
-    }
-}
-__device__ __forceinline__ Triple unpack_count(unsigned c) { return Triple{c & 0xffu, (c >> 8) & 0xffu, c >> 16}; }
-
-__global__ void __launch_bounds__(kScanThreads) k_scan_reduce(const uint32_t* __restrict__ counts, long long n, Triple* __restrict__ partials) {
-    const long long first = ((long long)blockIdx.x * kScanThreads + threadIdx.x) * kScanItems;
-    unsigned c[kScanItems];
-    load_counts8(counts, first, n, c);
-    Triple t{0, 0, 0};
-#pragma unroll
-    for (int i = 0; i < kScanItems; ++i) t = t + unpack_count(c[i]);
-    Triple total;
-    block_exclusive(t, &total);
-    if (threadIdx.x == 0) partials[blockIdx.x] = total;
-}
-
-// one block: partials[i] <- exclusive prefix; totals[0..2] <- grand totals {vertices, triangles, cut cubes}
-__global__ void __launch_bounds__(kScanThreads) k_scan_partials(Triple* __restrict__ partials, int nblocks, unsigned* __restrict__ totals) {
-    Triple carry{0, 0, 0};
-    for (int base = 0; base < nblocks; base += kScanThreads) {
-        const int i = base + threadIdx.x;
-        const Triple mine = (i < nblocks) ? partials[i] : Triple{0, 0, 0};
-        Triple total;
-        const Triple ex = block_exclusive(mine, &total);
-        if (i < nblocks) partials[i] = carry + ex;
-        carry = carry + total;
-    }
-    if (threadIdx.x == 0) { totals[0] = carry.v; totals[1] = carry.f; totals[2] = carry.a; }
-}
-
-// offsets[c] = {first vertex, first triangle} of chunk c; cubes[] = the cut cubes in scan order, as chunk * 32 + lane
-__global__ void __launch_bounds__(kScanThreads) k_scan_apply(const uint32_t* __restrict__ counts, long long n, const Triple* __restrict__ partials,
-                                                            const uint32_t* __restrict__ lane_bits, uint2* __restrict__ offsets,
-                                                            unsigned* __restrict__ cubes) {
-    const long long first = ((long long)blockIdx.x * kScanThreads + threadIdx.x) * kScanItems;
-    unsigned c[kScanItems];
-    load_counts8(counts, first, n, c);
-    Triple t{0, 0, 0};
-#pragma unroll
-    for (int i = 0; i < kScanItems; ++i) t = t + unpack_count(c[i]);
-    Triple total;
-    Triple run = partials[blockIdx.x] + block_exclusive(t, &total);
-#pragma unroll
-    for (int i = 0; i < kScanItems; ++i) {
-        if (first + i < n) {
-            offsets[first + i] = make_uint2(run.v, run.f);
-            if (c[i] != 0u) {
-                const uint32_t* lb = lane_bits + (first + i) * 5;
-                unsigned act = lb[2] | lb[3] | lb[4];
-                unsigned slot = run.a;
-                while (act) {
-                    const int l = __ffs(act) - 1;
-                    act &= act - 1;
-                    cubes[slot++] = (unsigned)((first + i) * 32 + l);
+    if (w == 0) {
+        const Triple t = (lane < kRowScanThreads / 32) ? s_warp[lane] : Triple{0, 0, 0};
+        const Triple ti = warp_inclusive(t, lane);
+        if (lane < kRowScanThreads / 32) s_warp[lane] = Triple{ti.v - t.v, ti.f - t.f, ti.a - t.a};
+        if (lane == kRowScanThreads / 32 - 1) {
+            // per block: {status, aggregate v f a, inclusive v f a, pad}; status 1 = aggregate ready, 2 = inclusive prefix ready
+            volatile unsigned* mine_state = scan_state + 8 + (size_t)blk * 8;
+            const Triple agg = ti;
+            Triple prefix{0, 0, 0};
+            if (blk > 0) {
+                mine_state[1] = agg.v; mine_state[2] = agg.f; mine_state[3] = agg.a;
+                __threadfence();
+                mine_state[0] = 1u;
+                for (long long j = (long long)blk - 1; j >= 0; --j) {       // an earlier ticket is always running or done
+                    volatile unsigned* sj = scan_state + 8 + (size_t)j * 8;
+                    unsigned st;
+                    while ((st = sj[0]) == 0u) {}
+                    __threadfence();
+                    if (st == 2u) { prefix = prefix + Triple{sj[4], sj[5], sj[6]}; break; }
+                    prefix = prefix + Triple{sj[1], sj[2], sj[3]};
                 }
             }
+            mine_state[4] = prefix.v + agg.v; mine_state[5] = prefix.f + agg.f; mine_state[6] = prefix.a + agg.a;
+            __threadfence();
+            mine_state[0] = 2u;
+            s_prefix = prefix;
         }
-        run = run + unpack_count(c[i]);
+    }
+    __syncthreads();
+    const Triple base = s_prefix + s_warp[w] + Triple{inc.v - mine.v, inc.f - mine.f, inc.a - mine.a};
+    if (row < m.n_rows) mb.row_base[row] = base;
+    if (m.ghost_rows > 0 && row == m.ghost_rows) { totals[4] = base.v; totals[5] = base.f; }
+    if (row == m.n_rows - 1) { totals[0] = base.v + mine.v; totals[1] = base.f + mine.f; totals[2] = base.a + mine.a; }
+}
+
+// One thread per segment of the work list: offsets become absolute, and the cut cubes go, in scan order, into cubes[]
+// as segment * 8 + position.
+__global__ void __launch_bounds__(256) k_seg_apply(McDesc m, McBuffers mb, unsigned long long* __restrict__ cubes) {
+    const long long n_seg = (long long)mb.counters[0] * 64;
+    for (long long seg = (long long)blockIdx.x * 256 + threadIdx.x; seg < n_seg; seg += (long long)gridDim.x * 256) {
+        const unsigned long long sb = mb.seg_bits[seg];
+        unsigned cut = planes_cut(sb);
+        if ((sb & 0xffffffffffull) == 0ull) continue;
+        const int t = (int)mb.list[seg >> 6], r = (int)(seg & 63);
+        const int ty = (t / m.g.tx) % m.g.ty, tzl = t / (m.g.tx * m.g.ty);
+        const int y = 8 * ty + (r & 7), z = m.g.z0 + 8 * tzl + (r >> 3);
+        const Triple base = mb.row_base[row_index(m, y, z)];
+        const uint2 rel = mb.seg_off[seg];
+        mb.seg_off[seg] = make_uint2(base.v + rel.x, base.f + rel.y);
+        unsigned long long slot = (unsigned long long)base.a + (sb >> 40);
+        while (cut) {
+            const int l = __ffs(cut) - 1;
+            cut &= cut - 1;
+            cubes[slot++] = (unsigned long long)seg * 8ull + (unsigned)l;
+        }
     }
 }
 
@@ -246,58 +281,52 @@ struct EmitArgs {
     long long f_local0;
 };
 
-// 34 sign bits of one row around chunk k: bit j <-> node x = 32k - 1 + j  (j = 0 is the halo node of the previous word)
-__device__ __forceinline__ unsigned long long row_bits34(const uint32_t* __restrict__ row, int k) {
-    const unsigned prev = (k > 0) ? (__ldg(row + k - 1) >> 31) : 1u;
-    return (unsigned long long)prev | ((unsigned long long)__ldg(row + k) << 1) | ((unsigned long long)(__ldg(row + k + 1) & 1u) << 33);
-}
-
-// first vertex (scan numbering) of the cube at (chunk c, lane l): chunk prefix + vertices of the lanes before it
-__device__ __forceinline__ unsigned cube_vertex_base(const uint2* __restrict__ offsets, const uint32_t* __restrict__ lane_bits, long long c, int l) {
-    const unsigned lt = (1u << l) - 1u;
-    return offsets[c].x + __popc(__ldg(lane_bits + c * 5) & lt) + 2u * __popc(__ldg(lane_bits + c * 5 + 1) & lt);
+// first vertex (scan numbering) of the cube at (x, y, z): its segment's offset + the new vertices of the cubes before it
+__device__ __forceinline__ long long cube_vertex_base(const McDesc& m, const McBuffers& mb, int x, int y, int z) {
+    const int zl = z - m.g.z0;
+    const long long tile = ((long long)(zl >> 3) * m.g.ty + (y >> 3)) * m.g.tx + (x >> 3);
+    const long long seg = (long long)__ldg(mb.tile_slot + tile) * 64 + ((zl & 7) * 8 + (y & 7));
+    return (long long)mb.seg_off[seg].x + planes_v(mb.seg_bits[seg], (1u << (x & 7)) - 1u);
 }
 
 constexpr int kEmitThreads = 128;
 
 // One thread per cut cube.  Its own new vertices (edges 5, 6, 10) are interpolated from the field; the other nine
-// edges' vertices were introduced by six neighbouring cubes, whose vertex ranks follow from their chunk's prefix and
-// lane bits and their own case code (for the order of their new vertices).
-__global__ void __launch_bounds__(kEmitThreads) k_mc_emit(McDesc m, EmitArgs ea, const float* __restrict__ field, const uint32_t* __restrict__ signs,
-                                                          const uint2* __restrict__ offsets, const uint32_t* __restrict__ lane_bits,
-                                                          const unsigned* __restrict__ cubes, const unsigned* __restrict__ n_cubes_ptr,
-                                                          float* __restrict__ verts, int* __restrict__ faces) {
+// edges' vertices were introduced by six neighbouring cubes, whose vertex ranks follow from their segment's offset and
+// bit planes and their own case code (for the order of their new vertices).
+__global__ void __launch_bounds__(kEmitThreads) k_mc_emit(McDesc m, McBuffers mb, EmitArgs ea, const float* __restrict__ field,
+                                                          const uint32_t* __restrict__ signs, const unsigned long long* __restrict__ cubes,
+                                                          const unsigned* __restrict__ n_cubes_ptr, float* __restrict__ verts, int* __restrict__ faces) {
     const unsigned n_cubes = *n_cubes_ptr;
-    const int S = m.g.S;
     for (unsigned i = blockIdx.x * kEmitThreads + threadIdx.x; i < n_cubes; i += gridDim.x * kEmitThreads) {
-        const unsigned id = cubes[i];
-        const long long chunk = id >> 5;
-        const int lane = (int)(id & 31u);
-        const int k = (int)(chunk % m.K);
-        const long long row = chunk / m.K;
-        const int y = 1 + (int)(row % m.NX);
-        const int z = m.scan_z0 + (int)(row / m.NX);
+        const unsigned long long id = cubes[i];
+        const long long seg = (long long)(id >> 3);
+        const int l = (int)(id & 7ull), r = (int)(seg & 63);
+        const int t = (int)mb.list[seg >> 6];
+        const int tx = t % m.g.tx, ty = (t / m.g.tx) % m.g.ty, tzl = t / (m.g.tx * m.g.ty);
+        const int x = 8 * tx + l, y = 8 * ty + (r & 7), z = m.g.z0 + 8 * tzl + (r >> 3);
         if (z < m.emit_z0) continue;          // ghost layer: counted here, emitted by the slab below
-        const int x = 32 * k + lane;
-        unsigned long long R[3][3];           // sign rows (dy, dz) in {-1,0,1}^2, 34 bits each
+        unsigned R[3][3];                     // sign rows (dy, dz) in {-1,0,1}^2: bit j <-> node x - 1 + j
 #pragma unroll
         for (int dz = 0; dz < 3; ++dz)
 #pragma unroll
-            for (int dy = 0; dy < 3; ++dy) R[dz][dy] = row_bits34(sign_row(m, signs, y + dy - 1, z + dz - 1), k);
-        // rows: 0 own (y,z)   1 B (y,z-1)   2 C (y-1,z)   3 A (y-1,z-1); the cube at x sits at bit position lane + 1
+            for (int dy = 0; dy < 3; ++dy) R[dz][dy] = sign_bits4(sign_row(m, signs, y + dy - 1, z + dz - 1), x - 1);
+        // rows: 0 own (y,z)   1 B (y,z-1)   2 C (y-1,z)   3 A (y-1,z-1); the cube at x sits at bit position 1
         const int rdy[4] = {1, 1, 0, 0}, rdz[4] = {1, 0, 1, 0};
         unsigned code[4], codep[3];
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            const unsigned long long a = R[rdz[r]][rdy[r]], b = R[rdz[r]][rdy[r] + 1], c = R[rdz[r] + 1][rdy[r]], d = R[rdz[r] + 1][rdy[r] + 1];
-            code[r] = case_code(a, b, c, d, lane + 1);
-            if (r < 3) codep[r] = (x > 1) ? case_code(a, b, c, d, lane) : 0u;      // the cube at x - 1 (x = 0 is never visited)
+        for (int q = 0; q < 4; ++q) {
+            const unsigned a = R[rdz[q]][rdy[q]], b = R[rdz[q]][rdy[q] + 1], c = R[rdz[q] + 1][rdy[q]], d = R[rdz[q] + 1][rdy[q] + 1];
+            code[q] = case_code(a, b, c, d, 1);
+            if (q < 3) codep[q] = (x > 1) ? case_code(a, b, c, d, 0) : 0u;      // the cube at x - 1 (x = 0 is never visited)
         }
         const unsigned code_self = code[0];
         const unsigned info_self = d_case_info[code_self];
         const unsigned nt = info_self & 0xffu, own_self = info_self >> 8, nv = own_self & 3u;
         const unsigned emask = ISD_EDGE_MASK(code_self);
-        const long long vself = (long long)cube_vertex_base(offsets, lane_bits, chunk, lane);
+        const unsigned long long sb_self = mb.seg_bits[seg];
+        const uint2 off_self = mb.seg_off[seg];
+        const long long vself = (long long)off_self.x + planes_v(sb_self, (1u << l) - 1u);
         // ---- vertices introduced by this cube -----------------------------------------------------------------------
         if (nv) {
             const float fx = ((float)x + m.g.xi0) * m.g.wx, fy = ((float)y + m.g.yi0) * m.g.wy, fz = ((float)z + m.g.zi0) * m.g.wz;   // :1041-1053
@@ -330,47 +359,39 @@ __global__ void __launch_bounds__(kEmitThreads) k_mc_emit(McDesc m, EmitArgs ea,
         }
         if (nt == 0) continue;
         // ---- vertex index of every cut edge (SURVEY Appendix A + first-appearance cube) --------------------------------
-        // neighbour cubes: chunk of row r at the same k; the cube at x-1 is lane-1 of it, or lane 31 of chunk k-1
-        const long long crow[3] = {chunk, chunk_index(m, z - 1, y, k), chunk_index(m, z, y - 1, k)};      // own, B, C
-        const long long cA = chunk_index(m, z - 1, y - 1, k);
-        const int lp = (lane > 0) ? lane - 1 : 31;
         long long ev[12];
 #pragma unroll
         for (int q = 0; q < 12; ++q) ev[q] = 0;
-        auto vidx = [&](long long c, int l, unsigned cd, unsigned edge_code) -> long long {
+        auto vidx = [&](int cx, int cy, int cz, unsigned cd, unsigned edge_code) -> long long {
             const unsigned own = d_case_info[cd] >> 8;
-            return ea.vbase + (long long)cube_vertex_base(offsets, lane_bits, c, l) + owned_rank(own, edge_code);
+            return ea.vbase + cube_vertex_base(m, mb, cx, cy, cz) + owned_rank(own, edge_code);
         };
         ev[5] = ea.vbase + vself + owned_rank(own_self, 0u);
         ev[6] = ea.vbase + vself + owned_rank(own_self, 1u);
         ev[10] = ea.vbase + vself + owned_rank(own_self, 2u);
-        if (emask & 0x001u) ev[0] = vidx(cA, lane, code[3], 1u);                    // x-edge at (x,y,z)    <- cube (x, y-1, z-1) edge 6
+        if (emask & 0x001u) ev[0] = vidx(x, y - 1, z - 1, code[3], 1u);             // x-edge at (x,y,z)    <- cube (x, y-1, z-1) edge 6
         if (emask & 0x006u) {                                                       // cube (x, y, z-1): edges 5 and 6
-            const long long b = ea.vbase + (long long)cube_vertex_base(offsets, lane_bits, crow[1], lane);
+            const long long b = ea.vbase + cube_vertex_base(m, mb, x, y, z - 1);
             const unsigned own = d_case_info[code[1]] >> 8;
             ev[1] = b + owned_rank(own, 0u);                                        // y-edge at (x+1,y,z)
             ev[2] = b + owned_rank(own, 1u);                                        // x-edge at (x,y+1,z)
         }
         if (emask & 0x210u) {                                                       // cube (x, y-1, z): edges 6 and 10
-            const long long b = ea.vbase + (long long)cube_vertex_base(offsets, lane_bits, crow[2], lane);
+            const long long b = ea.vbase + cube_vertex_base(m, mb, x, y - 1, z);
             const unsigned own = d_case_info[code[2]] >> 8;
             ev[4] = b + owned_rank(own, 1u);                                        // x-edge at (x,y,z+1)
             ev[9] = b + owned_rank(own, 2u);                                        // z-edge at (x+1,y,z)
         }
-        const long long dprev = (lane > 0) ? 0 : -1;                                // chunk k-1 of the same row
-        if (emask & 0x008u) ev[3] = vidx(crow[1] + dprev, lp, codep[1], 0u);        // y-edge at (x,y,z)    <- cube (x-1, y, z-1) edge 5
-        if (emask & 0x100u) ev[8] = vidx(crow[2] + dprev, lp, codep[2], 2u);        // z-edge at (x,y,z)    <- cube (x-1, y-1, z) edge 10
+        if (emask & 0x008u) ev[3] = vidx(x - 1, y, z - 1, codep[1], 0u);            // y-edge at (x,y,z)    <- cube (x-1, y, z-1) edge 5
+        if (emask & 0x100u) ev[8] = vidx(x - 1, y - 1, z, codep[2], 2u);            // z-edge at (x,y,z)    <- cube (x-1, y-1, z) edge 10
         if (emask & 0x880u) {                                                       // cube (x-1, y, z): edges 5 and 10
-            const long long b = ea.vbase + (long long)cube_vertex_base(offsets, lane_bits, crow[0] + dprev, lp);
+            const long long b = ea.vbase + cube_vertex_base(m, mb, x - 1, y, z);
             const unsigned own = d_case_info[codep[0]] >> 8;
             ev[7] = b + owned_rank(own, 0u);                                        // y-edge at (x,y,z+1)
             ev[11] = b + owned_rank(own, 2u);                                       // z-edge at (x,y+1,z)
         }
         // ---- triangles ---------------------------------------------------------------------------------------------------
-        const unsigned ltm = (1u << lane) - 1u;
-        const uint32_t* lb = lane_bits + chunk * 5;
-        const unsigned tbefore = __popc(__ldg(lb + 2) & ltm) + 2u * __popc(__ldg(lb + 3) & ltm) + 4u * __popc(__ldg(lb + 4) & ltm);
-        const long long floc = (long long)offsets[chunk].y + tbefore - ea.f_local0;
+        const long long floc = (long long)off_self.y + planes_t(sb_self, (1u << l) - 1u) - ea.f_local0;
         const int8_t* tri = d_tri_table + code_self * 16;
         for (unsigned t = 0; t < nt; ++t) {
             int* o = faces + (floc + t) * 3;
