@@ -245,7 +245,9 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     const size_t field_bytes = (size_t)gd.plane * gd.nz * sizeof(float);
     g.d_field.reserve(field_bytes);
     const long long n_rows = m.n_rows;
-    const int scan_blocks = (int)((n_rows + kRowScanThreads - 1) / kRowScanThreads);
+    int scan_blocks = (int)((n_rows + kRowScanThreads - 1) / kRowScanThreads);
+    if (scan_blocks > kRowScanMaxBlocks) scan_blocks = kRowScanMaxBlocks;
+    const long long rows_per_block = ((n_rows + scan_blocks - 1) / scan_blocks + kRowScanThreads - 1) / kRowScanThreads * kRowScanThreads;
     g.d_row_tot.reserve((size_t)n_rows * sizeof(Triple));
     g.d_row_base.reserve((size_t)n_rows * sizeof(Triple));
     g.d_scan_state.reserve(((size_t)scan_blocks + 1) * 8 * sizeof(unsigned));
@@ -356,9 +358,10 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
             k_debug_cases<<<(unsigned)((n_rows * m.NX + 255) / 256), 256, 0, g.stream>>>(m, g.d_signs.as<uint32_t>(), dbg_cases);
             ISD_LAUNCH_CHECK();
         }
-        k_mc_classify_tiles<<<gd.ty * gd.tz, 64, 0, g.stream>>>(m, mb, g.d_signs.as<uint32_t>());
+        if (gd.ty * gd.tz <= 8192) k_mc_classify_tiles<4><<<gd.ty * gd.tz, 256, 0, g.stream>>>(m, mb, g.d_signs.as<uint32_t>());
+        else k_mc_classify_tiles<1><<<gd.ty * gd.tz, 64, 0, g.stream>>>(m, mb, g.d_signs.as<uint32_t>());
         ISD_LAUNCH_CHECK();
-        k_row_scan<<<scan_blocks, kRowScanThreads, 0, g.stream>>>(m, mb, g.d_scan_state.as<unsigned>(), g.d_totals.as<unsigned>());
+        k_row_scan<<<scan_blocks, kRowScanThreads, 0, g.stream>>>(m, mb, rows_per_block, g.d_scan_state.as<unsigned>(), g.d_totals.as<unsigned>());
         ISD_LAUNCH_CHECK();
     }
     // totals back to the host: sizes of the vertex, face and cut-cube arrays (+ the ghost layer's share, z-slabs only)

@@ -109,11 +109,44 @@ __device__ __forceinline__ unsigned planes_cut(unsigned long long sb) {      // 
 }
 
 // ---- K2 ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(64) k_mc_classify_tiles(McDesc m, McBuffers mb, const uint32_t* __restrict__ signs) {
+// Block = one row of tiles (ty,tz); 64 * kClassifyTiles threads = kClassifyTiles tiles x 64 rows of cubes.  The block lists its work-list tiles in x
+// order, then takes them four at a time: every thread classifies one 8-cube segment, the segment totals of the group meet in
+// shared memory, and each row's running total (kept by all four threads of that row) advances by the group.
+// (Small grids have few rows of tiles and many tiles in each: four tiles at a time; large grids the opposite: one.)
+constexpr int kMaxTilesPerRow = 1024;
+
+template <int kClassifyTiles>
+__global__ void __launch_bounds__(64 * kClassifyTiles) k_mc_classify_tiles(McDesc m, McBuffers mb, const uint32_t* __restrict__ signs) {
     const int trow = blockIdx.x;
     if (!mb.tile_any[trow]) return;
+    __shared__ uint16_t s_tiles[kMaxTilesPerRow];
+    __shared__ int s_ntiles;
+    __shared__ Triple s_tot[kClassifyTiles][64];
+    if (threadIdx.x < 32) {      // ordered list of the row's work-list tiles (one lane per 32 tiles, popcount ranks)
+        int base = 0;
+        for (int w0 = 0; w0 < mb.TW; w0 += 32) {
+            const int w = w0 + (int)threadIdx.x;
+            unsigned bits = (w < mb.TW) ? __ldg(mb.tile_bits + (long long)trow * mb.TW + w) : 0u;
+            int cnt = __popc(bits), inc = cnt;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int o = __shfl_up_sync(0xffffffffu, inc, d);
+                if ((int)threadIdx.x >= d) inc += o;
+            }
+            int at = base + inc - cnt;
+            while (bits) {
+                s_tiles[at++] = (uint16_t)(32 * w + __ffs(bits) - 1);
+                bits &= bits - 1;
+            }
+            base += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        if (threadIdx.x == 0) s_ntiles = base;
+    }
+    __syncthreads();
+    const int ntiles = s_ntiles;
     const int ty = trow % m.g.ty, tz = trow / m.g.ty;
-    const int ly = threadIdx.x & 7, lz = threadIdx.x >> 3;
+    const int r = threadIdx.x & 63, j = threadIdx.x >> 6;
+    const int ly = r & 7, lz = r >> 3;
     const int y = 8 * ty + ly, z = m.g.z0 + 8 * tz + lz;
     const bool row_valid = y >= 1 && y <= m.g.S - 3 && z >= m.scan_z0 && z < m.zc_end;
     const uint32_t *s00 = nullptr, *s10 = nullptr, *s01 = nullptr, *s11 = nullptr;
@@ -122,13 +155,14 @@ __global__ void __launch_bounds__(64) k_mc_classify_tiles(McDesc m, McBuffers mb
         s01 = sign_row(m, signs, y, z + 1); s11 = sign_row(m, signs, y + 1, z + 1);
     }
     Triple run{0, 0, 0};
-    for (int w = 0; w < mb.TW; ++w) {
-        unsigned bits = __ldg(mb.tile_bits + (long long)trow * mb.TW + w);
-        while (bits) {
-            const int tx = 32 * w + __ffs(bits) - 1;
-            bits &= bits - 1;
-            const long long seg = (long long)__ldg(mb.tile_slot + (long long)trow * m.g.tx + tx) * 64 + threadIdx.x;
-            unsigned long long sb = 0ull;
+    for (int i0 = 0; i0 < ntiles; i0 += kClassifyTiles) {
+        const int i = i0 + j;
+        unsigned long long sb = 0ull;
+        long long seg = -1;
+        Triple tot{0, 0, 0};
+        if (i < ntiles) {
+            const int tx = s_tiles[i];
+            seg = (long long)__ldg(mb.tile_slot + (long long)trow * m.g.tx + tx) * 64 + r;
             if (row_valid) {
                 const unsigned r00 = sign_bits9(s00, tx), r10 = sign_bits9(s10, tx), r01 = sign_bits9(s01, tx), r11 = sign_bits9(s11, tx);
                 if ((r00 | r10 | r01 | r11) != 0u && (r00 & r10 & r01 & r11) != 0x1ffu) {
@@ -146,17 +180,30 @@ __global__ void __launch_bounds__(64) k_mc_classify_tiles(McDesc m, McBuffers mb
                         }
                     }
                     sb = (unsigned long long)(v0 | (v1 << 8) | (t0 << 16) | (t1 << 24)) | ((unsigned long long)t2 << 32);
+                    tot = Triple{planes_v(sb, 0xffu), planes_t(sb, 0xffu), (unsigned)__popc(planes_cut(sb))};
                 }
-                if (sb) {
-                    mb.seg_off[seg] = make_uint2(run.v, run.f);
-                    sb |= (unsigned long long)run.a << 40;
-                    run = run + Triple{planes_v(sb, 0xffu), planes_t(sb, 0xffu), (unsigned)__popc(planes_cut(sb))};
-                }
+            }
+        }
+        s_tot[j][r] = tot;
+        __syncthreads();
+        Triple before = run, all = run;
+#pragma unroll
+        for (int q = 0; q < kClassifyTiles; ++q) {
+            const Triple t = s_tot[q][r];
+            if (q < j) before = before + t;
+            all = all + t;
+        }
+        run = all;
+        if (seg >= 0) {
+            if (sb) {
+                mb.seg_off[seg] = make_uint2(before.v, before.f);
+                sb |= (unsigned long long)before.a << 40;
             }
             mb.seg_bits[seg] = sb;
         }
+        __syncthreads();
     }
-    if (row_valid) mb.row_tot[row_index(m, y, z)] = run;
+    if (row_valid && j == 0) mb.row_tot[row_index(m, y, z)] = run;
 }
 
 // Debug only (isd_get_case_codes): the dense array of case codes, straight from the sign bits.
@@ -172,11 +219,12 @@ __global__ void __launch_bounds__(256) k_debug_cases(McDesc m, const uint32_t* _
 }
 
 // ---- K3 ---------------------------------------------------------------------------------------------------------
-// Exclusive prefix of the row totals in scan order, one pass: blocks take tickets, publish their aggregate, and look back
-// over their predecessors' aggregates / inclusive prefixes (status 1 / 2).  `scan_state` = {ticket, pad, ...} followed by one
-// {status, v, f, a} per block, zeroed before the launch.  totals[0..2] <- grand totals, totals[4..5] <- vertices / triangles
-// before row `ghost_rows`.
-constexpr int kRowScanThreads = 512;
+// Exclusive prefix of the row totals in scan order, one launch of at most kRowScanMaxBlocks blocks: a block takes a ticket,
+// sums its contiguous range of rows, publishes the sum, waits for the sums of the tickets before it (all of them at once, one
+// thread per predecessor — an earlier ticket is always running or done, so the wait cannot deadlock), then scans its range
+// again from that prefix.  `scan_state` = {ticket, pad...} followed by {ready, v, f, a} per block, zeroed before the launch.
+// totals[0..2] <- grand totals, totals[4..5] <- vertices / triangles before row `ghost_rows`.
+constexpr int kRowScanThreads = 512, kRowScanMaxBlocks = 296;
 
 __device__ __forceinline__ Triple warp_inclusive(Triple t, int lane) {
 #pragma unroll
@@ -186,57 +234,65 @@ __device__ __forceinline__ Triple warp_inclusive(Triple t, int lane) {
     }
     return t;
 }
+// exclusive prefix of `mine` over the block (kRowScanThreads threads); *total gets the block sum
+__device__ __forceinline__ Triple block_exclusive(Triple mine, Triple* total, Triple* s_warp) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const Triple inc = warp_inclusive(mine, lane);
+    if (lane == 31) s_warp[w] = inc;
+    __syncthreads();
+    Triple base{0, 0, 0}, sum{0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < kRowScanThreads / 32; ++i) {
+        if (i < w) base = base + s_warp[i];
+        sum = sum + s_warp[i];
+    }
+    __syncthreads();
+    *total = sum;
+    return Triple{base.v + inc.v - mine.v, base.f + inc.f - mine.f, base.a + inc.a - mine.a};
+}
+__device__ __forceinline__ Triple row_total(const McDesc& m, const McBuffers& mb, long long row) {
+    if (row >= m.n_rows) return Triple{0, 0, 0};
+    const int y = 1 + (int)(row % m.NX), z = m.scan_z0 + (int)(row / m.NX);
+    if (!mb.tile_any[((z - m.g.z0) >> 3) * m.g.ty + (y >> 3)]) return Triple{0, 0, 0};      // never written: no work-list tile there
+    return mb.row_tot[row];
+}
 
-__global__ void __launch_bounds__(kRowScanThreads) k_row_scan(McDesc m, McBuffers mb, unsigned* __restrict__ scan_state, unsigned* __restrict__ totals) {
+__global__ void __launch_bounds__(kRowScanThreads) k_row_scan(McDesc m, McBuffers mb, long long rows_per_block, unsigned* __restrict__ scan_state,
+                                                              unsigned* __restrict__ totals) {
     __shared__ Triple s_warp[kRowScanThreads / 32];
-    __shared__ Triple s_prefix;
     __shared__ unsigned s_ticket;
     if (threadIdx.x == 0) s_ticket = atomicAdd(scan_state, 1u);
     __syncthreads();
     const unsigned blk = s_ticket;
-    const long long row = (long long)blk * kRowScanThreads + threadIdx.x;
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    Triple mine{0, 0, 0};
-    if (row < m.n_rows) {
-        const int y = 1 + (int)(row % m.NX), z = m.scan_z0 + (int)(row / m.NX);
-        if (mb.tile_any[((z - m.g.z0) >> 3) * m.g.ty + (y >> 3)]) mine = mb.row_tot[row];
+    const long long first = (long long)blk * rows_per_block, last = first + rows_per_block;      // rows_per_block % kRowScanThreads == 0
+    Triple mine{0, 0, 0}, sum;
+    for (long long r0 = first; r0 < last; r0 += kRowScanThreads) mine = mine + row_total(m, mb, r0 + threadIdx.x);
+    block_exclusive(mine, &sum, s_warp);
+    volatile unsigned* state = scan_state + 4;
+    if (threadIdx.x == 0) {
+        state[blk * 4 + 1] = sum.v; state[blk * 4 + 2] = sum.f; state[blk * 4 + 3] = sum.a;
+        __threadfence();
+        state[blk * 4] = 1u;
     }
-    const Triple inc = warp_inclusive(mine, lane);
-    if (lane == 31) s_warp[w] = inc;
-    __syncthreads();
-    if (w == 0) {
-        const Triple t = (lane < kRowScanThreads / 32) ? s_warp[lane] : Triple{0, 0, 0};
-        const Triple ti = warp_inclusive(t, lane);
-        if (lane < kRowScanThreads / 32) s_warp[lane] = Triple{ti.v - t.v, ti.f - t.f, ti.a - t.a};
-        if (lane == kRowScanThreads / 32 - 1) {
-            // per block: {status, aggregate v f a, inclusive v f a, pad}; status 1 = aggregate ready, 2 = inclusive prefix ready
-            volatile unsigned* mine_state = scan_state + 8 + (size_t)blk * 8;
-            const Triple agg = ti;
-            Triple prefix{0, 0, 0};
-            if (blk > 0) {
-                mine_state[1] = agg.v; mine_state[2] = agg.f; mine_state[3] = agg.a;
-                __threadfence();
-                mine_state[0] = 1u;
-                for (long long j = (long long)blk - 1; j >= 0; --j) {       // an earlier ticket is always running or done
-                    volatile unsigned* sj = scan_state + 8 + (size_t)j * 8;
-                    unsigned st;
-                    while ((st = sj[0]) == 0u) {}
-                    __threadfence();
-                    if (st == 2u) { prefix = prefix + Triple{sj[4], sj[5], sj[6]}; break; }
-                    prefix = prefix + Triple{sj[1], sj[2], sj[3]};
-                }
-            }
-            mine_state[4] = prefix.v + agg.v; mine_state[5] = prefix.f + agg.f; mine_state[6] = prefix.a + agg.a;
-            __threadfence();
-            mine_state[0] = 2u;
-            s_prefix = prefix;
-        }
+    Triple before{0, 0, 0};
+    for (unsigned j = threadIdx.x; j < blk; j += kRowScanThreads) {
+        while (state[j * 4] == 0u) {}
+        __threadfence();
+        before = before + Triple{state[j * 4 + 1], state[j * 4 + 2], state[j * 4 + 3]};
     }
-    __syncthreads();
-    const Triple base = s_prefix + s_warp[w] + Triple{inc.v - mine.v, inc.f - mine.f, inc.a - mine.a};
-    if (row < m.n_rows) mb.row_base[row] = base;
-    if (m.ghost_rows > 0 && row == m.ghost_rows) { totals[4] = base.v; totals[5] = base.f; }
-    if (row == m.n_rows - 1) { totals[0] = base.v + mine.v; totals[1] = base.f + mine.f; totals[2] = base.a + mine.a; }
+    Triple carry;
+    block_exclusive(before, &carry, s_warp);
+    for (long long r0 = first; r0 < last; r0 += kRowScanThreads) {
+        const long long row = r0 + threadIdx.x;
+        const Triple t = row_total(m, mb, row);
+        Triple step;
+        const Triple ex = block_exclusive(t, &step, s_warp);
+        const Triple base = carry + ex;
+        if (row < m.n_rows) mb.row_base[row] = base;
+        if (m.ghost_rows > 0 && row == m.ghost_rows) { totals[4] = base.v; totals[5] = base.f; }
+        if (row == m.n_rows - 1) { totals[0] = base.v + t.v; totals[1] = base.f + t.f; totals[2] = base.a + t.a; }
+        carry = carry + step;
+    }
 }
 
 // One thread per segment of the work list: offsets become absolute, and the cut cubes go, in scan order, into cubes[]
