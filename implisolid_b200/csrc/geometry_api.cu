@@ -110,6 +110,7 @@ struct Context {
         d_noise, d_scal, d_counters, d_upartials;
     bool adjacency_valid = false, fof_valid_ = false;
     float average_edge = 0.f;
+    bool alpha_ticket_zeroed = false;
     long long proj_n = 0;
 
     // HEAD-literal cube table
@@ -463,14 +464,14 @@ void gather_mesh() {
 // OB02 stages
 // ---------------------------------------------------------------------------------------------------------------------
 void exclusive_scan_u32(const unsigned* in, long long n, unsigned* out /* n + 1 */) {
-    const int blocks = (int)((n + kUScanTile - 1) / kUScanTile);
-    g.d_upartials.reserve((size_t)(blocks > 0 ? blocks : 1) * sizeof(unsigned));
-    if (blocks == 0) { ISD_CUDA(cudaMemsetAsync(out, 0, sizeof(unsigned), g.stream)); return; }
-    k_uscan_reduce<<<blocks, kUScanThreads, 0, g.stream>>>(in, n, g.d_upartials.as<unsigned>());
-    ISD_LAUNCH_CHECK();
-    k_uscan_partials<<<1, kUScanThreads, 0, g.stream>>>(g.d_upartials.as<unsigned>(), blocks);
-    ISD_LAUNCH_CHECK();
-    k_uscan_apply<<<blocks, kUScanThreads, 0, g.stream>>>(in, n, g.d_upartials.as<unsigned>(), out);
+    if (n == 0) { ISD_CUDA(cudaMemsetAsync(out, 0, sizeof(unsigned), g.stream)); return; }
+    int blocks = (int)((n + kUScanThreads - 1) / kUScanThreads);
+    if (blocks > kUScanMaxBlocks) blocks = kUScanMaxBlocks;
+    const long long per_block = ((n + blocks - 1) / blocks + kUScanThreads - 1) / kUScanThreads * kUScanThreads;
+    const size_t state_bytes = (4 + 2 * (size_t)kUScanMaxBlocks) * sizeof(unsigned);
+    g.d_upartials.reserve(state_bytes);
+    ISD_CUDA(cudaMemsetAsync(g.d_upartials.ptr, 0, state_bytes, g.stream));
+    k_uscan<<<blocks, kUScanThreads, 0, g.stream>>>(in, n, per_block, g.d_upartials.as<unsigned>(), out);
     ISD_LAUNCH_CHECK();
 }
 
@@ -518,10 +519,11 @@ void vertex_resampling_step(float c) {
     const int nv = (int)g.nv, nf = (int)g.nf;
     if (nf == 0) return;
     build_adjacency(true);
-    compute_centroids();
+    g.d_cen.reserve((size_t)nf * 3 * sizeof(float) + 16);
     g.d_nrm.reserve((size_t)nf * 3 * sizeof(float) + 16);
     g.d_w.reserve((size_t)nf * sizeof(float) + 16);
-    k_unit_gradients<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, g.d_cen.as<float>(), nf, g.d_nrm.as<float>());
+    k_centroid_gradients<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(),
+                                                                   g.d_nrm.as<float>());
     ISD_LAUNCH_CHECK();
     k_face_weights<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.d_cen.as<float>(), g.d_nrm.as<float>(), g.d_fof.as<int>(), nf, c, g.d_w.as<float>());
     ISD_LAUNCH_CHECK();
@@ -531,23 +533,6 @@ void vertex_resampling_step(float c) {
 }
 
 // make_alpha_list (centroids_projection.cpp:144-194)
-std::vector<float> make_alpha_list(float initial_step_size, float min_step_size, float max_dist, int max_iter) {
-    const float unit_of_length = max_dist;
-    std::vector<float> alphas;
-    float step_size = initial_step_size;
-    while (step_size > min_step_size) {
-        step_size = step_size * 0.5;
-        const int total_steps = (int)(std::floor(max_dist / std::abs(step_size) + 0.001));
-        const int max_steps = std::min(max_iter, total_steps);
-        for (int i = 1; i < max_steps + 1; i += 2) {
-            const float alpha = ((float)i) * step_size;
-            alphas.push_back(alpha / unit_of_length);
-            alphas.push_back(-alpha / unit_of_length);
-        }
-    }
-    return alphas;
-}
-
 // boost::random::mt11213b(seed 12) + uniform_01<float>, as make_random_pm1 uses them
 // (vectorised_algorithms/make_random_pm1.hpp:15-28); published Matsumoto-Nishimura parameters.
 struct Mt11213b {
@@ -589,36 +574,30 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     const int nv = (int)g.nv, nf = (int)g.nf;
     if (nf == 0) return;
     ISD_CUDA(cudaEventRecord(g.ev[6], g.stream));
-    g.d_len3.reserve((size_t)nf * 3 * sizeof(float) + 16);
-    g.d_scal.reserve(64);
+    const unsigned prep_blocks = blocks_for(nf, 256);
+    g.d_scal.reserve(sizeof(AlphaList) + (size_t)prep_blocks * sizeof(double) + 64);
     g.d_counters.reserve(sizeof(Ob02Counters));
-    float* d_avg = g.d_scal.as<float>();
-    double* d_acc = reinterpret_cast<double*>(g.d_scal.as<char>() + 16);
-    k_edge_lengths<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_len3.as<float>());
+    g.d_cen.reserve((size_t)nf * 3 * sizeof(float) + 16);
+    AlphaList* d_al = g.d_scal.as<AlphaList>();
+    double* d_partials = reinterpret_cast<double*>(g.d_scal.as<char>() + ((sizeof(AlphaList) + 15) & ~(size_t)15));
+    if (!g.alpha_ticket_zeroed) {      // the last block of k_face_prepare leaves the ticket at zero again
+        ISD_CUDA(cudaMemsetAsync(d_al, 0, sizeof(AlphaList), g.stream));
+        g.alpha_ticket_zeroed = true;
+    }
+    float* d_len3 = nullptr;
+    if (exact_reduce) {
+        g.d_len3.reserve((size_t)nf * 3 * sizeof(float) + 16);
+        d_len3 = g.d_len3.as<float>();
+    }
+    // centroids + mean edge length + alpha list, all on the device (centroids_projection.cpp:1230-1245)
+    k_face_prepare<<<prep_blocks, 256, 0, g.stream>>>(g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(), d_len3, d_partials, d_al);
     ISD_LAUNCH_CHECK();
     if (exact_reduce) {
-        k_sum_serial_float<<<1, 32, 0, g.stream>>>(g.d_len3.as<float>(), (long long)nf * 3, nf, d_avg);
+        k_sum_serial_float<<<1, 32, 0, g.stream>>>(d_len3, (long long)nf * 3, nf, &d_al->avg_edge);
         ISD_LAUNCH_CHECK();
-    } else {
-        ISD_CUDA(cudaMemsetAsync(d_acc, 0, sizeof(double), g.stream));
-        k_sum_double<<<296, 256, 0, g.stream>>>(g.d_len3.as<float>(), (long long)nf * 3, d_acc);
-        ISD_LAUNCH_CHECK();
-        k_finish_average<<<1, 1, 0, g.stream>>>(d_acc, nf, d_avg);
+        k_alpha_from_mean<<<1, 1, 0, g.stream>>>(&d_al->avg_edge, d_al);
         ISD_LAUNCH_CHECK();
     }
-    float* h_avg = reinterpret_cast<float*>(g.h_small.as<char>() + 1024);
-    ISD_CUDA(cudaMemcpyAsync(h_avg, d_avg, sizeof(float), cudaMemcpyDeviceToHost, g.stream));
-    compute_centroids();
-    ISD_CUDA(cudaStreamSynchronize(g.stream));
-    const float average_edge = *h_avg;
-    g.average_edge = average_edge;
-    std::vector<float> alphas = make_alpha_list(average_edge, 0.001f, average_edge, 20);
-    // Direction types 1-6 use the first ten alphas (centroids_projection.cpp:211); below an average edge of 0.004 the
-    // list is shorter than that and the reference slices out of range (undefined behaviour).  Here they use what exists.
-    const int n_alpha_short = alphas.size() < 10 ? (int)alphas.size() : 10;
-    if (alphas.size() > (size_t)kMaxAlphas) alphas.resize(kMaxAlphas);
-    ISD_CUDA(cudaMemcpyToSymbolAsync(c_alpha, alphas.data(), alphas.size() * sizeof(float), 0, cudaMemcpyHostToDevice, g.stream));
-
     g.d_best.reserve((size_t)nf * 3 * sizeof(float) + 16);
     g.d_fc.reserve((size_t)nf * sizeof(float) + 16);
     g.d_state.reserve((size_t)nf + 16);
@@ -627,16 +606,37 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     ISD_CUDA(cudaMemsetAsync(g.d_counters.ptr, 0, sizeof(Ob02Counters), g.stream));
     ProjectArgs a;
     a.verts = g.d_verts.as<float>(); a.faces = g.d_faces.as<int>(); a.cen = g.d_cen.as<float>(); a.noise = nullptr;
-    a.avg_edge = d_avg; a.best = g.d_best.as<float>(); a.fc = g.d_fc.as<float>(); a.state = g.d_state.as<unsigned char>();
+    a.al = d_al; a.best = g.d_best.as<float>(); a.fc = g.d_fc.as<float>(); a.state = g.d_state.as<unsigned char>();
     a.out = g.d_proj.as<float>(); a.nrm_out = g.d_pnrm.as<float>(); a.counters = g.d_counters.as<Ob02Counters>();
-    a.n = nf; a.n_alpha_full = (int)alphas.size(); a.n_alpha_short = n_alpha_short;
+    a.n = nf; a.speculative = 1;
     k_project_search<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a, 0);
     ISD_LAUNCH_CHECK();
+    // Phase B (direction types 2..6) is only needed when phase A left centroids over, which is rare and which only the device
+    // knows: the rest of the step is launched right away and does nothing in that case (the kernels test the counter), so the
+    // host does not have to wait here.
+    k_project_finish<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a);
+    ISD_LAUNCH_CHECK();
+    ISD_CUDA(cudaEventRecord(g.ev[7], g.stream));
+    if (enable_qem) {   // centroids_projection.cpp:1272-1310: the mesh only changes when QEM is on
+        build_adjacency(false);
+        k_qem<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(), g.d_proj.as<float>(),
+                                                        g.d_pnrm.as<float>(), d_al, g.d_counters.as<Ob02Counters>(), g.d_verts.as<float>());
+        ISD_LAUNCH_CHECK();
+    }
+    ISD_CUDA(cudaEventRecord(g.ev[8], g.stream));
     Ob02Counters* hc = reinterpret_cast<Ob02Counters*>(g.h_small.as<char>() + 2048);
+    float* h_avg = reinterpret_cast<float*>(g.h_small.as<char>() + 1024);
     ISD_CUDA(cudaMemcpyAsync(hc, g.d_counters.ptr, sizeof(Ob02Counters), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaMemcpyAsync(h_avg, &d_al->avg_edge, sizeof(float), cudaMemcpyDeviceToHost, g.stream));
     ISD_CUDA(cudaStreamSynchronize(g.stream));
+    float ms = 0;
+    ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[6], g.ev[7]));
+    g.timings[T_PROJECT] += ms;
+    ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[7], g.ev[8]));
+    g.timings[T_QEM] += ms;
     if (hc->c[10] > 0) {
         // rare: direction types 2..6 for the left-overs; type 2 needs make_random_pm1(n, 1e-6), centroid i <- draws 3i..3i+2
+        ISD_CUDA(cudaEventRecord(g.ev[6], g.stream));
         std::vector<float> noise((size_t)nf * 3);
         Mt11213b rng(12);
         const float amplitude = 0.000001f;
@@ -644,32 +644,31 @@ void projection_step(bool enable_qem, bool exact_reduce) {
         g.d_noise.reserve(noise.size() * sizeof(float));
         ISD_CUDA(cudaMemcpyAsync(g.d_noise.ptr, noise.data(), noise.size() * sizeof(float), cudaMemcpyHostToDevice, g.stream));
         a.noise = g.d_noise.as<float>();
+        a.speculative = 0;
         k_project_search<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a, 1);
         ISD_LAUNCH_CHECK();
-        ISD_CUDA(cudaStreamSynchronize(g.stream));   // noise lives on the host stack frame until the copy is done
-    }
-    k_project_finish<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a);
-    ISD_LAUNCH_CHECK();
-    ISD_CUDA(cudaMemcpyAsync(hc, g.d_counters.ptr, sizeof(Ob02Counters), cudaMemcpyDeviceToHost, g.stream));
-    g.proj_n = nf;
-    ISD_CUDA(cudaEventRecord(g.ev[7], g.stream));
-    if (enable_qem) {   // centroids_projection.cpp:1272-1310: the mesh only changes when QEM is on
-        build_adjacency(false);
-        k_qem<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(), g.d_proj.as<float>(),
-                                                        g.d_pnrm.as<float>(), d_avg, g.d_verts.as<float>());
+        k_project_finish<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a);
         ISD_LAUNCH_CHECK();
+        ISD_CUDA(cudaEventRecord(g.ev[7], g.stream));
+        if (enable_qem) {
+            k_qem<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(), g.d_proj.as<float>(),
+                                                            g.d_pnrm.as<float>(), d_al, nullptr, g.d_verts.as<float>());
+            ISD_LAUNCH_CHECK();
+        }
+        ISD_CUDA(cudaEventRecord(g.ev[8], g.stream));
+        ISD_CUDA(cudaMemcpyAsync(hc, g.d_counters.ptr, sizeof(Ob02Counters), cudaMemcpyDeviceToHost, g.stream));
+        ISD_CUDA(cudaStreamSynchronize(g.stream));   // also: `noise` lives on this stack frame until the copy is done
+        ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[6], g.ev[7]));
+        g.timings[T_PROJECT] += ms;
+        ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[7], g.ev[8]));
+        g.timings[T_QEM] += ms;
     }
-    ISD_CUDA(cudaEventRecord(g.ev[8], g.stream));
-    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    g.average_edge = *h_avg;
+    g.proj_n = nf;
     for (int i = 0; i < 7; ++i) g.counters[3 + i] += (int64_t)hc->c[i];
     g.counters[10] += (int64_t)hc->c[7];
     g.counters[11] += (int64_t)hc->c[8];
     g.counters[12] += (int64_t)hc->c[9];
-    float ms = 0;
-    ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[6], g.ev[7]));
-    g.timings[T_PROJECT] += ms;
-    ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[7], g.ev[8]));
-    g.timings[T_QEM] += ms;
 }
 
 // faces do not change after marching cubes: start their device->host copy now, on the side stream
@@ -725,23 +724,29 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     const bool any_ob02 = s.overall_repeats > 0 && (s.vresampl_iters > 0 || s.projection_enabled);
     if (any_ob02 && g.world > 1 && !g.emulate) gather_mesh();      // OB02 runs on the stitched mesh, replicated
     if (copy_out && any_ob02) start_faces_copy();
+    bool resample_timed = false;
     for (int overall_iter = 0; overall_iter < s.overall_repeats; ++overall_iter) {
         if (s.vresampl_iters > 0) {
             ISD_CUDA(cudaEventRecord(g.ev[4], g.stream));
             for (int i = 0; i < s.vresampl_iters; ++i) vertex_resampling_step(s.vresampl_c);   // polygonize_step_1
             ISD_CUDA(cudaEventRecord(g.ev[5], g.stream));
-            ISD_CUDA(cudaStreamSynchronize(g.stream));
+            resample_timed = true;
+        }
+        if (s.projection_enabled) projection_step(s.qem_enabled, s.exact_reduce != 0);     // polygonize_step_2
+        if (resample_timed && (s.projection_enabled || s.overall_repeats > 1)) {          // events are reused by the next repeat
+            if (!s.projection_enabled) ISD_CUDA(cudaStreamSynchronize(g.stream));
             float ms = 0;
             ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[4], g.ev[5]));
             g.timings[T_RESAMPLE] += ms;
+            resample_timed = false;
         }
-        if (s.projection_enabled) projection_step(s.qem_enabled, s.exact_reduce != 0);     // polygonize_step_2
         const bool is_last = overall_iter == s.overall_repeats - 1;
         if (s.subdiv_enabled && (s.overall_repeats <= 1 || is_last) && s.verbose)
             fprintf(stderr, "implisolid_b200: subdivision (polygonize_step_3) is outside this library's scope; skipped\n");
     }
     ISD_CUDA(cudaStreamSynchronize(g.stream));
     float ms = 0;
+    if (resample_timed) { ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[4], g.ev[5])); g.timings[T_RESAMPLE] += ms; }
     ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[0], g.ev[1])); g.timings[T_FIELD] = ms;
     ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[1], g.ev[2])); g.timings[T_CLASSIFY] = ms;
     ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[2], g.ev[3])); g.timings[T_EMIT] = ms;

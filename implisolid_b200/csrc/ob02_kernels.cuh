@@ -21,7 +21,33 @@ constexpr float kMinGradientLen = 0.000001f;                 // configs.hpp:57
 constexpr int kBisectionMaxIter = 100;                       // ours: the reference has no cap (bisection.hpp:204,415-437)
 constexpr int kMaxAlphas = 512;
 
-__constant__ float c_alpha[kMaxAlphas];      // make_alpha_list result (host), centroids_projection.cpp:144-194
+// make_alpha_list (centroids_projection.cpp:144-194), built on the device from the mean edge length: the host never has to
+// wait for that scalar.  Direction types 1-6 use the first ten alphas (:211); below a mean edge of 0.004 the list is shorter
+// than that and the reference slices out of range (undefined behaviour) — here they use what exists.
+struct AlphaList {
+    float alpha[kMaxAlphas];
+    int n_full, n_short;
+    float avg_edge;
+    unsigned ticket;          // last-block-done counter of k_face_prepare
+};
+__device__ inline void make_alpha_list(float initial_step_size, float min_step_size, float max_dist, int max_iter, AlphaList* out) {
+    const float unit_of_length = max_dist;
+    int n = 0;
+    float step_size = initial_step_size;
+    while (step_size > min_step_size) {
+        step_size = (float)(step_size * 0.5);
+        const int total_steps = (int)(floor((double)(max_dist / fabsf(step_size)) + 0.001));
+        const int max_steps = min(max_iter, total_steps);
+        for (int i = 1; i < max_steps + 1; i += 2) {
+            const float alpha = ((float)i) * step_size;
+            if (n + 1 < kMaxAlphas) { out->alpha[n] = alpha / unit_of_length; out->alpha[n + 1] = -alpha / unit_of_length; }
+            n += 2;
+        }
+    }
+    if (n > kMaxAlphas) n = kMaxAlphas;
+    out->n_full = n;
+    out->n_short = n < 10 ? n : 10;
+}
 
 // counters: [0..6] centroids resolved by direction type, [7] failed, [8] bisection capped, [9] bisected,
 // [10] centroids still unresolved after phase A
@@ -66,41 +92,42 @@ __device__ __forceinline__ unsigned block_exclusive_u32(unsigned mine, unsigned*
     *total = sum;
     return base + inc - mine;
 }
-__global__ void __launch_bounds__(kUScanThreads) k_uscan_reduce(const unsigned* __restrict__ in, long long n, unsigned* __restrict__ partials) {
-    const long long first = ((long long)blockIdx.x * kUScanThreads + threadIdx.x) * kUScanItems;
-    unsigned s = 0;
-#pragma unroll
-    for (int i = 0; i < kUScanItems; ++i)
-        if (first + i < n) s += in[first + i];
-    unsigned total;
-    block_exclusive_u32(s, &total);
-    if (threadIdx.x == 0) partials[blockIdx.x] = total;
-}
-__global__ void __launch_bounds__(kUScanThreads) k_uscan_partials(unsigned* __restrict__ partials, int nblocks) {
-    unsigned carry = 0;
-    for (int base = 0; base < nblocks; base += kUScanThreads) {
-        const int i = base + threadIdx.x;
-        const unsigned mine = (i < nblocks) ? partials[i] : 0u;
-        unsigned total;
-        const unsigned ex = block_exclusive_u32(mine, &total);
-        if (i < nblocks) partials[i] = carry + ex;
-        carry += total;
+// out[i] = exclusive prefix of in[0..n), out[n] = total; one launch of at most kUScanMaxBlocks blocks over contiguous ranges
+// (same scheme as k_row_scan, mc_kernels.cuh): ticket, range sum, publish, wait for the earlier tickets, scan the range.
+// `state` = {ticket, pad, pad, pad} + {ready, sum} per block, zeroed before the launch.
+constexpr int kUScanMaxBlocks = 296;
+__global__ void __launch_bounds__(kUScanThreads) k_uscan(const unsigned* __restrict__ in, long long n, long long per_block,
+                                                       unsigned* __restrict__ state, unsigned* __restrict__ out) {
+    __shared__ unsigned s_ticket;
+    if (threadIdx.x == 0) s_ticket = atomicAdd(state, 1u);
+    __syncthreads();
+    const unsigned blk = s_ticket;
+    const long long first = (long long)blk * per_block, last = first + per_block;      // per_block % kUScanThreads == 0
+    unsigned mine = 0, sum;
+    for (long long i = first + threadIdx.x; i < last; i += kUScanThreads) mine += (i < n) ? in[i] : 0u;
+    block_exclusive_u32(mine, &sum);
+    volatile unsigned* st = state + 4;
+    if (threadIdx.x == 0) {
+        st[blk * 2 + 1] = sum;
+        __threadfence();
+        st[blk * 2] = 1u;
     }
-}
-// out[i] = exclusive prefix; out[n] = total (out has n + 1 entries)
-__global__ void __launch_bounds__(kUScanThreads) k_uscan_apply(const unsigned* __restrict__ in, long long n, const unsigned* __restrict__ partials,
-                                                             unsigned* __restrict__ out) {
-    const long long first = ((long long)blockIdx.x * kUScanThreads + threadIdx.x) * kUScanItems;
-    unsigned v[kUScanItems], s = 0;
-#pragma unroll
-    for (int i = 0; i < kUScanItems; ++i) { v[i] = (first + i < n) ? in[first + i] : 0u; s += v[i]; }
-    unsigned total;
-    unsigned run = partials[blockIdx.x] + block_exclusive_u32(s, &total);
-#pragma unroll
-    for (int i = 0; i < kUScanItems; ++i) {
-        if (first + i < n) out[first + i] = run;
-        run += v[i];
-        if (first + i == n - 1) out[n] = run;
+    unsigned before = 0;
+    for (unsigned j = threadIdx.x; j < blk; j += kUScanThreads) {
+        while (st[j * 2] == 0u) {}
+        __threadfence();
+        before += st[j * 2 + 1];
+    }
+    unsigned carry;
+    block_exclusive_u32(before, &carry);
+    for (long long i0 = first; i0 < last; i0 += kUScanThreads) {
+        const long long i = i0 + threadIdx.x;
+        const unsigned v = (i < n) ? in[i] : 0u;
+        unsigned step;
+        const unsigned ex = block_exclusive_u32(v, &step);
+        if (i < n) out[i] = carry + ex;
+        if (i == n - 1) out[n] = carry + ex + v;
+        carry += step;
     }
 }
 
@@ -168,6 +195,23 @@ __global__ void __launch_bounds__(128) k_centroids(const float* __restrict__ ver
     const int f0 = faces[f * 3], f1 = faces[f * 3 + 1], f2 = faces[f * 3 + 2];
 #pragma unroll
     for (int d = 0; d < 3; ++d) cen[f * 3 + d] = (verts[f0 * 3 + d] + verts[f1 * 3 + d] + verts[f2 * 3 + d]) / 3.0f;
+}
+// both at once (vertex resampling: the gradient is taken at the centroid just stored, same bits)
+__global__ void __launch_bounds__(128) k_centroid_gradients(SdfGridView sdf, const float* __restrict__ verts, const int* __restrict__ faces, int nf,
+                                                            float* __restrict__ cen, float* __restrict__ nrm) {
+    const int f = blockIdx.x * 128 + threadIdx.x;
+    if (f >= nf) return;
+    const int f0 = faces[f * 3], f1 = faces[f * 3 + 1], f2 = faces[f * 3 + 2];
+    float c[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        c[d] = (verts[f0 * 3 + d] + verts[f1 * 3 + d] + verts[f2 * 3 + d]) / 3.0f;
+        cen[f * 3 + d] = c[d];
+    }
+    float fv, g0, g1, g2;
+    eval_value_gradient(ConstProgram(), sdf, c[0], c[1], c[2], fv, g0, g1, g2);
+    const float norm = norm2f(g0, g1, g2);
+    nrm[f * 3] = g0 / norm; nrm[f * 3 + 1] = g1 / norm; nrm[f * 3 + 2] = g2 / norm;
 }
 __global__ void __launch_bounds__(128) k_unit_gradients(SdfGridView sdf, const float* __restrict__ pts, int n, float* __restrict__ nrm) {
     const int i = blockIdx.x * 128 + threadIdx.x;
@@ -259,12 +303,68 @@ __global__ void __launch_bounds__(256) k_sum_double(const float* __restrict__ v,
 }
 __global__ void k_finish_average(const double* __restrict__ acc, int nf, float* __restrict__ out) { *out = (float)(*acc / (3. * nf)); }
 
+// Projection prologue in one launch: centroids, the three edge lengths per face (compute_average_edge_length,
+// centroids_projection.cpp:70-82) summed in double — per block, then by the last block to finish in block order, so the
+// result does not depend on scheduling — the mean edge, and the alpha list.  `len3` (optional) keeps the lengths for the
+// reference-order serial float sum (exact_reduce), which then overwrites the mean and rebuilds the list.
+__global__ void __launch_bounds__(256) k_face_prepare(const float* __restrict__ verts, const int* __restrict__ faces, int nf, float* __restrict__ cen,
+                                                      float* __restrict__ len3, double* __restrict__ partials, AlphaList* __restrict__ al) {
+    __shared__ double s[8];
+    __shared__ bool s_last;
+    const int j = blockIdx.x * 256 + threadIdx.x;
+    double t = 0.0;
+    if (j < nf) {
+        const int f0 = faces[j * 3], f1 = faces[j * 3 + 1], f2 = faces[j * 3 + 2];
+        const float* a = verts + f0 * 3; const float* b = verts + f1 * 3; const float* c = verts + f2 * 3;
+#pragma unroll
+        for (int d = 0; d < 3; ++d) cen[j * 3 + d] = (a[d] + b[d] + c[d]) / 3.0f;
+        const float l0 = norm2f(a[0] - b[0], a[1] - b[1], a[2] - b[2]);
+        const float l1 = norm2f(a[0] - c[0], a[1] - c[1], a[2] - c[2]);
+        const float l2 = norm2f(c[0] - b[0], c[1] - b[1], c[2] - b[2]);
+        if (len3 != nullptr) { len3[j * 3] = l0; len3[j * 3 + 1] = l1; len3[j * 3 + 2] = l2; }
+        t = (double)l0 + (double)l1 + (double)l2;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) t += __shfl_xor_sync(0xffffffffu, t, d);
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = t;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double b = 0.0;
+        for (int i = 0; i < 8; ++i) b += s[i];
+        partials[blockIdx.x] = b;
+        __threadfence();
+        s_last = atomicAdd(&al->ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    double acc = 0.0;
+    for (unsigned i = threadIdx.x; i < gridDim.x; i += 256) acc += ((volatile double*)partials)[i];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double b = 0.0;
+        for (int i = 0; i < 8; ++i) b += s[i];
+        const float avg = (float)(b / (3. * nf));
+        al->avg_edge = avg;
+        make_alpha_list(avg, 0.001f, avg, 20, al);
+        al->ticket = 0u;
+    }
+}
+// exact_reduce: the alpha list again, from the serial float mean
+__global__ void k_alpha_from_mean(const float* __restrict__ mean, AlphaList* __restrict__ al) {
+    al->avg_edge = *mean;
+    make_alpha_list(*mean, 0.001f, *mean, 20, al);
+}
+
 struct ProjectArgs {
     const float* verts;
     const int* faces;
     const float* cen;        // centroids (input)
     const float* noise;      // make_random_pm1(n, 1e-6) for direction type 2 (phase B only)
-    const float* avg_edge;   // device scalar
+    const AlphaList* al;     // mean edge length + alpha list (device)
     float* best;             // per centroid: candidate on the other side of the surface
     float* fc;               // f(centroid)
     unsigned char* state;    // bit 0: already success; bit 1: still searching after phase A
@@ -272,8 +372,7 @@ struct ProjectArgs {
     float* nrm_out;          // unit gradient at projected centroids
     Ob02Counters* counters;
     int n;
-    int n_alpha_full;
-    int n_alpha_short;       // min(10, n_alpha_full): alphas tried by direction types 1-6
+    int speculative;         // k_project_finish: do nothing if phase A left centroids over (the host then runs phase B and calls again)
 };
 
 // produce_facet_normals(force_normalisation = true)  implicit_vectorised_algorithms.hpp:52-133
@@ -298,9 +397,9 @@ __device__ __forceinline__ void facet_normal(const float* __restrict__ verts, co
 
 // tries the alphas of one direction; returns true (and the trial point) at the first sign change  (:604-892)
 __device__ __forceinline__ bool try_direction(const SdfGridView& sdf, float cx, float cy, float cz, float dx, float dy, float dz, float edge,
-                                              int n_alpha, float s_c, float& bx, float& by, float& bz) {
+                                              const float* __restrict__ alphas, int n_alpha, float s_c, float& bx, float& by, float& bz) {
     for (int ai = 0; ai < n_alpha; ++ai) {
-        const float c = edge * c_alpha[ai];                 // (length_factor * alpha) * 4.0 / 4.0
+        const float c = edge * __ldg(alphas + ai);          // (length_factor * alpha) * 4.0 / 4.0
         const float x = cx + c * dx, y = cy + c * dy, z = cz + c * dz;
         const float f = eval_f(sdf, x, y, z);
         if (sign_tol(f) * s_c <= 0.0f) { bx = x; by = y; bz = z; return true; }
@@ -314,7 +413,9 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
     const int i = blockIdx.x * 128 + threadIdx.x;
     if (i >= a.n) return;
     const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
-    const float edge = *a.avg_edge;
+    const float edge = a.al->avg_edge;
+    const float* alphas = a.al->alpha;
+    const int n_alpha_full = a.al->n_full, n_alpha_short = a.al->n_short;
     float bx = -10.0f, by = -10.0f, bz = -10.0f;
     bool ok = false;
     int type = -1;
@@ -332,12 +433,12 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
         s_c = sign_tol(fc);
         if (s_c < 0.0f) { g0 = -g0; g1 = -g1; g2 = -g2; }
         const float d0 = -g0 * s_c, d1 = -g1 * s_c, d2 = -g2 * s_c;
-        ok = try_direction(sdf, cx, cy, cz, d0, d1, d2, edge, a.n_alpha_full, s_c, bx, by, bz);
+        ok = try_direction(sdf, cx, cy, cz, d0, d1, d2, edge, alphas, n_alpha_full, s_c, bx, by, bz);
         type = 0;
         if (!ok) {
             float nx, ny, nz;
             facet_normal(a.verts, a.faces, i, nx, ny, nz);
-            ok = try_direction(sdf, cx, cy, cz, nx, ny, nz, edge, a.n_alpha_short, s_c, bx, by, bz);
+            ok = try_direction(sdf, cx, cy, cz, nx, ny, nz, edge, alphas, n_alpha_short, s_c, bx, by, bz);
             type = 1;
         }
         count_if(!ok, &a.counters->c[10]);
@@ -353,7 +454,7 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
             const float n = norm2f(zx, zy, zz);
             zx = zx / n; zy = zy / n; zz = zz / n;
         }
-        ok = try_direction(sdf, cx, cy, cz, zx, zy, zz, edge, a.n_alpha_short, s_c, bx, by, bz);
+        ok = try_direction(sdf, cx, cy, cz, zx, zy, zz, edge, alphas, n_alpha_short, s_c, bx, by, bz);
         type = 2;
         if (!ok) {   // type 3: facet normal x previous direction, normalise_inplace
             float wx = ny * zz - nz * zy, wy = nz * zx - nx * zz, wz = nx * zy - ny * zx;
@@ -361,11 +462,11 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
             n = (n < kMinGradientLen) ? 1.0f : n;
             const float factor = 1.0f / n;
             wx = wx * factor; wy = wy * factor; wz = wz * factor;
-            ok = try_direction(sdf, cx, cy, cz, wx, wy, wz, edge, a.n_alpha_short, s_c, bx, by, bz);
+            ok = try_direction(sdf, cx, cy, cz, wx, wy, wz, edge, alphas, n_alpha_short, s_c, bx, by, bz);
             type = 3;
         }
         for (int dim = 0; dim < 3 && !ok; ++dim) {
-            ok = try_direction(sdf, cx, cy, cz, dim == 0 ? 1.0f : 0.0f, dim == 1 ? 1.0f : 0.0f, dim == 2 ? 1.0f : 0.0f, edge, a.n_alpha_short, s_c, bx, by, bz);
+            ok = try_direction(sdf, cx, cy, cz, dim == 0 ? 1.0f : 0.0f, dim == 1 ? 1.0f : 0.0f, dim == 2 ? 1.0f : 0.0f, edge, alphas, n_alpha_short, s_c, bx, by, bz);
             type = 4 + dim;
         }
     }
@@ -384,6 +485,7 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
 __global__ void __launch_bounds__(128) k_project_finish(SdfGridView sdf, ProjectArgs a) {
     const int i = blockIdx.x * 128 + threadIdx.x;
     if (i >= a.n) return;
+    if (a.speculative && a.counters->c[10] != 0ull) return;
     const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
     const bool already = (a.state[i] & 1) != 0;
     float bx, by, bz;
@@ -477,10 +579,12 @@ __device__ __forceinline__ void sym_eig3(const float (&Ain)[3][3], float (&w)[3]
 
 // vertex_apply_qem + get_A_b (qem.hpp:256-599)
 __global__ void __launch_bounds__(128) k_qem(int nv, const unsigned* __restrict__ offsets, const int* __restrict__ items, const float* __restrict__ cen,
-                                             const float* __restrict__ nrm, const float* __restrict__ avg_edge, float* __restrict__ verts) {
+                                             const float* __restrict__ nrm, const AlphaList* __restrict__ al,
+                                             const Ob02Counters* __restrict__ skip_if_leftovers, float* __restrict__ verts) {
     const int vi = blockIdx.x * 128 + threadIdx.x;
     if (vi >= nv) return;
-    const float maxd = *avg_edge;
+    if (skip_if_leftovers != nullptr && skip_if_leftovers->c[10] != 0ull) return;      // speculative launch, see projection_step
+    const float maxd = al->avg_edge;
     const float o0 = verts[vi * 3], o1 = verts[vi * 3 + 1], o2 = verts[vi * 3 + 2];
     float A[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}}, b[3] = {0, 0, 0};
     for (unsigned k = offsets[vi], e = offsets[vi + 1]; k < e; ++k) {
