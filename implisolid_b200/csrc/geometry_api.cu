@@ -246,7 +246,7 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     const size_t field_bytes = (size_t)gd.plane * gd.nz * sizeof(float);
     g.d_field.reserve(field_bytes);
     const long long n_rows = m.n_rows;
-    int scan_blocks = (int)((n_rows + kRowScanThreads - 1) / kRowScanThreads);
+    int scan_blocks = (int)((n_rows + kRowScanThreads * 2 - 1) / (kRowScanThreads * 2));      // >= 2 rounds per block: fewer blocks to wait for
     if (scan_blocks > kRowScanMaxBlocks) scan_blocks = kRowScanMaxBlocks;
     const long long rows_per_block = ((n_rows + scan_blocks - 1) / scan_blocks + kRowScanThreads - 1) / kRowScanThreads * kRowScanThreads;
     g.d_row_tot.reserve((size_t)n_rows * sizeof(Triple));
@@ -465,7 +465,7 @@ void gather_mesh() {
 // ---------------------------------------------------------------------------------------------------------------------
 void exclusive_scan_u32(const unsigned* in, long long n, unsigned* out /* n + 1 */) {
     if (n == 0) { ISD_CUDA(cudaMemsetAsync(out, 0, sizeof(unsigned), g.stream)); return; }
-    int blocks = (int)((n + kUScanThreads - 1) / kUScanThreads);
+    int blocks = (int)((n + kUScanThreads * 4 - 1) / (kUScanThreads * 4));      // >= 4 rounds per block: fewer blocks to wait for
     if (blocks > kUScanMaxBlocks) blocks = kUScanMaxBlocks;
     const long long per_block = ((n + blocks - 1) / blocks + kUScanThreads - 1) / kUScanThreads * kUScanThreads;
     const size_t state_bytes = (4 + 2 * (size_t)kUScanMaxBlocks) * sizeof(unsigned);

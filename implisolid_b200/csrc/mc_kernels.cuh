@@ -275,11 +275,10 @@ __global__ void __launch_bounds__(kRowScanThreads) k_row_scan(McDesc m, McBuffer
         state[blk * 4] = 1u;
     }
     Triple before{0, 0, 0};
-    for (unsigned j = threadIdx.x; j < blk; j += kRowScanThreads) {
+    for (unsigned j = threadIdx.x; j < blk; j += kRowScanThreads)
         while (state[j * 4] == 0u) {}
-        __threadfence();
-        before = before + Triple{state[j * 4 + 1], state[j * 4 + 2], state[j * 4 + 3]};
-    }
+    __threadfence();      // one fence after all the flags have been seen, then the sums
+    for (unsigned j = threadIdx.x; j < blk; j += kRowScanThreads) before = before + Triple{state[j * 4 + 1], state[j * 4 + 2], state[j * 4 + 3]};
     Triple carry;
     block_exclusive(before, &carry, s_warp);
     for (long long r0 = first; r0 < last; r0 += kRowScanThreads) {

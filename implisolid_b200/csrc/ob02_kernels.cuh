@@ -113,11 +113,10 @@ __global__ void __launch_bounds__(kUScanThreads) k_uscan(const unsigned* __restr
         st[blk * 2] = 1u;
     }
     unsigned before = 0;
-    for (unsigned j = threadIdx.x; j < blk; j += kUScanThreads) {
+    for (unsigned j = threadIdx.x; j < blk; j += kUScanThreads)
         while (st[j * 2] == 0u) {}
-        __threadfence();
-        before += st[j * 2 + 1];
-    }
+    __threadfence();      // one fence after all the flags have been seen, then the sums
+    for (unsigned j = threadIdx.x; j < blk; j += kUScanThreads) before += st[j * 2 + 1];
     unsigned carry;
     block_exclusive_u32(before, &carry);
     for (long long i0 = first; i0 < last; i0 += kUScanThreads) {
@@ -150,7 +149,22 @@ __global__ void k_umbrella_sort(int nv, const unsigned* __restrict__ offsets, in
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= nv) return;
     const unsigned b = offsets[v], e = offsets[v + 1];
-    for (unsigned i = b + 1; i < e; ++i) {          // insertion sort; umbrellas hold ~6 faces
+    if (e - b <= 16u) {                             // umbrellas hold ~6 faces: sort them in registers (rank by counting; ties cannot
+        int key[16];                                // be told apart, a face listed twice is twice the same value)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) key[i] = (b + i < e) ? items[b + i] : 0x7fffffff;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            if (b + i < e) {
+                int rank = 0;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) rank += (key[j] < key[i] || (key[j] == key[i] && j < i)) ? 1 : 0;
+                items[b + rank] = key[i];
+            }
+        }
+        return;
+    }
+    for (unsigned i = b + 1; i < e; ++i) {          // insertion sort for the rare big umbrella
         const int key = items[i];
         unsigned j = i;
         while (j > b && items[j - 1] > key) { items[j] = items[j - 1]; --j; }
