@@ -210,16 +210,17 @@ def main():
                 stage_sum[k] = stage_sum.get(k, 0.0) + v
             launches += lib.last_counters()["launches"]
     barrier()
-    t_end = time.perf_counter() + 2.0
-    while len(sampler.rows) < 4 and time.perf_counter() < t_end:      # the timed region is ~25 ms: keep the same load up until
-        step_device()                                                  # nvidia-smi (100 ms period) has a few samples
-    barrier()
-    clocks = sampler.stop()
     ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_per_step = float(t.item()) / args.steps
+    # the timed region is a few ms: keep the same load up for ~0.5 s so that nvidia-smi (100 ms period) has samples of it.
+    # The number of extra steps comes from the reduced time, so every rank runs the same number of collectives.
+    for _ in range(int(min(5000, max(1, math.ceil(500.0 / max(ms_per_step, 0.05)))))):
+        step_device()
+    barrier()
+    clocks = sampler.stop()
     voxels = float(R) ** 3
     value = voxels / (ms_per_step * 1e-3)
     counters = lib.last_counters()

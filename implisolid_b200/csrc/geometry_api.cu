@@ -94,6 +94,7 @@ struct Context {
     long long nv = 0, nf = 0;     // mesh held on this GPU (a slab's part in sharded mode until gathered)
     bool host_valid = false;      // pinned mirrors hold the current mesh
     DeviceBuffer d_verts, d_faces;
+    long long local_voff = 0, local_foff = 0;   // sharded, before the gather: the slab sits at its global offset inside buffers sized for the whole mesh
     PinnedBuffer h_verts, h_faces;
 
     // field + marching cubes scratch
@@ -407,8 +408,11 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         fprintf(stderr, "implisolid_b200: mesh too large for 32-bit indices (%lld vertices, %lld faces)\n", gnv, gnf);
         abort();
     }
-    g.d_verts.reserve((size_t)(nv > 0 ? nv : 1) * 3 * sizeof(float));
-    g.d_faces.reserve((size_t)(nf > 0 ? nf : 1) * 3 * sizeof(int));
+    const bool in_place = g.world > 1 && !g.emulate;      // room for every slab: the gather is then a set of in-place broadcasts
+    g.local_voff = in_place ? voff : 0;
+    g.local_foff = in_place ? foff : 0;
+    g.d_verts.reserve((size_t)((in_place ? gnv : nv) > 0 ? (in_place ? gnv : nv) : 1) * 3 * sizeof(float));
+    g.d_faces.reserve((size_t)((in_place ? gnf : nf) > 0 ? (in_place ? gnf : nf) : 1) * 3 * sizeof(int));
     if (n_cubes > 0) {   // K4
         EmitArgs ea;
         ea.vbase = voff - ghost_v; ea.fbase = foff - ghost_f;
@@ -416,8 +420,8 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         unsigned blocks = (n_cubes + kEmitThreads - 1) / kEmitThreads;
         if (blocks > (unsigned)g.sm_count * 16u) blocks = (unsigned)g.sm_count * 16u;
         k_mc_emit<<<blocks, kEmitThreads, 0, g.stream>>>(m, mb, ea, g.d_field.as<float>(), g.d_signs.as<uint32_t>(),
-                                                         g.d_cubes.as<unsigned long long>(), g.d_totals.as<unsigned>() + 2, g.d_verts.as<float>(),
-                                                         g.d_faces.as<int>());
+                                                         g.d_cubes.as<unsigned long long>(), g.d_totals.as<unsigned>() + 2,
+                                                         g.d_verts.as<float>() + g.local_voff * 3, g.d_faces.as<int>() + g.local_foff * 3);
         ISD_LAUNCH_CHECK();
     }
     ISD_CUDA(cudaEventRecord(g.ev[3], g.stream));
@@ -438,23 +442,19 @@ void gather_mesh() {
     if (g.world == 1 || g.gathered || g.emulate) return;
     int64_t* hs = reinterpret_cast<int64_t*>(g.h_small.as<char>() + 256);
     const long long gnv = g.slab[6], gnf = g.slab[7];
-    DeviceBuffer all_v, all_f;
-    all_v.reserve((size_t)(gnv > 0 ? gnv : 1) * 3 * sizeof(float));
-    all_f.reserve((size_t)(gnf > 0 ? gnf : 1) * 3 * sizeof(int));
     g.nccl.check(g.nccl.GroupStart(), "ncclGroupStart");
     long long vo = 0, fo = 0;
-    for (int r = 0; r < g.world; ++r) {
+    for (int r = 0; r < g.world; ++r) {      // in place: every rank's slab already sits at its global offset
         const long long rv = hs[2 + 2 * r], rf = hs[3 + 2 * r];
-        if (rv > 0)
-            g.nccl.check(g.nccl.Broadcast(g.d_verts.ptr, all_v.as<float>() + vo * 3, (size_t)rv * 3, kNcclFloat32, r, g.comm, g.stream), "ncclBroadcast");
-        if (rf > 0)
-            g.nccl.check(g.nccl.Broadcast(g.d_faces.ptr, all_f.as<int>() + fo * 3, (size_t)rf * 3, kNcclInt32, r, g.comm, g.stream), "ncclBroadcast");
+        float* pv = g.d_verts.as<float>() + vo * 3;
+        int* pf = g.d_faces.as<int>() + fo * 3;
+        if (rv > 0) g.nccl.check(g.nccl.Broadcast(pv, pv, (size_t)rv * 3, kNcclFloat32, r, g.comm, g.stream), "ncclBroadcast");
+        if (rf > 0) g.nccl.check(g.nccl.Broadcast(pf, pf, (size_t)rf * 3, kNcclInt32, r, g.comm, g.stream), "ncclBroadcast");
         vo += rv; fo += rf;
     }
     g.nccl.check(g.nccl.GroupEnd(), "ncclGroupEnd");
-    ISD_CUDA(cudaStreamSynchronize(g.stream));
-    g.d_verts.release(); g.d_faces.release();
-    g.d_verts = all_v; g.d_faces = all_f;
+    if (getenv("ISD_GATHER_SYNC")) ISD_CUDA(cudaStreamSynchronize(g.stream));
+    g.local_voff = 0; g.local_foff = 0;
     g.nv = gnv; g.nf = gnf;
     g.gathered = true;
     g.host_valid = false;
@@ -677,7 +677,7 @@ void start_faces_copy() {
     g.h_faces.reserve((size_t)g.nf * 3 * sizeof(int));
     ISD_CUDA(cudaEventRecord(g.ev_faces, g.stream));
     ISD_CUDA(cudaStreamWaitEvent(g.copy_stream, g.ev_faces, 0));
-    ISD_CUDA(cudaMemcpyAsync(g.h_faces.ptr, g.d_faces.ptr, (size_t)g.nf * 3 * sizeof(int), cudaMemcpyDeviceToHost, g.copy_stream));
+    ISD_CUDA(cudaMemcpyAsync(g.h_faces.ptr, g.d_faces.as<int>() + g.local_foff * 3, (size_t)g.nf * 3 * sizeof(int), cudaMemcpyDeviceToHost, g.copy_stream));
     g.faces_in_flight = true;
 }
 
@@ -686,9 +686,9 @@ void copy_mesh_to_host() {
     g.h_verts.reserve((size_t)(g.nv > 0 ? g.nv : 1) * 3 * sizeof(float));
     g.h_faces.reserve((size_t)(g.nf > 0 ? g.nf : 1) * 3 * sizeof(int));
     ISD_CUDA(cudaEventRecord(g.ev[9], g.stream));
-    if (g.nv) ISD_CUDA(cudaMemcpyAsync(g.h_verts.ptr, g.d_verts.ptr, (size_t)g.nv * 3 * sizeof(float), cudaMemcpyDeviceToHost, g.stream));
+    if (g.nv) ISD_CUDA(cudaMemcpyAsync(g.h_verts.ptr, g.d_verts.as<float>() + g.local_voff * 3, (size_t)g.nv * 3 * sizeof(float), cudaMemcpyDeviceToHost, g.stream));
     if (g.nf && !g.faces_in_flight)
-        ISD_CUDA(cudaMemcpyAsync(g.h_faces.ptr, g.d_faces.ptr, (size_t)g.nf * 3 * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
+        ISD_CUDA(cudaMemcpyAsync(g.h_faces.ptr, g.d_faces.as<int>() + g.local_foff * 3, (size_t)g.nf * 3 * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
     ISD_CUDA(cudaEventRecord(g.ev[10], g.stream));
     ISD_CUDA(cudaStreamSynchronize(g.stream));
     if (g.faces_in_flight) ISD_CUDA(cudaStreamSynchronize(g.copy_stream));
@@ -782,8 +782,8 @@ void isd_build_geometry_device(const char* shape_parameters_json, const char* mc
     ensure_init();
     grand_algorithm(shape_parameters_json, s, /*copy_out=*/false);
 }
-const REAL* isd_device_verts(void) { return g.d_verts.as<float>(); }
-const int* isd_device_faces(void) { return g.d_faces.as<int>(); }
+const REAL* isd_device_verts(void) { return g.d_verts.as<float>() + g.local_voff * 3; }
+const int* isd_device_faces(void) { return g.d_faces.as<int>() + g.local_foff * 3; }
 
 int get_f_size(void) { return (int)g.nf; }
 int get_v_size(void) { return (int)g.nv; }
@@ -970,6 +970,7 @@ void isd_set_sdf_grid(int nx, int ny, int nz, float h, float ox, float oy, float
 }
 
 static void load_mesh(const float* verts, int nv, const int* faces, int nf) {
+    g.local_voff = 0; g.local_foff = 0;
     g.d_verts.reserve((size_t)(nv > 0 ? nv : 1) * 3 * sizeof(float));
     g.d_faces.reserve((size_t)(nf > 0 ? nf : 1) * 3 * sizeof(int));
     if (verts && nv) ISD_CUDA(cudaMemcpyAsync(g.d_verts.ptr, verts, (size_t)nv * 3 * sizeof(float), cudaMemcpyHostToDevice, g.stream));
