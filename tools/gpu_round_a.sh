@@ -14,6 +14,6 @@ ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start o
 python tools/one_step.py c2 256 --ob02 > $O/plain_c2.log 2>&1 &&
 ncu --set full --clock-control none --import-source on --profile-from-start off -o $O/full_c2_256 -f python tools/one_step.py c2 256 --ob02 > $O/ncu_full_c2.log 2>&1
 python tools/one_step.py c4 1024 > $O/plain_c4.log 2>&1 &&
-ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:'k_tile_bounds|k_eval_tiles|k_mc_classify|k_scan|k_mc_emit' -o $O/full_c4_1024 -f python tools/one_step.py c4 1024 > $O/ncu_full_c4.log 2>&1
+ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:'k_super_bounds|k_tile_bounds|k_eval_tiles|k_mc_classify|k_row_scan|k_seg_apply|k_mc_emit' -o $O/full_c4_1024 -f python tools/one_step.py c4 1024 > $O/ncu_full_c4.log 2>&1
 cat $O/plain_c4.log
 ls -la $O
