@@ -163,6 +163,132 @@ ISD_HD float prim_cube_sdf(const SdfGridView& g, float px, float py, float pz) {
     return -res;
 }
 
+// ---- the rest of the factory's analytic vocabulary (SURVEY §8 f-N1) ------------------------------------------------------
+// These follow C++'s promotion rules as the reference's expressions are written: std::pow(float, int|double) is a double
+// power, a double literal makes its sub-expression double, and the store rounds once to binary32.  Squares and cubes are
+// formed by multiplication and pow(.,0.5) by sqrt (IEEE-exact here; glibc's pow is within 0.52 ulp of the same double, so
+// after the final rounding to binary32 the two agree except with probability ~2^-29 per point: tolerance-level parity).
+//   torus            torus.hpp:55-118            r = 4, rx = ry = rz = 0.2 (the matrix12 constructor, :42-53)
+//   heart            heart.hpp:78-126
+//   double_mushroom  double_mushroom.hpp:68-134  (0.9, 0.2, 0.2, 1/0.2): r = 0.45, a = b = 0.2, c = 1/5; its own identity
+//                    matrix product is carried out as the reference does (signs of zero)
+//   top_bottom_lid   top_bottom_lid.hpp:51-76    on untransformed points
+//   tetrahedron      tetrahedron.hpp:145-193     four host-built planes, untransformed points
+//   half_plane       half_plane.hpp:109-150
+ISD_HD float prim_torus(float x, float y, float z) {
+    const float rx = 0.2f, r = 4.0f;
+    const double qx = (double)(x / rx), qy = (double)(y / rx), qz = (double)(z / rx);
+    const double a = sqrt(qx * qx + qy * qy);
+    const double d = (double)r - a;
+    return (float)(1 - d * d - qz * qz);
+}
+ISD_HD void grad_torus(float x, float y, float z, float& g0, float& g1, float& g2) {
+    const float rx = 0.2f, r = 4.0f;
+    const float a = (float)sqrt((double)(x * x / (rx * rx) + y * y / (rx * rx)));
+    g0 = (2 * x / (rx * rx * a)) * (r - a);
+    g1 = (2 * y / (rx * rx * a)) * (r - a);
+    g2 = -2 * z / (rx * rx);
+}
+ISD_HD double heart_core(float i1, float i2, float i3) {
+    return (double)(i1 * i1) + (9. / 4.) * (double)i2 * (double)i2 + (double)(i3 * i3);
+}
+ISD_HD float prim_heart(float i1, float i2, float i3) {
+    const double u = heart_core(i1, i2, i3) - 1.;
+    const double d2 = (double)i2, d3 = (double)i3;
+    return (float)(-(u * u * u - (double)(i1 * i1 * i3 * i3 * i3) - (9. / 200.) * d2 * d2 * d3 * d3 * d3));
+}
+ISD_HD void grad_heart(float i1, float i2, float i3, float& g0, float& g1, float& g2) {
+    const double u = heart_core(i1, i2, i3) - 1;
+    const float a = (float)(u * u);
+    const double d1 = (double)i1, d2 = (double)i2, d3 = (double)i3, da = (double)a;
+    g0 = (float)(-6. * d1 * da + 2. * d1 * d3 * d3 * d3);
+    g1 = (float)(-(27. / 2) * d2 * da + (9. / 100.) * d2 * d3 * d3 * d3);
+    g2 = (float)(-6. * d3 * da + 3. * d1 * d1 * d3 * d3 + (27. / 200.) * d2 * d2 * d3 * d3);
+}
+ISD_HD void identity_product(float& x, float& y, float& z) {      // matrix_vector_product with the identity, as written
+    const float one = 1.0f, zero = 0.0f;
+    const float nx = one * x + zero * y + zero * z + zero;
+    const float ny = zero * x + one * y + zero * z + zero;
+    const float nz = zero * x + zero * y + one * z + zero;
+    x = nx; y = ny; z = nz;
+}
+ISD_HD float prim_mushroom(float x, float y, float z) {
+    identity_product(x, y, z);
+    const float r = 0.9f / 2, a = (float)(0.4 / 2), c = 1 / (float)(1 / 0.2);
+    const float a2 = a * a, c2 = c * c;
+    if (z > r) return r - z;
+    if (z < -r) return r + z;
+    const double dx = (double)(x - 0.0f), dy = (double)(y - 0.0f), dz = (double)(z - 0.0f);
+    return (float)(-(dx * dx / (double)a2 + dy * dy / (double)a2 - dz * dz / (double)c2 - 1));
+}
+ISD_HD void grad_mushroom(float x, float y, float z, float& o0, float& o1, float& o2) {
+    identity_product(x, y, z);
+    const float r = 0.9f / 2, a = (float)(0.4 / 2), c = 1 / (float)(1 / 0.2);
+    const float a2 = a * a, c2 = c * c;
+    float g0, g1, g2;
+    if (z < -r) { g2 = 1; g1 = 0; g0 = 0; }
+    else if (z > r) { g2 = -1; g1 = 0; g0 = 0; }
+    else {
+        g0 = -2 * (x - 0.0f) / a2;
+        g1 = -2 * (y - 0.0f) / a2;
+        g2 = 2 * (z - 0.0f) / c2;
+    }
+    // double_mushroom's own (identity) inverse, :128-130; the wrapper's follows in the caller
+    const float one = 1.0f, zero = 0.0f;
+    o0 = one * g0 + zero * g1 + zero * g2;
+    o1 = zero * g0 + one * g1 + zero * g2;
+    o2 = zero * g0 + zero * g1 + one * g2;
+}
+ISD_HD float prim_lid(float z) {
+    const float p = z - 0.5f, q = (z + 0.5f) * -1;
+    return (p < q) ? q : p;
+}
+template <class Prog>
+ISD_HD float tetra_plane(const Prog& prog, int at, float x, float y, float z) {
+    const W4 q = prog.load4(at);
+    return as_float(q.x) * x + as_float(q.y) * y + as_float(q.z) * z + as_float(q.w);
+}
+template <class Prog>
+ISD_HD float prim_tetra(const Prog& prog, int at, float x, float y, float z) {
+    return ref_min(tetra_plane(prog, at, x, y, z),
+                   ref_min(tetra_plane(prog, at + 4, x, y, z), ref_min(tetra_plane(prog, at + 8, x, y, z), tetra_plane(prog, at + 12, x, y, z))));
+}
+template <class Prog>
+ISD_HD void grad_tetra(const Prog& prog, int at, float x, float y, float z, float& g0, float& g1, float& g2) {
+    int index = 0;
+    float mn = tetra_plane(prog, at, x, y, z);
+    for (int k = 1; k < 4; ++k) {
+        const float possible_min = tetra_plane(prog, at + 4 * k, x, y, z);
+        if (possible_min < mn) { index = k; mn = possible_min; }
+    }
+    const W4 q = prog.load4(at + 4 * index);
+    g0 = as_float(q.x); g1 = as_float(q.y); g2 = as_float(q.z);
+}
+template <class Prog>
+ISD_HD float prim_half_plane(const Prog& prog, int at, float x, float y, float z) {
+    const W4 n = prog.load4(at), p = prog.load4(at + 4);
+    return (x - as_float(p.x)) * as_float(n.x) + (y - as_float(p.y)) * as_float(n.y) + (z - as_float(p.z)) * as_float(n.z);
+}
+
+// One primitive other than METABALLS at one point: (cx,cy,cz) are the coordinates handed down by the parent, M the
+// instruction's matrix, `at` the word index of its parameters.
+template <class Prog>
+ISD_HD float prim_value(uint32_t op, const Prog& prog, int at, const Mat12<Prog>& M, const SdfGridView& sdf, float cx, float cy, float cz) {
+    if (op == OP_TETRA) return prim_tetra(prog, at, cx, cy, cz);
+    if (op == OP_LID) return prim_lid(cz);
+    float x, y, z;
+    M.apply(cx, cy, cz, x, y, z);
+    if (op == OP_ELLIPSOID) return prim_ellipsoid(x, y, z);
+    if (op == OP_CYLINDER) return prim_cylinder(x, y, z);
+    if (op == OP_CONE) return prim_cone(x, y, z);
+    if (op == OP_CUBE) return prim_cube(x, y, z);
+    if (op == OP_CUBE_SDF) return prim_cube_sdf(sdf, x, y, z);
+    if (op == OP_TORUS) return prim_torus(x, y, z);
+    if (op == OP_HEART) return prim_heart(x, y, z);
+    if (op == OP_MUSHROOM) return prim_mushroom(x, y, z);
+    return prim_half_plane(prog, at, x, y, z);
+}
+
 // ---- value mode -------------------------------------------------------------------------------------------------
 // Evaluates the program at P points held in registers; cur* are clobbered.
 // The two newest values of the stack live in registers (t0 = top, t1 = below); older ones spill to a per-thread
@@ -276,15 +402,8 @@ ISD_HD void eval_values(const Prog& prog, const SdfGridView& sdf, const Live& li
                 }
             } else {
 #pragma unroll
-                for (int p = 0; p < P; ++p) {
-                    float x, y, z;
-                    M.apply(cx[p], cy[p], cz[p], x, y, z);
-                    if (op == OP_ELLIPSOID) f[p] = prim_ellipsoid(x, y, z);
-                    else if (op == OP_CYLINDER) f[p] = prim_cylinder(x, y, z);
-                    else if (op == OP_CONE) f[p] = prim_cone(x, y, z);
-                    else if (op == OP_CUBE) f[p] = prim_cube(x, y, z);
-                    else f[p] = prim_cube_sdf(sdf, x, y, z);
-                }
+                for (int p = 0; p < P; ++p) f[p] = prim_value(op, prog, pc, M, sdf, cx[p], cy[p], cz[p]);
+                pc = (int)hdr.y;      // past the parameters, if any
             }
             // push
             if (sp >= 2) {
@@ -408,15 +527,7 @@ ISD_HD void eval_values_list(const Prog& prog, const SdfGridView& sdf, const Lis
             }
         } else {
 #pragma unroll
-            for (int p = 0; p < P; ++p) {
-                float x, y, z;
-                M.apply(cx[p], cy[p], cz[p], x, y, z);
-                if (op == OP_ELLIPSOID) f[p] = prim_ellipsoid(x, y, z);
-                else if (op == OP_CYLINDER) f[p] = prim_cylinder(x, y, z);
-                else if (op == OP_CONE) f[p] = prim_cone(x, y, z);
-                else if (op == OP_CUBE) f[p] = prim_cube(x, y, z);
-                else f[p] = prim_cube_sdf(sdf, x, y, z);
-            }
+            for (int p = 0; p < P; ++p) f[p] = prim_value(op, prog, pc, M, sdf, cx[p], cy[p], cz[p]);
         }
         if (sp >= 2) {
 #pragma unroll
@@ -501,9 +612,26 @@ ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, float 
             else if (op == OP_CYLINDER) { f = prim_cylinder(x, y, z); grad_cylinder(x, y, z, g0, g1, g2); }
             else if (op == OP_CONE) { f = prim_cone(x, y, z); grad_cone(x, y, z, g0, g1, g2); }
             else if (op == OP_CUBE) { f = prim_cube(x, y, z); grad_cube(x, y, z, g0, g1, g2); }
-            else { f = prim_cube_sdf(sdf, x, y, z); grad_cube(x, y, z, g0, g1, g2); }
+            else if (op == OP_CUBE_SDF) { f = prim_cube_sdf(sdf, x, y, z); grad_cube(x, y, z, g0, g1, g2); }
+            else if (op == OP_TORUS) { f = prim_torus(x, y, z); grad_torus(x, y, z, g0, g1, g2); }
+            else if (op == OP_HEART) { f = prim_heart(x, y, z); grad_heart(x, y, z, g0, g1, g2); }
+            else if (op == OP_MUSHROOM) { f = prim_mushroom(x, y, z); grad_mushroom(x, y, z, g0, g1, g2); }
+            else if (op == OP_HALF_PLANE) {
+                f = prim_half_plane(prog, pc, x, y, z);
+                const W4 n = prog.load4(pc);
+                const float s = (f >= 0) ? -1.0f : 1.0f;      // half_plane.hpp:129-138, as written
+                g0 = s * as_float(n.x); g1 = s * as_float(n.y); g2 = s * as_float(n.z);
+            } else if (op == OP_TETRA) {      // planes in the parent's frame; no matrix on the way back (tetrahedron.hpp:163-193)
+                f = prim_tetra(prog, pc, cx, cy, cz);
+                grad_tetra(prog, pc, cx, cy, cz, g0, g1, g2);
+            } else {                          // OP_LID: (0, 0, 1) everywhere (top_bottom_lid.hpp:62-76)
+                f = prim_lid(cz);
+                g0 = 0; g1 = 0; g2 = 1;
+            }
+            if (op != OP_METABALLS) pc = (int)hdr.y;
             float o0, o1, o2;
-            M.back(g0, g1, g2, o0, o1, o2);
+            if (op == OP_TETRA || op == OP_LID) { o0 = g0; o1 = g1; o2 = g2; }
+            else M.back(g0, g1, g2, o0, o1, o2);
             vs[sp][0] = f; vs[sp][1] = o0; vs[sp][2] = o1; vs[sp][3] = o2;
             ++sp;
         }

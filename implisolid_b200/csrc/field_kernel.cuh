@@ -145,6 +145,8 @@ __device__ inline Ival program_bounds(const uint32_t* __restrict__ bp, float bx,
         if (MASKED && !in_mask(word >> OP_ID_SHIFT)) {      // dead primitive: no bound needed, nothing pushed
             pc += 13;
             if (op == OP_METABALLS) pc += 1 + 5 * (int)__ldg(bp + pc);
+            else if (op == OP_TETRA) pc += 16;
+            else if (op == OP_HALF_PLANE) pc += 8;
             present <<= 1;
             continue;
         }
@@ -196,6 +198,66 @@ __device__ inline Ival program_bounds(const uint32_t* __restrict__ bp, float bx,
             }
             const float slack = 1e-4f * (fabsf(lo) + fabsf(hi) + (float)nb);
             r = Ival{lo - slack, hi + slack};
+        } else if (op == OP_TORUS) {
+            // 1 - (4 - sqrt(25 x^2 + 25 y^2))^2 - 25 z^2
+            const Ival X = iv_sq(cx, rx), Y = iv_sq(cy, ry), Z = iv_sq(cz, rz);
+            const float a_lo = 5.0f * sqrtf(X.lo + Y.lo), a_hi = 5.0f * sqrtf(X.hi + Y.hi);
+            const float d_lo = 4.0f - a_hi, d_hi = 4.0f - a_lo;
+            const float q_hi = fmaxf(d_lo * d_lo, d_hi * d_hi), q_lo = (d_lo > 0.0f || d_hi < 0.0f) ? fminf(d_lo * d_lo, d_hi * d_hi) : 0.0f;
+            r = Ival{1.0f - q_hi - 25.0f * Z.hi, 1.0f - q_lo - 25.0f * Z.lo};
+            const float slack = 1e-3f * (fabsf(r.lo) + fabsf(r.hi) + 16.0f);
+            r.lo -= slack; r.hi += slack;
+        } else if (op == OP_HEART) {
+            // -((x^2 + 2.25 y^2 + z^2 - 1)^3 - x^2 z^3 - 0.045 y^2 z^3)
+            const Ival X = iv_sq(cx, rx), Y = iv_sq(cy, ry), Z = iv_sq(cz, rz);
+            const float u_lo = X.lo + 2.25f * Y.lo + Z.lo - 1.0f, u_hi = X.hi + 2.25f * Y.hi + Z.hi - 1.0f;
+            const float zl = cz - rz, zh = cz + rz;
+            const float c_lo = zl * zl * zl, c_hi = zh * zh * zh;                     // z^3 is increasing
+            const float w_lo = X.lo + 0.045f * Y.lo, w_hi = X.hi + 0.045f * Y.hi;    // >= 0
+            const float t_lo = fminf(w_lo * c_lo, w_hi * c_lo), t_hi = fmaxf(w_lo * c_hi, w_hi * c_hi);
+            const float p_lo = u_lo * u_lo * u_lo, p_hi = u_hi * u_hi * u_hi;
+            r = Ival{-(p_hi - t_lo), -(p_lo - t_hi)};
+            const float slack = 1e-3f * (fabsf(p_lo) + fabsf(p_hi) + fabsf(t_lo) + fabsf(t_hi) + 1.0f);
+            r.lo -= slack; r.hi += slack;
+        } else if (op == OP_MUSHROOM) {
+            // z > 0.45: 0.45 - z;  z < -0.45: 0.45 + z;  else 1 - 25 x^2 - 25 y^2 + 25 z^2  (hull of the pieces the box meets)
+            const float R = 0.45f, zl = cz - rz, zh = cz + rz;
+            float lo = 3.0e38f, hi = -3.0e38f;
+            if (zh > R - pad) { lo = fminf(lo, R - zh); hi = fmaxf(hi, R - fmaxf(zl, R - pad)); }
+            if (zl < -R + pad) { lo = fminf(lo, R + zl); hi = fmaxf(hi, R + fminf(zh, -R + pad)); }
+            if (zh >= -R - pad && zl <= R + pad) {
+                const Ival X = iv_sq(cx, rx), Y = iv_sq(cy, ry);
+                const float a = fmaxf(zl, -R - pad), b = fminf(zh, R + pad);
+                const float m = fmaxf(fabsf(a), fabsf(b)), n = (a > 0.0f) ? a : ((b < 0.0f) ? -b : 0.0f);
+                lo = fminf(lo, 1.0f - 25.0f * (X.hi + Y.hi) + 25.0f * n * n);
+                hi = fmaxf(hi, 1.0f - 25.0f * (X.lo + Y.lo) + 25.0f * m * m);
+            }
+            const float slack = 1e-3f * (fabsf(lo) + fabsf(hi) + 1.0f);
+            r = Ival{lo - slack, hi + slack};
+        } else if (op == OP_LID) {
+            // max(z - 0.5, -z - 0.5) = |z| - 0.5 on the parent's coordinates (the composite here has no own inverse)
+            const float zl = cz - rz, zh = cz + rz;
+            const float m = fmaxf(fabsf(zl), fabsf(zh)), n = (zl > 0.0f) ? zl : ((zh < 0.0f) ? -zh : 0.0f);
+            r = Ival{n - 0.5f, m - 0.5f};
+        } else if (op == OP_TETRA) {
+            float lo = 3.0e38f, hi = 3.0e38f;
+            for (int k = 0; k < 4; ++k) {
+                const float a = __uint_as_float(__ldg(bp + pc + 4 * k)), b = __uint_as_float(__ldg(bp + pc + 4 * k + 1));
+                const float c = __uint_as_float(__ldg(bp + pc + 4 * k + 2)), d = __uint_as_float(__ldg(bp + pc + 4 * k + 3));
+                const float mid = a * cx + b * cy + c * cz + d, rad = fabsf(a) * rx + fabsf(b) * ry + fabsf(c) * rz;
+                const float slack = 1e-4f * (fabsf(a * cx) + fabsf(b * cy) + fabsf(c * cz) + fabsf(d) + rad);
+                lo = fminf(lo, mid - rad - slack);
+                hi = fminf(hi, mid + rad + slack);
+            }
+            pc += 16;
+            r = Ival{lo, hi};
+        } else if (op == OP_HALF_PLANE) {
+            const float n0 = __uint_as_float(__ldg(bp + pc)), n1 = __uint_as_float(__ldg(bp + pc + 1)), n2 = __uint_as_float(__ldg(bp + pc + 2));
+            const float p0 = __uint_as_float(__ldg(bp + pc + 4)), p1 = __uint_as_float(__ldg(bp + pc + 5)), p2 = __uint_as_float(__ldg(bp + pc + 6));
+            pc += 8;
+            const float mid = (cx - p0) * n0 + (cy - p1) * n1 + (cz - p2) * n2, rad = fabsf(n0) * rx + fabsf(n1) * ry + fabsf(n2) * rz;
+            const float slack = 1e-4f * (fabsf(cx - p0) + fabsf(cy - p1) + fabsf(cz - p2) + rad);
+            r = Ival{mid - rad - slack, mid + rad + slack};
         } else {   // OP_CUBE_SDF: a table look-up, no bound
             r = Ival{-3.0e38f, 3.0e38f};
         }

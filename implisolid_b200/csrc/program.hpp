@@ -15,6 +15,9 @@
 //                                   not evaluated last), cur <- m * cur
 //   ELLIPSOID|CYLINDER|CONE|CUBE|CUBE_SDF hdr m[12]     push f(m * cur)   (primitives apply their own inverse)
 //   METABALLS hdr(aux = nb) m[12] {bx,by,bz,strength, subtract,0,0,0}*nb
+//   TORUS|HEART|MUSHROOM|LID hdr m[12]                  (LID ignores m: top_bottom_lid never transforms its points)
+//   TETRA hdr m[12] planes[4][4]                        (m unused: the corners were moved by the forward matrix on the host)
+//   HALF_PLANE hdr m[12] {n0,n1,n2,0, p0,p1,p2,0}       (m = cofactor inverse, see cofactor_inverse)
 //   UNION|INTERSECT|SUBTRACT (+SWAPPED, +RESTORE flags) hdr m[12]   pop two values, push the selected one; m is the node's
 //                                   own inverse, used only in gradient mode to map the selected child's gradient back;
 //                                   RESTORE: then pop cur (closes a node entered with the SAVE flag)
@@ -47,9 +50,15 @@ enum Opcode : uint32_t {
     OP_CUBE = 7,
     OP_CUBE_SDF = 8,
     OP_METABALLS = 9,
-    OP_UNION = 10,
-    OP_INTERSECT = 11,
-    OP_SUBTRACT = 12,
+    OP_TORUS = 10,               // itorus                    object_factory.hpp:163-173
+    OP_HEART = 11,               // iheart                    :153-162
+    OP_TETRA = 12,               // tetrahedron               :175-188   params: planes[4][4]; points are NOT transformed
+    OP_MUSHROOM = 13,            // implicit_double_mushroom  :86-99     linearly_transformed(double_mushroom(0.9, 0.2, 0.2, 5))
+    OP_HALF_PLANE = 14,          // half_plane                :396-434   params: {n0,n1,n2,0, p0,p1,p2,0}
+    OP_LID = 15,                 // top_bottom_lid            :480-505   points are NOT transformed
+    OP_UNION = 24,
+    OP_INTERSECT = 25,
+    OP_SUBTRACT = 26,
     OP_MASK = 0xff,
     OP_FLAG_SWAPPED = 0x100,     // value stack holds (second child, first child)
     OP_FLAG_SAVE = 0x200,        // XFORM: push cur on the frame stack first
@@ -243,6 +252,79 @@ private:
         memset(n.minv, 0, sizeof(n.minv));     // the reference leaves heap garbage when the matrix is singular
         if (!affine_inverse(n.m, n.minv)) fprintf(stderr, "implisolid_b200: warning: singular shape matrix\n");
     }
+    static void set_identity_inverse(ShapeNode& n) {
+        for (int i = 0; i < 12; ++i) n.minv[i] = (i % 5 == 0) ? 1.0f : 0.0f;
+    }
+    // `rows` rows of three numbers: "corners":[[x,y,z] x4], or one flat triple ("plane_vector":[x,y,z])
+    static void read_rows(const JsonDoc& d, int node, const char* key, int rows, float* out) {
+        int arr = d.child(node, key);
+        if (arr < 0) { fprintf(stderr, "implisolid_b200: shape node without \"%s\"\n", key); abort(); }
+        int k = 0;
+        if (rows == 1) {
+            for (int c = d.first_child(arr); c >= 0 && k < 3; c = d.next(c))
+                if (!d.to_float(c, &out[k++])) { fprintf(stderr, "implisolid_b200: bad \"%s\" entry\n", key); abort(); }
+        } else {
+            for (int r = d.first_child(arr); r >= 0 && k < rows * 3; r = d.next(r)) {
+                int j = 0;
+                for (int c = d.first_child(r); c >= 0 && j < 3; c = d.next(c), ++j)
+                    if (!d.to_float(c, &out[k++])) { fprintf(stderr, "implisolid_b200: bad \"%s\" entry\n", key); abort(); }
+                if (j != 3) { fprintf(stderr, "implisolid_b200: a row of \"%s\" needs 3 numbers\n", key); abort(); }
+            }
+        }
+        if (k != rows * 3) { fprintf(stderr, "implisolid_b200: \"%s\" needs %d x 3 numbers\n", key, rows); abort(); }
+    }
+    // tetrahedron: constructor (tetrahedron.hpp:136-143: corners moved by the FORWARD matrix, basic_functions.hpp:140-177),
+    // calculatePlaneCoefficients :18-28, getPlanes :30-134 (each plane oriented so that the opposite corner is on the
+    // positive side, sign() with ROOT_TOLERANCE = 0.001/10, basic_functions.hpp:22-31, configs.hpp:33), all binary32.
+    static void plane_through(const float* p1, const float* p2, const float* p3, float* pl) {
+        const float x1 = p1[0], y1 = p1[1], z1 = p1[2], x2 = p2[0], y2 = p2[1], z2 = p2[2], x3 = p3[0], y3 = p3[1], z3 = p3[2];
+        pl[0] = y1 * z2 - y1 * z3 - y2 * z1 + y2 * z3 + y3 * z1 - y3 * z2;
+        pl[1] = x1 * z3 - x1 * z2 + x2 * z1 - x2 * z3 - x3 * z1 + x3 * z2;
+        pl[2] = x1 * y2 - x1 * y3 - x2 * y1 + x2 * y3 + x3 * y1 - x3 * y2;
+        pl[3] = x1 * y3 * z2 - x1 * y2 * z3 + x2 * y1 * z3 - x2 * y3 * z1 - x3 * y1 * z2 + x3 * y2 * z1;
+    }
+    static void tetra_planes(const float corners[4][3], const float m[12], std::vector<float>& out) {
+        float p[4][3];
+        for (int i = 0; i < 4; ++i) {
+            const float x = corners[i][0], y = corners[i][1], z = corners[i][2];
+            p[i][0] = m[0] * x + m[1] * y + m[2] * z + m[3];
+            p[i][1] = m[4] * x + m[5] * y + m[6] * z + m[7];
+            p[i][2] = m[8] * x + m[9] * y + m[10] * z + m[11];
+        }
+        float pl[4][4];
+        plane_through(p[1], p[2], p[3], pl[0]);
+        plane_through(p[0], p[2], p[3], pl[1]);
+        plane_through(p[0], p[1], p[3], pl[2]);
+        plane_through(p[0], p[1], p[2], pl[3]);
+        const float tol = 0.001 / 10.0;
+        for (int k = 0; k < 4; ++k) {
+            const float v = pl[k][0] * p[k][0] + pl[k][1] * p[k][1] + pl[k][2] * p[k][2] + pl[k][3];
+            const float s = (v > +tol) ? (+1) : (v < -tol) ? (-1) : (0.0);
+            for (int j = 0; j < 4; ++j) pl[k][j] *= s;
+        }
+        out.assign(&pl[0][0], &pl[0][0] + 16);
+    }
+    // half_plane.hpp:100-107 inverts [M; 0 0 0 1] with Eigen's Matrix4f::inverse() (cofactors over the determinant).  Eigen
+    // is absent and unpinned: plain binary32 cofactor expansion, so this primitive has tolerance-level parity only.
+    static void cofactor_inverse(const float m12[12], float inv12[12]) {
+        float a[16];
+        memcpy(a, m12, 12 * sizeof(float));
+        a[12] = 0.f; a[13] = 0.f; a[14] = 0.f; a[15] = 1.f;
+        float cof[16];
+        for (int r = 0; r < 4; ++r)
+            for (int c = 0; c < 4; ++c) {
+                float s[9];
+                int k = 0;
+                for (int i = 0; i < 4; ++i)
+                    for (int j = 0; j < 4; ++j)
+                        if (i != r && j != c) s[k++] = a[i * 4 + j];
+                const float det3 = s[0] * (s[4] * s[8] - s[5] * s[7]) - s[1] * (s[3] * s[8] - s[5] * s[6]) + s[2] * (s[3] * s[7] - s[4] * s[6]);
+                cof[r * 4 + c] = ((r + c) & 1) ? -det3 : det3;
+            }
+        const float det = a[0] * cof[0] + a[1] * cof[1] + a[2] * cof[2] + a[3] * cof[3];
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 4; ++c) inv12[r * 4 + c] = cof[c * 4 + r] / det;
+    }
     static std::unique_ptr<ShapeNode> leaf(Opcode op, const float m[12]) {
         std::unique_ptr<ShapeNode> n(new ShapeNode());
         n->op = op;
@@ -284,6 +366,45 @@ private:
             d.to_float(d.child(node, "time"), &time);
             std::unique_ptr<ShapeNode> n = leaf(OP_METABALLS, m);
             metaball_centres(4, time, n->params);
+            return n;
+        }
+        if (name == "iheart") {                                                       // :153-162
+            read_matrix12(d, node, ignore_root_matrix, m);
+            return leaf(OP_HEART, m);
+        }
+        if (name == "itorus") {                                                       // :163-173
+            read_matrix12(d, node, ignore_root_matrix, m);
+            return leaf(OP_TORUS, m);
+        }
+        if (name == "implicit_double_mushroom") {                                     // :86-99
+            read_matrix12(d, node, ignore_root_matrix, m);
+            return leaf(OP_MUSHROOM, m);
+        }
+        if (name == "top_bottom_lid") {                                               // :480-505 (matrix read, never applied)
+            read_matrix12(d, node, ignore_root_matrix, m);
+            std::unique_ptr<ShapeNode> n = leaf(OP_LID, m);
+            set_identity_inverse(*n);
+            return n;
+        }
+        if (name == "tetrahedron") {                                                  // :175-188, getCorners :32-45
+            read_matrix12(d, node, ignore_root_matrix, m);
+            float corners[4][3];
+            read_rows(d, node, "corners", 4, &corners[0][0]);
+            std::unique_ptr<ShapeNode> n = leaf(OP_TETRA, m);
+            set_identity_inverse(*n);
+            tetra_planes(corners, m, n->params);
+            return n;
+        }
+        if (name == "half_plane") {                                                   // :396-434
+            read_matrix12(d, node, ignore_root_matrix, m);
+            float nv[3], pp[3];
+            read_rows(d, node, "plane_vector", 1, nv);
+            read_rows(d, node, "plane_point", 1, pp);
+            std::unique_ptr<ShapeNode> n = leaf(OP_HALF_PLANE, m);
+            cofactor_inverse(m, n->minv);
+            // half_plane.hpp:88-89: the vector is normalised once in the constructor
+            const float norm = sqrtf(nv[0] * nv[0] + nv[1] * nv[1] + nv[2] * nv[2]);
+            n->params = {nv[0] / norm, nv[1] / norm, nv[2] / norm, 0.0f, pp[0], pp[1], pp[2], 0.0f};
             return n;
         }
         if (name == "Union" || name == "Intersection" || name == "Difference") {
@@ -370,6 +491,8 @@ private:
             if (n.op == OP_METABALLS) {
                 p.bounds.push_back((uint32_t)(n.params.size() / 5));
                 for (float v : n.params) { uint32_t w; memcpy(&w, &v, 4); p.bounds.push_back(w); }
+            } else if (n.op == OP_TETRA || n.op == OP_HALF_PLANE) {      // 16 / 8 words, as in the value program
+                for (float v : n.params) { uint32_t w; memcpy(&w, &v, 4); p.bounds.push_back(w); }
             }
             return;
         }
@@ -382,7 +505,7 @@ private:
         p.num_nodes++;
         if (!n.is_csg()) {
             put_itab(p, (uint32_t)(p.words.size() / 4), id_of(n), 0u, 0u);
-            const size_t skip_at = put_header(p, (uint32_t)n.op | (id_of(n) << OP_ID_SHIFT), (uint32_t)(n.params.size() / 5));
+            const size_t skip_at = put_header(p, (uint32_t)n.op | (id_of(n) << OP_ID_SHIFT), n.op == OP_METABALLS ? (uint32_t)(n.params.size() / 5) : 0u);
             put_matrix(p, n.minv);
             p.flops_per_point += 18;
             switch (n.op) {
@@ -400,6 +523,16 @@ private:
                     p.flops_per_point += 12.0 * nb;
                     break;
                 }
+                // double-precision operations counted as one flop each, like the binary32 ones
+                case OP_TORUS: p.flops_per_point += 13; break;
+                case OP_HEART: p.flops_per_point += 24; break;
+                case OP_MUSHROOM: p.flops_per_point += 18 + 11; break;
+                case OP_LID: p.flops_per_point += 3 - 18; break;           // no transform
+                case OP_TETRA:
+                case OP_HALF_PLANE:
+                    for (float v : n.params) { uint32_t w; memcpy(&w, &v, 4); p.words.push_back(w); }
+                    p.flops_per_point += (n.op == OP_TETRA) ? 24 + 3 - 18 : 8;
+                    break;
                 default: break;
             }
             p.words[skip_at] = (uint32_t)p.words.size();

@@ -118,3 +118,52 @@ def bushy_tree(seed=7):
     l = {"type": "Union", "matrix": aff(), "children": [prim("cube"), prim("cylinder"), prim("ellipsoid")]}
     r = {"type": "Intersection", "matrix": aff(), "children": [prim("cone"), {"type": "Difference", "matrix": aff(), "children": [prim("ellipsoid"), prim("cube")]}]}
     return json.dumps({"type": "Difference", "matrix": aff(), "children": [l, r]})
+
+
+# ---- the rest of the factory's analytic vocabulary (SURVEY §8 f-N1) ----------------------------------------------------
+def n1_torus():
+    """itorus (object_factory.hpp:163-173): major radius 4*0.2, tube 0.2 in local units, tilted and scaled by 0.55."""
+    return json.dumps({"type": "itorus", "matrix": _mat(_rot_axis([1, 0.3, 0], 25.0) * 0.55, [0.02, -0.01, 0.03])})
+
+
+def n1_heart():
+    """iheart (object_factory.hpp:153-162), scaled by 0.45."""
+    return json.dumps({"type": "iheart", "matrix": _mat(_rot_axis([0, 0, 1], 15.0) * 0.45, [0.0, 0.0, -0.05])})
+
+
+def n1_tetrahedron():
+    """tetrahedron (object_factory.hpp:175-188): corners moved by the forward matrix."""
+    return json.dumps({"type": "tetrahedron", "matrix": _mat(_rot_axis([1, 1, 1], 20.0) * 0.9, [0.01, 0.02, -0.03]),
+                       "corners": [[-0.5, -0.4, -0.45], [0.55, -0.35, -0.4], [0.0, 0.6, -0.35], [0.05, 0.0, 0.6]]})
+
+
+def n1_mushroom():
+    """implicit_double_mushroom (object_factory.hpp:86-99)."""
+    return json.dumps({"type": "implicit_double_mushroom", "matrix": _mat(_rot_axis([0, 1, 0], 10.0) * 1.1, [0.0, 0.03, 0.0])})
+
+
+def n1_half_plane_cut():
+    """Intersection[ellipsoid, half_plane] (object_factory.hpp:396-434): a sphere cut by an oblique plane."""
+    hp = {"type": "half_plane", "matrix": _mat(_rot_axis([1, 0, 0], 12.0), [0.0, 0.0, 0.05]),
+          "plane_vector": [0.2, 0.1, 1.0], "plane_point": [0.0, 0.0, -0.1]}
+    return json.dumps({"type": "Intersection", "matrix": EYE,
+                       "children": [{"type": "ellipsoid", "matrix": _mat(np.eye(3) * 1.3, [0, 0, 0])}, hp]})
+
+
+def n1_lid_slab():
+    """Difference[ellipsoid, top_bottom_lid] (object_factory.hpp:480-505): the lid is positive where |z| > 0.5."""
+    return json.dumps({"type": "Difference", "matrix": _mat(np.eye(3) * 0.8, [0, 0, 0]),
+                       "children": [{"type": "ellipsoid", "matrix": _mat(np.eye(3) * 1.6, [0, 0, 0])},
+                                    {"type": "top_bottom_lid", "matrix": EYE}]})
+
+
+def n1_medley():
+    """Every N1 primitive in one tree: Difference[Union[torus, heart, tetrahedron, mushroom], half_plane]."""
+    tor = {"type": "itorus", "matrix": _mat(_rot_axis([1, 0, 0], 90.0) * 0.5, [-0.35, 0.0, 0.0])}
+    hrt = {"type": "iheart", "matrix": _mat(np.eye(3) * 0.3, [0.45, 0.0, 0.1])}
+    tet = {"type": "tetrahedron", "matrix": _mat(np.eye(3) * 0.6, [0.0, 0.45, 0.0]),
+           "corners": [[-0.5, -0.4, -0.45], [0.55, -0.35, -0.4], [0.0, 0.6, -0.35], [0.05, 0.0, 0.6]]}
+    msh = {"type": "implicit_double_mushroom", "matrix": _mat(_rot_axis([1, 0, 0], 90.0) * 0.7, [0.0, -0.45, 0.0])}
+    hp = {"type": "half_plane", "matrix": _mat(np.eye(3), [0, 0, 0]), "plane_vector": [0.0, 0.3, 1.0], "plane_point": [0.0, 0.0, 0.35]}
+    u = {"type": "Union", "matrix": _mat(_rot_axis([0, 0, 1], 8.0) * 0.95, [0.01, 0.0, 0.0]), "children": [tor, hrt, tet, msh]}
+    return json.dumps({"type": "Difference", "matrix": EYE, "children": [u, hp]})

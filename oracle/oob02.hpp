@@ -29,7 +29,7 @@
 
 namespace oracle {
 
-const REAL ROOT_TOLERANCE = 0.001 / 10.0;          // configs.hpp:33
+// ROOT_TOLERANCE (configs.hpp:33) is defined in oshapes.hpp
 const REAL MILLIMETER = 1.0;                        // configs.hpp:38-48: every step is a REAL constexpr
 const REAL MICROMETER = MILLIMETER / 1000.0;
 const REAL NANOMETER = MICROMETER / 1000.0;

@@ -360,6 +360,250 @@ struct meta_balls : implicit_function {
     }
 };
 
+// ---- torus.hpp:42-118 -------------------------------------------------------------------------
+// std::pow(float, int) and std::pow(float, double) promote to double (C++11 <cmath>), so f is one double
+// expression rounded once to REAL; the gradient's `a` is a double power rounded to REAL, the rest binary32.
+struct torus : implicit_function {
+    REAL r = 4.f, rx = 0.2f, ry = 0.2f, rz = 0.2f;
+    explicit torus(const REAL m[12]) { set_matrix(m); }
+    void eval_implicit(const vects& xx, scalars* out) const override {
+        const vects lx = prepare_inner_vectors(Minv, xx);
+        for (size_t i = 0; i < lx.n(); i++) {
+            REAL x = lx[i][0], y = lx[i][1], z = lx[i][2];
+            REAL f = (1 - std::pow(r - std::pow((std::pow(x / rx, 2) + std::pow(y / ry, 2)), 0.5), 2) - std::pow(z / rz, 2));
+            (*out)[i] = f;
+        }
+    }
+    void eval_gradient(const vects& xx, vects* out) const override {
+        const vects lx = prepare_inner_vectors(Minv, xx);
+        for (size_t i = 0; i < lx.n(); i++) {
+            REAL x = lx[i][0], y = lx[i][1], z = lx[i][2];
+            REAL a = std::pow(x * x / (rx * rx) + y * y / (ry * ry), 0.5);
+            REAL gx = (2 * x / (rx * rx * a)) * (r - a);
+            REAL gy = (2 * y / (ry * ry * a)) * (r - a);
+            REAL gz = -2 * z / (rz * rz);
+            back(gx, gy, gz, (*out)[i]);
+        }
+    }
+};
+
+// ---- heart.hpp:33-52,78-126 -------------------------------------------------------------------
+// Mixed precision as written: i1*i1 and i3*i3 are binary32 products, (9./4.)*i2*i2 and everything they are
+// added to is double; the i1*i1*i3*i3*i3 chain is binary32; one rounding to REAL at the store.
+struct heart : implicit_function {
+    explicit heart(const REAL m[12]) { set_matrix(m); }
+    void eval_implicit(const vects& xx, scalars* out) const override {
+        vects lx = xx;
+        matrix_vector_product(Minv, lx);
+        for (size_t i = 0; i < lx.n(); i++) {
+            REAL i1 = lx[i][0], i2 = lx[i][1], i3 = lx[i][2];
+            (*out)[i] = -(std::pow(i1 * i1 + (9. / 4.) * i2 * i2 + i3 * i3 - 1., 3) - i1 * i1 * i3 * i3 * i3 - (9. / 200.) * i2 * i2 * i3 * i3 * i3);
+        }
+    }
+    void eval_gradient(const vects& xx, vects* out) const override {
+        vects lx = xx;
+        matrix_vector_product(Minv, lx);
+        for (size_t i = 0; i < lx.n(); i++) {
+            REAL i1 = lx[i][0], i2 = lx[i][1], i3 = lx[i][2];
+            REAL a = pow(i1 * i1 + (9. / 4.) * i2 * i2 + i3 * i3 - 1, 2);
+            REAL g0 = -6. * i1 * a + 2. * i1 * i3 * i3 * i3;
+            REAL g1 = -(27. / 2) * i2 * a + (9. / 100.) * i2 * i3 * i3 * i3;
+            REAL g2 = -6. * i3 * a + 3. * i1 * i1 * i3 * i3 + (27. / 200.) * i2 * i2 * i3 * i3;
+            back(g0, g1, g2, (*out)[i]);
+        }
+    }
+};
+
+// ---- basic_functions.hpp:22-31, configs.hpp:33 ------------------------------------------------
+inline REAL sign(REAL v, REAL tol) { return (v > +tol) ? (+1) : (v < -tol) ? (-1) : (0.0); }
+const REAL ROOT_TOLERANCE = 0.001 / 10.0;
+
+// ---- tetrahedron.hpp:18-134,136-193 -----------------------------------------------------------
+// The corners are moved by the FORWARD matrix once (constructor :136-143); points are never transformed.
+struct tetrahedron : implicit_function {
+    REAL p[4][3];
+    REAL planes[4][4];
+    static void calculatePlaneCoefficients(REAL x1, REAL y1, REAL z1, REAL x2, REAL y2, REAL z2, REAL x3, REAL y3, REAL z3, REAL& a, REAL& b,
+                                           REAL& c, REAL& d) {
+        a = y1 * z2 - y1 * z3 - y2 * z1 + y2 * z3 + y3 * z1 - y3 * z2;
+        b = x1 * z3 - x1 * z2 + x2 * z1 - x2 * z3 - x3 * z1 + x3 * z2;
+        c = x1 * y2 - x1 * y3 - x2 * y1 + x2 * y3 + x3 * y1 - x3 * y2;
+        d = x1 * y3 * z2 - x1 * y2 * z3 + x2 * y1 * z3 - x2 * y3 * z1 - x3 * y1 * z2 + x3 * y2 * z1;
+    }
+    void getPlanes() {
+        static const int others[4][3] = {{1, 2, 3}, {0, 2, 3}, {0, 1, 3}, {0, 1, 2}};
+        for (int k = 0; k < 4; k++) {
+            const int* o = others[k];
+            calculatePlaneCoefficients(p[o[0]][0], p[o[0]][1], p[o[0]][2], p[o[1]][0], p[o[1]][1], p[o[1]][2], p[o[2]][0], p[o[2]][1],
+                                       p[o[2]][2], planes[k][0], planes[k][1], planes[k][2], planes[k][3]);
+        }
+        for (int k = 0; k < 4; k++) {
+            REAL s = sign(planes[k][0] * p[k][0] + planes[k][1] * p[k][1] + planes[k][2] * p[k][2] + planes[k][3], ROOT_TOLERANCE);
+            for (int j = 0; j < 4; j++) planes[k][j] *= s;
+        }
+    }
+    tetrahedron(const REAL corners[4][3], const REAL m[12]) {
+        for (int i = 0; i < 12; i++) { M[i] = m[i]; Minv[i] = (i % 5 == 0) ? 1.0f : 0.0f; }
+        vects c(4);
+        for (int i = 0; i < 4; i++)
+            for (int j = 0; j < 3; j++) c[i][j] = corners[i][j];
+        matrix_vector_product(m, c);
+        for (int i = 0; i < 4; i++)
+            for (int j = 0; j < 3; j++) p[i][j] = c[i][j];
+        getPlanes();
+    }
+    REAL plane(int k, REAL i1, REAL i2, REAL i3) const { return planes[k][0] * i1 + planes[k][1] * i2 + planes[k][2] * i3 + planes[k][3]; }
+    void eval_implicit(const vects& x, scalars* out) const override {
+        for (size_t i = 0; i < x.n(); i++) {
+            REAL i1 = x[i][0], i2 = x[i][1], i3 = x[i][2];
+            (*out)[i] = std::min(plane(0, i1, i2, i3), std::min(plane(1, i1, i2, i3), std::min(plane(2, i1, i2, i3), plane(3, i1, i2, i3))));
+        }
+    }
+    void eval_gradient(const vects& x, vects* out) const override {
+        for (size_t i = 0; i < x.n(); i++) {
+            REAL i1 = x[i][0], i2 = x[i][1], i3 = x[i][2];
+            int index = 0;
+            REAL mn = plane(0, i1, i2, i3);
+            for (int k = 1; k < 4; k++) {
+                REAL possible_min = plane(k, i1, i2, i3);
+                if (possible_min < mn) { index = k; mn = possible_min; }
+            }
+            (*out)[i][0] = planes[index][0];
+            (*out)[i][1] = planes[index][1];
+            (*out)[i][2] = planes[index][2];
+        }
+    }
+};
+
+// ---- double_mushroom.hpp:21-43,68-134 ---------------------------------------------------------
+// Own matrices are the identity (the factory wraps it in linearly_transformed, object_factory.hpp:86-99), but the
+// identity product is still carried out.  std::pow(float, int) is a double power: f is one double expression.
+struct double_mushroom : implicit_function {
+    REAL r, a, b, c, x = 0, y = 0, z = 0;
+    double_mushroom(REAL height_mm, REAL center_radius_x_mm, REAL center_radius_y_mm, REAL curvature) {
+        r = height_mm / 2;
+        a = center_radius_x_mm;
+        b = center_radius_y_mm;
+        c = 1 / curvature;
+        for (int i = 0; i < 12; i++) M[i] = Minv[i] = (i % 5 == 0) ? 1.0f : 0.0f;
+    }
+    void eval_implicit(const vects& xx, scalars* out) const override {
+        vects lx = xx;
+        matrix_vector_product(Minv, lx);
+        const REAL a2 = squared(a), b2 = squared(b), c2 = squared(c);
+        for (size_t i = 0; i < lx.n(); i++) {
+            if (lx[i][2] > r) (*out)[i] = r - lx[i][2];
+            else if (lx[i][2] < -r) (*out)[i] = r + lx[i][2];
+            else (*out)[i] = -(std::pow(lx[i][0] - x, 2) / a2 + std::pow(lx[i][1] - y, 2) / b2 - pow(lx[i][2] - z, 2) / c2 - 1);
+        }
+    }
+    void eval_gradient(const vects& xx, vects* out) const override {
+        vects lx = xx;
+        matrix_vector_product(Minv, lx);
+        const REAL a2 = squared(a), b2 = squared(b), c2 = squared(c);
+        for (size_t i = 0; i < lx.n(); i++) {
+            REAL g0, g1, g2;
+            if (lx[i][2] < -r) { g2 = 1; g1 = 0; g0 = 0; }
+            else if (lx[i][2] > r) { g2 = -1; g1 = 0; g0 = 0; }
+            else {
+                g0 = -2 * (lx[i][0] - x) / a2;
+                g1 = -2 * (lx[i][1] - y) / b2;
+                g2 = 2 * (lx[i][2] - z) / c2;
+            }
+            back(g0, g1, g2, (*out)[i]);
+        }
+    }
+};
+
+// ---- linearly_transformed.hpp:24-59 -----------------------------------------------------------
+struct linearly_transformed : implicit_function {
+    const implicit_function* child;
+    linearly_transformed(const implicit_function* c, const REAL m[12]) : child(c) { set_matrix(m); }
+    void eval_implicit(const vects& x, scalars* f) const override {
+        const vects lx = prepare_inner_vectors(Minv, x);
+        child->eval_implicit(lx, f);
+    }
+    void eval_gradient(const vects& x, vects* out) const override {
+        const vects lx = prepare_inner_vectors(Minv, x);
+        child->eval_gradient(lx, out);
+        for (size_t i = 0; i < lx.n(); i++) {
+            REAL gx = (*out)[i][0], gy = (*out)[i][1], gz = (*out)[i][2];
+            back(gx, gy, gz, (*out)[i]);
+        }
+    }
+};
+
+// ---- top_bottom_lid.hpp:51-76 -----------------------------------------------------------------
+// No transform at all (the matrix is only checked); max(z - 0.5, -(z + 0.5)); the gradient's first branch can never
+// be taken (z >= 0.5 && 0 > z), so it is (0, 0, 1) everywhere.
+struct top_bottom_lid : implicit_function {
+    explicit top_bottom_lid(const REAL m[12]) { for (int i = 0; i < 12; i++) { M[i] = m[i]; Minv[i] = (i % 5 == 0) ? 1.0f : 0.0f; } }
+    void eval_implicit(const vects& x, scalars* out) const override {
+        for (size_t i = 0; i < x.n(); i++) {
+            REAL p = x[i][2] - 0.5f, q = (x[i][2] + 0.5f) * -1;
+            (*out)[i] = (p < q) ? q : p;          // Eigen's array max
+        }
+    }
+    void eval_gradient(const vects& x, vects* out) const override {
+        for (size_t i = 0; i < x.n(); i++) {
+            const REAL z = x[i][2];
+            (*out)[i][0] = 0;
+            (*out)[i][1] = 0;
+            (*out)[i][2] = (z >= 0.5 && (0.0 > z && z >= -0.5)) ? -1 : 1;
+        }
+    }
+};
+
+// ---- half_plane.hpp:85-150 --------------------------------------------------------------------
+// The reference inverts the 4x4 with Eigen (Matrix4f::inverse(): cofactors / determinant) and evaluates through
+// Eigen products.  Eigen is not in this image and the reference pins no version: restated as the plain cofactor
+// inverse and left-to-right sums in binary32 — tolerance-level parity only for this primitive.
+inline void cofactor_inverse4(const REAL m12[12], REAL inv16[16]) {
+    REAL a[16];
+    for (int i = 0; i < 12; i++) a[i] = m12[i];
+    a[12] = 0; a[13] = 0; a[14] = 0; a[15] = 1;
+    REAL cof[16];
+    for (int r = 0; r < 4; r++)
+        for (int c = 0; c < 4; c++) {
+            REAL s[9];
+            int k = 0;
+            for (int i = 0; i < 4; i++)
+                for (int j = 0; j < 4; j++)
+                    if (i != r && j != c) s[k++] = a[i * 4 + j];
+            REAL det3 = s[0] * (s[4] * s[8] - s[5] * s[7]) - s[1] * (s[3] * s[8] - s[5] * s[6]) + s[2] * (s[3] * s[7] - s[4] * s[6]);
+            cof[r * 4 + c] = ((r + c) & 1) ? -det3 : det3;
+        }
+    REAL det = a[0] * cof[0] + a[1] * cof[1] + a[2] * cof[2] + a[3] * cof[3];
+    for (int r = 0; r < 4; r++)
+        for (int c = 0; c < 4; c++) inv16[r * 4 + c] = cof[c * 4 + r] / det;
+}
+struct half_plane : implicit_function {
+    REAL n[3], pp[3];
+    half_plane(const REAL m[12], const REAL plane_vector[3], const REAL plane_point[3]) {
+        REAL norm = std::sqrt(plane_vector[0] * plane_vector[0] + plane_vector[1] * plane_vector[1] + plane_vector[2] * plane_vector[2]);
+        for (int i = 0; i < 3; i++) { n[i] = plane_vector[i] / norm; pp[i] = plane_point[i]; }
+        REAL inv[16];
+        cofactor_inverse4(m, inv);
+        for (int i = 0; i < 12; i++) { M[i] = m[i]; Minv[i] = inv[i]; }
+    }
+    REAL value(const REAL* x) const {
+        REAL lx = Minv[0] * x[0] + Minv[1] * x[1] + Minv[2] * x[2];
+        REAL ly = Minv[4] * x[0] + Minv[5] * x[1] + Minv[6] * x[2];
+        REAL lz = Minv[8] * x[0] + Minv[9] * x[1] + Minv[10] * x[2];
+        lx = lx + Minv[3]; ly = ly + Minv[7]; lz = lz + Minv[11];
+        return (lx - pp[0]) * n[0] + (ly - pp[1]) * n[1] + (lz - pp[2]) * n[2];
+    }
+    void eval_implicit(const vects& x, scalars* out) const override {
+        for (size_t i = 0; i < x.n(); i++) (*out)[i] = value(x[i]);
+    }
+    void eval_gradient(const vects& x, vects* out) const override {
+        for (size_t i = 0; i < x.n(); i++) {
+            const REAL s = (value(x[i]) >= 0) ? -1.0f : 1.0f;
+            back(s * n[0], s * n[1], s * n[2], (*out)[i]);
+        }
+    }
+};
+
 // ---- transformed_union / intersection / subtract ----------------------------------------------
 enum CsgOp { OP_UNION, OP_INTERSECTION, OP_SUBTRACT };
 struct csg_node : implicit_function {
@@ -440,6 +684,37 @@ inline const implicit_function* object_factory(Shape& S, const ojson::Node& node
     if (name == "icylinder" || name == "cylinder") { matrix(); return S.keep(new scylinder(m)); }
     if (name == "iellipsoid" || name == "ellipsoid") { matrix(); return S.keep(new egg(m)); }
     if (name == "icone" || name == "cone") { matrix(); return S.keep(new scone(m)); }
+    if (name == "iheart") { matrix(); return S.keep(new heart(m)); }                     // :153-162
+    if (name == "itorus") { matrix(); return S.keep(new torus(m)); }                     // :163-173
+    if (name == "implicit_double_mushroom") {                                            // :86-99
+        const implicit_function* dm = S.keep(new double_mushroom(0.9, 0.4 / 2, 0.4 / 2, 1 / 0.2));
+        matrix();
+        return S.keep(new linearly_transformed(dm, m));
+    }
+    if (name == "tetrahedron") {                                                         // :175-188, getCorners :32-45
+        getMatrix12(m, node);
+        REAL corners[4][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+        const ojson::Node* cs = node.child("corners");
+        if (!cs || cs->kids.size() != 4) { fprintf(stderr, "oracle: tetrahedron needs 4 corners\n"); abort(); }
+        for (int i = 0; i < 4; i++) {
+            const ojson::Node& row = cs->kids[i].second;
+            if (row.kids.size() != 3) { fprintf(stderr, "oracle: a corner needs 3 coordinates\n"); abort(); }
+            for (int j = 0; j < 3; j++)
+                if (!row.kids[j].second.as_float(&corners[i][j])) { fprintf(stderr, "oracle: bad corner\n"); abort(); }
+        }
+        if (ignore_root_matrix) copy_eye(m);
+        return S.keep(new tetrahedron(corners, m));
+    }
+    if (name == "half_plane") {                                                          // :396-434
+        matrix();
+        REAL pv[3] = {0, 0, 0}, ppt[3] = {0, 0, 0};
+        const ojson::Node* a = node.child("plane_vector");
+        const ojson::Node* b = node.child("plane_point");
+        if (!a || !b || a->kids.size() != 3 || b->kids.size() != 3) { fprintf(stderr, "oracle: half_plane needs plane_vector and plane_point\n"); abort(); }
+        for (int j = 0; j < 3; j++) { a->kids[j].second.as_float(&pv[j]); b->kids[j].second.as_float(&ppt[j]); }
+        return S.keep(new half_plane(m, pv, ppt));
+    }
+    if (name == "top_bottom_lid") { matrix(); return S.keep(new top_bottom_lid(m)); }    // :480-505
     if (name == "meta_balls") {                                                          // :654-673
         matrix();
         REAL time = node.get_float("time", 0.1);

@@ -89,6 +89,12 @@ float eval_tree(const ShapeCompiler& c, const ShapeNode& n, float x, float y, fl
             }
             return f;
         }
+        case OP_TORUS: return prim_torus(lx, ly, lz);
+        case OP_HEART: return prim_heart(lx, ly, lz);
+        case OP_MUSHROOM: return prim_mushroom(lx, ly, lz);
+        case OP_LID: return prim_lid(z);
+        case OP_TETRA: return prim_tetra(HostProg{reinterpret_cast<const uint32_t*>(n.params.data())}, 0, x, y, z);
+        case OP_HALF_PLANE: return prim_half_plane(HostProg{reinterpret_cast<const uint32_t*>(n.params.data())}, 0, lx, ly, lz);
         default: break;
     }
     // CSG: evaluate both children unmarked first to learn the selection, then mark the selected one
