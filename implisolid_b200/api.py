@@ -78,6 +78,11 @@ EXT_SIGNATURES = {
     "isd_faces_of_faces": (None, [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
     "isd_umbrella": (None, [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]),
     "isd_eval_points": (None, [ctypes.c_char_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p]),
+    "isd_set_progress_callback": (None, [ctypes.c_void_p, ctypes.c_void_p]),
+    "isd_get_n_ptr": (ctypes.c_void_p, []),
+    "isd_get_n": (None, [ctypes.c_void_p, ctypes.c_int]),
+    "isd_device_normals": (ctypes.c_void_p, []),
+    "isd_srand": (None, [ctypes.c_uint]),
     "isd_dist_unique_id": (ctypes.c_int, [ctypes.c_void_p]),
     "isd_dist_init": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
     "isd_dist_finalize": (None, []),
@@ -87,7 +92,7 @@ EXT_SIGNATURES = {
     "isd_dist_gather_mesh": (None, []),
 }
 
-TIMING_NAMES = ["field", "classify_scan", "emit", "resample", "project", "qem", "d2h", "total_host"]
+TIMING_NAMES = ["field", "classify_scan", "emit", "resample", "project", "qem", "d2h", "total_host", "subdiv", "gather"]
 
 
 def _b(s):
@@ -152,6 +157,42 @@ class GeometryLibrary:
     def finish_geometry(self):
         self.lib.finish_geometry()
 
+    # ---- progressive results (isd_set_progress_callback; the oracle exports the same under its own prefix) ----
+    PROGRESS_FN = ctypes.CFUNCTYPE(None, ctypes.POINTER(ctypes.c_float), ctypes.c_int, ctypes.POINTER(ctypes.c_int), ctypes.c_int,
+                                   ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p)
+    progress_symbol = "isd_set_progress_callback"
+    srand_symbol = "isd_srand"
+
+    def polygonize_progressive(self, shape_json, mc_json, call_specs=None):
+        """build_geometry_u with a progress callback installed: returns the list of reports
+        [(verts, faces, (progress_callback_id, shape_id, call_id)), ...] and the final (verts, faces)."""
+        reports = []
+
+        def on_progress(v, nv, f, nf, cb_id, shape_id, call_id, _user):
+            vv = np.ctypeslib.as_array(v, shape=(nv, 3)).copy() if nv else np.empty((0, 3), np.float32)
+            ff = np.ctypeslib.as_array(f, shape=(nf, 3)).copy() if nf else np.empty((0, 3), np.int32)
+            reports.append((vv, ff, (cb_id, shape_id, call_id)))
+
+        cb = self.PROGRESS_FN(on_progress)
+        setter = getattr(self.lib, self.progress_symbol)
+        setter.restype, setter.argtypes = None, [ctypes.c_void_p, ctypes.c_void_p]
+        setter(ctypes.cast(cb, ctypes.c_void_p), None)
+        try:
+            if call_specs is None:
+                self.build_geometry(shape_json, mc_json)
+            else:
+                self.build_geometry_u(shape_json, mc_json, call_specs)
+            v, f = self.get_v(), self.get_f()
+            self.finish_geometry()
+        finally:
+            setter(None, None)
+        return reports, (v, f)
+
+    def srand(self, seed=1):
+        fn = getattr(self.lib, self.srand_symbol)
+        fn.restype, fn.argtypes = None, [ctypes.c_uint]
+        fn(int(seed))
+
     def polygonize(self, shape_json, mc_json):
         """build_geometry -> copies of (verts, faces) -> finish_geometry: impli2.make_geometry (implisolid_main.js:201-249)."""
         self.build_geometry(shape_json, mc_json)
@@ -193,9 +234,21 @@ class GeometryLibrary:
     def build_geometry_device(self, shape_json, mc_json):
         self.lib.isd_build_geometry_device(_b(shape_json), _b(mc_json))
 
+    def get_n(self):
+        """Per-vertex normals of the last build (isd_get_n), shape (Nv, 3)."""
+        n = self.get_v_size()
+        out = np.empty((n, 3), dtype=np.float32)
+        self.lib.isd_get_n(out.ctypes.data, n)
+        return out
+
+    def get_n_view(self):
+        n = self.get_v_size()
+        p = self.lib.isd_get_n_ptr()
+        return np.ctypeslib.as_array(ctypes.cast(p, _c_float_p), shape=(n, 3)) if n else np.empty((0, 3), np.float32)
+
     def last_timings(self):
-        buf = np.zeros(8, dtype=np.float32)
-        self.lib.isd_last_timings(buf.ctypes.data, 8)
+        buf = np.zeros(len(TIMING_NAMES), dtype=np.float32)
+        self.lib.isd_last_timings(buf.ctypes.data, len(TIMING_NAMES))
         return dict(zip(TIMING_NAMES, [float(x) for x in buf]))
 
     def last_counters(self):

@@ -23,6 +23,7 @@
 #include "field_kernel.cuh"
 #include "mc_kernels.cuh"
 #include "ob02_kernels.cuh"
+#include "subdiv_kernels.cuh"
 #include "settings.hpp"
 
 using namespace isd;
@@ -77,7 +78,7 @@ constexpr int kNcclInt64 = 4, kNcclFloat32 = 7, kNcclInt32 = 2;   // ncclDataTyp
 // ---------------------------------------------------------------------------------------------------------------------
 // process-wide state (the reference keeps one global state_t _state, mcc2.cpp:165-193)
 // ---------------------------------------------------------------------------------------------------------------------
-enum { T_FIELD = 0, T_CLASSIFY, T_EMIT, T_RESAMPLE, T_PROJECT, T_QEM, T_COPY, T_TOTAL, T_COUNT };
+enum { T_FIELD = 0, T_CLASSIFY, T_EMIT, T_RESAMPLE, T_PROJECT, T_QEM, T_COPY, T_TOTAL, T_SUBDIV, T_GATHER, T_COUNT };
 
 struct Context {
     bool ready = false;
@@ -113,6 +114,15 @@ struct Context {
     float average_edge = 0.f;
     bool alpha_ticket_zeroed = false;
     long long proj_n = 0;
+
+    // polygonize_step_3 (subdivision) scratch, per-vertex normals, progress reports
+    DeviceBuffer d_sub_owner, d_sub_flag, d_sub_rank, d_verts2, d_faces2, d_ratio, d_normals;
+    PinnedBuffer h_normals;
+    bool normals_valid = false, normals_host_valid = false;
+    std::vector<uint32_t> last_program;     // the shape program of the last build (lazy normals re-upload it)
+    isd_progress_fn progress_fn = nullptr;
+    void* progress_user = nullptr;
+    int call_specs[3] = {-1, -1, -1};       // progressCallback_id, shape_id, call_id (worker_call_specs.hpp:20-34)
 
     // HEAD-literal cube table
     DeviceBuffer d_sdf;
@@ -442,6 +452,7 @@ void gather_mesh() {
     if (g.world == 1 || g.gathered || g.emulate) return;
     int64_t* hs = reinterpret_cast<int64_t*>(g.h_small.as<char>() + 256);
     const long long gnv = g.slab[6], gnf = g.slab[7];
+    ISD_CUDA(cudaEventRecord(g.ev[13], g.stream));
     g.nccl.check(g.nccl.GroupStart(), "ncclGroupStart");
     long long vo = 0, fo = 0;
     for (int r = 0; r < g.world; ++r) {      // in place: every rank's slab already sits at its global offset
@@ -453,6 +464,7 @@ void gather_mesh() {
         vo += rv; fo += rf;
     }
     g.nccl.check(g.nccl.GroupEnd(), "ncclGroupEnd");
+    ISD_CUDA(cudaEventRecord(g.ev[14], g.stream));
     if (getenv("ISD_GATHER_SYNC")) ISD_CUDA(cudaStreamSynchronize(g.stream));
     g.local_voff = 0; g.local_foff = 0;
     g.nv = gnv; g.nf = gnf;
@@ -569,6 +581,29 @@ struct Mt11213b {
     }
 };
 
+// make_random_pm1(n, 3, 1e-6) seeds a fresh mt11213b(12) on every call (make_random_pm1.hpp:15-28), so draw j is the same
+// number in every build: the stream is generated once (sequentially, on the host: a Mersenne twister with data-dependent
+// rejections in uniform_01) and kept in HBM; a larger mesh only generates the tail it is missing.
+const float* noise_stream(size_t count) {
+    static Mt11213b rng(12);
+    static size_t have = 0;
+    if (count > have) {
+        const size_t want = count + count / 4;
+        DeviceBuffer bigger;
+        bigger.reserve(want * sizeof(float));
+        if (have) ISD_CUDA(cudaMemcpyAsync(bigger.ptr, g.d_noise.ptr, have * sizeof(float), cudaMemcpyDeviceToDevice, g.stream));
+        std::vector<float> tail(want - have);
+        const float amplitude = 0.000001f;
+        for (size_t i = 0; i < tail.size(); ++i) tail[i] = (float)((rng.uniform01() * 2.0 - 1.0) * amplitude);
+        ISD_CUDA(cudaMemcpyAsync(bigger.as<float>() + have, tail.data(), tail.size() * sizeof(float), cudaMemcpyHostToDevice, g.stream));
+        ISD_CUDA(cudaStreamSynchronize(g.stream));      // `tail` is pageable and dies here
+        g.d_noise.release();
+        g.d_noise = bigger;
+        have = want;
+    }
+    return g.d_noise.as<float>();
+}
+
 // polygonize_step_2 (polygonizer_algorithm_ob02.hpp:108-116) -> centroids_projection (centroids_projection.cpp:1219-1311)
 void projection_step(bool enable_qem, bool exact_reduce) {
     const int nv = (int)g.nv, nf = (int)g.nf;
@@ -637,13 +672,7 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     if (hc->c[10] > 0) {
         // rare: direction types 2..6 for the left-overs; type 2 needs make_random_pm1(n, 1e-6), centroid i <- draws 3i..3i+2
         ISD_CUDA(cudaEventRecord(g.ev[6], g.stream));
-        std::vector<float> noise((size_t)nf * 3);
-        Mt11213b rng(12);
-        const float amplitude = 0.000001f;
-        for (size_t i = 0; i < noise.size(); ++i) noise[i] = (float)((rng.uniform01() * 2.0 - 1.0) * amplitude);
-        g.d_noise.reserve(noise.size() * sizeof(float));
-        ISD_CUDA(cudaMemcpyAsync(g.d_noise.ptr, noise.data(), noise.size() * sizeof(float), cudaMemcpyHostToDevice, g.stream));
-        a.noise = g.d_noise.as<float>();
+        a.noise = noise_stream((size_t)nf * 3);
         a.speculative = 0;
         k_project_search<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a, 1);
         ISD_LAUNCH_CHECK();
@@ -657,7 +686,7 @@ void projection_step(bool enable_qem, bool exact_reduce) {
         }
         ISD_CUDA(cudaEventRecord(g.ev[8], g.stream));
         ISD_CUDA(cudaMemcpyAsync(hc, g.d_counters.ptr, sizeof(Ob02Counters), cudaMemcpyDeviceToHost, g.stream));
-        ISD_CUDA(cudaStreamSynchronize(g.stream));   // also: `noise` lives on this stack frame until the copy is done
+        ISD_CUDA(cudaStreamSynchronize(g.stream));
         ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[6], g.ev[7]));
         g.timings[T_PROJECT] += ms;
         ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[7], g.ev[8]));
@@ -669,6 +698,109 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     g.counters[10] += (int64_t)hc->c[7];
     g.counters[11] += (int64_t)hc->c[8];
     g.counters[12] += (int64_t)hc->c[9];
+}
+
+// ---- polygonize_step_3 ---------------------------------------------------------------------------------------------------
+// glibc's rand(): random_r.c TYPE_3 (x^31 + x^3 + 1 additive feedback), srandom_r's Lehmer fill (16807, Schrage) and its 310
+// discarded outputs.  The reference calls rand() without ever seeding it, so its stream is glibc's seed-1 stream running on
+// from build to build; a private copy keeps other users of the process-wide rand() out of it.
+struct GlibcRand {
+    uint32_t ring[31];
+    int f = 3, b = 0;
+    unsigned long long pending_skips = 0;      // draws made by builds with zero amplitude: their values are never needed
+    GlibcRand() { seed(1); }
+    void seed(unsigned s) {
+        int32_t word = (int32_t)(s ? s : 1);
+        ring[0] = (uint32_t)word;
+        for (int i = 1; i < 31; ++i) {
+            const long hi = word / 127773, lo = word % 127773;
+            word = (int32_t)(16807 * lo - 2836 * hi);
+            if (word < 0) word += 2147483647;
+            ring[i] = (uint32_t)word;
+        }
+        f = 3; b = 0; pending_skips = 0;
+        for (int i = 0; i < 310; ++i) next();
+    }
+    int next() {
+        ring[f] += ring[b];
+        const uint32_t r = ring[f] >> 1;
+        if (++f >= 31) f = 0;
+        if (++b >= 31) b = 0;
+        return (int)r;
+    }
+    void catch_up() { for (; pending_skips; --pending_skips) next(); }
+} g_rand;
+
+// 1-to-4 subdivision of every face + randomize_verts (subdiv_kernels.cuh).  One device->host read (the number of new vertices).
+void subdivision_step(float amplitude) {
+    const int nv = (int)g.nv, nf = (int)g.nf;
+    if (nf == 0) return;
+    if ((long long)nf * 4 * 3 > 2147483647LL) { fprintf(stderr, "implisolid_b200: mesh too large to subdivide (32-bit face indices)\n"); abort(); }
+    ISD_CUDA(cudaEventRecord(g.ev[11], g.stream));
+    build_adjacency(false);
+    const long long n3 = (long long)nf * 3;
+    g.d_sub_owner.reserve((size_t)n3 * sizeof(unsigned));
+    g.d_sub_flag.reserve((size_t)n3 * sizeof(unsigned));
+    g.d_sub_rank.reserve((size_t)(n3 + 1) * sizeof(unsigned));
+    k_subdiv_mark<<<blocks_for(n3, 256), 256, 0, g.stream>>>(g.d_faces.as<int>(), nf, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(),
+                                                            g.d_sub_owner.as<unsigned>(), g.d_sub_flag.as<unsigned>());
+    ISD_LAUNCH_CHECK();
+    exclusive_scan_u32(g.d_sub_flag.as<unsigned>(), n3, g.d_sub_rank.as<unsigned>());
+    unsigned* h_new = reinterpret_cast<unsigned*>(g.h_small.as<char>() + 3072);
+    ISD_CUDA(cudaMemcpyAsync(h_new, g.d_sub_rank.as<unsigned>() + n3, sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    const long long nv2 = (long long)nv + (long long)*h_new, nf2 = (long long)nf * 4;
+    g.d_verts2.reserve((size_t)nv2 * 3 * sizeof(float) + 16);
+    g.d_faces2.reserve((size_t)nf2 * 3 * sizeof(int) + 16);
+    ISD_CUDA(cudaMemcpyAsync(g.d_verts2.ptr, g.d_verts.ptr, (size_t)nv * 3 * sizeof(float), cudaMemcpyDeviceToDevice, g.stream));
+    k_subdiv_emit<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.d_verts.as<float>(), nv, g.d_faces.as<int>(), nf, g.d_sub_owner.as<unsigned>(),
+                                                            g.d_sub_rank.as<unsigned>(), g.d_verts2.as<float>(), g.d_faces2.as<int>());
+    ISD_LAUNCH_CHECK();
+    std::swap(g.d_verts, g.d_verts2);
+    std::swap(g.d_faces, g.d_faces2);
+    g.nv = nv2; g.nf = nf2;
+    g.adjacency_valid = false; g.fof_valid_ = false;
+    g.host_valid = false;
+    // randomize_verts draws 3*nv2 numbers whatever the amplitude
+    const long long draws = nv2 * 3;
+    if (amplitude == 0.0f) {
+        g_rand.pending_skips += (unsigned long long)draws;      // v + (+-0) == v
+    } else {
+        g_rand.catch_up();
+        std::vector<float> ratio((size_t)draws);
+        for (long long i = 0; i < draws; ++i) ratio[(size_t)i] = static_cast<float>(g_rand.next()) / static_cast<float>(2147483647);
+        g.d_ratio.reserve((size_t)draws * sizeof(float));
+        ISD_CUDA(cudaMemcpyAsync(g.d_ratio.ptr, ratio.data(), (size_t)draws * sizeof(float), cudaMemcpyHostToDevice, g.stream));
+        k_add_noise<<<blocks_for(draws, 256), 256, 0, g.stream>>>(g.d_verts.as<float>(), draws, g.d_ratio.as<float>(), amplitude);
+        ISD_LAUNCH_CHECK();
+        ISD_CUDA(cudaStreamSynchronize(g.stream));      // `ratio` is pageable and dies here
+    }
+    ISD_CUDA(cudaEventRecord(g.ev[12], g.stream));
+}
+
+// N2: -grad f/|grad f| at the final vertices (mode 2|4 of k_eval_points = calculate_implicit_gradients(true))
+void compute_normals() {
+    if (g.normals_valid) return;
+    const long long nv = g.nv;
+    g.d_normals.reserve((size_t)(nv > 0 ? nv : 1) * 3 * sizeof(float));
+    if (nv) {
+        upload_program(g.last_program);
+        k_eval_points<<<blocks_for(nv, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>() + g.local_voff * 3, nv, nullptr,
+                                                               g.d_normals.as<float>(), 2 | 4);
+        ISD_LAUNCH_CHECK();
+    }
+    g.normals_valid = true;
+    g.normals_host_valid = false;
+}
+
+void copy_mesh_to_host();
+
+// N3: send_mesh_back_to_client (polygonizer_algorithm_ob02.hpp:180-220)
+void report_progress() {
+    if (!g.progress_fn) return;
+    copy_mesh_to_host();
+    g.progress_fn(g.h_verts.as<float>(), (int)g.nv, g.h_faces.as<int>(), (int)g.nf, g.call_specs[0], g.call_specs[1], g.call_specs[2], g.progress_user);
+    g.host_valid = false;       // the next step changes the mesh
 }
 
 // faces do not change after marching cubes: start their device->host copy now, on the side stream
@@ -715,16 +847,21 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     g.adjacency_valid = false;
     g.fof_valid_ = false;
     g.proj_n = 0;
+    g.normals_valid = false;
+    g.normals_host_valid = false;
     ShapeCompiler::Program prog = compile_shape(shape_json, s.ignore_root_matrix, s.cube_mode);
     upload_program(prog.words);
+    g.last_program = prog.words;
     g.prog_stats[0] = prog.flops_per_point; g.prog_stats[1] = prog.num_nodes; g.prog_stats[2] = (double)prog.words.size();
     g.prog_stats[3] = prog.value_depth;
     g.keep_field = true;
     run_marching_cubes(s, prog);                                   // polygonize_step_0
-    const bool any_ob02 = s.overall_repeats > 0 && (s.vresampl_iters > 0 || s.projection_enabled);
+    const bool any_ob02 = s.overall_repeats > 0 && (s.vresampl_iters > 0 || s.projection_enabled || s.subdiv_enabled);
     if (any_ob02 && g.world > 1 && !g.emulate) gather_mesh();      // OB02 runs on the stitched mesh, replicated
-    if (copy_out && any_ob02) start_faces_copy();
-    bool resample_timed = false;
+    const bool faces_final = !(s.overall_repeats > 0 && s.subdiv_enabled) && !g.progress_fn;
+    if (copy_out && any_ob02 && faces_final) start_faces_copy();
+    report_progress();                                             // mcc2.cpp:351
+    bool resample_timed = false, subdiv_timed = false;
     for (int overall_iter = 0; overall_iter < s.overall_repeats; ++overall_iter) {
         if (s.vresampl_iters > 0) {
             ISD_CUDA(cudaEventRecord(g.ev[4], g.stream));
@@ -732,7 +869,11 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
             ISD_CUDA(cudaEventRecord(g.ev[5], g.stream));
             resample_timed = true;
         }
-        if (s.projection_enabled) projection_step(s.qem_enabled, s.exact_reduce != 0);     // polygonize_step_2
+        report_progress();                                                                 // mcc2.cpp:372
+        if (s.projection_enabled) {
+            projection_step(s.qem_enabled, s.exact_reduce != 0);                           // polygonize_step_2
+            report_progress();                                                             // mcc2.cpp:390
+        }
         if (resample_timed && (s.projection_enabled || s.overall_repeats > 1)) {          // events are reused by the next repeat
             if (!s.projection_enabled) ISD_CUDA(cudaStreamSynchronize(g.stream));
             float ms = 0;
@@ -741,8 +882,11 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
             resample_timed = false;
         }
         const bool is_last = overall_iter == s.overall_repeats - 1;
-        if (s.subdiv_enabled && (s.overall_repeats <= 1 || is_last) && s.verbose)
-            fprintf(stderr, "implisolid_b200: subdivision (polygonize_step_3) is outside this library's scope; skipped\n");
+        if (s.subdiv_enabled && (s.overall_repeats <= 1 || is_last)) {                     // polygonize_step_3, mcc2.cpp:396-410
+            const float scale_noise_according_to_matrix = 1.0 * 10.0;
+            subdivision_step(is_last ? s.post_subdiv_noise * scale_noise_according_to_matrix : 0.0f);
+            subdiv_timed = true;
+        }
     }
     ISD_CUDA(cudaStreamSynchronize(g.stream));
     float ms = 0;
@@ -750,6 +894,9 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[0], g.ev[1])); g.timings[T_FIELD] = ms;
     ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[1], g.ev[2])); g.timings[T_CLASSIFY] = ms;
     ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[2], g.ev[3])); g.timings[T_EMIT] = ms;
+    if (g.gathered && g.world > 1) { ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[13], g.ev[14])); g.timings[T_GATHER] = ms; }
+    if (subdiv_timed) { ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[11], g.ev[12])); g.timings[T_SUBDIV] = ms; }
+    if (s.normals) compute_normals();
     if (copy_out) copy_mesh_to_host();
     g.active = true;                                               // polygonize_terminate
     g.counters[13] = g.launches;
@@ -774,8 +921,44 @@ void build_geometry(const char* shape_parameters_json, const char* mc_parameters
     ensure_init();
     grand_algorithm(shape_parameters_json, s, /*copy_out=*/true);
 }
-void build_geometry_u(const char* shape_parameters_json, const char* mc_parameters_json, const char* /*call_specs*/) {
+void build_geometry_u(const char* shape_parameters_json, const char* mc_parameters_json, const char* call_specs) {
+    // worker_call_sepcs_t (worker_call_specs.hpp:20-34): three optional ints, -1 when absent
+    if (call_specs && *call_specs) {
+        JsonDoc d(call_specs);
+        g.call_specs[0] = d.get_int("progressCallback_id", -1);
+        g.call_specs[2] = d.get_int("call_id", -1);
+        g.call_specs[1] = d.get_int("shape_id", -1);
+    }
     build_geometry(shape_parameters_json, mc_parameters_json);
+    g.call_specs[0] = g.call_specs[1] = g.call_specs[2] = -1;
+}
+void isd_set_progress_callback(isd_progress_fn fn, void* user) { g.progress_fn = fn; g.progress_user = user; }
+void isd_srand(unsigned seed) { g_rand.seed(seed); }
+
+static void normals_to_host() {
+    compute_normals();
+    if (g.normals_host_valid) return;
+    g.h_normals.reserve((size_t)(g.nv > 0 ? g.nv : 1) * 3 * sizeof(float));
+    if (g.nv) ISD_CUDA(cudaMemcpyAsync(g.h_normals.ptr, g.d_normals.ptr, (size_t)g.nv * 3 * sizeof(float), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    g.normals_host_valid = true;
+}
+void* isd_get_n_ptr(void) {
+    if (!g.ready) return nullptr;
+    normals_to_host();
+    return g.h_normals.ptr;
+}
+void isd_get_n(REAL* n_out, int vcount) {
+    if (!g.ready) return;
+    normals_to_host();
+    const size_t n = (size_t)g.nv * 3;
+    if (n) memcpy(n_out, g.h_normals.ptr, n * sizeof(float));
+    if ((long long)vcount * 3 != (long long)n) fprintf(stderr, "sizes dont match: %g %d\n", n / 3., vcount);
+}
+const REAL* isd_device_normals(void) {
+    if (!g.ready) return nullptr;
+    compute_normals();
+    return g.d_normals.as<float>();
 }
 void isd_build_geometry_device(const char* shape_parameters_json, const char* mc_parameters_json) {
     const McSettings s = parse_mc_settings(mc_parameters_json);

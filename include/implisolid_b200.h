@@ -32,7 +32,9 @@ typedef float REAL; /* basic_data_structures.hpp:60 */
  * (object_factory.hpp:56-758); mc_parameters_json: mc_settings (polygoniser_settings.hpp:147-305). */
 void build_geometry(const char* shape_parameters_json, const char* mc_parameters_json);
 /* mcc2.cpp:90 (declared, body commented out at :296-302; JS cwraps it, js/worker_api.js:126).
- * call_specs is accepted and ignored (no progress callbacks natively). */
+ * call_specs = {"progressCallback_id","call_id","shape_id"} (worker_call_specs.hpp:20-34): the ids handed back with every
+ * progress report (isd_set_progress_callback below), the native stand-in for send_mesh_back_to_client
+ * (polygonizer_algorithm_ob02.hpp:180-220). */
 void build_geometry_u(const char* shape_parameters_json, const char* mc_parameters_json, const char* call_specs);
 int get_v_size(void);              /* mcc2.cpp:470-473  number of vertices  */
 int get_f_size(void);              /* mcc2.cpp:466-469  number of triangles */
@@ -60,6 +62,27 @@ int get_pointset_size(char* id);   /* mcc2.cpp:210-215  always 0 */
 void about(void);                  /* mcc2.cpp:574-617 */
 
 /* ---- group 4: extensions (ours) ------------------------------------------------------------ */
+/* Progressive results (SURVEY §8 f-N3).  The reference reports the mesh back to its JS client after marching cubes, after
+ * the resampling iterations and after the projection of every repeat (mcc2.cpp:351,372,390 -> send_mesh_back_to_client,
+ * polygonizer_algorithm_ob02.hpp:180-220, an EM_ASM block with no native meaning).  Natively the same three points call
+ * `fn` with host pointers to the current mesh (what get_v_ptr/get_f_ptr return at that moment) and the ids of
+ * build_geometry_u's call_specs (-1 for build_geometry).  NULL (the default) disables reporting and its copies. */
+typedef void (*isd_progress_fn)(const REAL* verts, int nverts, const int* faces, int nfaces, int progress_callback_id,
+                                int shape_id, int call_id, void* user);
+void isd_set_progress_callback(isd_progress_fn fn, void* user);
+
+/* Per-vertex normals of the last build (SURVEY §8 f-N2): -grad f/|grad f| at the final vertices with the -42 rule of
+ * calculate_implicit_gradients(true) (mcc2.cpp:852-870) — what the JS flow asks for after every build through
+ * set_object/set_x/calculate_implicit_gradients (implisolid_main.js:551-600), without the second tree upload, the
+ * 50 000-point cap of set_x (mcc2.cpp:770-773) or the round trip.  Computed on the device right after the last step when
+ * mc_parameters_json holds "gpu":{"normals":1}, otherwise on first use.  3*Nv floats; valid until the next build. */
+void* isd_get_n_ptr(void);
+void isd_get_n(REAL* n_out, int vcount);
+const REAL* isd_device_normals(void);
+
+/* polygonize_step_3's noise uses libc rand(), never seeded (basic_functions.hpp:551-557): the library keeps a private
+ * glibc-compatible generator that starts like srand(1) and runs on across builds as the reference's does; this resets it. */
+void isd_srand(unsigned seed);
 /* Device selection / lifetime.  isd_init is implicit on first use (device = $ISD_DEVICE or
  * $LOCAL_RANK or 0).  Returns 0 on success; any failure aborts. */
 int isd_init(int device);

@@ -17,6 +17,7 @@
 #include <vector>
 #include "omc.hpp"
 #include "oob02.hpp"
+#include "osubdiv.hpp"
 
 using namespace oracle;
 
@@ -120,6 +121,18 @@ Env make_env(int cube_mode) {
     return e;
 }
 
+// send_mesh_back_to_client (polygonizer_algorithm_ob02.hpp:180-220): the EM_ASM block hands the JS client typed-array views on
+// _state.mc_result_verts / faces plus the three ids of worker_call_sepcs_t; here a C callback receives the same.
+typedef void (*progress_fn_t)(const REAL*, int, const int*, int, int, int, int, void*);
+progress_fn_t g_progress = nullptr;
+void* g_progress_user = nullptr;
+int g_call_specs[3] = {-1, -1, -1};      // progress_callback_id, shape_id, call_id
+void send_mesh_back_to_client() {
+    if (!g_progress) return;
+    g_progress(_state.mc_result_verts.data(), (int)(_state.mc_result_verts.size() / 3), _state.mc_result_faces.data(),
+               (int)(_state.mc_result_faces.size() / 3), g_call_specs[0], g_call_specs[1], g_call_specs[2], g_progress_user);
+}
+
 void grand_algorithm(const char* shape_json, const mc_settings& s) {
     if (_state.active) {
         std::clog << "Error: There are non-deallocated geometry resources. Call finit_geometry() first. Not doing anything.";
@@ -140,15 +153,18 @@ void grand_algorithm(const char* shape_json, const mc_settings& s) {
         g_keys = std::move(mc.result_keys);
         g_S = mc.S;
     }
+    send_mesh_back_to_client();                                                                  // mcc2.cpp:351
     for (int overall_iter = 0; overall_iter < s.overall_repeats; ++overall_iter) {
         for (int i = 0; i < s.vresampl.iters; i++)
             vertex_resampling(*object, s.vresampl.c, _state.mc_result_verts, _state.mc_result_faces);   // polygonize_step_1
-        if (s.projection.enabled)
+        send_mesh_back_to_client();                                                              // mcc2.cpp:372
+        if (s.projection.enabled) {
             centroids_projection(*object, _state.mc_result_verts, _state.mc_result_faces, s.qem.enabled, &g_stats, &g_proj);
-        const bool is_last = overall_iter == s.overall_repeats - 1;
-        if (s.subdiv.enabled && (s.overall_repeats <= 1 || is_last)) {
-            if (!g_quiet) std::clog << "oracle: subdivision (step 3) is out of scope and skipped" << std::endl;
+            send_mesh_back_to_client();                                                          // mcc2.cpp:390
         }
+        const bool is_last = overall_iter == s.overall_repeats - 1;
+        if (s.subdiv.enabled && (s.overall_repeats <= 1 || is_last))                             // mcc2.cpp:396-410
+            polygonize_step_3(_state.mc_result_verts, _state.mc_result_faces, s.debug.post_subdiv_noise, is_last);
     }
     _state.active = true;   // polygonize_terminate
 }
@@ -169,8 +185,34 @@ void build_geometry(const char* shape_parameters_json, const char* mc_parameters
     mc_settings s = parse_mc_properties_json(mc_parameters_json);
     grand_algorithm(shape_parameters_json, s);
 }
-void build_geometry_u(const char* shape_parameters_json, const char* mc_parameters_json, const char*) {
+void build_geometry_u(const char* shape_parameters_json, const char* mc_parameters_json, const char* call_specs) {
+    if (call_specs && *call_specs) {                 // worker_call_specs.hpp:20-34
+        ojson::Node d = ojson::parse(call_specs);
+        g_call_specs[0] = d.get_int("progressCallback_id", -1);
+        g_call_specs[2] = d.get_int("call_id", -1);
+        g_call_specs[1] = d.get_int("shape_id", -1);
+    }
     build_geometry(shape_parameters_json, mc_parameters_json);
+    g_call_specs[0] = g_call_specs[1] = g_call_specs[2] = -1;
+}
+void oracle_set_progress_callback(progress_fn_t fn, void* user) { g_progress = fn; g_progress_user = user; }
+void oracle_srand(unsigned seed) { subdiv_rand().seed(seed); }
+// the private generator against libc's own rand() (test_oracle_known_answers.py): number of mismatches in n draws after srand(seed)
+int oracle_rand_check(unsigned seed, int n) {
+    GlibcRand g;
+    g.seed(seed);
+    srand(seed);
+    int bad = 0;
+    for (int i = 0; i < n; i++) bad += (g.next() != rand());
+    return bad;
+}
+void oracle_subdivide(float* verts_in, int nv, const int* faces_in, int nf, float* verts_out, int* faces_out, int* nv_out) {
+    std::vector<REAL> v(verts_in, verts_in + (size_t)nv * 3);
+    std::vector<int> f(faces_in, faces_in + (size_t)nf * 3);
+    subdivide_all_1to4(v, f);
+    *nv_out = (int)(v.size() / 3);
+    std::copy(v.begin(), v.end(), verts_out);
+    std::copy(f.begin(), f.end(), faces_out);
 }
 int get_f_size() { return (int)(_state.mc_result_faces.size() / 3); }
 int get_v_size() { return (int)(_state.mc_result_verts.size() / 3); }

@@ -13,6 +13,9 @@ EMU_DIR = os.path.join(ROOT, "tests", "emu")
 
 
 class Oracle(GeometryLibrary):
+    progress_symbol = "oracle_set_progress_callback"
+    srand_symbol = "oracle_srand"
+
     def __init__(self, path):
         super().__init__(path, extensions=False)
         L = self.lib
