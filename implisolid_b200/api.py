@@ -90,6 +90,9 @@ EXT_SIGNATURES = {
     "isd_dist_set_offsets": (None, [ctypes.c_int64, ctypes.c_int64]),
     "isd_dist_last_slab": (ctypes.c_int, [ctypes.c_void_p]),
     "isd_dist_gather_mesh": (None, []),
+    "isd_dist_set_edge_total": (None, [ctypes.c_uint64, ctypes.c_int64]),
+    "isd_dist_last_edge_sum": (ctypes.c_uint64, []),
+    "isd_dist_last_halo": (ctypes.c_int, []),
 }
 
 TIMING_NAMES = ["field", "classify_scan", "emit", "resample", "project", "qem", "d2h", "total_host", "subdiv", "gather"]

@@ -40,6 +40,7 @@ struct NcclApi {
     int (*CommInitRank)(void**, int, unique_id, int) = nullptr;
     int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
     int (*Broadcast)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
     int (*GroupStart)() = nullptr;
     int (*GroupEnd)() = nullptr;
     int (*CommDestroy)(void*) = nullptr;
@@ -59,6 +60,7 @@ struct NcclApi {
         ISD_NCCL_SYM(CommInitRank, "ncclCommInitRank");
         ISD_NCCL_SYM(AllGather, "ncclAllGather");
         ISD_NCCL_SYM(Broadcast, "ncclBroadcast");
+        ISD_NCCL_SYM(AllReduce, "ncclAllReduce");
         ISD_NCCL_SYM(GroupStart, "ncclGroupStart");
         ISD_NCCL_SYM(GroupEnd, "ncclGroupEnd");
         ISD_NCCL_SYM(CommDestroy, "ncclCommDestroy");
@@ -73,7 +75,8 @@ struct NcclApi {
         }
     }
 };
-constexpr int kNcclInt64 = 4, kNcclFloat32 = 7, kNcclInt32 = 2;   // ncclDataType_t values (nccl.h)
+constexpr int kNcclInt64 = 4, kNcclUint64 = 5, kNcclFloat32 = 7, kNcclInt32 = 2;   // ncclDataType_t values (nccl.h)
+constexpr int kNcclSum = 0;                                                        // ncclRedOp_t
 
 // ---------------------------------------------------------------------------------------------------------------------
 // process-wide state (the reference keeps one global state_t _state, mcc2.cpp:165-193)
@@ -143,6 +146,15 @@ struct Context {
     DeviceBuffer d_gather;
     int64_t slab[8] = {0};
     bool gathered = false;
+    // halo mode (sharded OB02 without a mesh exchange): the GPU holds a LOCAL mesh of its slab plus `halo` recomputed cube
+    // layers on either side, numbered from 0 in scan order (ghost-layer vertices first, never written); the slab's own part is
+    // the contiguous range [own_v0, own_v1) x [own_f0, own_f1) and global index = local index + (global offset - own_*0).
+    bool halo_mode = false, halo_pending = false;
+    int halo = 0, own_zb = 0, own_ze = 0;
+    long long own_v0 = 0, own_v1 = 0, own_f0 = 0, own_f1 = 0;
+    unsigned long long emu_edge_total = 0;      // emulated ranks: the global fixed-point edge sum and face count
+    long long emu_gnf = 0;
+    unsigned long long last_edge_sum = 0;       // this GPU's share of the fixed-point edge sum (own faces only)
 
     // direct evaluation service (mcc2.cpp:699-705)
     bool svc_object = false;
@@ -236,6 +248,20 @@ void setup_grid(const McSettings& s) {
     gd.xi0 = s.box.xmin / gd.wx - 2; gd.yi0 = s.box.ymin / gd.wy - 2; gd.zi0 = s.box.zmin / gd.wz - 2;
     int zb, ze;
     slab_layers(S, g.rank, g.world, &zb, &ze);
+    g.own_zb = zb; g.own_ze = ze;
+    g.halo_mode = false;
+    g.halo = 0;
+    if (g.world > 1 && s.halo != 0 && s.overall_repeats > 0 && (s.vresampl_iters > 0 || s.projection_enabled) && !s.exact_reduce &&
+        !s.subdiv_enabled && !g.progress_fn) {
+        // Dependency radius in cube layers: a resampling iteration moves a vertex from the centroids, normals and
+        // neighbour-face curvatures of its umbrella (2 layers of input around it), projection + QEM from the faces around it
+        // (1 layer); one more layer because the lowest halo layer's faces hang on ghost vertices that are never written.
+        const int per_repeat = 2 * s.vresampl_iters + ((s.projection_enabled && s.qem_enabled) ? 1 : 0);
+        g.halo = s.halo > 0 ? s.halo : s.overall_repeats * per_repeat + 1;
+        g.halo_mode = true;
+        zb = (zb - g.halo > 1) ? zb - g.halo : 1;
+        ze = (ze + g.halo < S - 2) ? ze + g.halo : S - 2;
+    }
     McDesc& m = g.mc;
     m.emit_z0 = zb;
     m.zc_end = ze;
@@ -378,6 +404,11 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     }
     // totals back to the host: sizes of the vertex, face and cut-cube arrays (+ the ghost layer's share, z-slabs only)
     ISD_CUDA(cudaMemcpyAsync(h, g.d_totals.ptr, 10 * sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));      // [8] = work-list length
+    const long long own_row0 = (long long)(g.own_zb - m.scan_z0) * m.NX, own_row1 = (long long)(g.own_ze - m.scan_z0) * m.NX;
+    if (g.halo_mode) {      // vertices / faces counted before the slab's first own row and before the first row above it
+        ISD_CUDA(cudaMemcpyAsync(h + 16, mb.row_base + own_row0, sizeof(Triple), cudaMemcpyDeviceToHost, g.stream));
+        if (own_row1 < n_rows) ISD_CUDA(cudaMemcpyAsync(h + 20, mb.row_base + own_row1, sizeof(Triple), cudaMemcpyDeviceToHost, g.stream));
+    }
     ISD_CUDA(cudaStreamSynchronize(g.stream));
     const unsigned n_cubes = h[2];
     if (m.ghost_rows == 0) { h[4] = 0; h[5] = 0; }
@@ -391,12 +422,32 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     ISD_CUDA(cudaEventRecord(g.ev[2], g.stream));
     const long long scan_v = h[0], scan_f = h[1];
     const long long ghost_v = h[4], ghost_f = h[5];
-    const long long nv = scan_v - ghost_v, nf = scan_f - ghost_f;
+    long long nv = scan_v - ghost_v, nf = scan_f - ghost_f;
+    if (g.halo_mode) {      // what the slab owns, and what it tells the others
+        g.own_v0 = h[16]; g.own_f0 = h[17];
+        g.own_v1 = (own_row1 < n_rows) ? h[20] : scan_v;
+        g.own_f1 = (own_row1 < n_rows) ? h[21] : scan_f;
+        nv = g.own_v1 - g.own_v0; nf = g.own_f1 - g.own_f0;
+    }
 
     long long voff = 0, foff = 0, gnv = nv, gnf = nf;
+    g.halo_pending = false;
     if (g.world > 1) {
         if (g.emulate) {
+            if (g.halo_mode) { gnv = -1; gnf = g.emu_gnf; }
             voff = g.emu_voff; foff = g.emu_foff;
+        } else if (g.halo_mode) {
+            // the collective is only needed when the slab is exported (global indices) and by the mean edge length: it is
+            // enqueued here and read back at the end of the step, so nothing waits for the slowest rank in between
+            g.d_gather.reserve((size_t)g.world * 2 * sizeof(int64_t) + 64);
+            int64_t* dg = g.d_gather.as<int64_t>();
+            int64_t* hs = reinterpret_cast<int64_t*>(g.h_small.as<char>() + 256);
+            hs[0] = nv; hs[1] = nf;
+            ISD_CUDA(cudaMemcpyAsync(dg + 2 * g.world, hs, 2 * sizeof(int64_t), cudaMemcpyHostToDevice, g.stream));
+            g.nccl.check(g.nccl.AllGather(dg + 2 * g.world, dg, 2, kNcclInt64, g.comm, g.stream), "ncclAllGather");
+            ISD_CUDA(cudaMemcpyAsync(hs + 2, dg, (size_t)g.world * 2 * sizeof(int64_t), cudaMemcpyDeviceToHost, g.stream));
+            g.halo_pending = true;
+            gnv = -1; gnf = -1;
         } else {
             // the one collective of the path: {nv, nf} of every slab (16 bytes per rank)
             g.d_gather.reserve((size_t)g.world * 2 * sizeof(int64_t) + 64);
@@ -418,15 +469,18 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         fprintf(stderr, "implisolid_b200: mesh too large for 32-bit indices (%lld vertices, %lld faces)\n", gnv, gnf);
         abort();
     }
-    const bool in_place = g.world > 1 && !g.emulate;      // room for every slab: the gather is then a set of in-place broadcasts
+    const bool in_place = g.world > 1 && !g.emulate && !g.halo_mode;      // room for every slab: the gather is then a set of in-place broadcasts
     g.local_voff = in_place ? voff : 0;
     g.local_foff = in_place ? foff : 0;
-    g.d_verts.reserve((size_t)((in_place ? gnv : nv) > 0 ? (in_place ? gnv : nv) : 1) * 3 * sizeof(float));
-    g.d_faces.reserve((size_t)((in_place ? gnf : nf) > 0 ? (in_place ? gnf : nf) : 1) * 3 * sizeof(int));
+    const long long store_v = g.halo_mode ? scan_v : (in_place ? gnv : nv), store_f = g.halo_mode ? scan_f - ghost_f : (in_place ? gnf : nf);
+    g.d_verts.reserve((size_t)(store_v > 0 ? store_v : 1) * 3 * sizeof(float));
+    g.d_faces.reserve((size_t)(store_f > 0 ? store_f : 1) * 3 * sizeof(int));
+    if (g.halo_mode && ghost_v > 0) ISD_CUDA(cudaMemsetAsync(g.d_verts.ptr, 0, (size_t)ghost_v * 3 * sizeof(float), g.stream));
     if (n_cubes > 0) {   // K4
         EmitArgs ea;
         ea.vbase = voff - ghost_v; ea.fbase = foff - ghost_f;
         ea.v_local0 = ghost_v; ea.f_local0 = ghost_f;
+        if (g.halo_mode) { ea.vbase = 0; ea.fbase = 0; ea.v_local0 = 0; }      // local numbering = scan order, ghost vertices first
         unsigned blocks = (n_cubes + kEmitThreads - 1) / kEmitThreads;
         if (blocks > (unsigned)g.sm_count * 16u) blocks = (unsigned)g.sm_count * 16u;
         k_mc_emit<<<blocks, kEmitThreads, 0, g.stream>>>(m, mb, ea, g.d_field.as<float>(), g.d_signs.as<uint32_t>(),
@@ -436,8 +490,12 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     }
     ISD_CUDA(cudaEventRecord(g.ev[3], g.stream));
     g.nv = nv; g.nf = nf;
+    if (g.halo_mode) {      // the local mesh the OB02 stages work on; export_own_slab() narrows it to the slab afterwards
+        g.nv = scan_v; g.nf = scan_f - ghost_f;
+        g.own_f0 -= ghost_f; g.own_f1 -= ghost_f;
+    }
     g.gathered = false;
-    g.slab[0] = m.emit_z0; g.slab[1] = m.zc_end; g.slab[2] = voff; g.slab[3] = foff;
+    g.slab[0] = g.own_zb; g.slab[1] = g.own_ze; g.slab[2] = voff; g.slab[3] = foff;
     g.slab[4] = nv; g.slab[5] = nf; g.slab[6] = gnv; g.slab[7] = gnf;
     g.counters[0] = (int64_t)gd.S * gd.S * gd.nz;
     g.counters[1] = (int64_t)(m.zc_end - m.emit_z0) * m.NX * m.NX;
@@ -453,6 +511,14 @@ void gather_mesh() {
     int64_t* hs = reinterpret_cast<int64_t*>(g.h_small.as<char>() + 256);
     const long long gnv = g.slab[6], gnf = g.slab[7];
     ISD_CUDA(cudaEventRecord(g.ev[13], g.stream));
+    if (g.halo_mode) {      // the exported slab sits inside local arrays: move it to its global offset in arrays sized for the whole mesh
+        g.d_verts2.reserve((size_t)(gnv > 0 ? gnv : 1) * 3 * sizeof(float));
+        g.d_faces2.reserve((size_t)(gnf > 0 ? gnf : 1) * 3 * sizeof(int));
+        if (g.nv) ISD_CUDA(cudaMemcpyAsync(g.d_verts2.as<float>() + g.slab[2] * 3, g.d_verts.as<float>() + g.local_voff * 3, (size_t)g.nv * 3 * sizeof(float), cudaMemcpyDeviceToDevice, g.stream));
+        if (g.nf) ISD_CUDA(cudaMemcpyAsync(g.d_faces2.as<int>() + g.slab[3] * 3, g.d_faces.as<int>() + g.local_foff * 3, (size_t)g.nf * 3 * sizeof(int), cudaMemcpyDeviceToDevice, g.stream));
+        std::swap(g.d_verts, g.d_verts2);
+        std::swap(g.d_faces, g.d_faces2);
+    }
     g.nccl.check(g.nccl.GroupStart(), "ncclGroupStart");
     long long vo = 0, fo = 0;
     for (int r = 0; r < g.world; ++r) {      // in place: every rank's slab already sits at its global offset
@@ -581,6 +647,27 @@ struct Mt11213b {
     }
 };
 
+// Halo mode: global offsets of the slab (slab[2], slab[3]) and global sizes (slab[6], slab[7]) from the all-gather enqueued after
+// the scan; waits for it if nobody has yet.
+void resolve_halo_offsets() {
+    if (!g.halo_mode) return;
+    if (g.emulate) { g.slab[2] = g.emu_voff; g.slab[3] = g.emu_foff; g.slab[6] = -1; g.slab[7] = g.emu_gnf; return; }
+    if (!g.halo_pending) return;
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    const int64_t* hs = reinterpret_cast<const int64_t*>(g.h_small.as<char>() + 256);
+    long long voff = 0, foff = 0, gnv = 0, gnf = 0;
+    for (int r = 0; r < g.world; ++r) {
+        if (r == g.rank) { voff = gnv; foff = gnf; }
+        gnv += hs[2 + 2 * r]; gnf += hs[3 + 2 * r];
+    }
+    g.halo_pending = false;
+    if (gnv >= (1ll << 31) || gnf >= (1ll << 31)) {
+        fprintf(stderr, "implisolid_b200: mesh too large for 32-bit indices (%lld vertices, %lld faces)\n", gnv, gnf);
+        abort();
+    }
+    g.slab[2] = voff; g.slab[3] = foff; g.slab[6] = gnv; g.slab[7] = gnf;
+}
+
 // make_random_pm1(n, 3, 1e-6) seeds a fresh mt11213b(12) on every call (make_random_pm1.hpp:15-28), so draw j is the same
 // number in every build: the stream is generated once (sequentially, on the host: a Mersenne twister with data-dependent
 // rejections in uniform_01) and kept in HBM; a larger mesh only generates the tail it is missing.
@@ -610,11 +697,15 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     if (nf == 0) return;
     ISD_CUDA(cudaEventRecord(g.ev[6], g.stream));
     const unsigned prep_blocks = blocks_for(nf, 256);
-    g.d_scal.reserve(sizeof(AlphaList) + (size_t)prep_blocks * sizeof(double) + 64);
+    {
+        const void* before = g.d_scal.ptr;
+        g.d_scal.reserve(sizeof(AlphaList) + (size_t)prep_blocks * sizeof(unsigned long long) + 64);
+        if (g.d_scal.ptr != before) g.alpha_ticket_zeroed = false;      // a fresh allocation holds a garbage ticket
+    }
     g.d_counters.reserve(sizeof(Ob02Counters));
     g.d_cen.reserve((size_t)nf * 3 * sizeof(float) + 16);
     AlphaList* d_al = g.d_scal.as<AlphaList>();
-    double* d_partials = reinterpret_cast<double*>(g.d_scal.as<char>() + ((sizeof(AlphaList) + 15) & ~(size_t)15));
+    unsigned long long* d_partials = reinterpret_cast<unsigned long long*>(g.d_scal.as<char>() + ((sizeof(AlphaList) + 15) & ~(size_t)15));
     if (!g.alpha_ticket_zeroed) {      // the last block of k_face_prepare leaves the ticket at zero again
         ISD_CUDA(cudaMemsetAsync(d_al, 0, sizeof(AlphaList), g.stream));
         g.alpha_ticket_zeroed = true;
@@ -625,8 +716,27 @@ void projection_step(bool enable_qem, bool exact_reduce) {
         d_len3 = g.d_len3.as<float>();
     }
     // centroids + mean edge length + alpha list, all on the device (centroids_projection.cpp:1230-1245)
-    k_face_prepare<<<prep_blocks, 256, 0, g.stream>>>(g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(), d_len3, d_partials, d_al);
-    ISD_LAUNCH_CHECK();
+    if (g.halo_mode) {
+        // only the slab's own faces are summed; the all-reduce (8 bytes) gives every GPU the whole mesh's sum, in the stream
+        k_face_prepare<<<prep_blocks, 256, 0, g.stream>>>(g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(), d_len3, d_partials, d_al,
+                                                          (int)g.own_f0, (int)g.own_f1, 0);
+        ISD_LAUNCH_CHECK();
+        if (g.emulate) {
+            ISD_CUDA(cudaMemcpyAsync(&g.last_edge_sum, &d_al->edge_sum, sizeof(unsigned long long), cudaMemcpyDeviceToHost, g.stream));
+            ISD_CUDA(cudaMemcpyAsync(&d_al->edge_total, &g.emu_edge_total, sizeof(unsigned long long), cudaMemcpyHostToDevice, g.stream));
+            k_alpha_from_sum<<<1, 1, 0, g.stream>>>(d_al, &d_al->edge_total, nullptr, g.world, g.emu_gnf);
+        } else {
+            g.nccl.check(g.nccl.AllReduce(&d_al->edge_sum, &d_al->edge_total, 1, kNcclUint64, kNcclSum, g.comm, g.stream), "ncclAllReduce");
+            k_alpha_from_sum<<<1, 1, 0, g.stream>>>(d_al, &d_al->edge_total, reinterpret_cast<const long long*>(g.d_gather.as<int64_t>()), g.world, 0);
+        }
+        ISD_LAUNCH_CHECK();
+    } else {
+        k_face_prepare<<<prep_blocks, 256, 0, g.stream>>>(g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(), d_len3, d_partials, d_al,
+                                                          0, nf, 1);
+        ISD_LAUNCH_CHECK();
+        if (g.world == 1 || g.emulate)      // the sum of a whole mesh: what emulated ranks are handed as the all-reduce result
+            ISD_CUDA(cudaMemcpyAsync(&g.last_edge_sum, &d_al->edge_sum, sizeof(unsigned long long), cudaMemcpyDeviceToHost, g.stream));
+    }
     if (exact_reduce) {
         k_sum_serial_float<<<1, 32, 0, g.stream>>>(d_len3, (long long)nf * 3, nf, &d_al->avg_edge);
         ISD_LAUNCH_CHECK();
@@ -672,7 +782,10 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     if (hc->c[10] > 0) {
         // rare: direction types 2..6 for the left-overs; type 2 needs make_random_pm1(n, 1e-6), centroid i <- draws 3i..3i+2
         ISD_CUDA(cudaEventRecord(g.ev[6], g.stream));
-        a.noise = noise_stream((size_t)nf * 3);
+        // centroid i draws 3i..3i+2 of the stream, i being the face's index in the WHOLE mesh
+        long long face_base = 0;
+        if (g.halo_mode) { resolve_halo_offsets(); face_base = g.slab[3] - g.own_f0; }
+        a.noise = noise_stream((size_t)(face_base + nf) * 3) + face_base * 3;
         a.speculative = 0;
         k_project_search<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a, 1);
         ISD_LAUNCH_CHECK();
@@ -803,6 +916,24 @@ void report_progress() {
     g.host_valid = false;       // the next step changes the mesh
 }
 
+// Halo mode, end of the step: the collective enqueued after the scan has long finished; the slab's own vertices are a
+// contiguous range of the local arrays and its own faces only need the constant shift to global indices.
+void export_own_slab() {
+    if (!g.halo_mode) return;
+    resolve_halo_offsets();
+    const long long voff = g.slab[2], foff = g.slab[3], gnv = g.slab[6], gnf = g.slab[7];
+    const long long own_nv = g.own_v1 - g.own_v0, own_nf = g.own_f1 - g.own_f0;
+    if (own_nf > 0) {
+        k_rebase_faces<<<blocks_for(own_nf * 3, 256), 256, 0, g.stream>>>(g.d_faces.as<int>() + g.own_f0 * 3, own_nf * 3, (int)(voff - g.own_v0));
+        ISD_LAUNCH_CHECK();
+    }
+    g.local_voff = g.own_v0; g.local_foff = g.own_f0;
+    g.nv = own_nv; g.nf = own_nf;
+    g.adjacency_valid = false; g.fof_valid_ = false;      // they describe the local mesh, which is gone
+    g.host_valid = false;
+    g.slab[2] = voff; g.slab[3] = foff; g.slab[4] = own_nv; g.slab[5] = own_nf; g.slab[6] = gnv; g.slab[7] = gnf;
+}
+
 // faces do not change after marching cubes: start their device->host copy now, on the side stream
 void start_faces_copy() {
     if (g.nf == 0) return;
@@ -849,6 +980,7 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     g.proj_n = 0;
     g.normals_valid = false;
     g.normals_host_valid = false;
+    g.last_edge_sum = 0;
     ShapeCompiler::Program prog = compile_shape(shape_json, s.ignore_root_matrix, s.cube_mode);
     upload_program(prog.words);
     g.last_program = prog.words;
@@ -857,9 +989,9 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     g.keep_field = true;
     run_marching_cubes(s, prog);                                   // polygonize_step_0
     const bool any_ob02 = s.overall_repeats > 0 && (s.vresampl_iters > 0 || s.projection_enabled || s.subdiv_enabled);
-    if (any_ob02 && g.world > 1 && !g.emulate) gather_mesh();      // OB02 runs on the stitched mesh, replicated
+    if (any_ob02 && g.world > 1 && !g.emulate && !g.halo_mode) gather_mesh();      // OB02 runs on the stitched mesh, replicated
     const bool faces_final = !(s.overall_repeats > 0 && s.subdiv_enabled) && !g.progress_fn;
-    if (copy_out && any_ob02 && faces_final) start_faces_copy();
+    if (copy_out && any_ob02 && faces_final && !g.halo_mode) start_faces_copy();
     report_progress();                                             // mcc2.cpp:351
     bool resample_timed = false, subdiv_timed = false;
     for (int overall_iter = 0; overall_iter < s.overall_repeats; ++overall_iter) {
@@ -875,7 +1007,7 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
             report_progress();                                                             // mcc2.cpp:390
         }
         if (resample_timed && (s.projection_enabled || s.overall_repeats > 1)) {          // events are reused by the next repeat
-            if (!s.projection_enabled) ISD_CUDA(cudaStreamSynchronize(g.stream));
+            ISD_CUDA(cudaEventSynchronize(g.ev[5]));      // (projection_step has waited for the stream unless the mesh is empty)
             float ms = 0;
             ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[4], g.ev[5]));
             g.timings[T_RESAMPLE] += ms;
@@ -888,6 +1020,7 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
             subdiv_timed = true;
         }
     }
+    export_own_slab();
     ISD_CUDA(cudaStreamSynchronize(g.stream));
     float ms = 0;
     if (resample_timed) { ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[4], g.ev[5])); g.timings[T_RESAMPLE] += ms; }
@@ -1239,5 +1372,8 @@ int isd_dist_last_slab(int64_t* out8) {
     return 0;
 }
 void isd_dist_gather_mesh(void) { gather_mesh(); }
+void isd_dist_set_edge_total(uint64_t edge_total_fixed_point, int64_t global_faces) { g.emu_edge_total = edge_total_fixed_point; g.emu_gnf = global_faces; }
+uint64_t isd_dist_last_edge_sum(void) { return g.last_edge_sum; }
+int isd_dist_last_halo(void) { return g.halo_mode ? g.halo : 0; }
 
 }  // extern "C"

@@ -29,6 +29,8 @@ struct AlphaList {
     int n_full, n_short;
     float avg_edge;
     unsigned ticket;          // last-block-done counter of k_face_prepare
+    unsigned long long edge_sum;      // fixed-point (2^-32) sum of the edge lengths k_face_prepare was asked to sum
+    unsigned long long edge_total;    // z-slab runs: the all-reduced sum
 };
 __device__ inline void make_alpha_list(float initial_step_size, float min_step_size, float max_dist, int max_iter, AlphaList* out) {
     const float unit_of_length = max_dist;
@@ -318,15 +320,19 @@ __global__ void __launch_bounds__(256) k_sum_double(const float* __restrict__ v,
 __global__ void k_finish_average(const double* __restrict__ acc, int nf, float* __restrict__ out) { *out = (float)(*acc / (3. * nf)); }
 
 // Projection prologue in one launch: centroids, the three edge lengths per face (compute_average_edge_length,
-// centroids_projection.cpp:70-82) summed in double — per block, then by the last block to finish in block order, so the
-// result does not depend on scheduling — the mean edge, and the alpha list.  `len3` (optional) keeps the lengths for the
-// reference-order serial float sum (exact_reduce), which then overwrites the mean and rebuilds the list.
+// centroids_projection.cpp:70-82), the mean edge and the alpha list.  The lengths are summed in 64-bit fixed point (quantum
+// 2^-32): integer addition is associative, so the mean does not depend on block scheduling NOR on how a z-slab run splits
+// the faces between GPUs — one GPU and eight give the same bits.  Only faces in [sum_f0, sum_f1) are summed (a slab's own
+// faces; its halo faces belong to the neighbours' sums).  With `finish` the last block turns the sum into the mean over `nf`
+// faces and builds the list; without, the sum is left in al->edge_sum for the all-reduce and k_alpha_from_sum.
+// `len3` (optional) keeps the lengths for the reference-order serial float sum (exact_reduce), which then overwrites the mean.
 __global__ void __launch_bounds__(256) k_face_prepare(const float* __restrict__ verts, const int* __restrict__ faces, int nf, float* __restrict__ cen,
-                                                      float* __restrict__ len3, double* __restrict__ partials, AlphaList* __restrict__ al) {
-    __shared__ double s[8];
+                                                      float* __restrict__ len3, unsigned long long* __restrict__ partials, AlphaList* __restrict__ al,
+                                                      int sum_f0, int sum_f1, int finish) {
+    __shared__ unsigned long long s[8];
     __shared__ bool s_last;
     const int j = blockIdx.x * 256 + threadIdx.x;
-    double t = 0.0;
+    unsigned long long t = 0ull;
     if (j < nf) {
         const int f0 = faces[j * 3], f1 = faces[j * 3 + 1], f2 = faces[j * 3 + 2];
         const float* a = verts + f0 * 3; const float* b = verts + f1 * 3; const float* c = verts + f2 * 3;
@@ -336,14 +342,15 @@ __global__ void __launch_bounds__(256) k_face_prepare(const float* __restrict__ 
         const float l1 = norm2f(a[0] - c[0], a[1] - c[1], a[2] - c[2]);
         const float l2 = norm2f(c[0] - b[0], c[1] - b[1], c[2] - b[2]);
         if (len3 != nullptr) { len3[j * 3] = l0; len3[j * 3 + 1] = l1; len3[j * 3 + 2] = l2; }
-        t = (double)l0 + (double)l1 + (double)l2;
+        const double sum3 = (double)l0 + (double)l1 + (double)l2;
+        if (j >= sum_f0 && j < sum_f1 && sum3 < 2147483648.0) t = (unsigned long long)__double2ll_rn(sum3 * 4294967296.0);
     }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) t += __shfl_xor_sync(0xffffffffu, t, d);
     if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = t;
     __syncthreads();
     if (threadIdx.x == 0) {
-        double b = 0.0;
+        unsigned long long b = 0ull;
         for (int i = 0; i < 8; ++i) b += s[i];
         partials[blockIdx.x] = b;
         __threadfence();
@@ -352,20 +359,36 @@ __global__ void __launch_bounds__(256) k_face_prepare(const float* __restrict__ 
     __syncthreads();
     if (!s_last) return;
     __threadfence();
-    double acc = 0.0;
-    for (unsigned i = threadIdx.x; i < gridDim.x; i += 256) acc += ((volatile double*)partials)[i];
+    unsigned long long acc = 0ull;
+    for (unsigned i = threadIdx.x; i < gridDim.x; i += 256) acc += ((volatile unsigned long long*)partials)[i];
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
     if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = acc;
     __syncthreads();
     if (threadIdx.x == 0) {
-        double b = 0.0;
+        unsigned long long b = 0ull;
         for (int i = 0; i < 8; ++i) b += s[i];
-        const float avg = (float)(b / (3. * nf));
-        al->avg_edge = avg;
-        make_alpha_list(avg, 0.001f, avg, 20, al);
+        al->edge_sum = b;
         al->ticket = 0u;
+        if (finish) {
+            const float avg = (float)(((double)b * (1.0 / 4294967296.0)) / (3. * nf));
+            al->avg_edge = avg;
+            make_alpha_list(avg, 0.001f, avg, 20, al);
+        }
     }
+}
+// z-slab runs: the mean over the whole mesh from the all-reduced sum; the face count is the sum of every slab's count
+// (`counts` = the all-gathered {nv, nf} pairs) or `nf_fixed` when emulating ranks on one GPU
+__global__ void k_alpha_from_sum(AlphaList* __restrict__ al, const unsigned long long* __restrict__ total, const long long* __restrict__ counts,
+                                 int world, long long nf_fixed) {
+    long long nf = nf_fixed;
+    if (counts != nullptr) {
+        nf = 0;
+        for (int r = 0; r < world; ++r) nf += counts[2 * r + 1];
+    }
+    const float avg = (float)(((double)*total * (1.0 / 4294967296.0)) / (3. * (double)nf));
+    al->avg_edge = avg;
+    make_alpha_list(avg, 0.001f, avg, 20, al);
 }
 // exact_reduce: the alpha list again, from the serial float mean
 __global__ void k_alpha_from_mean(const float* __restrict__ mean, AlphaList* __restrict__ al) {

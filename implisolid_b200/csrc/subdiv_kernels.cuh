@@ -78,3 +78,12 @@ __global__ void __launch_bounds__(256) k_add_noise(float* __restrict__ verts, lo
 }
 
 }  // namespace isd
+
+namespace isd {
+// z-slab halo mode: a slab's own faces leave the local numbering (scan order of the slab plus its halo) for the global one,
+// a constant shift because both are scan order.
+__global__ void __launch_bounds__(256) k_rebase_faces(int* __restrict__ faces, long long n, int delta) {
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i < n) faces[i] += delta;
+}
+}  // namespace isd

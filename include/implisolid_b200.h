@@ -151,6 +151,13 @@ int isd_dist_last_slab(int64_t* out8);
 /* Gather the stitched mesh on every rank (ncclAllGather of padded ranges); afterwards get_v/get_f
  * return the global mesh on every rank. */
 void isd_dist_gather_mesh(void);
+/* z-slab runs with OB02 ("halo mode"): every GPU optimises its own slab plus a halo of recomputed cube layers,
+ * the only exchanges being the {nv,nf} all-gather and an 8-byte all-reduce of the fixed-point edge-length sum.  When ranks
+ * are emulated on one GPU (isd_dist_emulate) the test driver plays the all-reduce: it hands every rank the whole mesh's
+ * sum and face count, and reads a rank's share back. */
+void isd_dist_set_edge_total(uint64_t edge_total_fixed_point, int64_t global_faces);
+uint64_t isd_dist_last_edge_sum(void);
+int isd_dist_last_halo(void); /* halo layers used by the last build (0: none / replicated OB02) */
 
 #ifdef __cplusplus
 }
