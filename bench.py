@@ -233,7 +233,8 @@ def main():
         lib.build_geometry(shape, mc)          # JSON strings (host) in; mesh copied to pinned host memory inside
         v = lib.get_v_view()                   # get_v_ptr / get_f_ptr: typed views on the library's host buffers, what the
         f = lib.get_f_view()                   # reference's JS layer does (HEAPF32.subarray, implisolid_main.js:230-237)
-        _ = float(v[-1, 2]) + int(f[-1, 2])     # touch the last elements: the data is in host memory
+        if len(v) and len(f):
+            _ = float(v[-1, 2]) + int(f[-1, 2])     # touch the last elements: the data is in host memory
         lib.finish_geometry()
         return v, f
     for _ in range(2):
