@@ -357,6 +357,26 @@ __global__ void __launch_bounds__(128) k_super_bounds(GridDesc g, const uint32_t
     }
 }
 
+// z-slab load balance: how much surface each layer of tiles holds, over the WHOLE grid (g.z0 = 0, g.nz = S).  One thread per
+// supertile; a mixed supertile is looked at again in its four 32x32x8 slices and every mixed slice adds one to its tile
+// layer's bin.  Integer counts from interval bounds: every rank computes the same histogram, so all ranks derive the same
+// slab boundaries without talking to each other.
+__global__ void __launch_bounds__(128) k_balance_hist(GridDesc g, const uint32_t* __restrict__ bounds_prog, unsigned* __restrict__ hist) {
+    const int stx = (g.tx + 3) / 4, sty = (g.ty + 3) / 4, stz = (g.tz + 3) / 4;
+    const int t = blockIdx.x * 128 + threadIdx.x;
+    if (t >= stx * sty * stz) return;
+    const int sx = t % stx, r = t / stx, sy = r % sty, sz = r / sty;
+    const int x0 = sx * 32, y0 = sy * 32, z0 = sz * 32;
+    const int x1 = min(x0 + 31, g.S - 1), y1 = min(y0 + 31, g.S - 1), z1 = min(z0 + 31, g.S - 1);
+    uint32_t none[1];
+    if (classify_box<false, false>(g, bounds_prog, x0, y0, z0, x1, y1, z1, none, NoMask()) != TILE_MIXED) return;
+    for (int j = 0; j < 4; ++j) {
+        const int a = z0 + 8 * j, b = min(a + 7, g.S - 1);
+        if (a > g.S - 1) break;
+        if (classify_box<false, false>(g, bounds_prog, x0, y0, a, x1, y1, b, none, NoMask()) == TILE_MIXED) atomicAdd(hist + (a >> 3), 1u);
+    }
+}
+
 // Where the work-list tiles are, for marching cubes (mc_kernels.cuh walks the work list, row of tiles by row of tiles):
 // tile_slot[tile] = work-list position; tile_any[tz * ty_count + ty] = 1 if some tile of that row of tiles is listed;
 // tile_bits = one bit per tile, TW words per row of tiles.

@@ -143,7 +143,7 @@ struct Context {
     long long emu_voff = 0, emu_foff = 0;
     NcclApi nccl;
     void* comm = nullptr;
-    DeviceBuffer d_gather;
+    DeviceBuffer d_gather, d_balance;
     int64_t slab[8] = {0};
     bool gathered = false;
     // halo mode (sharded OB02 without a mesh exchange): the GPU holds a LOCAL mesh of its slab plus `halo` recomputed cube
@@ -233,7 +233,54 @@ void slab_layers(int S, int rank, int world, int* z_begin, int* z_end) {
     *z_end = 1 + (int)((long long)(rank + 1) * layers / world);
 }
 
-void setup_grid(const McSettings& s) {
+// Slab boundaries that follow the surface (gpu.balance): cube layers weighted by the number of surface tiles in their layer of
+// tiles (k_balance_hist over the whole grid) plus a small uniform term for the per-layer fixed costs; rank r gets the layers
+// whose cumulative weight falls in [r, r+1) / world of the total.  Deterministic and identical on every rank.
+void balanced_layers(const McSettings& s, const ShapeCompiler::Program& prog, int* z_begin, int* z_end) {
+    const int S = g.grid.S, layers = S - 3, world = g.world, bins = (S + 7) / 8;
+    static std::vector<int> cuts;          // the partition of the last (shape, grid, world): emulated ranks ask one after the other
+    static std::vector<uint32_t> cut_key;
+    std::vector<uint32_t> key(prog.bounds);
+    const float boxv[6] = {s.box.xmin, s.box.xmax, s.box.ymin, s.box.ymax, s.box.zmin, s.box.zmax};
+    for (float v : boxv) { uint32_t w; memcpy(&w, &v, 4); key.push_back(w); }
+    key.push_back((uint32_t)S); key.push_back((uint32_t)world);
+    if (key != cut_key) {
+        GridDesc full = g.grid;
+        full.z0 = 0; full.nz = S;
+        full.tx = full.pitch / 8; full.ty = (S + 7) / 8; full.tz = (S + 7) / 8;
+        const size_t prog_bytes = prog.bounds.size() * sizeof(uint32_t), hist_bytes = (size_t)bins * sizeof(unsigned);
+        g.d_balance.reserve(prog_bytes + hist_bytes + 64);
+        uint32_t* d_prog = g.d_balance.as<uint32_t>();
+        unsigned* d_hist = reinterpret_cast<unsigned*>(g.d_balance.as<char>() + ((prog_bytes + 15) & ~(size_t)15));
+        ISD_CUDA(cudaMemcpyAsync(d_prog, prog.bounds.data(), prog_bytes, cudaMemcpyHostToDevice, g.stream));
+        ISD_CUDA(cudaMemsetAsync(d_hist, 0, hist_bytes, g.stream));
+        const int nsuper = ((full.tx + 3) / 4) * ((full.ty + 3) / 4) * ((full.tz + 3) / 4);
+        k_balance_hist<<<(nsuper + 127) / 128, 128, 0, g.stream>>>(full, d_prog, d_hist);
+        ISD_LAUNCH_CHECK();
+        std::vector<unsigned> hist((size_t)bins);
+        ISD_CUDA(cudaMemcpyAsync(hist.data(), d_hist, hist_bytes, cudaMemcpyDeviceToHost, g.stream));
+        ISD_CUDA(cudaStreamSynchronize(g.stream));
+        // integer weights per cube layer: its bin's count, plus a uniform term worth a quarter of the mean (per-layer fixed costs)
+        unsigned long long total_bins = 0;
+        for (unsigned h : hist) total_bins += h;
+        const unsigned long long uniform = total_bins * 8ull / (4ull * (unsigned long long)layers) + 1ull;
+        std::vector<unsigned long long> cum((size_t)layers + 1, 0ull);
+        for (int l = 0; l < layers; ++l) cum[(size_t)l + 1] = cum[(size_t)l] + (unsigned long long)hist[(size_t)((l + 1) >> 3)] + uniform;
+        cuts.assign((size_t)world + 1, 0);
+        cuts[(size_t)world] = layers;
+        for (int r = 1; r < world; ++r) {
+            const unsigned long long target = cum[(size_t)layers] * (unsigned long long)r / (unsigned long long)world;
+            int l = cuts[(size_t)r - 1] + 1;                                   // at least one layer per rank
+            while (l < layers - (world - r) && cum[(size_t)l] < target) ++l;
+            cuts[(size_t)r] = l;
+        }
+        cut_key = key;
+    }
+    *z_begin = 1 + cuts[(size_t)g.rank];
+    *z_end = 1 + cuts[(size_t)g.rank + 1];
+}
+
+void setup_grid(const McSettings& s, const ShapeCompiler::Program& prog) {
     const int S = s.resolution + 5;                       // skip_count_l + skip_count_h, marching_cubes.hpp:178-181
     GridDesc& gd = g.grid;
     gd.S = S;
@@ -247,7 +294,8 @@ void setup_grid(const McSettings& s) {
     gd.two_wx = 2 * gd.wx; gd.two_wy = 2 * gd.wy; gd.two_wz = 2 * gd.wz;
     gd.xi0 = s.box.xmin / gd.wx - 2; gd.yi0 = s.box.ymin / gd.wy - 2; gd.zi0 = s.box.zmin / gd.wz - 2;
     int zb, ze;
-    slab_layers(S, g.rank, g.world, &zb, &ze);
+    if (g.world > 1 && s.balance && S - 3 >= 2 * g.world) balanced_layers(s, prog, &zb, &ze);
+    else slab_layers(S, g.rank, g.world, &zb, &ze);
     g.own_zb = zb; g.own_ze = ze;
     g.halo_mode = false;
     g.halo = 0;
@@ -277,7 +325,7 @@ void setup_grid(const McSettings& s) {
 }
 
 void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog) {
-    setup_grid(s);
+    setup_grid(s, prog);
     const GridDesc& gd = g.grid;
     McDesc& m = g.mc;
     const size_t field_bytes = (size_t)gd.plane * gd.nz * sizeof(float);
@@ -722,8 +770,9 @@ void projection_step(bool enable_qem, bool exact_reduce) {
                                                           (int)g.own_f0, (int)g.own_f1, 0);
         ISD_LAUNCH_CHECK();
         if (g.emulate) {
-            ISD_CUDA(cudaMemcpyAsync(&g.last_edge_sum, &d_al->edge_sum, sizeof(unsigned long long), cudaMemcpyDeviceToHost, g.stream));
-            ISD_CUDA(cudaMemcpyAsync(&d_al->edge_total, &g.emu_edge_total, sizeof(unsigned long long), cudaMemcpyHostToDevice, g.stream));
+            ISD_CUDA(cudaMemcpyAsync(g.h_small.as<char>() + 3200, &d_al->edge_sum, sizeof(unsigned long long), cudaMemcpyDeviceToHost, g.stream));
+            memcpy(g.h_small.as<char>() + 3208, &g.emu_edge_total, sizeof(unsigned long long));
+            ISD_CUDA(cudaMemcpyAsync(&d_al->edge_total, g.h_small.as<char>() + 3208, sizeof(unsigned long long), cudaMemcpyHostToDevice, g.stream));
             k_alpha_from_sum<<<1, 1, 0, g.stream>>>(d_al, &d_al->edge_total, nullptr, g.world, g.emu_gnf);
         } else {
             g.nccl.check(g.nccl.AllReduce(&d_al->edge_sum, &d_al->edge_total, 1, kNcclUint64, kNcclSum, g.comm, g.stream), "ncclAllReduce");
@@ -735,7 +784,7 @@ void projection_step(bool enable_qem, bool exact_reduce) {
                                                           0, nf, 1);
         ISD_LAUNCH_CHECK();
         if (g.world == 1 || g.emulate)      // the sum of a whole mesh: what emulated ranks are handed as the all-reduce result
-            ISD_CUDA(cudaMemcpyAsync(&g.last_edge_sum, &d_al->edge_sum, sizeof(unsigned long long), cudaMemcpyDeviceToHost, g.stream));
+            ISD_CUDA(cudaMemcpyAsync(g.h_small.as<char>() + 3200, &d_al->edge_sum, sizeof(unsigned long long), cudaMemcpyDeviceToHost, g.stream));
     }
     if (exact_reduce) {
         k_sum_serial_float<<<1, 32, 0, g.stream>>>(d_len3, (long long)nf * 3, nf, &d_al->avg_edge);
@@ -806,6 +855,7 @@ void projection_step(bool enable_qem, bool exact_reduce) {
         g.timings[T_QEM] += ms;
     }
     g.average_edge = *h_avg;
+    if (g.world == 1 || g.emulate) memcpy(&g.last_edge_sum, g.h_small.as<char>() + 3200, sizeof(unsigned long long));
     g.proj_n = nf;
     for (int i = 0; i < 7; ++i) g.counters[3 + i] += (int64_t)hc->c[i];
     g.counters[10] += (int64_t)hc->c[7];

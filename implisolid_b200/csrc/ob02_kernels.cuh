@@ -570,13 +570,19 @@ __device__ __forceinline__ void sym_eig3(const float (&Ain)[3][3], float (&w)[3]
     for (int i = 0; i < 3; ++i)
 #pragma unroll
         for (int j = 0; j < 3; ++j) { A[i][j] = Ain[i][j]; V[i][j] = (i == j) ? 1.0f : 0.0f; }
+    // stopping rule of Eigen's JacobiSVD (Eigen/src/SVD/JacobiSVD.h): rotate a pair only while an off-diagonal entry exceeds
+    // max(FLT_MIN, 2*epsilon*maxDiagEntry); stop after a sweep that rotated nothing
+    const float precision = 2.0f * 1.1920929e-07f, considerAsZero = 1.17549435e-38f;
+    float maxDiagEntry = fmaxf(fabsf(A[0][0]), fmaxf(fabsf(A[1][1]), fabsf(A[2][2])));
     for (int sweep = 0; sweep < 12; ++sweep) {
-        const float off = fabsf(A[0][1]) + fabsf(A[0][2]) + fabsf(A[1][2]);
-        if (off == 0.0f) break;
+        bool finished = true;
 #pragma unroll
         for (int p = 0; p < 2; ++p)
 #pragma unroll
             for (int q = p + 1; q < 3; ++q) {
+                const float threshold = fmaxf(considerAsZero, precision * maxDiagEntry);
+                if (!(fabsf(A[p][q]) > threshold || fabsf(A[q][p]) > threshold)) continue;
+                finished = false;
                 if (A[p][q] == 0.0f) continue;
                 const float theta = (A[q][q] - A[p][p]) / (2.0f * A[p][q]);
                 const float t = (theta >= 0 ? 1.0f : -1.0f) / (fabsf(theta) + sqrtf(theta * theta + 1.0f));
@@ -599,7 +605,9 @@ __device__ __forceinline__ void sym_eig3(const float (&Ain)[3][3], float (&w)[3]
                     V[k][p] = c * vkp - s * vkq;
                     V[k][q] = s * vkp + c * vkq;
                 }
+                maxDiagEntry = fmaxf(maxDiagEntry, fmaxf(fabsf(A[p][p]), fabsf(A[q][q])));
             }
+        if (finished) break;
     }
 #pragma unroll
     for (int i = 0; i < 3; ++i) w[i] = A[i][i];

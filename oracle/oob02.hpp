@@ -429,11 +429,18 @@ inline void set_centers_on_surface(const implicit_function& object, const vects&
 inline void sym_eig3(const REAL Ain[3][3], REAL w[3], REAL V[3][3]) {
     REAL A[3][3];
     for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) { A[i][j] = Ain[i][j]; V[i][j] = (i == j) ? 1.0f : 0.0f; }
+    // Stopping rule of Eigen's JacobiSVD (Eigen/src/SVD/JacobiSVD.h, the solver qem.hpp:397 instantiates): a pair is rotated
+    // only while an off-diagonal entry exceeds max(FLT_MIN, 2*epsilon*maxDiagEntry), maxDiagEntry growing with the diagonal;
+    // the sweeps end when one of them rotates nothing.
+    const REAL precision = 2.0f * 1.1920929e-07f, considerAsZero = 1.17549435e-38f;
+    REAL maxDiagEntry = std::max(std::fabs(A[0][0]), std::max(std::fabs(A[1][1]), std::fabs(A[2][2])));
     for (int sweep = 0; sweep < 12; sweep++) {
-        REAL off = std::fabs(A[0][1]) + std::fabs(A[0][2]) + std::fabs(A[1][2]);
-        if (off == 0.0f) break;
+        bool finished = true;
         for (int p = 0; p < 2; p++)
             for (int q = p + 1; q < 3; q++) {
+                const REAL threshold = std::max(considerAsZero, precision * maxDiagEntry);
+                if (!(std::fabs(A[p][q]) > threshold || std::fabs(A[q][p]) > threshold)) continue;
+                finished = false;
                 if (A[p][q] == 0.0f) continue;
                 REAL theta = (A[q][q] - A[p][p]) / (2.0f * A[p][q]);
                 REAL t = (theta >= 0 ? 1.0f : -1.0f) / (std::fabs(theta) + std::sqrt(theta * theta + 1.0f));
@@ -453,7 +460,9 @@ inline void sym_eig3(const REAL Ain[3][3], REAL w[3], REAL V[3][3]) {
                     V[k][p] = c * vkp - s * vkq;
                     V[k][q] = s * vkp + c * vkq;
                 }
+                maxDiagEntry = std::max(maxDiagEntry, std::max(std::fabs(A[p][p]), std::fabs(A[q][q])));
             }
+        if (finished) break;
     }
     for (int i = 0; i < 3; i++) w[i] = A[i][i];
     for (int i = 0; i < 2; i++)

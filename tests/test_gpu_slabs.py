@@ -8,10 +8,13 @@ from implisolid_b200 import shapes, slabs
 pytestmark = pytest.mark.gpu
 
 
+@pytest.mark.parametrize("balance", [0, 1])
 @pytest.mark.parametrize("world", [2, 3, 8])
 @pytest.mark.parametrize("shape,R,half", [(shapes.c2_cube_minus_cylinder, 70, 0.8), (shapes.c4_deep_chain, 61, 1.0)])
-def test_emulated_slabs_stitch_to_the_single_gpu_mesh(gpu_lib, world, shape, R, half):
-    sj, mc = shape(), shapes.mc_settings(R, half)
+def test_emulated_slabs_stitch_to_the_single_gpu_mesh(gpu_lib, world, shape, R, half, balance):
+    """balance=0: equal numbers of cube layers (SURVEY §8e's formula, mirrored by implisolid_b200/slabs.py); balance=1 (the
+    default): boundaries follow the surface — contiguous, covering, at least one layer each, and the same stitched mesh."""
+    sj, mc = shape(), shapes.mc_settings(R, half, balance=balance)
     L = gpu_lib.lib
     L.isd_dist_emulate(0, 1)
     v1, f1 = gpu_lib.polygonize(sj, mc)
@@ -21,9 +24,13 @@ def test_emulated_slabs_stitch_to_the_single_gpu_mesh(gpu_lib, world, shape, R, 
             L.isd_dist_emulate(r, world)
             gpu_lib.build_geometry(sj, mc)
             s = gpu_lib.last_slab()
-            assert (s["z_begin"], s["z_end"]) == slabs.slab_layers(R, r, world)
+            if balance == 0:
+                assert (s["z_begin"], s["z_end"]) == slabs.slab_layers(R, r, world)
+            assert s["z_end"] > s["z_begin"] and s["z_begin"] == (1 if r == 0 else prev_end)
+            prev_end = s["z_end"]
             counts.append((s["nv"], s["nf"]))
             gpu_lib.finish_geometry()
+        assert prev_end == R + 5 - 2
         offsets, totals = slabs.global_offsets(counts)
         assert totals == (v1.shape[0], f1.shape[0])
         vs, fs = [], []
