@@ -542,17 +542,26 @@ ISD_HD void eval_values_list(const Prog& prog, const SdfGridView& sdf, const Lis
 }
 
 // ---- gradient mode: f and grad f in one pass (identical to the reference's O(depth^2) recursion) ----
-template <class Prog>
-ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, float cx, float cy, float cz, float& f_out, float& g0_out,
-                                float& g1_out, float& g2_out) {
+// `live` as in eval_values: a dead node is jumped over; a CSG node with one operand passes it on (value and gradient; the
+// lone second operand of a subtraction negated, transformed_subtract.hpp:76-85) through its own matrix, which is exactly
+// what the reference does with the child it selects.
+template <class Prog, class Live>
+ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, const Live& live, float cx, float cy, float cz, float& f_out,
+                                float& g0_out, float& g1_out, float& g2_out) {
     float vs[kMaxValueStack][4];
     float fs[kMaxFrameStack][3];
     int sp = 0, fp = 0, pc = 0;
+    unsigned long long present = 0ull;
     for (;;) {
         const W4 hdr = prog.load4(pc);
         const uint32_t word = hdr.x;
         const uint32_t op = word & OP_MASK;
         if (op == OP_END) break;
+        if (op < OP_UNION && !live(word >> OP_ID_SHIFT)) {      // dead node-opening instruction: skip the node's whole code
+            pc = (int)hdr.y;
+            present <<= 1;
+            continue;
+        }
         Mat12<Prog> M;
         M.load(prog, pc + 4);
         pc += kInstrWords;
@@ -562,19 +571,26 @@ ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, float 
             M.apply(cx, cy, cz, x, y, z);
             cx = x; cy = y; cz = z;
         } else if (op >= OP_UNION) {
-            --sp;
+            const bool top_there = (present & 1ull) != 0, below_there = (present & 2ull) != 0;
+            present = ((present >> 2) << 1) | 1ull;
             const bool swapped = (word & OP_FLAG_SWAPPED) != 0;
-            const int i1 = swapped ? sp : sp - 1, i2 = swapped ? sp - 1 : sp;
-            const float f1 = vs[i1][0], f2 = vs[i2][0];
-            bool first;
-            float r;
-            if (op == OP_UNION) { first = (f1 > f2); r = first ? f1 : f2; }
-            else if (op == OP_INTERSECT) { first = !(f1 > f2); r = (f1 > f2) ? f2 : f1; }
-            else { first = (f1 < -f2); r = first ? f1 : -f2; }
-            float a0, a1, a2;
-            if (first) { a0 = vs[i1][1]; a1 = vs[i1][2]; a2 = vs[i1][3]; }
-            else if (op == OP_SUBTRACT) { a0 = -vs[i2][1]; a1 = -vs[i2][2]; a2 = -vs[i2][3]; }
-            else { a0 = vs[i2][1]; a1 = vs[i2][2]; a2 = vs[i2][3]; }
+            float r, a0, a1, a2;
+            if (top_there && below_there) {
+                --sp;
+                const int i1 = swapped ? sp : sp - 1, i2 = swapped ? sp - 1 : sp;
+                const float f1 = vs[i1][0], f2 = vs[i2][0];
+                bool first;
+                if (op == OP_UNION) { first = (f1 > f2); r = first ? f1 : f2; }
+                else if (op == OP_INTERSECT) { first = !(f1 > f2); r = (f1 > f2) ? f2 : f1; }
+                else { first = (f1 < -f2); r = first ? f1 : -f2; }
+                if (first) { a0 = vs[i1][1]; a1 = vs[i1][2]; a2 = vs[i1][3]; }
+                else if (op == OP_SUBTRACT) { a0 = -vs[i2][1]; a1 = -vs[i2][2]; a2 = -vs[i2][3]; }
+                else { a0 = vs[i2][1]; a1 = vs[i2][2]; a2 = vs[i2][3]; }
+            } else {
+                const bool negate = (op == OP_SUBTRACT) && (top_there != swapped);      // the lone operand is f2
+                r = vs[sp - 1][0]; a0 = vs[sp - 1][1]; a1 = vs[sp - 1][2]; a2 = vs[sp - 1][3];
+                if (negate) { r = -r; a0 = -a0; a1 = -a1; a2 = -a2; }
+            }
             float o0, o1, o2;
             M.back(a0, a1, a2, o0, o1, o2);
             vs[sp - 1][0] = r; vs[sp - 1][1] = o0; vs[sp - 1][2] = o1; vs[sp - 1][3] = o2;
@@ -634,9 +650,15 @@ ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, float 
             else M.back(g0, g1, g2, o0, o1, o2);
             vs[sp][0] = f; vs[sp][1] = o0; vs[sp][2] = o1; vs[sp][3] = o2;
             ++sp;
+            present = (present << 1) | 1ull;
         }
     }
     f_out = vs[0][0]; g0_out = vs[0][1]; g1_out = vs[0][2]; g2_out = vs[0][3];
+}
+template <class Prog>
+ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, float cx, float cy, float cz, float& f_out, float& g0_out,
+                                float& g1_out, float& g2_out) {
+    eval_value_gradient(prog, sdf, AllLive(), cx, cy, cz, f_out, g0_out, g1_out, g2_out);
 }
 
 }  // namespace isd

@@ -464,6 +464,31 @@ struct TileLive {             // liveness mask of the tile being evaluated (unif
     }
 };
 
+// Liveness masks for evaluations at arbitrary points (the OB02 kernels: centroids, search points, bisection midpoints).  A
+// work-list tile's mask was proven over the tile's box grown by one cell, so it holds at every point whose containing node
+// cell lies in the tile; elsewhere (tiles proven inside / outside, points off the resident planes) there is no mask and the
+// whole tree runs.  Same bits either way (eval_values / eval_value_gradient with a Live predicate).
+struct PointSpec {
+    GridDesc g;
+    const uint32_t* tile_bits;
+    const unsigned* tile_slot;
+    const uint32_t* masks;
+    int TW, mask_words, enabled;
+};
+__constant__ PointSpec c_point_spec;      // set by the host after K1 of every build; disabled whenever another program is uploaded
+__device__ __forceinline__ const uint32_t* point_mask(const PointSpec& ps, float x, float y, float z) {
+    if (!ps.enabled) return nullptr;
+    // node_coord(i) = i * w + min - 2w  =>  containing cell i = floor((p - min) / w + 2)
+    const float fx = (x - ps.g.xmin) / ps.g.wx + 2.0f, fy = (y - ps.g.ymin) / ps.g.wy + 2.0f, fz = (z - ps.g.zmin) / ps.g.wz + 2.0f;
+    if (!(fx >= 0.0f && fy >= 0.0f && fz >= (float)ps.g.z0)) return nullptr;      // also rejects NaN
+    if (!(fx < (float)ps.g.S && fy < (float)ps.g.S && fz < (float)(ps.g.z0 + ps.g.nz))) return nullptr;
+    const int tx = (int)fx >> 3, ty = (int)fy >> 3, tz = ((int)fz - ps.g.z0) >> 3;
+    const int row = tz * ps.g.ty + ty;
+    if (!((__ldg(ps.tile_bits + (size_t)row * ps.TW + (tx >> 5)) >> (tx & 31)) & 1u)) return nullptr;
+    const unsigned slot = __ldg(ps.tile_slot + (size_t)row * ps.g.tx + tx);
+    return ps.masks + (size_t)slot * ps.mask_words;
+}
+
 // SPEC: before evaluating a tile the block turns its liveness mask into the list of instructions the tile really runs
 // (spec_entry, one instruction per thread, order kept by ballot ranks) in shared memory; eval_values_list then has no
 // liveness tests, no dead-node jumps and no operand bookkeeping left.

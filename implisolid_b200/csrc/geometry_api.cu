@@ -207,7 +207,17 @@ void ensure_init(int device = -1) {
 inline void launched() { g.launches++; }
 #define ISD_LAUNCH_CHECK() do { ISD_CUDA(cudaGetLastError()); launched(); } while (0)
 
+// liveness masks at arbitrary points (field_kernel.cuh PointSpec): valid only for the program K1 has just bounded
+void set_point_spec(const PointSpec* ps) {
+    static bool on = false;
+    if (ps == nullptr && !on) return;
+    PointSpec off{};
+    ISD_CUDA(cudaMemcpyToSymbolAsync(c_point_spec, ps ? ps : &off, sizeof(PointSpec), 0, cudaMemcpyHostToDevice, g.stream));
+    on = ps != nullptr;
+}
+
 void upload_program(const std::vector<uint32_t>& words) {
+    set_point_spec(nullptr);
     ISD_CUDA(cudaMemcpyToSymbolAsync(d_program, words.data(), words.size() * sizeof(uint32_t), 0, cudaMemcpyHostToDevice, g.stream));
 }
 
@@ -419,6 +429,12 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         }
     }
     ISD_CUDA(cudaEventRecord(g.ev[1], g.stream));
+    if (spec.enabled && s.point_spec != 0 && (s.point_spec > 0 || prog.num_nodes >= 8)) {
+        PointSpec ps;
+        ps.g = gd; ps.tile_bits = hints.tile_bits; ps.tile_slot = hints.tile_slot; ps.masks = spec.masks;
+        ps.TW = hints.TW; ps.mask_words = spec.mask_words; ps.enabled = 1;
+        set_point_spec(&ps);
+    }
     // Per-segment arrays: sized for every tile when that is small (no read-back), else for the work list (one extra
     // read-back, negligible at the grid sizes where it happens).
     unsigned* h = g.h_small.as<unsigned>();

@@ -64,10 +64,20 @@ __device__ __forceinline__ void count_if(bool pred, unsigned long long* ctr) {
 __device__ __forceinline__ float norm2f(float x, float y, float z) { return sqrtf(x * x + y * y + z * z); }
 __device__ __forceinline__ float sign_tol(float v) { return (v > kRootTolerance) ? 1.0f : (v < -kRootTolerance) ? -1.0f : 0.0f; }
 
+// f at a point / f and grad f at a point.  Near the surface the point lies in a work-list tile of K1, whose liveness mask
+// lets the interpreter jump over the CSG children that can never be selected there (same bits, a fraction of the work for
+// deep trees); elsewhere the whole tree runs.
 __device__ __forceinline__ float eval_f(const SdfGridView& sdf, float x, float y, float z) {
     float cx[1] = {x}, cy[1] = {y}, cz[1] = {z}, out[1];
-    eval_values<1>(ConstProgram(), sdf, AllLive(), cx, cy, cz, out);
+    const uint32_t* mask = point_mask(c_point_spec, x, y, z);
+    if (mask != nullptr) eval_values<1>(ConstProgram(), sdf, TileLive(mask, c_point_spec.mask_words), cx, cy, cz, out);
+    else eval_values<1>(ConstProgram(), sdf, AllLive(), cx, cy, cz, out);
     return out[0];
+}
+__device__ __forceinline__ void eval_fg(const SdfGridView& sdf, float x, float y, float z, float& f, float& g0, float& g1, float& g2) {
+    const uint32_t* mask = point_mask(c_point_spec, x, y, z);
+    if (mask != nullptr) eval_value_gradient(ConstProgram(), sdf, TileLive(mask, c_point_spec.mask_words), x, y, z, f, g0, g1, g2);
+    else eval_value_gradient(ConstProgram(), sdf, x, y, z, f, g0, g1, g2);
 }
 
 // ---- generic exclusive scan of a u32 array (three launches) ----------------------------------------------------------
@@ -225,7 +235,7 @@ __global__ void __launch_bounds__(128) k_centroid_gradients(SdfGridView sdf, con
         cen[f * 3 + d] = c[d];
     }
     float fv, g0, g1, g2;
-    eval_value_gradient(ConstProgram(), sdf, c[0], c[1], c[2], fv, g0, g1, g2);
+    eval_fg(sdf, c[0], c[1], c[2], fv, g0, g1, g2);
     const float norm = norm2f(g0, g1, g2);
     nrm[f * 3] = g0 / norm; nrm[f * 3 + 1] = g1 / norm; nrm[f * 3 + 2] = g2 / norm;
 }
@@ -233,7 +243,7 @@ __global__ void __launch_bounds__(128) k_unit_gradients(SdfGridView sdf, const f
     const int i = blockIdx.x * 128 + threadIdx.x;
     if (i >= n) return;
     float f, g0, g1, g2;
-    eval_value_gradient(ConstProgram(), sdf, pts[i * 3], pts[i * 3 + 1], pts[i * 3 + 2], f, g0, g1, g2);
+    eval_fg(sdf, pts[i * 3], pts[i * 3 + 1], pts[i * 3 + 2], f, g0, g1, g2);
     const float norm = norm2f(g0, g1, g2);
     nrm[i * 3] = g0 / norm; nrm[i * 3 + 1] = g1 / norm; nrm[i * 3 + 2] = g2 / norm;
 }
@@ -459,7 +469,7 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
     float s_c;
     if (phase == 0) {
         float fc, g0, g1, g2;
-        eval_value_gradient(ConstProgram(), sdf, cx, cy, cz, fc, g0, g1, g2);
+        eval_fg(sdf, cx, cy, cz, fc, g0, g1, g2);
         fc = eval_f(sdf, cx, cy, cz);      // eval_implicit's value (the gradient pass may round metaball sums differently)
         a.fc[i] = fc;
         // normalise_inplace(g, min_gradient_len)  normalise_inplace.hpp:19-58
@@ -556,7 +566,7 @@ __global__ void __launch_bounds__(128) k_project_finish(SdfGridView sdf, Project
     if (zeros12) { ox = bx; oy = by; oz = bz; }
     a.out[i * 3] = ox; a.out[i * 3 + 1] = oy; a.out[i * 3 + 2] = oz;
     float f, g0, g1, g2;
-    eval_value_gradient(ConstProgram(), sdf, ox, oy, oz, f, g0, g1, g2);
+    eval_fg(sdf, ox, oy, oz, f, g0, g1, g2);
     const float norm = norm2f(g0, g1, g2);
     a.nrm_out[i * 3] = g0 / norm; a.nrm_out[i * 3 + 1] = g1 / norm; a.nrm_out[i * 3 + 2] = g2 / norm;
 }

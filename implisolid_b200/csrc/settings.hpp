@@ -37,6 +37,8 @@ struct McSettings {
                           // (no mesh exchange); 0: gather the stitched mesh on every GPU and optimise it replicated
     int balance;          // z-slab runs: 1 (default) slab boundaries follow the surface (equal counts of surface tiles per GPU, from a
                           // bounds-only pass every rank repeats identically); 0: equal numbers of cube layers (SURVEY §8e's formula)
+    int point_spec;       // -1 (default): the OB02 kernels use K1's per-tile liveness masks at their evaluation points when the tree has
+                          // at least 8 nodes; 0: never; 1: always (when masks exist)
     int normals;          // 1: per-vertex normals (-grad f/|grad f|) computed right after the last step (isd_get_n_ptr); 0: on first use
     int specialize;       // 1 (default): per-tile liveness masks let the evaluator skip CSG children that interval bounds prove
                           // are never selected in that tile (field values bit-identical); 0: every tile runs the whole tree
@@ -99,6 +101,7 @@ inline McSettings parse_mc_settings(const char* json) {
     s.specialize = d.get_int("gpu.specialize", 1);
     s.normals = d.get_int("gpu.normals", 0);
     s.halo = d.get_int("gpu.halo", -1);
+    s.point_spec = d.get_int("gpu.point_spec", -1);
     s.balance = d.get_int("gpu.balance", 1);
     if (s.qem_enabled && !s.projection_enabled) {
         fprintf(stderr, "Invalid settings: QEM will not be applied if centroid projection is disabled\n");

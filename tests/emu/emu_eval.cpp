@@ -136,6 +136,13 @@ extern "C" int emu_eval_masked(const char* shape_json, const float* pts, int n, 
             eval_values_list<1>(prog, sdf, list.data(), (int)list.size(), x2, y2, z2, out2);
             if (memcmp(out2, out, 4) != 0) f_masked[i] = __builtin_nanf("");
         }
+        // gradient mode with the same mask (what the OB02 kernels run near the surface): value and gradient must keep their bits
+        {
+            float fa, ga[3], fb, gb[3];
+            eval_value_gradient(prog, sdf, pts[i * 3], pts[i * 3 + 1], pts[i * 3 + 2], fa, ga[0], ga[1], ga[2]);
+            eval_value_gradient(prog, sdf, MaskLive{mask}, pts[i * 3], pts[i * 3 + 1], pts[i * 3 + 2], fb, gb[0], gb[1], gb[2]);
+            if (memcmp(&fa, &fb, 4) != 0 || memcmp(ga, gb, 12) != 0) f_masked[i] = __builtin_nanf("");
+        }
         int cnt = 0;
         for (int k = 0; k < p.num_nodes; k++) cnt += (mask[k >> 5] >> (k & 31)) & 1;
         live_nodes[i] = cnt;

@@ -98,3 +98,22 @@ def test_projected_centroids_lie_on_surface(gpu_lib):
     assert resolved + st["projection_failed"] == c.shape[0]
     # |f| <= ROOT_TOLERANCE for every centroid that found the surface and did not hit the bisection cap
     assert (np.abs(f) > 1.0001e-4).sum() <= st["projection_failed"] + st["bisection_capped"]
+
+
+@pytest.mark.parametrize("shape,R,half", [(shapes.c4_deep_chain, 96, 1.0), (shapes.bushy_tree, 80, 0.9), (shapes.c3_metaballs, 64, 1.2),
+                                          (shapes.n1_medley, 72, 0.9)], ids=["c4", "bushy", "c3", "medley"])
+def test_point_masks_change_nothing(gpu_lib, shape, R, half):
+    """OB02 evaluations near the surface reuse K1's per-tile liveness masks (gpu.point_spec) and skip CSG children that can
+    never be selected there: vertices, projected centroids and their normals must keep every bit."""
+    sj = shape()
+    out = []
+    for ps in (0, 1):
+        gpu_lib.build_geometry(sj, shapes.mc_settings(R, half, iters=2, c=1.0, projection=1, qem=1, point_spec=ps))
+        v, f = gpu_lib.get_v(), gpu_lib.get_f()
+        c, n = gpu_lib.projected_centroids()
+        gpu_lib.finish_geometry()
+        out.append((v, f, c, n))
+    (v0, f0, c0, n0), (v1, f1, c1, n1) = out
+    assert np.array_equal(f0, f1)
+    assert np.array_equal(v0.view(np.uint32), v1.view(np.uint32))
+    assert np.array_equal(c0.view(np.uint32), c1.view(np.uint32)) and np.array_equal(n0.view(np.uint32), n1.view(np.uint32))
