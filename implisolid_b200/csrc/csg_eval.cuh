@@ -25,8 +25,10 @@
 
 #if defined(__CUDACC__)
 #define ISD_HD __host__ __device__ __forceinline__
-#else
+#define ISD_COLD __host__ __device__ __noinline__      // rarely used primitives with double-precision bodies: kept out of the
+#else                                                   // interpreters' hot loops (registers, instruction cache)
 #define ISD_HD inline
+#define ISD_COLD inline
 #endif
 
 namespace isd {
@@ -175,14 +177,14 @@ ISD_HD float prim_cube_sdf(const SdfGridView& g, float px, float py, float pz) {
 //   top_bottom_lid   top_bottom_lid.hpp:51-76    on untransformed points
 //   tetrahedron      tetrahedron.hpp:145-193     four host-built planes, untransformed points
 //   half_plane       half_plane.hpp:109-150
-ISD_HD float prim_torus(float x, float y, float z) {
+ISD_COLD float prim_torus(float x, float y, float z) {
     const float rx = 0.2f, r = 4.0f;
     const double qx = (double)(x / rx), qy = (double)(y / rx), qz = (double)(z / rx);
     const double a = sqrt(qx * qx + qy * qy);
     const double d = (double)r - a;
     return (float)(1 - d * d - qz * qz);
 }
-ISD_HD void grad_torus(float x, float y, float z, float& g0, float& g1, float& g2) {
+ISD_COLD void grad_torus(float x, float y, float z, float& g0, float& g1, float& g2) {
     const float rx = 0.2f, r = 4.0f;
     const float a = (float)sqrt((double)(x * x / (rx * rx) + y * y / (rx * rx)));
     g0 = (2 * x / (rx * rx * a)) * (r - a);
@@ -192,12 +194,12 @@ ISD_HD void grad_torus(float x, float y, float z, float& g0, float& g1, float& g
 ISD_HD double heart_core(float i1, float i2, float i3) {
     return (double)(i1 * i1) + (9. / 4.) * (double)i2 * (double)i2 + (double)(i3 * i3);
 }
-ISD_HD float prim_heart(float i1, float i2, float i3) {
+ISD_COLD float prim_heart(float i1, float i2, float i3) {
     const double u = heart_core(i1, i2, i3) - 1.;
     const double d2 = (double)i2, d3 = (double)i3;
     return (float)(-(u * u * u - (double)(i1 * i1 * i3 * i3 * i3) - (9. / 200.) * d2 * d2 * d3 * d3 * d3));
 }
-ISD_HD void grad_heart(float i1, float i2, float i3, float& g0, float& g1, float& g2) {
+ISD_COLD void grad_heart(float i1, float i2, float i3, float& g0, float& g1, float& g2) {
     const double u = heart_core(i1, i2, i3) - 1;
     const float a = (float)(u * u);
     const double d1 = (double)i1, d2 = (double)i2, d3 = (double)i3, da = (double)a;
@@ -212,7 +214,7 @@ ISD_HD void identity_product(float& x, float& y, float& z) {      // matrix_vect
     const float nz = zero * x + zero * y + one * z + zero;
     x = nx; y = ny; z = nz;
 }
-ISD_HD float prim_mushroom(float x, float y, float z) {
+ISD_COLD float prim_mushroom(float x, float y, float z) {
     identity_product(x, y, z);
     const float r = 0.9f / 2, a = (float)(0.4 / 2), c = 1 / (float)(1 / 0.2);
     const float a2 = a * a, c2 = c * c;
@@ -221,7 +223,7 @@ ISD_HD float prim_mushroom(float x, float y, float z) {
     const double dx = (double)(x - 0.0f), dy = (double)(y - 0.0f), dz = (double)(z - 0.0f);
     return (float)(-(dx * dx / (double)a2 + dy * dy / (double)a2 - dz * dz / (double)c2 - 1));
 }
-ISD_HD void grad_mushroom(float x, float y, float z, float& o0, float& o1, float& o2) {
+ISD_COLD void grad_mushroom(float x, float y, float z, float& o0, float& o1, float& o2) {
     identity_product(x, y, z);
     const float r = 0.9f / 2, a = (float)(0.4 / 2), c = 1 / (float)(1 / 0.2);
     const float a2 = a * a, c2 = c * c;
@@ -304,6 +306,8 @@ ISD_HD float prim_value(uint32_t op, const Prog& prog, int at, const Mat12<Prog>
 struct AllLive {
     ISD_HD bool operator()(uint32_t) const { return true; }
 };
+template <class Live> struct IsAllLive { static constexpr bool value = false; };
+template <> struct IsAllLive<AllLive> { static constexpr bool value = true; };
 
 template <int P, class Prog, class Live>
 ISD_HD void eval_values(const Prog& prog, const SdfGridView& sdf, const Live& live, float (&cx)[P], float (&cy)[P], float (&cz)[P],
@@ -571,7 +575,7 @@ ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, const 
             M.apply(cx, cy, cz, x, y, z);
             cx = x; cy = y; cz = z;
         } else if (op >= OP_UNION) {
-            const bool top_there = (present & 1ull) != 0, below_there = (present & 2ull) != 0;
+            const bool top_there = IsAllLive<Live>::value || (present & 1ull) != 0, below_there = IsAllLive<Live>::value || (present & 2ull) != 0;
             present = ((present >> 2) << 1) | 1ull;
             const bool swapped = (word & OP_FLAG_SWAPPED) != 0;
             float r, a0, a1, a2;

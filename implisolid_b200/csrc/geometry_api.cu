@@ -122,6 +122,7 @@ struct Context {
     DeviceBuffer d_sub_owner, d_sub_flag, d_sub_rank, d_verts2, d_faces2, d_ratio, d_normals;
     PinnedBuffer h_normals;
     bool normals_valid = false, normals_host_valid = false;
+    bool point_spec_on = false;             // the OB02 kernels may use K1's tile masks (c_point_spec describes the current program)
     std::vector<uint32_t> last_program;     // the shape program of the last build (lazy normals re-upload it)
     isd_progress_fn progress_fn = nullptr;
     void* progress_user = nullptr;
@@ -209,11 +210,9 @@ inline void launched() { g.launches++; }
 
 // liveness masks at arbitrary points (field_kernel.cuh PointSpec): valid only for the program K1 has just bounded
 void set_point_spec(const PointSpec* ps) {
-    static bool on = false;
-    if (ps == nullptr && !on) return;
-    PointSpec off{};
-    ISD_CUDA(cudaMemcpyToSymbolAsync(c_point_spec, ps ? ps : &off, sizeof(PointSpec), 0, cudaMemcpyHostToDevice, g.stream));
-    on = ps != nullptr;
+    if (ps == nullptr) { g.point_spec_on = false; return; }      // the plain kernel instantiations never read c_point_spec
+    ISD_CUDA(cudaMemcpyToSymbolAsync(c_point_spec, ps, sizeof(PointSpec), 0, cudaMemcpyHostToDevice, g.stream));
+    g.point_spec_on = true;
 }
 
 void upload_program(const std::vector<uint32_t>& words) {
@@ -664,7 +663,7 @@ void vertex_resampling_step(float c) {
     g.d_cen.reserve((size_t)nf * 3 * sizeof(float) + 16);
     g.d_nrm.reserve((size_t)nf * 3 * sizeof(float) + 16);
     g.d_w.reserve((size_t)nf * sizeof(float) + 16);
-    k_centroid_gradients<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(),
+    (g.point_spec_on ? k_centroid_gradients<true> : k_centroid_gradients<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(),
                                                                    g.d_nrm.as<float>());
     ISD_LAUNCH_CHECK();
     k_face_weights<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.d_cen.as<float>(), g.d_nrm.as<float>(), g.d_fof.as<int>(), nf, c, g.d_w.as<float>());
@@ -819,12 +818,12 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     a.al = d_al; a.best = g.d_best.as<float>(); a.fc = g.d_fc.as<float>(); a.state = g.d_state.as<unsigned char>();
     a.out = g.d_proj.as<float>(); a.nrm_out = g.d_pnrm.as<float>(); a.counters = g.d_counters.as<Ob02Counters>();
     a.n = nf; a.speculative = 1;
-    k_project_search<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a, 0);
+    (g.point_spec_on ? k_project_search<true> : k_project_search<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a, 0);
     ISD_LAUNCH_CHECK();
     // Phase B (direction types 2..6) is only needed when phase A left centroids over, which is rare and which only the device
     // knows: the rest of the step is launched right away and does nothing in that case (the kernels test the counter), so the
     // host does not have to wait here.
-    k_project_finish<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a);
+    (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a);
     ISD_LAUNCH_CHECK();
     ISD_CUDA(cudaEventRecord(g.ev[7], g.stream));
     if (enable_qem) {   // centroids_projection.cpp:1272-1310: the mesh only changes when QEM is on
@@ -852,9 +851,9 @@ void projection_step(bool enable_qem, bool exact_reduce) {
         if (g.halo_mode) { resolve_halo_offsets(); face_base = g.slab[3] - g.own_f0; }
         a.noise = noise_stream((size_t)(face_base + nf) * 3) + face_base * 3;
         a.speculative = 0;
-        k_project_search<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a, 1);
+        (g.point_spec_on ? k_project_search<true> : k_project_search<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a, 1);
         ISD_LAUNCH_CHECK();
-        k_project_finish<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a);
+        (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a);
         ISD_LAUNCH_CHECK();
         ISD_CUDA(cudaEventRecord(g.ev[7], g.stream));
         if (enable_qem) {

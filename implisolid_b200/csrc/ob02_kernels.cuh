@@ -67,16 +67,20 @@ __device__ __forceinline__ float sign_tol(float v) { return (v > kRootTolerance)
 // f at a point / f and grad f at a point.  Near the surface the point lies in a work-list tile of K1, whose liveness mask
 // lets the interpreter jump over the CSG children that can never be selected there (same bits, a fraction of the work for
 // deep trees); elsewhere the whole tree runs.
+// MASKED is a compile-time switch: shallow trees (and meshes that did not come from K1) run the plain instantiation, which
+// carries neither the tile look-up nor a second copy of the interpreter.
+template <bool MASKED>
 __device__ __forceinline__ float eval_f(const SdfGridView& sdf, float x, float y, float z) {
     float cx[1] = {x}, cy[1] = {y}, cz[1] = {z}, out[1];
-    const uint32_t* mask = point_mask(c_point_spec, x, y, z);
-    if (mask != nullptr) eval_values<1>(ConstProgram(), sdf, TileLive(mask, c_point_spec.mask_words), cx, cy, cz, out);
+    const uint32_t* mask = MASKED ? point_mask(c_point_spec, x, y, z) : nullptr;
+    if (MASKED && mask != nullptr) eval_values<1>(ConstProgram(), sdf, TileLive(mask, c_point_spec.mask_words), cx, cy, cz, out);
     else eval_values<1>(ConstProgram(), sdf, AllLive(), cx, cy, cz, out);
     return out[0];
 }
+template <bool MASKED>
 __device__ __forceinline__ void eval_fg(const SdfGridView& sdf, float x, float y, float z, float& f, float& g0, float& g1, float& g2) {
-    const uint32_t* mask = point_mask(c_point_spec, x, y, z);
-    if (mask != nullptr) eval_value_gradient(ConstProgram(), sdf, TileLive(mask, c_point_spec.mask_words), x, y, z, f, g0, g1, g2);
+    const uint32_t* mask = MASKED ? point_mask(c_point_spec, x, y, z) : nullptr;
+    if (MASKED && mask != nullptr) eval_value_gradient(ConstProgram(), sdf, TileLive(mask, c_point_spec.mask_words), x, y, z, f, g0, g1, g2);
     else eval_value_gradient(ConstProgram(), sdf, x, y, z, f, g0, g1, g2);
 }
 
@@ -223,6 +227,7 @@ __global__ void __launch_bounds__(128) k_centroids(const float* __restrict__ ver
     for (int d = 0; d < 3; ++d) cen[f * 3 + d] = (verts[f0 * 3 + d] + verts[f1 * 3 + d] + verts[f2 * 3 + d]) / 3.0f;
 }
 // both at once (vertex resampling: the gradient is taken at the centroid just stored, same bits)
+template <bool MASKED>
 __global__ void __launch_bounds__(128) k_centroid_gradients(SdfGridView sdf, const float* __restrict__ verts, const int* __restrict__ faces, int nf,
                                                             float* __restrict__ cen, float* __restrict__ nrm) {
     const int f = blockIdx.x * 128 + threadIdx.x;
@@ -235,7 +240,7 @@ __global__ void __launch_bounds__(128) k_centroid_gradients(SdfGridView sdf, con
         cen[f * 3 + d] = c[d];
     }
     float fv, g0, g1, g2;
-    eval_fg(sdf, c[0], c[1], c[2], fv, g0, g1, g2);
+    eval_fg<MASKED>(sdf, c[0], c[1], c[2], fv, g0, g1, g2);
     const float norm = norm2f(g0, g1, g2);
     nrm[f * 3] = g0 / norm; nrm[f * 3 + 1] = g1 / norm; nrm[f * 3 + 2] = g2 / norm;
 }
@@ -243,7 +248,7 @@ __global__ void __launch_bounds__(128) k_unit_gradients(SdfGridView sdf, const f
     const int i = blockIdx.x * 128 + threadIdx.x;
     if (i >= n) return;
     float f, g0, g1, g2;
-    eval_fg(sdf, pts[i * 3], pts[i * 3 + 1], pts[i * 3 + 2], f, g0, g1, g2);
+    eval_fg<false>(sdf, pts[i * 3], pts[i * 3 + 1], pts[i * 3 + 2], f, g0, g1, g2);
     const float norm = norm2f(g0, g1, g2);
     nrm[i * 3] = g0 / norm; nrm[i * 3 + 1] = g1 / norm; nrm[i * 3 + 2] = g2 / norm;
 }
@@ -443,12 +448,13 @@ __device__ __forceinline__ void facet_normal(const float* __restrict__ verts, co
 }
 
 // tries the alphas of one direction; returns true (and the trial point) at the first sign change  (:604-892)
+template <bool MASKED>
 __device__ __forceinline__ bool try_direction(const SdfGridView& sdf, float cx, float cy, float cz, float dx, float dy, float dz, float edge,
                                               const float* __restrict__ alphas, int n_alpha, float s_c, float& bx, float& by, float& bz) {
     for (int ai = 0; ai < n_alpha; ++ai) {
         const float c = edge * __ldg(alphas + ai);          // (length_factor * alpha) * 4.0 / 4.0
         const float x = cx + c * dx, y = cy + c * dy, z = cz + c * dz;
-        const float f = eval_f(sdf, x, y, z);
+        const float f = eval_f<MASKED>(sdf, x, y, z);
         if (sign_tol(f) * s_c <= 0.0f) { bx = x; by = y; bz = z; return true; }
     }
     return false;
@@ -456,6 +462,7 @@ __device__ __forceinline__ bool try_direction(const SdfGridView& sdf, float cx, 
 
 // set_centers_on_surface, search part.  phase 0: direction types 0 (gradient) and 1 (facet normal);
 // phase 1: types 2..6 for the centroids phase 0 left over (needs the host-generated noise).
+template <bool MASKED>
 __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, ProjectArgs a, int phase) {
     const int i = blockIdx.x * 128 + threadIdx.x;
     if (i >= a.n) return;
@@ -469,8 +476,8 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
     float s_c;
     if (phase == 0) {
         float fc, g0, g1, g2;
-        eval_fg(sdf, cx, cy, cz, fc, g0, g1, g2);
-        fc = eval_f(sdf, cx, cy, cz);      // eval_implicit's value (the gradient pass may round metaball sums differently)
+        eval_fg<MASKED>(sdf, cx, cy, cz, fc, g0, g1, g2);
+        fc = eval_f<MASKED>(sdf, cx, cy, cz);      // eval_implicit's value (the gradient pass may round metaball sums differently)
         a.fc[i] = fc;
         // normalise_inplace(g, min_gradient_len)  normalise_inplace.hpp:19-58
         float norm = norm2f(g0, g1, g2);
@@ -480,12 +487,12 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
         s_c = sign_tol(fc);
         if (s_c < 0.0f) { g0 = -g0; g1 = -g1; g2 = -g2; }
         const float d0 = -g0 * s_c, d1 = -g1 * s_c, d2 = -g2 * s_c;
-        ok = try_direction(sdf, cx, cy, cz, d0, d1, d2, edge, alphas, n_alpha_full, s_c, bx, by, bz);
+        ok = try_direction<MASKED>(sdf, cx, cy, cz, d0, d1, d2, edge, alphas, n_alpha_full, s_c, bx, by, bz);
         type = 0;
         if (!ok) {
             float nx, ny, nz;
             facet_normal(a.verts, a.faces, i, nx, ny, nz);
-            ok = try_direction(sdf, cx, cy, cz, nx, ny, nz, edge, alphas, n_alpha_short, s_c, bx, by, bz);
+            ok = try_direction<MASKED>(sdf, cx, cy, cz, nx, ny, nz, edge, alphas, n_alpha_short, s_c, bx, by, bz);
             type = 1;
         }
         count_if(!ok, &a.counters->c[10]);
@@ -501,7 +508,7 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
             const float n = norm2f(zx, zy, zz);
             zx = zx / n; zy = zy / n; zz = zz / n;
         }
-        ok = try_direction(sdf, cx, cy, cz, zx, zy, zz, edge, alphas, n_alpha_short, s_c, bx, by, bz);
+        ok = try_direction<MASKED>(sdf, cx, cy, cz, zx, zy, zz, edge, alphas, n_alpha_short, s_c, bx, by, bz);
         type = 2;
         if (!ok) {   // type 3: facet normal x previous direction, normalise_inplace
             float wx = ny * zz - nz * zy, wy = nz * zx - nx * zz, wz = nx * zy - ny * zx;
@@ -509,11 +516,11 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
             n = (n < kMinGradientLen) ? 1.0f : n;
             const float factor = 1.0f / n;
             wx = wx * factor; wy = wy * factor; wz = wz * factor;
-            ok = try_direction(sdf, cx, cy, cz, wx, wy, wz, edge, alphas, n_alpha_short, s_c, bx, by, bz);
+            ok = try_direction<MASKED>(sdf, cx, cy, cz, wx, wy, wz, edge, alphas, n_alpha_short, s_c, bx, by, bz);
             type = 3;
         }
         for (int dim = 0; dim < 3 && !ok; ++dim) {
-            ok = try_direction(sdf, cx, cy, cz, dim == 0 ? 1.0f : 0.0f, dim == 1 ? 1.0f : 0.0f, dim == 2 ? 1.0f : 0.0f, edge, alphas, n_alpha_short, s_c, bx, by, bz);
+            ok = try_direction<MASKED>(sdf, cx, cy, cz, dim == 0 ? 1.0f : 0.0f, dim == 1 ? 1.0f : 0.0f, dim == 2 ? 1.0f : 0.0f, edge, alphas, n_alpha_short, s_c, bx, by, bz);
             type = 4 + dim;
         }
     }
@@ -529,6 +536,7 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
 
 // set_centers_on_surface, second half (:893-1214): zero tests, bisection between the centroid and the candidate,
 // final assembly; then the unit gradient at the projected centroid (compute_centroid_gradient, :1262).
+template <bool MASKED>
 __global__ void __launch_bounds__(128) k_project_finish(SdfGridView sdf, ProjectArgs a) {
     const int i = blockIdx.x * 128 + threadIdx.x;
     if (i >= a.n) return;
@@ -541,7 +549,7 @@ __global__ void __launch_bounds__(128) k_project_finish(SdfGridView sdf, Project
         bx = cx; by = cy; bz = cz;
     }
     count_if(!already, &a.counters->c[7]);
-    const float f2 = eval_f(sdf, bx, by, bz);
+    const float f2 = eval_f<MASKED>(sdf, bx, by, bz);
     const bool zeros2 = fabsf(f2) <= kRootTolerance;
     const bool zeros1 = fabsf(a.fc[i]) <= kRootTolerance;
     if (zeros1) { bx = cx; by = cy; bz = cz; }
@@ -553,7 +561,7 @@ __global__ void __launch_bounds__(128) k_project_finish(SdfGridView sdf, Project
         if (f2 < -kRootTolerance) { x1x = bx; x1y = by; x1z = bz; x2x = cx; x2y = cy; x2z = cz; }
         for (int it = 1;; ++it) {
             const float mx = (x1x + x2x) / 2.0f, my = (x1y + x2y) / 2.0f, mz = (x1z + x2z) / 2.0f;
-            const float v = eval_f(sdf, mx, my, mz);
+            const float v = eval_f<MASKED>(sdf, mx, my, mz);
             if (fabsf(v) <= kRootTolerance || it >= kBisectionMaxIter) {
                 if (fabsf(v) > kRootTolerance) atomicAdd(&a.counters->c[8], 1ull);
                 ox = mx; oy = my; oz = mz;
@@ -566,7 +574,7 @@ __global__ void __launch_bounds__(128) k_project_finish(SdfGridView sdf, Project
     if (zeros12) { ox = bx; oy = by; oz = bz; }
     a.out[i * 3] = ox; a.out[i * 3 + 1] = oy; a.out[i * 3 + 2] = oz;
     float f, g0, g1, g2;
-    eval_fg(sdf, ox, oy, oz, f, g0, g1, g2);
+    eval_fg<MASKED>(sdf, ox, oy, oz, f, g0, g1, g2);
     const float norm = norm2f(g0, g1, g2);
     a.nrm_out[i * 3] = g0 / norm; a.nrm_out[i * 3 + 1] = g1 / norm; a.nrm_out[i * 3 + 2] = g2 / norm;
 }
