@@ -47,3 +47,47 @@ def exchange_counts(local_nv, local_nf, group=None):
     gathered = [torch.zeros_like(mine) for _ in range(world)]
     dist.all_gather(gathered, mine, group=group)
     return [(int(t[0]), int(t[1])) for t in gathered]
+
+
+def balanced_cuts(tile_hist, resolution, world):
+    """Cube-layer cuts that follow the surface (`gpu.balance`), the mirror of csrc/geometry_api.cu: balanced_layers.
+
+    tile_hist[b] = surface tiles whose z-range is node layers [8b, 8b+8) (k_balance_hist over the whole grid).  Cube layer l
+    (z = l + 1) weighs its bin's count plus a uniform term worth a quarter of the mean; rank r gets the layers whose
+    cumulative weight falls in [r, r+1)/world of the total, never fewer than one.  Integer arithmetic throughout, so every
+    rank computes the same cuts.  Returns world+1 layer indices; rank r owns cube layers [1 + cuts[r], 1 + cuts[r+1])."""
+    layers = resolution + 2
+    total_bins = sum(int(h) for h in tile_hist)
+    uniform = total_bins * 8 // (4 * layers) + 1
+    cum = [0] * (layers + 1)
+    for l in range(layers):
+        cum[l + 1] = cum[l] + int(tile_hist[(l + 1) >> 3]) + uniform
+    cuts = [0] * (world + 1)
+    cuts[world] = layers
+    for r in range(1, world):
+        target = cum[layers] * r // world
+        l = cuts[r - 1] + 1
+        while l < layers - (world - r) and cum[l] < target:
+            l += 1
+        cuts[r] = l
+    return cuts
+
+
+def halo_layers(overall_repeats, vresampl_iters, projection, qem, override=-1):
+    """Cube layers a slab recomputes on each side in halo mode (csrc/geometry_api.cu: setup_grid): a
+    resampling iteration reads two layers around a vertex, projection + QEM one, and one more layer because the lowest
+    halo layer's faces hang on ghost vertices that are never written."""
+    if override > 0:
+        return override
+    per_repeat = 2 * vresampl_iters + (1 if (projection and qem) else 0)
+    return overall_repeats * per_repeat + 1
+
+
+def halo_slab(resolution, rank, world, halo, cuts=None):
+    """Cube layers [zb, ze) a rank computes in halo mode: its own layers widened by `halo` and clamped to [1, S-2)."""
+    S = resolution + 5
+    if cuts is None:
+        zb, ze = slab_layers(resolution, rank, world)
+    else:
+        zb, ze = 1 + cuts[rank], 1 + cuts[rank + 1]
+    return max(zb - halo, 1), min(ze + halo, S - 2)

@@ -83,7 +83,7 @@ def test_halo_slabs_with_ob02_stitch_to_the_single_gpu_mesh(gpu_lib, world, shap
             L.isd_dist_set_offsets(offsets[r][0], offsets[r][1])
             L.isd_dist_set_edge_total(total, f1.shape[0])
             gpu_lib.build_geometry(sj, mc)
-            assert L.isd_dist_last_halo() >= 2
+            assert L.isd_dist_last_halo() == slabs.halo_layers(1, kw["iters"], kw["projection"], kw["qem"])
             s = gpu_lib.last_slab()
             assert (s["nv"], s["nf"]) == counts[r]
             part += L.isd_dist_last_edge_sum()

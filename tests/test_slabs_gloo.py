@@ -88,3 +88,57 @@ def test_partition_covers_all_layers():
                 z0, nz = slabs.slab_node_planes(R, r, world)
                 assert z0 >= 0 and z0 + nz <= R + 5
             assert prev == R + 3            # cube layers are z in [1, S-2), S = R + 5
+
+
+@pytest.mark.parametrize("world", [2, 3, 4, 8])
+@pytest.mark.parametrize("R", [16, 61, 256])
+def test_balanced_cuts_properties(R, world):
+    """slabs.balanced_cuts (mirror of geometry_api.cu: balanced_layers): strictly increasing, covering, >= 1 layer per rank,
+    and balanced to within one layer's weight for any histogram."""
+    rng = np.random.default_rng(R * 31 + world)
+    layers, bins = R + 2, (R + 5 + 7) // 8
+    for trial in range(20):
+        kind = trial % 4
+        if kind == 0:
+            hist = np.zeros(bins, dtype=np.int64)                     # empty field: uniform term alone
+        elif kind == 1:
+            hist = rng.integers(0, 500, bins)
+        elif kind == 2:
+            hist = np.zeros(bins, dtype=np.int64); hist[rng.integers(0, bins)] = 10000      # all the surface in one bin
+        else:
+            hist = np.zeros(bins, dtype=np.int64); hist[:max(1, bins // 4)] = 300           # surface at the bottom only
+        cuts = slabs.balanced_cuts(hist, R, world)
+        assert cuts[0] == 0 and cuts[-1] == layers and len(cuts) == world + 1
+        assert all(b > a for a, b in zip(cuts, cuts[1:]))
+        uniform = int(hist.sum()) * 8 // (4 * layers) + 1
+        w = np.array([int(hist[(l + 1) >> 3]) + uniform for l in range(layers)])
+        cum = np.concatenate([[0], np.cumsum(w)])
+        for r in range(1, world):
+            target = int(cum[-1]) * r // world
+            forced_lo = cuts[r] == cuts[r - 1] + 1
+            forced_hi = cuts[r] == layers - (world - r)
+            if not (forced_lo or forced_hi):
+                assert cum[cuts[r] - 1] < target <= cum[cuts[r]]
+
+
+def test_balanced_cuts_equal_plain_partition_on_a_flat_histogram():
+    R, world = 254, 4
+    hist = np.full((R + 12) // 8, 64)
+    cuts = slabs.balanced_cuts(hist, R, world)
+    plain = [slabs.slab_layers(R, r, world)[0] - 1 for r in range(world)] + [R + 2]
+    assert max(abs(a - b) for a, b in zip(cuts, plain)) <= 1
+
+
+def test_halo_radius_and_clamping():
+    assert slabs.halo_layers(1, 1, True, True) == 4
+    assert slabs.halo_layers(2, 1, True, True) == 7
+    assert slabs.halo_layers(1, 0, True, False) == 1
+    assert slabs.halo_layers(3, 2, False, False) == 13
+    assert slabs.halo_layers(2, 1, True, True, override=5) == 5
+    R, world = 64, 4
+    S = R + 5
+    for r in range(world):
+        zb, ze = slabs.slab_layers(R, r, world)
+        hb, he = slabs.halo_slab(R, r, world, 7)
+        assert 1 <= hb <= zb < ze <= he <= S - 2
+        assert hb == max(1, zb - 7) and he == min(S - 2, ze + 7)
