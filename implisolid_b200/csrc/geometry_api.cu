@@ -807,7 +807,7 @@ void projection_step(bool enable_qem, bool exact_reduce) {
         k_alpha_from_mean<<<1, 1, 0, g.stream>>>(&d_al->avg_edge, d_al);
         ISD_LAUNCH_CHECK();
     }
-    g.d_best.reserve((size_t)nf * 3 * sizeof(float) + 16);
+    g.d_best.reserve((size_t)nf * sizeof(float4) + 16);
     g.d_fc.reserve((size_t)nf * sizeof(float) + 16);
     g.d_state.reserve((size_t)nf + 16);
     g.d_proj.reserve((size_t)nf * 3 * sizeof(float) + 16);
@@ -815,10 +815,12 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     ISD_CUDA(cudaMemsetAsync(g.d_counters.ptr, 0, sizeof(Ob02Counters), g.stream));
     ProjectArgs a;
     a.verts = g.d_verts.as<float>(); a.faces = g.d_faces.as<int>(); a.cen = g.d_cen.as<float>(); a.noise = nullptr;
-    a.al = d_al; a.best = g.d_best.as<float>(); a.fc = g.d_fc.as<float>(); a.state = g.d_state.as<unsigned char>();
+    a.al = d_al; a.best = g.d_best.as<float4>(); a.fc = g.d_fc.as<float>(); a.state = g.d_state.as<unsigned char>();
     a.out = g.d_proj.as<float>(); a.nrm_out = g.d_pnrm.as<float>(); a.counters = g.d_counters.as<Ob02Counters>();
     a.n = nf; a.speculative = 1;
-    (g.point_spec_on ? k_project_search<true> : k_project_search<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a, 0);
+    // the list of left-over centroids lives in the output array: k_project_finish only writes it once there are none left to list
+    a.leftover = reinterpret_cast<int*>(g.d_proj.as<float>());
+    (g.point_spec_on ? k_project_search<true> : k_project_search<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a);
     ISD_LAUNCH_CHECK();
     // Phase B (direction types 2..6) is only needed when phase A left centroids over, which is rare and which only the device
     // knows: the rest of the step is launched right away and does nothing in that case (the kernels test the counter), so the
@@ -851,7 +853,8 @@ void projection_step(bool enable_qem, bool exact_reduce) {
         if (g.halo_mode) { resolve_halo_offsets(); face_base = g.slab[3] - g.own_f0; }
         a.noise = noise_stream((size_t)(face_base + nf) * 3) + face_base * 3;
         a.speculative = 0;
-        (g.point_spec_on ? k_project_search<true> : k_project_search<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a, 1);
+        const int n_left = (int)hc->c[10];
+        (g.point_spec_on ? k_project_leftovers<true> : k_project_leftovers<false>)<<<blocks_for(n_left, 4), 128, 0, g.stream>>>(g.sdf, a, n_left);
         ISD_LAUNCH_CHECK();
         (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a);
         ISD_LAUNCH_CHECK();

@@ -417,8 +417,9 @@ struct ProjectArgs {
     const float* cen;        // centroids (input)
     const float* noise;      // make_random_pm1(n, 1e-6) for direction type 2 (phase B only)
     const AlphaList* al;     // mean edge length + alpha list (device)
-    float* best;             // per centroid: candidate on the other side of the surface
+    float4* best;            // per centroid: candidate on the other side of the surface, and f there
     float* fc;               // f(centroid)
+    int* leftover;           // centroids phase A left over, in no particular order (count: counters->c[10])
     unsigned char* state;    // bit 0: already success; bit 1: still searching after phase A
     float* out;              // projected centroids
     float* nrm_out;          // unit gradient at projected centroids
@@ -450,55 +451,83 @@ __device__ __forceinline__ void facet_normal(const float* __restrict__ verts, co
 // tries the alphas of one direction; returns true (and the trial point) at the first sign change  (:604-892)
 template <bool MASKED>
 __device__ __forceinline__ bool try_direction(const SdfGridView& sdf, float cx, float cy, float cz, float dx, float dy, float dz, float edge,
-                                              const float* __restrict__ alphas, int n_alpha, float s_c, float& bx, float& by, float& bz) {
+                                              const float* __restrict__ alphas, int n_alpha, float s_c, float& bx, float& by, float& bz, float& bf) {
     for (int ai = 0; ai < n_alpha; ++ai) {
         const float c = edge * __ldg(alphas + ai);          // (length_factor * alpha) * 4.0 / 4.0
         const float x = cx + c * dx, y = cy + c * dy, z = cz + c * dz;
         const float f = eval_f<MASKED>(sdf, x, y, z);
-        if (sign_tol(f) * s_c <= 0.0f) { bx = x; by = y; bz = z; return true; }
+        if (sign_tol(f) * s_c <= 0.0f) { bx = x; by = y; bz = z; bf = f; return true; }
     }
     return false;
 }
 
-// set_centers_on_surface, search part.  phase 0: direction types 0 (gradient) and 1 (facet normal);
-// phase 1: types 2..6 for the centroids phase 0 left over (needs the host-generated noise).
+// set_centers_on_surface, search part, phase A: direction types 0 (gradient) and 1 (facet normal).  The value at the candidate
+// is kept beside it (k_project_finish starts from it), and f(centroid) is the value the gradient pass returns: the gradient
+// interpreter selects and computes f with the same operations as the value interpreter (tests/test_program_emulation.py holds
+// the two equal bit for bit on every shape).  Centroids left over go to a list; phase B works from it.
 template <bool MASKED>
-__global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, ProjectArgs a, int phase) {
+__global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, ProjectArgs a) {
     const int i = blockIdx.x * 128 + threadIdx.x;
     if (i >= a.n) return;
     const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
     const float edge = a.al->avg_edge;
     const float* alphas = a.al->alpha;
     const int n_alpha_full = a.al->n_full, n_alpha_short = a.al->n_short;
-    float bx = -10.0f, by = -10.0f, bz = -10.0f;
-    bool ok = false;
-    int type = -1;
-    float s_c;
-    if (phase == 0) {
-        float fc, g0, g1, g2;
-        eval_fg<MASKED>(sdf, cx, cy, cz, fc, g0, g1, g2);
-        fc = eval_f<MASKED>(sdf, cx, cy, cz);      // eval_implicit's value (the gradient pass may round metaball sums differently)
-        a.fc[i] = fc;
-        // normalise_inplace(g, min_gradient_len)  normalise_inplace.hpp:19-58
-        float norm = norm2f(g0, g1, g2);
-        norm = (norm < kMinGradientLen) ? 1.0f : norm;
-        const float factor = 1.0f / norm;
-        g0 = g0 * factor; g1 = g1 * factor; g2 = g2 * factor;
-        s_c = sign_tol(fc);
-        if (s_c < 0.0f) { g0 = -g0; g1 = -g1; g2 = -g2; }
-        const float d0 = -g0 * s_c, d1 = -g1 * s_c, d2 = -g2 * s_c;
-        ok = try_direction<MASKED>(sdf, cx, cy, cz, d0, d1, d2, edge, alphas, n_alpha_full, s_c, bx, by, bz);
-        type = 0;
-        if (!ok) {
-            float nx, ny, nz;
-            facet_normal(a.verts, a.faces, i, nx, ny, nz);
-            ok = try_direction<MASKED>(sdf, cx, cy, cz, nx, ny, nz, edge, alphas, n_alpha_short, s_c, bx, by, bz);
-            type = 1;
-        }
-        count_if(!ok, &a.counters->c[10]);
+    float bx = -10.0f, by = -10.0f, bz = -10.0f, bf = 0.0f;
+    float fc, g0, g1, g2;
+    eval_fg<MASKED>(sdf, cx, cy, cz, fc, g0, g1, g2);
+    a.fc[i] = fc;
+    // normalise_inplace(g, min_gradient_len)  normalise_inplace.hpp:19-58
+    float norm = norm2f(g0, g1, g2);
+    norm = (norm < kMinGradientLen) ? 1.0f : norm;
+    const float factor = 1.0f / norm;
+    g0 = g0 * factor; g1 = g1 * factor; g2 = g2 * factor;
+    const float s_c = sign_tol(fc);
+    if (s_c < 0.0f) { g0 = -g0; g1 = -g1; g2 = -g2; }
+    const float d0 = -g0 * s_c, d1 = -g1 * s_c, d2 = -g2 * s_c;
+    bool ok = try_direction<MASKED>(sdf, cx, cy, cz, d0, d1, d2, edge, alphas, n_alpha_full, s_c, bx, by, bz, bf);
+    int type = 0;
+    if (!ok) {
+        float nx, ny, nz;
+        facet_normal(a.verts, a.faces, i, nx, ny, nz);
+        ok = try_direction<MASKED>(sdf, cx, cy, cz, nx, ny, nz, edge, alphas, n_alpha_short, s_c, bx, by, bz, bf);
+        type = 1;
+    }
+    if (ok) {
+        a.best[i] = make_float4(bx, by, bz, bf);
+        a.state[i] = 1;
     } else {
-        if (!(a.state[i] & 2)) return;
-        s_c = sign_tol(a.fc[i]);
+        a.state[i] = 2;
+    }
+    {   // left-overs: one atomic per warp hands out list slots
+        const unsigned m = __ballot_sync(__activemask(), !ok);
+        if (!ok) {
+            const int leader = __ffs(m) - 1, lane = threadIdx.x & 31;
+            unsigned long long base = 0ull;
+            if (lane == leader) base = atomicAdd(&a.counters->c[10], (unsigned long long)__popc(m));
+            base = __shfl_sync(m, base, leader);
+            a.leftover[base + __popc(m & ((1u << lane) - 1u))] = i;
+        }
+    }
+    count_if(ok && type == 0, &a.counters->c[0]);
+    count_if(ok && type == 1, &a.counters->c[1]);
+}
+
+// Phase B: direction types 2..6 for the centroids phase A left over (rare; needs the host-generated noise).  One warp per
+// centroid: the candidates (five directions x the short alpha list, in the reference's order of trial) are independent
+// evaluations, so the lanes take one each and the first success in that order wins, as in the reference's sequential walk.
+template <bool MASKED>
+__global__ void __launch_bounds__(128) k_project_leftovers(SdfGridView sdf, ProjectArgs a, int n_left) {
+    const int li = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (li >= n_left) return;
+    const int i = a.leftover[li];
+    const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
+    const float edge = a.al->avg_edge;
+    const float* alphas = a.al->alpha;
+    const int n_short = a.al->n_short;
+    const float s_c = sign_tol(a.fc[i]);
+    float dir[5][3];
+    {
         float nx, ny, nz;
         facet_normal(a.verts, a.faces, i, nx, ny, nz);
         // type 2: facet normal x noise, normalize_1111   (create_directions_bundle :230-262; add_inplace works on copies)
@@ -508,30 +537,54 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
             const float n = norm2f(zx, zy, zz);
             zx = zx / n; zy = zy / n; zz = zz / n;
         }
-        ok = try_direction<MASKED>(sdf, cx, cy, cz, zx, zy, zz, edge, alphas, n_alpha_short, s_c, bx, by, bz);
-        type = 2;
-        if (!ok) {   // type 3: facet normal x previous direction, normalise_inplace
-            float wx = ny * zz - nz * zy, wy = nz * zx - nx * zz, wz = nx * zy - ny * zx;
-            float n = norm2f(wx, wy, wz);
-            n = (n < kMinGradientLen) ? 1.0f : n;
-            const float factor = 1.0f / n;
-            wx = wx * factor; wy = wy * factor; wz = wz * factor;
-            ok = try_direction<MASKED>(sdf, cx, cy, cz, wx, wy, wz, edge, alphas, n_alpha_short, s_c, bx, by, bz);
-            type = 3;
-        }
-        for (int dim = 0; dim < 3 && !ok; ++dim) {
-            ok = try_direction<MASKED>(sdf, cx, cy, cz, dim == 0 ? 1.0f : 0.0f, dim == 1 ? 1.0f : 0.0f, dim == 2 ? 1.0f : 0.0f, edge, alphas, n_alpha_short, s_c, bx, by, bz);
-            type = 4 + dim;
-        }
-    }
-    if (ok) {
-        a.best[i * 3] = bx; a.best[i * 3 + 1] = by; a.best[i * 3 + 2] = bz;
-        a.state[i] = 1;
-    } else {
-        a.state[i] = 2;
-    }
+        // type 3: facet normal x previous direction, normalise_inplace
+        float wx = ny * zz - nz * zy, wy = nz * zx - nx * zz, wz = nx * zy - ny * zx;
+        float n = norm2f(wx, wy, wz);
+        n = (n < kMinGradientLen) ? 1.0f : n;
+        const float factor = 1.0f / n;
+        wx = wx * factor; wy = wy * factor; wz = wz * factor;
+        dir[0][0] = zx; dir[0][1] = zy; dir[0][2] = zz;
+        dir[1][0] = wx; dir[1][1] = wy; dir[1][2] = wz;
 #pragma unroll
-    for (int t = 0; t < 7; ++t) count_if(ok && type == t, &a.counters->c[t]);
+        for (int d = 0; d < 3; ++d) { dir[2 + d][0] = d == 0 ? 1.0f : 0.0f; dir[2 + d][1] = d == 1 ? 1.0f : 0.0f; dir[2 + d][2] = d == 2 ? 1.0f : 0.0f; }
+    }
+    const int n_cand = 5 * n_short;
+    bool ok = false;
+    int type = -1;
+    float bx = -10.0f, by = -10.0f, bz = -10.0f, bf = 0.0f;
+    for (int c0 = 0; c0 < n_cand && !ok; c0 += 32) {
+        const int c = c0 + lane;
+        bool mine = false;
+        float x = 0.0f, y = 0.0f, z = 0.0f, f = 0.0f;
+        if (c < n_cand) {
+            const int d = c / n_short, ai = c - d * n_short;
+            float dx = 0.0f, dy = 0.0f, dz = 0.0f;
+#pragma unroll
+            for (int k = 0; k < 5; ++k)
+                if (d == k) { dx = dir[k][0]; dy = dir[k][1]; dz = dir[k][2]; }
+            const float cc = edge * __ldg(alphas + ai);
+            x = cx + cc * dx; y = cy + cc * dy; z = cz + cc * dz;
+            f = eval_f<MASKED>(sdf, x, y, z);
+            mine = sign_tol(f) * s_c <= 0.0f;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, mine);
+        if (m) {
+            const int w = __ffs(m) - 1;
+            bx = __shfl_sync(0xffffffffu, x, w); by = __shfl_sync(0xffffffffu, y, w); bz = __shfl_sync(0xffffffffu, z, w);
+            bf = __shfl_sync(0xffffffffu, f, w);
+            type = 2 + (c0 + w) / n_short;
+            ok = true;
+        }
+    }
+    if (lane == 0) {
+        if (ok) {
+            a.best[i] = make_float4(bx, by, bz, bf);
+            a.state[i] = 1;
+            atomicAdd(&a.counters->c[type], 1ull);
+        } else {
+            a.state[i] = 2;
+        }
+    }
 }
 
 // set_centers_on_surface, second half (:893-1214): zero tests, bisection between the centroid and the candidate,
@@ -543,15 +596,15 @@ __global__ void __launch_bounds__(128) k_project_finish(SdfGridView sdf, Project
     if (a.speculative && a.counters->c[10] != 0ull) return;
     const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
     const bool already = (a.state[i] & 1) != 0;
-    float bx, by, bz;
-    if (already) { bx = a.best[i * 3]; by = a.best[i * 3 + 1]; bz = a.best[i * 3 + 2]; }
-    else {
-        bx = cx; by = cy; bz = cz;
+    const float fc = a.fc[i];
+    float bx = cx, by = cy, bz = cz, f2 = fc;      // no candidate: the reference evaluates the centroid again
+    if (already) {
+        const float4 b = a.best[i];
+        bx = b.x; by = b.y; bz = b.z; f2 = b.w;    // f at the candidate, from the search that found it
     }
     count_if(!already, &a.counters->c[7]);
-    const float f2 = eval_f<MASKED>(sdf, bx, by, bz);
     const bool zeros2 = fabsf(f2) <= kRootTolerance;
-    const bool zeros1 = fabsf(a.fc[i]) <= kRootTolerance;
+    const bool zeros1 = fabsf(fc) <= kRootTolerance;
     if (zeros1) { bx = cx; by = cy; bz = cz; }
     const bool zeros12 = zeros2 || zeros1;
     float ox = cx, oy = cy, oz = cz;
