@@ -445,6 +445,21 @@ ISD_HD uint32_t spec_entry(const W4& it, const Live& live) {
     return e | LE_VALID;
 }
 
+// The same for gradient mode, where a live CSG node with a single live child still has work to do (the child's gradient goes
+// through the node's own matrix): such closing instructions stay in the list, marked LE_PASS.
+template <class Live>
+ISD_HD uint32_t spec_entry_gradient(const W4& it, const Live& live) {
+    if (!live(it.y)) return 0u;
+    if (!(it.x & IT_CLOSING)) return (it.x & IT_PC_MASK) | LE_VALID;
+    const bool la = live(it.z), lb = live(it.w);
+    const uint32_t op = (it.x >> IT_OP_SHIFT) & 3u;
+    uint32_t e = (it.x & (IT_PC_MASK | IT_CLOSING | IT_RESTORE | IT_SWAPPED)) | (op << LE_OP_SHIFT);
+    if (la && lb) e |= LE_COMBINE;
+    else if (op == (uint32_t)OP_SUBTRACT - (uint32_t)OP_UNION && lb) e |= LE_NEGATE;
+    if (!(e & (LE_COMBINE | LE_NEGATE | LE_RESTORE))) e |= LE_PASS;
+    return e | LE_VALID;
+}
+
 template <int P, class Prog, class List>
 ISD_HD void eval_values_list(const Prog& prog, const SdfGridView& sdf, const List& list, int n_list, float (&cx)[P], float (&cy)[P],
                              float (&cz)[P], float (&out)[P]) {
@@ -545,6 +560,63 @@ ISD_HD void eval_values_list(const Prog& prog, const SdfGridView& sdf, const Lis
     for (int p = 0; p < P; ++p) out[p] = t0[p];
 }
 
+// One live primitive in gradient mode: f and the gradient in the parent's frame (shared by the two gradient interpreters'
+// list form; `pc` is the word index of the primitive's parameters, (cx,cy,cz) the coordinates handed down by the parent).
+template <class Prog>
+ISD_HD void prim_value_gradient(uint32_t op, const W4& hdr, const Prog& prog, int pc, const Mat12<Prog>& M, const SdfGridView& sdf, float cx,
+                                float cy, float cz, float& f, float& o0, float& o1, float& o2) {
+    float x, y, z;
+    M.apply(cx, cy, cz, x, y, z);
+    float g0, g1, g2;
+    if (op == OP_METABALLS) {
+        const int nb = (int)hdr.z;
+        f = 0.0f; g0 = 0.0f; g1 = 0.0f; g2 = 0.0f;
+        for (int b = 0; b < nb; ++b) {
+            const W4 q = prog.load4(pc), q2 = prog.load4(pc + 4);
+            const float bx = as_float(q.x), by = as_float(q.y), bz = as_float(q.z);
+            const float strength = as_float(q.w), subtract = as_float(q2.x);
+            pc += 8;
+            const float fx = x - bx, fx2 = fx * fx;
+            const float fy = y - by, fy2 = fy * fy;
+            const float fz = z - bz, fz2 = fz * fz;
+            {   // implicit_ball :89-100
+                const float h = 0.000001f + fx2 + fy2 + fz2;
+                const float hinv = 1.0f / h;
+                const float val = strength * hinv - subtract;
+                f += val / 100.0f;
+            }
+            {   // gradient_ball :118-136
+                const float h = (float)(0.000001 + (double)fx2 + (double)fy2 + (double)fz2);
+                const float hinv = 1.0f / h;
+                g0 += strength * (-2.0f * fx * hinv * hinv) / 100.0f;
+                g1 += strength * (-2.0f * fy * hinv * hinv) / 100.0f;
+                g2 += strength * (-2.0f * fz * hinv * hinv) / 100.0f;
+            }
+        }
+    } else if (op == OP_ELLIPSOID) { f = prim_ellipsoid(x, y, z); grad_ellipsoid(x, y, z, g0, g1, g2); }
+    else if (op == OP_CYLINDER) { f = prim_cylinder(x, y, z); grad_cylinder(x, y, z, g0, g1, g2); }
+    else if (op == OP_CONE) { f = prim_cone(x, y, z); grad_cone(x, y, z, g0, g1, g2); }
+    else if (op == OP_CUBE) { f = prim_cube(x, y, z); grad_cube(x, y, z, g0, g1, g2); }
+    else if (op == OP_CUBE_SDF) { f = prim_cube_sdf(sdf, x, y, z); grad_cube(x, y, z, g0, g1, g2); }
+    else if (op == OP_TORUS) { f = prim_torus(x, y, z); grad_torus(x, y, z, g0, g1, g2); }
+    else if (op == OP_HEART) { f = prim_heart(x, y, z); grad_heart(x, y, z, g0, g1, g2); }
+    else if (op == OP_MUSHROOM) { f = prim_mushroom(x, y, z); grad_mushroom(x, y, z, g0, g1, g2); }
+    else if (op == OP_HALF_PLANE) {
+        f = prim_half_plane(prog, pc, x, y, z);
+        const W4 n = prog.load4(pc);
+        const float s = (f >= 0) ? -1.0f : 1.0f;      // half_plane.hpp:129-138, as written
+        g0 = s * as_float(n.x); g1 = s * as_float(n.y); g2 = s * as_float(n.z);
+    } else if (op == OP_TETRA) {      // planes in the parent's frame; no matrix on the way back (tetrahedron.hpp:163-193)
+        f = prim_tetra(prog, pc, cx, cy, cz);
+        grad_tetra(prog, pc, cx, cy, cz, g0, g1, g2);
+    } else {                          // OP_LID: (0, 0, 1) everywhere (top_bottom_lid.hpp:62-76)
+        f = prim_lid(cz);
+        g0 = 0; g1 = 0; g2 = 1;
+    }
+    if (op == OP_TETRA || op == OP_LID) { o0 = g0; o1 = g1; o2 = g2; }
+    else M.back(g0, g1, g2, o0, o1, o2);
+}
+
 // ---- gradient mode: f and grad f in one pass (identical to the reference's O(depth^2) recursion) ----
 // `live` as in eval_values: a dead node is jumped over; a CSG node with one operand passes it on (value and gradient; the
 // lone second operand of a subtraction negated, transformed_subtract.hpp:76-85) through its own matrix, which is exactly
@@ -600,58 +672,9 @@ ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, const 
             vs[sp - 1][0] = r; vs[sp - 1][1] = o0; vs[sp - 1][2] = o1; vs[sp - 1][3] = o2;
             if (word & OP_FLAG_RESTORE) { --fp; cx = fs[fp][0]; cy = fs[fp][1]; cz = fs[fp][2]; }
         } else {
-            float x, y, z;
-            M.apply(cx, cy, cz, x, y, z);
-            float f, g0, g1, g2;
-            if (op == OP_METABALLS) {
-                const int nb = (int)hdr.z;
-                f = 0.0f; g0 = 0.0f; g1 = 0.0f; g2 = 0.0f;
-                for (int b = 0; b < nb; ++b) {
-                    const W4 q = prog.load4(pc), q2 = prog.load4(pc + 4);
-                    const float bx = as_float(q.x), by = as_float(q.y), bz = as_float(q.z);
-                    const float strength = as_float(q.w), subtract = as_float(q2.x);
-                    pc += 8;
-                    const float fx = x - bx, fx2 = fx * fx;
-                    const float fy = y - by, fy2 = fy * fy;
-                    const float fz = z - bz, fz2 = fz * fz;
-                    {   // implicit_ball :89-100: float literal, float sum
-                        const float h = 0.000001f + fx2 + fy2 + fz2;
-                        const float hinv = 1.0f / h;
-                        const float val = strength * hinv - subtract;
-                        f += val / 100.0f;
-                    }
-                    {   // gradient_ball :118-136: the literal is a double, h is summed in double then rounded
-                        const float h = (float)(0.000001 + (double)fx2 + (double)fy2 + (double)fz2);
-                        const float hinv = 1.0f / h;
-                        g0 += strength * (-2.0f * fx * hinv * hinv) / 100.0f;
-                        g1 += strength * (-2.0f * fy * hinv * hinv) / 100.0f;
-                        g2 += strength * (-2.0f * fz * hinv * hinv) / 100.0f;
-                    }
-                }
-            } else if (op == OP_ELLIPSOID) { f = prim_ellipsoid(x, y, z); grad_ellipsoid(x, y, z, g0, g1, g2); }
-            else if (op == OP_CYLINDER) { f = prim_cylinder(x, y, z); grad_cylinder(x, y, z, g0, g1, g2); }
-            else if (op == OP_CONE) { f = prim_cone(x, y, z); grad_cone(x, y, z, g0, g1, g2); }
-            else if (op == OP_CUBE) { f = prim_cube(x, y, z); grad_cube(x, y, z, g0, g1, g2); }
-            else if (op == OP_CUBE_SDF) { f = prim_cube_sdf(sdf, x, y, z); grad_cube(x, y, z, g0, g1, g2); }
-            else if (op == OP_TORUS) { f = prim_torus(x, y, z); grad_torus(x, y, z, g0, g1, g2); }
-            else if (op == OP_HEART) { f = prim_heart(x, y, z); grad_heart(x, y, z, g0, g1, g2); }
-            else if (op == OP_MUSHROOM) { f = prim_mushroom(x, y, z); grad_mushroom(x, y, z, g0, g1, g2); }
-            else if (op == OP_HALF_PLANE) {
-                f = prim_half_plane(prog, pc, x, y, z);
-                const W4 n = prog.load4(pc);
-                const float s = (f >= 0) ? -1.0f : 1.0f;      // half_plane.hpp:129-138, as written
-                g0 = s * as_float(n.x); g1 = s * as_float(n.y); g2 = s * as_float(n.z);
-            } else if (op == OP_TETRA) {      // planes in the parent's frame; no matrix on the way back (tetrahedron.hpp:163-193)
-                f = prim_tetra(prog, pc, cx, cy, cz);
-                grad_tetra(prog, pc, cx, cy, cz, g0, g1, g2);
-            } else {                          // OP_LID: (0, 0, 1) everywhere (top_bottom_lid.hpp:62-76)
-                f = prim_lid(cz);
-                g0 = 0; g1 = 0; g2 = 1;
-            }
-            if (op != OP_METABALLS) pc = (int)hdr.y;
-            float o0, o1, o2;
-            if (op == OP_TETRA || op == OP_LID) { o0 = g0; o1 = g1; o2 = g2; }
-            else M.back(g0, g1, g2, o0, o1, o2);
+            float f, o0, o1, o2;
+            prim_value_gradient(op, hdr, prog, pc, M, sdf, cx, cy, cz, f, o0, o1, o2);
+            pc = (int)hdr.y;
             vs[sp][0] = f; vs[sp][1] = o0; vs[sp][2] = o1; vs[sp][3] = o2;
             ++sp;
             present = (present << 1) | 1ull;
@@ -663,6 +686,62 @@ template <class Prog>
 ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, float cx, float cy, float cz, float& f_out, float& g0_out,
                                 float& g1_out, float& g2_out) {
     eval_value_gradient(prog, sdf, AllLive(), cx, cy, cz, f_out, g0_out, g1_out, g2_out);
+}
+
+// Gradient mode over a per-tile instruction list (entries from spec_entry_gradient, program order): what eval_value_gradient
+// does with the same liveness, without the dead-node jumps and the operand bookkeeping.
+template <class Prog, class List>
+ISD_HD void eval_value_gradient_list(const Prog& prog, const SdfGridView& sdf, const List& list, int n_list, float cx, float cy, float cz,
+                                     float& f_out, float& g0_out, float& g1_out, float& g2_out) {
+    float vs[kMaxValueStack][4];
+    float fs[kMaxFrameStack][3];
+    int sp = 0, fp = 0;
+    for (int k = 0; k < n_list; ++k) {
+        const uint32_t e = list[k];
+        const int pc = (int)(e & IT_PC_MASK) * 4;
+        Mat12<Prog> M;
+        M.load(prog, pc + 4);
+        if (e & LE_CLOSING) {
+            float r, a0, a1, a2;
+            if (e & LE_COMBINE) {
+                const bool swapped = (e & LE_SWAPPED) != 0;
+                const uint32_t op = (e >> LE_OP_SHIFT) & 3u;
+                --sp;
+                const int i1 = swapped ? sp : sp - 1, i2 = swapped ? sp - 1 : sp;
+                const float f1 = vs[i1][0], f2 = vs[i2][0];
+                bool first;
+                if (op == 0u) { first = (f1 > f2); r = first ? f1 : f2; }
+                else if (op == 1u) { first = !(f1 > f2); r = (f1 > f2) ? f2 : f1; }
+                else { first = (f1 < -f2); r = first ? f1 : -f2; }
+                if (first) { a0 = vs[i1][1]; a1 = vs[i1][2]; a2 = vs[i1][3]; }
+                else if (op == 2u) { a0 = -vs[i2][1]; a1 = -vs[i2][2]; a2 = -vs[i2][3]; }
+                else { a0 = vs[i2][1]; a1 = vs[i2][2]; a2 = vs[i2][3]; }
+            } else {
+                r = vs[sp - 1][0]; a0 = vs[sp - 1][1]; a1 = vs[sp - 1][2]; a2 = vs[sp - 1][3];
+                if (e & LE_NEGATE) { r = -r; a0 = -a0; a1 = -a1; a2 = -a2; }
+            }
+            float o0, o1, o2;
+            M.back(a0, a1, a2, o0, o1, o2);
+            vs[sp - 1][0] = r; vs[sp - 1][1] = o0; vs[sp - 1][2] = o1; vs[sp - 1][3] = o2;
+            if (e & LE_RESTORE) { --fp; cx = fs[fp][0]; cy = fs[fp][1]; cz = fs[fp][2]; }
+            continue;
+        }
+        const W4 hdr = prog.load4(pc);
+        const uint32_t word = hdr.x;
+        const uint32_t op = word & OP_MASK;
+        if (op == OP_XFORM) {
+            if (word & OP_FLAG_SAVE) { fs[fp][0] = cx; fs[fp][1] = cy; fs[fp][2] = cz; ++fp; }
+            float x, y, z;
+            M.apply(cx, cy, cz, x, y, z);
+            cx = x; cy = y; cz = z;
+            continue;
+        }
+        float f, o0, o1, o2;
+        prim_value_gradient(op, hdr, prog, pc + kInstrWords, M, sdf, cx, cy, cz, f, o0, o1, o2);
+        vs[sp][0] = f; vs[sp][1] = o0; vs[sp][2] = o1; vs[sp][3] = o2;
+        ++sp;
+    }
+    f_out = vs[0][0]; g0_out = vs[0][1]; g1_out = vs[0][2]; g2_out = vs[0][3];
 }
 
 }  // namespace isd

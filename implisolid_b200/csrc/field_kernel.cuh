@@ -464,29 +464,66 @@ struct TileLive {             // liveness mask of the tile being evaluated (unif
     }
 };
 
-// Liveness masks for evaluations at arbitrary points (the OB02 kernels: centroids, search points, bisection midpoints).  A
-// work-list tile's mask was proven over the tile's box grown by one cell, so it holds at every point whose containing node
-// cell lies in the tile; elsewhere (tiles proven inside / outside, points off the resident planes) there is no mask and the
-// whole tree runs.  Same bits either way (eval_values / eval_value_gradient with a Live predicate).
+// Per-tile instruction lists for evaluations at arbitrary points (the OB02 kernels: centroids, search points, bisection
+// midpoints).  A work-list tile's liveness mask was proven over the tile's box grown by one cell, so it holds at every point
+// whose containing node cell lies in the tile; k_build_point_lists turns every such mask into the tile's value list
+// (spec_entry) and gradient list (spec_entry_gradient) once per build, and an evaluation near the surface runs its tile's
+// list: no liveness tests, no dead-node jumps, no operand bookkeeping.  Elsewhere (tiles proven inside / outside, points off
+// the resident planes) there is no list and the whole tree runs.  Same bits either way (tests/emu checks the interpreters
+// against each other on the host).
 struct PointSpec {
     GridDesc g;
     const uint32_t* tile_bits;
     const unsigned* tile_slot;
-    const uint32_t* masks;
-    int TW, mask_words, enabled;
+    const uint32_t* lists;        // per work-list slot: `stride` value entries, then `stride` gradient entries
+    const uint32_t* list_len;     // per slot: value entries | gradient entries << 16
+    int TW, stride, enabled;
 };
 __constant__ PointSpec c_point_spec;      // set by the host after K1 of every build; disabled whenever another program is uploaded
-__device__ __forceinline__ const uint32_t* point_mask(const PointSpec& ps, float x, float y, float z) {
-    if (!ps.enabled) return nullptr;
+// work-list slot of the tile holding the point's node cell, or -1
+__device__ __forceinline__ int point_slot(const PointSpec& ps, float x, float y, float z) {
+    if (!ps.enabled) return -1;
     // node_coord(i) = i * w + min - 2w  =>  containing cell i = floor((p - min) / w + 2)
     const float fx = (x - ps.g.xmin) / ps.g.wx + 2.0f, fy = (y - ps.g.ymin) / ps.g.wy + 2.0f, fz = (z - ps.g.zmin) / ps.g.wz + 2.0f;
-    if (!(fx >= 0.0f && fy >= 0.0f && fz >= (float)ps.g.z0)) return nullptr;      // also rejects NaN
-    if (!(fx < (float)ps.g.S && fy < (float)ps.g.S && fz < (float)(ps.g.z0 + ps.g.nz))) return nullptr;
+    if (!(fx >= 0.0f && fy >= 0.0f && fz >= (float)ps.g.z0)) return -1;      // also rejects NaN
+    if (!(fx < (float)ps.g.S && fy < (float)ps.g.S && fz < (float)(ps.g.z0 + ps.g.nz))) return -1;
     const int tx = (int)fx >> 3, ty = (int)fy >> 3, tz = ((int)fz - ps.g.z0) >> 3;
     const int row = tz * ps.g.ty + ty;
-    if (!((__ldg(ps.tile_bits + (size_t)row * ps.TW + (tx >> 5)) >> (tx & 31)) & 1u)) return nullptr;
-    const unsigned slot = __ldg(ps.tile_slot + (size_t)row * ps.g.tx + tx);
-    return ps.masks + (size_t)slot * ps.mask_words;
+    if (!((__ldg(ps.tile_bits + (size_t)row * ps.TW + (tx >> 5)) >> (tx & 31)) & 1u)) return -1;
+    return (int)__ldg(ps.tile_slot + (size_t)row * ps.g.tx + tx);
+}
+struct GlobalList {
+    const uint32_t* p;
+    __device__ __forceinline__ uint32_t operator[](int k) const { return __ldg(p + k); }
+};
+
+// One warp per work-list tile: the tile's two instruction lists from its liveness mask, program order kept by ballot ranks.
+__global__ void __launch_bounds__(128) k_build_point_lists(const unsigned* __restrict__ list_count, const uint32_t* __restrict__ masks, int mask_words,
+                                                           const uint4* __restrict__ itab, int n_instr, int stride, uint32_t* __restrict__ lists,
+                                                           uint32_t* __restrict__ list_len) {
+    const unsigned n = list_count[0];
+    const int lane = threadIdx.x & 31;
+    for (unsigned slot = blockIdx.x * 4 + (threadIdx.x >> 5); slot < n; slot += gridDim.x * 4) {
+        const TileLive live(masks + (size_t)slot * mask_words, mask_words);
+        uint32_t* lv = lists + (size_t)slot * 2 * stride;
+        uint32_t* lg = lv + stride;
+        int nv = 0, ng = 0;
+        for (int i0 = 0; i0 < n_instr; i0 += 32) {
+            const int i = i0 + lane;
+            uint32_t eg = 0u;
+            if (i < n_instr) {
+                const uint4 it = __ldg(itab + i);
+                eg = spec_entry_gradient(W4{it.x, it.y, it.z, it.w}, live);
+            }
+            const uint32_t ev = (eg & LE_PASS) ? 0u : eg;      // spec_entry's answer: in value mode a pass-through does nothing
+            const unsigned mg = __ballot_sync(0xffffffffu, eg != 0u), mv = __ballot_sync(0xffffffffu, ev != 0u);
+            const unsigned below = (1u << lane) - 1u;
+            if (eg) lg[ng + __popc(mg & below)] = eg;
+            if (ev) lv[nv + __popc(mv & below)] = ev;
+            ng += __popc(mg); nv += __popc(mv);
+        }
+        if (lane == 0) list_len[slot] = (uint32_t)nv | ((uint32_t)ng << 16);
+    }
 }
 
 // SPEC: before evaluating a tile the block turns its liveness mask into the list of instructions the tile really runs

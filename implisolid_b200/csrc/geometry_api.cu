@@ -111,7 +111,7 @@ struct Context {
     int S = 0;
 
     // OB02 scratch
-    DeviceBuffer d_cen, d_nrm, d_deg, d_uoff, d_uitems, d_cursor, d_fof, d_w, d_len3, d_best, d_fc, d_state, d_proj, d_pnrm,
+    DeviceBuffer d_cen, d_nrm, d_deg, d_uoff, d_uitems, d_cursor, d_fof, d_w, d_len3, d_best, d_fc, d_state, d_proj, d_pnrm, d_point_lists,
         d_noise, d_scal, d_counters, d_upartials;
     bool adjacency_valid = false, fof_valid_ = false;
     float average_edge = 0.f;
@@ -208,7 +208,8 @@ void ensure_init(int device = -1) {
 inline void launched() { g.launches++; }
 #define ISD_LAUNCH_CHECK() do { ISD_CUDA(cudaGetLastError()); launched(); } while (0)
 
-// liveness masks at arbitrary points (field_kernel.cuh PointSpec): valid only for the program K1 has just bounded
+// per-tile instruction lists for evaluations at arbitrary points (field_kernel.cuh PointSpec): valid only for the program
+// and the grid K1 has just bounded
 void set_point_spec(const PointSpec* ps) {
     if (ps == nullptr) { g.point_spec_on = false; return; }      // the plain kernel instantiations never read c_point_spec
     ISD_CUDA(cudaMemcpyToSymbolAsync(c_point_spec, ps, sizeof(PointSpec), 0, cudaMemcpyHostToDevice, g.stream));
@@ -428,12 +429,9 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         }
     }
     ISD_CUDA(cudaEventRecord(g.ev[1], g.stream));
-    if (spec.enabled && s.point_spec != 0 && (s.point_spec > 0 || prog.num_nodes >= 8)) {
-        PointSpec ps;
-        ps.g = gd; ps.tile_bits = hints.tile_bits; ps.tile_slot = hints.tile_slot; ps.masks = spec.masks;
-        ps.TW = hints.TW; ps.mask_words = spec.mask_words; ps.enabled = 1;
-        set_point_spec(&ps);
-    }
+    // OB02 evaluates at points near the surface: they run per-tile instruction lists, built below once the work-list length is known
+    const bool want_point_lists = spec.enabled && s.point_spec != 0 && (s.point_spec > 0 || prog.num_nodes >= 8) && s.overall_repeats > 0 &&
+                                  (s.vresampl_iters > 0 || s.projection_enabled);
     // Per-segment arrays: sized for every tile when that is small (no read-back), else for the work list (one extra
     // read-back, negligible at the grid sizes where it happens).
     unsigned* h = g.h_small.as<unsigned>();
@@ -473,6 +471,23 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         if (own_row1 < n_rows) ISD_CUDA(cudaMemcpyAsync(h + 20, mb.row_base + own_row1, sizeof(Triple), cudaMemcpyDeviceToHost, g.stream));
     }
     ISD_CUDA(cudaStreamSynchronize(g.stream));
+    if (want_point_lists && h[8] > 0) {
+        const int n_instr = (int)(itab_words / 4);
+        const size_t list_bytes = (size_t)h[8] * 2 * n_instr * sizeof(uint32_t);
+        if (list_bytes <= ((size_t)4 << 30)) {      // enormous trees on enormous grids: the whole tree runs instead
+            g.d_point_lists.reserve(list_bytes + (size_t)h[8] * sizeof(uint32_t));
+            PointSpec ps;
+            ps.g = gd; ps.tile_bits = hints.tile_bits; ps.tile_slot = hints.tile_slot;
+            ps.lists = g.d_point_lists.as<uint32_t>();
+            ps.list_len = ps.lists + (size_t)h[8] * 2 * n_instr;
+            ps.TW = hints.TW; ps.stride = n_instr; ps.enabled = 1;
+            const unsigned want_blocks = (h[8] + 3) / 4, cap = (unsigned)g.sm_count * 16;
+            k_build_point_lists<<<want_blocks < cap ? want_blocks : cap, 128, 0, g.stream>>>(tile_count, spec.masks, spec.mask_words, d_itab, n_instr, n_instr,
+                                                                                             const_cast<uint32_t*>(ps.lists), const_cast<uint32_t*>(ps.list_len));
+            ISD_LAUNCH_CHECK();
+            set_point_spec(&ps);
+        }
+    }
     const unsigned n_cubes = h[2];
     if (m.ghost_rows == 0) { h[4] = 0; h[5] = 0; }
     g.d_cubes.reserve((size_t)(n_cubes > 0 ? n_cubes : 1) * sizeof(unsigned long long));

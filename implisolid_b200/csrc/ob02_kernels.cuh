@@ -64,24 +64,32 @@ __device__ __forceinline__ void count_if(bool pred, unsigned long long* ctr) {
 __device__ __forceinline__ float norm2f(float x, float y, float z) { return sqrtf(x * x + y * y + z * z); }
 __device__ __forceinline__ float sign_tol(float v) { return (v > kRootTolerance) ? 1.0f : (v < -kRootTolerance) ? -1.0f : 0.0f; }
 
-// f at a point / f and grad f at a point.  Near the surface the point lies in a work-list tile of K1, whose liveness mask
-// lets the interpreter jump over the CSG children that can never be selected there (same bits, a fraction of the work for
-// deep trees); elsewhere the whole tree runs.
+// f at a point / f and grad f at a point.  Near the surface the point lies in a work-list tile of K1, whose instruction
+// lists hold only what can matter there (same bits, a fraction of the work for deep trees); elsewhere the whole tree runs.
 // MASKED is a compile-time switch: shallow trees (and meshes that did not come from K1) run the plain instantiation, which
 // carries neither the tile look-up nor a second copy of the interpreter.
 template <bool MASKED>
 __device__ __forceinline__ float eval_f(const SdfGridView& sdf, float x, float y, float z) {
     float cx[1] = {x}, cy[1] = {y}, cz[1] = {z}, out[1];
-    const uint32_t* mask = MASKED ? point_mask(c_point_spec, x, y, z) : nullptr;
-    if (MASKED && mask != nullptr) eval_values<1>(ConstProgram(), sdf, TileLive(mask, c_point_spec.mask_words), cx, cy, cz, out);
-    else eval_values<1>(ConstProgram(), sdf, AllLive(), cx, cy, cz, out);
+    const int slot = MASKED ? point_slot(c_point_spec, x, y, z) : -1;
+    if (MASKED && slot >= 0) {
+        const int n = (int)(__ldg(c_point_spec.list_len + slot) & 0xffffu);
+        eval_values_list<1>(ConstProgram(), sdf, GlobalList{c_point_spec.lists + (size_t)slot * 2 * c_point_spec.stride}, n, cx, cy, cz, out);
+    } else {
+        eval_values<1>(ConstProgram(), sdf, AllLive(), cx, cy, cz, out);
+    }
     return out[0];
 }
 template <bool MASKED>
 __device__ __forceinline__ void eval_fg(const SdfGridView& sdf, float x, float y, float z, float& f, float& g0, float& g1, float& g2) {
-    const uint32_t* mask = MASKED ? point_mask(c_point_spec, x, y, z) : nullptr;
-    if (MASKED && mask != nullptr) eval_value_gradient(ConstProgram(), sdf, TileLive(mask, c_point_spec.mask_words), x, y, z, f, g0, g1, g2);
-    else eval_value_gradient(ConstProgram(), sdf, x, y, z, f, g0, g1, g2);
+    const int slot = MASKED ? point_slot(c_point_spec, x, y, z) : -1;
+    if (MASKED && slot >= 0) {
+        const int n = (int)(__ldg(c_point_spec.list_len + slot) >> 16);
+        eval_value_gradient_list(ConstProgram(), sdf, GlobalList{c_point_spec.lists + ((size_t)slot * 2 + 1) * c_point_spec.stride}, n, x, y, z,
+                                 f, g0, g1, g2);
+    } else {
+        eval_value_gradient(ConstProgram(), sdf, x, y, z, f, g0, g1, g2);
+    }
 }
 
 // ---- generic exclusive scan of a u32 array (three launches) ----------------------------------------------------------

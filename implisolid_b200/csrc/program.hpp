@@ -80,6 +80,7 @@ enum : uint32_t {
     IT_CLOSING = 1u << 16, IT_RESTORE = 1u << 17, IT_SWAPPED = 1u << 18, IT_OP_SHIFT = 19,      // op - OP_UNION in 2 bits
     LE_CLOSING = 1u << 16, LE_RESTORE = 1u << 17, LE_SWAPPED = 1u << 18, LE_OP_SHIFT = 19,
     LE_COMBINE = 1u << 21, LE_NEGATE = 1u << 22, LE_VALID = 1u << 31,
+    LE_PASS = 1u << 23,       // gradient lists only: live closing instruction with one operand and nothing to do in value mode
 };
 constexpr int kMaxSpecNodes = 2048;       // tile specialisation: per-tile liveness mask of at most this many bits
 constexpr int kMaxPendingDepth = 64;      // liveness pass: pending-sibling stack held in one 64-bit register

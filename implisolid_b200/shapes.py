@@ -90,15 +90,16 @@ def c4_deep_chain(n_prims=32, seed=1234):
 
 
 def demo_moon():
-    """MOON demo (nested Difference of cylinders), examples/js/example_objects.js:22-70, scaled to a unit box."""
-    s = 1.0 / 60.0
-    def sc(m):
+    """MOON demo (nested Difference of cylinders), examples/js/example_objects.js:22-70; the root matrix is scaled by 1/60 so
+    that the 42.5 x 49.6 x 10 plate fits a unit box (children's matrices are relative to their parents and stay as they are)."""
+    def sc(m, scale=1.0):
         m = np.array(m, dtype=np.float64).reshape(4, 4)
+        m[:3, :] *= scale
         return [float(np.float32(v)) for v in m.reshape(-1)]
     inner = {"type": "Difference", "matrix": sc([2.38, 0, 0, 0.36, 0, 2.38, 0, 0.56, 0, 0, 2.38, 6.9, 0, 0, 0, 1]),
              "children": [{"type": "cylinder", "matrix": sc([10, 0, 0, 0, 0, 10, 0, 0, 0, 0, 10, 0, 0, 0, 0, 1])},
                           {"type": "cylinder", "matrix": sc([10, 0, 0, 0.66, 0, 10, 0, 6.22, 0, 0, 10, 0.00001, 0, 0, 0, 1])}]}
-    return json.dumps({"type": "Difference", "matrix": sc([1, 0, 0, 0.33, 0, 1, 0, 0.156, 0, 0, 1, 0.000000000000014, 0, 0, 0, 1]),
+    return json.dumps({"type": "Difference", "matrix": sc([1, 0, 0, 0.33, 0, 1, 0, 0.156, 0, 0, 1, 0.000000000000014, 0, 0, 0, 1], 1.0 / 60.0),
                        "children": [{"type": "cylinder", "matrix": sc([42.5, 0, 0, 0, 0, 49.6, 0, 0, 0, 0, 10, 0, 0, 0, 0, 1])}, inner]})
 
 

@@ -142,6 +142,19 @@ extern "C" int emu_eval_masked(const char* shape_json, const float* pts, int n, 
             eval_value_gradient(prog, sdf, pts[i * 3], pts[i * 3 + 1], pts[i * 3 + 2], fa, ga[0], ga[1], ga[2]);
             eval_value_gradient(prog, sdf, MaskLive{mask}, pts[i * 3], pts[i * 3 + 1], pts[i * 3 + 2], fb, gb[0], gb[1], gb[2]);
             if (memcmp(&fa, &fb, 4) != 0 || memcmp(ga, gb, 12) != 0) f_masked[i] = __builtin_nanf("");
+            // and through the per-tile gradient list (what the OB02 kernels run from the lists k_build_point_lists leaves);
+            // the value interpreter must also accept that list (its LE_PASS entries do nothing there)
+            std::vector<uint32_t> glist;
+            for (size_t k = 0; k + 3 < p.itab.size(); k += 4) {
+                const uint32_t e = spec_entry_gradient(W4{p.itab[k], p.itab[k + 1], p.itab[k + 2], p.itab[k + 3]}, MaskLive{mask});
+                if (e) glist.push_back(e);
+            }
+            float fc, gc[3];
+            eval_value_gradient_list(prog, sdf, glist.data(), (int)glist.size(), pts[i * 3], pts[i * 3 + 1], pts[i * 3 + 2], fc, gc[0], gc[1], gc[2]);
+            if (memcmp(&fa, &fc, 4) != 0 || memcmp(ga, gc, 12) != 0) f_masked[i] = __builtin_nanf("");
+            float x3[1] = {pts[i * 3]}, y3[1] = {pts[i * 3 + 1]}, z3[1] = {pts[i * 3 + 2]}, out3[1];
+            eval_values_list<1>(prog, sdf, glist.data(), (int)glist.size(), x3, y3, z3, out3);
+            if (memcmp(out3, out, 4) != 0) f_masked[i] = __builtin_nanf("");
         }
         int cnt = 0;
         for (int k = 0; k < p.num_nodes; k++) cnt += (mask[k >> 5] >> (k & 31)) & 1;

@@ -101,10 +101,11 @@ def test_projected_centroids_lie_on_surface(gpu_lib):
 
 
 @pytest.mark.parametrize("shape,R,half", [(shapes.c4_deep_chain, 96, 1.0), (shapes.bushy_tree, 80, 0.9), (shapes.c3_metaballs, 64, 1.2),
-                                          (shapes.n1_medley, 72, 0.9)], ids=["c4", "bushy", "c3", "medley"])
+                                          (shapes.n1_medley, 72, 0.9), (shapes.c2_cube_minus_cylinder, 64, 0.8), (shapes.demo_moon, 64, 0.6)],
+                         ids=["c4", "bushy", "c3", "medley", "c2", "moon"])
 def test_point_masks_change_nothing(gpu_lib, shape, R, half):
-    """OB02 evaluations near the surface reuse K1's per-tile liveness masks (gpu.point_spec) and skip CSG children that can
-    never be selected there: vertices, projected centroids and their normals must keep every bit."""
+    """OB02 evaluations near the surface run per-tile instruction lists made from K1's liveness masks (gpu.point_spec) and so
+    skip CSG children that can never be selected there: vertices, projected centroids and their normals must keep every bit."""
     sj = shape()
     out = []
     for ps in (0, 1):
