@@ -37,8 +37,8 @@ struct McSettings {
                           // (no mesh exchange); 0: gather the stitched mesh on every GPU and optimise it replicated
     int balance;          // z-slab runs: 1 (default) slab boundaries follow the surface (equal counts of surface tiles per GPU, from a
                           // bounds-only pass every rank repeats identically); 0: equal numbers of cube layers (SURVEY §8e's formula)
-    int point_spec;       // -1 (default): the OB02 kernels use K1's per-tile liveness masks at their evaluation points when the tree has
-                          // at least 8 nodes; 0: never; 1: always (when masks exist)
+    int point_spec;       // -1 (default): the OB02 kernels run per-tile instruction lists (from K1's liveness masks) at their evaluation
+                          // points when the tree has at least 8 nodes; 0: never; 1: always (when masks exist)
     int normals;          // 1: per-vertex normals (-grad f/|grad f|) computed right after the last step (isd_get_n_ptr); 0: on first use
     int specialize;       // 1 (default): per-tile liveness masks let the evaluator skip CSG children that interval bounds prove
                           // are never selected in that tile (field values bit-identical); 0: every tile runs the whole tree
