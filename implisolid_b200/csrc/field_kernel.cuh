@@ -475,8 +475,8 @@ struct PointSpec {
     GridDesc g;
     const uint32_t* tile_bits;
     const unsigned* tile_slot;
-    const uint32_t* lists;        // per work-list slot: `stride` value entries, then `stride` gradient entries
-    const uint32_t* list_len;     // per slot: value entries | gradient entries << 16
+    const uint32_t* lists;        // per work-list slot two records of `stride` words, value list then gradient list:
+                                  // word 0 = number of entries, entries from word 1 (count and first entries share a sector)
     int TW, stride, enabled;
 };
 __constant__ PointSpec c_point_spec;      // set by the host after K1 of every build; disabled whenever another program is uploaded
@@ -499,13 +499,12 @@ struct GlobalList {
 
 // One warp per work-list tile: the tile's two instruction lists from its liveness mask, program order kept by ballot ranks.
 __global__ void __launch_bounds__(128) k_build_point_lists(const unsigned* __restrict__ list_count, const uint32_t* __restrict__ masks, int mask_words,
-                                                           const uint4* __restrict__ itab, int n_instr, int stride, uint32_t* __restrict__ lists,
-                                                           uint32_t* __restrict__ list_len) {
+                                                           const uint4* __restrict__ itab, int n_instr, int stride, uint32_t* __restrict__ lists) {
     const unsigned n = list_count[0];
     const int lane = threadIdx.x & 31;
     for (unsigned slot = blockIdx.x * 4 + (threadIdx.x >> 5); slot < n; slot += gridDim.x * 4) {
         const TileLive live(masks + (size_t)slot * mask_words, mask_words);
-        uint32_t* lv = lists + (size_t)slot * 2 * stride;
+        uint32_t* lv = lists + (size_t)slot * 2 * stride + 1;
         uint32_t* lg = lv + stride;
         int nv = 0, ng = 0;
         for (int i0 = 0; i0 < n_instr; i0 += 32) {
@@ -522,7 +521,7 @@ __global__ void __launch_bounds__(128) k_build_point_lists(const unsigned* __res
             if (ev) lv[nv + __popc(mv & below)] = ev;
             ng += __popc(mg); nv += __popc(mv);
         }
-        if (lane == 0) list_len[slot] = (uint32_t)nv | ((uint32_t)ng << 16);
+        if (lane == 0) { lv[-1] = (uint32_t)nv; lg[-1] = (uint32_t)ng; }
     }
 }
 

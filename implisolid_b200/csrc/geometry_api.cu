@@ -472,18 +472,17 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     }
     ISD_CUDA(cudaStreamSynchronize(g.stream));
     if (want_point_lists && h[8] > 0) {
-        const int n_instr = (int)(itab_words / 4);
-        const size_t list_bytes = (size_t)h[8] * 2 * n_instr * sizeof(uint32_t);
+        const int n_instr = (int)(itab_words / 4), stride = n_instr + 1;
+        const size_t list_bytes = (size_t)h[8] * 2 * stride * sizeof(uint32_t);
         if (list_bytes <= ((size_t)4 << 30)) {      // enormous trees on enormous grids: the whole tree runs instead
-            g.d_point_lists.reserve(list_bytes + (size_t)h[8] * sizeof(uint32_t));
+            g.d_point_lists.reserve(list_bytes);
             PointSpec ps;
             ps.g = gd; ps.tile_bits = hints.tile_bits; ps.tile_slot = hints.tile_slot;
             ps.lists = g.d_point_lists.as<uint32_t>();
-            ps.list_len = ps.lists + (size_t)h[8] * 2 * n_instr;
-            ps.TW = hints.TW; ps.stride = n_instr; ps.enabled = 1;
+            ps.TW = hints.TW; ps.stride = stride; ps.enabled = 1;
             const unsigned want_blocks = (h[8] + 3) / 4, cap = (unsigned)g.sm_count * 16;
-            k_build_point_lists<<<want_blocks < cap ? want_blocks : cap, 128, 0, g.stream>>>(tile_count, spec.masks, spec.mask_words, d_itab, n_instr, n_instr,
-                                                                                             const_cast<uint32_t*>(ps.lists), const_cast<uint32_t*>(ps.list_len));
+            k_build_point_lists<<<want_blocks < cap ? want_blocks : cap, 128, 0, g.stream>>>(tile_count, spec.masks, spec.mask_words, d_itab, n_instr, stride,
+                                                                                             g.d_point_lists.as<uint32_t>());
             ISD_LAUNCH_CHECK();
             set_point_spec(&ps);
         }
@@ -869,7 +868,8 @@ void projection_step(bool enable_qem, bool exact_reduce) {
         a.noise = noise_stream((size_t)(face_base + nf) * 3) + face_base * 3;
         a.speculative = 0;
         const int n_left = (int)hc->c[10];
-        (g.point_spec_on ? k_project_leftovers<true> : k_project_leftovers<false>)<<<blocks_for(n_left, 4), 128, 0, g.stream>>>(g.sdf, a, n_left);
+        const unsigned left_blocks = blocks_for(n_left, 4) < (unsigned)g.sm_count * 16 ? blocks_for(n_left, 4) : (unsigned)g.sm_count * 16;
+        (g.point_spec_on ? k_project_leftovers<true> : k_project_leftovers<false>)<<<left_blocks, 128, 0, g.stream>>>(g.sdf, a, n_left);
         ISD_LAUNCH_CHECK();
         (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a);
         ISD_LAUNCH_CHECK();

@@ -73,8 +73,8 @@ __device__ __forceinline__ float eval_f(const SdfGridView& sdf, float x, float y
     float cx[1] = {x}, cy[1] = {y}, cz[1] = {z}, out[1];
     const int slot = MASKED ? point_slot(c_point_spec, x, y, z) : -1;
     if (MASKED && slot >= 0) {
-        const int n = (int)(__ldg(c_point_spec.list_len + slot) & 0xffffu);
-        eval_values_list<1>(ConstProgram(), sdf, GlobalList{c_point_spec.lists + (size_t)slot * 2 * c_point_spec.stride}, n, cx, cy, cz, out);
+        const uint32_t* rec = c_point_spec.lists + (size_t)slot * 2 * c_point_spec.stride;
+        eval_values_list<1>(ConstProgram(), sdf, GlobalList{rec + 1}, (int)__ldg(rec), cx, cy, cz, out);
     } else {
         eval_values<1>(ConstProgram(), sdf, AllLive(), cx, cy, cz, out);
     }
@@ -84,9 +84,8 @@ template <bool MASKED>
 __device__ __forceinline__ void eval_fg(const SdfGridView& sdf, float x, float y, float z, float& f, float& g0, float& g1, float& g2) {
     const int slot = MASKED ? point_slot(c_point_spec, x, y, z) : -1;
     if (MASKED && slot >= 0) {
-        const int n = (int)(__ldg(c_point_spec.list_len + slot) >> 16);
-        eval_value_gradient_list(ConstProgram(), sdf, GlobalList{c_point_spec.lists + ((size_t)slot * 2 + 1) * c_point_spec.stride}, n, x, y, z,
-                                 f, g0, g1, g2);
+        const uint32_t* rec = c_point_spec.lists + ((size_t)slot * 2 + 1) * c_point_spec.stride;
+        eval_value_gradient_list(ConstProgram(), sdf, GlobalList{rec + 1}, (int)__ldg(rec), x, y, z, f, g0, g1, g2);
     } else {
         eval_value_gradient(ConstProgram(), sdf, x, y, z, f, g0, g1, g2);
     }
@@ -526,71 +525,73 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
 // evaluations, so the lanes take one each and the first success in that order wins, as in the reference's sequential walk.
 template <bool MASKED>
 __global__ void __launch_bounds__(128) k_project_leftovers(SdfGridView sdf, ProjectArgs a, int n_left) {
-    const int li = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (li >= n_left) return;
-    const int i = a.leftover[li];
-    const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
+    const int lane = threadIdx.x & 31;
     const float edge = a.al->avg_edge;
     const float* alphas = a.al->alpha;
     const int n_short = a.al->n_short;
-    const float s_c = sign_tol(a.fc[i]);
-    float dir[5][3];
-    {
-        float nx, ny, nz;
-        facet_normal(a.verts, a.faces, i, nx, ny, nz);
-        // type 2: facet normal x noise, normalize_1111   (create_directions_bundle :230-262; add_inplace works on copies)
-        const float px = a.noise[i * 3], py = a.noise[i * 3 + 1], pz = a.noise[i * 3 + 2];
-        float zx = ny * pz - nz * py, zy = nz * px - nx * pz, zz = nx * py - ny * px;
+    if (n_short == 0) return;      // mean edge below the reference's smallest step: no candidates, every left-over stays failed
+    for (int li = blockIdx.x * 4 + (threadIdx.x >> 5); li < n_left; li += gridDim.x * 4) {
+        const int i = a.leftover[li];
+        const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
+        const float s_c = sign_tol(a.fc[i]);
+        float dir[5][3];
         {
-            const float n = norm2f(zx, zy, zz);
-            zx = zx / n; zy = zy / n; zz = zz / n;
+            float nx, ny, nz;
+            facet_normal(a.verts, a.faces, i, nx, ny, nz);
+            // type 2: facet normal x noise, normalize_1111   (create_directions_bundle :230-262; add_inplace works on copies)
+            const float px = a.noise[i * 3], py = a.noise[i * 3 + 1], pz = a.noise[i * 3 + 2];
+            float zx = ny * pz - nz * py, zy = nz * px - nx * pz, zz = nx * py - ny * px;
+            {
+                const float n = norm2f(zx, zy, zz);
+                zx = zx / n; zy = zy / n; zz = zz / n;
+            }
+            // type 3: facet normal x previous direction, normalise_inplace
+            float wx = ny * zz - nz * zy, wy = nz * zx - nx * zz, wz = nx * zy - ny * zx;
+            float n = norm2f(wx, wy, wz);
+            n = (n < kMinGradientLen) ? 1.0f : n;
+            const float factor = 1.0f / n;
+            wx = wx * factor; wy = wy * factor; wz = wz * factor;
+            dir[0][0] = zx; dir[0][1] = zy; dir[0][2] = zz;
+            dir[1][0] = wx; dir[1][1] = wy; dir[1][2] = wz;
+    #pragma unroll
+            for (int d = 0; d < 3; ++d) { dir[2 + d][0] = d == 0 ? 1.0f : 0.0f; dir[2 + d][1] = d == 1 ? 1.0f : 0.0f; dir[2 + d][2] = d == 2 ? 1.0f : 0.0f; }
         }
-        // type 3: facet normal x previous direction, normalise_inplace
-        float wx = ny * zz - nz * zy, wy = nz * zx - nx * zz, wz = nx * zy - ny * zx;
-        float n = norm2f(wx, wy, wz);
-        n = (n < kMinGradientLen) ? 1.0f : n;
-        const float factor = 1.0f / n;
-        wx = wx * factor; wy = wy * factor; wz = wz * factor;
-        dir[0][0] = zx; dir[0][1] = zy; dir[0][2] = zz;
-        dir[1][0] = wx; dir[1][1] = wy; dir[1][2] = wz;
-#pragma unroll
-        for (int d = 0; d < 3; ++d) { dir[2 + d][0] = d == 0 ? 1.0f : 0.0f; dir[2 + d][1] = d == 1 ? 1.0f : 0.0f; dir[2 + d][2] = d == 2 ? 1.0f : 0.0f; }
-    }
-    const int n_cand = 5 * n_short;
-    bool ok = false;
-    int type = -1;
-    float bx = -10.0f, by = -10.0f, bz = -10.0f, bf = 0.0f;
-    for (int c0 = 0; c0 < n_cand && !ok; c0 += 32) {
-        const int c = c0 + lane;
-        bool mine = false;
-        float x = 0.0f, y = 0.0f, z = 0.0f, f = 0.0f;
-        if (c < n_cand) {
-            const int d = c / n_short, ai = c - d * n_short;
-            float dx = 0.0f, dy = 0.0f, dz = 0.0f;
-#pragma unroll
-            for (int k = 0; k < 5; ++k)
-                if (d == k) { dx = dir[k][0]; dy = dir[k][1]; dz = dir[k][2]; }
-            const float cc = edge * __ldg(alphas + ai);
-            x = cx + cc * dx; y = cy + cc * dy; z = cz + cc * dz;
-            f = eval_f<MASKED>(sdf, x, y, z);
-            mine = sign_tol(f) * s_c <= 0.0f;
+        const int n_cand = 5 * n_short;
+        bool ok = false;
+        int type = -1;
+        float bx = -10.0f, by = -10.0f, bz = -10.0f, bf = 0.0f;
+        for (int c0 = 0; c0 < n_cand && !ok; c0 += 32) {
+            const int c = c0 + lane;
+            bool mine = false;
+            float x = 0.0f, y = 0.0f, z = 0.0f, f = 0.0f;
+            if (c < n_cand) {
+                const int d = c / n_short, ai = c - d * n_short;
+                float dx = 0.0f, dy = 0.0f, dz = 0.0f;
+    #pragma unroll
+                for (int k = 0; k < 5; ++k)
+                    if (d == k) { dx = dir[k][0]; dy = dir[k][1]; dz = dir[k][2]; }
+                const float cc = edge * __ldg(alphas + ai);
+                x = cx + cc * dx; y = cy + cc * dy; z = cz + cc * dz;
+                f = eval_f<MASKED>(sdf, x, y, z);
+                mine = sign_tol(f) * s_c <= 0.0f;
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, mine);
+            if (m) {
+                const int w = __ffs(m) - 1;
+                bx = __shfl_sync(0xffffffffu, x, w); by = __shfl_sync(0xffffffffu, y, w); bz = __shfl_sync(0xffffffffu, z, w);
+                bf = __shfl_sync(0xffffffffu, f, w);
+                type = 2 + (c0 + w) / n_short;
+                ok = true;
+            }
         }
-        const unsigned m = __ballot_sync(0xffffffffu, mine);
-        if (m) {
-            const int w = __ffs(m) - 1;
-            bx = __shfl_sync(0xffffffffu, x, w); by = __shfl_sync(0xffffffffu, y, w); bz = __shfl_sync(0xffffffffu, z, w);
-            bf = __shfl_sync(0xffffffffu, f, w);
-            type = 2 + (c0 + w) / n_short;
-            ok = true;
-        }
-    }
-    if (lane == 0) {
-        if (ok) {
-            a.best[i] = make_float4(bx, by, bz, bf);
-            a.state[i] = 1;
-            atomicAdd(&a.counters->c[type], 1ull);
-        } else {
-            a.state[i] = 2;
+        if (lane == 0) {
+            if (ok) {
+                a.best[i] = make_float4(bx, by, bz, bf);
+                a.state[i] = 1;
+                atomicAdd(&a.counters->c[type], 1ull);
+            } else {
+                a.state[i] = 2;
+            }
         }
     }
 }

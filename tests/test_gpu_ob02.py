@@ -39,6 +39,8 @@ def test_adjacency_octahedron_and_mc_mesh(gpu_lib, oracle):
     ("metaballs", shapes.c3_metaballs, 40, 1.2),
     ("chain", shapes.c4_deep_chain, 56, 1.0),
     ("bushy", shapes.bushy_tree, 44, 0.9),
+    ("short_alpha_list", shapes.tiny_sphere, 12, 0.02),      # mean edge 0.0029: six alphas
+    ("empty_alpha_list", shapes.tiny_sphere, 40, 0.02),      # mean edge 0.0009: none, every centroid stays where it is
 ])
 def test_full_pipeline_vs_oracle(gpu_lib, oracle, name, shape, R, half):
     sj = shape()

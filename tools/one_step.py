@@ -24,6 +24,9 @@ ap.add_argument("--warm", type=int, default=2)
 ap.add_argument("--gpu", nargs="*", default=[])
 a = ap.parse_args()
 
+if os.environ.get("ISD_LIB_OVERRIDE"):      # A/B against another build of the library (profiling only)
+    import implisolid_b200.api as _api
+    _api._LIB = os.environ["ISD_LIB_OVERRIDE"]
 lib = implisolid_b200.load_library()
 fn, half = CFG[a.cfg]
 kw = dict(iters=1, c=1.0, projection=1, qem=1) if a.ob02 else {}
