@@ -624,8 +624,9 @@ ISD_HD void prim_value_gradient(uint32_t op, const W4& hdr, const Prog& prog, in
 template <class Prog, class Live>
 ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, const Live& live, float cx, float cy, float cz, float& f_out,
                                 float& g0_out, float& g1_out, float& g2_out) {
-    float vs[kMaxValueStack][4];
+    float vs[kMaxValueStack][4];      // all but the newest entry; the newest lives in registers (t*), valid when sp > 0
     float fs[kMaxFrameStack][3];
+    float tf = 0.0f, t0 = 0.0f, t1 = 0.0f, t2 = 0.0f;
     int sp = 0, fp = 0, pc = 0;
     unsigned long long present = 0ull;
     for (;;) {
@@ -653,34 +654,34 @@ ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, const 
             float r, a0, a1, a2;
             if (top_there && below_there) {
                 --sp;
-                const int i1 = swapped ? sp : sp - 1, i2 = swapped ? sp - 1 : sp;
-                const float f1 = vs[i1][0], f2 = vs[i2][0];
+                const float bf = vs[sp - 1][0], b0 = vs[sp - 1][1], b1 = vs[sp - 1][2], b2 = vs[sp - 1][3];      // the entry below the top
+                const float f1 = swapped ? tf : bf, f2 = swapped ? bf : tf;
                 bool first;
                 if (op == OP_UNION) { first = (f1 > f2); r = first ? f1 : f2; }
                 else if (op == OP_INTERSECT) { first = !(f1 > f2); r = (f1 > f2) ? f2 : f1; }
                 else { first = (f1 < -f2); r = first ? f1 : -f2; }
-                if (first) { a0 = vs[i1][1]; a1 = vs[i1][2]; a2 = vs[i1][3]; }
-                else if (op == OP_SUBTRACT) { a0 = -vs[i2][1]; a1 = -vs[i2][2]; a2 = -vs[i2][3]; }
-                else { a0 = vs[i2][1]; a1 = vs[i2][2]; a2 = vs[i2][3]; }
+                const bool take_top = (first == swapped);      // operand 1 is the top entry when swapped
+                a0 = take_top ? t0 : b0; a1 = take_top ? t1 : b1; a2 = take_top ? t2 : b2;
+                if (!first && op == OP_SUBTRACT) { a0 = -a0; a1 = -a1; a2 = -a2; }
             } else {
                 const bool negate = (op == OP_SUBTRACT) && (top_there != swapped);      // the lone operand is f2
-                r = vs[sp - 1][0]; a0 = vs[sp - 1][1]; a1 = vs[sp - 1][2]; a2 = vs[sp - 1][3];
+                r = tf; a0 = t0; a1 = t1; a2 = t2;
                 if (negate) { r = -r; a0 = -a0; a1 = -a1; a2 = -a2; }
             }
-            float o0, o1, o2;
-            M.back(a0, a1, a2, o0, o1, o2);
-            vs[sp - 1][0] = r; vs[sp - 1][1] = o0; vs[sp - 1][2] = o1; vs[sp - 1][3] = o2;
+            tf = r;
+            M.back(a0, a1, a2, t0, t1, t2);
             if (word & OP_FLAG_RESTORE) { --fp; cx = fs[fp][0]; cy = fs[fp][1]; cz = fs[fp][2]; }
         } else {
             float f, o0, o1, o2;
             prim_value_gradient(op, hdr, prog, pc, M, sdf, cx, cy, cz, f, o0, o1, o2);
             pc = (int)hdr.y;
-            vs[sp][0] = f; vs[sp][1] = o0; vs[sp][2] = o1; vs[sp][3] = o2;
+            if (sp > 0) { vs[sp - 1][0] = tf; vs[sp - 1][1] = t0; vs[sp - 1][2] = t1; vs[sp - 1][3] = t2; }
+            tf = f; t0 = o0; t1 = o1; t2 = o2;
             ++sp;
             present = (present << 1) | 1ull;
         }
     }
-    f_out = vs[0][0]; g0_out = vs[0][1]; g1_out = vs[0][2]; g2_out = vs[0][3];
+    f_out = tf; g0_out = t0; g1_out = t1; g2_out = t2;
 }
 template <class Prog>
 ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, float cx, float cy, float cz, float& f_out, float& g0_out,
@@ -693,8 +694,9 @@ ISD_HD void eval_value_gradient(const Prog& prog, const SdfGridView& sdf, float 
 template <class Prog, class List>
 ISD_HD void eval_value_gradient_list(const Prog& prog, const SdfGridView& sdf, const List& list, int n_list, float cx, float cy, float cz,
                                      float& f_out, float& g0_out, float& g1_out, float& g2_out) {
-    float vs[kMaxValueStack][4];
+    float vs[kMaxValueStack][4];      // all but the newest entry; the newest lives in registers (t*), valid when sp > 0
     float fs[kMaxFrameStack][3];
+    float tf = 0.0f, t0 = 0.0f, t1 = 0.0f, t2 = 0.0f;
     int sp = 0, fp = 0;
     for (int k = 0; k < n_list; ++k) {
         const uint32_t e = list[k];
@@ -702,27 +704,25 @@ ISD_HD void eval_value_gradient_list(const Prog& prog, const SdfGridView& sdf, c
         Mat12<Prog> M;
         M.load(prog, pc + 4);
         if (e & LE_CLOSING) {
-            float r, a0, a1, a2;
+            float r = tf, a0 = t0, a1 = t1, a2 = t2;      // one operand: it passes through the node's matrix (LE_PASS, LE_NEGATE)
             if (e & LE_COMBINE) {
                 const bool swapped = (e & LE_SWAPPED) != 0;
                 const uint32_t op = (e >> LE_OP_SHIFT) & 3u;
                 --sp;
-                const int i1 = swapped ? sp : sp - 1, i2 = swapped ? sp - 1 : sp;
-                const float f1 = vs[i1][0], f2 = vs[i2][0];
+                const float bf = vs[sp - 1][0], b0 = vs[sp - 1][1], b1 = vs[sp - 1][2], b2 = vs[sp - 1][3];      // the entry below the top
+                const float f1 = swapped ? tf : bf, f2 = swapped ? bf : tf;
                 bool first;
                 if (op == 0u) { first = (f1 > f2); r = first ? f1 : f2; }
                 else if (op == 1u) { first = !(f1 > f2); r = (f1 > f2) ? f2 : f1; }
                 else { first = (f1 < -f2); r = first ? f1 : -f2; }
-                if (first) { a0 = vs[i1][1]; a1 = vs[i1][2]; a2 = vs[i1][3]; }
-                else if (op == 2u) { a0 = -vs[i2][1]; a1 = -vs[i2][2]; a2 = -vs[i2][3]; }
-                else { a0 = vs[i2][1]; a1 = vs[i2][2]; a2 = vs[i2][3]; }
-            } else {
-                r = vs[sp - 1][0]; a0 = vs[sp - 1][1]; a1 = vs[sp - 1][2]; a2 = vs[sp - 1][3];
-                if (e & LE_NEGATE) { r = -r; a0 = -a0; a1 = -a1; a2 = -a2; }
+                const bool take_top = (first == swapped);      // operand 1 is the top entry when swapped
+                a0 = take_top ? t0 : b0; a1 = take_top ? t1 : b1; a2 = take_top ? t2 : b2;
+                if (!first && op == 2u) { a0 = -a0; a1 = -a1; a2 = -a2; }
+            } else if (e & LE_NEGATE) {
+                r = -r; a0 = -a0; a1 = -a1; a2 = -a2;
             }
-            float o0, o1, o2;
-            M.back(a0, a1, a2, o0, o1, o2);
-            vs[sp - 1][0] = r; vs[sp - 1][1] = o0; vs[sp - 1][2] = o1; vs[sp - 1][3] = o2;
+            tf = r;
+            M.back(a0, a1, a2, t0, t1, t2);
             if (e & LE_RESTORE) { --fp; cx = fs[fp][0]; cy = fs[fp][1]; cz = fs[fp][2]; }
             continue;
         }
@@ -738,10 +738,11 @@ ISD_HD void eval_value_gradient_list(const Prog& prog, const SdfGridView& sdf, c
         }
         float f, o0, o1, o2;
         prim_value_gradient(op, hdr, prog, pc + kInstrWords, M, sdf, cx, cy, cz, f, o0, o1, o2);
-        vs[sp][0] = f; vs[sp][1] = o0; vs[sp][2] = o1; vs[sp][3] = o2;
+        if (sp > 0) { vs[sp - 1][0] = tf; vs[sp - 1][1] = t0; vs[sp - 1][2] = t1; vs[sp - 1][3] = t2; }
+        tf = f; t0 = o0; t1 = o1; t2 = o2;
         ++sp;
     }
-    f_out = vs[0][0]; g0_out = vs[0][1]; g1_out = vs[0][2]; g2_out = vs[0][3];
+    f_out = tf; g0_out = t0; g1_out = t1; g2_out = t2;
 }
 
 }  // namespace isd
