@@ -175,3 +175,37 @@ def n1_medley():
     hp = {"type": "half_plane", "matrix": _mat(np.eye(3), [0, 0, 0]), "plane_vector": [0.0, 0.3, 1.0], "plane_point": [0.0, 0.0, 0.35]}
     u = {"type": "Union", "matrix": _mat(_rot_axis([0, 0, 1], 8.0) * 0.95, [0.01, 0.0, 0.0]), "children": [tor, hrt, tet, msh]}
     return json.dumps({"type": "Difference", "matrix": EYE, "children": [u, hp]})
+
+
+def random_tree(seed, depth=4):
+    """A random CSG tree for property tests: random shape (chains and bushy parts mixed), every operator, every analytic
+    primitive except the double-precision ones (torus / heart / mushroom agree with glibc's pow only on most points),
+    n-ary unions, random similarity-ish transforms on every node."""
+    rng = np.random.default_rng(seed)
+    kinds = ["cube", "cylinder", "ellipsoid", "icone", "meta_balls", "tetrahedron", "half_plane", "top_bottom_lid"]
+
+    def aff(scale_lo, scale_hi, shift):
+        R = _rot_axis(rng.normal(size=3), rng.uniform(-40, 40)) * rng.uniform(scale_lo, scale_hi)
+        return _mat(R, rng.uniform(-shift, shift, size=3))
+
+    def prim():
+        k = kinds[int(rng.integers(len(kinds)))]
+        node = {"type": k, "matrix": aff(0.5, 1.1, 0.3)}
+        if k == "tetrahedron":
+            node["corners"] = [[-0.5, -0.4, -0.45], [0.55, -0.35, -0.4], [0.0, 0.6, -0.35], [0.05, 0.0, 0.6]]
+        elif k == "half_plane":
+            node["plane_vector"] = [float(np.float32(v)) for v in rng.normal(size=3)]
+            node["plane_point"] = [float(np.float32(v)) for v in rng.uniform(-0.2, 0.2, size=3)]
+        return node
+
+    def tree(d):
+        if d == 0 or rng.uniform() < 0.25:
+            return prim()
+        op = ["Union", "Intersection", "Difference"][int(rng.integers(3))]
+        n = int(rng.integers(2, 5)) if op == "Union" else 2      # the factory folds n-ary unions; the others take two
+        return {"type": op, "matrix": aff(0.9, 1.1, 0.05), "children": [tree(d - 1) for _ in range(n)]}
+
+    root = tree(depth)
+    if "children" not in root:
+        root = {"type": "Union", "matrix": EYE, "children": [root, prim()]}
+    return json.dumps(root)

@@ -59,3 +59,20 @@ def test_dead_children_are_skipped_without_changing_bits(emu, oracle, name):
     assert np.array_equal(fm.view(np.uint32), fo.view(np.uint32))
     depth_bound = int(np.ceil(np.log2(nodes + 1))) if name == "bushy_tree" else nodes
     assert live.max() <= depth_bound and live.min() >= 1
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_trees_every_interpreter_bit_exact(emu, oracle, seed):
+    """Random CSG trees (every operator, n-ary unions, chains and bushy parts, random transforms on every node): the value
+    interpreter (1 and 4 points), the gradient interpreter, both under per-point liveness masks and both in per-tile list
+    form must return the oracle's bits."""
+    sj = shapes.random_tree(seed)
+    rng = np.random.default_rng(100 + seed)
+    pts = np.concatenate([rng.uniform(-1.2, 1.2, (1500, 3)), rng.normal(0, 0.3, (500, 3))]).astype(np.float32)
+    fo = oracle.query_implicit_values(sj, pts)
+    go = oracle.query_normals(sj, pts, normalize_and_invert=False)
+    f1, f4, g = emu.eval(sj, pts)
+    ft, fm, live, nodes = emu.eval_masked(sj, pts)       # NaN-poisoned if any masked / list interpreter disagrees
+    for got in (f1, f4, ft, fm):
+        assert np.array_equal(got.view(np.uint32), fo.view(np.uint32))
+    assert np.array_equal(g.view(np.uint32), go.view(np.uint32))
