@@ -114,6 +114,8 @@ def fp32_peak_tflops():
     """Non-tensor FP32 peak of this GPU, measured by tools/fp32_peak (FMUL+FADD separately rounded = exact mode)."""
     exe = os.path.join(ROOT, "tools", "fp32_peak")
     try:
+        if not os.path.exists(exe):      # __graft_entry__.build() makes it; a bare checkout builds it here
+            subprocess.run(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-o", exe, exe + ".cu"], check=True, capture_output=True, timeout=120)
         out = subprocess.run([exe], capture_output=True, text=True, timeout=60).stdout.strip().splitlines()[-1]
         d = json.loads(out)
         return d
