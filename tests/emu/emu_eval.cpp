@@ -162,3 +162,73 @@ extern "C" int emu_eval_masked(const char* shape_json, const float* pts, int n, 
     }
     return p.can_specialize ? p.num_nodes : -p.num_nodes;
 }
+
+// ---- interval bounds, pruning decisions and liveness masks (csg_bounds.cuh) ----------------------------------------------
+// For every box: bounds of the tree over the box, the liveness mask made from the decisions, then a second level the way K1
+// does it (a sub-box bounded under the first mask).  At random points of the box the exact value must lie inside the bounds,
+// and every interpreter run under the mask (walk, value list, gradient list) must return the bits of the full evaluation;
+// the second-level mask must never be looser than the first.
+// out[0] bounds violations, out[1] value mismatches under a mask, out[2] gradient mismatches, out[3] second-level masks with a
+// bit the first level lacks, out[4] sum of live nodes over the boxes, out[5] boxes proven entirely inside or outside.
+#include "../../implisolid_b200/csrc/csg_bounds.cuh"
+
+extern "C" int emu_bounds_check(const char* shape_json, const float* boxes, int n_boxes, int samples, unsigned seed, long long* out) {
+    ShapeOptions o;
+    ShapeCompiler c(o);
+    auto tree = c.parse(shape_json, false);
+    ShapeCompiler::Program p = c.compile(*tree);
+    for (int k = 0; k < 6; k++) out[k] = 0;
+    if (!p.can_specialize) return -p.num_nodes;
+    HostProg prog{p.words.data()};
+    SdfGridView sdf{nullptr, 0, 0, 0, 0, 0, 0, 0};
+    SpecDesc spec{};
+    spec.enabled = 1; spec.num_nodes = p.num_nodes; spec.num_ops = (p.num_nodes - 1) / 2; spec.mask_words = (p.num_nodes + 31) / 32;
+    spec.topo = p.topo.data();
+    unsigned long long rng = 0x9E3779B97F4A7C15ull ^ seed;
+    auto uni = [&rng]() {      // xorshift64*, uniform in [0, 1)
+        rng ^= rng >> 12; rng ^= rng << 25; rng ^= rng >> 27;
+        return (float)(((rng * 0x2545F4914F6CDD1Dull) >> 40) * (1.0 / 16777216.0));
+    };
+    std::vector<uint32_t> mask(spec.mask_words), mask2(spec.mask_words);
+    uint32_t decisions[kDecisionWords];
+    auto check_points = [&](const float* bx, const Ival& b, const std::vector<uint32_t>& m, bool check_bounds) {
+        std::vector<uint32_t> vlist, glist;
+        for (size_t k = 0; k + 3 < p.itab.size(); k += 4) {
+            const W4 it{p.itab[k], p.itab[k + 1], p.itab[k + 2], p.itab[k + 3]};
+            const uint32_t ev = spec_entry(it, MaskLive{m.data()}), eg = spec_entry_gradient(it, MaskLive{m.data()});
+            if (ev) vlist.push_back(ev);
+            if (eg) glist.push_back(eg);
+        }
+        for (int s = 0; s < samples; s++) {
+            const float x = bx[0] + (2.0f * uni() - 1.0f) * bx[3], y = bx[1] + (2.0f * uni() - 1.0f) * bx[4], z = bx[2] + (2.0f * uni() - 1.0f) * bx[5];
+            float fa, ga[3];
+            eval_value_gradient(prog, sdf, x, y, z, fa, ga[0], ga[1], ga[2]);
+            if (check_bounds && !(fa >= b.lo && fa <= b.hi)) out[0]++;
+            float X[1] = {x}, Y[1] = {y}, Z[1] = {z}, fm[1];
+            eval_values<1>(prog, sdf, MaskLive{m.data()}, X, Y, Z, fm);
+            float X2[1] = {x}, Y2[1] = {y}, Z2[1] = {z}, fl[1];
+            eval_values_list<1>(prog, sdf, vlist.data(), (int)vlist.size(), X2, Y2, Z2, fl);
+            if (memcmp(&fa, fm, 4) != 0 || memcmp(&fa, fl, 4) != 0) out[1]++;
+            float fb, gb[3], fc, gc[3];
+            eval_value_gradient(prog, sdf, MaskLive{m.data()}, x, y, z, fb, gb[0], gb[1], gb[2]);
+            eval_value_gradient_list(prog, sdf, glist.data(), (int)glist.size(), x, y, z, fc, gc[0], gc[1], gc[2]);
+            if (memcmp(&fa, &fb, 4) != 0 || memcmp(ga, gb, 12) != 0 || memcmp(&fa, &fc, 4) != 0 || memcmp(ga, gc, 12) != 0) out[2]++;
+        }
+    };
+    for (int i = 0; i < n_boxes; i++) {
+        const float* bx = boxes + i * 6;
+        const Ival b = program_bounds<true, false>(p.bounds.data(), bx[0], bx[1], bx[2], bx[3], bx[4], bx[5], decisions, NoMask());
+        write_live_mask(spec, decisions, mask.data());
+        for (int k = 0; k < p.num_nodes; k++) out[4] += (mask[k >> 5] >> (k & 31)) & 1;
+        if (b.hi < 0.0f || b.lo > 0.0f) out[5]++;
+        check_points(bx, b, mask, true);
+        // second level: a sub-box (one octant, chosen at random) bounded under the first level's mask
+        float sub[6];
+        for (int d = 0; d < 3; d++) { sub[3 + d] = 0.5f * bx[3 + d]; sub[d] = bx[d] + (uni() < 0.5f ? -0.5f : 0.5f) * bx[3 + d]; }
+        const Ival b2 = program_bounds<true, true>(p.bounds.data(), sub[0], sub[1], sub[2], sub[3], sub[4], sub[5], decisions, WordMask{mask.data()});
+        write_live_mask(spec, decisions, mask2.data());
+        for (int w = 0; w < spec.mask_words; w++) if (mask2[w] & ~mask[w]) out[3]++;
+        check_points(sub, b2, mask2, true);
+    }
+    return p.num_nodes;
+}

@@ -148,6 +148,17 @@ class Emu:
                                          fm.ctypes.data_as(ctypes.c_void_p), live.ctypes.data_as(ctypes.c_void_p))
         return ft, fm, live, nodes
 
+    def bounds_check(self, shape_json, boxes, samples=16, seed=1):
+        """Interval bounds / liveness masks of csg_bounds.cuh against the exact interpreters on random points of every box
+        (centre xyz, half extents xyz).  Returns (node count or -count when the tree cannot be specialised, dict of counters)."""
+        b = np.ascontiguousarray(boxes, dtype=np.float32).reshape(-1, 6)
+        out = np.zeros(6, dtype=np.int64)
+        self.lib.emu_bounds_check.restype = ctypes.c_int
+        nodes = self.lib.emu_bounds_check(shape_json.encode(), b.ctypes.data_as(ctypes.c_void_p), b.shape[0], int(samples), int(seed),
+                                          out.ctypes.data_as(ctypes.c_void_p))
+        keys = ["bounds_violations", "value_mismatches", "gradient_mismatches", "looser_second_level", "live_nodes", "boxes_decided"]
+        return nodes, dict(zip(keys, (int(v) for v in out)))
+
     def affine_inverse(self, m12):
         a = np.ascontiguousarray(m12, dtype=np.float32)
         out = np.zeros(12, dtype=np.float32)

@@ -76,3 +76,29 @@ def test_random_trees_every_interpreter_bit_exact(emu, oracle, seed):
     for got in (f1, f4, ft, fm):
         assert np.array_equal(got.view(np.uint32), fo.view(np.uint32))
     assert np.array_equal(g.view(np.uint32), go.view(np.uint32))
+
+
+def _boxes_near_surface(emu, sj, rng, n, half_extent):
+    """Box centres where |f| is small (the tiles K1 cannot prove inside or outside), half extents around `half_extent`."""
+    pts = rng.uniform(-1.1, 1.1, (30 * n, 3)).astype(np.float32)
+    f, _, _ = emu.eval(sj, pts)
+    order = np.argsort(np.abs(f))[:n]
+    h = (half_extent * rng.uniform(0.5, 1.5, (n, 3))).astype(np.float32)
+    return np.concatenate([pts[order], h], axis=1)
+
+
+@pytest.mark.parametrize("name", SHAPES + ["random_%d" % s for s in range(8)])
+def test_interval_bounds_and_tile_masks_are_sound(emu, name):
+    """K1's pruning and specialisation (csg_bounds.cuh, compiled for the host): over boxes of tile and supertile size near the
+    surface, the interval bounds contain the exact values at random points of the box, the liveness mask made from the
+    decisions changes no bit of any interpreter's value or gradient there (mask walk, value list, gradient list), and a
+    sub-box bounded under that mask (K1's second level) never gets a looser mask."""
+    sj = shapes.random_tree(int(name.split("_")[1])) if name.startswith("random_") else getattr(shapes, name)()
+    rng = np.random.default_rng(17)
+    for half_extent in (0.012, 0.05):
+        nodes, st = emu.bounds_check(sj, _boxes_near_surface(emu, sj, rng, 300, half_extent), samples=10, seed=3)
+        if nodes < 0:
+            pytest.skip("tree too large to specialise")
+        assert st["bounds_violations"] == 0 and st["value_mismatches"] == 0 and st["gradient_mismatches"] == 0, st
+        assert st["looser_second_level"] == 0, st
+        assert st["live_nodes"] >= 300          # the root is always live
