@@ -129,3 +129,35 @@ def test_make_a_cube_fixture_ob02(oracle):
     st = oracle.stats()
     assert st["projection_by_type"][0] == 12 and st["projection_failed"] == 0
     assert np.isfinite(v).all() and (np.linalg.norm(v, axis=1) > 0.5).all()
+
+
+# sha256 of the reference's two tables (marching_cubes.hpp:1207-1240, :1246-1503), "edge values,...;triangle values,..."
+MC_TABLES_SHA256 = "ca355f6a8bfd54741af8032c0fadb6dff3c0cf22b0ffd5fc349ddc21de657ed9"
+
+
+def _table(src, name):
+    import re
+    body = re.search(name + r"\[[^\]]*\]\s*=\s*\{(.*?)\};", src, re.S).group(1)
+    body = re.sub(r"//[^\n]*", "", body)
+    return [int(t, 0) for t in re.findall(r"-?0x[0-9a-fA-F]+|-?\d+", body)]
+
+
+def test_mc_tables_are_the_references():
+    """The two marching-cubes tables (product's mc_tables.h and the oracle's omc_tables.h) are verbatim transcriptions of
+    the reference's `mc_edge_lookup_table` and `mc_triangles_table` (marching_cubes.hpp:1207-1240, :1246-1503): compared with
+    the reference's source where it is present (the build container), and everywhere with the digest of that source's tables
+    recorded from it."""
+    import hashlib
+    root = os.path.dirname(HERE)
+    prod = open(os.path.join(root, "implisolid_b200", "csrc", "mc_tables.h")).read()
+    orac = open(os.path.join(root, "oracle", "omc_tables.h")).read()
+    edge, tri = _table(prod, "ISD_MC_EDGE_MASK"), _table(prod, "ISD_MC_TRI")
+    assert len(edge) == 256 and len(tri) == 4096
+    assert _table(orac, "OMC_EDGE_MASK") == edge and _table(orac, "OMC_TRI") == tri
+    digest = hashlib.sha256((",".join(map(str, edge)) + ";" + ",".join(map(str, tri))).encode()).hexdigest()
+    ref = "/root/reference/js_iteration_2/marching_cubes.hpp"
+    if os.path.exists(ref):
+        src = open(ref).read()
+        assert _table(src, "mc_edge_lookup_table") == edge
+        assert _table(src, "mc_triangles_table") == tri
+    assert digest == MC_TABLES_SHA256, digest
