@@ -80,3 +80,13 @@ def test_unknown_shape_aborts():
     r = _run("from tests.oracle_lib import load_oracle; L = load_oracle()\nfrom implisolid_b200 import shapes as s\n"
              "L.build_geometry('{\"type\":\"teapot\",\"matrix\":[1,0,0,0,0,1,0,0,0,0,1,0]}', s.mc_settings(8, 0.5))")
     assert r.returncode != 0 and "Invalid object" in r.stderr
+
+
+def test_header_is_plain_c_and_cpp():
+    """include/implisolid_b200.h is the drop-in boundary: it must compile on its own as C99 and as C++11 (no torch or CUDA
+    types in any signature)."""
+    import subprocess
+    hdr = os.path.join(ROOT, "include", "implisolid_b200.h")
+    subprocess.run(["gcc", "-fsyntax-only", "-x", "c", "-std=c99", "-Wall", "-Werror", hdr], check=True)
+    subprocess.run(["g++", "-fsyntax-only", "-x", "c++", "-std=c++11", "-Wall", "-Werror", hdr], check=True)
+    assert "torch" not in open(hdr).read()
