@@ -89,4 +89,6 @@ def test_header_is_plain_c_and_cpp():
     hdr = os.path.join(ROOT, "include", "implisolid_b200.h")
     subprocess.run(["gcc", "-fsyntax-only", "-x", "c", "-std=c99", "-Wall", "-Werror", hdr], check=True)
     subprocess.run(["g++", "-fsyntax-only", "-x", "c++", "-std=c++11", "-Wall", "-Werror", hdr], check=True)
-    assert "torch" not in open(hdr).read()
+    import re
+    code = re.sub(r"/\*.*?\*/", "", open(hdr).read(), flags=re.S)        # comments may mention the launcher's torch.distributed
+    assert "torch" not in code and "#include <cuda" not in code
