@@ -177,12 +177,14 @@ def n1_medley():
     return json.dumps({"type": "Difference", "matrix": EYE, "children": [u, hp]})
 
 
-def random_tree(seed, depth=4):
+def random_tree(seed, depth=4, all_prims=False):
     """A random CSG tree for property tests: random shape (chains and bushy parts mixed), every operator, every analytic
     primitive except the double-precision ones (torus / heart / mushroom agree with glibc's pow only on most points),
     n-ary unions, random similarity-ish transforms on every node."""
     rng = np.random.default_rng(seed)
     kinds = ["cube", "cylinder", "ellipsoid", "icone", "meta_balls", "tetrahedron", "half_plane", "top_bottom_lid"]
+    if all_prims:      # for checks that do not compare with glibc's pow (interval bounds, masks)
+        kinds += ["itorus", "iheart", "implicit_double_mushroom"]
 
     def aff(scale_lo, scale_hi, shift):
         R = _rot_axis(rng.normal(size=3), rng.uniform(-40, 40)) * rng.uniform(scale_lo, scale_hi)

@@ -87,13 +87,17 @@ def _boxes_near_surface(emu, sj, rng, n, half_extent):
     return np.concatenate([pts[order], h], axis=1)
 
 
-@pytest.mark.parametrize("name", SHAPES + ["random_%d" % s for s in range(8)])
+@pytest.mark.parametrize("name", SHAPES + ["random_%d" % s for s in range(8)] + ["randomall_%d" % s for s in (322, 335, 339)])
 def test_interval_bounds_and_tile_masks_are_sound(emu, name):
     """K1's pruning and specialisation (csg_bounds.cuh, compiled for the host): over boxes of tile and supertile size near the
     surface, the interval bounds contain the exact values at random points of the box, the liveness mask made from the
     decisions changes no bit of any interpreter's value or gradient there (mask walk, value list, gradient list), and a
     sub-box bounded under that mask (K1's second level) never gets a looser mask."""
-    sj = shapes.random_tree(int(name.split("_")[1])) if name.startswith("random_") else getattr(shapes, name)()
+    if name.startswith("randomall_"):      # every primitive kind, torus / heart / mushroom included; up to 187 nodes
+        seed = int(name.split("_")[1])
+        sj = shapes.random_tree(seed, depth=3 + seed % 4, all_prims=True)
+    else:
+        sj = shapes.random_tree(int(name.split("_")[1])) if name.startswith("random_") else getattr(shapes, name)()
     rng = np.random.default_rng(17)
     for half_extent in (0.012, 0.05):
         nodes, st = emu.bounds_check(sj, _boxes_near_surface(emu, sj, rng, 300, half_extent), samples=10, seed=3)
