@@ -92,3 +92,15 @@ def test_header_is_plain_c_and_cpp():
     import re
     code = re.sub(r"/\*.*?\*/", "", open(hdr).read(), flags=re.S)        # comments may mention the launcher's torch.distributed
     assert "torch" not in code and "#include <cuda" not in code
+
+
+def test_example_caller_compiles_and_links(tmp_path):
+    """examples/polygonize_to_obj.c — plain C99 against include/ and the built library (link only: running needs a GPU)."""
+    import subprocess
+    from implisolid_b200 import build_library
+    lib_dir = os.path.dirname(build_library())
+    out = str(tmp_path / "polygonize_to_obj")
+    subprocess.run(["gcc", "-std=c99", "-O2", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"),
+                    os.path.join(ROOT, "examples", "polygonize_to_obj.c"), "-L" + lib_dir, "-limplisolid_b200",
+                    "-Wl,-rpath," + lib_dir, "-o", out], check=True)
+    assert os.path.exists(out)
