@@ -502,7 +502,7 @@ private:
         p.bounds.push_back((uint32_t)n.op | (id_of(n) << OP_ID_SHIFT));
     }
 
-    void emit_node(const ShapeNode& n, bool preserve, Program& p) {
+    void emit_node(const ShapeNode& n, bool preserve, Program& p, bool parent_identity = false) {
         p.num_nodes++;
         if (!n.is_csg()) {
             put_itab(p, (uint32_t)(p.words.size() / 4), id_of(n), 0u, 0u);
@@ -540,24 +540,41 @@ private:
             push_value(p);
             return;
         }
-        if (preserve && ++fs_ > p.frame_depth) p.frame_depth = fs_;
+        // A node asked to preserve `cur` normally saves it on the frame stack.  A node whose own inverse is the identity and
+        // whose parent's is too (the inner nodes of the factory's n-ary Union fold, object_factory.hpp:537-580) leaves cur as
+        // it found it: I*(I*x) == I*x bit for bit (the product's final "+ 0" has already turned every -0 into +0), so it
+        // needs no frame as long as BOTH its children preserve cur.
+        const bool soft = preserve && parent_identity && is_identity(n.minv);
+        const bool save = preserve && !soft;
+        if (save && ++fs_ > p.frame_depth) p.frame_depth = fs_;
         put_itab(p, (uint32_t)(p.words.size() / 4), id_of(n), 0u, 0u);
-        const size_t skip_at = put_header(p, (uint32_t)OP_XFORM | (preserve ? (uint32_t)OP_FLAG_SAVE : 0u) | (id_of(n) << OP_ID_SHIFT), 0u);
+        const size_t skip_at = put_header(p, (uint32_t)OP_XFORM | (save ? (uint32_t)OP_FLAG_SAVE : 0u) | (id_of(n) << OP_ID_SHIFT), 0u);
         put_matrix(p, n.minv);
         p.flops_per_point += 18 + 1;
-        // deeper child last; ties keep the reference order
-        const bool b_first = n.b->depth() < n.a->depth();
+        // Deeper child last (no frame to keep while descending; ties keep the reference order) — except down a run of
+        // identity nodes, where the deeper child goes FIRST: it preserves cur for free (soft, above), so a Union of N children
+        // runs in two value-stack slots and one frame instead of N slots.
+        const bool identity_run = is_identity(n.minv) && n.a->is_csg() && is_identity(n.a->minv) && n.a->depth() >= n.b->depth();
+        const bool b_first = !identity_run && n.b->depth() < n.a->depth();
         const ShapeNode& first = b_first ? *n.b : *n.a;
         const ShapeNode& second = b_first ? *n.a : *n.b;
-        emit_node(first, /*preserve=*/first.is_csg(), p);
-        emit_node(second, /*preserve=*/false, p);
-        put_itab(p, (uint32_t)(p.words.size() / 4) | IT_CLOSING | (preserve ? IT_RESTORE : 0u) | (b_first ? IT_SWAPPED : 0u) |
+        const bool here_identity = is_identity(n.minv);
+        emit_node(first, /*preserve=*/first.is_csg(), p, here_identity);
+        emit_node(second, /*preserve=*/soft && second.is_csg(), p, here_identity);
+        put_itab(p, (uint32_t)(p.words.size() / 4) | IT_CLOSING | (save ? IT_RESTORE : 0u) | (b_first ? IT_SWAPPED : 0u) |
                         (((uint32_t)n.op - (uint32_t)OP_UNION) << IT_OP_SHIFT), id_of(n), id_of(*n.a), id_of(*n.b));
-        put_header(p, (uint32_t)n.op | (b_first ? (uint32_t)OP_FLAG_SWAPPED : 0u) | (preserve ? (uint32_t)OP_FLAG_RESTORE : 0u), 0u);
+        put_header(p, (uint32_t)n.op | (b_first ? (uint32_t)OP_FLAG_SWAPPED : 0u) | (save ? (uint32_t)OP_FLAG_RESTORE : 0u), 0u);
         put_matrix(p, n.minv);
         vs_ -= 1;   // pops two, pushes one
-        if (preserve) --fs_;
+        if (save) --fs_;
         p.words[skip_at] = (uint32_t)p.words.size();
+    }
+    static bool is_identity(const float minv[12]) {      // bitwise: ones on the diagonal, +0 elsewhere
+        for (int i = 0; i < 12; ++i) {
+            uint32_t w; memcpy(&w, &minv[i], 4);
+            if (w != ((i % 5 == 0) ? 0x3f800000u : 0u)) return false;
+        }
+        return true;
     }
 };
 

@@ -36,12 +36,26 @@ struct MarchingCubes {
     std::vector<uint8_t> case_codes;           // per visited cube, scan order (z,y,x in [1,S-2))
     std::map<int64_t, int> e3map;
 
-    MarchingCubes(int R, const bounding_box& b) : S(R + skip_count_l + skip_count_h), box(b) {
+    // Window of cube layers [cz0, cz1) (ours, for bounded samples of a large grid and for slab parity checks): only node
+    // planes [cz0, cz1] are stored and evaluated, cube layers outside the window are not visited; everything else — node
+    // coordinates, seal, scan order inside the window, edge keys (global node numbers) — is what the whole grid gives.
+    // The default window is the whole grid: the reference's behaviour.
+    int cz0, cz1;                 // cube layers visited: [cz0, cz1) within [1, S-2)
+    int zb, nzp;                  // node planes stored: [zb, zb + nzp)
+    bool keep_cases = true;
+
+    MarchingCubes(int R, const bounding_box& b, int layer0 = -1, int layer1 = -1) : S(R + skip_count_l + skip_count_h), box(b) {
         widthx = (b.xmax - b.xmin) / (REAL)R;
         widthy = (b.ymax - b.ymin) / (REAL)R;
         widthz = (b.zmax - b.zmin) / (REAL)R;
-        field.assign((size_t)S * S * S, 0.0f);
+        if (layer0 < 0) { cz0 = 1; cz1 = S - 2; zb = 0; nzp = S; }
+        else {
+            cz0 = std::max(1, layer0); cz1 = std::min(S - 2, layer1);
+            zb = cz0; nzp = cz1 - cz0 + 1;
+        }
+        field.assign((size_t)S * S * nzp, 0.0f);
     }
+    int64_t zoff() const { return (int64_t)zb * (int64_t)zstride(); }
     size_t ystride() const { return (size_t)S; }
     size_t zstride() const { return (size_t)S * S; }
 
@@ -51,8 +65,11 @@ struct MarchingCubes {
         REAL xfactor = wx / (REAL)e, yfactor = wy / (REAL)e, zfactor = wz / (REAL)e;
         const size_t plane = zstride();
         int planes_per_chunk = (int)std::max<size_t>(1, (size_t)2000000 / plane);
-        for (int z0 = 0; z0 < S; z0 += planes_per_chunk) {
-            int z1 = std::min(S, z0 + planes_per_chunk);
+        const int zend = zb + nzp, nchunks = (nzp + planes_per_chunk - 1) / planes_per_chunk;
+        // chunks are independent (pointwise evaluation, disjoint slices of the field): threads() > 1 runs them concurrently
+        parallel_for(nchunks, [&](long ci) {
+            int z0 = zb + (int)ci * planes_per_chunk;
+            int z1 = std::min(zend, z0 + planes_per_chunk);
             vects grid((size_t)(z1 - z0) * plane);
             for (int z = z0; z < z1; z++)
                 for (int y = 0; y < S; y++)
@@ -64,17 +81,17 @@ struct MarchingCubes {
                     }
             scalars f(grid.n());
             object.eval_implicit(grid, &f);
-            for (size_t i = 0; i < f.size(); i++) field[(size_t)z0 * plane + i] += f[i];
-        }
+            for (size_t i = 0; i < f.size(); i++) field[(size_t)(z0 - zb) * plane + i] += f[i];
+        });
     }
 
     void seal_exterior(const REAL exterior_value) {
         for (int x = 0; x < S; x++)
             for (int y = 0; y < S; y++)
-                for (int z = 0; z < S; z++) {
+                for (int z = zb; z < zb + nzp; z++) {
                     bool border0 = (x == 0) || (x == S - 1) || (y == 0) || (y == S - 1) || (z == 0) || (z == S - 1);
                     bool border = (x == 1) || (x == S - 2) || (y == 1) || (y == S - 2) || (z == 1) || (z == S - 2);
-                    if (border || border0) field[zstride() * z + x + y * ystride()] = exterior_value;
+                    if (border || border0) field[zstride() * (size_t)(z - zb) + x + y * ystride()] = exterior_value;
                 }
     }
 
@@ -96,8 +113,9 @@ struct MarchingCubes {
         const int64_t ys = (int64_t)ystride(), zs = (int64_t)zstride();
         int64_t qx = q + 1, qy = q + ys, qz = q + zs, qxy = qx + ys, qxz = qx + zs, qyz = q + ys + zs, qxyz = qx + ys + zs;
         unsigned cubeindex = 0;
-        REAL field0 = field[q], field1 = field[qx], field2 = field[qy], field3 = field[qxy], field4 = field[qz],
-             field5 = field[qxz], field6 = field[qyz], field7 = field[qxyz];
+        const REAL* fw = field.data() - zoff();      // q is the global node number (edge keys); the window starts at plane zb
+        REAL field0 = fw[q], field1 = fw[qx], field2 = fw[qy], field3 = fw[qxy], field4 = fw[qz],
+             field5 = fw[qxz], field6 = fw[qyz], field7 = fw[qxyz];
         if (field0 < isol) cubeindex |= 1;
         if (field1 < isol) cubeindex |= 2;
         if (field2 < isol) cubeindex |= 8;
@@ -106,7 +124,7 @@ struct MarchingCubes {
         if (field5 < isol) cubeindex |= 32;
         if (field6 < isol) cubeindex |= 128;
         if (field7 < isol) cubeindex |= 64;
-        case_codes.push_back((uint8_t)cubeindex);
+        if (keep_cases) case_codes.push_back((uint8_t)cubeindex);
         int bits = OMC_EDGE_MASK[cubeindex];
         if (bits == 0) return 0;
         REAL fx2 = fx + widthx, fy2 = fy + widthy, fz2 = fz + widthz;
@@ -155,8 +173,8 @@ struct MarchingCubes {
         const REAL yi0 = (+box.ymin) / widthy - skip_count_l;
         const REAL zi0 = (+box.zmin) / widthz - skip_count_l;
         const int end = S - 2;
-        case_codes.reserve((size_t)(end - 1) * (end - 1) * (end - 1));
-        for (int zi = 1; zi < end; zi++) {
+        if (keep_cases) case_codes.reserve((size_t)(cz1 - cz0) * (end - 1) * (end - 1));
+        for (int zi = cz0; zi < cz1; zi++) {
             int64_t z_offset = (int64_t)zstride() * zi;
             REAL fz = (zi + zi0) * widthz;
             for (int yi = 1; yi < end; yi++) {

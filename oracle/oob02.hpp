@@ -198,6 +198,23 @@ inline REAL compute_average_edge_length(const std::vector<int>& faces, const vec
     }
     return edge_length / (3. * nfaces);
 }
+// The product's default (a documented deviation from the serial float sum above, which stagnates beyond ~1e7
+// terms and depends on the order of summation, so it cannot be sharded): every face's three lengths are added in double,
+// rounded to a multiple of 2^-32 and accumulated in a 64-bit integer; the mean is formed in double and rounded once.
+inline REAL compute_average_edge_length_fixed_point(const std::vector<int>& faces, const vects& verts, unsigned long long* sum_out = nullptr) {
+    int nfaces = (int)(faces.size() / 3);
+    unsigned long long acc = 0ull;
+    for (int j = 0; j < nfaces; j++) {
+        int f0 = faces[j * 3], f1 = faces[j * 3 + 1], f2 = faces[j * 3 + 2];
+        REAL l0 = norm_2(verts[f0][0] - verts[f1][0], verts[f0][1] - verts[f1][1], verts[f0][2] - verts[f1][2]);
+        REAL l1 = norm_2(verts[f0][0] - verts[f2][0], verts[f0][1] - verts[f2][1], verts[f0][2] - verts[f2][2]);
+        REAL l2 = norm_2(verts[f2][0] - verts[f1][0], verts[f2][1] - verts[f1][1], verts[f2][2] - verts[f1][2]);
+        double sum3 = (double)l0 + (double)l1 + (double)l2;
+        if (sum3 < 2147483648.0) acc += (unsigned long long)std::llrint(sum3 * 4294967296.0);      // NaN / huge lengths add nothing
+    }
+    if (sum_out) *sum_out = acc;
+    return (REAL)(((double)acc * (1.0 / 4294967296.0)) / (3. * nfaces));
+}
 
 inline std::vector<REAL> make_alpha_list(REAL initial_step_size, REAL min_step_size, REAL max_dist, int max_iter) {
     REAL unit_of_length = max_dist;
@@ -532,11 +549,11 @@ struct ProjectionDebug {           // what the reference keeps in point_set_set 
 };
 
 inline void centroids_projection(const implicit_function& object, std::vector<REAL>& result_verts, const std::vector<int>& faces,
-                                 bool enable_qem, Stats* st, ProjectionDebug* dbg = nullptr) {
+                                 bool enable_qem, Stats* st, ProjectionDebug* dbg = nullptr, bool serial_float_edge_sum = true) {
     int nv = (int)(result_verts.size() / 3), nf = (int)(faces.size() / 3);
     vects verts(nv);
     verts.d = result_verts;
-    REAL average_edge = compute_average_edge_length(faces, verts);
+    REAL average_edge = serial_float_edge_sum ? compute_average_edge_length(faces, verts) : compute_average_edge_length_fixed_point(faces, verts);
     vects centroids(nf);
     compute_centroids(faces, verts, centroids);
     if (dbg) { dbg->centroids_before = centroids; dbg->average_edge = average_edge; }

@@ -8,6 +8,7 @@
 // :446-552 (build_geometry, getters, finish_geometry), :699-911 (direct evaluation service),
 // polygoniser_settings.hpp:70-84,101-141,147-305 (settings) and polygonizer_algorithm_ob02.hpp:74-176.
 // Extra oracle_* entry points expose intermediates (field, case codes, stats) to the parity tests.
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -32,6 +33,8 @@ struct mc_settings {
     struct { bool enabled; } qem, projection, subdiv;
     struct { REAL post_subdiv_noise; } debug;
     int cube_mode;     // ours: "gpu.cube_mode" 0 analytic (default) / 1 HEAD SDF grid
+    int exact_reduce;  // ours: "gpu.exact_reduce" 1 = the reference's serial float sum of the edge lengths (centroids_projection.cpp:70-82);
+                       // 0 (default, like the product) = the product's 64-bit fixed-point sum, a documented deviation
 };
 
 bool read_bool_from_json(const ojson::Node& d, const std::string& field, bool dflt, bool* needs_abort,
@@ -86,6 +89,7 @@ mc_settings parse_mc_properties_json(const char* json) {
     s.overall_repeats = d.get_int("overall_repeats", 1);
     s.ignore_root_matrix = d.get_bool("ignore_root_matrix", false);
     s.cube_mode = d.get_int("gpu.cube_mode", 0);
+    s.exact_reduce = d.get_int("gpu.exact_reduce", 0);
     if (s.qem.enabled && !s.projection.enabled) {
         std::clog << "Invalid settings: QEM will not be applied if centroid projection is disabled" << std::endl;
         needs_abort = true;
@@ -133,7 +137,11 @@ void send_mesh_back_to_client() {
                (int)(_state.mc_result_faces.size() / 3), g_call_specs[0], g_call_specs[1], g_call_specs[2], g_progress_user);
 }
 
-void grand_algorithm(const char* shape_json, const mc_settings& s) {
+double g_stage_s[4] = {0, 0, 0, 0};      // eval, marching cubes, resampling, projection+qem (seconds, last build)
+double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+// layer0 < 0: the whole grid (the reference).  Otherwise cube layers [layer0, layer1) only (MarchingCubes' window).
+void grand_algorithm(const char* shape_json, const mc_settings& s, int layer0 = -1, int layer1 = -1, bool keep_debug = true) {
     if (_state.active) {
         std::clog << "Error: There are non-deallocated geometry resources. Call finit_geometry() first. Not doing anything.";
         std::clog << "build_geometry() called in a bad state.";
@@ -141,11 +149,20 @@ void grand_algorithm(const char* shape_json, const mc_settings& s) {
     }
     Shape shape;
     ojson::Node doc = ojson::parse(shape_json);
-    const implicit_function* object = object_factory(shape, doc, s.ignore_root_matrix, make_env(s.cube_mode));
+    const implicit_function* root = object_factory(shape, doc, s.ignore_root_matrix, make_env(s.cube_mode));
+    chunked_function chunked(root);      // threads() == 1: passes every call straight through
+    const implicit_function* object = &chunked;
     g_stats = Stats();
+    for (double& t : g_stage_s) t = 0;
     {   // polygonize_step_0 / mc_start
-        MarchingCubes mc(s.resolution, s.box);
-        mc.produce_mesh(*object);
+        MarchingCubes mc(s.resolution, s.box, layer0, layer1);
+        mc.keep_cases = keep_debug;
+        double t0 = now_s();
+        mc.eval_shape(*root);            // chunks of z-planes, concurrent when threads() > 1
+        mc.seal_exterior(-10000000.0);
+        double t1 = now_s();
+        mc.render_geometry();
+        g_stage_s[0] = t1 - t0; g_stage_s[1] = now_s() - t1;
         _state.mc_result_verts = std::move(mc.result_verts);
         _state.mc_result_faces = std::move(mc.result_faces);
         g_field = std::move(mc.field);
@@ -155,11 +172,16 @@ void grand_algorithm(const char* shape_json, const mc_settings& s) {
     }
     send_mesh_back_to_client();                                                                  // mcc2.cpp:351
     for (int overall_iter = 0; overall_iter < s.overall_repeats; ++overall_iter) {
+        double t0 = now_s();
         for (int i = 0; i < s.vresampl.iters; i++)
             vertex_resampling(*object, s.vresampl.c, _state.mc_result_verts, _state.mc_result_faces);   // polygonize_step_1
+        double t1 = now_s();
+        g_stage_s[2] += t1 - t0;
         send_mesh_back_to_client();                                                              // mcc2.cpp:372
         if (s.projection.enabled) {
-            centroids_projection(*object, _state.mc_result_verts, _state.mc_result_faces, s.qem.enabled, &g_stats, &g_proj);
+            centroids_projection(*object, _state.mc_result_verts, _state.mc_result_faces, s.qem.enabled, &g_stats, &g_proj,
+                                 s.exact_reduce != 0);
+            g_stage_s[3] += now_s() - t1;
             send_mesh_back_to_client();                                                          // mcc2.cpp:390
         }
         const bool is_last = overall_iter == s.overall_repeats - 1;
@@ -320,6 +342,18 @@ int get_gradients_size() {
 void* get_pointset_ptr(char*) { return nullptr; }
 int get_pointset_size(char*) { return 0; }
 void about() { std::cout << "implisolid oracle (CPU restatement; test infrastructure)" << std::endl; }
+
+// ---- oracle-only: host threads, bounded samples of a large grid ---------------------------------
+void oracle_set_threads(int n) { threads() = n > 1 ? n : 1; }
+int oracle_get_threads() { return threads(); }
+// build_geometry restricted to cube layers [layer0, layer1) of the grid the settings describe: field evaluation of the node
+// planes those layers touch, marching cubes over them, then the OB02 steps on the mesh that results (its open rims included).
+// For timing a bounded sample of a workload too large to run whole, and for checking a slab of a large GPU mesh.
+void oracle_build_layers(const char* shape_parameters_json, const char* mc_parameters_json, int layer0, int layer1) {
+    mc_settings s = parse_mc_properties_json(mc_parameters_json);
+    grand_algorithm(shape_parameters_json, s, layer0, layer1, false);
+}
+void oracle_stage_seconds(double* out4) { for (int i = 0; i < 4; i++) out4[i] = g_stage_s[i]; }
 
 // ---- oracle-only introspection ----------------------------------------------------------------
 int oracle_grid_size() { return g_S; }

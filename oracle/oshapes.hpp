@@ -16,11 +16,13 @@
 //   object_factory           object_factory.hpp:21-30,56-173,537-673,741-758
 #pragma once
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <memory>
 #include <string>
+#include <thread>
 #include <vector>
 #include "ojson.hpp"
 
@@ -743,5 +745,59 @@ inline const implicit_function* object_factory(Shape& S, const ojson::Node& node
     fprintf(stderr, "Invalid object you asked for: \"%s\"\n", name.c_str());              // :731-733
     abort();
 }
+
+// ---- host threads (bench baselines and large parity cases only) ---------------------------------------------------
+// The reference is single-threaded.  Its whole-array passes are pointwise (point i of the output depends on point i of
+// the input only), so splitting an array into contiguous chunks and evaluating the chunks on different threads gives
+// the same bits as the one call the reference makes.  threads() == 1 (the default) makes the reference's single call.
+inline int& threads() { static int t = 1; return t; }
+
+// fn(k) for k in [0, n), work handed out dynamically to threads() std::threads (no OpenMP runtime needed)
+template <class F>
+inline void parallel_for(long n, const F& fn) {
+    const int t = (int)std::min<long>(threads(), n);
+    if (t <= 1) { for (long k = 0; k < n; k++) fn(k); return; }
+    std::atomic<long> next(0);
+    auto worker = [&]() { for (long k; (k = next.fetch_add(1)) < n;) fn(k); };
+    std::vector<std::thread> pool;
+    for (int i = 1; i < t; i++) pool.emplace_back(worker);
+    worker();
+    for (std::thread& th : pool) th.join();
+}
+
+struct chunked_function : implicit_function {
+    const implicit_function* inner;
+    explicit chunked_function(const implicit_function* f) : inner(f) {}
+    static size_t chunk_of(size_t n) {
+        size_t c = (n + (size_t)threads() * 4 - 1) / ((size_t)threads() * 4);
+        return c < 4096 ? 4096 : c;
+    }
+    void eval_implicit(const vects& x, scalars* f) const override {
+        const size_t n = x.n();
+        if (threads() <= 1 || n < 8192) { inner->eval_implicit(x, f); return; }
+        const size_t c = chunk_of(n), nchunks = (n + c - 1) / c;
+        parallel_for((long)nchunks, [&](long k) {
+            const size_t b = (size_t)k * c, e = std::min(n, b + c);
+            vects xs(e - b);
+            std::copy(x.d.begin() + b * 3, x.d.begin() + e * 3, xs.d.begin());
+            scalars fs(e - b);
+            inner->eval_implicit(xs, &fs);
+            std::copy(fs.begin(), fs.end(), f->begin() + b);
+        });
+    }
+    void eval_gradient(const vects& x, vects* g) const override {
+        const size_t n = x.n();
+        if (threads() <= 1 || n < 8192) { inner->eval_gradient(x, g); return; }
+        const size_t c = chunk_of(n), nchunks = (n + c - 1) / c;
+        parallel_for((long)nchunks, [&](long k) {
+            const size_t b = (size_t)k * c, e = std::min(n, b + c);
+            vects xs(e - b);
+            std::copy(x.d.begin() + b * 3, x.d.begin() + e * 3, xs.d.begin());
+            vects gs(e - b);
+            inner->eval_gradient(xs, &gs);
+            std::copy(gs.d.begin(), gs.d.end(), g->d.begin() + b * 3);
+        });
+    }
+};
 
 }  // namespace oracle

@@ -23,8 +23,14 @@ CASES = {
     "cone_r28": (shapes.simple_cone, 28, 0.5, {}),
     "c3_metaballs_r32": (shapes.c3_metaballs, 32, 1.2, {}),
     "c4_chain_r40": (shapes.c4_deep_chain, 40, 1.0, {}),
-    "c1_sphere_r28_ob02": (shapes.c1_sphere, 28, 0.55, dict(iters=1, c=1.0, projection=1, qem=1)),
-    "c2_cube_cyl_r40_ob02": (shapes.c2_cube_minus_cylinder, 40, 0.8, dict(iters=1, c=1.0, projection=1, qem=1)),
+    # the reference's serial float sum of the edge lengths (exact_reduce 1) ...
+    "c1_sphere_r28_ob02": (shapes.c1_sphere, 28, 0.55, dict(iters=1, c=1.0, projection=1, qem=1, exact_reduce=1)),
+    "c2_cube_cyl_r40_ob02": (shapes.c2_cube_minus_cylinder, 40, 0.8, dict(iters=1, c=1.0, projection=1, qem=1, exact_reduce=1)),
+    # ... and the product's default 64-bit fixed-point sum
+    "c1_sphere_r28_ob02_fixed_point_sum": (shapes.c1_sphere, 28, 0.55, dict(iters=1, c=1.0, projection=1, qem=1)),
+    "c2_cube_cyl_r40_ob02_fixed_point_sum": (shapes.c2_cube_minus_cylinder, 40, 0.8, dict(iters=1, c=1.0, projection=1, qem=1)),
+    "c4_chain_r40_ob02_fixed_point_sum": (shapes.c4_deep_chain, 40, 1.0, dict(iters=1, c=1.0, projection=1, qem=1)),
+    "heart_r40": (shapes.n1_heart, 40, 1.0, {}),
 }
 
 

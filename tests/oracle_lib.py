@@ -29,6 +29,26 @@ class Oracle(GeometryLibrary):
         L.oracle_centroid_normals_ptr.restype = ctypes.POINTER(ctypes.c_float)
         L.oracle_average_edge.restype = ctypes.c_float
         L.oracle_alpha_list.restype = ctypes.c_int
+        L.oracle_get_threads.restype = ctypes.c_int
+
+    def set_threads(self, n):
+        """Host threads for the pointwise whole-array passes (1 = the reference's single-threaded calls; same bits either way)."""
+        self.lib.oracle_set_threads(int(n))
+
+    def build_layers(self, shape_json, mc_json, layer0, layer1):
+        """build_geometry restricted to cube layers [layer0, layer1) of the grid (MarchingCubes' window, oracle/omc.hpp)."""
+        self.lib.oracle_build_layers(shape_json.encode(), mc_json.encode(), int(layer0), int(layer1))
+
+    def polygonize_layers(self, shape_json, mc_json, layer0, layer1):
+        self.build_layers(shape_json, mc_json, layer0, layer1)
+        v, f = self.get_v(), self.get_f()
+        self.finish_geometry()
+        return v, f
+
+    def stage_seconds(self):
+        buf = (ctypes.c_double * 4)()
+        self.lib.oracle_stage_seconds(buf)
+        return {"eval": buf[0], "marching_cubes": buf[1], "resample": buf[2], "projection_qem": buf[3]}
 
     def grid_size(self):
         return self.lib.oracle_grid_size()
@@ -108,7 +128,34 @@ def build_oracle():
     return os.path.join(ORACLE_DIR, "liboracle.so")
 
 
+def _cpu_tag():
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("flags"):
+                    import hashlib
+                    return hashlib.sha1(line.encode()).hexdigest()
+    except OSError:
+        pass
+    return "unknown"
+
+
+def build_oracle_mt():
+    """liboracle_mt.so is built -march=native: rebuild it when this machine's CPU is not the one it was built on (the .so
+    travels to the GPU box with the snapshot)."""
+    tag_path, so = os.path.join(ORACLE_DIR, "liboracle_mt.cpu"), os.path.join(ORACLE_DIR, "liboracle_mt.so")
+    tag = _cpu_tag()
+    have = open(tag_path).read().strip() if os.path.exists(tag_path) else ""
+    if have != tag and os.path.exists(so):
+        os.remove(so)
+    subprocess.run(["make", "-C", ORACLE_DIR, "mt"], check=True, stdout=subprocess.DEVNULL)
+    with open(tag_path, "w") as f:
+        f.write(tag)
+    return so
+
+
 _oracle = None
+_oracle_mt = None
 
 
 def load_oracle():
@@ -116,6 +163,23 @@ def load_oracle():
     if _oracle is None:
         _oracle = Oracle(build_oracle())
     return _oracle
+
+
+def host_threads():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def load_oracle_mt(threads=None):
+    """The multi-threaded -O3 -march=native build of the same oracle sources (bit-identical results): the timed CPU baseline
+    and parity cases too large for one thread."""
+    global _oracle_mt
+    if _oracle_mt is None:
+        _oracle_mt = Oracle(build_oracle_mt())
+    _oracle_mt.set_threads(threads if threads else host_threads())
+    return _oracle_mt
 
 
 class Emu:
