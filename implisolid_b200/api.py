@@ -65,6 +65,9 @@ EXT_SIGNATURES = {
     "isd_last_timings": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "isd_last_counters": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "isd_last_program_stats": (ctypes.c_int, [ctypes.c_void_p]),
+    "isd_last_kernel_times": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]),
+    "isd_kernel_name": (ctypes.c_char_p, [ctypes.c_int]),
+    "isd_last_kernel_flops": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "isd_grid_size": (ctypes.c_int, []),
     "isd_get_field": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int64]),
     "isd_get_case_codes": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int64]),
@@ -86,6 +89,8 @@ EXT_SIGNATURES = {
     "isd_dist_unique_id": (ctypes.c_int, [ctypes.c_void_p]),
     "isd_dist_init": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
     "isd_dist_finalize": (None, []),
+    "isd_dist_suspend": (None, []),
+    "isd_dist_resume": (None, []),
     "isd_dist_emulate": (ctypes.c_int, [ctypes.c_int, ctypes.c_int]),
     "isd_dist_set_offsets": (None, [ctypes.c_int64, ctypes.c_int64]),
     "isd_dist_last_slab": (ctypes.c_int, [ctypes.c_void_p]),
@@ -261,6 +266,19 @@ class GeometryLibrary:
                 "projection_by_type": [int(x) for x in buf[3:10]], "projection_failed": int(buf[10]),
                 "bisection_capped": int(buf[11]), "bisected": int(buf[12]), "launches": int(buf[13]),
                 "field_bytes": int(buf[14]), "nodes_full_eval": int(buf[15])}
+
+    def last_kernel_times(self):
+        """{kernel name: (ms summed over its launches, launches)} of the last build; needs "gpu":{"kernel_times":1}."""
+        ms = np.zeros(64, dtype=np.float32)
+        cnt = np.zeros(64, dtype=np.int32)
+        n = self.lib.isd_last_kernel_times(ms.ctypes.data, cnt.ctypes.data, 64)
+        return {self.lib.isd_kernel_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n) if cnt[i]}
+
+    def last_kernel_flops(self):
+        """{kernel name: FP32 operations its CSG evaluations executed} for the last build; needs "gpu":{"count_flops":1}."""
+        fl = np.zeros(64, dtype=np.float64)
+        n = self.lib.isd_last_kernel_flops(fl.ctypes.data, 64)
+        return {self.lib.isd_kernel_name(i).decode(): float(fl[i]) for i in range(n) if fl[i] > 0}
 
     def last_program_stats(self):
         buf = np.zeros(4, dtype=np.float64)

@@ -291,6 +291,64 @@ ISD_HD float prim_value(uint32_t op, const Prog& prog, int at, const Mat12<Prog>
     return prim_half_plane(prog, at, x, y, z);
 }
 
+// ---- flop accounting (bench.py's FP32 roofline entries) ---------------------------------------------------------------
+// Floating-point operations one instruction executes per point, multiplications and additions counted separately (exact mode
+// has no FMA), comparisons / selects / sqrt / division one each.  Value-mode numbers are the ones ShapeCompiler adds up into
+// Program::flops_per_point (program.hpp); gradient mode adds the primitive's gradient body and the 3x3 transposed product
+// (M.back, 15) on the way up.  A closing CSG instruction: 1 select (+1 negation for a subtraction) in value mode, + M.back in
+// gradient mode.
+ISD_HD uint32_t op_flops(uint32_t op, uint32_t aux, bool gradient) {
+    uint32_t v = 18, g = 15;
+    switch (op) {
+        case OP_XFORM: return 18;
+        case OP_ELLIPSOID: v += 9; g += 3; break;
+        case OP_CYLINDER: v += 14; g += 15; break;
+        case OP_CONE: v += 14; g += 10; break;
+        case OP_CUBE: v += 11; g += 5; break;
+        case OP_CUBE_SDF: v += 40; g += 5; break;
+        case OP_METABALLS: v += 12 * aux; g += 21 * aux; break;
+        case OP_TORUS: v += 13; g += 14; break;
+        case OP_HEART: v += 24; g += 30; break;
+        case OP_MUSHROOM: v += 18 + 11; g += 18 + 9; break;
+        case OP_LID: v = 3; g = 0; break;
+        case OP_TETRA: v = 24 + 3; g = 0; break;
+        case OP_HALF_PLANE: v += 8; g += 4; break;
+        default: return 0;
+    }
+    return gradient ? v + g : v;
+}
+ISD_HD uint32_t closing_flops(uint32_t op_minus_union, bool combine, bool negate, bool gradient) {
+    uint32_t v = combine ? (op_minus_union == 2u ? 2u : 1u) : (negate ? 1u : 0u);
+    if (gradient) v = (combine ? v + 3u : (negate ? 4u : 0u)) + 15u;
+    return v;
+}
+// the whole program at one point (what eval_values / eval_value_gradient run with AllLive)
+template <class Prog>
+ISD_HD uint32_t program_flops(const Prog& prog, bool gradient) {
+    uint32_t total = 0;
+    for (int pc = 0;;) {
+        const W4 hdr = prog.load4(pc);
+        const uint32_t op = hdr.x & OP_MASK;
+        if (op == OP_END) break;
+        if (op >= OP_UNION) { total += closing_flops(op - OP_UNION, true, false, gradient); pc += kInstrWords; }
+        else if (op == OP_XFORM) { total += 18; pc += kInstrWords; }
+        else { total += op_flops(op, hdr.z, gradient); pc = (int)hdr.y; }
+    }
+    return total;
+}
+// a per-tile instruction list (entries from spec_entry / spec_entry_gradient)
+template <class Prog, class List>
+ISD_HD uint32_t list_flops(const Prog& prog, const List& list, int n_list, bool gradient) {
+    uint32_t total = 0;
+    for (int k = 0; k < n_list; ++k) {
+        const uint32_t e = list[k];
+        if (e & LE_CLOSING) { total += closing_flops((e >> LE_OP_SHIFT) & 3u, (e & LE_COMBINE) != 0, (e & LE_NEGATE) != 0, gradient); continue; }
+        const W4 hdr = prog.load4((int)(e & IT_PC_MASK) * 4);
+        total += op_flops(hdr.x & OP_MASK, hdr.z, gradient);
+    }
+    return total;
+}
+
 // ---- value mode -------------------------------------------------------------------------------------------------
 // Evaluates the program at P points held in registers; cur* are clobbered.
 // The two newest values of the stack live in registers (t0 = top, t1 = below); older ones spill to a per-thread

@@ -36,6 +36,19 @@ struct ConstProgram {
     }
 };
 
+// Flop counting ("gpu":{"count_flops":1}, an untimed instrumented pass of bench.py): every evaluation adds the flops of the
+// instruction list it ran (list_flops / program_flops, csg_eval.cuh) to d_flops_now; the host moves the sum to the launching
+// kernel's slot after each launch.  The timed kernels are the same binaries with the flag off (one uniform branch per evaluation).
+__constant__ int c_count_flops;
+__device__ unsigned long long d_flops_now;
+__device__ unsigned long long d_flops_by_kernel[32];
+__device__ __forceinline__ void add_flops(unsigned long long n) {
+    const unsigned m = __activemask();
+    const unsigned sum = __reduce_add_sync(m, (unsigned)n);      // one evaluation is far below 2^27 flops
+    if ((threadIdx.x & 31) == (unsigned)(__ffs(m) - 1)) atomicAdd(&d_flops_now, (unsigned long long)sum);
+}
+__global__ void k_flops_move(int id) { d_flops_by_kernel[id] += d_flops_now; d_flops_now = 0ull; }
+
 struct GridDesc {
     int S;             // nodes per axis = R + 5
     int pitch;         // floats per x-row in HBM
@@ -346,6 +359,7 @@ __global__ void __launch_bounds__(kTileThreads) k_eval_tiles(GridDesc g, SdfGrid
                 }
                 if (SPEC) eval_values_list<4>(ConstProgram(), sdf, s_list, s_n_list, cx, cy, cz, f);
                 else eval_values<4>(ConstProgram(), sdf, AllLive(), cx, cy, cz, f);
+                if (c_count_flops) add_flops(4ull * (SPEC ? list_flops(ConstProgram(), s_list, s_n_list, false) : program_flops(ConstProgram(), false)));
                 nib = 0;
 #pragma unroll
                 for (int p = 0; p < 4; ++p) {
@@ -371,6 +385,7 @@ __global__ void __launch_bounds__(128) k_eval_points(SdfGridView sdf, const floa
     const float x = xyz[i * 3], y = xyz[i * 3 + 1], z = xyz[i * 3 + 2];
     float f, g0, g1, g2;
     eval_value_gradient(ConstProgram(), sdf, x, y, z, f, g0, g1, g2);
+    if (c_count_flops) add_flops(program_flops(ConstProgram(), true));
     if (mode & 1) f_out[i] = f;
     if (mode & 2) {
         if (mode & 4) {

@@ -104,6 +104,7 @@ struct Context {
     // field + marching cubes scratch
     DeviceBuffer d_field, d_signs, d_tile_list, d_tile_masks, d_super_list, d_super_masks, d_bounds, d_row_tot, d_row_base, d_scan_state, d_tile_hints, d_seg_bits, d_seg_off, d_cubes, d_totals, d_cases;
     PinnedBuffer h_small;         // totals and other small read-backs
+    PinnedBuffer h_gather;        // {nv,nf} of this slab + of every rank (sized from world in isd_dist_init)
     PinnedBuffer h_program;       // staging of the bounds program + topology
     GridDesc grid{};
     McDesc mc{};
@@ -140,6 +141,7 @@ struct Context {
 
     // z-slab sharding
     int rank = 0, world = 1;
+    int comm_rank = 0, comm_world = 1;      // what the communicator was made for (isd_dist_suspend / isd_dist_resume)
     bool emulate = false;
     long long emu_voff = 0, emu_foff = 0;
     NcclApi nccl;
@@ -207,6 +209,74 @@ void ensure_init(int device = -1) {
 
 inline void launched() { g.launches++; }
 #define ISD_LAUNCH_CHECK() do { ISD_CUDA(cudaGetLastError()); launched(); } while (0)
+
+// Per-kernel device times ("gpu":{"kernel_times":1}; bench.py's roofline entries): a pair of events around every launch,
+// read after the build's last synchronisation.  Off by default: two event records per launch are a few per cent of a 0.4 ms step.
+enum { KT_SUPER_BOUNDS = 0, KT_TILE_BOUNDS, KT_EVAL_TILES, KT_CLASSIFY, KT_ROW_SCAN, KT_POINT_LISTS, KT_SEG_APPLY, KT_EMIT, KT_ADJACENCY, KT_FOF,
+       KT_CENTROID_GRAD, KT_FACE_WEIGHTS, KT_RESAMPLE, KT_FACE_PREPARE, KT_SEARCH, KT_FINISH, KT_LEFTOVERS, KT_QEM, KT_OTHER, KT_N };
+const char* const kKernelNames[KT_N] = {"k_super_bounds", "k_tile_bounds", "k_eval_tiles", "k_mc_classify_tiles", "k_row_scan", "k_build_point_lists",
+                                        "k_seg_apply", "k_mc_emit", "adjacency(k_vertex_degree+k_uscan+k_umbrella_fill+k_umbrella_sort)", "k_faces_of_faces",
+                                        "k_centroid_gradients", "k_face_weights", "k_resample", "k_face_prepare", "k_project_search", "k_project_finish",
+                                        "k_project_leftovers", "k_qem", "other(subdivision scan)"};
+struct KernelTimes {
+    bool on = false;
+    std::vector<cudaEvent_t> pool;
+    size_t used = 0;
+    struct Span { int id; cudaEvent_t a, b; };
+    std::vector<Span> spans;
+    float ms[KT_N] = {0};
+    int launches[KT_N] = {0};
+    bool counting = false, flag_on_device = false;      // "gpu":{"count_flops":1}: executed FP32 operations per kernel
+    double flops[KT_N] = {0};
+    cudaEvent_t get() {
+        if (used == pool.size()) { cudaEvent_t e; ISD_CUDA(cudaEventCreate(&e)); pool.push_back(e); }
+        return pool[used++];
+    }
+    void reset(bool enable) { on = enable; used = 0; spans.clear(); for (float& v : ms) v = 0; for (int& v : launches) v = 0; }
+    void start_counting(bool count);
+    void finish_counting();
+    void collect() {      // the stream has been synchronised
+        for (const Span& sp : spans) {
+            float t = 0;
+            ISD_CUDA(cudaEventElapsedTime(&t, sp.a, sp.b));
+            ms[sp.id] += t;
+            launches[sp.id]++;
+        }
+        spans.clear(); used = 0;
+    }
+} g_kt;
+void KernelTimes::start_counting(bool count) {
+    for (double& v : flops) v = 0;
+    if (count != flag_on_device) {
+        const int flag = count ? 1 : 0;
+        ISD_CUDA(cudaMemcpyToSymbolAsync(c_count_flops, &flag, sizeof(int), 0, cudaMemcpyHostToDevice, g.stream));
+        ISD_CUDA(cudaStreamSynchronize(g.stream));      // `flag` is a stack variable
+        flag_on_device = count;
+    }
+    counting = count;
+    if (count) {
+        static const unsigned long long zeros[33] = {0};
+        ISD_CUDA(cudaMemcpyToSymbolAsync(d_flops_by_kernel, zeros, 32 * sizeof(unsigned long long), 0, cudaMemcpyHostToDevice, g.stream));
+        ISD_CUDA(cudaMemcpyToSymbolAsync(d_flops_now, zeros, sizeof(unsigned long long), 0, cudaMemcpyHostToDevice, g.stream));
+    }
+}
+void KernelTimes::finish_counting() {
+    if (!counting) return;
+    unsigned long long h[32];
+    ISD_CUDA(cudaMemcpyFromSymbolAsync(h, d_flops_by_kernel, sizeof(h), 0, cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    for (int i = 0; i < KT_N; ++i) flops[i] = (double)h[i];
+    counting = false;
+}
+struct KtScope {
+    int id; cudaEvent_t a = nullptr;
+    explicit KtScope(int i) : id(i) { if (g_kt.on) { a = g_kt.get(); ISD_CUDA(cudaEventRecord(a, g.stream)); } }
+    ~KtScope() { if (a) { cudaEvent_t b = g_kt.get(); ISD_CUDA(cudaEventRecord(b, g.stream)); g_kt.spans.push_back({id, a, b}); } }
+};
+#define KT_CAT2(a, b) a##b
+#define KT_CAT(a, b) KT_CAT2(a, b)
+#define KT(id) KtScope KT_CAT(kt_scope_, __LINE__)(id)
+#define ISD_TIMED(id, ...) do { { KT(id); __VA_ARGS__; ISD_LAUNCH_CHECK(); } if (g_kt.counting) k_flops_move<<<1, 1, 0, g.stream>>>(id); } while (0)
 
 // per-tile instruction lists for evaluations at arbitrary points (field_kernel.cuh PointSpec): valid only for the program
 // and the grid K1 has just bounded
@@ -408,24 +478,18 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         const int want = g.sm_count * resident[spec.enabled ? 1 : 0];
         const int blocks = ntiles < want ? ntiles : want;
         if (spec.enabled) {
-            k_super_bounds<true><<<(nsuper + 127) / 128, 128, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(), tile_count);
-            ISD_LAUNCH_CHECK();
-            k_tile_bounds<true><<<level2_blocks, 64, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(),
-                                                                   g.d_signs.as<uint32_t>(), g.d_tile_list.as<unsigned>(), tile_count, hints);
-            ISD_LAUNCH_CHECK();
-            k_eval_tiles<true><<<blocks, kTileThreads, 0, g.stream>>>(gd, g.sdf, g.d_tile_list.as<unsigned>(), tile_count, spec.masks,
+            ISD_TIMED(KT_SUPER_BOUNDS, k_super_bounds<true><<<(nsuper + 127) / 128, 128, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(), tile_count));
+            ISD_TIMED(KT_TILE_BOUNDS, k_tile_bounds<true><<<level2_blocks, 64, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(),
+                                                                   g.d_signs.as<uint32_t>(), g.d_tile_list.as<unsigned>(), tile_count, hints));
+            ISD_TIMED(KT_EVAL_TILES, k_eval_tiles<true><<<blocks, kTileThreads, 0, g.stream>>>(gd, g.sdf, g.d_tile_list.as<unsigned>(), tile_count, spec.masks,
                                                                      spec.mask_words, d_itab, (int)(itab_words / 4), g.d_field.as<float>(),
-                                                                     g.d_signs.as<uint32_t>());
-            ISD_LAUNCH_CHECK();
+                                                                     g.d_signs.as<uint32_t>()));
         } else {
-            k_super_bounds<false><<<(nsuper + 127) / 128, 128, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(), tile_count);
-            ISD_LAUNCH_CHECK();
-            k_tile_bounds<false><<<level2_blocks, 64, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(),
-                                                                    g.d_signs.as<uint32_t>(), g.d_tile_list.as<unsigned>(), tile_count, hints);
-            ISD_LAUNCH_CHECK();
-            k_eval_tiles<false><<<blocks, kTileThreads, 0, g.stream>>>(gd, g.sdf, g.d_tile_list.as<unsigned>(), tile_count, nullptr, 0,
-                                                                      nullptr, 0, g.d_field.as<float>(), g.d_signs.as<uint32_t>());
-            ISD_LAUNCH_CHECK();
+            ISD_TIMED(KT_SUPER_BOUNDS, k_super_bounds<false><<<(nsuper + 127) / 128, 128, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(), tile_count));
+            ISD_TIMED(KT_TILE_BOUNDS, k_tile_bounds<false><<<level2_blocks, 64, 0, g.stream>>>(gd, d_bounds_prog, s.prune, spec, g.d_super_list.as<unsigned>(),
+                                                                    g.d_signs.as<uint32_t>(), g.d_tile_list.as<unsigned>(), tile_count, hints));
+            ISD_TIMED(KT_EVAL_TILES, k_eval_tiles<false><<<blocks, kTileThreads, 0, g.stream>>>(gd, g.sdf, g.d_tile_list.as<unsigned>(), tile_count, nullptr, 0,
+                                                                      nullptr, 0, g.d_field.as<float>(), g.d_signs.as<uint32_t>()));
         }
     }
     ISD_CUDA(cudaEventRecord(g.ev[1], g.stream));
@@ -457,11 +521,9 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
             k_debug_cases<<<(unsigned)((n_rows * m.NX + 255) / 256), 256, 0, g.stream>>>(m, g.d_signs.as<uint32_t>(), dbg_cases);
             ISD_LAUNCH_CHECK();
         }
-        if (gd.ty * gd.tz <= 8192) k_mc_classify_tiles<4><<<gd.ty * gd.tz, 256, 0, g.stream>>>(m, mb, g.d_signs.as<uint32_t>());
-        else k_mc_classify_tiles<1><<<gd.ty * gd.tz, 64, 0, g.stream>>>(m, mb, g.d_signs.as<uint32_t>());
-        ISD_LAUNCH_CHECK();
-        k_row_scan<<<scan_blocks, kRowScanThreads, 0, g.stream>>>(m, mb, rows_per_block, g.d_scan_state.as<unsigned>(), g.d_totals.as<unsigned>());
-        ISD_LAUNCH_CHECK();
+        if (gd.ty * gd.tz <= 8192) ISD_TIMED(KT_CLASSIFY, k_mc_classify_tiles<4><<<gd.ty * gd.tz, 256, 0, g.stream>>>(m, mb, g.d_signs.as<uint32_t>()));
+        else ISD_TIMED(KT_CLASSIFY, k_mc_classify_tiles<1><<<gd.ty * gd.tz, 64, 0, g.stream>>>(m, mb, g.d_signs.as<uint32_t>()));
+        ISD_TIMED(KT_ROW_SCAN, k_row_scan<<<scan_blocks, kRowScanThreads, 0, g.stream>>>(m, mb, rows_per_block, g.d_scan_state.as<unsigned>(), g.d_totals.as<unsigned>()));
     }
     // totals back to the host: sizes of the vertex, face and cut-cube arrays (+ the ghost layer's share, z-slabs only)
     ISD_CUDA(cudaMemcpyAsync(h, g.d_totals.ptr, 10 * sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));      // [8] = work-list length
@@ -481,9 +543,8 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
             ps.lists = g.d_point_lists.as<uint32_t>();
             ps.TW = hints.TW; ps.stride = stride; ps.enabled = 1;
             const unsigned want_blocks = (h[8] + 3) / 4, cap = (unsigned)g.sm_count * 16;
-            k_build_point_lists<<<want_blocks < cap ? want_blocks : cap, 128, 0, g.stream>>>(tile_count, spec.masks, spec.mask_words, d_itab, n_instr, stride,
-                                                                                             g.d_point_lists.as<uint32_t>());
-            ISD_LAUNCH_CHECK();
+            ISD_TIMED(KT_POINT_LISTS, k_build_point_lists<<<want_blocks < cap ? want_blocks : cap, 128, 0, g.stream>>>(tile_count, spec.masks, spec.mask_words, d_itab, n_instr, stride,
+                                                                                             g.d_point_lists.as<uint32_t>()));
             set_point_spec(&ps);
         }
     }
@@ -493,8 +554,7 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     if (n_work > 0) {   // K3, second half: absolute segment offsets + the ordered list of cut cubes
         unsigned blocks = (unsigned)((n_seg + 255) / 256);
         if (blocks > (unsigned)g.sm_count * 32u) blocks = (unsigned)g.sm_count * 32u;
-        k_seg_apply<<<blocks, 256, 0, g.stream>>>(m, mb, g.d_cubes.as<unsigned long long>());
-        ISD_LAUNCH_CHECK();
+        ISD_TIMED(KT_SEG_APPLY, k_seg_apply<<<blocks, 256, 0, g.stream>>>(m, mb, g.d_cubes.as<unsigned long long>()));
     }
     ISD_CUDA(cudaEventRecord(g.ev[2], g.stream));
     const long long scan_v = h[0], scan_f = h[1];
@@ -518,7 +578,7 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
             // enqueued here and read back at the end of the step, so nothing waits for the slowest rank in between
             g.d_gather.reserve((size_t)g.world * 2 * sizeof(int64_t) + 64);
             int64_t* dg = g.d_gather.as<int64_t>();
-            int64_t* hs = reinterpret_cast<int64_t*>(g.h_small.as<char>() + 256);
+            int64_t* hs = g.h_gather.as<int64_t>();
             hs[0] = nv; hs[1] = nf;
             ISD_CUDA(cudaMemcpyAsync(dg + 2 * g.world, hs, 2 * sizeof(int64_t), cudaMemcpyHostToDevice, g.stream));
             g.nccl.check(g.nccl.AllGather(dg + 2 * g.world, dg, 2, kNcclInt64, g.comm, g.stream), "ncclAllGather");
@@ -529,7 +589,7 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
             // the one collective of the path: {nv, nf} of every slab (16 bytes per rank)
             g.d_gather.reserve((size_t)g.world * 2 * sizeof(int64_t) + 64);
             int64_t* dg = g.d_gather.as<int64_t>();
-            int64_t* hs = reinterpret_cast<int64_t*>(g.h_small.as<char>() + 256);
+            int64_t* hs = g.h_gather.as<int64_t>();
             hs[0] = nv; hs[1] = nf;
             ISD_CUDA(cudaMemcpyAsync(dg + 2 * g.world, hs, 2 * sizeof(int64_t), cudaMemcpyHostToDevice, g.stream));
             g.nccl.check(g.nccl.AllGather(dg + 2 * g.world, dg, 2, kNcclInt64, g.comm, g.stream), "ncclAllGather");
@@ -560,10 +620,9 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         if (g.halo_mode) { ea.vbase = 0; ea.fbase = 0; ea.v_local0 = 0; }      // local numbering = scan order, ghost vertices first
         unsigned blocks = (n_cubes + kEmitThreads - 1) / kEmitThreads;
         if (blocks > (unsigned)g.sm_count * 16u) blocks = (unsigned)g.sm_count * 16u;
-        k_mc_emit<<<blocks, kEmitThreads, 0, g.stream>>>(m, mb, ea, g.d_field.as<float>(), g.d_signs.as<uint32_t>(),
+        ISD_TIMED(KT_EMIT, k_mc_emit<<<blocks, kEmitThreads, 0, g.stream>>>(m, mb, ea, g.d_field.as<float>(), g.d_signs.as<uint32_t>(),
                                                          g.d_cubes.as<unsigned long long>(), g.d_totals.as<unsigned>() + 2,
-                                                         g.d_verts.as<float>() + g.local_voff * 3, g.d_faces.as<int>() + g.local_foff * 3);
-        ISD_LAUNCH_CHECK();
+                                                         g.d_verts.as<float>() + g.local_voff * 3, g.d_faces.as<int>() + g.local_foff * 3));
     }
     ISD_CUDA(cudaEventRecord(g.ev[3], g.stream));
     g.nv = nv; g.nf = nf;
@@ -585,7 +644,7 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
 // all ranks end up with the whole stitched mesh (vertices of rank r at [voff_r, voff_r + nv_r))
 void gather_mesh() {
     if (g.world == 1 || g.gathered || g.emulate) return;
-    int64_t* hs = reinterpret_cast<int64_t*>(g.h_small.as<char>() + 256);
+    int64_t* hs = g.h_gather.as<int64_t>();
     const long long gnv = g.slab[6], gnf = g.slab[7];
     ISD_CUDA(cudaEventRecord(g.ev[13], g.stream));
     if (g.halo_mode) {      // the exported slab sits inside local arrays: move it to its global offset in arrays sized for the whole mesh
@@ -618,7 +677,7 @@ void gather_mesh() {
 // ---------------------------------------------------------------------------------------------------------------------
 // OB02 stages
 // ---------------------------------------------------------------------------------------------------------------------
-void exclusive_scan_u32(const unsigned* in, long long n, unsigned* out /* n + 1 */) {
+void exclusive_scan_u32(const unsigned* in, long long n, unsigned* out /* n + 1 */, int kt_id = KT_ADJACENCY) {
     if (n == 0) { ISD_CUDA(cudaMemsetAsync(out, 0, sizeof(unsigned), g.stream)); return; }
     int blocks = (int)((n + kUScanThreads * 4 - 1) / (kUScanThreads * 4));      // >= 4 rounds per block: fewer blocks to wait for
     if (blocks > kUScanMaxBlocks) blocks = kUScanMaxBlocks;
@@ -626,8 +685,7 @@ void exclusive_scan_u32(const unsigned* in, long long n, unsigned* out /* n + 1 
     const size_t state_bytes = (4 + 2 * (size_t)kUScanMaxBlocks) * sizeof(unsigned);
     g.d_upartials.reserve(state_bytes);
     ISD_CUDA(cudaMemsetAsync(g.d_upartials.ptr, 0, state_bytes, g.stream));
-    k_uscan<<<blocks, kUScanThreads, 0, g.stream>>>(in, n, per_block, g.d_upartials.as<unsigned>(), out);
-    ISD_LAUNCH_CHECK();
+    ISD_TIMED(kt_id, k_uscan<<<blocks, kUScanThreads, 0, g.stream>>>(in, n, per_block, g.d_upartials.as<unsigned>(), out));
 }
 
 inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
@@ -642,22 +700,18 @@ void build_adjacency(bool need_fof) {
         g.d_uitems.reserve((size_t)nf * 3 * sizeof(int) + 16);
         ISD_CUDA(cudaMemsetAsync(g.d_deg.ptr, 0, (size_t)(nv + 1) * sizeof(unsigned), g.stream));
         ISD_CUDA(cudaMemsetAsync(g.d_cursor.ptr, 0, (size_t)(nv + 1) * sizeof(unsigned), g.stream));
-        k_vertex_degree<<<blocks_for((long long)nf * 3, 256), 256, 0, g.stream>>>(g.d_faces.as<int>(), nf, g.d_deg.as<unsigned>());
-        ISD_LAUNCH_CHECK();
+        ISD_TIMED(KT_ADJACENCY, k_vertex_degree<<<blocks_for((long long)nf * 3, 256), 256, 0, g.stream>>>(g.d_faces.as<int>(), nf, g.d_deg.as<unsigned>()));
         exclusive_scan_u32(g.d_deg.as<unsigned>(), nv, g.d_uoff.as<unsigned>());
-        k_umbrella_fill<<<blocks_for((long long)nf * 3, 256), 256, 0, g.stream>>>(g.d_faces.as<int>(), nf, g.d_uoff.as<unsigned>(),
-                                                                                 g.d_cursor.as<unsigned>(), g.d_uitems.as<int>());
-        ISD_LAUNCH_CHECK();
-        k_umbrella_sort<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>());
-        ISD_LAUNCH_CHECK();
+        ISD_TIMED(KT_ADJACENCY, k_umbrella_fill<<<blocks_for((long long)nf * 3, 256), 256, 0, g.stream>>>(g.d_faces.as<int>(), nf, g.d_uoff.as<unsigned>(),
+                                                                                 g.d_cursor.as<unsigned>(), g.d_uitems.as<int>()));
+        ISD_TIMED(KT_ADJACENCY, k_umbrella_sort<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>()));
         g.adjacency_valid = true;
         g.fof_valid_ = false;
     }
     if (need_fof && !g.fof_valid_) {
         g.d_fof.reserve((size_t)nf * 3 * sizeof(int) + 16);
-        k_faces_of_faces<<<blocks_for((long long)nf * 3, 256), 256, 0, g.stream>>>(g.d_faces.as<int>(), nf, g.d_uoff.as<unsigned>(),
-                                                                                  g.d_uitems.as<int>(), g.d_fof.as<int>());
-        ISD_LAUNCH_CHECK();
+        ISD_TIMED(KT_FOF, k_faces_of_faces<<<blocks_for((long long)nf * 3, 256), 256, 0, g.stream>>>(g.d_faces.as<int>(), nf, g.d_uoff.as<unsigned>(),
+                                                                                  g.d_uitems.as<int>(), g.d_fof.as<int>()));
         g.fof_valid_ = true;
     }
 }
@@ -677,14 +731,11 @@ void vertex_resampling_step(float c) {
     g.d_cen.reserve((size_t)nf * 3 * sizeof(float) + 16);
     g.d_nrm.reserve((size_t)nf * 3 * sizeof(float) + 16);
     g.d_w.reserve((size_t)nf * sizeof(float) + 16);
-    (g.point_spec_on ? k_centroid_gradients<true> : k_centroid_gradients<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(),
-                                                                   g.d_nrm.as<float>());
-    ISD_LAUNCH_CHECK();
-    k_face_weights<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.d_cen.as<float>(), g.d_nrm.as<float>(), g.d_fof.as<int>(), nf, c, g.d_w.as<float>());
-    ISD_LAUNCH_CHECK();
-    k_resample<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(), g.d_w.as<float>(), g.d_cen.as<float>(),
-                                                          g.d_verts.as<float>());
-    ISD_LAUNCH_CHECK();
+    ISD_TIMED(KT_CENTROID_GRAD, (g.point_spec_on ? k_centroid_gradients<true> : k_centroid_gradients<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(),
+                                                                   g.d_nrm.as<float>()));
+    ISD_TIMED(KT_FACE_WEIGHTS, k_face_weights<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.d_cen.as<float>(), g.d_nrm.as<float>(), g.d_fof.as<int>(), nf, c, g.d_w.as<float>()));
+    ISD_TIMED(KT_RESAMPLE, k_resample<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(), g.d_w.as<float>(), g.d_cen.as<float>(),
+                                                          g.d_verts.as<float>()));
 }
 
 // make_alpha_list (centroids_projection.cpp:144-194)
@@ -731,7 +782,7 @@ void resolve_halo_offsets() {
     if (g.emulate) { g.slab[2] = g.emu_voff; g.slab[3] = g.emu_foff; g.slab[6] = -1; g.slab[7] = g.emu_gnf; return; }
     if (!g.halo_pending) return;
     ISD_CUDA(cudaStreamSynchronize(g.stream));
-    const int64_t* hs = reinterpret_cast<const int64_t*>(g.h_small.as<char>() + 256);
+    const int64_t* hs = g.h_gather.as<int64_t>();
     long long voff = 0, foff = 0, gnv = 0, gnf = 0;
     for (int r = 0; r < g.world; ++r) {
         if (r == g.rank) { voff = gnv; foff = gnf; }
@@ -771,7 +822,18 @@ const float* noise_stream(size_t count) {
 // polygonize_step_2 (polygonizer_algorithm_ob02.hpp:108-116) -> centroids_projection (centroids_projection.cpp:1219-1311)
 void projection_step(bool enable_qem, bool exact_reduce) {
     const int nv = (int)g.nv, nf = (int)g.nf;
-    if (nf == 0) return;
+    if (nf == 0) {
+        // A slab (plus halo) without faces still owes the other ranks its term of the mean-edge all-reduce: every rank enqueues
+        // the collective once per projection step, whatever it holds.
+        if (g.halo_mode && !g.emulate && g.world > 1) {
+            g.d_scal.reserve(sizeof(AlphaList) + 64);
+            AlphaList* al0 = g.d_scal.as<AlphaList>();
+            ISD_CUDA(cudaMemsetAsync(al0, 0, sizeof(AlphaList), g.stream));
+            g.alpha_ticket_zeroed = true;
+            g.nccl.check(g.nccl.AllReduce(&al0->edge_sum, &al0->edge_total, 1, kNcclUint64, kNcclSum, g.comm, g.stream), "ncclAllReduce");
+        }
+        return;
+    }
     ISD_CUDA(cudaEventRecord(g.ev[6], g.stream));
     const unsigned prep_blocks = blocks_for(nf, 256);
     {
@@ -795,9 +857,8 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     // centroids + mean edge length + alpha list, all on the device (centroids_projection.cpp:1230-1245)
     if (g.halo_mode) {
         // only the slab's own faces are summed; the all-reduce (8 bytes) gives every GPU the whole mesh's sum, in the stream
-        k_face_prepare<<<prep_blocks, 256, 0, g.stream>>>(g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(), d_len3, d_partials, d_al,
-                                                          (int)g.own_f0, (int)g.own_f1, 0);
-        ISD_LAUNCH_CHECK();
+        ISD_TIMED(KT_FACE_PREPARE, k_face_prepare<<<prep_blocks, 256, 0, g.stream>>>(g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(), d_len3, d_partials, d_al,
+                                                          (int)g.own_f0, (int)g.own_f1, 0));
         if (g.emulate) {
             ISD_CUDA(cudaMemcpyAsync(g.h_small.as<char>() + 3200, &d_al->edge_sum, sizeof(unsigned long long), cudaMemcpyDeviceToHost, g.stream));
             memcpy(g.h_small.as<char>() + 3208, &g.emu_edge_total, sizeof(unsigned long long));
@@ -809,9 +870,8 @@ void projection_step(bool enable_qem, bool exact_reduce) {
         }
         ISD_LAUNCH_CHECK();
     } else {
-        k_face_prepare<<<prep_blocks, 256, 0, g.stream>>>(g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(), d_len3, d_partials, d_al,
-                                                          0, nf, 1);
-        ISD_LAUNCH_CHECK();
+        ISD_TIMED(KT_FACE_PREPARE, k_face_prepare<<<prep_blocks, 256, 0, g.stream>>>(g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(), d_len3, d_partials, d_al,
+                                                          0, nf, 1));
         if (g.world == 1 || g.emulate)      // the sum of a whole mesh: what emulated ranks are handed as the all-reduce result
             ISD_CUDA(cudaMemcpyAsync(g.h_small.as<char>() + 3200, &d_al->edge_sum, sizeof(unsigned long long), cudaMemcpyDeviceToHost, g.stream));
     }
@@ -834,19 +894,16 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     a.n = nf; a.speculative = 1;
     // the list of left-over centroids lives in the output array: k_project_finish only writes it once there are none left to list
     a.leftover = reinterpret_cast<int*>(g.d_proj.as<float>());
-    (g.point_spec_on ? k_project_search<true> : k_project_search<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a);
-    ISD_LAUNCH_CHECK();
+    ISD_TIMED(KT_SEARCH, (g.point_spec_on ? k_project_search<true> : k_project_search<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a));
     // Phase B (direction types 2..6) is only needed when phase A left centroids over, which is rare and which only the device
     // knows: the rest of the step is launched right away and does nothing in that case (the kernels test the counter), so the
     // host does not have to wait here.
-    (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a);
-    ISD_LAUNCH_CHECK();
+    ISD_TIMED(KT_FINISH, (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a));
     ISD_CUDA(cudaEventRecord(g.ev[7], g.stream));
     if (enable_qem) {   // centroids_projection.cpp:1272-1310: the mesh only changes when QEM is on
         build_adjacency(false);
-        k_qem<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(), g.d_proj.as<float>(),
-                                                        g.d_pnrm.as<float>(), d_al, g.d_counters.as<Ob02Counters>(), g.d_verts.as<float>());
-        ISD_LAUNCH_CHECK();
+        ISD_TIMED(KT_QEM, k_qem<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(), g.d_proj.as<float>(),
+                                                        g.d_pnrm.as<float>(), d_al, g.d_counters.as<Ob02Counters>(), g.d_verts.as<float>()));
     }
     ISD_CUDA(cudaEventRecord(g.ev[8], g.stream));
     Ob02Counters* hc = reinterpret_cast<Ob02Counters*>(g.h_small.as<char>() + 2048);
@@ -869,15 +926,12 @@ void projection_step(bool enable_qem, bool exact_reduce) {
         a.speculative = 0;
         const int n_left = (int)hc->c[10];
         const unsigned left_blocks = blocks_for(n_left, 4) < (unsigned)g.sm_count * 16 ? blocks_for(n_left, 4) : (unsigned)g.sm_count * 16;
-        (g.point_spec_on ? k_project_leftovers<true> : k_project_leftovers<false>)<<<left_blocks, 128, 0, g.stream>>>(g.sdf, a, n_left);
-        ISD_LAUNCH_CHECK();
-        (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a);
-        ISD_LAUNCH_CHECK();
+        ISD_TIMED(KT_LEFTOVERS, (g.point_spec_on ? k_project_leftovers<true> : k_project_leftovers<false>)<<<left_blocks, 128, 0, g.stream>>>(g.sdf, a, n_left));
+        ISD_TIMED(KT_FINISH, (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a));
         ISD_CUDA(cudaEventRecord(g.ev[7], g.stream));
         if (enable_qem) {
-            k_qem<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(), g.d_proj.as<float>(),
-                                                            g.d_pnrm.as<float>(), d_al, nullptr, g.d_verts.as<float>());
-            ISD_LAUNCH_CHECK();
+            ISD_TIMED(KT_QEM, k_qem<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(), g.d_proj.as<float>(),
+                                                            g.d_pnrm.as<float>(), d_al, nullptr, g.d_verts.as<float>()));
         }
         ISD_CUDA(cudaEventRecord(g.ev[8], g.stream));
         ISD_CUDA(cudaMemcpyAsync(hc, g.d_counters.ptr, sizeof(Ob02Counters), cudaMemcpyDeviceToHost, g.stream));
@@ -941,7 +995,7 @@ void subdivision_step(float amplitude) {
     k_subdiv_mark<<<blocks_for(n3, 256), 256, 0, g.stream>>>(g.d_faces.as<int>(), nf, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(),
                                                             g.d_sub_owner.as<unsigned>(), g.d_sub_flag.as<unsigned>());
     ISD_LAUNCH_CHECK();
-    exclusive_scan_u32(g.d_sub_flag.as<unsigned>(), n3, g.d_sub_rank.as<unsigned>());
+    exclusive_scan_u32(g.d_sub_flag.as<unsigned>(), n3, g.d_sub_rank.as<unsigned>(), KT_OTHER);
     unsigned* h_new = reinterpret_cast<unsigned*>(g.h_small.as<char>() + 3072);
     ISD_CUDA(cudaMemcpyAsync(h_new, g.d_sub_rank.as<unsigned>() + n3, sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));
     ISD_CUDA(cudaStreamSynchronize(g.stream));
@@ -1056,6 +1110,8 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     for (float& t : g.timings) t = 0;
     for (int64_t& c : g.counters) c = 0;
     g.launches = 0;
+    g_kt.reset(s.kernel_times != 0);
+    g_kt.start_counting(s.count_flops != 0);
     g.host_valid = false;
     g.faces_in_flight = false;
     g.adjacency_valid = false;
@@ -1112,6 +1168,9 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[2], g.ev[3])); g.timings[T_EMIT] = ms;
     if (g.gathered && g.world > 1) { ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[13], g.ev[14])); g.timings[T_GATHER] = ms; }
     if (subdiv_timed) { ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[11], g.ev[12])); g.timings[T_SUBDIV] = ms; }
+    g_kt.collect();
+    g_kt.finish_counting();
+    g_kt.on = false;      // lazily computed normals and the other entry points are not part of a build's table
     if (s.normals) compute_normals();
     if (copy_out) copy_mesh_to_host();
     g.active = true;                                               // polygonize_terminate
@@ -1324,6 +1383,17 @@ int isd_last_counters(int64_t* out, int cap) {
     for (int i = 0; i < n; ++i) out[i] = g.counters[i];
     return n;
 }
+int isd_last_kernel_times(float* out_ms, int* out_launches, int cap) {
+    int n = cap < (int)KT_N ? cap : (int)KT_N;
+    for (int i = 0; i < n; ++i) { out_ms[i] = g_kt.ms[i]; out_launches[i] = g_kt.launches[i]; }
+    return n;
+}
+int isd_last_kernel_flops(double* out, int cap) {
+    int n = cap < (int)KT_N ? cap : (int)KT_N;
+    for (int i = 0; i < n; ++i) out[i] = g_kt.flops[i];
+    return n;
+}
+const char* isd_kernel_name(int id) { return (id >= 0 && id < (int)KT_N) ? kKernelNames[id] : ""; }
 int isd_last_program_stats(double* out4) {
     for (int i = 0; i < 4; ++i) out4[i] = g.prog_stats[i];
     return 4;
@@ -1433,18 +1503,32 @@ int isd_dist_unique_id(uint8_t* id128) {
 int isd_dist_init(int rank, int world, const uint8_t* id128) {
     ensure_init();
     if (world <= 1) { g.rank = 0; g.world = 1; return 0; }
+    if (rank < 0 || rank >= world || world > 4096) {
+        fprintf(stderr, "implisolid_b200: isd_dist_init: rank %d / world %d out of range\n", rank, world);
+        return 1;
+    }
+    g.h_gather.reserve((size_t)(2 + 2 * world) * sizeof(int64_t));
     if (!g.nccl.load()) abort();
     NcclApi::unique_id id;
     memcpy(&id, id128, 128);
     g.nccl.check(g.nccl.CommInitRank(&g.comm, world, id, rank), "ncclCommInitRank");
     g.rank = rank; g.world = world; g.emulate = false;
+    g.comm_rank = rank; g.comm_world = world;
     return 0;
+}
+void isd_dist_suspend(void) { g.rank = 0; g.world = 1; g.emulate = false; }
+void isd_dist_resume(void) {
+    if (g.comm) { g.rank = g.comm_rank; g.world = g.comm_world; g.emulate = false; }
 }
 void isd_dist_finalize(void) {
     if (g.comm) { g.nccl.CommDestroy(g.comm); g.comm = nullptr; }
-    g.rank = 0; g.world = 1; g.emulate = false;
+    g.rank = 0; g.world = 1; g.emulate = false; g.comm_rank = 0; g.comm_world = 1;
 }
 int isd_dist_emulate(int rank, int world) {
+    if (world > 1 && (rank < 0 || rank >= world)) {
+        fprintf(stderr, "implisolid_b200: isd_dist_emulate: rank %d / world %d out of range\n", rank, world);
+        return 1;
+    }
     g.rank = rank; g.world = world; g.emulate = world > 1;
     g.emu_voff = 0; g.emu_foff = 0;
     return 0;

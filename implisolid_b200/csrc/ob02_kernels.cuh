@@ -75,8 +75,10 @@ __device__ __forceinline__ float eval_f(const SdfGridView& sdf, float x, float y
     if (MASKED && slot >= 0) {
         const uint32_t* rec = c_point_spec.lists + (size_t)slot * 2 * c_point_spec.stride;
         eval_values_list<1>(ConstProgram(), sdf, GlobalList{rec + 1}, (int)__ldg(rec), cx, cy, cz, out);
+        if (c_count_flops) add_flops(list_flops(ConstProgram(), GlobalList{rec + 1}, (int)__ldg(rec), false));
     } else {
         eval_values<1>(ConstProgram(), sdf, AllLive(), cx, cy, cz, out);
+        if (c_count_flops) add_flops(program_flops(ConstProgram(), false));
     }
     return out[0];
 }
@@ -86,8 +88,10 @@ __device__ __forceinline__ void eval_fg(const SdfGridView& sdf, float x, float y
     if (MASKED && slot >= 0) {
         const uint32_t* rec = c_point_spec.lists + ((size_t)slot * 2 + 1) * c_point_spec.stride;
         eval_value_gradient_list(ConstProgram(), sdf, GlobalList{rec + 1}, (int)__ldg(rec), x, y, z, f, g0, g1, g2);
+        if (c_count_flops) add_flops(list_flops(ConstProgram(), GlobalList{rec + 1}, (int)__ldg(rec), true));
     } else {
         eval_value_gradient(ConstProgram(), sdf, x, y, z, f, g0, g1, g2);
+        if (c_count_flops) add_flops(program_flops(ConstProgram(), true));
     }
 }
 

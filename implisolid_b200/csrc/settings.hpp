@@ -27,10 +27,12 @@ struct McSettings {
     float post_subdiv_noise;
     // ---- ours ("gpu": {...}) ----
     int cube_mode;        // 0: analytic six-plane cube (default), 1: HEAD-literal SDF grid (needs isd_set_sdf_grid)
-    int fast_math;        // 0: exact (no FMA contraction; parity mode), 1: contraction allowed
     int verbose;
+    int kernel_times;     // 1: time every kernel of the build with its own pair of events (isd_last_kernel_times)
+    int count_flops;      // 1: the interpreters count the FP32 operations they execute, per kernel (isd_last_kernel_flops); an
+                          // instrumented pass for bench.py's roofline entries, never a timed one
     int debug_cases;      // 1: keep the dense per-cube case codes for isd_get_case_codes (parity tests)
-    int exact_reduce;     // 1: mean edge length as the reference's serial float sum, bit for bit (slow); 0: pairwise double
+    int exact_reduce;     // 1: mean edge length as the reference's serial float sum, bit for bit (slow); 0: 64-bit fixed-point sum
     int prune;            // 1 (default): skip grid tiles proven off-surface by interval bounds (mesh identical; field values
                           // exist only in tiles near the surface); 0: evaluate every node (dense field, parity mode)
     int halo;             // z-slab runs with OB02: -1 (default) every GPU optimises its own slab plus a halo of recomputed cube layers
@@ -93,9 +95,10 @@ inline McSettings parse_mc_settings(const char* json) {
     s.overall_repeats = d.get_int("overall_repeats", 1);
     s.ignore_root_matrix = d.get_bool("ignore_root_matrix", false);
     s.cube_mode = d.get_int("gpu.cube_mode", 0);
-    s.fast_math = d.get_int("gpu.fast_math", 0);
     s.verbose = d.get_int("gpu.verbose", 0);
     s.debug_cases = d.get_int("gpu.debug_cases", 0);
+    s.kernel_times = d.get_int("gpu.kernel_times", 0);
+    s.count_flops = d.get_int("gpu.count_flops", 0);
     s.exact_reduce = d.get_int("gpu.exact_reduce", 0);
     s.prune = d.get_int("gpu.prune", 1);
     s.specialize = d.get_int("gpu.specialize", 1);

@@ -108,6 +108,14 @@ int isd_last_counters(int64_t* out, int cap);
 /* Shape program of the last build: out = {flops per point (mul and add counted separately), tree nodes,
  * program words, value-stack depth}. */
 int isd_last_program_stats(double* out4);
+/* With "gpu":{"kernel_times":1} in mc_parameters_json: device time (ms, summed over its launches) and launch count of every
+ * kernel of the last build, each launch between its own pair of events on isd_stream().  isd_kernel_name(i) names entry i
+ * ("" past the end).  Returns entries written.  Without the setting every entry is zero. */
+int isd_last_kernel_times(float* out_ms, int* out_launches, int cap);
+/* With "gpu":{"count_flops":1}: FP32 operations executed by each kernel's CSG evaluations in the last build (mul and add counted
+ * separately; the instruction lists each evaluation really ran, not the whole tree).  Same indices as isd_last_kernel_times. */
+int isd_last_kernel_flops(double* out, int cap);
+const char* isd_kernel_name(int id);
 
 /* Parity introspection (needs "gpu":{"keep_field":1} in mc_parameters_json for the field). */
 int isd_grid_size(void);                       /* S = resolution + 5 nodes per axis */
@@ -141,6 +149,10 @@ void isd_eval_points(const char* shape_parameters_json, int ignore_root_matrix, 
 int isd_dist_unique_id(uint8_t* id128);
 int isd_dist_init(int rank, int world, const uint8_t* id128);
 void isd_dist_finalize(void);
+/* Build the next geometries whole on this GPU (world 1) while keeping the communicator, and go back to this rank's slab:
+ * lets one rank produce the single-GPU mesh a sharded run is checked against (bench.py's parity_ok). */
+void isd_dist_suspend(void);
+void isd_dist_resume(void);
 /* Test hook: emulate rank `rank` of `world` without NCCL; the caller supplies the gathered counts
  * global vertex/face offsets of this slab through isd_dist_set_offsets (see tests/test_gpu_slabs.py). */
 int isd_dist_emulate(int rank, int world);
@@ -148,8 +160,8 @@ void isd_dist_set_offsets(int64_t global_vertex_offset, int64_t global_face_offs
 /* Slab owned by this rank in the last build: out = {first cube layer, end cube layer, global vertex
  * offset, global face offset, local Nv, local Nf, global Nv, global Nf}. */
 int isd_dist_last_slab(int64_t* out8);
-/* Gather the stitched mesh on every rank (ncclAllGather of padded ranges); afterwards get_v/get_f
- * return the global mesh on every rank. */
+/* Gather the stitched mesh on every rank (one group of in-place ncclBroadcasts, rank r's slab from rank r, at
+ * the offsets the {nv,nf} all-gather gave); afterwards get_v/get_f return the global mesh on every rank. */
 void isd_dist_gather_mesh(void);
 /* z-slab runs with OB02 ("halo mode"): every GPU optimises its own slab plus a halo of recomputed cube layers,
  * the only exchanges being the {nv,nf} all-gather and an 8-byte all-reduce of the fixed-point edge-length sum.  When ranks

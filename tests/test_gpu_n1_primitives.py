@@ -89,7 +89,7 @@ def test_direct_evaluation(gpu_lib, oracle):
 @pytest.mark.parametrize("name,shape,R,half", [N1[0], N1[1], N1[6]], ids=["torus", "heart", "medley"])
 def test_ob02_on_new_primitives(gpu_lib, oracle, name, shape, R, half):
     sj = shape()
-    mc = shapes.mc_settings(R, half, iters=1, c=1.0, projection=1, qem=1, exact_reduce=1)
+    mc = shapes.mc_settings(R, half, iters=1, c=1.0, projection=1, qem=1)
     gv, gf = gpu_lib.polygonize(sj, mc)
     ov, of = oracle.polygonize(sj, mc)
     assert np.array_equal(gf, of)

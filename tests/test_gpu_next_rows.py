@@ -51,7 +51,7 @@ def test_subdivision_noise_is_the_glibc_rand_stream(gpu_lib, oracle):
 def test_full_default_pipeline_with_subdivision(gpu_lib, oracle):
     """MC -> 2 x (resample, project + QEM) -> subdivision on the last repeat only (mcc2.cpp:396-401)."""
     sj = shapes.c2_cube_minus_cylinder()
-    mc = _mc(40, 0.8, noise=0.0, iters=1, c=1.0, projection=1, qem=1, repeats=2, exact_reduce=1)
+    mc = _mc(40, 0.8, noise=0.0, iters=1, c=1.0, projection=1, qem=1, repeats=2)
     ov, of = oracle.polygonize(sj, mc)
     gv, gf = gpu_lib.polygonize(sj, mc)
     assert np.array_equal(gf, of)
@@ -60,7 +60,7 @@ def test_full_default_pipeline_with_subdivision(gpu_lib, oracle):
 
 def test_progress_reports_match_the_oracle(gpu_lib, oracle):
     sj = shapes.c2_cube_minus_cylinder()
-    mc = _mc(48, 0.8, subdiv=0, iters=2, c=1.0, projection=1, qem=1, exact_reduce=1)
+    mc = _mc(48, 0.8, subdiv=0, iters=2, c=1.0, projection=1, qem=1)
     specs = '{"progressCallback_id": 11, "call_id": 4, "shape_id": 9}'
     o_rep, (ov, of) = oracle.polygonize_progressive(sj, mc, call_specs=specs)
     g_rep, (gv, gf) = gpu_lib.polygonize_progressive(sj, mc, call_specs=specs)
