@@ -42,6 +42,10 @@ struct Stats {
     long projection_failed = 0;
     long bisection_capped = 0;
     long bisected = 0;
+    // the reference's ASSERT_USED invariants, counted instead of asserted (tests hold them at zero):
+    long not_conjugated = 0;        // bisection inputs that do not bracket the surface, check_bisection_input_signs (bisection.hpp:51-95)
+                                    // and test_if_points_are_inside/outside (centroids_projection.cpp:1140-1143)
+    long unresolved_after_bisection = 0;      // |f| > ROOT_TOLERANCE at a bisection result that did not hit the iteration cap
 };
 
 inline REAL norm_2(REAL x, REAL y, REAL z) { return std::sqrt(x * x + y * y + z * z); }
@@ -428,9 +432,24 @@ inline void set_centers_on_surface(const implicit_function& object, const vects&
     for (int i = 0; i < m; i++)
         if (f2r[i] < -ROOT_TOLERANCE)
             for (int d = 0; d < 3; d++) std::swap(x2r[i][d], x1r[i][d]);
+    if (st && m) {      // x1: outside (f < -tol), x2: inside (f > +tol), after the swap above
+        scalars v1(m), v2(m);
+        object.eval_implicit(x1r, &v1);
+        object.eval_implicit(x2r, &v2);
+        for (int i = 0; i < m; i++)
+            if (!(sign_tol(v1[i]) * sign_tol(v2[i]) < 0) || !(v1[i] < -ROOT_TOLERANCE)) st->not_conjugated++;
+    }
     vects xb(m);
+    const long capped_before = st ? st->bisection_capped : 0;
     bisection(object, xb, x1r, x2r, st);
     if (st) st->bisected += m;
+    if (st && m) {
+        scalars vb(m);
+        object.eval_implicit(xb, &vb);
+        long off = 0;
+        for (int i = 0; i < m; i++) if (std::abs(vb[i]) > ROOT_TOLERANCE) off++;
+        st->unresolved_after_bisection += std::max(0L, off - (st->bisection_capped - capped_before));
+    }
     vects out = centroids;
     for (int i = 0; i < m; i++)
         for (int d = 0; d < 3; d++) out[rel[i]][d] = xb[i][d];

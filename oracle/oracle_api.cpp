@@ -355,6 +355,30 @@ void oracle_build_layers(const char* shape_parameters_json, const char* mc_param
 }
 void oracle_stage_seconds(double* out4) { for (int i = 0; i < 4; i++) out4[i] = g_stage_s[i]; }
 
+// ---- oracle-only: pins against the reference's own known answers and independent implementations ----------------------------
+int oracle_tetrahedron_integrity(const float* corners12, const float* m12) {
+    REAL c[4][3];
+    for (int i = 0; i < 4; i++) for (int j = 0; j < 3; j++) c[i][j] = corners12[i * 3 + j];
+    tetrahedron t(c, m12);
+    return t.integrity_failure();
+}
+void oracle_tetrahedron_planes(const float* corners12, const float* m12, float* planes16) {
+    REAL c[4][3];
+    for (int i = 0; i < 4; i++) for (int j = 0; j < 3; j++) c[i][j] = corners12[i * 3 + j];
+    tetrahedron t(c, m12);
+    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) planes16[i * 4 + j] = t.planes[i][j];
+}
+void oracle_sym_eig3(const float* a9, float* w3, float* v9) {
+    REAL A[3][3], w[3], V[3][3];
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) A[i][j] = a9[i * 3 + j];
+    sym_eig3(A, w, V);
+    for (int i = 0; i < 3; i++) { w3[i] = w[i]; for (int j = 0; j < 3; j++) v9[i * 3 + j] = V[i][j]; }
+}
+void oracle_mt11213b_raw(unsigned seed, int n, unsigned* out) {
+    mt11213b rng(seed);
+    for (int i = 0; i < n; i++) out[i] = rng();
+}
+
 // ---- oracle-only introspection ----------------------------------------------------------------
 int oracle_grid_size() { return g_S; }
 const float* oracle_field_ptr() { return g_field.data(); }
@@ -366,6 +390,7 @@ void oracle_get_stats(long* out9) {     // [0..6] by type, [7] failed, [8] cappe
     out9[7] = g_stats.projection_failed;
     out9[8] = g_stats.bisection_capped;
 }
+void oracle_get_invariants(long* out2) { out2[0] = g_stats.not_conjugated; out2[1] = g_stats.unresolved_after_bisection; }
 int oracle_projection_count() { return (int)g_proj.centroids_after.n(); }
 const float* oracle_projected_centroids_ptr() { return g_proj.centroids_after.d.data(); }
 const float* oracle_centroid_normals_ptr() { return g_proj.centroid_normals.d.data(); }

@@ -444,6 +444,34 @@ struct tetrahedron : implicit_function {
             for (int j = 0; j < 4; j++) planes[k][j] *= s;
         }
     }
+    // integrity_invariant (tetrahedron.hpp:212-321): the reference asserts it in eval_implicit; its own three FAILED TESTS
+    // (:346-383) are the fixtures tests/test_oracle_pins.py holds this restatement — and through it getPlanes — to.
+    // Returns 0 when the tetrahedron is sound, else the number of the check that rejects it (1 points too close, 2 three
+    // points on a line, 3 a corner too close to the opposite plane).
+    int integrity_failure() const {
+        const REAL MIN_PRINTABLE_LENGTH = 0.01 / 2.0, MIN_THICKNESS = 0.2;      // configs.hpp:45-46
+        for (int i = 0; i < 3; i++)
+            for (int j = i + 1; j < 4; j++) {
+                REAL d = std::sqrt((p[i][0] - p[j][0]) * (p[i][0] - p[j][0]) + (p[i][1] - p[j][1]) * (p[i][1] - p[j][1]) +
+                                   (p[i][2] - p[j][2]) * (p[i][2] - p[j][2]));
+                if (d < MIN_PRINTABLE_LENGTH) return 1;
+            }
+        for (int i = 0; i < 4; i++) {
+            const int i_1 = (i + 1) % 4, i_2 = (i + 2) % 4, i_3 = (i + 3) % 4;
+            REAL u[3], v[3];
+            for (int k = 0; k < 3; k++) { u[k] = p[i_2][k] - p[i_1][k]; v[k] = p[i_3][k] - p[i_1][k]; }
+            REAL d = std::sqrt((u[1] * v[2] - u[2] * v[1]) * (u[1] * v[2] - u[2] * v[1]) + (u[2] * v[0] - u[0] * v[2]) * (u[2] * v[0] - u[0] * v[2]) +
+                               (u[0] * v[1] - u[1] * v[0]) * (u[0] * v[1] - u[1] * v[0]));
+            if (d < MIN_PRINTABLE_LENGTH) return 2;
+        }
+        for (int i = 0; i < 4; i++) {
+            REAL d = planes[i][0] * p[i][0] + planes[i][1] * p[i][1] + planes[i][2] * p[i][2] + planes[i][3];
+            d /= std::sqrt(planes[i][0] * planes[i][0] + planes[i][1] * planes[i][1] + planes[i][2] * planes[i][2]);
+            d = d < 0 ? -d : d;
+            if (!(d >= MIN_THICKNESS)) return 3;      // NaN (a degenerate plane) fails like a small distance
+        }
+        return 0;
+    }
     tetrahedron(const REAL corners[4][3], const REAL m[12]) {
         for (int i = 0; i < 12; i++) { M[i] = m[i]; Minv[i] = (i % 5 == 0) ? 1.0f : 0.0f; }
         vects c(4);

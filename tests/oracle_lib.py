@@ -70,6 +70,36 @@ class Oracle(GeometryLibrary):
         self.lib.oracle_get_stats(buf)
         return {"projection_by_type": list(buf[0:7]), "projection_failed": buf[7], "bisection_capped": buf[8]}
 
+    def invariants(self):
+        """The reference's ASSERT_USED checks around the bisection, counted by the last build (oob02.hpp Stats)."""
+        buf = (ctypes.c_long * 2)()
+        self.lib.oracle_get_invariants(buf)
+        return {"not_conjugated": buf[0], "unresolved_after_bisection": buf[1]}
+
+    def tetrahedron_integrity(self, corners, m12=None):
+        c = np.ascontiguousarray(corners, dtype=np.float32).reshape(12)
+        m = np.ascontiguousarray(m12 if m12 is not None else [1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0], dtype=np.float32)
+        return int(self.lib.oracle_tetrahedron_integrity(c.ctypes.data_as(ctypes.c_void_p), m.ctypes.data_as(ctypes.c_void_p)))
+
+    def tetrahedron_planes(self, corners, m12=None):
+        c = np.ascontiguousarray(corners, dtype=np.float32).reshape(12)
+        m = np.ascontiguousarray(m12 if m12 is not None else [1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0], dtype=np.float32)
+        out = np.zeros((4, 4), dtype=np.float32)
+        self.lib.oracle_tetrahedron_planes(c.ctypes.data_as(ctypes.c_void_p), m.ctypes.data_as(ctypes.c_void_p), out.ctypes.data_as(ctypes.c_void_p))
+        return out
+
+    def sym_eig3(self, A):
+        a = np.ascontiguousarray(A, dtype=np.float32).reshape(9)
+        w = np.zeros(3, dtype=np.float32)
+        V = np.zeros((3, 3), dtype=np.float32)
+        self.lib.oracle_sym_eig3(a.ctypes.data_as(ctypes.c_void_p), w.ctypes.data_as(ctypes.c_void_p), V.ctypes.data_as(ctypes.c_void_p))
+        return w, V
+
+    def mt11213b_raw(self, seed, n):
+        out = np.zeros(n, dtype=np.uint32)
+        self.lib.oracle_mt11213b_raw(ctypes.c_uint(seed), int(n), out.ctypes.data_as(ctypes.c_void_p))
+        return out
+
     def projected_centroids(self):
         n = self.lib.oracle_projection_count()
         c = np.ctypeslib.as_array(self.lib.oracle_projected_centroids_ptr(), shape=(n, 3)).copy()
