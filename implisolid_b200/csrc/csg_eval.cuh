@@ -291,6 +291,216 @@ ISD_HD float prim_value(uint32_t op, const Prog& prog, int at, const Mat12<Prog>
     return prim_half_plane(prog, at, x, y, z);
 }
 
+// ---- packed pairs: two points per thread on the sm_100 f32x2 pipe ------------------------------------------------------------------
+// Blackwell issues FMUL2 / FADD2 / FFMA2 on register pairs: two binary32 operations per instruction, each rounded exactly like
+// its scalar form, with a scalar register broadcast to both lanes where an operand is `splat(s)`.  The interpreters below
+// run TWO points through one instruction stream with them; every lane performs the reference's operations in the reference's
+// order, so the results keep every bit of the scalar interpreters (held on the host by tests/emu, where F2 is two plain floats,
+// and on the GPU by the parity tests).
+// ptxas (12.9) contracts mul.rn.f32x2 followed by add.rn.f32x2 into one FFMA2 even with explicit .rn and -fmad=false, which would
+// round once instead of twice.  The product is therefore written fma(a, b, nz) with nz = -0.0 read from constant memory — a value
+// the optimiser cannot see — which is fl(a*b) exactly (x + (-0) = x for every x, signed zeros included) and cannot be merged with
+// the addition that follows.  Sums and differences are add.rn.f32x2 / sub.rn.f32x2.
+struct alignas(8) F2 { float x, y; };
+#if defined(__CUDACC__)
+__constant__ float c_negzero = -0.0f;
+#endif
+ISD_HD F2 splat(float s) { return F2{s, s}; }
+ISD_HD F2 neg2(F2 a) { return F2{-a.x, -a.y}; }
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ unsigned long long f2_bits(F2 a) { return *reinterpret_cast<unsigned long long*>(&a); }
+__device__ __forceinline__ F2 f2_from(unsigned long long v) { return *reinterpret_cast<F2*>(&v); }
+#endif
+ISD_HD F2 mul2(F2 a, F2 b) {
+#if defined(__CUDA_ARCH__)
+    unsigned long long r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(f2_bits(a)), "l"(f2_bits(b)), "l"(f2_bits(F2{c_negzero, c_negzero})));
+    return f2_from(r);
+#else
+    return F2{a.x * b.x, a.y * b.y};
+#endif
+}
+ISD_HD F2 add2(F2 a, F2 b) {
+#if defined(__CUDA_ARCH__)
+    unsigned long long r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(f2_bits(a)), "l"(f2_bits(b)));
+    return f2_from(r);
+#else
+    return F2{a.x + b.x, a.y + b.y};
+#endif
+}
+ISD_HD F2 sub2(F2 a, F2 b) {
+#if defined(__CUDA_ARCH__)
+    unsigned long long r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(f2_bits(a)), "l"(f2_bits(b)));
+    return f2_from(r);
+#else
+    return F2{a.x - b.x, a.y - b.y};
+#endif
+}
+ISD_HD F2 sqrt2(F2 a) { return F2{sqrtf(a.x), sqrtf(a.y)}; }
+ISD_HD F2 min2(F2 a, F2 b) { return F2{ref_min(a.x, b.x), ref_min(a.y, b.y)}; }
+
+// Mat12::apply / Mat12::back on a pair, operation for operation
+template <class Prog>
+ISD_HD void apply2(const Mat12<Prog>& M, F2 x, F2 y, F2 z, F2& ox, F2& oy, F2& oz) {
+    const float* m = M.m;
+    ox = add2(add2(add2(mul2(splat(m[0]), x), mul2(splat(m[1]), y)), mul2(splat(m[2]), z)), splat(m[3]));
+    oy = add2(add2(add2(mul2(splat(m[4]), x), mul2(splat(m[5]), y)), mul2(splat(m[6]), z)), splat(m[7]));
+    oz = add2(add2(add2(mul2(splat(m[8]), x), mul2(splat(m[9]), y)), mul2(splat(m[10]), z)), splat(m[11]));
+}
+template <class Prog>
+ISD_HD void back2(const Mat12<Prog>& M, F2 g0, F2 g1, F2 g2, F2& o0, F2& o1, F2& o2) {
+    const float* m = M.m;
+    o0 = add2(add2(mul2(splat(m[0]), g0), mul2(splat(m[4]), g1)), mul2(splat(m[8]), g2));
+    o1 = add2(add2(mul2(splat(m[1]), g0), mul2(splat(m[5]), g1)), mul2(splat(m[9]), g2));
+    o2 = add2(add2(mul2(splat(m[2]), g0), mul2(splat(m[6]), g1)), mul2(splat(m[10]), g2));
+}
+// the factory's four everyday primitives on a pair (same expressions as prim_ellipsoid / cyl_terms / prim_cone / prim_cube)
+ISD_HD F2 prim_ellipsoid2(F2 x, F2 y, F2 z) {
+    const F2 X = add2(x, x), Y = add2(y, y), Z = add2(z, z);
+    return sub2(splat(1.0f), add2(add2(mul2(X, X), mul2(Y, Y)), mul2(Z, Z)));
+}
+ISD_HD void cyl_terms2(F2 i0, F2 i1, F2 i2, F2& t0, F2& t1, F2& r_) {
+    t0 = add2(i2, splat(0.5f));
+    t1 = sub2(splat(1.0f), t0);
+    const F2 d2 = add2(sub2(i2, t0), splat(0.5f));
+    r_ = sub2(splat(0.5f), sqrt2(add2(add2(mul2(i0, i0), mul2(i1, i1)), mul2(d2, d2))));
+}
+ISD_HD F2 prim_cylinder2(F2 x, F2 y, F2 z) {
+    F2 t0, t1, r_;
+    cyl_terms2(x, y, z, t0, t1, r_);
+    return min2(t0, min2(t1, r_));
+}
+ISD_HD F2 prim_cone2(F2 x, F2 y, F2 z) {
+    const F2 dz = sub2(z, splat(0.5f));
+    const F2 f = add2(neg2(sqrt2(add2(mul2(x, x), mul2(y, y)))), sqrt2(mul2(mul2(dz, dz), splat(0.25f))));
+    const F2 uperside = sub2(neg2(dz), splat(0.0f));
+    const F2 lowerside = add2(dz, splat(1.0f));
+    return min2(f, min2(uperside, lowerside));
+}
+ISD_HD F2 prim_cube2(F2 x, F2 y, F2 z) {
+    const F2 h = splat(0.5f);
+    const F2 t0 = sub2(h, x), t1 = add2(x, h), t2 = sub2(h, y), t3 = add2(y, h), t4 = sub2(h, z), t5 = add2(z, h);
+    return min2(t0, min2(t1, min2(t2, min2(t3, min2(t4, t5)))));
+}
+ISD_HD bool packed_primitive(uint32_t op) { return op == OP_ELLIPSOID || op == OP_CYLINDER || op == OP_CONE || op == OP_CUBE; }
+// one primitive (not METABALLS) on a pair: packed where it pays, lane by lane otherwise
+template <class Prog>
+ISD_HD F2 prim_value2(uint32_t op, const Prog& prog, int at, const Mat12<Prog>& M, const SdfGridView& sdf, F2 cx, F2 cy, F2 cz) {
+    if (packed_primitive(op)) {
+        F2 x, y, z;
+        apply2(M, cx, cy, cz, x, y, z);
+        if (op == OP_ELLIPSOID) return prim_ellipsoid2(x, y, z);
+        if (op == OP_CYLINDER) return prim_cylinder2(x, y, z);
+        if (op == OP_CONE) return prim_cone2(x, y, z);
+        return prim_cube2(x, y, z);
+    }
+    return F2{prim_value(op, prog, at, M, sdf, cx.x, cy.x, cz.x), prim_value(op, prog, at, M, sdf, cx.y, cy.y, cz.y)};
+}
+ISD_HD float csg_select(uint32_t op_minus_union, float f1, float f2) {
+    if (op_minus_union == 0u) return (f1 > f2) ? f1 : f2;
+    if (op_minus_union == 1u) return (f1 > f2) ? f2 : f1;
+    return (f1 < -f2) ? f1 : -f2;
+}
+
+// eval_values_list for NP pairs of points (2 * NP points per thread)
+template <int NP, class Prog, class List>
+ISD_HD void eval_values_list2(const Prog& prog, const SdfGridView& sdf, const List& list, int n_list, F2 (&cx)[NP], F2 (&cy)[NP], F2 (&cz)[NP],
+                              F2 (&out)[NP]) {
+    F2 spill[kMaxValueStack][NP];
+    F2 fs[kMaxFrameStack][3][NP];
+    F2 t0[NP], t1[NP];
+#pragma unroll
+    for (int p = 0; p < NP; ++p) { t0[p] = splat(0.0f); t1[p] = splat(0.0f); }
+    int sp = 0, fp = 0;
+    for (int k = 0; k < n_list; ++k) {
+        const uint32_t e = list[k];
+        int pc = (int)(e & IT_PC_MASK) * 4;
+        if (e & LE_CLOSING) {
+            if (e & LE_COMBINE) {
+                const bool swapped = (e & LE_SWAPPED) != 0;
+                const uint32_t op = (e >> LE_OP_SHIFT) & 3u;
+#pragma unroll
+                for (int p = 0; p < NP; ++p) {
+                    const F2 top = t0[p], below = t1[p];
+                    const F2 f1 = swapped ? top : below, f2 = swapped ? below : top;
+                    t0[p] = F2{csg_select(op, f1.x, f2.x), csg_select(op, f1.y, f2.y)};
+                }
+                --sp;
+                if (sp >= 2) {
+#pragma unroll
+                    for (int p = 0; p < NP; ++p) t1[p] = spill[sp - 2][p];
+                }
+            } else if (e & LE_NEGATE) {
+#pragma unroll
+                for (int p = 0; p < NP; ++p) t0[p] = neg2(t0[p]);
+            }
+            if (e & LE_RESTORE) {
+                --fp;
+#pragma unroll
+                for (int p = 0; p < NP; ++p) { cx[p] = fs[fp][0][p]; cy[p] = fs[fp][1][p]; cz[p] = fs[fp][2][p]; }
+            }
+            continue;
+        }
+        const W4 hdr = prog.load4(pc);
+        const uint32_t word = hdr.x;
+        const uint32_t op = word & OP_MASK;
+        Mat12<Prog> M;
+        M.load(prog, pc + 4);
+        pc += kInstrWords;
+        if (op == OP_XFORM) {
+            if (word & OP_FLAG_SAVE) {
+#pragma unroll
+                for (int p = 0; p < NP; ++p) { fs[fp][0][p] = cx[p]; fs[fp][1][p] = cy[p]; fs[fp][2][p] = cz[p]; }
+                ++fp;
+            }
+#pragma unroll
+            for (int p = 0; p < NP; ++p) {
+                F2 x, y, z;
+                apply2(M, cx[p], cy[p], cz[p], x, y, z);
+                cx[p] = x; cy[p] = y; cz[p] = z;
+            }
+            continue;
+        }
+        F2 f[NP];
+        if (op == OP_METABALLS) {
+            const int nb = (int)hdr.z;
+            F2 lx[NP], ly[NP], lz[NP];
+#pragma unroll
+            for (int p = 0; p < NP; ++p) { apply2(M, cx[p], cy[p], cz[p], lx[p], ly[p], lz[p]); f[p] = splat(0.0f); }
+            for (int b = 0; b < nb; ++b) {
+                const W4 q = prog.load4(pc), q2 = prog.load4(pc + 4);
+                const float bx = as_float(q.x), by = as_float(q.y), bz = as_float(q.z);
+                const float strength = as_float(q.w), subtract = as_float(q2.x);
+                pc += 8;
+#pragma unroll
+                for (int p = 0; p < NP; ++p) {
+                    const F2 fx = sub2(lx[p], splat(bx)), fx2 = mul2(fx, fx);
+                    const F2 fy = sub2(ly[p], splat(by)), fy2 = mul2(fy, fy);
+                    const F2 fz = sub2(lz[p], splat(bz)), fz2 = mul2(fz, fz);
+                    const F2 h = add2(add2(add2(splat(0.000001f), fx2), fy2), fz2);
+                    const F2 hinv = F2{1.0f / h.x, 1.0f / h.y};
+                    const F2 val = sub2(mul2(splat(strength), hinv), splat(subtract));
+                    f[p] = add2(f[p], F2{val.x / 100.0f, val.y / 100.0f});
+                }
+            }
+        } else {
+#pragma unroll
+            for (int p = 0; p < NP; ++p) f[p] = prim_value2(op, prog, pc, M, sdf, cx[p], cy[p], cz[p]);
+        }
+        if (sp >= 2) {
+#pragma unroll
+            for (int p = 0; p < NP; ++p) spill[sp - 2][p] = t1[p];
+        }
+#pragma unroll
+        for (int p = 0; p < NP; ++p) { t1[p] = t0[p]; t0[p] = f[p]; }
+        ++sp;
+    }
+#pragma unroll
+    for (int p = 0; p < NP; ++p) out[p] = t0[p];
+}
+
 // ---- flop accounting (bench.py's FP32 roofline entries) ---------------------------------------------------------------
 // Floating-point operations one instruction executes per point, multiplications and additions counted separately (exact mode
 // has no FMA), comparisons / selects / sqrt / division one each.  Value-mode numbers are the ones ShapeCompiler adds up into
@@ -796,6 +1006,107 @@ ISD_HD void eval_value_gradient_list(const Prog& prog, const SdfGridView& sdf, c
         }
         float f, o0, o1, o2;
         prim_value_gradient(op, hdr, prog, pc + kInstrWords, M, sdf, cx, cy, cz, f, o0, o1, o2);
+        if (sp > 0) { vs[sp - 1][0] = tf; vs[sp - 1][1] = t0; vs[sp - 1][2] = t1; vs[sp - 1][3] = t2; }
+        tf = f; t0 = o0; t1 = o1; t2 = o2;
+        ++sp;
+    }
+    f_out = tf; g0_out = t0; g1_out = t1; g2_out = t2;
+}
+
+// ---- gradient mode on a pair of points (same list for both) ------------------------------------------------------------------------------
+// grad_cylinder from the terms cyl_terms2 has already produced for this lane (grad_cylinder recomputes them: same operations, same bits)
+ISD_HD void grad_cylinder_from_terms(float t0, float t1, float r_, float i0, float i1, float i2, float& g0, float& g1, float& g2) {
+    const float c_t0 = (t0 <= t1 && t0 <= r_) ? 1.0f : 0.0f;
+    const float c_t1 = (t1 <= t0 && t1 <= r_) ? 1.0f : 0.0f;
+    const float c_r = (r_ <= t0 && r_ <= t1) ? 1.0f : 0.0f;
+    const float w0 = 0.0f, w1 = 0.0f, w2 = 1.0f, cx = 0.0f, cy = 0.0f, cz = -0.5f;
+    g0 = c_t0 * w0 + c_t1 * (-w0) + c_r * (w0 * t0 + cx - i0);
+    g1 = c_t0 * w1 + c_t1 * (-w1) + c_r * (w1 * t0 + cy - i1);
+    g2 = c_t0 * w2 + c_t1 * (-w2) + c_r * (w2 * t0 + cz - i2);
+}
+template <class Prog>
+ISD_HD void prim_value_gradient2(uint32_t op, const W4& hdr, const Prog& prog, int pc, const Mat12<Prog>& M, const SdfGridView& sdf, F2 cx, F2 cy,
+                                 F2 cz, F2& f, F2& o0, F2& o1, F2& o2) {
+    if (!packed_primitive(op)) {      // lane by lane through the scalar form (transform and back-transform included)
+        prim_value_gradient(op, hdr, prog, pc, M, sdf, cx.x, cy.x, cz.x, f.x, o0.x, o1.x, o2.x);
+        prim_value_gradient(op, hdr, prog, pc, M, sdf, cx.y, cy.y, cz.y, f.y, o0.y, o1.y, o2.y);
+        return;
+    }
+    F2 x, y, z, g0, g1, g2;
+    apply2(M, cx, cy, cz, x, y, z);
+    if (op == OP_ELLIPSOID) {
+        f = prim_ellipsoid2(x, y, z);
+        g0 = mul2(splat(-8.0f), x); g1 = mul2(splat(-8.0f), y); g2 = mul2(splat(-8.0f), z);
+    } else if (op == OP_CYLINDER) {
+        F2 t0, t1, r_;
+        cyl_terms2(x, y, z, t0, t1, r_);
+        f = min2(t0, min2(t1, r_));
+        grad_cylinder_from_terms(t0.x, t1.x, r_.x, x.x, y.x, z.x, g0.x, g1.x, g2.x);
+        grad_cylinder_from_terms(t0.y, t1.y, r_.y, x.y, y.y, z.y, g0.y, g1.y, g2.y);
+    } else if (op == OP_CONE) {
+        f = prim_cone2(x, y, z);
+        grad_cone(x.x, y.x, z.x, g0.x, g1.x, g2.x);
+        grad_cone(x.y, y.y, z.y, g0.y, g1.y, g2.y);
+    } else {
+        f = prim_cube2(x, y, z);
+        grad_cube(x.x, y.x, z.x, g0.x, g1.x, g2.x);
+        grad_cube(x.y, y.y, z.y, g0.y, g1.y, g2.y);
+    }
+    back2(M, g0, g1, g2, o0, o1, o2);
+}
+// one lane of a closing CSG instruction with both operands: the selected value and which operand's gradient goes up
+ISD_HD void csg_select_gradient(uint32_t op, bool swapped, float tf, float bf, float t0, float t1, float t2, float b0, float b1, float b2, float& r,
+                                float& a0, float& a1, float& a2) {
+    const float f1 = swapped ? tf : bf, f2 = swapped ? bf : tf;
+    bool first;
+    if (op == 0u) { first = (f1 > f2); r = first ? f1 : f2; }
+    else if (op == 1u) { first = !(f1 > f2); r = (f1 > f2) ? f2 : f1; }
+    else { first = (f1 < -f2); r = first ? f1 : -f2; }
+    const bool take_top = (first == swapped);
+    a0 = take_top ? t0 : b0; a1 = take_top ? t1 : b1; a2 = take_top ? t2 : b2;
+    if (!first && op == 2u) { a0 = -a0; a1 = -a1; a2 = -a2; }
+}
+template <class Prog, class List>
+ISD_HD void eval_value_gradient_list2(const Prog& prog, const SdfGridView& sdf, const List& list, int n_list, F2 cx, F2 cy, F2 cz, F2& f_out,
+                                      F2& g0_out, F2& g1_out, F2& g2_out) {
+    F2 vs[kMaxValueStack][4];
+    F2 fs[kMaxFrameStack][3];
+    F2 tf = splat(0.0f), t0 = splat(0.0f), t1 = splat(0.0f), t2 = splat(0.0f);
+    int sp = 0, fp = 0;
+    for (int k = 0; k < n_list; ++k) {
+        const uint32_t e = list[k];
+        const int pc = (int)(e & IT_PC_MASK) * 4;
+        Mat12<Prog> M;
+        M.load(prog, pc + 4);
+        if (e & LE_CLOSING) {
+            F2 r = tf, a0 = t0, a1 = t1, a2 = t2;
+            if (e & LE_COMBINE) {
+                const bool swapped = (e & LE_SWAPPED) != 0;
+                const uint32_t op = (e >> LE_OP_SHIFT) & 3u;
+                --sp;
+                const F2 bf = vs[sp - 1][0], b0 = vs[sp - 1][1], b1 = vs[sp - 1][2], b2 = vs[sp - 1][3];
+                csg_select_gradient(op, swapped, tf.x, bf.x, t0.x, t1.x, t2.x, b0.x, b1.x, b2.x, r.x, a0.x, a1.x, a2.x);
+                csg_select_gradient(op, swapped, tf.y, bf.y, t0.y, t1.y, t2.y, b0.y, b1.y, b2.y, r.y, a0.y, a1.y, a2.y);
+            } else if (e & LE_NEGATE) {
+                r = neg2(r); a0 = neg2(a0); a1 = neg2(a1); a2 = neg2(a2);
+            }
+            tf = r;
+            back2(M, a0, a1, a2, t0, t1, t2);
+            if (e & LE_RESTORE) { --fp; cx = fs[fp][0]; cy = fs[fp][1]; cz = fs[fp][2]; }
+            continue;
+        }
+        const W4 hdr = prog.load4(pc);
+        const uint32_t word = hdr.x;
+        const uint32_t op = word & OP_MASK;
+        if (op == OP_XFORM) {
+            if (word & OP_FLAG_SAVE) { fs[fp][0] = cx; fs[fp][1] = cy; fs[fp][2] = cz; ++fp; }
+            F2 x, y, z;
+            apply2(M, cx, cy, cz, x, y, z);
+            cx = x; cy = y; cz = z;
+            continue;
+        }
+        F2 f, o0, o1, o2;
+        prim_value_gradient2(op, hdr, prog, pc + kInstrWords, M, sdf, cx, cy, cz, f, o0, o1, o2);
         if (sp > 0) { vs[sp - 1][0] = tf; vs[sp - 1][1] = t0; vs[sp - 1][2] = t1; vs[sp - 1][3] = t2; }
         tf = f; t0 = o0; t1 = o1; t2 = o2;
         ++sp;

@@ -357,8 +357,13 @@ __global__ void __launch_bounds__(kTileThreads) k_eval_tiles(GridDesc g, SdfGrid
                     cy[p] = yy;
                     cz[p] = zz;
                 }
-                if (SPEC) eval_values_list<4>(ConstProgram(), sdf, s_list, s_n_list, cx, cy, cz, f);
-                else eval_values<4>(ConstProgram(), sdf, AllLive(), cx, cy, cz, f);
+                if (SPEC) {      // two packed pairs (f32x2): half the floating-point instructions, the same bits
+                    F2 px[2] = {F2{cx[0], cx[1]}, F2{cx[2], cx[3]}}, py[2] = {splat(yy), splat(yy)}, pz[2] = {splat(zz), splat(zz)}, pf[2];
+                    eval_values_list2<2>(ConstProgram(), sdf, s_list, s_n_list, px, py, pz, pf);
+                    f[0] = pf[0].x; f[1] = pf[0].y; f[2] = pf[1].x; f[3] = pf[1].y;
+                } else {
+                    eval_values<4>(ConstProgram(), sdf, AllLive(), cx, cy, cz, f);
+                }
                 if (c_count_flops) add_flops(4ull * (SPEC ? list_flops(ConstProgram(), s_list, s_n_list, false) : program_flops(ConstProgram(), false)));
                 nib = 0;
 #pragma unroll

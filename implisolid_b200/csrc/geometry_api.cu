@@ -124,6 +124,7 @@ struct Context {
     PinnedBuffer h_normals;
     bool normals_valid = false, normals_host_valid = false;
     bool point_spec_on = false;             // the OB02 kernels may use K1's tile masks (c_point_spec describes the current program)
+    bool pair_kernels = true;               // "gpu":{"pair":1}: with point lists, two centroids per thread through the f32x2 interpreters
     std::vector<uint32_t> last_program;     // the shape program of the last build (lazy normals re-upload it)
     isd_progress_fn progress_fn = nullptr;
     void* progress_user = nullptr;
@@ -731,7 +732,11 @@ void vertex_resampling_step(float c) {
     g.d_cen.reserve((size_t)nf * 3 * sizeof(float) + 16);
     g.d_nrm.reserve((size_t)nf * 3 * sizeof(float) + 16);
     g.d_w.reserve((size_t)nf * sizeof(float) + 16);
-    ISD_TIMED(KT_CENTROID_GRAD, (g.point_spec_on ? k_centroid_gradients<true> : k_centroid_gradients<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(),
+    if (g.point_spec_on && g.pair_kernels)
+        ISD_TIMED(KT_CENTROID_GRAD, k_centroid_gradients_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf,
+                                                                                                                  g.d_cen.as<float>(), g.d_nrm.as<float>()));
+    else
+        ISD_TIMED(KT_CENTROID_GRAD, (g.point_spec_on ? k_centroid_gradients<true> : k_centroid_gradients<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(),
                                                                    g.d_nrm.as<float>()));
     ISD_TIMED(KT_FACE_WEIGHTS, k_face_weights<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.d_cen.as<float>(), g.d_nrm.as<float>(), g.d_fof.as<int>(), nf, c, g.d_w.as<float>()));
     ISD_TIMED(KT_RESAMPLE, k_resample<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(), g.d_w.as<float>(), g.d_cen.as<float>(),
@@ -894,11 +899,14 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     a.n = nf; a.speculative = 1;
     // the list of left-over centroids lives in the output array: k_project_finish only writes it once there are none left to list
     a.leftover = reinterpret_cast<int*>(g.d_proj.as<float>());
-    ISD_TIMED(KT_SEARCH, (g.point_spec_on ? k_project_search<true> : k_project_search<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a));
+    const bool pairs = g.point_spec_on && g.pair_kernels;
+    if (pairs) ISD_TIMED(KT_SEARCH, k_project_search_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, a));
+    else ISD_TIMED(KT_SEARCH, (g.point_spec_on ? k_project_search<true> : k_project_search<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a));
     // Phase B (direction types 2..6) is only needed when phase A left centroids over, which is rare and which only the device
     // knows: the rest of the step is launched right away and does nothing in that case (the kernels test the counter), so the
     // host does not have to wait here.
-    ISD_TIMED(KT_FINISH, (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a));
+    if (pairs) ISD_TIMED(KT_FINISH, k_project_finish_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, a));
+    else ISD_TIMED(KT_FINISH, (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a));
     ISD_CUDA(cudaEventRecord(g.ev[7], g.stream));
     if (enable_qem) {   // centroids_projection.cpp:1272-1310: the mesh only changes when QEM is on
         build_adjacency(false);
@@ -927,7 +935,8 @@ void projection_step(bool enable_qem, bool exact_reduce) {
         const int n_left = (int)hc->c[10];
         const unsigned left_blocks = blocks_for(n_left, 4) < (unsigned)g.sm_count * 16 ? blocks_for(n_left, 4) : (unsigned)g.sm_count * 16;
         ISD_TIMED(KT_LEFTOVERS, (g.point_spec_on ? k_project_leftovers<true> : k_project_leftovers<false>)<<<left_blocks, 128, 0, g.stream>>>(g.sdf, a, n_left));
-        ISD_TIMED(KT_FINISH, (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a));
+        if (pairs) ISD_TIMED(KT_FINISH, k_project_finish_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, a));
+        else ISD_TIMED(KT_FINISH, (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a));
         ISD_CUDA(cudaEventRecord(g.ev[7], g.stream));
         if (enable_qem) {
             ISD_TIMED(KT_QEM, k_qem<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(), g.d_proj.as<float>(),
@@ -1110,6 +1119,7 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     for (float& t : g.timings) t = 0;
     for (int64_t& c : g.counters) c = 0;
     g.launches = 0;
+    g.pair_kernels = s.pair != 0;
     g_kt.reset(s.kernel_times != 0);
     g_kt.start_counting(s.count_flops != 0);
     g.host_valid = false;

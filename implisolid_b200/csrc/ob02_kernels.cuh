@@ -645,6 +645,247 @@ __global__ void __launch_bounds__(128) k_project_finish(SdfGridView sdf, Project
     a.nrm_out[i * 3] = g0 / norm; a.nrm_out[i * 3 + 1] = g1 / norm; a.nrm_out[i * 3 + 2] = g2 / norm;
 }
 
+// ---- two centroids per thread (f32x2 packed pairs, csg_eval.cuh) ----------------------------------------------------------------
+// The evaluations above are bound by instruction issue, and more than half of what they issue is not floating point: list
+// entries, matrix loads, flag decoding, branches.  Faces 2t and 2t+1 of a marching-cubes mesh come from the same or from
+// neighbouring cubes, so their centroids — and the search and bisection points around them — almost always lie in one tile and
+// run the SAME instruction list: one thread takes both, one instruction stream serves two points (eval_values_list2<1>,
+// eval_value_gradient_list2), and the floating-point work itself goes through FMUL2/FADD2 register pairs.  Every lane performs
+// the scalar kernels' operations in their order: the results keep every bit (tests: test_pair_kernels_change_nothing).
+//
+// A tile's liveness mask was proven over the tile's box grown by one cell; in node-cell terms the box covers the tile's own
+// cells and the one layer of cells below them on each axis (classify_box, field_kernel.cuh).  Two points in different tiles can
+// therefore still share a list: that of the tile with the larger index on every axis, provided neither point's cell lies more
+// than one cell below it.  Otherwise the two points are evaluated one after the other by the scalar interpreters.
+__device__ __forceinline__ int pair_slot(const PointSpec& ps, float ax, float ay, float az, float bx, float by, float bz) {
+    if (!ps.enabled) return -1;
+    const float fax = (ax - ps.g.xmin) / ps.g.wx + 2.0f, fay = (ay - ps.g.ymin) / ps.g.wy + 2.0f, faz = (az - ps.g.zmin) / ps.g.wz + 2.0f;
+    const float fbx = (bx - ps.g.xmin) / ps.g.wx + 2.0f, fby = (by - ps.g.ymin) / ps.g.wy + 2.0f, fbz = (bz - ps.g.zmin) / ps.g.wz + 2.0f;
+    const float S = (float)ps.g.S, zlo = (float)ps.g.z0, zhi = (float)(ps.g.z0 + ps.g.nz);
+    if (!(fax >= 0.0f && fay >= 0.0f && faz >= zlo && fbx >= 0.0f && fby >= 0.0f && fbz >= zlo)) return -1;      // also rejects NaN
+    if (!(fax < S && fay < S && faz < zhi && fbx < S && fby < S && fbz < zhi)) return -1;
+    const int cax = (int)fax, cay = (int)fay, caz = (int)faz - ps.g.z0, cbx = (int)fbx, cby = (int)fby, cbz = (int)fbz - ps.g.z0;
+    const int tx = max(cax, cbx) >> 3, ty = max(cay, cby) >> 3, tz = max(caz, cbz) >> 3;
+    if (min(cax, cbx) < tx * 8 - 1 || min(cay, cby) < ty * 8 - 1 || min(caz, cbz) < tz * 8 - 1) return -1;
+    const int row = tz * ps.g.ty + ty;
+    if (!((__ldg(ps.tile_bits + (size_t)row * ps.TW + (tx >> 5)) >> (tx & 31)) & 1u)) return -1;
+    return (int)__ldg(ps.tile_slot + (size_t)row * ps.g.tx + tx);
+}
+// f at two points / f and grad f at two points (.x = first point, .y = second)
+__device__ __noinline__ F2 eval_f_pair(SdfGridView sdf, float ax, float ay, float az, float bx, float by, float bz) {
+    const int slot = pair_slot(c_point_spec, ax, ay, az, bx, by, bz);
+    if (slot >= 0) {
+        const uint32_t* rec = c_point_spec.lists + (size_t)slot * 2 * c_point_spec.stride;
+        F2 cx[1] = {F2{ax, bx}}, cy[1] = {F2{ay, by}}, cz[1] = {F2{az, bz}}, out[1];
+        eval_values_list2<1>(ConstProgram(), sdf, GlobalList{rec + 1}, (int)__ldg(rec), cx, cy, cz, out);
+        if (c_count_flops) add_flops(2ull * list_flops(ConstProgram(), GlobalList{rec + 1}, (int)__ldg(rec), false));
+        return out[0];
+    }
+    return F2{eval_f<true>(sdf, ax, ay, az), eval_f<true>(sdf, bx, by, bz)};
+}
+struct FG2 { F2 f, g0, g1, g2; };
+__device__ __noinline__ FG2 eval_fg_pair(SdfGridView sdf, float ax, float ay, float az, float bx, float by, float bz) {
+    FG2 r;
+    const int slot = pair_slot(c_point_spec, ax, ay, az, bx, by, bz);
+    if (slot >= 0) {
+        const uint32_t* rec = c_point_spec.lists + ((size_t)slot * 2 + 1) * c_point_spec.stride;
+        eval_value_gradient_list2(ConstProgram(), sdf, GlobalList{rec + 1}, (int)__ldg(rec), F2{ax, bx}, F2{ay, by}, F2{az, bz}, r.f, r.g0, r.g1, r.g2);
+        if (c_count_flops) add_flops(2ull * list_flops(ConstProgram(), GlobalList{rec + 1}, (int)__ldg(rec), true));
+        return r;
+    }
+    eval_fg<true>(sdf, ax, ay, az, r.f.x, r.g0.x, r.g1.x, r.g2.x);
+    eval_fg<true>(sdf, bx, by, bz, r.f.y, r.g0.y, r.g1.y, r.g2.y);
+    return r;
+}
+
+// k_centroid_gradients, faces 2t and 2t+1 per thread
+__global__ void __launch_bounds__(128) k_centroid_gradients_pair(SdfGridView sdf, const float* __restrict__ verts, const int* __restrict__ faces, int nf,
+                                                                 float* __restrict__ cen, float* __restrict__ nrm) {
+    const int fa = (blockIdx.x * 128 + threadIdx.x) * 2;
+    if (fa >= nf) return;
+    const bool two = fa + 1 < nf;
+    float c[2][3];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const int f = (k == 1 && two) ? fa + 1 : fa;      // an odd face count: the last thread evaluates its face twice
+        const int f0 = faces[f * 3], f1 = faces[f * 3 + 1], f2 = faces[f * 3 + 2];
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            c[k][d] = (verts[f0 * 3 + d] + verts[f1 * 3 + d] + verts[f2 * 3 + d]) / 3.0f;
+            cen[f * 3 + d] = c[k][d];
+        }
+    }
+    const FG2 r = eval_fg_pair(sdf, c[0][0], c[0][1], c[0][2], c[1][0], c[1][1], c[1][2]);
+    {
+        const float norm = norm2f(r.g0.x, r.g1.x, r.g2.x);
+        nrm[fa * 3] = r.g0.x / norm; nrm[fa * 3 + 1] = r.g1.x / norm; nrm[fa * 3 + 2] = r.g2.x / norm;
+    }
+    if (two) {
+        const float norm = norm2f(r.g0.y, r.g1.y, r.g2.y);
+        nrm[fa * 3 + 3] = r.g0.y / norm; nrm[fa * 3 + 4] = r.g1.y / norm; nrm[fa * 3 + 5] = r.g2.y / norm;
+    }
+}
+
+// k_project_search, centroids 2t and 2t+1 per thread.  Each centroid's result is the first sign change along its own sequence of
+// trial points (direction type 0 over the whole alpha list, then type 1 over the short list), exactly as in the scalar kernel;
+// the two sequences advance in lockstep and a lane that has finished a phase rides along on its partner's point.
+__global__ void __launch_bounds__(128) k_project_search_pair(SdfGridView sdf, ProjectArgs a) {
+    const int ia = (blockIdx.x * 128 + threadIdx.x) * 2;
+    if (ia >= a.n) return;
+    const bool two = ia + 1 < a.n;
+    const int idx[2] = {ia, two ? ia + 1 : ia};
+    const float edge = a.al->avg_edge;
+    const float* alphas = a.al->alpha;
+    const int n_alpha_full = a.al->n_full, n_alpha_short = a.al->n_short;
+    float c[2][3], d[2][3], s_c[2], best[2][4];
+    bool ok[2] = {false, false};
+    int type[2] = {0, 0};
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+#pragma unroll
+        for (int q = 0; q < 3; ++q) c[k][q] = a.cen[idx[k] * 3 + q];
+        best[k][0] = -10.0f; best[k][1] = -10.0f; best[k][2] = -10.0f; best[k][3] = 0.0f;
+    }
+    {
+        const FG2 r = eval_fg_pair(sdf, c[0][0], c[0][1], c[0][2], c[1][0], c[1][1], c[1][2]);
+        const float fc[2] = {r.f.x, r.f.y};
+        float g[2][3] = {{r.g0.x, r.g1.x, r.g2.x}, {r.g0.y, r.g1.y, r.g2.y}};
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            if (k == 0 || two) a.fc[idx[k]] = fc[k];
+            float norm = norm2f(g[k][0], g[k][1], g[k][2]);      // normalise_inplace(g, min_gradient_len)  normalise_inplace.hpp:19-58
+            norm = (norm < kMinGradientLen) ? 1.0f : norm;
+            const float factor = 1.0f / norm;
+            float g0 = g[k][0] * factor, g1 = g[k][1] * factor, g2 = g[k][2] * factor;
+            s_c[k] = sign_tol(fc[k]);
+            if (s_c[k] < 0.0f) { g0 = -g0; g1 = -g1; g2 = -g2; }
+            d[k][0] = -g0 * s_c[k]; d[k][1] = -g1 * s_c[k]; d[k][2] = -g2 * s_c[k];
+        }
+    }
+    for (int phase = 0; phase < 2; ++phase) {
+        if (phase == 1) {
+            if (ok[0] && ok[1]) break;
+#pragma unroll
+            for (int k = 0; k < 2; ++k)
+                if (!ok[k]) { facet_normal(a.verts, a.faces, idx[k], d[k][0], d[k][1], d[k][2]); type[k] = 1; }
+        }
+        const int n_alpha = phase == 0 ? n_alpha_full : n_alpha_short;
+        bool done[2] = {ok[0], ok[1]};      // finished with this phase
+        for (int ai = 0; ai < n_alpha && !(done[0] && done[1]); ++ai) {
+            const float cc = edge * __ldg(alphas + ai);          // (length_factor * alpha) * 4.0 / 4.0
+            float p[2][3];
+#pragma unroll
+            for (int k = 0; k < 2; ++k)
+#pragma unroll
+                for (int q = 0; q < 3; ++q) p[k][q] = c[k][q] + cc * d[k][q];
+            if (done[0]) { p[0][0] = p[1][0]; p[0][1] = p[1][1]; p[0][2] = p[1][2]; }
+            if (done[1]) { p[1][0] = p[0][0]; p[1][1] = p[0][1]; p[1][2] = p[0][2]; }
+            const F2 f = eval_f_pair(sdf, p[0][0], p[0][1], p[0][2], p[1][0], p[1][1], p[1][2]);
+            const float fv[2] = {f.x, f.y};
+#pragma unroll
+            for (int k = 0; k < 2; ++k)
+                if (!done[k] && sign_tol(fv[k]) * s_c[k] <= 0.0f) {
+                    best[k][0] = p[k][0]; best[k][1] = p[k][1]; best[k][2] = p[k][2]; best[k][3] = fv[k];
+                    ok[k] = true; done[k] = true;
+                }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        if (k == 1 && !two) break;
+        if (ok[k]) {
+            a.best[idx[k]] = make_float4(best[k][0], best[k][1], best[k][2], best[k][3]);
+            a.state[idx[k]] = 1;
+        } else {
+            a.state[idx[k]] = 2;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {   // left-overs: one atomic per warp hands out list slots
+        const bool left = !ok[k] && (k == 0 || two);
+        const unsigned m = __ballot_sync(__activemask(), left);
+        if (left) {
+            const int leader = __ffs(m) - 1, lane = threadIdx.x & 31;
+            unsigned long long base = 0ull;
+            if (lane == leader) base = atomicAdd(&a.counters->c[10], (unsigned long long)__popc(m));
+            base = __shfl_sync(m, base, leader);
+            a.leftover[base + __popc(m & ((1u << lane) - 1u))] = idx[k];
+        }
+        const bool mine = ok[k] && (k == 0 || two);
+        count_if(mine && type[k] == 0, &a.counters->c[0]);
+        count_if(mine && type[k] == 1, &a.counters->c[1]);
+    }
+}
+
+// k_project_finish, centroids 2t and 2t+1 per thread: the two bisections advance in lockstep, each with its own interval and
+// its own stopping test; a lane that has finished rides along on its partner's midpoint.
+__global__ void __launch_bounds__(128) k_project_finish_pair(SdfGridView sdf, ProjectArgs a) {
+    const int ia = (blockIdx.x * 128 + threadIdx.x) * 2;
+    if (ia >= a.n) return;
+    if (a.speculative && a.counters->c[10] != 0ull) return;
+    const bool two = ia + 1 < a.n;
+    const int idx[2] = {ia, two ? ia + 1 : ia};
+    float o[2][3], x1[2][3], x2[2][3];
+    bool zeros12[2], active[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const int i = idx[k];
+        const bool mine = k == 0 || two;
+        const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
+        const bool already = (a.state[i] & 1) != 0;
+        const float fc = a.fc[i];
+        float bx = cx, by = cy, bz = cz, f2 = fc;      // no candidate: the reference evaluates the centroid again
+        if (already) {
+            const float4 b = a.best[i];
+            bx = b.x; by = b.y; bz = b.z; f2 = b.w;    // f at the candidate, from the search that found it
+        }
+        count_if(mine && !already, &a.counters->c[7]);
+        const bool zeros2 = fabsf(f2) <= kRootTolerance;
+        const bool zeros1 = fabsf(fc) <= kRootTolerance;
+        if (zeros1) { bx = cx; by = cy; bz = cz; }
+        zeros12[k] = zeros2 || zeros1;
+        o[k][0] = cx; o[k][1] = cy; o[k][2] = cz;
+        active[k] = already && !zeros12[k];
+        count_if(mine && active[k], &a.counters->c[9]);
+        x1[k][0] = cx; x1[k][1] = cy; x1[k][2] = cz; x2[k][0] = bx; x2[k][1] = by; x2[k][2] = bz;
+        if (f2 < -kRootTolerance) { x1[k][0] = bx; x1[k][1] = by; x1[k][2] = bz; x2[k][0] = cx; x2[k][1] = cy; x2[k][2] = cz; }
+        if (zeros12[k]) { o[k][0] = bx; o[k][1] = by; o[k][2] = bz; }
+    }
+    for (int it = 1; active[0] || active[1]; ++it) {
+        float m[2][3];
+#pragma unroll
+        for (int k = 0; k < 2; ++k)
+#pragma unroll
+            for (int q = 0; q < 3; ++q) m[k][q] = (x1[k][q] + x2[k][q]) / 2.0f;
+        if (!active[0]) { m[0][0] = m[1][0]; m[0][1] = m[1][1]; m[0][2] = m[1][2]; }
+        if (!active[1]) { m[1][0] = m[0][0]; m[1][1] = m[0][1]; m[1][2] = m[0][2]; }
+        const F2 f = eval_f_pair(sdf, m[0][0], m[0][1], m[0][2], m[1][0], m[1][1], m[1][2]);
+        const float v[2] = {f.x, f.y};
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            if (!active[k]) continue;
+            if (fabsf(v[k]) <= kRootTolerance || it >= kBisectionMaxIter) {
+                if (fabsf(v[k]) > kRootTolerance && (k == 0 || two)) atomicAdd(&a.counters->c[8], 1ull);
+                o[k][0] = m[k][0]; o[k][1] = m[k][1]; o[k][2] = m[k][2];
+                active[k] = false;
+                continue;
+            }
+            if (v[k] > kRootTolerance) { x2[k][0] = m[k][0]; x2[k][1] = m[k][1]; x2[k][2] = m[k][2]; }
+            if (v[k] < -kRootTolerance) { x1[k][0] = m[k][0]; x1[k][1] = m[k][1]; x1[k][2] = m[k][2]; }
+        }
+    }
+    const FG2 r = eval_fg_pair(sdf, o[0][0], o[0][1], o[0][2], o[1][0], o[1][1], o[1][2]);
+    const float g[2][3] = {{r.g0.x, r.g1.x, r.g2.x}, {r.g0.y, r.g1.y, r.g2.y}};
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        if (k == 1 && !two) break;
+        const int i = idx[k];
+        a.out[i * 3] = o[k][0]; a.out[i * 3 + 1] = o[k][1]; a.out[i * 3 + 2] = o[k][2];
+        const float norm = norm2f(g[k][0], g[k][1], g[k][2]);
+        a.nrm_out[i * 3] = g[k][0] / norm; a.nrm_out[i * 3 + 1] = g[k][1] / norm; a.nrm_out[i * 3 + 2] = g[k][2] / norm;
+    }
+}
+
 // ---- K9 QEM vertex update ---------------------------------------------------------------------------------------------
 // Eigen's JacobiSVD of the symmetric PSD 3x3 (qem.hpp:397-405) as a cyclic Jacobi eigen-decomposition, operation for
 // operation the same as the oracle's restatement; eigenvalues sorted descending.

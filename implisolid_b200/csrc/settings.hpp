@@ -39,6 +39,8 @@ struct McSettings {
                           // (no mesh exchange); 0: gather the stitched mesh on every GPU and optimise it replicated
     int balance;          // z-slab runs: 1 (default) slab boundaries follow the surface (equal counts of surface tiles per GPU, from a
                           // bounds-only pass every rank repeats identically); 0: equal numbers of cube layers (SURVEY §8e's formula)
+    int pair;             // 1 (default): with per-tile point lists the OB02 kernels take two centroids per thread through the packed f32x2
+                          // interpreters (same bits); 0: one centroid per thread
     int point_spec;       // -1 (default): the OB02 kernels run per-tile instruction lists (from K1's liveness masks) at their evaluation
                           // points when the tree has at least 8 nodes; 0: never; 1: always (when masks exist)
     int normals;          // 1: per-vertex normals (-grad f/|grad f|) computed right after the last step (isd_get_n_ptr); 0: on first use
@@ -106,6 +108,7 @@ inline McSettings parse_mc_settings(const char* json) {
     s.halo = d.get_int("gpu.halo", -1);
     s.point_spec = d.get_int("gpu.point_spec", -1);
     s.balance = d.get_int("gpu.balance", 1);
+    s.pair = d.get_int("gpu.pair", 1);
     if (s.qem_enabled && !s.projection_enabled) {
         fprintf(stderr, "Invalid settings: QEM will not be applied if centroid projection is disabled\n");
         needs_abort = true;

@@ -232,3 +232,75 @@ extern "C" int emu_bounds_check(const char* shape_json, const float* boxes, int 
     }
     return p.num_nodes;
 }
+
+// ---- packed-pair interpreters (csg_eval.cuh F2): two points through one instruction list -------------------------------------
+// Points are taken four at a time; the lists come from the liveness mask interval bounds give for the box that holds the four
+// (what K1 does per tile, csg_bounds.cuh).  Packed value (1 and 2 pairs) and packed gradient results must carry the bits of the
+// scalar list interpreters and of the full tree.  Returns the number of mismatching results.
+extern "C" int emu_eval_packed(const char* shape_json, const float* pts, int n) {
+    ShapeOptions o;
+    ShapeCompiler c(o);
+    auto tree = c.parse(shape_json, false);
+    ShapeCompiler::Program p = c.compile(*tree);
+    if (!p.can_specialize) return -1;
+    HostProg prog{p.words.data()};
+    SdfGridView sdf{nullptr, 0, 0, 0, 0, 0, 0, 0};
+    SpecDesc spec{};
+    spec.enabled = 1; spec.num_nodes = p.num_nodes; spec.num_ops = (p.num_nodes - 1) / 2; spec.mask_words = (p.num_nodes + 31) / 32;
+    spec.topo = p.topo.data();
+    uint32_t decisions[kDecisionWords];
+    int bad = 0;
+    for (int i = 0; i + 3 < n; i += 4) {
+        uint32_t mask[kMaxSpecNodes / 32 + 1], scratch[kMaxSpecNodes / 32 + 1];
+        memset(mask, 0, sizeof(mask));
+        float ft[4], lo[3] = {1e30f, 1e30f, 1e30f}, hi[3] = {-1e30f, -1e30f, -1e30f};
+        for (int j = 0; j < 4; j++) {
+            ft[j] = eval_tree(c, *tree, pts[(i + j) * 3], pts[(i + j) * 3 + 1], pts[(i + j) * 3 + 2], false, scratch);
+            for (int d = 0; d < 3; d++) { lo[d] = std::min(lo[d], pts[(i + j) * 3 + d]); hi[d] = std::max(hi[d], pts[(i + j) * 3 + d]); }
+        }
+        program_bounds<true, false>(p.bounds.data(), 0.5f * (lo[0] + hi[0]), 0.5f * (lo[1] + hi[1]), 0.5f * (lo[2] + hi[2]), 0.5f * (hi[0] - lo[0]) * 1.001f + 1e-6f,
+                                    0.5f * (hi[1] - lo[1]) * 1.001f + 1e-6f, 0.5f * (hi[2] - lo[2]) * 1.001f + 1e-6f, decisions, NoMask());
+        write_live_mask(spec, decisions, mask);
+        std::vector<uint32_t> vlist, glist;
+        for (size_t k = 0; k + 3 < p.itab.size(); k += 4) {
+            const W4 it{p.itab[k], p.itab[k + 1], p.itab[k + 2], p.itab[k + 3]};
+            const uint32_t ev = spec_entry(it, MaskLive{mask}), eg = spec_entry_gradient(it, MaskLive{mask});
+            if (ev) vlist.push_back(ev);
+            if (eg) glist.push_back(eg);
+        }
+        const float* q = pts + i * 3;
+        // scalar references under the same lists
+        float fs[4], gs[4][3];
+        for (int j = 0; j < 4; j++) {
+            float x[1] = {q[j * 3]}, y[1] = {q[j * 3 + 1]}, z[1] = {q[j * 3 + 2]}, out[1];
+            eval_values_list<1>(prog, sdf, vlist.data(), (int)vlist.size(), x, y, z, out);
+            fs[j] = out[0];
+            float fg;
+            eval_value_gradient_list(prog, sdf, glist.data(), (int)glist.size(), q[j * 3], q[j * 3 + 1], q[j * 3 + 2], fg, gs[j][0], gs[j][1], gs[j][2]);
+            if (memcmp(&fg, &fs[j], 4) != 0 || memcmp(&fs[j], &ft[j], 4) != 0) bad++;
+        }
+        {   // two pairs at once (what k_eval_tiles runs)
+            F2 x[2] = {{q[0], q[3]}, {q[6], q[9]}}, y[2] = {{q[1], q[4]}, {q[7], q[10]}}, z[2] = {{q[2], q[5]}, {q[8], q[11]}}, out[2];
+            eval_values_list2<2>(prog, sdf, vlist.data(), (int)vlist.size(), x, y, z, out);
+            const float got[4] = {out[0].x, out[0].y, out[1].x, out[1].y};
+            if (memcmp(got, fs, 16) != 0) bad++;
+        }
+        for (int h = 0; h < 2; h++) {   // one pair: value and gradient (what the OB02 kernels run)
+            const float* a = q + h * 6;
+            F2 x[1] = {{a[0], a[3]}}, y[1] = {{a[1], a[4]}}, z[1] = {{a[2], a[5]}}, out[1];
+            eval_values_list2<1>(prog, sdf, vlist.data(), (int)vlist.size(), x, y, z, out);
+            if (memcmp(&out[0].x, &fs[h * 2], 4) != 0 || memcmp(&out[0].y, &fs[h * 2 + 1], 4) != 0) bad++;
+            F2 f, g0, g1, g2;
+            eval_value_gradient_list2(prog, sdf, glist.data(), (int)glist.size(), F2{a[0], a[3]}, F2{a[1], a[4]}, F2{a[2], a[5]}, f, g0, g1, g2);
+            const float ga[3] = {g0.x, g1.x, g2.x}, gb[3] = {g0.y, g1.y, g2.y};
+            if (memcmp(&f.x, &fs[h * 2], 4) != 0 || memcmp(&f.y, &fs[h * 2 + 1], 4) != 0) bad++;
+            if (memcmp(ga, gs[h * 2], 12) != 0 || memcmp(gb, gs[h * 2 + 1], 12) != 0) bad++;
+            // the value interpreter must also accept the gradient list
+            F2 x3[1] = {{a[0], a[3]}}, y3[1] = {{a[1], a[4]}}, z3[1] = {{a[2], a[5]}}, out3[1];
+            eval_values_list2<1>(prog, sdf, glist.data(), (int)glist.size(), x3, y3, z3, out3);
+            if (memcmp(&out3[0].x, &fs[h * 2], 4) != 0 || memcmp(&out3[0].y, &fs[h * 2 + 1], 4) != 0) bad++;
+        }
+    }
+    return bad;
+}
+

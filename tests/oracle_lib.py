@@ -242,6 +242,13 @@ class Emu:
                                          fm.ctypes.data_as(ctypes.c_void_p), live.ctypes.data_as(ctypes.c_void_p))
         return ft, fm, live, nodes
 
+    def eval_packed_mismatches(self, shape_json, pts):
+        """Packed-pair interpreters (two points per instruction stream) against the scalar list interpreters and the full tree;
+        returns the number of mismatching results (-1: the tree cannot be specialised)."""
+        p = np.ascontiguousarray(pts, dtype=np.float32).reshape(-1, 3)
+        self.lib.emu_eval_packed.restype = ctypes.c_int
+        return int(self.lib.emu_eval_packed(shape_json.encode(), p.ctypes.data_as(ctypes.c_void_p), p.shape[0]))
+
     def bounds_check(self, shape_json, boxes, samples=16, seed=1):
         """Interval bounds / liveness masks of csg_bounds.cuh against the exact interpreters on random points of every box
         (centre xyz, half extents xyz).  Returns (node count or -count when the tree cannot be specialised, dict of counters)."""

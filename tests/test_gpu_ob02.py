@@ -150,3 +150,27 @@ def test_random_trees_full_pipeline_vs_oracle(gpu_lib, oracle, seed, mode):
     assert gst["projection_failed"] == ost["projection_failed"]
     assert np.abs(gv - ov).max() <= _tol(1.0), np.abs(gv - ov).max()
     assert np.array_equal(gv.view(np.uint32), gv0.view(np.uint32))
+
+
+@pytest.mark.parametrize("shape,R,half", [(shapes.c4_deep_chain, 96, 1.0), (shapes.bushy_tree, 80, 0.9), (shapes.c3_metaballs, 64, 1.2),
+                                          (shapes.n1_medley, 72, 0.9), (shapes.c2_cube_minus_cylinder, 64, 0.8), (lambda: shapes.random_tree(9), 48, 1.0)],
+                         ids=["c4", "bushy", "c3", "medley", "c2", "random9"])
+def test_pair_kernels_change_nothing(gpu_lib, shape, R, half):
+    """With per-tile point lists the OB02 kernels take two centroids per thread through the packed f32x2 interpreters
+    ("gpu":{"pair":1}, the default): vertices, projected centroids, their normals and every counter must keep the bits of the
+    one-centroid-per-thread kernels (pair 0), over two OB02 repeats."""
+    sj = shape()
+    out = []
+    for pair in (0, 1):
+        gpu_lib.build_geometry(sj, shapes.mc_settings(R, half, iters=2, c=1.0, projection=1, qem=1, repeats=2, point_spec=1, pair=pair))
+        v, f = gpu_lib.get_v(), gpu_lib.get_f()
+        c, n = gpu_lib.projected_centroids()
+        st = gpu_lib.last_counters()
+        gpu_lib.finish_geometry()
+        out.append((v, f, c, n, st))
+    (v0, f0, c0, n0, s0), (v1, f1, c1, n1, s1) = out
+    assert np.array_equal(f0, f1)
+    assert np.array_equal(v0.view(np.uint32), v1.view(np.uint32))
+    assert np.array_equal(c0.view(np.uint32), c1.view(np.uint32)) and np.array_equal(n0.view(np.uint32), n1.view(np.uint32))
+    for k in ("projection_by_type", "projection_failed", "bisection_capped", "bisected"):
+        assert s0[k] == s1[k], (k, s0[k], s1[k])

@@ -106,3 +106,22 @@ def test_interval_bounds_and_tile_masks_are_sound(emu, name):
         assert st["bounds_violations"] == 0 and st["value_mismatches"] == 0 and st["gradient_mismatches"] == 0, st
         assert st["looser_second_level"] == 0, st
         assert st["live_nodes"] >= 300          # the root is always live
+
+
+@pytest.mark.parametrize("name", SHAPES + ["random_%d" % s for s in range(6)] + ["randomall_%d" % s for s in (322, 335)])
+def test_packed_pair_interpreters_keep_every_bit(emu, name):
+    """The f32x2 interpreters (csg_eval.cuh: eval_values_list2, eval_value_gradient_list2) run two points through one instruction
+    list; on the host a pair is two plain floats, so this holds their operation ORDER to the scalar interpreters' and the full
+    tree's, for nearby point pairs (the GPU case: neighbouring nodes / centroids) and for unrelated ones."""
+    if name.startswith("randomall_"):
+        sj = shapes.random_tree(int(name.split("_")[1]), all_prims=True)
+    elif name.startswith("random_"):
+        sj = shapes.random_tree(int(name.split("_")[1]))
+    else:
+        sj = getattr(shapes, name)()
+    rng = np.random.default_rng(5)
+    base = rng.uniform(-1.1, 1.1, (1500, 1, 3))
+    near = (base + rng.normal(0, 0.004, (1500, 4, 3))).reshape(-1, 3)
+    far = rng.uniform(-1.2, 1.2, (2000, 3))
+    pts = np.concatenate([near, far]).astype(np.float32)
+    assert emu.eval_packed_mismatches(sj, pts) == 0
