@@ -232,25 +232,27 @@ def digest(a):
 def match_window_to_mesh(np, wv, wf, n_tail, gv, gf):
     """A marching-cubes mesh of a window of cube layers (oracle) against the whole grid's mesh (GPU).  The last `n_tail` faces of
     the window (its top layer's: scan order is z-major) only use vertices whose owner cube — the first cube of the scan to see
-    the edge, which is the one whose arithmetic places the vertex — lies inside the window, so those vertices must exist bit for
-    bit in the whole mesh, and the faces, renamed through that match, must be one contiguous run of the whole mesh's faces."""
+    the edge, which is the one whose arithmetic places the vertex — lies inside the window.  Those faces must therefore appear
+    in the whole mesh as ONE contiguous run with the same corner positions bit for bit, in the same corner order, and the
+    window's vertex numbers must map one-to-one onto the whole mesh's along that run (the same topology).  Faces are matched
+    by their nine coordinates, not vertex by vertex: a vertex that lands exactly on a grid node (f = 0 there) shares its position
+    with the vertices of the other cut edges at that node."""
     if n_tail == 0:
         return True
-    tail = wf[wf.shape[0] - n_tail:]
-    used = np.unique(tail)
-    key = lambda v: np.ascontiguousarray(v).view(np.dtype((np.void, 12))).ravel()
-    gk, wk = key(gv), key(wv[used])
-    order = np.argsort(gk, kind="stable")
-    pos = np.searchsorted(gk[order], wk)
-    pos[pos >= gk.shape[0]] = 0
-    idx = order[pos]
-    if not (gk[idx] == wk).all():
-        return False
-    rename = np.full(wv.shape[0], -1, dtype=np.int64)
-    rename[used] = idx
-    renamed = rename[tail].astype(np.int32)
-    for s in np.flatnonzero((gf == renamed[0]).all(axis=1)):
-        if s + n_tail <= gf.shape[0] and np.array_equal(gf[s:s + n_tail], renamed):
+    tail = np.ascontiguousarray(wf[wf.shape[0] - n_tail:])
+    wkeys = np.ascontiguousarray(wv[tail].reshape(n_tail, 9)).view(np.dtype((np.void, 36))).ravel()
+    # candidate starts: faces of the whole mesh whose first corner has the first tail face's first corner position
+    first = np.ascontiguousarray(wv[tail[0, 0]]).view(np.uint32)
+    g0 = gv.view(np.uint32)[gf[:, 0]]
+    for s in np.flatnonzero((g0 == first).all(axis=1)):
+        if s + n_tail > gf.shape[0]:
+            continue
+        run = gf[s:s + n_tail]
+        gkeys = np.ascontiguousarray(gv[run].reshape(n_tail, 9)).view(np.dtype((np.void, 36))).ravel()
+        if not (gkeys == wkeys).all():
+            continue
+        pairs = np.unique(np.stack([tail.ravel().astype(np.int64), run.ravel().astype(np.int64)], axis=1), axis=0)
+        if np.unique(pairs[:, 0]).shape[0] == pairs.shape[0] and np.unique(pairs[:, 1]).shape[0] == pairs.shape[0]:
             return True
     return False
 
@@ -500,8 +502,9 @@ def main():
     dominant_kernel = max(kernels, key=lambda k: kernels[k][0]) if kernels else None
     roofline = dict(per_kernel.get(dominant_kernel, {}))
     roofline["kernel"] = dominant_kernel
-    roofline["peak_source"] = ("tools/fp32_peak on this GPU: packed f32x2 FMUL2+FADD2, separately rounded (the exact mode's ceiling; scalar FMUL+FADD %.1f, "
-                               "FFMA %.1f TFLOP/s)" % (fp["fmul_fadd_tflops"], fp["ffma_tflops"])) if roofline.get("bound") == "fp32" and fp else hbm_src
+    roofline["peak_source"] = ("tools/fp32_peak on this GPU: separately rounded multiply and add on register pairs (FFMA2(a,b,-0) + FADD2), the exact mode's "
+                               "ceiling; the scalar forms give %.1f, and %.1f TFLOP/s of fused FFMA are out of reach without contraction. Packed instructions "
+                               "issue at half rate: they save issue slots, not FP32-pipe cycles" % (fp["fmul_fadd_tflops"], fp["ffma_tflops"])) if roofline.get("bound") == "fp32" and fp else hbm_src
     roofline["traffic_source"] = traffic_src
     roofline["how"] = ("achieved = FP32 operations the kernel's CSG evaluations execute in one step (counted by an instrumented untimed step: the per-tile "
                        "instruction lists each evaluation really runs, mul and add separately) / the kernel's mean time per step inside the timed region"

@@ -213,7 +213,14 @@ __global__ void __launch_bounds__(64) k_tile_bounds(GridDesc g, const uint32_t* 
     }
 }
 
-constexpr int kTileThreads = 128;
+#ifndef ISD_TILE_NODES
+#define ISD_TILE_NODES 4
+#endif
+constexpr int kNodesPerThread = ISD_TILE_NODES;      // 4 or 8 x-adjacent nodes per thread (2 or 4 packed pairs)
+constexpr int kTileThreads = 512 / kNodesPerThread;
+#ifndef ISD_EVAL_MINBLOCKS
+#define ISD_EVAL_MINBLOCKS 1
+#endif
 
 struct TileLive {             // liveness mask of the tile being evaluated (uniform across the block)
     const uint32_t* mask;
@@ -293,7 +300,7 @@ __global__ void __launch_bounds__(128) k_build_point_lists(const unsigned* __res
 // (spec_entry, one instruction per thread, order kept by ballot ranks) in shared memory; eval_values_list then has no
 // liveness tests, no dead-node jumps and no operand bookkeeping left.
 template <bool SPEC>
-__global__ void __launch_bounds__(kTileThreads) k_eval_tiles(GridDesc g, SdfGridView sdf, const unsigned* __restrict__ list,
+__global__ void __launch_bounds__(kTileThreads, ISD_EVAL_MINBLOCKS) k_eval_tiles(GridDesc g, SdfGridView sdf, const unsigned* __restrict__ list,
                                                             const unsigned* __restrict__ list_count, const uint32_t* __restrict__ masks,
                                                             int mask_words, const uint4* __restrict__ itab, int n_instr,
                                                             float* __restrict__ field, uint32_t* __restrict__ signs) {
@@ -302,7 +309,8 @@ __global__ void __launch_bounds__(kTileThreads) k_eval_tiles(GridDesc g, SdfGrid
     __shared__ int s_n_list;
     const unsigned n = list_count[0];
     unsigned* next_item = const_cast<unsigned*>(list_count) + 1;      // dynamic queue: specialised tiles differ a lot in cost
-    const int q = threadIdx.x & 1, row = threadIdx.x >> 1;
+    constexpr int NPT = kNodesPerThread, QPR = 8 / NPT;      // threads per row of 8 nodes
+    const int q = threadIdx.x % QPR, row = threadIdx.x / QPR;
     uint8_t* sb = reinterpret_cast<uint8_t*>(signs);
     __shared__ unsigned s_item;
     for (;;) {
@@ -338,45 +346,59 @@ __global__ void __launch_bounds__(kTileThreads) k_eval_tiles(GridDesc g, SdfGrid
         const int tx = t % g.tx;
         const int r = t / g.tx;
         const int ty = r % g.ty, tzl = r / g.ty;
-        const int x0 = tx * 8 + q * 4, y = ty * 8 + (row & 7), zl = tzl * 8 + (row >> 3);
+        const int x0 = tx * 8 + q * NPT, y = ty * 8 + (row & 7), zl = tzl * 8 + (row >> 3);
         const int z = g.z0 + zl;
-        unsigned nib = 0xfu;
+        unsigned nib = (1u << NPT) - 1u;
         const bool in_grid = (y < g.S) && (zl < g.nz) && (x0 < g.pitch);
         if (in_grid) {
             float4* dst = reinterpret_cast<float4*>(field + (long long)zl * g.plane + (long long)y * g.pitch + x0);
             const bool row_sealed = sealed_index(y, g.S) || sealed_index(z, g.S);
-            if (row_sealed || x0 + 3 <= 1 || x0 >= g.S - 2) {
-                *dst = make_float4(kExteriorValue, kExteriorValue, kExteriorValue, kExteriorValue);
+            if (row_sealed || x0 + NPT - 1 <= 1 || x0 >= g.S - 2) {
+#pragma unroll
+                for (int h = 0; h < NPT / 4; ++h) dst[h] = make_float4(kExteriorValue, kExteriorValue, kExteriorValue, kExteriorValue);
             } else {
-                float cx[4], cy[4], cz[4], f[4];
+                float f[NPT];
                 const float yy = node_coord(y, g.wy, g.ymin, g.two_wy);
                 const float zz = node_coord(z, g.wz, g.zmin, g.two_wz);
+                if (SPEC) {      // packed pairs (f32x2): half the floating-point instructions, the same bits
+                    F2 px[NPT / 2], py[NPT / 2], pz[NPT / 2], pf[NPT / 2];
 #pragma unroll
-                for (int p = 0; p < 4; ++p) {
-                    cx[p] = node_coord(x0 + p, g.wx, g.xmin, g.two_wx);
-                    cy[p] = yy;
-                    cz[p] = zz;
-                }
-                if (SPEC) {      // two packed pairs (f32x2): half the floating-point instructions, the same bits
-                    F2 px[2] = {F2{cx[0], cx[1]}, F2{cx[2], cx[3]}}, py[2] = {splat(yy), splat(yy)}, pz[2] = {splat(zz), splat(zz)}, pf[2];
-                    eval_values_list2<2>(ConstProgram(), sdf, s_list, s_n_list, px, py, pz, pf);
-                    f[0] = pf[0].x; f[1] = pf[0].y; f[2] = pf[1].x; f[3] = pf[1].y;
+                    for (int p = 0; p < NPT / 2; ++p) {
+                        px[p] = F2{node_coord(x0 + 2 * p, g.wx, g.xmin, g.two_wx), node_coord(x0 + 2 * p + 1, g.wx, g.xmin, g.two_wx)};
+                        py[p] = splat(yy); pz[p] = splat(zz);
+                    }
+                    eval_values_list2<NPT / 2>(ConstProgram(), sdf, s_list, s_n_list, px, py, pz, pf);
+#pragma unroll
+                    for (int p = 0; p < NPT / 2; ++p) { f[2 * p] = pf[p].x; f[2 * p + 1] = pf[p].y; }
+                    if (c_count_flops) add_flops((unsigned long long)NPT * list_flops(ConstProgram(), s_list, s_n_list, false));
                 } else {
-                    eval_values<4>(ConstProgram(), sdf, AllLive(), cx, cy, cz, f);
+#pragma unroll
+                    for (int h = 0; h < NPT / 4; ++h) {
+                        float cx[4], cy[4], cz[4], f4[4];
+#pragma unroll
+                        for (int p = 0; p < 4; ++p) { cx[p] = node_coord(x0 + 4 * h + p, g.wx, g.xmin, g.two_wx); cy[p] = yy; cz[p] = zz; }
+                        eval_values<4>(ConstProgram(), sdf, AllLive(), cx, cy, cz, f4);
+#pragma unroll
+                        for (int p = 0; p < 4; ++p) f[4 * h + p] = f4[p];
+                    }
+                    if (c_count_flops) add_flops((unsigned long long)NPT * program_flops(ConstProgram(), false));
                 }
-                if (c_count_flops) add_flops(4ull * (SPEC ? list_flops(ConstProgram(), s_list, s_n_list, false) : program_flops(ConstProgram(), false)));
                 nib = 0;
 #pragma unroll
-                for (int p = 0; p < 4; ++p) {
+                for (int p = 0; p < NPT; ++p) {
                     if (sealed_index(x0 + p, g.S)) f[p] = kExteriorValue;
                     nib |= (f[p] < 0.0f ? 1u : 0u) << p;
                 }
-                *dst = make_float4(f[0], f[1], f[2], f[3]);
+#pragma unroll
+                for (int h = 0; h < NPT / 4; ++h) dst[h] = make_float4(f[4 * h], f[4 * h + 1], f[4 * h + 2], f[4 * h + 3]);
             }
         }
-        // two quads -> one sign byte (lanes 2j, 2j+1 share a row)
-        const unsigned other = __shfl_xor_sync(0xffffffffu, nib, 1);
-        if (q == 0 && y < g.S && zl < g.nz) sb[((long long)zl * g.S + y) * (g.SW * 4) + tx] = (uint8_t)(nib | (other << 4));
+        if (NPT == 4) {      // two quads -> one sign byte (lanes 2j, 2j+1 share a row)
+            const unsigned other = __shfl_xor_sync(0xffffffffu, nib, 1);
+            if (q == 0 && y < g.S && zl < g.nz) sb[((long long)zl * g.S + y) * (g.SW * 4) + tx] = (uint8_t)(nib | (other << 4));
+        } else {
+            if (y < g.S && zl < g.nz) sb[((long long)zl * g.S + y) * (g.SW * 4) + tx] = (uint8_t)nib;
+        }
     }
 }
 

@@ -113,7 +113,7 @@ struct Context {
 
     // OB02 scratch
     DeviceBuffer d_cen, d_nrm, d_deg, d_uoff, d_uitems, d_cursor, d_fof, d_w, d_len3, d_best, d_fc, d_state, d_proj, d_pnrm, d_point_lists,
-        d_noise, d_scal, d_counters, d_upartials;
+        d_noise, d_scal, d_counters, d_upartials, d_bis;
     bool adjacency_valid = false, fof_valid_ = false;
     float average_edge = 0.f;
     bool alpha_ticket_zeroed = false;
@@ -124,6 +124,7 @@ struct Context {
     PinnedBuffer h_normals;
     bool normals_valid = false, normals_host_valid = false;
     bool point_spec_on = false;             // the OB02 kernels may use K1's tile masks (c_point_spec describes the current program)
+    bool finish_split = true;               // "gpu":{"finish_split":1}: the pair path's projection finish as classify / bisect-the-list / gradients
     bool pair_kernels = true;               // "gpu":{"pair":1}: with point lists, two centroids per thread through the f32x2 interpreters
     std::vector<uint32_t> last_program;     // the shape program of the last build (lazy normals re-upload it)
     isd_progress_fn progress_fn = nullptr;
@@ -153,7 +154,8 @@ struct Context {
     // halo mode (sharded OB02 without a mesh exchange): the GPU holds a LOCAL mesh of its slab plus `halo` recomputed cube
     // layers on either side, numbered from 0 in scan order (ghost-layer vertices first, never written); the slab's own part is
     // the contiguous range [own_v0, own_v1) x [own_f0, own_f1) and global index = local index + (global offset - own_*0).
-    bool halo_mode = false, halo_pending = false;
+    bool halo_mode = false, halo_pending = false, halo_gather_enqueued = false;
+    long long halo_counts[2] = {0, 0};       // this slab's {nv, nf}, what it contributes to the gather
     int halo = 0, own_zb = 0, own_ze = 0;
     long long own_v0 = 0, own_v1 = 0, own_f0 = 0, own_f1 = 0;
     unsigned long long emu_edge_total = 0;      // emulated ranks: the global fixed-point edge sum and face count
@@ -405,6 +407,23 @@ void setup_grid(const McSettings& s, const ShapeCompiler::Program& prog) {
     g.S = S;
 }
 
+// The one collective of a z-slab step: every rank contributes {nv, nf, fixed-point edge-length sum of its own faces} (24 bytes);
+// afterwards d_gather holds the triples of all ranks in rank order and their copy is on its way to h_gather + 3.  `edge_sum`
+// (device, may be null = 0) is read in the stream, so the call can follow the kernel that produces it without a host wait.
+__global__ void k_pack_slab_triple(long long* __restrict__ dst, long long nv, long long nf, const unsigned long long* __restrict__ edge_sum) {
+    dst[0] = nv; dst[1] = nf; dst[2] = edge_sum ? (long long)*edge_sum : 0ll;
+}
+void enqueue_slab_gather(const unsigned long long* d_edge_sum) {
+    g.d_gather.reserve(((size_t)g.world + 1) * 3 * sizeof(int64_t) + 64);
+    int64_t* dg = g.d_gather.as<int64_t>();
+    int64_t* hs = g.h_gather.as<int64_t>();
+    k_pack_slab_triple<<<1, 1, 0, g.stream>>>(reinterpret_cast<long long*>(dg + 3 * g.world), g.halo_counts[0], g.halo_counts[1], d_edge_sum);
+    ISD_LAUNCH_CHECK();
+    g.nccl.check(g.nccl.AllGather(dg + 3 * g.world, dg, 3, kNcclInt64, g.comm, g.stream), "ncclAllGather");
+    ISD_CUDA(cudaMemcpyAsync(hs + 3, dg, (size_t)g.world * 3 * sizeof(int64_t), cudaMemcpyDeviceToHost, g.stream));
+    g.halo_gather_enqueued = true;
+}
+
 void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog) {
     setup_grid(s, prog);
     const GridDesc& gd = g.grid;
@@ -575,31 +594,22 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
             if (g.halo_mode) { gnv = -1; gnf = g.emu_gnf; }
             voff = g.emu_voff; foff = g.emu_foff;
         } else if (g.halo_mode) {
-            // the collective is only needed when the slab is exported (global indices) and by the mean edge length: it is
-            // enqueued here and read back at the end of the step, so nothing waits for the slowest rank in between
-            g.d_gather.reserve((size_t)g.world * 2 * sizeof(int64_t) + 64);
-            int64_t* dg = g.d_gather.as<int64_t>();
-            int64_t* hs = g.h_gather.as<int64_t>();
-            hs[0] = nv; hs[1] = nf;
-            ISD_CUDA(cudaMemcpyAsync(dg + 2 * g.world, hs, 2 * sizeof(int64_t), cudaMemcpyHostToDevice, g.stream));
-            g.nccl.check(g.nccl.AllGather(dg + 2 * g.world, dg, 2, kNcclInt64, g.comm, g.stream), "ncclAllGather");
-            ISD_CUDA(cudaMemcpyAsync(hs + 2, dg, (size_t)g.world * 2 * sizeof(int64_t), cudaMemcpyDeviceToHost, g.stream));
+            // Nothing is exchanged here.  The slab's {nv, nf} travel with its edge-length sum in the ONE collective of the step (after
+            // k_face_prepare, projection_step) — or, when no projection runs, in a gather of their own when the slab is exported.
+            g.halo_counts[0] = nv; g.halo_counts[1] = nf;
+            g.halo_gather_enqueued = false;
             g.halo_pending = true;
             gnv = -1; gnf = -1;
         } else {
             // the one collective of the path: {nv, nf} of every slab (16 bytes per rank)
-            g.d_gather.reserve((size_t)g.world * 2 * sizeof(int64_t) + 64);
-            int64_t* dg = g.d_gather.as<int64_t>();
-            int64_t* hs = g.h_gather.as<int64_t>();
-            hs[0] = nv; hs[1] = nf;
-            ISD_CUDA(cudaMemcpyAsync(dg + 2 * g.world, hs, 2 * sizeof(int64_t), cudaMemcpyHostToDevice, g.stream));
-            g.nccl.check(g.nccl.AllGather(dg + 2 * g.world, dg, 2, kNcclInt64, g.comm, g.stream), "ncclAllGather");
-            ISD_CUDA(cudaMemcpyAsync(hs + 2, dg, (size_t)g.world * 2 * sizeof(int64_t), cudaMemcpyDeviceToHost, g.stream));
+            g.halo_counts[0] = nv; g.halo_counts[1] = nf;
+            enqueue_slab_gather(nullptr);
             ISD_CUDA(cudaStreamSynchronize(g.stream));
+            const int64_t* hs = g.h_gather.as<int64_t>();
             gnv = 0; gnf = 0;
             for (int r = 0; r < g.world; ++r) {
                 if (r == g.rank) { voff = gnv; foff = gnf; }
-                gnv += hs[2 + 2 * r]; gnf += hs[3 + 2 * r];
+                gnv += hs[3 + 3 * r]; gnf += hs[4 + 3 * r];
             }
         }
     }
@@ -659,7 +669,7 @@ void gather_mesh() {
     g.nccl.check(g.nccl.GroupStart(), "ncclGroupStart");
     long long vo = 0, fo = 0;
     for (int r = 0; r < g.world; ++r) {      // in place: every rank's slab already sits at its global offset
-        const long long rv = hs[2 + 2 * r], rf = hs[3 + 2 * r];
+        const long long rv = hs[3 + 3 * r], rf = hs[4 + 3 * r];
         float* pv = g.d_verts.as<float>() + vo * 3;
         int* pf = g.d_faces.as<int>() + fo * 3;
         if (rv > 0) g.nccl.check(g.nccl.Broadcast(pv, pv, (size_t)rv * 3, kNcclFloat32, r, g.comm, g.stream), "ncclBroadcast");
@@ -786,12 +796,13 @@ void resolve_halo_offsets() {
     if (!g.halo_mode) return;
     if (g.emulate) { g.slab[2] = g.emu_voff; g.slab[3] = g.emu_foff; g.slab[6] = -1; g.slab[7] = g.emu_gnf; return; }
     if (!g.halo_pending) return;
+    if (!g.halo_gather_enqueued) enqueue_slab_gather(nullptr);      // no projection in this build: the counts travel alone
     ISD_CUDA(cudaStreamSynchronize(g.stream));
     const int64_t* hs = g.h_gather.as<int64_t>();
     long long voff = 0, foff = 0, gnv = 0, gnf = 0;
     for (int r = 0; r < g.world; ++r) {
         if (r == g.rank) { voff = gnv; foff = gnf; }
-        gnv += hs[2 + 2 * r]; gnf += hs[3 + 2 * r];
+        gnv += hs[3 + 3 * r]; gnf += hs[4 + 3 * r];
     }
     g.halo_pending = false;
     if (gnv >= (1ll << 31) || gnf >= (1ll << 31)) {
@@ -828,14 +839,10 @@ const float* noise_stream(size_t count) {
 void projection_step(bool enable_qem, bool exact_reduce) {
     const int nv = (int)g.nv, nf = (int)g.nf;
     if (nf == 0) {
-        // A slab (plus halo) without faces still owes the other ranks its term of the mean-edge all-reduce: every rank enqueues
-        // the collective once per projection step, whatever it holds.
+        // A slab (plus halo) without faces still owes the other ranks its triple: every rank enqueues the collective once per
+        // projection step, whatever it holds.
         if (g.halo_mode && !g.emulate && g.world > 1) {
-            g.d_scal.reserve(sizeof(AlphaList) + 64);
-            AlphaList* al0 = g.d_scal.as<AlphaList>();
-            ISD_CUDA(cudaMemsetAsync(al0, 0, sizeof(AlphaList), g.stream));
-            g.alpha_ticket_zeroed = true;
-            g.nccl.check(g.nccl.AllReduce(&al0->edge_sum, &al0->edge_total, 1, kNcclUint64, kNcclSum, g.comm, g.stream), "ncclAllReduce");
+            enqueue_slab_gather(nullptr);
         }
         return;
     }
@@ -870,8 +877,8 @@ void projection_step(bool enable_qem, bool exact_reduce) {
             ISD_CUDA(cudaMemcpyAsync(&d_al->edge_total, g.h_small.as<char>() + 3208, sizeof(unsigned long long), cudaMemcpyHostToDevice, g.stream));
             k_alpha_from_sum<<<1, 1, 0, g.stream>>>(d_al, &d_al->edge_total, nullptr, g.world, g.emu_gnf);
         } else {
-            g.nccl.check(g.nccl.AllReduce(&d_al->edge_sum, &d_al->edge_total, 1, kNcclUint64, kNcclSum, g.comm, g.stream), "ncclAllReduce");
-            k_alpha_from_sum<<<1, 1, 0, g.stream>>>(d_al, &d_al->edge_total, reinterpret_cast<const long long*>(g.d_gather.as<int64_t>()), g.world, 0);
+            enqueue_slab_gather(&d_al->edge_sum);
+            k_alpha_from_gather<<<1, 1, 0, g.stream>>>(d_al, reinterpret_cast<const long long*>(g.d_gather.as<int64_t>()), g.world);
         }
         ISD_LAUNCH_CHECK();
     } else {
@@ -905,8 +912,24 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     // Phase B (direction types 2..6) is only needed when phase A left centroids over, which is rare and which only the device
     // knows: the rest of the step is launched right away and does nothing in that case (the kernels test the counter), so the
     // host does not have to wait here.
-    if (pairs) ISD_TIMED(KT_FINISH, k_project_finish_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, a));
-    else ISD_TIMED(KT_FINISH, (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a));
+    // k_project_finish: one kernel, or (pair path) classify -> bisect the listed third of the centroids -> gradients of all
+    g.d_bis.reserve((size_t)nf * sizeof(int) + 64);
+    FinishList fl{g.d_bis.as<int>() + 16, reinterpret_cast<unsigned long long*>(g.d_bis.ptr)};
+    auto finish_pass = [&](const ProjectArgs& pa) {
+        if (pairs && g.finish_split) {
+            ISD_CUDA(cudaMemsetAsync(fl.count, 0, sizeof(unsigned long long), g.stream));
+            ISD_TIMED(KT_FINISH, k_finish_classify<<<blocks_for(nf, 256), 256, 0, g.stream>>>(pa, fl));
+            const unsigned want = blocks_for((nf + 1) / 2, 128), cap = (unsigned)g.sm_count * 16u;
+            ISD_TIMED(KT_FINISH, k_finish_bisect_pair<<<want < cap ? want : cap, 128, 0, g.stream>>>(g.sdf, pa, fl));
+            ISD_TIMED(KT_FINISH, k_unit_gradients_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, pa.out, nf, pa.nrm_out,
+                                                                                                            pa.speculative ? pa.counters : nullptr));
+        } else if (pairs) {
+            ISD_TIMED(KT_FINISH, k_project_finish_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, pa));
+        } else {
+            ISD_TIMED(KT_FINISH, (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, pa));
+        }
+    };
+    finish_pass(a);
     ISD_CUDA(cudaEventRecord(g.ev[7], g.stream));
     if (enable_qem) {   // centroids_projection.cpp:1272-1310: the mesh only changes when QEM is on
         build_adjacency(false);
@@ -935,8 +958,7 @@ void projection_step(bool enable_qem, bool exact_reduce) {
         const int n_left = (int)hc->c[10];
         const unsigned left_blocks = blocks_for(n_left, 4) < (unsigned)g.sm_count * 16 ? blocks_for(n_left, 4) : (unsigned)g.sm_count * 16;
         ISD_TIMED(KT_LEFTOVERS, (g.point_spec_on ? k_project_leftovers<true> : k_project_leftovers<false>)<<<left_blocks, 128, 0, g.stream>>>(g.sdf, a, n_left));
-        if (pairs) ISD_TIMED(KT_FINISH, k_project_finish_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, a));
-        else ISD_TIMED(KT_FINISH, (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a));
+        finish_pass(a);
         ISD_CUDA(cudaEventRecord(g.ev[7], g.stream));
         if (enable_qem) {
             ISD_TIMED(KT_QEM, k_qem<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(), g.d_proj.as<float>(),
@@ -1120,6 +1142,7 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     for (int64_t& c : g.counters) c = 0;
     g.launches = 0;
     g.pair_kernels = s.pair != 0;
+    g.finish_split = s.finish_split != 0;
     g_kt.reset(s.kernel_times != 0);
     g_kt.start_counting(s.count_flops != 0);
     g.host_valid = false;
@@ -1517,7 +1540,7 @@ int isd_dist_init(int rank, int world, const uint8_t* id128) {
         fprintf(stderr, "implisolid_b200: isd_dist_init: rank %d / world %d out of range\n", rank, world);
         return 1;
     }
-    g.h_gather.reserve((size_t)(2 + 2 * world) * sizeof(int64_t));
+    g.h_gather.reserve((size_t)(3 + 3 * world) * sizeof(int64_t));
     if (!g.nccl.load()) abort();
     NcclApi::unique_id id;
     memcpy(&id, id128, 128);

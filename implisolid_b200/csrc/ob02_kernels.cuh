@@ -416,6 +416,17 @@ __global__ void k_alpha_from_sum(AlphaList* __restrict__ al, const unsigned long
     al->avg_edge = avg;
     make_alpha_list(avg, 0.001f, avg, 20, al);
 }
+// real z-slab runs: the gathered {nv, nf, edge sum} triples of all ranks (geometry_api.cu enqueue_slab_gather), summed in rank
+// order — integer additions, the same total on every rank and the same as one GPU's sum over the whole mesh
+__global__ void k_alpha_from_gather(AlphaList* __restrict__ al, const long long* __restrict__ triples, int world) {
+    long long nf = 0;
+    unsigned long long total = 0ull;
+    for (int r = 0; r < world; ++r) { nf += triples[3 * r + 1]; total += (unsigned long long)triples[3 * r + 2]; }
+    al->edge_total = total;
+    const float avg = (float)(((double)total * (1.0 / 4294967296.0)) / (3. * (double)nf));
+    al->avg_edge = avg;
+    make_alpha_list(avg, 0.001f, avg, 20, al);
+}
 // exact_reduce: the alpha list again, from the serial float mean
 __global__ void k_alpha_from_mean(const float* __restrict__ mean, AlphaList* __restrict__ al) {
     al->avg_edge = *mean;
@@ -671,8 +682,19 @@ __device__ __forceinline__ int pair_slot(const PointSpec& ps, float ax, float ay
     if (!((__ldg(ps.tile_bits + (size_t)row * ps.TW + (tx >> 5)) >> (tx & 31)) & 1u)) return -1;
     return (int)__ldg(ps.tile_slot + (size_t)row * ps.g.tx + tx);
 }
+#ifndef ISD_PAIR_INLINE
+#define ISD_PAIR_INLINE 1
+#endif
+#if ISD_PAIR_INLINE
+#define ISD_PAIR_FN __device__ __forceinline__
+#else
+#define ISD_PAIR_FN __device__ __noinline__      // one copy per kernel, but every load inside pays two R2UR for its descriptor
+#endif
+#ifndef ISD_PAIR_MINBLOCKS
+#define ISD_PAIR_MINBLOCKS 1
+#endif
 // f at two points / f and grad f at two points (.x = first point, .y = second)
-__device__ __noinline__ F2 eval_f_pair(SdfGridView sdf, float ax, float ay, float az, float bx, float by, float bz) {
+ISD_PAIR_FN F2 eval_f_pair(SdfGridView sdf, float ax, float ay, float az, float bx, float by, float bz) {
     const int slot = pair_slot(c_point_spec, ax, ay, az, bx, by, bz);
     if (slot >= 0) {
         const uint32_t* rec = c_point_spec.lists + (size_t)slot * 2 * c_point_spec.stride;
@@ -684,7 +706,7 @@ __device__ __noinline__ F2 eval_f_pair(SdfGridView sdf, float ax, float ay, floa
     return F2{eval_f<true>(sdf, ax, ay, az), eval_f<true>(sdf, bx, by, bz)};
 }
 struct FG2 { F2 f, g0, g1, g2; };
-__device__ __noinline__ FG2 eval_fg_pair(SdfGridView sdf, float ax, float ay, float az, float bx, float by, float bz) {
+ISD_PAIR_FN FG2 eval_fg_pair(SdfGridView sdf, float ax, float ay, float az, float bx, float by, float bz) {
     FG2 r;
     const int slot = pair_slot(c_point_spec, ax, ay, az, bx, by, bz);
     if (slot >= 0) {
@@ -699,7 +721,7 @@ __device__ __noinline__ FG2 eval_fg_pair(SdfGridView sdf, float ax, float ay, fl
 }
 
 // k_centroid_gradients, faces 2t and 2t+1 per thread
-__global__ void __launch_bounds__(128) k_centroid_gradients_pair(SdfGridView sdf, const float* __restrict__ verts, const int* __restrict__ faces, int nf,
+__global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_centroid_gradients_pair(SdfGridView sdf, const float* __restrict__ verts, const int* __restrict__ faces, int nf,
                                                                  float* __restrict__ cen, float* __restrict__ nrm) {
     const int fa = (blockIdx.x * 128 + threadIdx.x) * 2;
     if (fa >= nf) return;
@@ -729,7 +751,7 @@ __global__ void __launch_bounds__(128) k_centroid_gradients_pair(SdfGridView sdf
 // k_project_search, centroids 2t and 2t+1 per thread.  Each centroid's result is the first sign change along its own sequence of
 // trial points (direction type 0 over the whole alpha list, then type 1 over the short list), exactly as in the scalar kernel;
 // the two sequences advance in lockstep and a lane that has finished a phase rides along on its partner's point.
-__global__ void __launch_bounds__(128) k_project_search_pair(SdfGridView sdf, ProjectArgs a) {
+__global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_project_search_pair(SdfGridView sdf, ProjectArgs a) {
     const int ia = (blockIdx.x * 128 + threadIdx.x) * 2;
     if (ia >= a.n) return;
     const bool two = ia + 1 < a.n;
@@ -819,7 +841,7 @@ __global__ void __launch_bounds__(128) k_project_search_pair(SdfGridView sdf, Pr
 
 // k_project_finish, centroids 2t and 2t+1 per thread: the two bisections advance in lockstep, each with its own interval and
 // its own stopping test; a lane that has finished rides along on its partner's midpoint.
-__global__ void __launch_bounds__(128) k_project_finish_pair(SdfGridView sdf, ProjectArgs a) {
+__global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_project_finish_pair(SdfGridView sdf, ProjectArgs a) {
     const int ia = (blockIdx.x * 128 + threadIdx.x) * 2;
     if (ia >= a.n) return;
     if (a.speculative && a.counters->c[10] != 0ull) return;
@@ -883,6 +905,116 @@ __global__ void __launch_bounds__(128) k_project_finish_pair(SdfGridView sdf, Pr
         a.out[i * 3] = o[k][0]; a.out[i * 3 + 1] = o[k][1]; a.out[i * 3 + 2] = o[k][2];
         const float norm = norm2f(g[k][0], g[k][1], g[k][2]);
         a.nrm_out[i * 3] = g[k][0] / norm; a.nrm_out[i * 3 + 1] = g[k][1] / norm; a.nrm_out[i * 3 + 2] = g[k][2] / norm;
+    }
+}
+
+// k_project_finish in three passes (pair path).  Only a third of the centroids of a typical mesh bisect at all (the others
+// already sit within ROOT_TOLERANCE at the centroid or at the candidate), so inside one kernel two thirds of the lanes idle
+// through every bisection step.  Pass 1 settles the centroids that need no bisection and lists the others (one atomic per
+// warp; a warp's entries stay consecutive, so neighbours in the list are neighbours in space); pass 2 bisects list entries
+// 2t and 2t+1 in lockstep with every lane busy; pass 3 takes the unit gradient at all projected centroids, two per thread.
+struct FinishList { int* items; unsigned long long* count; };
+__global__ void __launch_bounds__(256) k_finish_classify(ProjectArgs a, FinishList fl) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (a.speculative && a.counters->c[10] != 0ull) return;
+    const bool mine = i < a.n;
+    bool bisect = false;
+    if (mine) {
+        const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
+        const bool already = (a.state[i] & 1) != 0;
+        const float fc = a.fc[i];
+        float bx = cx, by = cy, bz = cz, f2 = fc;
+        if (already) {
+            const float4 b = a.best[i];
+            bx = b.x; by = b.y; bz = b.z; f2 = b.w;
+        }
+        const bool zeros2 = fabsf(f2) <= kRootTolerance;
+        const bool zeros1 = fabsf(fc) <= kRootTolerance;
+        if (zeros1) { bx = cx; by = cy; bz = cz; }
+        const bool zeros12 = zeros2 || zeros1;
+        bisect = already && !zeros12;
+        if (!bisect) {
+            float ox = cx, oy = cy, oz = cz;
+            if (zeros12) { ox = bx; oy = by; oz = bz; }
+            a.out[i * 3] = ox; a.out[i * 3 + 1] = oy; a.out[i * 3 + 2] = oz;
+        }
+        count_if(!already, &a.counters->c[7]);
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, bisect);
+    if (m) {
+        const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+        unsigned long long base = 0ull;
+        if (lane == leader) {
+            base = atomicAdd(fl.count, (unsigned long long)__popc(m));
+            atomicAdd(&a.counters->c[9], (unsigned long long)__popc(m));
+        }
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (bisect) fl.items[base + __popc(m & ((1u << lane) - 1u))] = i;
+    }
+}
+__global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_finish_bisect_pair(SdfGridView sdf, ProjectArgs a, FinishList fl) {
+    if (a.speculative && a.counters->c[10] != 0ull) return;
+    const long long n = (long long)*fl.count;
+    for (long long t = (long long)blockIdx.x * 128 + threadIdx.x; t * 2 < n; t += (long long)gridDim.x * 128) {
+        const bool two = t * 2 + 1 < n;
+        const int idx[2] = {fl.items[t * 2], fl.items[two ? t * 2 + 1 : t * 2]};
+        float o[2][3], x1[2][3], x2[2][3];
+        bool active[2] = {true, true};
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int i = idx[k];
+            const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
+            const float4 b = a.best[i];
+            x1[k][0] = cx; x1[k][1] = cy; x1[k][2] = cz; x2[k][0] = b.x; x2[k][1] = b.y; x2[k][2] = b.z;
+            if (b.w < -kRootTolerance) { x1[k][0] = b.x; x1[k][1] = b.y; x1[k][2] = b.z; x2[k][0] = cx; x2[k][1] = cy; x2[k][2] = cz; }
+            o[k][0] = cx; o[k][1] = cy; o[k][2] = cz;
+        }
+        for (int it = 1; active[0] || active[1]; ++it) {
+            float m[2][3];
+#pragma unroll
+            for (int k = 0; k < 2; ++k)
+#pragma unroll
+                for (int q = 0; q < 3; ++q) m[k][q] = (x1[k][q] + x2[k][q]) / 2.0f;
+            if (!active[0]) { m[0][0] = m[1][0]; m[0][1] = m[1][1]; m[0][2] = m[1][2]; }
+            if (!active[1]) { m[1][0] = m[0][0]; m[1][1] = m[0][1]; m[1][2] = m[0][2]; }
+            const F2 f = eval_f_pair(sdf, m[0][0], m[0][1], m[0][2], m[1][0], m[1][1], m[1][2]);
+            const float v[2] = {f.x, f.y};
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                if (!active[k]) continue;
+                if (fabsf(v[k]) <= kRootTolerance || it >= kBisectionMaxIter) {
+                    if (fabsf(v[k]) > kRootTolerance && (k == 0 || two)) atomicAdd(&a.counters->c[8], 1ull);
+                    o[k][0] = m[k][0]; o[k][1] = m[k][1]; o[k][2] = m[k][2];
+                    active[k] = false;
+                    continue;
+                }
+                if (v[k] > kRootTolerance) { x2[k][0] = m[k][0]; x2[k][1] = m[k][1]; x2[k][2] = m[k][2]; }
+                if (v[k] < -kRootTolerance) { x1[k][0] = m[k][0]; x1[k][1] = m[k][1]; x1[k][2] = m[k][2]; }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            if (k == 1 && !two) break;
+            a.out[idx[k] * 3] = o[k][0]; a.out[idx[k] * 3 + 1] = o[k][1]; a.out[idx[k] * 3 + 2] = o[k][2];
+        }
+    }
+}
+// unit gradients at points 2t and 2t+1 (compute_centroid_gradient at the projected centroids, centroids_projection.cpp:1262)
+__global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_unit_gradients_pair(SdfGridView sdf, const float* __restrict__ pts, int n, float* __restrict__ nrm,
+                                                                                 const Ob02Counters* __restrict__ skip_if_leftovers) {
+    const int ia = (blockIdx.x * 128 + threadIdx.x) * 2;
+    if (ia >= n) return;
+    if (skip_if_leftovers != nullptr && skip_if_leftovers->c[10] != 0ull) return;
+    const bool two = ia + 1 < n;
+    const int ib = two ? ia + 1 : ia;
+    const FG2 r = eval_fg_pair(sdf, pts[ia * 3], pts[ia * 3 + 1], pts[ia * 3 + 2], pts[ib * 3], pts[ib * 3 + 1], pts[ib * 3 + 2]);
+    {
+        const float norm = norm2f(r.g0.x, r.g1.x, r.g2.x);
+        nrm[ia * 3] = r.g0.x / norm; nrm[ia * 3 + 1] = r.g1.x / norm; nrm[ia * 3 + 2] = r.g2.x / norm;
+    }
+    if (two) {
+        const float norm = norm2f(r.g0.y, r.g1.y, r.g2.y);
+        nrm[ib * 3] = r.g0.y / norm; nrm[ib * 3 + 1] = r.g1.y / norm; nrm[ib * 3 + 2] = r.g2.y / norm;
     }
 }
 

@@ -44,11 +44,11 @@ def c1_sphere():
     return json.dumps({"type": "ellipsoid", "matrix": EYE})
 
 
-def tiny_sphere(scale=0.03):
+def tiny_sphere(scale=0.03, center=(0.0, 0.0, 0.0)):
     """A sphere of radius scale/2: polygonized in a box of a few hundredths its mean edge falls below 0.004 (the projection's
     alpha list has fewer than the ten entries direction types 1-6 ask for) or below 0.001 (the list is empty and no centroid
     finds a candidate) — make_alpha_list, centroids_projection.cpp:144-194."""
-    return json.dumps({"type": "ellipsoid", "matrix": [scale, 0, 0, 0, 0, scale, 0, 0, 0, 0, scale, 0, 0, 0, 0, 1]})
+    return json.dumps({"type": "ellipsoid", "matrix": [scale, 0, 0, center[0], 0, scale, 0, center[1], 0, 0, scale, center[2], 0, 0, 0, 1]})
 
 
 def c2_cube_minus_cylinder():

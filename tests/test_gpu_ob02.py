@@ -161,16 +161,17 @@ def test_pair_kernels_change_nothing(gpu_lib, shape, R, half):
     one-centroid-per-thread kernels (pair 0), over two OB02 repeats."""
     sj = shape()
     out = []
-    for pair in (0, 1):
-        gpu_lib.build_geometry(sj, shapes.mc_settings(R, half, iters=2, c=1.0, projection=1, qem=1, repeats=2, point_spec=1, pair=pair))
+    for pair, split in ((0, 0), (1, 0), (1, 1)):
+        gpu_lib.build_geometry(sj, shapes.mc_settings(R, half, iters=2, c=1.0, projection=1, qem=1, repeats=2, point_spec=1, pair=pair, finish_split=split))
         v, f = gpu_lib.get_v(), gpu_lib.get_f()
         c, n = gpu_lib.projected_centroids()
         st = gpu_lib.last_counters()
         gpu_lib.finish_geometry()
         out.append((v, f, c, n, st))
-    (v0, f0, c0, n0, s0), (v1, f1, c1, n1, s1) = out
-    assert np.array_equal(f0, f1)
-    assert np.array_equal(v0.view(np.uint32), v1.view(np.uint32))
-    assert np.array_equal(c0.view(np.uint32), c1.view(np.uint32)) and np.array_equal(n0.view(np.uint32), n1.view(np.uint32))
-    for k in ("projection_by_type", "projection_failed", "bisection_capped", "bisected"):
-        assert s0[k] == s1[k], (k, s0[k], s1[k])
+    v0, f0, c0, n0, s0 = out[0]
+    for v1, f1, c1, n1, s1 in out[1:]:
+        assert np.array_equal(f0, f1)
+        assert np.array_equal(v0.view(np.uint32), v1.view(np.uint32))
+        assert np.array_equal(c0.view(np.uint32), c1.view(np.uint32)) and np.array_equal(n0.view(np.uint32), n1.view(np.uint32))
+        for k in ("projection_by_type", "projection_failed", "bisection_capped", "bisected"):
+            assert s0[k] == s1[k], (k, s0[k], s1[k])

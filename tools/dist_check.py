@@ -24,7 +24,14 @@ def main():
     cases = [("c2", shapes.c2_cube_minus_cylinder, 96, 0.8, {}), ("c4", shapes.c4_deep_chain, 120, 1.0, {}),
              ("c2_ob02", shapes.c2_cube_minus_cylinder, 64, 0.8, dict(iters=1, c=1.0, projection=1, qem=1)),                 # halo mode
              ("c4_ob02", shapes.c4_deep_chain, 90, 1.0, dict(iters=2, c=1.0, projection=1, qem=1, repeats=2)),               # halo mode
-             ("c2_ob02_replicated", shapes.c2_cube_minus_cylinder, 64, 0.8, dict(iters=1, c=1.0, projection=1, qem=1, halo=0))]
+             ("c2_ob02_replicated", shapes.c2_cube_minus_cylinder, 64, 0.8, dict(iters=1, c=1.0, projection=1, qem=1, halo=0)),
+             # a small off-centre shape with equal-layer slabs: at least one rank's slab (plus halo) holds no faces and must still
+             # take part in the step's collective (the mean-edge gather); with and without projection, MC only, and balanced cuts
+             ("tiny_empty_slabs_ob02", lambda: shapes.tiny_sphere(0.3, (0.1, -0.2, 0.55)), 64, 1.0, dict(iters=1, c=1.0, projection=1, qem=1, balance=0)),
+             ("tiny_empty_slabs_resample_only", lambda: shapes.tiny_sphere(0.3, (0.1, -0.2, 0.55)), 64, 1.0, dict(iters=1, c=1.0, balance=0)),
+             ("tiny_empty_slabs_mc", lambda: shapes.tiny_sphere(0.3, (0.1, -0.2, 0.55)), 64, 1.0, dict(balance=0)),
+             ("tiny_balanced_ob02", lambda: shapes.tiny_sphere(0.3, (0.1, -0.2, 0.55)), 64, 1.0, dict(iters=1, c=1.0, projection=1, qem=1, repeats=2)),
+             ("c4_ob02_point_lists", shapes.c4_deep_chain, 128, 1.0, dict(iters=1, c=1.0, projection=1, qem=1, point_spec=1))]
     singles = [lib.polygonize(shape(), shapes.mc_settings(R, half, **kw)) for _, shape, R, half, kw in cases]
     uid = torch.zeros(128, dtype=torch.uint8)
     if rank == 0:
