@@ -64,10 +64,12 @@ EXT_SIGNATURES = {
     "isd_device_faces": (ctypes.c_void_p, []),
     "isd_last_timings": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "isd_last_counters": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
+    "isd_debug_spoil_speculation": (None, [ctypes.c_int]),
     "isd_last_program_stats": (ctypes.c_int, [ctypes.c_void_p]),
     "isd_last_kernel_times": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]),
     "isd_kernel_name": (ctypes.c_char_p, [ctypes.c_int]),
     "isd_last_kernel_flops": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
+    "isd_last_kernel_gaps": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "isd_grid_size": (ctypes.c_int, []),
     "isd_get_field": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int64]),
     "isd_get_case_codes": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int64]),
@@ -260,12 +262,16 @@ class GeometryLibrary:
         return dict(zip(TIMING_NAMES, [float(x) for x in buf]))
 
     def last_counters(self):
-        buf = np.zeros(16, dtype=np.int64)
-        self.lib.isd_last_counters(buf.ctypes.data, 16)
+        buf = np.zeros(18, dtype=np.int64)
+        self.lib.isd_last_counters(buf.ctypes.data, 18)
         return {"nodes": int(buf[0]), "cubes": int(buf[1]), "cut_cubes": int(buf[2]),
                 "projection_by_type": [int(x) for x in buf[3:10]], "projection_failed": int(buf[10]),
                 "bisection_capped": int(buf[11]), "bisected": int(buf[12]), "launches": int(buf[13]),
-                "field_bytes": int(buf[14]), "nodes_full_eval": int(buf[15])}
+                "field_bytes": int(buf[14]), "nodes_full_eval": int(buf[15]),
+                "speculative": int(buf[16]), "speculation_redone": int(buf[17])}
+
+    def spoil_speculation(self, what=1):
+        self.lib.isd_debug_spoil_speculation(what)
 
     def last_kernel_times(self):
         """{kernel name: (ms summed over its launches, launches)} of the last build; needs "gpu":{"kernel_times":1}."""
@@ -273,6 +279,12 @@ class GeometryLibrary:
         cnt = np.zeros(64, dtype=np.int32)
         n = self.lib.isd_last_kernel_times(ms.ctypes.data, cnt.ctypes.data, 64)
         return {self.lib.isd_kernel_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n) if cnt[i]}
+
+    def last_kernel_gaps(self):
+        """{kernel name: ms the stream spent between the previous timed kernel and this one} (memsets, copies, host waits)."""
+        ms = np.zeros(64, dtype=np.float32)
+        n = self.lib.isd_last_kernel_gaps(ms.ctypes.data, 64)
+        return {self.lib.isd_kernel_name(i).decode(): float(ms[i]) for i in range(n) if ms[i] > 0}
 
     def last_kernel_flops(self):
         """{kernel name: FP32 operations its CSG evaluations executed} for the last build; needs "gpu":{"count_flops":1}."""

@@ -113,7 +113,7 @@ struct Context {
 
     // OB02 scratch
     DeviceBuffer d_cen, d_nrm, d_deg, d_uoff, d_uitems, d_cursor, d_fof, d_w, d_len3, d_best, d_fc, d_state, d_proj, d_pnrm, d_point_lists,
-        d_noise, d_scal, d_counters, d_upartials, d_bis;
+        d_noise, d_scal, d_counters, d_upartials;
     bool adjacency_valid = false, fof_valid_ = false;
     float average_edge = 0.f;
     bool alpha_ticket_zeroed = false;
@@ -137,7 +137,7 @@ struct Context {
 
     // stats
     float timings[T_COUNT] = {0};
-    int64_t counters[16] = {0};
+    int64_t counters[24] = {0};
     int launches = 0;
     double prog_stats[4] = {0, 0, 0, 0};   // flops/point, nodes, words, value-stack depth
 
@@ -228,6 +228,7 @@ struct KernelTimes {
     struct Span { int id; cudaEvent_t a, b; };
     std::vector<Span> spans;
     float ms[KT_N] = {0};
+    float gap_ms[KT_N] = {0};      // idle stream time BEFORE each kernel (memsets, copies, host waits, collectives), same indices
     int launches[KT_N] = {0};
     bool counting = false, flag_on_device = false;      // "gpu":{"count_flops":1}: executed FP32 operations per kernel
     double flops[KT_N] = {0};
@@ -235,15 +236,17 @@ struct KernelTimes {
         if (used == pool.size()) { cudaEvent_t e; ISD_CUDA(cudaEventCreate(&e)); pool.push_back(e); }
         return pool[used++];
     }
-    void reset(bool enable) { on = enable; used = 0; spans.clear(); for (float& v : ms) v = 0; for (int& v : launches) v = 0; }
+    void reset(bool enable) { on = enable; used = 0; spans.clear(); for (float& v : ms) v = 0; for (float& v : gap_ms) v = 0; for (int& v : launches) v = 0; }
     void start_counting(bool count);
     void finish_counting();
     void collect() {      // the stream has been synchronised
-        for (const Span& sp : spans) {
+        for (size_t k = 0; k < spans.size(); ++k) {
+            const Span& sp = spans[k];
             float t = 0;
             ISD_CUDA(cudaEventElapsedTime(&t, sp.a, sp.b));
             ms[sp.id] += t;
             launches[sp.id]++;
+            if (k > 0) { ISD_CUDA(cudaEventElapsedTime(&t, spans[k - 1].b, sp.a)); gap_ms[sp.id] += t; }
         }
         spans.clear(); used = 0;
     }
@@ -294,7 +297,23 @@ void upload_program(const std::vector<uint32_t>& words) {
     ISD_CUDA(cudaMemcpyToSymbolAsync(d_program, words.data(), words.size() * sizeof(uint32_t), 0, cudaMemcpyHostToDevice, g.stream));
 }
 
-ShapeCompiler::Program compile_shape(const char* shape_json, bool ignore_root_matrix, int cube_mode) {
+// Parsing the shape JSON and flattening the tree is a pure function of (text, ignore_root_matrix, cube_mode) and costs 0.3-0.5 ms
+// of host time for a 60-node tree, during which the GPU would sit idle: the last few programs are kept (a caller that
+// re-polygonizes a shape at another resolution, as the reference's UI does, compiles it once).
+const ShapeCompiler::Program& compile_shape(const char* shape_json, bool ignore_root_matrix, int cube_mode) {
+    struct Entry { std::string text; bool ignore_root; int cube_mode; ShapeCompiler::Program prog; unsigned long long used; };
+    static std::vector<Entry> cache;
+    static unsigned long long clock = 0;
+    ++clock;
+    for (Entry& e : cache)
+        if (e.ignore_root == ignore_root_matrix && e.cube_mode == cube_mode && e.text == shape_json) {
+            e.used = clock;
+            if (e.prog.uses_sdf_grid && g.sdf.v == nullptr) {
+                fprintf(stderr, "implisolid_b200: \"gpu.cube_mode\":1 needs isd_set_sdf_grid() first\n");
+                abort();
+            }
+            return e.prog;
+        }
     ShapeOptions opt;
     opt.cube_mode = cube_mode;
     ShapeCompiler compiler(opt);
@@ -304,7 +323,13 @@ ShapeCompiler::Program compile_shape(const char* shape_json, bool ignore_root_ma
         fprintf(stderr, "implisolid_b200: \"gpu.cube_mode\":1 needs isd_set_sdf_grid() first\n");
         abort();
     }
-    return p;
+    if (cache.size() >= 8) {      // evict the least recently used
+        size_t victim = 0;
+        for (size_t i = 1; i < cache.size(); ++i) if (cache[i].used < cache[victim].used) victim = i;
+        cache.erase(cache.begin() + (long)victim);
+    }
+    cache.push_back(Entry{std::string(shape_json), ignore_root_matrix, cube_mode, std::move(p), clock});
+    return cache.back().prog;
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -424,6 +449,21 @@ void enqueue_slab_gather(const unsigned long long* d_edge_sum) {
     g.halo_gather_enqueued = true;
 }
 
+// Sizes a build learns from the device half-way (work-list length, vertex / face / cut-cube totals, a slab's own ranges) are a
+// deterministic function of (program, grid, slab, settings).  A build whose key equals the previous build's takes them from
+// there and never waits for the device in mid-step ("gpu":{"speculate":1}, default); the device's own values still come back
+// with the final synchronisation and are compared — a mismatch (never seen: the path is integer-deterministic) discards the
+// result and rebuilds without speculation.  A caller that re-polygonizes the same spec pays for one host wait per build, not four.
+struct SpecCache {
+    bool valid = false;
+    std::vector<uint32_t> key;
+    unsigned h[24] = {0};
+    // projection: centroids left over after phase A, per overall repeat (-1 unknown)
+    long long leftovers[8] = {-1, -1, -1, -1, -1, -1, -1, -1};
+    long long face_base[8] = {0, 0, 0, 0, 0, 0, 0, 0};      // global index of local face 0 (noise stream offset), per repeat
+} g_spec;
+bool g_spec_used = false;
+
 void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog) {
     setup_grid(s, prog);
     const GridDesc& gd = g.grid;
@@ -518,12 +558,37 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
                                   (s.vresampl_iters > 0 || s.projection_enabled);
     // Per-segment arrays: sized for every tile when that is small (no read-back), else for the work list (one extra
     // read-back, negligible at the grid sizes where it happens).
-    unsigned* h = g.h_small.as<unsigned>();
+    unsigned* h_actual = g.h_small.as<unsigned>();      // what the device reports (pinned)
+    std::vector<uint32_t> key;
+    key.reserve(prog.words.size() + prog.bounds.size() + 128);
+    key.insert(key.end(), prog.words.begin(), prog.words.end());
+    key.insert(key.end(), prog.bounds.begin(), prog.bounds.end());
+    {
+        uint32_t raw[(sizeof(McDesc) + 3) / 4] = {0};
+        memcpy(raw, &m, sizeof(McDesc));      // grid, box, slab layers (McDesc holds the GridDesc)
+        key.insert(key.end(), raw, raw + (sizeof(McDesc) + 3) / 4);
+        const uint32_t extra[] = {(uint32_t)s.prune, (uint32_t)s.specialize, (uint32_t)g.rank, (uint32_t)g.world, (uint32_t)g.emulate, (uint32_t)g.halo,
+                                  (uint32_t)g.own_zb, (uint32_t)g.own_ze, (uint32_t)(uintptr_t)g.sdf.v, (uint32_t)((uintptr_t)g.sdf.v >> 32), (uint32_t)g.sdf.nx,
+                                  (uint32_t)s.overall_repeats, (uint32_t)s.vresampl_iters, (uint32_t)s.projection_enabled, (uint32_t)s.qem_enabled,
+                                  (uint32_t)s.exact_reduce, (uint32_t)s.subdiv_enabled, (uint32_t)s.point_spec};
+        key.insert(key.end(), extra, extra + sizeof(extra) / 4);
+        uint32_t cbits;
+        memcpy(&cbits, &s.vresampl_c, 4);
+        key.push_back(cbits);
+    }
+    const bool spec_hit = s.speculate != 0 && g_spec.valid && g_spec.key == key;
+    g_spec_used = spec_hit;
+    unsigned h[24];
+    if (spec_hit) memcpy(h, g_spec.h, sizeof(h));
     unsigned n_work = (unsigned)ntiles;
     if ((size_t)ntiles * 64 * 16 > ((size_t)512 << 20)) {
-        ISD_CUDA(cudaMemcpyAsync(h + 8, tile_count, sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));
-        ISD_CUDA(cudaStreamSynchronize(g.stream));
-        n_work = h[8];
+        if (spec_hit) {
+            n_work = h[8];
+        } else {
+            ISD_CUDA(cudaMemcpyAsync(h_actual + 8, tile_count, sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));
+            ISD_CUDA(cudaStreamSynchronize(g.stream));
+            n_work = h_actual[8];
+        }
     }
     const size_t n_seg = (size_t)(n_work > 0 ? n_work : 1) * 64;
     g.d_seg_bits.reserve(n_seg * sizeof(unsigned long long));
@@ -546,13 +611,21 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         ISD_TIMED(KT_ROW_SCAN, k_row_scan<<<scan_blocks, kRowScanThreads, 0, g.stream>>>(m, mb, rows_per_block, g.d_scan_state.as<unsigned>(), g.d_totals.as<unsigned>()));
     }
     // totals back to the host: sizes of the vertex, face and cut-cube arrays (+ the ghost layer's share, z-slabs only)
-    ISD_CUDA(cudaMemcpyAsync(h, g.d_totals.ptr, 10 * sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));      // [8] = work-list length
+    memset(h_actual, 0, 24 * sizeof(unsigned));
+    ISD_CUDA(cudaMemcpyAsync(h_actual, g.d_totals.ptr, 10 * sizeof(unsigned), cudaMemcpyDeviceToHost, g.stream));      // [8] = work-list length
     const long long own_row0 = (long long)(g.own_zb - m.scan_z0) * m.NX, own_row1 = (long long)(g.own_ze - m.scan_z0) * m.NX;
     if (g.halo_mode) {      // vertices / faces counted before the slab's first own row and before the first row above it
-        ISD_CUDA(cudaMemcpyAsync(h + 16, mb.row_base + own_row0, sizeof(Triple), cudaMemcpyDeviceToHost, g.stream));
-        if (own_row1 < n_rows) ISD_CUDA(cudaMemcpyAsync(h + 20, mb.row_base + own_row1, sizeof(Triple), cudaMemcpyDeviceToHost, g.stream));
+        ISD_CUDA(cudaMemcpyAsync(h_actual + 16, mb.row_base + own_row0, sizeof(Triple), cudaMemcpyDeviceToHost, g.stream));
+        if (own_row1 < n_rows) ISD_CUDA(cudaMemcpyAsync(h_actual + 20, mb.row_base + own_row1, sizeof(Triple), cudaMemcpyDeviceToHost, g.stream));
     }
-    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    if (!spec_hit) {
+        ISD_CUDA(cudaStreamSynchronize(g.stream));
+        memcpy(h, h_actual, sizeof(h));
+        g_spec.valid = true;
+        g_spec.key = key;
+        memcpy(g_spec.h, h, sizeof(h));
+        for (long long& l : g_spec.leftovers) l = -1;
+    }
     if (want_point_lists && h[8] > 0) {
         const int n_instr = (int)(itab_words / 4), stride = n_instr + 1;
         const size_t list_bytes = (size_t)h[8] * 2 * stride * sizeof(uint32_t);
@@ -836,7 +909,13 @@ const float* noise_stream(size_t count) {
 }
 
 // polygonize_step_2 (polygonizer_algorithm_ob02.hpp:108-116) -> centroids_projection (centroids_projection.cpp:1219-1311)
-void projection_step(bool enable_qem, bool exact_reduce) {
+// stage times and counters of projection steps that did not wait for the device (speculative builds): resolved by
+// finish_deferred_projection() after the build's final synchronisation
+struct DeferredSpan { int stage; cudaEvent_t a, b; };
+std::vector<DeferredSpan> g_deferred_spans;
+std::vector<int> g_deferred_slots;      // counter slots (= overall repeat) of the projection steps that ran speculatively
+
+void projection_step(bool enable_qem, bool exact_reduce, int repeat) {
     const int nv = (int)g.nv, nf = (int)g.nf;
     if (nf == 0) {
         // A slab (plus halo) without faces still owes the other ranks its triple: every rank enqueues the collective once per
@@ -847,6 +926,8 @@ void projection_step(bool enable_qem, bool exact_reduce) {
         return;
     }
     ISD_CUDA(cudaEventRecord(g.ev[6], g.stream));
+    cudaEvent_t ev_start = nullptr;
+    if (g_spec_used) { ev_start = g_kt.get(); ISD_CUDA(cudaEventRecord(ev_start, g.stream)); }
     const unsigned prep_blocks = blocks_for(nf, 256);
     {
         const void* before = g.d_scal.ptr;
@@ -912,15 +993,10 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     // Phase B (direction types 2..6) is only needed when phase A left centroids over, which is rare and which only the device
     // knows: the rest of the step is launched right away and does nothing in that case (the kernels test the counter), so the
     // host does not have to wait here.
-    // k_project_finish: one kernel, or (pair path) classify -> bisect the listed third of the centroids -> gradients of all
-    g.d_bis.reserve((size_t)nf * sizeof(int) + 64);
-    FinishList fl{g.d_bis.as<int>() + 16, reinterpret_cast<unsigned long long*>(g.d_bis.ptr)};
+    // k_project_finish: one kernel, or (pair path) bisect from per-warp queues -> gradients of all
     auto finish_pass = [&](const ProjectArgs& pa) {
         if (pairs && g.finish_split) {
-            ISD_CUDA(cudaMemsetAsync(fl.count, 0, sizeof(unsigned long long), g.stream));
-            ISD_TIMED(KT_FINISH, k_finish_classify<<<blocks_for(nf, 256), 256, 0, g.stream>>>(pa, fl));
-            const unsigned want = blocks_for((nf + 1) / 2, 128), cap = (unsigned)g.sm_count * 16u;
-            ISD_TIMED(KT_FINISH, k_finish_bisect_pair<<<want < cap ? want : cap, 128, 0, g.stream>>>(g.sdf, pa, fl));
+            ISD_TIMED(KT_FINISH, k_finish_bisect_queue<<<blocks_for(nf, 4 * kFinishRange), 128, 0, g.stream>>>(g.sdf, pa));
             ISD_TIMED(KT_FINISH, k_unit_gradients_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, pa.out, nf, pa.nrm_out,
                                                                                                             pa.speculative ? pa.counters : nullptr));
         } else if (pairs) {
@@ -929,6 +1005,34 @@ void projection_step(bool enable_qem, bool exact_reduce) {
             ISD_TIMED(KT_FINISH, (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, pa));
         }
     };
+    Ob02Counters* hc = reinterpret_cast<Ob02Counters*>(g.h_small.as<char>() + 2048) + (repeat >= 0 && repeat < 8 ? repeat : 0);
+    float* h_avg = reinterpret_cast<float*>(g.h_small.as<char>() + 1024);
+    if (g_spec_used && repeat >= 0 && repeat < 8 && g_spec.leftovers[repeat] >= 0) {
+        // Speculative build: the previous build of this very spec tells whether phase A leaves centroids over, and how many.  The
+        // whole step is enqueued without waiting; the counter comes back with the build's last synchronisation and is checked.
+        const long long n_left = g_spec.leftovers[repeat];
+        if (enable_qem) build_adjacency(false);
+        cudaEvent_t ev_m = g_kt.get(), ev_b = g_kt.get();
+        if (n_left > 0) {
+            a.noise = noise_stream((size_t)(g_spec.face_base[repeat] + nf) * 3) + g_spec.face_base[repeat] * 3;
+            a.speculative = 0;
+            const unsigned left_blocks = blocks_for(n_left, 4) < (unsigned)g.sm_count * 16 ? blocks_for(n_left, 4) : (unsigned)g.sm_count * 16;
+            ISD_TIMED(KT_LEFTOVERS, (g.point_spec_on ? k_project_leftovers<true> : k_project_leftovers<false>)<<<left_blocks, 128, 0, g.stream>>>(g.sdf, a, (int)n_left));
+        }
+        finish_pass(a);
+        ISD_CUDA(cudaEventRecord(ev_m, g.stream));
+        if (enable_qem)
+            ISD_TIMED(KT_QEM, k_qem<<<blocks_for(nv, 128), 128, 0, g.stream>>>(nv, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(), g.d_proj.as<float>(),
+                                                            g.d_pnrm.as<float>(), d_al, n_left > 0 ? nullptr : g.d_counters.as<Ob02Counters>(), g.d_verts.as<float>()));
+        ISD_CUDA(cudaEventRecord(ev_b, g.stream));
+        ISD_CUDA(cudaMemcpyAsync(hc, g.d_counters.ptr, sizeof(Ob02Counters), cudaMemcpyDeviceToHost, g.stream));
+        ISD_CUDA(cudaMemcpyAsync(h_avg, &d_al->avg_edge, sizeof(float), cudaMemcpyDeviceToHost, g.stream));
+        g_deferred_spans.push_back(DeferredSpan{T_PROJECT, ev_start, ev_m});
+        g_deferred_spans.push_back(DeferredSpan{T_QEM, ev_m, ev_b});
+        g_deferred_slots.push_back(repeat);
+        g.proj_n = nf;
+        return;
+    }
     finish_pass(a);
     ISD_CUDA(cudaEventRecord(g.ev[7], g.stream));
     if (enable_qem) {   // centroids_projection.cpp:1272-1310: the mesh only changes when QEM is on
@@ -937,8 +1041,6 @@ void projection_step(bool enable_qem, bool exact_reduce) {
                                                         g.d_pnrm.as<float>(), d_al, g.d_counters.as<Ob02Counters>(), g.d_verts.as<float>()));
     }
     ISD_CUDA(cudaEventRecord(g.ev[8], g.stream));
-    Ob02Counters* hc = reinterpret_cast<Ob02Counters*>(g.h_small.as<char>() + 2048);
-    float* h_avg = reinterpret_cast<float*>(g.h_small.as<char>() + 1024);
     ISD_CUDA(cudaMemcpyAsync(hc, g.d_counters.ptr, sizeof(Ob02Counters), cudaMemcpyDeviceToHost, g.stream));
     ISD_CUDA(cudaMemcpyAsync(h_avg, &d_al->avg_edge, sizeof(float), cudaMemcpyDeviceToHost, g.stream));
     ISD_CUDA(cudaStreamSynchronize(g.stream));
@@ -947,12 +1049,14 @@ void projection_step(bool enable_qem, bool exact_reduce) {
     g.timings[T_PROJECT] += ms;
     ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[7], g.ev[8]));
     g.timings[T_QEM] += ms;
+    if (repeat >= 0 && repeat < 8) { g_spec.leftovers[repeat] = (long long)hc->c[10]; g_spec.face_base[repeat] = 0; }
     if (hc->c[10] > 0) {
         // rare: direction types 2..6 for the left-overs; type 2 needs make_random_pm1(n, 1e-6), centroid i <- draws 3i..3i+2
         ISD_CUDA(cudaEventRecord(g.ev[6], g.stream));
         // centroid i draws 3i..3i+2 of the stream, i being the face's index in the WHOLE mesh
         long long face_base = 0;
         if (g.halo_mode) { resolve_halo_offsets(); face_base = g.slab[3] - g.own_f0; }
+        if (repeat >= 0 && repeat < 8) g_spec.face_base[repeat] = face_base;
         a.noise = noise_stream((size_t)(face_base + nf) * 3) + face_base * 3;
         a.speculative = 0;
         const int n_left = (int)hc->c[10];
@@ -1131,11 +1235,11 @@ void copy_mesh_to_host() {
 }
 
 // grand_algorithm (mcc2.cpp:309-444)
-void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out) {
+bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
     if (g.active) {
         fprintf(stderr, "Error: There are non-deallocated geometry resources. Call finit_geometry() first. Not doing anything.");
         fprintf(stderr, "build_geometry() called in a bad state.");
-        return;
+        return true;
     }
     const auto t0 = std::chrono::steady_clock::now();
     for (float& t : g.timings) t = 0;
@@ -1153,7 +1257,7 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     g.normals_valid = false;
     g.normals_host_valid = false;
     g.last_edge_sum = 0;
-    ShapeCompiler::Program prog = compile_shape(shape_json, s.ignore_root_matrix, s.cube_mode);
+    const ShapeCompiler::Program& prog = compile_shape(shape_json, s.ignore_root_matrix, s.cube_mode);
     upload_program(prog.words);
     g.last_program = prog.words;
     g.prog_stats[0] = prog.flops_per_point; g.prog_stats[1] = prog.num_nodes; g.prog_stats[2] = (double)prog.words.size();
@@ -1168,14 +1272,17 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     bool resample_timed = false, subdiv_timed = false;
     for (int overall_iter = 0; overall_iter < s.overall_repeats; ++overall_iter) {
         if (s.vresampl_iters > 0) {
-            ISD_CUDA(cudaEventRecord(g.ev[4], g.stream));
+            cudaEvent_t ra = g.ev[4], rb = g.ev[5];
+            if (g_spec_used) { ra = g_kt.get(); rb = g_kt.get(); }      // nobody waits in mid-build: private events, read at the end
+            ISD_CUDA(cudaEventRecord(ra, g.stream));
             for (int i = 0; i < s.vresampl_iters; ++i) vertex_resampling_step(s.vresampl_c);   // polygonize_step_1
-            ISD_CUDA(cudaEventRecord(g.ev[5], g.stream));
-            resample_timed = true;
+            ISD_CUDA(cudaEventRecord(rb, g.stream));
+            if (g_spec_used) g_deferred_spans.push_back(DeferredSpan{T_RESAMPLE, ra, rb});
+            else resample_timed = true;
         }
         report_progress();                                                                 // mcc2.cpp:372
         if (s.projection_enabled) {
-            projection_step(s.qem_enabled, s.exact_reduce != 0);                           // polygonize_step_2
+            projection_step(s.qem_enabled, s.exact_reduce != 0, overall_iter);             // polygonize_step_2
             report_progress();                                                             // mcc2.cpp:390
         }
         if (resample_timed && (s.projection_enabled || s.overall_repeats > 1)) {          // events are reused by the next repeat
@@ -1195,6 +1302,34 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     export_own_slab();
     ISD_CUDA(cudaStreamSynchronize(g.stream));
     float ms = 0;
+    if (g_spec_used) {
+        // What the device counted against what the build assumed.  A difference means arrays sized and grids launched for another
+        // mesh: the result is dropped and the caller (grand_algorithm) builds again, waiting for the device at every step.
+        bool held = memcmp(g.h_small.ptr, g_spec.h, sizeof(g_spec.h)) == 0;
+        for (int slot : g_deferred_slots) {
+            const Ob02Counters* hc = reinterpret_cast<const Ob02Counters*>(g.h_small.as<char>() + 2048) + slot;
+            if ((long long)hc->c[10] != g_spec.leftovers[slot]) held = false;
+        }
+        if (!held) {
+            g_deferred_spans.clear(); g_deferred_slots.clear();
+            g_kt.collect(); g_kt.finish_counting(); g_kt.on = false;
+            g_spec.valid = false; g_spec_used = false;
+            return false;
+        }
+        for (const DeferredSpan& sp : g_deferred_spans) { ISD_CUDA(cudaEventElapsedTime(&ms, sp.a, sp.b)); g.timings[sp.stage] += ms; }
+        for (int slot : g_deferred_slots) {
+            const Ob02Counters* hc = reinterpret_cast<const Ob02Counters*>(g.h_small.as<char>() + 2048) + slot;
+            for (int i = 0; i < 7; ++i) g.counters[3 + i] += (int64_t)hc->c[i];
+            g.counters[10] += (int64_t)hc->c[7];
+            g.counters[11] += (int64_t)hc->c[8];
+            g.counters[12] += (int64_t)hc->c[9];
+        }
+        if (!g_deferred_slots.empty()) {
+            g.average_edge = *reinterpret_cast<const float*>(g.h_small.as<char>() + 1024);
+            if (g.world == 1 || g.emulate) memcpy(&g.last_edge_sum, g.h_small.as<char>() + 3200, sizeof(unsigned long long));
+        }
+        g_deferred_spans.clear(); g_deferred_slots.clear();
+    }
     if (resample_timed) { ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[4], g.ev[5])); g.timings[T_RESAMPLE] += ms; }
     ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[0], g.ev[1])); g.timings[T_FIELD] = ms;
     ISD_CUDA(cudaEventElapsedTime(&ms, g.ev[1], g.ev[2])); g.timings[T_CLASSIFY] = ms;
@@ -1208,7 +1343,23 @@ void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out)
     if (copy_out) copy_mesh_to_host();
     g.active = true;                                               // polygonize_terminate
     g.counters[13] = g.launches;
+    g.counters[16] = g_spec_used ? 1 : 0;
+    g_spec_used = false;
     g.timings[T_TOTAL] = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return true;
+}
+
+void grand_algorithm(const char* shape_json, const McSettings& s, bool copy_out) {
+    const GlibcRand rand_before = g_rand;      // a dropped build must not leave its draws behind
+    if (build_once(shape_json, s, copy_out)) return;
+    if (g.world > 1 && !g.emulate) {      // the other ranks are not building again: their collectives would not meet this rank's
+        fprintf(stderr, "implisolid_b200: rank %d: the device's counts differ from the previous build of this spec\n", g.rank);
+        abort();
+    }
+    fprintf(stderr, "implisolid_b200: the device's counts differ from the previous build of this spec; building again without speculation\n");
+    g_rand = rand_before;
+    if (!build_once(shape_json, s, copy_out)) { fprintf(stderr, "implisolid_b200: speculation used by a build that has none\n"); abort(); }
+    g.counters[17] = 1;
 }
 
 }  // namespace
@@ -1412,13 +1563,18 @@ int isd_last_timings(float* out_ms, int cap) {
     return n;
 }
 int isd_last_counters(int64_t* out, int cap) {
-    int n = cap < 16 ? cap : 16;
+    int n = cap < 18 ? cap : 18;
     for (int i = 0; i < n; ++i) out[i] = g.counters[i];
     return n;
 }
 int isd_last_kernel_times(float* out_ms, int* out_launches, int cap) {
     int n = cap < (int)KT_N ? cap : (int)KT_N;
     for (int i = 0; i < n; ++i) { out_ms[i] = g_kt.ms[i]; out_launches[i] = g_kt.launches[i]; }
+    return n;
+}
+int isd_last_kernel_gaps(float* out_ms, int cap) {
+    int n = cap < (int)KT_N ? cap : (int)KT_N;
+    for (int i = 0; i < n; ++i) out_ms[i] = g_kt.gap_ms[i];
     return n;
 }
 int isd_last_kernel_flops(double* out, int cap) {
@@ -1489,7 +1645,8 @@ void isd_ob02_on_mesh(const char* shape_parameters_json, float* verts, int nv, c
     for (int64_t& v : g.counters) v = 0;
     load_mesh(verts, nv, faces, nf);
     for (int i = 0; i < resample_iters; ++i) vertex_resampling_step(c);
-    if (projection) projection_step(qem != 0, true);
+    g_spec_used = false;
+    if (projection) projection_step(qem != 0, true, -1);
     ISD_CUDA(cudaMemcpyAsync(verts, g.d_verts.ptr, (size_t)nv * 3 * sizeof(float), cudaMemcpyDeviceToHost, g.stream));
     ISD_CUDA(cudaStreamSynchronize(g.stream));
 }
@@ -1548,6 +1705,12 @@ int isd_dist_init(int rank, int world, const uint8_t* id128) {
     g.rank = rank; g.world = world; g.emulate = false;
     g.comm_rank = rank; g.comm_world = world;
     return 0;
+}
+void isd_debug_spoil_speculation(int what) {
+    // tests only: make the next speculative build of the cached spec assume a wrong left-over count for its first projection step
+    // (the one count whose misprediction cannot overrun an array), so that the check-and-build-again path runs
+    if (what == 0) { g_spec.valid = false; return; }
+    if (g_spec.valid && g_spec.leftovers[0] >= 0) g_spec.leftovers[0] = g_spec.leftovers[0] > 0 ? 0 : 1;
 }
 void isd_dist_suspend(void) { g.rank = 0; g.world = 1; g.emulate = false; }
 void isd_dist_resume(void) {

@@ -545,6 +545,10 @@ __global__ void __launch_bounds__(128) k_project_leftovers(SdfGridView sdf, Proj
     const float* alphas = a.al->alpha;
     const int n_short = a.al->n_short;
     if (n_short == 0) return;      // mean edge below the reference's smallest step: no candidates, every left-over stays failed
+    {   // n_left may be a previous build's count (speculative builds): never walk past what this step listed
+        const int listed = (int)a.counters->c[10];
+        n_left = n_left < listed ? n_left : listed;
+    }
     for (int li = blockIdx.x * 4 + (threadIdx.x >> 5); li < n_left; li += gridDim.x * 4) {
         const int i = a.leftover[li];
         const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
@@ -908,95 +912,118 @@ __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_project_finish_pair
     }
 }
 
-// k_project_finish in three passes (pair path).  Only a third of the centroids of a typical mesh bisect at all (the others
-// already sit within ROOT_TOLERANCE at the centroid or at the candidate), so inside one kernel two thirds of the lanes idle
-// through every bisection step.  Pass 1 settles the centroids that need no bisection and lists the others (one atomic per
-// warp; a warp's entries stay consecutive, so neighbours in the list are neighbours in space); pass 2 bisects list entries
-// 2t and 2t+1 in lockstep with every lane busy; pass 3 takes the unit gradient at all projected centroids, two per thread.
-struct FinishList { int* items; unsigned long long* count; };
-__global__ void __launch_bounds__(256) k_finish_classify(ProjectArgs a, FinishList fl) {
-    const int i = blockIdx.x * 256 + threadIdx.x;
-    if (a.speculative && a.counters->c[10] != 0ull) return;
-    const bool mine = i < a.n;
-    bool bisect = false;
-    if (mine) {
+// k_project_finish in two passes (pair path).  Only a third of the centroids of a typical mesh bisect at all (the others
+// already sit within ROOT_TOLERANCE at the centroid or at the candidate), so inside one thread-per-centroid kernel two thirds
+// of the lanes idle through every bisection step.  Pass 1 (k_finish_bisect_queue): a warp walks a contiguous range of
+// centroids 32 at a time, settles those that need no bisection on the spot and queues the others (ballot ranks: the queue
+// keeps the mesh's order, so neighbours in the queue are neighbours in space and share tile lists); whenever 64 are waiting the
+// warp bisects them, two per lane in lockstep, every lane busy.  Pass 2 (k_unit_gradients_pair) takes the unit gradient at all
+// projected centroids, two per thread.  Per centroid the operations are those of k_project_finish, in the same order.
+constexpr int kFinishRange = 1024;      // centroids per warp
+__device__ __forceinline__ void bisect_two(const SdfGridView& sdf, const ProjectArgs& a, int ia, int ib, bool two) {
+    const int idx[2] = {ia, ib};
+    float o[2][3], x1[2][3], x2[2][3];
+    bool active[2] = {true, true};
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const int i = idx[k];
         const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
-        const bool already = (a.state[i] & 1) != 0;
-        const float fc = a.fc[i];
-        float bx = cx, by = cy, bz = cz, f2 = fc;
-        if (already) {
-            const float4 b = a.best[i];
-            bx = b.x; by = b.y; bz = b.z; f2 = b.w;
-        }
-        const bool zeros2 = fabsf(f2) <= kRootTolerance;
-        const bool zeros1 = fabsf(fc) <= kRootTolerance;
-        if (zeros1) { bx = cx; by = cy; bz = cz; }
-        const bool zeros12 = zeros2 || zeros1;
-        bisect = already && !zeros12;
-        if (!bisect) {
-            float ox = cx, oy = cy, oz = cz;
-            if (zeros12) { ox = bx; oy = by; oz = bz; }
-            a.out[i * 3] = ox; a.out[i * 3 + 1] = oy; a.out[i * 3 + 2] = oz;
-        }
-        count_if(!already, &a.counters->c[7]);
+        const float4 b = a.best[i];
+        x1[k][0] = cx; x1[k][1] = cy; x1[k][2] = cz; x2[k][0] = b.x; x2[k][1] = b.y; x2[k][2] = b.z;
+        if (b.w < -kRootTolerance) { x1[k][0] = b.x; x1[k][1] = b.y; x1[k][2] = b.z; x2[k][0] = cx; x2[k][1] = cy; x2[k][2] = cz; }
+        o[k][0] = cx; o[k][1] = cy; o[k][2] = cz;
     }
-    const unsigned m = __ballot_sync(0xffffffffu, bisect);
-    if (m) {
-        const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
-        unsigned long long base = 0ull;
-        if (lane == leader) {
-            base = atomicAdd(fl.count, (unsigned long long)__popc(m));
-            atomicAdd(&a.counters->c[9], (unsigned long long)__popc(m));
+    for (int it = 1; active[0] || active[1]; ++it) {
+        float m[2][3];
+#pragma unroll
+        for (int k = 0; k < 2; ++k)
+#pragma unroll
+            for (int q = 0; q < 3; ++q) m[k][q] = (x1[k][q] + x2[k][q]) / 2.0f;
+        if (!active[0]) { m[0][0] = m[1][0]; m[0][1] = m[1][1]; m[0][2] = m[1][2]; }
+        if (!active[1]) { m[1][0] = m[0][0]; m[1][1] = m[0][1]; m[1][2] = m[0][2]; }
+        const F2 f = eval_f_pair(sdf, m[0][0], m[0][1], m[0][2], m[1][0], m[1][1], m[1][2]);
+        const float v[2] = {f.x, f.y};
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            if (!active[k]) continue;
+            if (fabsf(v[k]) <= kRootTolerance || it >= kBisectionMaxIter) {
+                if (fabsf(v[k]) > kRootTolerance && (k == 0 || two)) atomicAdd(&a.counters->c[8], 1ull);
+                o[k][0] = m[k][0]; o[k][1] = m[k][1]; o[k][2] = m[k][2];
+                active[k] = false;
+                continue;
+            }
+            if (v[k] > kRootTolerance) { x2[k][0] = m[k][0]; x2[k][1] = m[k][1]; x2[k][2] = m[k][2]; }
+            if (v[k] < -kRootTolerance) { x1[k][0] = m[k][0]; x1[k][1] = m[k][1]; x1[k][2] = m[k][2]; }
         }
-        base = __shfl_sync(0xffffffffu, base, leader);
-        if (bisect) fl.items[base + __popc(m & ((1u << lane) - 1u))] = i;
+    }
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        if (k == 1 && !two) break;
+        a.out[idx[k] * 3] = o[k][0]; a.out[idx[k] * 3 + 1] = o[k][1]; a.out[idx[k] * 3 + 2] = o[k][2];
     }
 }
-__global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_finish_bisect_pair(SdfGridView sdf, ProjectArgs a, FinishList fl) {
+__global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_finish_bisect_queue(SdfGridView sdf, ProjectArgs a) {
     if (a.speculative && a.counters->c[10] != 0ull) return;
-    const long long n = (long long)*fl.count;
-    for (long long t = (long long)blockIdx.x * 128 + threadIdx.x; t * 2 < n; t += (long long)gridDim.x * 128) {
-        const bool two = t * 2 + 1 < n;
-        const int idx[2] = {fl.items[t * 2], fl.items[two ? t * 2 + 1 : t * 2]};
-        float o[2][3], x1[2][3], x2[2][3];
-        bool active[2] = {true, true};
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const int i = idx[k];
+    __shared__ int s_queue[4][96];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int* queue = s_queue[warp];
+    const long long first = ((long long)blockIdx.x * 4 + warp) * kFinishRange;
+    const long long last = first + kFinishRange < (long long)a.n ? first + kFinishRange : (long long)a.n;
+    int waiting = 0;
+    unsigned long long n_failed = 0ull, n_bisect = 0ull;
+    for (long long base = first; base < last; base += 32) {
+        const long long i = base + lane;
+        bool bisect = false;
+        if (i < last) {
             const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
-            const float4 b = a.best[i];
-            x1[k][0] = cx; x1[k][1] = cy; x1[k][2] = cz; x2[k][0] = b.x; x2[k][1] = b.y; x2[k][2] = b.z;
-            if (b.w < -kRootTolerance) { x1[k][0] = b.x; x1[k][1] = b.y; x1[k][2] = b.z; x2[k][0] = cx; x2[k][1] = cy; x2[k][2] = cz; }
-            o[k][0] = cx; o[k][1] = cy; o[k][2] = cz;
-        }
-        for (int it = 1; active[0] || active[1]; ++it) {
-            float m[2][3];
-#pragma unroll
-            for (int k = 0; k < 2; ++k)
-#pragma unroll
-                for (int q = 0; q < 3; ++q) m[k][q] = (x1[k][q] + x2[k][q]) / 2.0f;
-            if (!active[0]) { m[0][0] = m[1][0]; m[0][1] = m[1][1]; m[0][2] = m[1][2]; }
-            if (!active[1]) { m[1][0] = m[0][0]; m[1][1] = m[0][1]; m[1][2] = m[0][2]; }
-            const F2 f = eval_f_pair(sdf, m[0][0], m[0][1], m[0][2], m[1][0], m[1][1], m[1][2]);
-            const float v[2] = {f.x, f.y};
-#pragma unroll
-            for (int k = 0; k < 2; ++k) {
-                if (!active[k]) continue;
-                if (fabsf(v[k]) <= kRootTolerance || it >= kBisectionMaxIter) {
-                    if (fabsf(v[k]) > kRootTolerance && (k == 0 || two)) atomicAdd(&a.counters->c[8], 1ull);
-                    o[k][0] = m[k][0]; o[k][1] = m[k][1]; o[k][2] = m[k][2];
-                    active[k] = false;
-                    continue;
-                }
-                if (v[k] > kRootTolerance) { x2[k][0] = m[k][0]; x2[k][1] = m[k][1]; x2[k][2] = m[k][2]; }
-                if (v[k] < -kRootTolerance) { x1[k][0] = m[k][0]; x1[k][1] = m[k][1]; x1[k][2] = m[k][2]; }
+            const bool already = (a.state[i] & 1) != 0;
+            const float fc = a.fc[i];
+            float bx = cx, by = cy, bz = cz, f2 = fc;      // no candidate: the reference evaluates the centroid again
+            if (already) {
+                const float4 b = a.best[i];
+                bx = b.x; by = b.y; bz = b.z; f2 = b.w;    // f at the candidate, from the search that found it
             }
+            const bool zeros2 = fabsf(f2) <= kRootTolerance;
+            const bool zeros1 = fabsf(fc) <= kRootTolerance;
+            if (zeros1) { bx = cx; by = cy; bz = cz; }
+            const bool zeros12 = zeros2 || zeros1;
+            bisect = already && !zeros12;
+            if (!bisect) {
+                float ox = cx, oy = cy, oz = cz;
+                if (zeros12) { ox = bx; oy = by; oz = bz; }
+                a.out[i * 3] = ox; a.out[i * 3 + 1] = oy; a.out[i * 3 + 2] = oz;
+            }
+            if (!already) ++n_failed;
+            if (bisect) ++n_bisect;
         }
+        const unsigned m = __ballot_sync(0xffffffffu, bisect);
+        if (bisect) queue[waiting + __popc(m & ((1u << lane) - 1u))] = (int)i;
+        waiting += __popc(m);
+        __syncwarp();
+        if (waiting >= 64) {
+            bisect_two(sdf, a, queue[2 * lane], queue[2 * lane + 1], true);
+            __syncwarp();
+            const int rest = waiting - 64;      // < 32: move the tail to the front
+            const int moved = lane < rest ? queue[64 + lane] : 0;
+            __syncwarp();
+            if (lane < rest) queue[lane] = moved;
+            waiting = rest;
+            __syncwarp();
+        }
+    }
+    if (2 * lane < waiting) {      // what is left at the end of the range
+        const bool two = 2 * lane + 1 < waiting;
+        bisect_two(sdf, a, queue[2 * lane], queue[two ? 2 * lane + 1 : 2 * lane], two);
+    }
+    // counters: one atomic per warp each
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            if (k == 1 && !two) break;
-            a.out[idx[k] * 3] = o[k][0]; a.out[idx[k] * 3 + 1] = o[k][1]; a.out[idx[k] * 3 + 2] = o[k][2];
-        }
+    for (int d = 16; d > 0; d >>= 1) {
+        n_failed += __shfl_xor_sync(0xffffffffu, n_failed, d);
+        n_bisect += __shfl_xor_sync(0xffffffffu, n_bisect, d);
+    }
+    if (lane == 0) {
+        if (n_failed) atomicAdd(&a.counters->c[7], n_failed);
+        if (n_bisect) atomicAdd(&a.counters->c[9], n_bisect);
     }
 }
 // unit gradients at points 2t and 2t+1 (compute_centroid_gradient at the projected centroids, centroids_projection.cpp:1262)

@@ -103,8 +103,14 @@ int isd_last_timings(float* out_ms, int cap);
 /* Counters of the last build: [0]=nodes evaluated, [1]=cubes visited, [2]=cut cubes,
  * [3..9]=centroids resolved by projection direction type 0..6, [10]=projection failed,
  * [11]=bisection capped, [12]=bisected, [13]=kernel launches, [14]=field bytes, [15]=nodes
- * evaluated with the full program (others were proven off-surface and skipped). */
+ * evaluated with the full program (others were proven off-surface and skipped), [16]=1 when the build
+ * ran without waiting for the device in mid-step (sizes taken from the previous build of the same spec
+ * and checked at the end, "gpu":{"speculate":1}), [17]=1 when such a build was dropped and done again. */
 int isd_last_counters(int64_t* out, int cap);
+/* Tests: what=0 forgets the previous build's counts (the next build waits for the device); what=1 makes the next
+ * speculative build of the same spec assume a wrong left-over count, so that its end-of-build check fails and
+ * the build is done again. */
+void isd_debug_spoil_speculation(int what);
 /* Shape program of the last build: out = {flops per point (mul and add counted separately), tree nodes,
  * program words, value-stack depth}. */
 int isd_last_program_stats(double* out4);
@@ -115,6 +121,9 @@ int isd_last_kernel_times(float* out_ms, int* out_launches, int cap);
 /* With "gpu":{"count_flops":1}: FP32 operations executed by each kernel's CSG evaluations in the last build (mul and add counted
  * separately; the instruction lists each evaluation really ran, not the whole tree).  Same indices as isd_last_kernel_times. */
 int isd_last_kernel_flops(double* out, int cap);
+/* Stream time between the end of the previous timed kernel and the start of kernel i, summed over its launches (memsets,
+ * copies, host waits and collectives that precede it).  Same indices and setting as isd_last_kernel_times. */
+int isd_last_kernel_gaps(float* out_ms, int cap);
 const char* isd_kernel_name(int id);
 
 /* Parity introspection (needs "gpu":{"keep_field":1} in mc_parameters_json for the field). */
