@@ -381,6 +381,11 @@ def main():
     clocks = sampler.stop()
     value = voxels / (ms_per_step * 1e-3)
     counters = lib.last_counters()
+    # The timed builds repeat one spec, so after the first they take their array sizes from the build before (checked at the end of
+    # every build) and never wait for the device in mid-step; every kernel still runs on every step.  The same steps with that
+    # switched off ("gpu":{"speculate":0}: the host waits for the device's counts three times per step) are reported beside them.
+    speculative_builds = counters["speculative"]
+    ms_waiting, _, _, _ = timed_device_steps(cfg, settings(cfg, kernel_times=1, speculate=0), max(3, min(args.steps, 20)), 3)
     prog = lib.last_program_stats()
     slab = lib.last_slab()
     per_rank = gather_all({"rank": rank, "stage_ms": stages, "nv": slab["nv"], "nf": slab["nf"], "z": [slab["z_begin"], slab["z_end"]],
@@ -527,7 +532,11 @@ def main():
             "counters": {"projection_by_type": e2e_counters["projection_by_type"], "projection_failed": e2e_counters["projection_failed"],
                          "bisection_capped": e2e_counters["bisection_capped"], "bisected": e2e_counters["bisected"], "scope": "rank 0's slab + halo" if world > 1 else "whole mesh"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},
-            "gpu_launches": launches, "clocks": clocks, "other_configs": others}
+            "gpu_launches": launches, "clocks": clocks, "other_configs": others,
+            "speculation": {"timed_builds_speculative": bool(speculative_builds), "what": "a build of the spec the previous build had sizes its arrays and "
+                            "grids from that build's counts instead of waiting for the device; all kernels run every step and the device's own counts are "
+                            "compared after the step's last synchronisation (a mismatch rebuilds); nothing of the result is reused",
+                            "ms_per_step_waiting": ms_waiting, "value_waiting": voxels / (ms_waiting * 1e-3), "steps_waiting": max(3, min(args.steps, 20))}}
     if world > 1:
         line["per_rank"] = sorted(per_rank, key=lambda r: r["rank"])
         smin = {k: min(r["stage_ms"][k] for r in per_rank) for k in stages}

@@ -214,12 +214,12 @@ __global__ void __launch_bounds__(64) k_tile_bounds(GridDesc g, const uint32_t* 
 }
 
 #ifndef ISD_TILE_NODES
-#define ISD_TILE_NODES 4
+#define ISD_TILE_NODES 8      // measured on C4 1024^3: 8 nodes/thread, 64-thread blocks, >= 10 blocks/SM: 0.63 ms; 4 nodes/thread: 0.77 ms
 #endif
 constexpr int kNodesPerThread = ISD_TILE_NODES;      // 4 or 8 x-adjacent nodes per thread (2 or 4 packed pairs)
 constexpr int kTileThreads = 512 / kNodesPerThread;
 #ifndef ISD_EVAL_MINBLOCKS
-#define ISD_EVAL_MINBLOCKS 1
+#define ISD_EVAL_MINBLOCKS 10
 #endif
 
 struct TileLive {             // liveness mask of the tile being evaluated (uniform across the block)

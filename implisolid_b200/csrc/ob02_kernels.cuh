@@ -695,7 +695,10 @@ __device__ __forceinline__ int pair_slot(const PointSpec& ps, float ax, float ay
 #define ISD_PAIR_FN __device__ __noinline__      // one copy per kernel, but every load inside pays two R2UR for its descriptor
 #endif
 #ifndef ISD_PAIR_MINBLOCKS
-#define ISD_PAIR_MINBLOCKS 1
+#define ISD_PAIR_MINBLOCKS 6      // 80 registers: measured best for search / finish (5: 96 regs, 7: 72 regs and spills in the search)
+#endif
+#ifndef ISD_PAIR_MINBLOCKS_CG
+#define ISD_PAIR_MINBLOCKS_CG 7
 #endif
 // f at two points / f and grad f at two points (.x = first point, .y = second)
 ISD_PAIR_FN F2 eval_f_pair(SdfGridView sdf, float ax, float ay, float az, float bx, float by, float bz) {
@@ -725,7 +728,7 @@ ISD_PAIR_FN FG2 eval_fg_pair(SdfGridView sdf, float ax, float ay, float az, floa
 }
 
 // k_centroid_gradients, faces 2t and 2t+1 per thread
-__global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_centroid_gradients_pair(SdfGridView sdf, const float* __restrict__ verts, const int* __restrict__ faces, int nf,
+__global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS_CG) k_centroid_gradients_pair(SdfGridView sdf, const float* __restrict__ verts, const int* __restrict__ faces, int nf,
                                                                  float* __restrict__ cen, float* __restrict__ nrm) {
     const int fa = (blockIdx.x * 128 + threadIdx.x) * 2;
     if (fa >= nf) return;

@@ -54,8 +54,7 @@ def test_speculative_builds_change_nothing(gpu_lib, name, shape, R, half, kw):
     for i in range(3):
         gpu_lib.srand(1)
         runs.append(_build(gpu_lib, sj, spec))
-    assert runs[0][2]["speculative"] == 0           # nothing to go by yet (the waiting build above had another key)
-    assert runs[1][2]["speculative"] == 1 and runs[2][2]["speculative"] == 1
+    assert all(r[2]["speculative"] == 1 for r in runs)      # the waiting build left its counts behind
     assert all(r[2]["speculation_redone"] == 0 for r in runs)
     for r in runs:
         assert _same(ref, r), name
