@@ -996,7 +996,7 @@ void projection_step(bool enable_qem, bool exact_reduce, int repeat) {
     // k_project_finish: one kernel, or (pair path) bisect from per-warp queues -> gradients of all
     auto finish_pass = [&](const ProjectArgs& pa) {
         if (pairs && g.finish_split) {
-            ISD_TIMED(KT_FINISH, k_finish_bisect_queue<<<blocks_for(nf, 4 * kFinishRange), 128, 0, g.stream>>>(g.sdf, pa));
+            ISD_TIMED(KT_FINISH, k_finish_bisect_units<<<blocks_for((nf + 1) / 2, 4 * kFinishRange), 128, 0, g.stream>>>(g.sdf, pa));
             ISD_TIMED(KT_FINISH, k_unit_gradients_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, pa.out, nf, pa.nrm_out,
                                                                                                             pa.speculative ? pa.counters : nullptr));
         } else if (pairs) {

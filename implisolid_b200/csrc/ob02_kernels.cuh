@@ -915,26 +915,32 @@ __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_project_finish_pair
     }
 }
 
-// k_project_finish in two passes (pair path).  Only a third of the centroids of a typical mesh bisect at all (the others
-// already sit within ROOT_TOLERANCE at the centroid or at the candidate), so inside one thread-per-centroid kernel two thirds
-// of the lanes idle through every bisection step.  Pass 1 (k_finish_bisect_queue): a warp walks a contiguous range of
-// centroids 32 at a time, settles those that need no bisection on the spot and queues the others (ballot ranks: the queue
-// keeps the mesh's order, so neighbours in the queue are neighbours in space and share tile lists); whenever 64 are waiting the
-// warp bisects them, two per lane in lockstep, every lane busy.  Pass 2 (k_unit_gradients_pair) takes the unit gradient at all
-// projected centroids, two per thread.  Per centroid the operations are those of k_project_finish, in the same order.
-constexpr int kFinishRange = 1024;      // centroids per warp
-__device__ __forceinline__ void bisect_two(const SdfGridView& sdf, const ProjectArgs& a, int ia, int ib, bool two) {
-    const int idx[2] = {ia, ib};
+// k_project_finish in two passes (pair path, "gpu":{"finish_split":1}).  Only a third of the centroids of a typical mesh
+// bisect at all (the others already sit within ROOT_TOLERANCE at the centroid or at the candidate), so inside the one-kernel form
+// about half of the lanes — those whose two centroids both need nothing — idle through every bisection step.  Pass 1
+// (k_finish_bisect_units): a warp walks a contiguous range of UNITS (faces 2u and 2u+1: the pair the other pair kernels take,
+// neighbours in space that share a tile list) 32 at a time, settles the centroids that need no bisection on the spot and queues
+// the units with at least one that does (ballot ranks: mesh order is kept); whenever 32 units are waiting, every lane takes one
+// and bisects its two centroids in lockstep, a member that needs nothing riding along as in k_project_finish_pair.  Pass 2
+// (k_unit_gradients_pair) takes the unit gradient at all projected centroids.  Per centroid the operations are those of
+// k_project_finish, in the same order.
+constexpr int kFinishRange = 512;      // units per warp
+__device__ __forceinline__ void bisect_unit(const SdfGridView& sdf, const ProjectArgs& a, int entry) {
+    const int u = entry >> 2;
+    const int idx[2] = {2 * u, 2 * u + 1};
+    bool active[2] = {(entry & 1) != 0, (entry & 2) != 0};
+    const bool need[2] = {active[0], active[1]};
     float o[2][3], x1[2][3], x2[2][3];
-    bool active[2] = {true, true};
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
+#pragma unroll
+        for (int q = 0; q < 3; ++q) { o[k][q] = 0.0f; x1[k][q] = 0.0f; x2[k][q] = 0.0f; }
+        if (!need[k]) continue;
         const int i = idx[k];
         const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
         const float4 b = a.best[i];
         x1[k][0] = cx; x1[k][1] = cy; x1[k][2] = cz; x2[k][0] = b.x; x2[k][1] = b.y; x2[k][2] = b.z;
         if (b.w < -kRootTolerance) { x1[k][0] = b.x; x1[k][1] = b.y; x1[k][2] = b.z; x2[k][0] = cx; x2[k][1] = cy; x2[k][2] = cz; }
-        o[k][0] = cx; o[k][1] = cy; o[k][2] = cz;
     }
     for (int it = 1; active[0] || active[1]; ++it) {
         float m[2][3];
@@ -950,7 +956,7 @@ __device__ __forceinline__ void bisect_two(const SdfGridView& sdf, const Project
         for (int k = 0; k < 2; ++k) {
             if (!active[k]) continue;
             if (fabsf(v[k]) <= kRootTolerance || it >= kBisectionMaxIter) {
-                if (fabsf(v[k]) > kRootTolerance && (k == 0 || two)) atomicAdd(&a.counters->c[8], 1ull);
+                if (fabsf(v[k]) > kRootTolerance) atomicAdd(&a.counters->c[8], 1ull);
                 o[k][0] = m[k][0]; o[k][1] = m[k][1]; o[k][2] = m[k][2];
                 active[k] = false;
                 continue;
@@ -960,64 +966,68 @@ __device__ __forceinline__ void bisect_two(const SdfGridView& sdf, const Project
         }
     }
 #pragma unroll
-    for (int k = 0; k < 2; ++k) {
-        if (k == 1 && !two) break;
-        a.out[idx[k] * 3] = o[k][0]; a.out[idx[k] * 3 + 1] = o[k][1]; a.out[idx[k] * 3 + 2] = o[k][2];
-    }
+    for (int k = 0; k < 2; ++k)
+        if (need[k]) { a.out[idx[k] * 3] = o[k][0]; a.out[idx[k] * 3 + 1] = o[k][1]; a.out[idx[k] * 3 + 2] = o[k][2]; }
 }
-__global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_finish_bisect_queue(SdfGridView sdf, ProjectArgs a) {
+#ifndef ISD_FINISH_UNITS_MINBLOCKS
+#define ISD_FINISH_UNITS_MINBLOCKS 5
+#endif
+__global__ void __launch_bounds__(128, ISD_FINISH_UNITS_MINBLOCKS) k_finish_bisect_units(SdfGridView sdf, ProjectArgs a) {
     if (a.speculative && a.counters->c[10] != 0ull) return;
-    __shared__ int s_queue[4][96];
+    __shared__ int s_queue[4][64];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int* queue = s_queue[warp];
+    const int n_units = (a.n + 1) / 2;
     const long long first = ((long long)blockIdx.x * 4 + warp) * kFinishRange;
-    const long long last = first + kFinishRange < (long long)a.n ? first + kFinishRange : (long long)a.n;
+    const long long last = first + kFinishRange < (long long)n_units ? first + kFinishRange : (long long)n_units;
     int waiting = 0;
-    unsigned long long n_failed = 0ull, n_bisect = 0ull;
+    unsigned n_failed = 0u, n_bisect = 0u;
     for (long long base = first; base < last; base += 32) {
-        const long long i = base + lane;
-        bool bisect = false;
-        if (i < last) {
-            const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
-            const bool already = (a.state[i] & 1) != 0;
-            const float fc = a.fc[i];
-            float bx = cx, by = cy, bz = cz, f2 = fc;      // no candidate: the reference evaluates the centroid again
-            if (already) {
-                const float4 b = a.best[i];
-                bx = b.x; by = b.y; bz = b.z; f2 = b.w;    // f at the candidate, from the search that found it
+        const long long u = base + lane;
+        int needs = 0;
+        if (u < last) {
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const long long i = 2 * u + k;
+                if (i >= (long long)a.n) break;
+                const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
+                const bool already = (a.state[i] & 1) != 0;
+                const float fc = a.fc[i];
+                float bx = cx, by = cy, bz = cz, f2 = fc;      // no candidate: the reference evaluates the centroid again
+                if (already) {
+                    const float4 b = a.best[i];
+                    bx = b.x; by = b.y; bz = b.z; f2 = b.w;    // f at the candidate, from the search that found it
+                }
+                const bool zeros2 = fabsf(f2) <= kRootTolerance;
+                const bool zeros1 = fabsf(fc) <= kRootTolerance;
+                if (zeros1) { bx = cx; by = cy; bz = cz; }
+                const bool zeros12 = zeros2 || zeros1;
+                const bool bisect = already && !zeros12;
+                if (!bisect) {
+                    float ox = cx, oy = cy, oz = cz;
+                    if (zeros12) { ox = bx; oy = by; oz = bz; }
+                    a.out[i * 3] = ox; a.out[i * 3 + 1] = oy; a.out[i * 3 + 2] = oz;
+                }
+                if (!already) ++n_failed;
+                if (bisect) { ++n_bisect; needs |= 1 << k; }
             }
-            const bool zeros2 = fabsf(f2) <= kRootTolerance;
-            const bool zeros1 = fabsf(fc) <= kRootTolerance;
-            if (zeros1) { bx = cx; by = cy; bz = cz; }
-            const bool zeros12 = zeros2 || zeros1;
-            bisect = already && !zeros12;
-            if (!bisect) {
-                float ox = cx, oy = cy, oz = cz;
-                if (zeros12) { ox = bx; oy = by; oz = bz; }
-                a.out[i * 3] = ox; a.out[i * 3 + 1] = oy; a.out[i * 3 + 2] = oz;
-            }
-            if (!already) ++n_failed;
-            if (bisect) ++n_bisect;
         }
-        const unsigned m = __ballot_sync(0xffffffffu, bisect);
-        if (bisect) queue[waiting + __popc(m & ((1u << lane) - 1u))] = (int)i;
+        const unsigned m = __ballot_sync(0xffffffffu, needs != 0);
+        if (needs) queue[waiting + __popc(m & ((1u << lane) - 1u))] = (int)(u << 2) | needs;
         waiting += __popc(m);
         __syncwarp();
-        if (waiting >= 64) {
-            bisect_two(sdf, a, queue[2 * lane], queue[2 * lane + 1], true);
+        if (waiting >= 32) {
+            bisect_unit(sdf, a, queue[lane]);
             __syncwarp();
-            const int rest = waiting - 64;      // < 32: move the tail to the front
-            const int moved = lane < rest ? queue[64 + lane] : 0;
+            const int rest = waiting - 32;      // < 32: move the tail to the front
+            const int moved = lane < rest ? queue[32 + lane] : 0;
             __syncwarp();
             if (lane < rest) queue[lane] = moved;
             waiting = rest;
             __syncwarp();
         }
     }
-    if (2 * lane < waiting) {      // what is left at the end of the range
-        const bool two = 2 * lane + 1 < waiting;
-        bisect_two(sdf, a, queue[2 * lane], queue[two ? 2 * lane + 1 : 2 * lane], two);
-    }
+    if (lane < waiting) bisect_unit(sdf, a, queue[lane]);      // what is left at the end of the range
     // counters: one atomic per warp each
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
@@ -1025,8 +1035,8 @@ __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_finish_bisect_queue
         n_bisect += __shfl_xor_sync(0xffffffffu, n_bisect, d);
     }
     if (lane == 0) {
-        if (n_failed) atomicAdd(&a.counters->c[7], n_failed);
-        if (n_bisect) atomicAdd(&a.counters->c[9], n_bisect);
+        if (n_failed) atomicAdd(&a.counters->c[7], (unsigned long long)n_failed);
+        if (n_bisect) atomicAdd(&a.counters->c[9], (unsigned long long)n_bisect);
     }
 }
 // unit gradients at points 2t and 2t+1 (compute_centroid_gradient at the projected centroids, centroids_projection.cpp:1262)

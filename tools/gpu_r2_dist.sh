@@ -18,3 +18,7 @@ for l in open('$O/bench_n$N.json'):
         for r in d.get('per_rank', []): print(r['rank'], r['z'], r['nv'], r['nf'], {k: round(v,3) for k,v in r['stage_ms'].items() if v})
         print({k:(v.get('ms_per_step'), v.get('value')) for k,v in d['other_configs'].items()})
 PY
+if [ "${AB_FINISH:-0}" = "1" ]; then
+for extra in "finish_split=0" "finish_split=1"; do echo "== $extra"; python tools/one_step.py c4 1024 --ob02 --warm 3 --gpu kernel_times=1 $extra 2>&1 | tail -3 | cut -c1-400; done
+timeout 600 python -m pytest tests/test_gpu_ob02.py -m gpu -x -q -k "pair_kernels" 2>&1 | tail -3
+fi
