@@ -354,15 +354,18 @@ def main():
     cfg = cfgs[HEADLINE]
     R = cfg["R"]
     voxels = float(R) ** 3
-    mc_timed = settings(cfg, kernel_times=1)
+    mc_dev = settings(cfg)                      # the timed region: default settings, nothing but the path's own kernels in the stream
+    mc_timed = settings(cfg, kernel_times=1)    # the instrumented region: a pair of events around every launch (+4 % per step)
     sampler = ClockSampler(local_rank)
     sampler.start()
     for _ in range(2):      # first builds allocate; not part of the warm-up count
-        lib.build_geometry_device(cfg["shape"], mc_timed)
+        lib.build_geometry_device(cfg["shape"], mc_dev)
         lib.finish_geometry()
     barrier()
     sampler.rows.clear()
-    ms_per_step, stages, kernels, launches = timed_device_steps(cfg, mc_timed, args.steps, args.warmup)
+    ms_per_step, stages, _, launches = timed_device_steps(cfg, mc_dev, args.steps, args.warmup)
+    # the same steps again with per-kernel events: the kernels' durations are the same, the step is longer by the event records
+    ms_instrumented, _, kernels, _ = timed_device_steps(cfg, mc_timed, args.steps, 3)
     # keep the same load up until the region is >= 0.5 s long, so that nvidia-smi (100 ms period) has samples of it; the
     # count comes from the reduced time, so every rank runs the same number of collectives.  Timed as one block, no flush.
     extra = int(min(5000, max(0, math.ceil((600.0 - ms_per_step * args.steps) / max(ms_per_step, 0.05)))))
@@ -373,7 +376,7 @@ def main():
         with torch.cuda.stream(stream):
             e0.record(stream)
             for _ in range(extra):
-                lib.build_geometry_device(cfg["shape"], mc_timed)
+                lib.build_geometry_device(cfg["shape"], mc_dev)
                 lib.finish_geometry()
             e1.record(stream)
         barrier()
@@ -385,7 +388,7 @@ def main():
     # every build) and never wait for the device in mid-step; every kernel still runs on every step.  The same steps with that
     # switched off ("gpu":{"speculate":0}: the host waits for the device's counts three times per step) are reported beside them.
     speculative_builds = counters["speculative"]
-    ms_waiting, _, _, _ = timed_device_steps(cfg, settings(cfg, kernel_times=1, speculate=0), max(3, min(args.steps, 20)), 3)
+    ms_waiting, _, _, _ = timed_device_steps(cfg, settings(cfg, speculate=0), max(3, min(args.steps, 20)), 3)
     prog = lib.last_program_stats()
     slab = lib.last_slab()
     per_rank = gather_all({"rank": rank, "stage_ms": stages, "nv": slab["nv"], "nf": slab["nf"], "z": [slab["z_begin"], slab["z_end"]],
@@ -493,7 +496,7 @@ def main():
     }
     per_kernel = {}
     for k, (ms, n) in sorted(kernels.items(), key=lambda kv: -kv[1][0]):
-        e = {"ms_per_step": ms, "launches_per_step": n, "share_of_step": ms / ms_per_step}
+        e = {"ms_per_step": ms, "launches_per_step": n, "share_of_step": ms / ms_instrumented}
         if k in flops and ms > 0:
             tf = flops[k] / (ms * 1e-3) / 1e12
             e.update({"bound": "fp32", "achieved": tf, "peak": fp_peak, "unit": "TFLOP/s", "frac": tf / fp_peak if fp_peak else None,
@@ -527,7 +530,10 @@ def main():
             "mesh": {"nv": slab["global_nv"] if world > 1 else slab["nv"], "nf": slab["global_nf"] if world > 1 else slab["nf"],
                      "grid_nodes_per_gpu": counters["nodes"], "nodes_full_eval_rank0": counters["nodes_full_eval"], "cut_cubes_rank0": cut,
                      "tree_nodes": prog["nodes"], "flops_per_node_whole_tree": prog["flops_per_point"]},
-            "timed_region_ms": ms_per_step * args.steps, "sustained": {"ms_per_step": sustained_ms, "steps": extra, "l2": "not flushed, back to back"},
+            "timed_region_ms": ms_per_step * args.steps,
+            "instrumented": {"ms_per_step": ms_instrumented, "steps": args.steps, "what": "the timed steps repeated with a pair of CUDA events around every "
+                             "launch (\"gpu\":{\"kernel_times\":1}); `kernels` and `roofline` come from this region, `value` from the plain one"},
+            "sustained": {"ms_per_step": sustained_ms, "steps": extra, "l2": "not flushed, back to back"},
             "stage_ms": stages, "dominant_stage": dominant_stage, "roofline": roofline, "kernels": per_kernel, "roofline_mc_conventional": roof_mc,
             "counters": {"projection_by_type": e2e_counters["projection_by_type"], "projection_failed": e2e_counters["projection_failed"],
                          "bisection_capped": e2e_counters["bisection_capped"], "bisected": e2e_counters["bisected"], "scope": "rank 0's slab + halo" if world > 1 else "whole mesh"},

@@ -124,7 +124,7 @@ struct Context {
     PinnedBuffer h_normals;
     bool normals_valid = false, normals_host_valid = false;
     bool point_spec_on = false;             // the OB02 kernels may use K1's tile masks (c_point_spec describes the current program)
-    bool finish_split = true;               // "gpu":{"finish_split":1}: the pair path's projection finish as classify / bisect-the-list / gradients
+    int finish_split = 0;                   // "gpu":{"finish_split":..}: the pair path's projection finish; 0 one kernel, 1 bisect batches of 32 units + gradients, 2 bisect with lane refill + gradients
     bool pair_kernels = true;               // "gpu":{"pair":1}: with point lists, two centroids per thread through the f32x2 interpreters
     std::vector<uint32_t> last_program;     // the shape program of the last build (lazy normals re-upload it)
     isd_progress_fn progress_fn = nullptr;
@@ -996,7 +996,8 @@ void projection_step(bool enable_qem, bool exact_reduce, int repeat) {
     // k_project_finish: one kernel, or (pair path) bisect from per-warp queues -> gradients of all
     auto finish_pass = [&](const ProjectArgs& pa) {
         if (pairs && g.finish_split) {
-            ISD_TIMED(KT_FINISH, k_finish_bisect_units<<<blocks_for((nf + 1) / 2, 4 * kFinishRange), 128, 0, g.stream>>>(g.sdf, pa));
+            if (g.finish_split == 2) ISD_TIMED(KT_FINISH, k_finish_bisect_refill<<<blocks_for((nf + 1) / 2, 4 * kRefillRange), 128, 0, g.stream>>>(g.sdf, pa));
+            else ISD_TIMED(KT_FINISH, k_finish_bisect_units<<<blocks_for((nf + 1) / 2, 4 * kFinishRange), 128, 0, g.stream>>>(g.sdf, pa));
             ISD_TIMED(KT_FINISH, k_unit_gradients_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, pa.out, nf, pa.nrm_out,
                                                                                                             pa.speculative ? pa.counters : nullptr));
         } else if (pairs) {
@@ -1246,7 +1247,7 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
     for (int64_t& c : g.counters) c = 0;
     g.launches = 0;
     g.pair_kernels = s.pair != 0;
-    g.finish_split = s.finish_split != 0;
+    g.finish_split = s.finish_split;
     g_kt.reset(s.kernel_times != 0);
     g_kt.start_counting(s.count_flops != 0);
     g.host_valid = false;

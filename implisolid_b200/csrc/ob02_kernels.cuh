@@ -1039,6 +1039,134 @@ __global__ void __launch_bounds__(128, ISD_FINISH_UNITS_MINBLOCKS) k_finish_bise
         if (n_bisect) atomicAdd(&a.counters->c[9], (unsigned long long)n_bisect);
     }
 }
+// The same pass with LANE REFILL ("gpu":{"finish_split":2}).  In k_project_finish_pair a lane bisects for as long as the slowest
+// centroid of its warp (ncu, C4 1024^3: 13.7 of 32 lanes active in the bisection part); the batch form above fills all lanes at the
+// start of a batch but still runs every batch to its slowest member.  Here a lane that has finished its unit takes the next one
+// from the warp's queue at once, so every evaluation runs with (nearly) all lanes busy; the queue is topped up from the warp's
+// range of units, 32 classified at a time, whenever fewer units wait than lanes are idle.  Per centroid the sequence of
+// midpoints, tests and the iteration cap are those of k_project_finish.
+constexpr int kRefillRange = 512;      // units per warp
+#ifndef ISD_FINISH_REFILL_MINBLOCKS
+#define ISD_FINISH_REFILL_MINBLOCKS 5
+#endif
+__global__ void __launch_bounds__(128, ISD_FINISH_REFILL_MINBLOCKS) k_finish_bisect_refill(SdfGridView sdf, ProjectArgs a) {
+    if (a.speculative && a.counters->c[10] != 0ull) return;
+    __shared__ int s_queue[4][128];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int* queue = s_queue[warp];
+    const int n_units = (a.n + 1) / 2;
+    const long long first = ((long long)blockIdx.x * 4 + warp) * kRefillRange;
+    const long long last = first + kRefillRange < (long long)n_units ? first + kRefillRange : (long long)n_units;
+    long long next = first;
+    int head = 0, waiting = 0;
+    unsigned n_failed = 0u, n_bisect = 0u;
+    int entry = -1, it = 0;      // this lane's unit (u << 2 | members that bisect), or -1: idle
+    bool active[2] = {false, false};
+    float x1[2][3], x2[2][3];
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+#pragma unroll
+        for (int q = 0; q < 3; ++q) { x1[k][q] = 0.0f; x2[k][q] = 0.0f; }
+    for (;;) {
+        const unsigned idle = __ballot_sync(0xffffffffu, entry < 0);
+        const int n_idle = __popc(idle);
+        while (waiting < n_idle && next < last) {      // classify the next 32 units of the range
+            const long long u = next + lane;
+            int needs = 0;
+            if (u < last) {
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    const long long i = 2 * u + k;
+                    if (i >= (long long)a.n) break;
+                    const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
+                    const bool already = (a.state[i] & 1) != 0;
+                    const float fc = a.fc[i];
+                    float bx = cx, by = cy, bz = cz, f2 = fc;      // no candidate: the reference evaluates the centroid again
+                    if (already) {
+                        const float4 b = a.best[i];
+                        bx = b.x; by = b.y; bz = b.z; f2 = b.w;    // f at the candidate, from the search that found it
+                    }
+                    const bool zeros2 = fabsf(f2) <= kRootTolerance;
+                    const bool zeros1 = fabsf(fc) <= kRootTolerance;
+                    if (zeros1) { bx = cx; by = cy; bz = cz; }
+                    const bool zeros12 = zeros2 || zeros1;
+                    const bool bisect = already && !zeros12;
+                    if (!bisect) {
+                        float ox = cx, oy = cy, oz = cz;
+                        if (zeros12) { ox = bx; oy = by; oz = bz; }
+                        a.out[i * 3] = ox; a.out[i * 3 + 1] = oy; a.out[i * 3 + 2] = oz;
+                    }
+                    if (!already) ++n_failed;
+                    if (bisect) { ++n_bisect; needs |= 1 << k; }
+                }
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, needs != 0);
+            if (needs) queue[(head + waiting + __popc(m & ((1u << lane) - 1u))) & 127] = (int)(u << 2) | needs;
+            waiting += __popc(m);
+            next += 32;
+            __syncwarp();
+        }
+        if (entry < 0) {      // idle lanes take the waiting units in lane order
+            const int r = __popc(idle & ((1u << lane) - 1u));
+            if (r < waiting) {
+                entry = queue[(head + r) & 127];
+                it = 1;
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    active[k] = ((entry >> k) & 1) != 0;
+                    if (!active[k]) continue;
+                    const long long i = 2ll * (entry >> 2) + k;
+                    const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
+                    const float4 b = a.best[i];
+                    x1[k][0] = cx; x1[k][1] = cy; x1[k][2] = cz; x2[k][0] = b.x; x2[k][1] = b.y; x2[k][2] = b.z;
+                    if (b.w < -kRootTolerance) { x1[k][0] = b.x; x1[k][1] = b.y; x1[k][2] = b.z; x2[k][0] = cx; x2[k][1] = cy; x2[k][2] = cz; }
+                }
+            }
+        }
+        {
+            const int taken = waiting < n_idle ? waiting : n_idle;
+            head = (head + taken) & 127;
+            waiting -= taken;
+        }
+        __syncwarp();
+        if (__ballot_sync(0xffffffffu, entry >= 0) == 0u) break;      // no unit in flight, none waiting, range exhausted
+        if (entry >= 0) {      // one bisection step of this lane's unit
+            float m[2][3];
+#pragma unroll
+            for (int k = 0; k < 2; ++k)
+#pragma unroll
+                for (int q = 0; q < 3; ++q) m[k][q] = (x1[k][q] + x2[k][q]) / 2.0f;
+            if (!active[0]) { m[0][0] = m[1][0]; m[0][1] = m[1][1]; m[0][2] = m[1][2]; }
+            if (!active[1]) { m[1][0] = m[0][0]; m[1][1] = m[0][1]; m[1][2] = m[0][2]; }
+            const F2 f = eval_f_pair(sdf, m[0][0], m[0][1], m[0][2], m[1][0], m[1][1], m[1][2]);
+            const float v[2] = {f.x, f.y};
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                if (!active[k]) continue;
+                if (fabsf(v[k]) <= kRootTolerance || it >= kBisectionMaxIter) {
+                    if (fabsf(v[k]) > kRootTolerance) atomicAdd(&a.counters->c[8], 1ull);
+                    const long long i = 2ll * (entry >> 2) + k;
+                    a.out[i * 3] = m[k][0]; a.out[i * 3 + 1] = m[k][1]; a.out[i * 3 + 2] = m[k][2];
+                    active[k] = false;
+                    continue;
+                }
+                if (v[k] > kRootTolerance) { x2[k][0] = m[k][0]; x2[k][1] = m[k][1]; x2[k][2] = m[k][2]; }
+                if (v[k] < -kRootTolerance) { x1[k][0] = m[k][0]; x1[k][1] = m[k][1]; x1[k][2] = m[k][2]; }
+            }
+            ++it;
+            if (!active[0] && !active[1]) entry = -1;
+        }
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        n_failed += __shfl_xor_sync(0xffffffffu, n_failed, d);
+        n_bisect += __shfl_xor_sync(0xffffffffu, n_bisect, d);
+    }
+    if (lane == 0) {
+        if (n_failed) atomicAdd(&a.counters->c[7], (unsigned long long)n_failed);
+        if (n_bisect) atomicAdd(&a.counters->c[9], (unsigned long long)n_bisect);
+    }
+}
 // unit gradients at points 2t and 2t+1 (compute_centroid_gradient at the projected centroids, centroids_projection.cpp:1262)
 __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_unit_gradients_pair(SdfGridView sdf, const float* __restrict__ pts, int n, float* __restrict__ nrm,
                                                                                  const Ob02Counters* __restrict__ skip_if_leftovers) {

@@ -7,6 +7,7 @@ import argparse
 import ctypes
 import os
 import sys
+import time
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import implisolid_b200
@@ -40,11 +41,14 @@ for _ in range(a.warm):
 rt = ctypes.CDLL("libcudart.so.12")
 rt.cudaDeviceSynchronize()
 rt.cudaProfilerStart()
+t0 = time.perf_counter()
 for _ in range(a.reps):
     lib.build_geometry_device(sj, mc)
     lib.finish_geometry()
 rt.cudaDeviceSynchronize()
+wall_ms = (time.perf_counter() - t0) * 1e3 / a.reps
 rt.cudaProfilerStop()
+print("wall per build (host clock, %d builds back to back): %.4f ms" % (a.reps, wall_ms))
 c, t, s = lib.last_counters(), lib.last_timings(), lib.last_slab()
 kt = lib.last_kernel_times()
 if kt:
