@@ -996,10 +996,13 @@ void projection_step(bool enable_qem, bool exact_reduce, int repeat) {
     // k_project_finish: one kernel, or (pair path) bisect from per-warp queues -> gradients of all
     auto finish_pass = [&](const ProjectArgs& pa) {
         if (pairs && g.finish_split) {
-            if (g.finish_split == 2) ISD_TIMED(KT_FINISH, k_finish_bisect_refill<<<blocks_for((nf + 1) / 2, 4 * kRefillRange), 128, 0, g.stream>>>(g.sdf, pa));
+            if (g.finish_split == 2) {
+                const unsigned want = blocks_for((nf + 1) / 2, 4 * kRefillRange), resident = (unsigned)g.sm_count * ISD_FINISH_REFILL_MINBLOCKS;
+                ISD_TIMED(KT_FINISH, k_finish_bisect_refill<<<want < resident ? want : resident, 128, 0, g.stream>>>(g.sdf, pa));
+            }
             else ISD_TIMED(KT_FINISH, k_finish_bisect_units<<<blocks_for((nf + 1) / 2, 4 * kFinishRange), 128, 0, g.stream>>>(g.sdf, pa));
             ISD_TIMED(KT_FINISH, k_unit_gradients_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, pa.out, nf, pa.nrm_out,
-                                                                                                            pa.speculative ? pa.counters : nullptr));
+                                                                                                            pa.speculative ? pa.counters : nullptr, pa.state));
         } else if (pairs) {
             ISD_TIMED(KT_FINISH, k_project_finish_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, pa));
         } else {
@@ -1265,13 +1268,21 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
     g.prog_stats[3] = prog.value_depth;
     g.keep_field = true;
     run_marching_cubes(s, prog);                                   // polygonize_step_0
-    const bool any_ob02 = s.overall_repeats > 0 && (s.vresampl_iters > 0 || s.projection_enabled || s.subdiv_enabled);
+    bool any_ob02 = s.overall_repeats > 0 && (s.vresampl_iters > 0 || s.projection_enabled || s.subdiv_enabled);
+    bool skip_ob02 = false;
+    if (any_ob02 && g.world > 1 && g.emulate && !g.halo_mode) {
+        // An emulated rank has nobody to gather from: its slab's faces carry global vertex numbers, some of them owned by the slab
+        // below, so the replicated OB02 of a real run (gather_mesh() first) cannot be run on it.  The marching-cubes slab is returned.
+        fprintf(stderr, "implisolid_b200: emulated rank %d of %d without halo mode: OB02 needs the gathered mesh, returning the marching-cubes slab\n", g.rank, g.world);
+        any_ob02 = false;
+        skip_ob02 = true;
+    }
     if (any_ob02 && g.world > 1 && !g.emulate && !g.halo_mode) gather_mesh();      // OB02 runs on the stitched mesh, replicated
     const bool faces_final = !(s.overall_repeats > 0 && s.subdiv_enabled) && !g.progress_fn;
     if (copy_out && any_ob02 && faces_final && !g.halo_mode) start_faces_copy();
     report_progress();                                             // mcc2.cpp:351
     bool resample_timed = false, subdiv_timed = false;
-    for (int overall_iter = 0; overall_iter < s.overall_repeats; ++overall_iter) {
+    for (int overall_iter = 0; !skip_ob02 && overall_iter < s.overall_repeats; ++overall_iter) {
         if (s.vresampl_iters > 0) {
             cudaEvent_t ra = g.ev[4], rb = g.ev[5];
             if (g_spec_used) { ra = g_kt.get(); rb = g_kt.get(); }      // nobody waits in mid-build: private events, read at the end

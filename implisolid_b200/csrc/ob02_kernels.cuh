@@ -501,13 +501,26 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
     a.fc[i] = fc;
     // normalise_inplace(g, min_gradient_len)  normalise_inplace.hpp:19-58
     float norm = norm2f(g0, g1, g2);
+    const float norm_raw = norm, graw0 = g0, graw1 = g1, graw2 = g2;
     norm = (norm < kMinGradientLen) ? 1.0f : norm;
     const float factor = 1.0f / norm;
     g0 = g0 * factor; g1 = g1 * factor; g2 = g2 * factor;
     const float s_c = sign_tol(fc);
     if (s_c < 0.0f) { g0 = -g0; g1 = -g1; g2 = -g2; }
     const float d0 = -g0 * s_c, d1 = -g1 * s_c, d2 = -g2 * s_c;
-    bool ok = try_direction<MASKED>(sdf, cx, cy, cz, d0, d1, d2, edge, alphas, n_alpha_full, s_c, bx, by, bz, bf);
+    bool ok;
+    if (s_c == 0.0f && n_alpha_full > 0) {
+        // |f(centroid)| <= ROOT_TOLERANCE: the first trial point passes the reference's test whatever f is there (sign * 0 <= 0; the
+        // primitives are NaN-free on finite points), and k_project_finish returns the centroid itself without looking at the
+        // candidate or its value — so the trial evaluation is skipped.  The unit gradient the finish would take at its result is
+        // the one of this very point: it is written here (same operations on the same evaluation) and state bit 2 says so.
+        const float c = edge * __ldg(alphas);
+        bx = cx + c * d0; by = cy + c * d1; bz = cz + c * d2; bf = 0.0f;
+        ok = true;
+        a.nrm_out[i * 3] = graw0 / norm_raw; a.nrm_out[i * 3 + 1] = graw1 / norm_raw; a.nrm_out[i * 3 + 2] = graw2 / norm_raw;
+    } else {
+        ok = try_direction<MASKED>(sdf, cx, cy, cz, d0, d1, d2, edge, alphas, n_alpha_full, s_c, bx, by, bz, bf);
+    }
     int type = 0;
     if (!ok) {
         float nx, ny, nz;
@@ -517,7 +530,7 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
     }
     if (ok) {
         a.best[i] = make_float4(bx, by, bz, bf);
-        a.state[i] = 1;
+        a.state[i] = (s_c == 0.0f && n_alpha_full > 0) ? 5 : 1;
     } else {
         a.state[i] = 2;
     }
@@ -535,9 +548,11 @@ __global__ void __launch_bounds__(128) k_project_search(SdfGridView sdf, Project
     count_if(ok && type == 1, &a.counters->c[1]);
 }
 
-// Phase B: direction types 2..6 for the centroids phase A left over (rare; needs the host-generated noise).  One warp per
+// Phase B: direction types 2..6 for the centroids phase A left over (rare; needs the host-generated noise).  A group of lanes per
 // centroid: the candidates (five directions x the short alpha list, in the reference's order of trial) are independent
 // evaluations, so the lanes take one each and the first success in that order wins, as in the reference's sequential walk.
+// The group is the smallest of 8 / 16 / 32 lanes that holds all candidates at once (10 candidates at C4 1024^3, where the short
+// list has two alphas: two centroids per warp), else the whole warp in rounds of 32.
 template <bool MASKED>
 __global__ void __launch_bounds__(128) k_project_leftovers(SdfGridView sdf, ProjectArgs a, int n_left) {
     const int lane = threadIdx.x & 31;
@@ -549,8 +564,14 @@ __global__ void __launch_bounds__(128) k_project_leftovers(SdfGridView sdf, Proj
         const int listed = (int)a.counters->c[10];
         n_left = n_left < listed ? n_left : listed;
     }
-    for (int li = blockIdx.x * 4 + (threadIdx.x >> 5); li < n_left; li += gridDim.x * 4) {
-        const int i = a.leftover[li];
+    const int n_cand = 5 * n_short;
+    const int G = n_cand > 16 ? 32 : (n_cand > 8 ? 16 : 8), per_warp = 32 / G;
+    const int sub = lane / G, gl = lane - sub * G;
+    const unsigned gmask = G == 32 ? 0xffffffffu : ((1u << G) - 1u);
+    for (int l0 = (blockIdx.x * 4 + (threadIdx.x >> 5)) * per_warp; l0 < n_left; l0 += gridDim.x * 4 * per_warp) {
+        const int li = l0 + sub;
+        const bool valid = li < n_left;
+        const int i = valid ? a.leftover[li] : 0;
         const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
         const float s_c = sign_tol(a.fc[i]);
         float dir[5][3];
@@ -575,15 +596,14 @@ __global__ void __launch_bounds__(128) k_project_leftovers(SdfGridView sdf, Proj
     #pragma unroll
             for (int d = 0; d < 3; ++d) { dir[2 + d][0] = d == 0 ? 1.0f : 0.0f; dir[2 + d][1] = d == 1 ? 1.0f : 0.0f; dir[2 + d][2] = d == 2 ? 1.0f : 0.0f; }
         }
-        const int n_cand = 5 * n_short;
         bool ok = false;
         int type = -1;
         float bx = -10.0f, by = -10.0f, bz = -10.0f, bf = 0.0f;
-        for (int c0 = 0; c0 < n_cand && !ok; c0 += 32) {
-            const int c = c0 + lane;
+        for (int c0 = 0; __any_sync(0xffffffffu, valid && !ok && c0 < n_cand); c0 += G) {
+            const int c = c0 + gl;
             bool mine = false;
             float x = 0.0f, y = 0.0f, z = 0.0f, f = 0.0f;
-            if (c < n_cand) {
+            if (valid && !ok && c < n_cand) {
                 const int d = c / n_short, ai = c - d * n_short;
                 float dx = 0.0f, dy = 0.0f, dz = 0.0f;
     #pragma unroll
@@ -594,16 +614,17 @@ __global__ void __launch_bounds__(128) k_project_leftovers(SdfGridView sdf, Proj
                 f = eval_f<MASKED>(sdf, x, y, z);
                 mine = sign_tol(f) * s_c <= 0.0f;
             }
-            const unsigned m = __ballot_sync(0xffffffffu, mine);
-            if (m) {
-                const int w = __ffs(m) - 1;
-                bx = __shfl_sync(0xffffffffu, x, w); by = __shfl_sync(0xffffffffu, y, w); bz = __shfl_sync(0xffffffffu, z, w);
-                bf = __shfl_sync(0xffffffffu, f, w);
+            const unsigned m = (__ballot_sync(0xffffffffu, mine) >> (sub * G)) & gmask;
+            const int w = m ? __ffs(m) - 1 : 0, src = sub * G + w;
+            const float sx = __shfl_sync(0xffffffffu, x, src), sy = __shfl_sync(0xffffffffu, y, src), sz = __shfl_sync(0xffffffffu, z, src);
+            const float sf = __shfl_sync(0xffffffffu, f, src);
+            if (m && !ok) {
+                bx = sx; by = sy; bz = sz; bf = sf;
                 type = 2 + (c0 + w) / n_short;
                 ok = true;
             }
         }
-        if (lane == 0) {
+        if (gl == 0 && valid) {
             if (ok) {
                 a.best[i] = make_float4(bx, by, bz, bf);
                 a.state[i] = 1;
@@ -654,6 +675,7 @@ __global__ void __launch_bounds__(128) k_project_finish(SdfGridView sdf, Project
     }
     if (zeros12) { ox = bx; oy = by; oz = bz; }
     a.out[i * 3] = ox; a.out[i * 3 + 1] = oy; a.out[i * 3 + 2] = oz;
+    if (a.state[i] & 4) return;      // the result is the centroid and the search has written the unit gradient there
     float f, g0, g1, g2;
     eval_fg<MASKED>(sdf, ox, oy, oz, f, g0, g1, g2);
     const float norm = norm2f(g0, g1, g2);
@@ -767,7 +789,7 @@ __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_project_search_pair
     const float* alphas = a.al->alpha;
     const int n_alpha_full = a.al->n_full, n_alpha_short = a.al->n_short;
     float c[2][3], d[2][3], s_c[2], best[2][4];
-    bool ok[2] = {false, false};
+    bool ok[2] = {false, false}, settled[2] = {false, false};
     int type[2] = {0, 0};
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
@@ -789,6 +811,15 @@ __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_project_search_pair
             s_c[k] = sign_tol(fc[k]);
             if (s_c[k] < 0.0f) { g0 = -g0; g1 = -g1; g2 = -g2; }
             d[k][0] = -g0 * s_c[k]; d[k][1] = -g1 * s_c[k]; d[k][2] = -g2 * s_c[k];
+            if (s_c[k] == 0.0f && n_alpha_full > 0) {      // see k_project_search: no trial evaluation, the unit gradient is final
+                const float cc = edge * __ldg(alphas);
+                best[k][0] = c[k][0] + cc * d[k][0]; best[k][1] = c[k][1] + cc * d[k][1]; best[k][2] = c[k][2] + cc * d[k][2]; best[k][3] = 0.0f;
+                ok[k] = true; settled[k] = true;
+                if (k == 0 || two) {
+                    const float nr = norm2f(g[k][0], g[k][1], g[k][2]);
+                    a.nrm_out[idx[k] * 3] = g[k][0] / nr; a.nrm_out[idx[k] * 3 + 1] = g[k][1] / nr; a.nrm_out[idx[k] * 3 + 2] = g[k][2] / nr;
+                }
+            }
         }
     }
     for (int phase = 0; phase < 2; ++phase) {
@@ -824,7 +855,7 @@ __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_project_search_pair
         if (k == 1 && !two) break;
         if (ok[k]) {
             a.best[idx[k]] = make_float4(best[k][0], best[k][1], best[k][2], best[k][3]);
-            a.state[idx[k]] = 1;
+            a.state[idx[k]] = settled[k] ? 5 : 1;
         } else {
             a.state[idx[k]] = 2;
         }
@@ -903,13 +934,18 @@ __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_project_finish_pair
             if (v[k] < -kRootTolerance) { x1[k][0] = m[k][0]; x1[k][1] = m[k][1]; x1[k][2] = m[k][2]; }
         }
     }
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        if (k == 1 && !two) break;
+        a.out[idx[k] * 3] = o[k][0]; a.out[idx[k] * 3 + 1] = o[k][1]; a.out[idx[k] * 3 + 2] = o[k][2];
+    }
+    if ((a.state[idx[0]] & 4) && (a.state[idx[1]] & 4)) return;      // both unit gradients were written by the search
     const FG2 r = eval_fg_pair(sdf, o[0][0], o[0][1], o[0][2], o[1][0], o[1][1], o[1][2]);
     const float g[2][3] = {{r.g0.x, r.g1.x, r.g2.x}, {r.g0.y, r.g1.y, r.g2.y}};
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
         if (k == 1 && !two) break;
         const int i = idx[k];
-        a.out[i * 3] = o[k][0]; a.out[i * 3 + 1] = o[k][1]; a.out[i * 3 + 2] = o[k][2];
         const float norm = norm2f(g[k][0], g[k][1], g[k][2]);
         a.nrm_out[i * 3] = g[k][0] / norm; a.nrm_out[i * 3 + 1] = g[k][1] / norm; a.nrm_out[i * 3 + 2] = g[k][2] / norm;
     }
@@ -1045,19 +1081,21 @@ __global__ void __launch_bounds__(128, ISD_FINISH_UNITS_MINBLOCKS) k_finish_bise
 // from the warp's queue at once, so every evaluation runs with (nearly) all lanes busy; the queue is topped up from the warp's
 // range of units, 32 classified at a time, whenever fewer units wait than lanes are idle.  Per centroid the sequence of
 // midpoints, tests and the iteration cap are those of k_project_finish.
-constexpr int kRefillRange = 512;      // units per warp
+constexpr int kRefillRange = 128;      // units per ticket
 #ifndef ISD_FINISH_REFILL_MINBLOCKS
-#define ISD_FINISH_REFILL_MINBLOCKS 5
+#define ISD_FINISH_REFILL_MINBLOCKS 6
 #endif
+// Persistent grid (one block per resident slot); a warp draws ranges of kRefillRange units from a ticket (counters->c[11], zeroed
+// with the other counters at the start of the projection step) for as long as it has idle lanes, so lanes stay busy across range
+// boundaries and only the very end of the kernel runs with part of the lanes.
 __global__ void __launch_bounds__(128, ISD_FINISH_REFILL_MINBLOCKS) k_finish_bisect_refill(SdfGridView sdf, ProjectArgs a) {
     if (a.speculative && a.counters->c[10] != 0ull) return;
     __shared__ int s_queue[4][128];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int* queue = s_queue[warp];
-    const int n_units = (a.n + 1) / 2;
-    const long long first = ((long long)blockIdx.x * 4 + warp) * kRefillRange;
-    const long long last = first + kRefillRange < (long long)n_units ? first + kRefillRange : (long long)n_units;
-    long long next = first;
+    const long long n_units = ((long long)a.n + 1) / 2;
+    long long next = 0, last = 0;
+    bool exhausted = false;
     int head = 0, waiting = 0;
     unsigned n_failed = 0u, n_bisect = 0u;
     int entry = -1, it = 0;      // this lane's unit (u << 2 | members that bisect), or -1: idle
@@ -1070,7 +1108,15 @@ __global__ void __launch_bounds__(128, ISD_FINISH_REFILL_MINBLOCKS) k_finish_bis
     for (;;) {
         const unsigned idle = __ballot_sync(0xffffffffu, entry < 0);
         const int n_idle = __popc(idle);
-        while (waiting < n_idle && next < last) {      // classify the next 32 units of the range
+        while (waiting < n_idle && !exhausted) {      // classify the next 32 units
+            if (next >= last) {      // draw another range
+                unsigned long long t = 0ull;
+                if (lane == 0) t = atomicAdd(&a.counters->c[11], 1ull);
+                t = __shfl_sync(0xffffffffu, t, 0);
+                next = (long long)t * kRefillRange;
+                last = next + kRefillRange < n_units ? next + kRefillRange : n_units;
+                if (next >= n_units) { exhausted = true; break; }
+            }
             const long long u = next + lane;
             int needs = 0;
             if (u < last) {
@@ -1169,12 +1215,14 @@ __global__ void __launch_bounds__(128, ISD_FINISH_REFILL_MINBLOCKS) k_finish_bis
 }
 // unit gradients at points 2t and 2t+1 (compute_centroid_gradient at the projected centroids, centroids_projection.cpp:1262)
 __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_unit_gradients_pair(SdfGridView sdf, const float* __restrict__ pts, int n, float* __restrict__ nrm,
-                                                                                 const Ob02Counters* __restrict__ skip_if_leftovers) {
+                                                                                 const Ob02Counters* __restrict__ skip_if_leftovers,
+                                                                                 const unsigned char* __restrict__ state) {
     const int ia = (blockIdx.x * 128 + threadIdx.x) * 2;
     if (ia >= n) return;
     if (skip_if_leftovers != nullptr && skip_if_leftovers->c[10] != 0ull) return;
     const bool two = ia + 1 < n;
     const int ib = two ? ia + 1 : ia;
+    if (state != nullptr && (state[ia] & 4) && (state[ib] & 4)) return;      // both written by the search (state bit 2, k_project_search)
     const FG2 r = eval_fg_pair(sdf, pts[ia * 3], pts[ia * 3 + 1], pts[ia * 3 + 2], pts[ib * 3], pts[ib * 3 + 1], pts[ib * 3 + 2]);
     {
         const float norm = norm2f(r.g0.x, r.g1.x, r.g2.x);

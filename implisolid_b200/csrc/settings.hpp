@@ -41,7 +41,8 @@ struct McSettings {
                           // bounds-only pass every rank repeats identically); 0: equal numbers of cube layers (SURVEY §8e's formula)
     int pair;             // 1 (default): with per-tile point lists the OB02 kernels take two centroids per thread through the packed f32x2
                           // interpreters (same bits); 0: one centroid per thread
-    int finish_split;     // 0 (default): one kernel; 1: pair path only — the projection's finish runs as bisect-from-warp-queues, then gradients of all
+    int finish_split;     // pair path only, the projection's finish: 2 (default) bisection with lane refill from per-warp queues, then the
+                          // gradients of all; 1: bisection in batches of 32 units, then gradients; 0: one kernel (two centroids per thread in lockstep)
     int speculate;        // 1 (default): a build of the spec the previous build had takes that build's counts (mesh size, cut cubes, left-over
                           // centroids) instead of waiting for the device in mid-step; the counts are checked when the build ends and a
                           // mismatch drops the result and builds again the waiting way; 0: always wait
@@ -113,7 +114,7 @@ inline McSettings parse_mc_settings(const char* json) {
     s.point_spec = d.get_int("gpu.point_spec", -1);
     s.balance = d.get_int("gpu.balance", 1);
     s.pair = d.get_int("gpu.pair", 1);
-    s.finish_split = d.get_int("gpu.finish_split", 0);
+    s.finish_split = d.get_int("gpu.finish_split", 2);
     s.speculate = d.get_int("gpu.speculate", 1);
     if (s.qem_enabled && !s.projection_enabled) {
         fprintf(stderr, "Invalid settings: QEM will not be applied if centroid projection is disabled\n");
