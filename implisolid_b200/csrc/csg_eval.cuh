@@ -33,6 +33,18 @@
 
 namespace isd {
 
+// The interpreters read list entry k + 1 while they execute entry k (one register): the loads of an instruction's matrix then
+// depend on a value that is already there instead of on a load issued in the same iteration.
+#ifndef ISD_LIST_PREFETCH
+#define ISD_LIST_PREFETCH 1
+#endif
+#if ISD_LIST_PREFETCH
+#define ISD_LIST_FIRST(list, n) uint32_t e_next__ = (n) > 0 ? (list)[0] : 0u
+#define ISD_LIST_ENTRY(list, n, k) const uint32_t e = e_next__; if ((k) + 1 < (n)) e_next__ = (list)[(k) + 1]
+#else
+#define ISD_LIST_FIRST(list, n) do {} while (0)
+#define ISD_LIST_ENTRY(list, n, k) const uint32_t e = (list)[k]
+#endif
 struct SdfGridView {          // HEAD-literal cube (cube.hpp:65-72): table lives in global memory
     const float* v;
     int nx, ny, nz;
@@ -414,8 +426,9 @@ ISD_HD void eval_values_list2(const Prog& prog, const SdfGridView& sdf, const Li
 #pragma unroll
     for (int p = 0; p < NP; ++p) { t0[p] = splat(0.0f); t1[p] = splat(0.0f); }
     int sp = 0, fp = 0;
+    ISD_LIST_FIRST(list, n_list);
     for (int k = 0; k < n_list; ++k) {
-        const uint32_t e = list[k];
+        ISD_LIST_ENTRY(list, n_list, k);
         int pc = (int)(e & IT_PC_MASK) * 4;
         if (e & LE_CLOSING) {
             if (e & LE_COMBINE) {
@@ -737,8 +750,9 @@ ISD_HD void eval_values_list(const Prog& prog, const SdfGridView& sdf, const Lis
 #pragma unroll
     for (int p = 0; p < P; ++p) { t0[p] = 0.0f; t1[p] = 0.0f; }
     int sp = 0, fp = 0;
+    ISD_LIST_FIRST(list, n_list);
     for (int k = 0; k < n_list; ++k) {
-        const uint32_t e = list[k];
+        ISD_LIST_ENTRY(list, n_list, k);
         int pc = (int)(e & IT_PC_MASK) * 4;
         if (e & LE_CLOSING) {
             if (e & LE_COMBINE) {
@@ -966,8 +980,9 @@ ISD_HD void eval_value_gradient_list(const Prog& prog, const SdfGridView& sdf, c
     float fs[kMaxFrameStack][3];
     float tf = 0.0f, t0 = 0.0f, t1 = 0.0f, t2 = 0.0f;
     int sp = 0, fp = 0;
+    ISD_LIST_FIRST(list, n_list);
     for (int k = 0; k < n_list; ++k) {
-        const uint32_t e = list[k];
+        ISD_LIST_ENTRY(list, n_list, k);
         const int pc = (int)(e & IT_PC_MASK) * 4;
         Mat12<Prog> M;
         M.load(prog, pc + 4);
@@ -1073,8 +1088,9 @@ ISD_HD void eval_value_gradient_list2(const Prog& prog, const SdfGridView& sdf, 
     F2 fs[kMaxFrameStack][3];
     F2 tf = splat(0.0f), t0 = splat(0.0f), t1 = splat(0.0f), t2 = splat(0.0f);
     int sp = 0, fp = 0;
+    ISD_LIST_FIRST(list, n_list);
     for (int k = 0; k < n_list; ++k) {
-        const uint32_t e = list[k];
+        ISD_LIST_ENTRY(list, n_list, k);
         const int pc = (int)(e & IT_PC_MASK) * 4;
         Mat12<Prog> M;
         M.load(prog, pc + 4);

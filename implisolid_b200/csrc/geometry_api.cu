@@ -344,15 +344,49 @@ void slab_layers(int S, int rank, int world, int* z_begin, int* z_end) {
 // Slab boundaries that follow the surface (gpu.balance): cube layers weighted by the number of surface tiles in their layer of
 // tiles (k_balance_hist over the whole grid) plus a small uniform term for the per-layer fixed costs; rank r gets the layers
 // whose cumulative weight falls in [r, r+1) / world of the total.  Deterministic and identical on every rank.
+//
+// Feedback (real NCCL runs in halo mode, repeated builds of one spec).  Equal surface is not equal work: where the projection's
+// first direction fails, warps walk the whole alpha list and phase B runs (C4 1024^3 on two GPUs: 2.28 against 2.83 ms of kernels
+// per step with equal surface, the lighter rank idling in the step's collective).  Every build measures its own busy time (device
+// time of the build minus the time spent inside the collective) and sends the previous build's along in the step's one
+// all-gather (a fourth word beside {nv, nf, edge sum}), tagged with the generation of the cuts it was measured under.  Once every
+// rank has reported a time for the current cuts and they differ by more than kRecutThreshold, each layer's weight is multiplied by
+// its owner's measured cost per unit of weight and the cuts are drawn again — the same table on every rank, hence the same cuts.
+// At most kMaxRecuts times per (shape, grid, world); a build after a re-cut has a new slab and does not speculate.
+constexpr int kGatherWords = 4;            // per rank: nv, nf, fixed-point edge sum, busy word
+constexpr int kMaxRecuts = 8;
+constexpr double kRecutThreshold = 1.03;
+struct BalanceState {
+    std::vector<uint32_t> key;
+    std::vector<int> cuts;
+    std::vector<unsigned long long> weight;      // per cube layer, current (after feedback)
+    int gen = 0, recuts = 0;
+    long long my_busy_us = 0; int my_busy_gen = -1;      // this rank's last completed build
+    std::vector<long long> table_busy; std::vector<int> table_gen;      // what the last gather said about every rank
+} g_bal;
+
+// `shift` = 16 for the weights as first computed (whole numbers << 16: the cuts are those of the unscaled integers, which
+// implisolid_b200/slabs.py mirrors), 0 once feedback factors have been multiplied in
+void draw_cuts(int layers, int world, int shift) {
+    std::vector<unsigned long long> cum((size_t)layers + 1, 0ull);
+    for (int l = 0; l < layers; ++l) cum[(size_t)l + 1] = cum[(size_t)l] + (g_bal.weight[(size_t)l] >> shift);
+    g_bal.cuts.assign((size_t)world + 1, 0);
+    g_bal.cuts[(size_t)world] = layers;
+    for (int r = 1; r < world; ++r) {
+        const unsigned long long target = cum[(size_t)layers] * (unsigned long long)r / (unsigned long long)world;
+        int l = g_bal.cuts[(size_t)r - 1] + 1;                                   // at least one layer per rank
+        while (l < layers - (world - r) && cum[(size_t)l] < target) ++l;
+        g_bal.cuts[(size_t)r] = l;
+    }
+}
+
 void balanced_layers(const McSettings& s, const ShapeCompiler::Program& prog, int* z_begin, int* z_end) {
     const int S = g.grid.S, layers = S - 3, world = g.world, bins = (S + 7) / 8;
-    static std::vector<int> cuts;          // the partition of the last (shape, grid, world): emulated ranks ask one after the other
-    static std::vector<uint32_t> cut_key;
     std::vector<uint32_t> key(prog.bounds);
     const float boxv[6] = {s.box.xmin, s.box.xmax, s.box.ymin, s.box.ymax, s.box.zmin, s.box.zmax};
     for (float v : boxv) { uint32_t w; memcpy(&w, &v, 4); key.push_back(w); }
     key.push_back((uint32_t)S); key.push_back((uint32_t)world);
-    if (key != cut_key) {
+    if (key != g_bal.key) {
         GridDesc full = g.grid;
         full.z0 = 0; full.nz = S;
         full.tx = full.pitch / 8; full.ty = (S + 7) / 8; full.tz = (S + 7) / 8;
@@ -368,24 +402,46 @@ void balanced_layers(const McSettings& s, const ShapeCompiler::Program& prog, in
         std::vector<unsigned> hist((size_t)bins);
         ISD_CUDA(cudaMemcpyAsync(hist.data(), d_hist, hist_bytes, cudaMemcpyDeviceToHost, g.stream));
         ISD_CUDA(cudaStreamSynchronize(g.stream));
-        // integer weights per cube layer: its bin's count, plus a uniform term worth a quarter of the mean (per-layer fixed costs)
+        // integer weights per cube layer: its bin's count, plus a uniform term worth a quarter of the mean (per-layer fixed costs);
+        // scaled by 2^16 so that the feedback factors keep their resolution
         unsigned long long total_bins = 0;
         for (unsigned h : hist) total_bins += h;
         const unsigned long long uniform = total_bins * 8ull / (4ull * (unsigned long long)layers) + 1ull;
-        std::vector<unsigned long long> cum((size_t)layers + 1, 0ull);
-        for (int l = 0; l < layers; ++l) cum[(size_t)l + 1] = cum[(size_t)l] + (unsigned long long)hist[(size_t)((l + 1) >> 3)] + uniform;
-        cuts.assign((size_t)world + 1, 0);
-        cuts[(size_t)world] = layers;
-        for (int r = 1; r < world; ++r) {
-            const unsigned long long target = cum[(size_t)layers] * (unsigned long long)r / (unsigned long long)world;
-            int l = cuts[(size_t)r - 1] + 1;                                   // at least one layer per rank
-            while (l < layers - (world - r) && cum[(size_t)l] < target) ++l;
-            cuts[(size_t)r] = l;
+        g_bal.weight.assign((size_t)layers, 0ull);
+        for (int l = 0; l < layers; ++l) g_bal.weight[(size_t)l] = ((unsigned long long)hist[(size_t)((l + 1) >> 3)] + uniform) << 16;
+        draw_cuts(layers, world, 16);
+        g_bal.key = key;
+        g_bal.gen = 0; g_bal.recuts = 0; g_bal.my_busy_gen = -1;
+        g_bal.table_busy.assign((size_t)world, 0); g_bal.table_gen.assign((size_t)world, -1);
+    } else if (s.balance >= 2 && !g.emulate && g_bal.recuts < kMaxRecuts && (int)g_bal.table_busy.size() == world) {
+        bool complete = true;
+        long long lo = 0, hi = 0, sum = 0;
+        for (int r = 0; r < world; ++r) {
+            if (g_bal.table_gen[(size_t)r] != g_bal.gen || g_bal.table_busy[(size_t)r] <= 0) { complete = false; break; }
+            const long long t = g_bal.table_busy[(size_t)r];
+            lo = (r == 0 || t < lo) ? t : lo; hi = (r == 0 || t > hi) ? t : hi; sum += t;
         }
-        cut_key = key;
+        if (complete && (double)hi * world > kRecutThreshold * (double)sum) {
+            for (int r = 0; r < world; ++r) {      // cost per unit of weight of rank r's slab, relative to the mean: x / 2^10 fixed point
+                unsigned long long w = 0;
+                for (int l = g_bal.cuts[(size_t)r]; l < g_bal.cuts[(size_t)r + 1]; ++l) w += g_bal.weight[(size_t)l] >> 16;
+                if (w == 0) continue;
+                // density_r / mean density = (t_r / w_r) / (sum t / sum w): integers only, the same on every rank
+                unsigned long long wsum = 0;
+                for (int l = 0; l < layers; ++l) wsum += g_bal.weight[(size_t)l] >> 16;
+                unsigned long long f = (unsigned long long)(((__int128)g_bal.table_busy[(size_t)r] * (__int128)wsum * 1024) / ((__int128)sum * (__int128)w));
+                f = f < 256 ? 256 : (f > 4096 ? 4096 : f);      // a quarter to four times: one noisy step must not fling the cuts away
+                for (int l = g_bal.cuts[(size_t)r]; l < g_bal.cuts[(size_t)r + 1]; ++l) {
+                    unsigned long long nw = (g_bal.weight[(size_t)l] >> 10) * f;
+                    g_bal.weight[(size_t)l] = nw > 0 ? nw : 1ull;
+                }
+            }
+            draw_cuts(layers, world, 0);
+            ++g_bal.gen; ++g_bal.recuts;
+        }
     }
-    *z_begin = 1 + cuts[(size_t)g.rank];
-    *z_end = 1 + cuts[(size_t)g.rank + 1];
+    *z_begin = 1 + g_bal.cuts[(size_t)g.rank];
+    *z_end = 1 + g_bal.cuts[(size_t)g.rank + 1];
 }
 
 void setup_grid(const McSettings& s, const ShapeCompiler::Program& prog) {
@@ -435,17 +491,26 @@ void setup_grid(const McSettings& s, const ShapeCompiler::Program& prog) {
 // The one collective of a z-slab step: every rank contributes {nv, nf, fixed-point edge-length sum of its own faces} (24 bytes);
 // afterwards d_gather holds the triples of all ranks in rank order and their copy is on its way to h_gather + 3.  `edge_sum`
 // (device, may be null = 0) is read in the stream, so the call can follow the kernel that produces it without a host wait.
-__global__ void k_pack_slab_triple(long long* __restrict__ dst, long long nv, long long nf, const unsigned long long* __restrict__ edge_sum) {
-    dst[0] = nv; dst[1] = nf; dst[2] = edge_sum ? (long long)*edge_sum : 0ll;
+__global__ void k_pack_slab_triple(long long* __restrict__ dst, long long nv, long long nf, const unsigned long long* __restrict__ edge_sum, long long busy_word) {
+    dst[0] = nv; dst[1] = nf; dst[2] = edge_sum ? (long long)*edge_sum : 0ll; dst[3] = busy_word;
 }
+// events around the collectives of the running build: the time between them is waiting for the other ranks, not work
+std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_gather_spans;
+cudaEvent_t g_ev_build_start = nullptr, g_ev_build_end = nullptr;
 void enqueue_slab_gather(const unsigned long long* d_edge_sum) {
-    g.d_gather.reserve(((size_t)g.world + 1) * 3 * sizeof(int64_t) + 64);
+    g.d_gather.reserve(((size_t)g.world + 1) * kGatherWords * sizeof(int64_t) + 64);
     int64_t* dg = g.d_gather.as<int64_t>();
     int64_t* hs = g.h_gather.as<int64_t>();
-    k_pack_slab_triple<<<1, 1, 0, g.stream>>>(reinterpret_cast<long long*>(dg + 3 * g.world), g.halo_counts[0], g.halo_counts[1], d_edge_sum);
+    // this rank's busy time of its previous build, tagged with the generation of the cuts it ran under (balanced_layers)
+    const long long busy_word = g_bal.my_busy_gen >= 0 ? (g_bal.my_busy_us & ((1ll << 40) - 1)) | ((long long)(g_bal.my_busy_gen + 1) << 40) : 0ll;
+    cudaEvent_t ea = g_kt.get(), eb = g_kt.get();
+    ISD_CUDA(cudaEventRecord(ea, g.stream));
+    k_pack_slab_triple<<<1, 1, 0, g.stream>>>(reinterpret_cast<long long*>(dg + kGatherWords * g.world), g.halo_counts[0], g.halo_counts[1], d_edge_sum, busy_word);
     ISD_LAUNCH_CHECK();
-    g.nccl.check(g.nccl.AllGather(dg + 3 * g.world, dg, 3, kNcclInt64, g.comm, g.stream), "ncclAllGather");
-    ISD_CUDA(cudaMemcpyAsync(hs + 3, dg, (size_t)g.world * 3 * sizeof(int64_t), cudaMemcpyDeviceToHost, g.stream));
+    g.nccl.check(g.nccl.AllGather(dg + kGatherWords * g.world, dg, kGatherWords, kNcclInt64, g.comm, g.stream), "ncclAllGather");
+    ISD_CUDA(cudaEventRecord(eb, g.stream));
+    g_gather_spans.push_back({ea, eb});
+    ISD_CUDA(cudaMemcpyAsync(hs + 3, dg, (size_t)g.world * kGatherWords * sizeof(int64_t), cudaMemcpyDeviceToHost, g.stream));
     g.halo_gather_enqueued = true;
 }
 
@@ -682,7 +747,7 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
             gnv = 0; gnf = 0;
             for (int r = 0; r < g.world; ++r) {
                 if (r == g.rank) { voff = gnv; foff = gnf; }
-                gnv += hs[3 + 3 * r]; gnf += hs[4 + 3 * r];
+                gnv += hs[3 + kGatherWords * r]; gnf += hs[4 + kGatherWords * r];
             }
         }
     }
@@ -742,7 +807,7 @@ void gather_mesh() {
     g.nccl.check(g.nccl.GroupStart(), "ncclGroupStart");
     long long vo = 0, fo = 0;
     for (int r = 0; r < g.world; ++r) {      // in place: every rank's slab already sits at its global offset
-        const long long rv = hs[3 + 3 * r], rf = hs[4 + 3 * r];
+        const long long rv = hs[3 + kGatherWords * r], rf = hs[4 + kGatherWords * r];
         float* pv = g.d_verts.as<float>() + vo * 3;
         int* pf = g.d_faces.as<int>() + fo * 3;
         if (rv > 0) g.nccl.check(g.nccl.Broadcast(pv, pv, (size_t)rv * 3, kNcclFloat32, r, g.comm, g.stream), "ncclBroadcast");
@@ -875,7 +940,7 @@ void resolve_halo_offsets() {
     long long voff = 0, foff = 0, gnv = 0, gnf = 0;
     for (int r = 0; r < g.world; ++r) {
         if (r == g.rank) { voff = gnv; foff = gnf; }
-        gnv += hs[3 + 3 * r]; gnf += hs[4 + 3 * r];
+        gnv += hs[3 + kGatherWords * r]; gnf += hs[4 + kGatherWords * r];
     }
     g.halo_pending = false;
     if (gnv >= (1ll << 31) || gnf >= (1ll << 31)) {
@@ -1267,6 +1332,9 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
     g.prog_stats[0] = prog.flops_per_point; g.prog_stats[1] = prog.num_nodes; g.prog_stats[2] = (double)prog.words.size();
     g.prog_stats[3] = prog.value_depth;
     g.keep_field = true;
+    if (!g_ev_build_start) { ISD_CUDA(cudaEventCreate(&g_ev_build_start)); ISD_CUDA(cudaEventCreate(&g_ev_build_end)); }
+    g_gather_spans.clear();
+    ISD_CUDA(cudaEventRecord(g_ev_build_start, g.stream));
     run_marching_cubes(s, prog);                                   // polygonize_step_0
     bool any_ob02 = s.overall_repeats > 0 && (s.vresampl_iters > 0 || s.projection_enabled || s.subdiv_enabled);
     bool skip_ob02 = false;
@@ -1312,8 +1380,27 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
         }
     }
     export_own_slab();
+    ISD_CUDA(cudaEventRecord(g_ev_build_end, g.stream));
     ISD_CUDA(cudaStreamSynchronize(g.stream));
     float ms = 0;
+    if (g.world > 1 && !g.emulate && g.halo_mode && !g_gather_spans.empty()) {
+        // feedback for the slab balance (balanced_layers): this build's busy time, and what the others reported in the gather.
+        // Only builds that did not wait for the device in mid-step count (the first build of a slab waits and allocates).
+        float total = 0, waited = 0;
+        ISD_CUDA(cudaEventElapsedTime(&total, g_ev_build_start, g_ev_build_end));
+        for (const auto& sp : g_gather_spans) { ISD_CUDA(cudaEventElapsedTime(&ms, sp.first, sp.second)); waited += ms; }
+        if (g_spec_used) {
+            g_bal.my_busy_us = (long long)((total - waited) * 1000.0f);
+            g_bal.my_busy_gen = g_bal.gen;
+        }
+        const int64_t* hs = g.h_gather.as<int64_t>();
+        if ((int)g_bal.table_busy.size() == g.world)
+            for (int r = 0; r < g.world; ++r) {
+                const long long w = hs[3 + kGatherWords * r + 3];
+                g_bal.table_busy[(size_t)r] = w & ((1ll << 40) - 1);
+                g_bal.table_gen[(size_t)r] = (int)(w >> 40) - 1;
+            }
+    }
     if (g_spec_used) {
         // What the device counted against what the build assumed.  A difference means arrays sized and grids launched for another
         // mesh: the result is dropped and the caller (grand_algorithm) builds again, waiting for the device at every step.
@@ -1709,7 +1796,7 @@ int isd_dist_init(int rank, int world, const uint8_t* id128) {
         fprintf(stderr, "implisolid_b200: isd_dist_init: rank %d / world %d out of range\n", rank, world);
         return 1;
     }
-    g.h_gather.reserve((size_t)(3 + 3 * world) * sizeof(int64_t));
+    g.h_gather.reserve((size_t)(3 + kGatherWords * world) * sizeof(int64_t));
     if (!g.nccl.load()) abort();
     NcclApi::unique_id id;
     memcpy(&id, id128, 128);

@@ -421,7 +421,7 @@ __global__ void k_alpha_from_sum(AlphaList* __restrict__ al, const unsigned long
 __global__ void k_alpha_from_gather(AlphaList* __restrict__ al, const long long* __restrict__ triples, int world) {
     long long nf = 0;
     unsigned long long total = 0ull;
-    for (int r = 0; r < world; ++r) { nf += triples[3 * r + 1]; total += (unsigned long long)triples[3 * r + 2]; }
+    for (int r = 0; r < world; ++r) { nf += triples[4 * r + 1]; total += (unsigned long long)triples[4 * r + 2]; }      // 4 = kGatherWords
     al->edge_total = total;
     const float avg = (float)(((double)total * (1.0 / 4294967296.0)) / (3. * (double)nf));
     al->avg_edge = avg;

@@ -37,8 +37,10 @@ struct McSettings {
                           // exist only in tiles near the surface); 0: evaluate every node (dense field, parity mode)
     int halo;             // z-slab runs with OB02: -1 (default) every GPU optimises its own slab plus a halo of recomputed cube layers
                           // (no mesh exchange); 0: gather the stitched mesh on every GPU and optimise it replicated
-    int balance;          // z-slab runs: 1 (default) slab boundaries follow the surface (equal counts of surface tiles per GPU, from a
-                          // bounds-only pass every rank repeats identically); 0: equal numbers of cube layers (SURVEY §8e's formula)
+    int balance;          // z-slab runs: 2 (default) slab boundaries follow the surface (equal counts of surface tiles per GPU, from a
+                          // bounds-only pass every rank repeats identically) and, over repeated builds of one spec, the measured busy
+                          // time of every rank (sent along in the step's one all-gather); 1: surface tiles only; 0: equal numbers of
+                          // cube layers (SURVEY §8e's formula)
     int pair;             // 1 (default): with per-tile point lists the OB02 kernels take two centroids per thread through the packed f32x2
                           // interpreters (same bits); 0: one centroid per thread
     int finish_split;     // pair path only, the projection's finish: 2 (default) bisection with lane refill from per-warp queues, then the
@@ -112,7 +114,7 @@ inline McSettings parse_mc_settings(const char* json) {
     s.normals = d.get_int("gpu.normals", 0);
     s.halo = d.get_int("gpu.halo", -1);
     s.point_spec = d.get_int("gpu.point_spec", -1);
-    s.balance = d.get_int("gpu.balance", 1);
+    s.balance = d.get_int("gpu.balance", 2);
     s.pair = d.get_int("gpu.pair", 1);
     s.finish_split = d.get_int("gpu.finish_split", 2);
     s.speculate = d.get_int("gpu.speculate", 1);

@@ -23,6 +23,7 @@ ap.add_argument("--ob02", action="store_true")
 ap.add_argument("--reps", type=int, default=1)
 ap.add_argument("--warm", type=int, default=2)
 ap.add_argument("--gpu", nargs="*", default=[])
+ap.add_argument("--emulate", default="", help="r/w: build rank r's slab of a w-GPU run on this GPU (halo mode, no NCCL)")
 a = ap.parse_args()
 
 if os.environ.get("ISD_LIB_OVERRIDE"):      # A/B against another build of the library (profiling only)
@@ -35,6 +36,11 @@ for kv in a.gpu:
     k, v = kv.split("=")
     kw[k] = int(v)
 sj, mc = fn(), shapes.mc_settings(a.R, half, **kw)
+if a.emulate:
+    r, w = (int(x) for x in a.emulate.split("/"))
+    lib.lib.isd_dist_emulate(r, w)
+    lib.lib.isd_dist_set_offsets(0, 0)
+    lib.lib.isd_dist_set_edge_total(95371408039445, 5212532)      # about C4 1024^3's mean edge 0.00142 x 3 x faces
 for _ in range(a.warm):
     lib.build_geometry_device(sj, mc)
     lib.finish_geometry()
