@@ -33,10 +33,12 @@
 
 namespace isd {
 
-// The interpreters read list entry k + 1 while they execute entry k (one register): the loads of an instruction's matrix then
-// depend on a value that is already there instead of on a load issued in the same iteration.
+// Optional (-DISD_LIST_PREFETCH=1): the interpreters read list entry k + 1 while they execute entry k (one register), so that
+// the loads of an instruction's matrix depend on a value that is already there.  Measured slower (C4 1024^3: 4.32 against 4.22 ms
+// per build, k_centroid_gradients_pair 0.417 against 0.371 ms — profiles/r02_ab_prefetch.txt): the extra live register and the
+// second load per iteration cost more than the shorter dependency chain saves at 24-28 warps per SM.  Off.
 #ifndef ISD_LIST_PREFETCH
-#define ISD_LIST_PREFETCH 1
+#define ISD_LIST_PREFETCH 0
 #endif
 #if ISD_LIST_PREFETCH
 #define ISD_LIST_FIRST(list, n) uint32_t e_next__ = (n) > 0 ? (list)[0] : 0u
@@ -1128,6 +1130,77 @@ ISD_HD void eval_value_gradient_list2(const Prog& prog, const SdfGridView& sdf, 
         ++sp;
     }
     f_out = tf; g0_out = t0; g1_out = t1; g2_out = t2;
+}
+
+// The same for NP pairs of points per thread (2 * NP points through one instruction stream): the list entry, the header and the
+// matrix are fetched and decoded once for all of them.  Per point the operations and their order are those of
+// eval_value_gradient_list2.
+template <int NP, class Prog, class List>
+ISD_HD void eval_value_gradient_listN(const Prog& prog, const SdfGridView& sdf, const List& list, int n_list, F2 (&cx)[NP], F2 (&cy)[NP], F2 (&cz)[NP],
+                                      F2 (&f_out)[NP], F2 (&g0_out)[NP], F2 (&g1_out)[NP], F2 (&g2_out)[NP]) {
+    F2 vs[kMaxValueStack][4][NP];
+    F2 fs[kMaxFrameStack][3][NP];
+    F2 tf[NP], t0[NP], t1[NP], t2[NP];
+#pragma unroll
+    for (int p = 0; p < NP; ++p) { tf[p] = splat(0.0f); t0[p] = splat(0.0f); t1[p] = splat(0.0f); t2[p] = splat(0.0f); }
+    int sp = 0, fp = 0;
+    for (int k = 0; k < n_list; ++k) {
+        const uint32_t e = list[k];
+        const int pc = (int)(e & IT_PC_MASK) * 4;
+        Mat12<Prog> M;
+        M.load(prog, pc + 4);
+        if (e & LE_CLOSING) {
+            const bool combine = (e & LE_COMBINE) != 0, negate = (e & LE_NEGATE) != 0;
+            const bool swapped = (e & LE_SWAPPED) != 0;
+            const uint32_t op = (e >> LE_OP_SHIFT) & 3u;
+            if (combine) --sp;
+#pragma unroll
+            for (int p = 0; p < NP; ++p) {
+                F2 r = tf[p], a0 = t0[p], a1 = t1[p], a2 = t2[p];
+                if (combine) {
+                    const F2 bf = vs[sp - 1][0][p], b0 = vs[sp - 1][1][p], b1 = vs[sp - 1][2][p], b2 = vs[sp - 1][3][p];
+                    csg_select_gradient(op, swapped, tf[p].x, bf.x, t0[p].x, t1[p].x, t2[p].x, b0.x, b1.x, b2.x, r.x, a0.x, a1.x, a2.x);
+                    csg_select_gradient(op, swapped, tf[p].y, bf.y, t0[p].y, t1[p].y, t2[p].y, b0.y, b1.y, b2.y, r.y, a0.y, a1.y, a2.y);
+                } else if (negate) {
+                    r = neg2(r); a0 = neg2(a0); a1 = neg2(a1); a2 = neg2(a2);
+                }
+                tf[p] = r;
+                back2(M, a0, a1, a2, t0[p], t1[p], t2[p]);
+            }
+            if (e & LE_RESTORE) {
+                --fp;
+#pragma unroll
+                for (int p = 0; p < NP; ++p) { cx[p] = fs[fp][0][p]; cy[p] = fs[fp][1][p]; cz[p] = fs[fp][2][p]; }
+            }
+            continue;
+        }
+        const W4 hdr = prog.load4(pc);
+        const uint32_t word = hdr.x;
+        const uint32_t op = word & OP_MASK;
+        if (op == OP_XFORM) {
+            if (word & OP_FLAG_SAVE) {
+#pragma unroll
+                for (int p = 0; p < NP; ++p) { fs[fp][0][p] = cx[p]; fs[fp][1][p] = cy[p]; fs[fp][2][p] = cz[p]; }
+                ++fp;
+            }
+#pragma unroll
+            for (int p = 0; p < NP; ++p) {
+                F2 x, y, z;
+                apply2(M, cx[p], cy[p], cz[p], x, y, z);
+                cx[p] = x; cy[p] = y; cz[p] = z;
+            }
+            continue;
+        }
+        if (sp > 0) {
+#pragma unroll
+            for (int p = 0; p < NP; ++p) { vs[sp - 1][0][p] = tf[p]; vs[sp - 1][1][p] = t0[p]; vs[sp - 1][2][p] = t1[p]; vs[sp - 1][3][p] = t2[p]; }
+        }
+#pragma unroll
+        for (int p = 0; p < NP; ++p) prim_value_gradient2(op, hdr, prog, pc + kInstrWords, M, sdf, cx[p], cy[p], cz[p], tf[p], t0[p], t1[p], t2[p]);
+        ++sp;
+    }
+#pragma unroll
+    for (int p = 0; p < NP; ++p) { f_out[p] = tf[p]; g0_out[p] = t0[p]; g1_out[p] = t1[p]; g2_out[p] = t2[p]; }
 }
 
 }  // namespace isd

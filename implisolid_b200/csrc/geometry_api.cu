@@ -25,6 +25,7 @@
 #include "ob02_kernels.cuh"
 #include "subdiv_kernels.cuh"
 #include "settings.hpp"
+#include "slab_balance.hpp"
 
 using namespace isd;
 
@@ -125,6 +126,7 @@ struct Context {
     bool normals_valid = false, normals_host_valid = false;
     bool point_spec_on = false;             // the OB02 kernels may use K1's tile masks (c_point_spec describes the current program)
     int finish_split = 0;                   // "gpu":{"finish_split":..}: the pair path's projection finish; 0 one kernel, 1 bisect batches of 32 units + gradients, 2 bisect with lane refill + gradients
+    bool quad_kernels = false;              // "gpu":{"quad":1}: the gradient passes take four faces per thread
     bool pair_kernels = true;               // "gpu":{"pair":1}: with point lists, two centroids per thread through the f32x2 interpreters
     std::vector<uint32_t> last_program;     // the shape program of the last build (lazy normals re-upload it)
     isd_progress_fn progress_fn = nullptr;
@@ -350,35 +352,18 @@ void slab_layers(int S, int rank, int world, int* z_begin, int* z_end) {
 // per step with equal surface, the lighter rank idling in the step's collective).  Every build measures its own busy time (device
 // time of the build minus the time spent inside the collective) and sends the previous build's along in the step's one
 // all-gather (a fourth word beside {nv, nf, edge sum}), tagged with the generation of the cuts it was measured under.  Once every
-// rank has reported a time for the current cuts and they differ by more than kRecutThreshold, each layer's weight is multiplied by
+// rank has reported a time for the current cuts and the slowest is more than 3 % above the mean, each layer's weight is multiplied by
 // its owner's measured cost per unit of weight and the cuts are drawn again — the same table on every rank, hence the same cuts.
 // At most kMaxRecuts times per (shape, grid, world); a build after a re-cut has a new slab and does not speculate.
 constexpr int kGatherWords = 4;            // per rank: nv, nf, fixed-point edge sum, busy word
 constexpr int kMaxRecuts = 8;
-constexpr double kRecutThreshold = 1.03;
+constexpr int kRecutThresholdPermille = 1030;
 struct BalanceState {
     std::vector<uint32_t> key;
-    std::vector<int> cuts;
-    std::vector<unsigned long long> weight;      // per cube layer, current (after feedback)
-    int gen = 0, recuts = 0;
+    SlabBalance b;                               // weights, cuts, generation (slab_balance.hpp)
     long long my_busy_us = 0; int my_busy_gen = -1;      // this rank's last completed build
     std::vector<long long> table_busy; std::vector<int> table_gen;      // what the last gather said about every rank
 } g_bal;
-
-// `shift` = 16 for the weights as first computed (whole numbers << 16: the cuts are those of the unscaled integers, which
-// implisolid_b200/slabs.py mirrors), 0 once feedback factors have been multiplied in
-void draw_cuts(int layers, int world, int shift) {
-    std::vector<unsigned long long> cum((size_t)layers + 1, 0ull);
-    for (int l = 0; l < layers; ++l) cum[(size_t)l + 1] = cum[(size_t)l] + (g_bal.weight[(size_t)l] >> shift);
-    g_bal.cuts.assign((size_t)world + 1, 0);
-    g_bal.cuts[(size_t)world] = layers;
-    for (int r = 1; r < world; ++r) {
-        const unsigned long long target = cum[(size_t)layers] * (unsigned long long)r / (unsigned long long)world;
-        int l = g_bal.cuts[(size_t)r - 1] + 1;                                   // at least one layer per rank
-        while (l < layers - (world - r) && cum[(size_t)l] < target) ++l;
-        g_bal.cuts[(size_t)r] = l;
-    }
-}
 
 void balanced_layers(const McSettings& s, const ShapeCompiler::Program& prog, int* z_begin, int* z_end) {
     const int S = g.grid.S, layers = S - 3, world = g.world, bins = (S + 7) / 8;
@@ -402,46 +387,18 @@ void balanced_layers(const McSettings& s, const ShapeCompiler::Program& prog, in
         std::vector<unsigned> hist((size_t)bins);
         ISD_CUDA(cudaMemcpyAsync(hist.data(), d_hist, hist_bytes, cudaMemcpyDeviceToHost, g.stream));
         ISD_CUDA(cudaStreamSynchronize(g.stream));
-        // integer weights per cube layer: its bin's count, plus a uniform term worth a quarter of the mean (per-layer fixed costs);
-        // scaled by 2^16 so that the feedback factors keep their resolution
-        unsigned long long total_bins = 0;
-        for (unsigned h : hist) total_bins += h;
-        const unsigned long long uniform = total_bins * 8ull / (4ull * (unsigned long long)layers) + 1ull;
-        g_bal.weight.assign((size_t)layers, 0ull);
-        for (int l = 0; l < layers; ++l) g_bal.weight[(size_t)l] = ((unsigned long long)hist[(size_t)((l + 1) >> 3)] + uniform) << 16;
-        draw_cuts(layers, world, 16);
+        g_bal.b.init(hist.data(), bins, layers, world);
         g_bal.key = key;
-        g_bal.gen = 0; g_bal.recuts = 0; g_bal.my_busy_gen = -1;
+        g_bal.my_busy_gen = -1;
         g_bal.table_busy.assign((size_t)world, 0); g_bal.table_gen.assign((size_t)world, -1);
-    } else if (s.balance >= 2 && !g.emulate && g_bal.recuts < kMaxRecuts && (int)g_bal.table_busy.size() == world) {
+    } else if (s.balance >= 2 && !g.emulate && g_bal.b.recuts < kMaxRecuts && (int)g_bal.table_busy.size() == world) {
         bool complete = true;
-        long long lo = 0, hi = 0, sum = 0;
-        for (int r = 0; r < world; ++r) {
-            if (g_bal.table_gen[(size_t)r] != g_bal.gen || g_bal.table_busy[(size_t)r] <= 0) { complete = false; break; }
-            const long long t = g_bal.table_busy[(size_t)r];
-            lo = (r == 0 || t < lo) ? t : lo; hi = (r == 0 || t > hi) ? t : hi; sum += t;
-        }
-        if (complete && (double)hi * world > kRecutThreshold * (double)sum) {
-            for (int r = 0; r < world; ++r) {      // cost per unit of weight of rank r's slab, relative to the mean: x / 2^10 fixed point
-                unsigned long long w = 0;
-                for (int l = g_bal.cuts[(size_t)r]; l < g_bal.cuts[(size_t)r + 1]; ++l) w += g_bal.weight[(size_t)l] >> 16;
-                if (w == 0) continue;
-                // density_r / mean density = (t_r / w_r) / (sum t / sum w): integers only, the same on every rank
-                unsigned long long wsum = 0;
-                for (int l = 0; l < layers; ++l) wsum += g_bal.weight[(size_t)l] >> 16;
-                unsigned long long f = (unsigned long long)(((__int128)g_bal.table_busy[(size_t)r] * (__int128)wsum * 1024) / ((__int128)sum * (__int128)w));
-                f = f < 256 ? 256 : (f > 4096 ? 4096 : f);      // a quarter to four times: one noisy step must not fling the cuts away
-                for (int l = g_bal.cuts[(size_t)r]; l < g_bal.cuts[(size_t)r + 1]; ++l) {
-                    unsigned long long nw = (g_bal.weight[(size_t)l] >> 10) * f;
-                    g_bal.weight[(size_t)l] = nw > 0 ? nw : 1ull;
-                }
-            }
-            draw_cuts(layers, world, 0);
-            ++g_bal.gen; ++g_bal.recuts;
-        }
+        for (int r = 0; r < world; ++r)
+            if (g_bal.table_gen[(size_t)r] != g_bal.b.gen || g_bal.table_busy[(size_t)r] <= 0) complete = false;
+        if (complete) g_bal.b.feedback(g_bal.table_busy.data(), world, kRecutThresholdPermille);
     }
-    *z_begin = 1 + g_bal.cuts[(size_t)g.rank];
-    *z_end = 1 + g_bal.cuts[(size_t)g.rank + 1];
+    *z_begin = 1 + g_bal.b.cuts[(size_t)g.rank];
+    *z_end = 1 + g_bal.b.cuts[(size_t)g.rank + 1];
 }
 
 void setup_grid(const McSettings& s, const ShapeCompiler::Program& prog) {
@@ -880,7 +837,10 @@ void vertex_resampling_step(float c) {
     g.d_cen.reserve((size_t)nf * 3 * sizeof(float) + 16);
     g.d_nrm.reserve((size_t)nf * 3 * sizeof(float) + 16);
     g.d_w.reserve((size_t)nf * sizeof(float) + 16);
-    if (g.point_spec_on && g.pair_kernels)
+    if (g.point_spec_on && g.pair_kernels && g.quad_kernels)
+        ISD_TIMED(KT_CENTROID_GRAD, k_centroid_gradients_quad<<<blocks_for((nf + 3) / 4, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf,
+                                                                                                                  g.d_cen.as<float>(), g.d_nrm.as<float>()));
+    else if (g.point_spec_on && g.pair_kernels)
         ISD_TIMED(KT_CENTROID_GRAD, k_centroid_gradients_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf,
                                                                                                                   g.d_cen.as<float>(), g.d_nrm.as<float>()));
     else
@@ -1315,6 +1275,7 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
     for (int64_t& c : g.counters) c = 0;
     g.launches = 0;
     g.pair_kernels = s.pair != 0;
+    g.quad_kernels = s.quad != 0;
     g.finish_split = s.finish_split;
     g_kt.reset(s.kernel_times != 0);
     g_kt.start_counting(s.count_flops != 0);
@@ -1391,7 +1352,7 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
         for (const auto& sp : g_gather_spans) { ISD_CUDA(cudaEventElapsedTime(&ms, sp.first, sp.second)); waited += ms; }
         if (g_spec_used) {
             g_bal.my_busy_us = (long long)((total - waited) * 1000.0f);
-            g_bal.my_busy_gen = g_bal.gen;
+            g_bal.my_busy_gen = g_bal.b.gen;
         }
         const int64_t* hs = g.h_gather.as<int64_t>();
         if ((int)g_bal.table_busy.size() == g.world)

@@ -4,6 +4,7 @@
 #include <cstring>
 #include <vector>
 #include "../../implisolid_b200/csrc/csg_eval.cuh"
+#include "../../implisolid_b200/csrc/slab_balance.hpp"
 
 using namespace isd;
 
@@ -304,3 +305,25 @@ extern "C" int emu_eval_packed(const char* shape_json, const float* pts, int n) 
     return bad;
 }
 
+
+// z-slab balance (slab_balance.hpp, the code geometry_api.cu runs): first cuts from a tile histogram, then `rounds` feedback steps
+// against a synthetic cost model — rank r's busy time = fixed_us + the sum of cost_us[l] over its layers.  cuts_out receives
+// (rounds + 1) x (world + 1) entries (the cuts before every round and the final ones), busy_out (rounds + 1) x world times.
+// Returns the number of re-cuts made.
+extern "C" int emu_slab_balance(const unsigned* hist, int bins, int layers, int world, const long long* cost_us, long long fixed_us, int rounds,
+                                int threshold_permille, int* cuts_out, long long* busy_out) {
+    SlabBalance b;
+    b.init(hist, bins, layers, world);
+    std::vector<long long> busy((size_t)world);
+    for (int it = 0; it <= rounds; ++it) {
+        for (int r = 0; r < world; ++r) {
+            long long t = fixed_us;
+            for (int l = b.cuts[(size_t)r]; l < b.cuts[(size_t)r + 1]; ++l) t += cost_us[l];
+            busy[(size_t)r] = t;
+            busy_out[(size_t)it * world + r] = t;
+        }
+        for (int r = 0; r <= world; ++r) cuts_out[(size_t)it * (world + 1) + r] = b.cuts[(size_t)r];
+        if (it < rounds) b.feedback(busy.data(), world, threshold_permille);
+    }
+    return b.recuts;
+}

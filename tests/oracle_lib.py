@@ -233,6 +233,19 @@ class Emu:
                           f.ctypes.data_as(ctypes.c_void_p), f4.ctypes.data_as(ctypes.c_void_p), g.ctypes.data_as(ctypes.c_void_p))
         return f, f4, g
 
+    def slab_balance(self, hist, layers, world, cost_us, fixed_us, rounds, threshold_permille=1030):
+        """csrc/slab_balance.hpp on a synthetic cost model: (cuts per round [rounds+1, world+1], busy times [rounds+1, world], re-cuts)."""
+        hist = np.ascontiguousarray(hist, dtype=np.uint32)
+        cost = np.ascontiguousarray(cost_us, dtype=np.int64)
+        assert cost.shape[0] == layers and hist.shape[0] >= ((layers + 1) >> 3) + 1
+        cuts = np.zeros((rounds + 1, world + 1), dtype=np.int32)
+        busy = np.zeros((rounds + 1, world), dtype=np.int64)
+        self.lib.emu_slab_balance.restype = ctypes.c_int
+        n = self.lib.emu_slab_balance(hist.ctypes.data_as(ctypes.c_void_p), int(hist.shape[0]), int(layers), int(world), cost.ctypes.data_as(ctypes.c_void_p),
+                                      ctypes.c_longlong(int(fixed_us)), int(rounds), int(threshold_permille), cuts.ctypes.data_as(ctypes.c_void_p),
+                                      busy.ctypes.data_as(ctypes.c_void_p))
+        return cuts, busy, n
+
     def eval_masked(self, shape_json, pts):
         """(tree value, interpreter value with only the selected children live, live node count per point, node count)."""
         p = np.ascontiguousarray(pts, dtype=np.float32).reshape(-1, 3)

@@ -23,6 +23,7 @@ ap.add_argument("--ob02", action="store_true")
 ap.add_argument("--reps", type=int, default=1)
 ap.add_argument("--warm", type=int, default=2)
 ap.add_argument("--gpu", nargs="*", default=[])
+ap.add_argument("--flops", action="store_true", help="one more build with the flop counters on: flops per kernel and per face")
 ap.add_argument("--emulate", default="", help="r/w: build rank r's slab of a w-GPU run on this GPU (halo mode, no NCCL)")
 a = ap.parse_args()
 
@@ -63,3 +64,11 @@ if kt:
     print("gaps before:", " ".join("%s=%.3f" % (k.split("(")[0].replace("k_", ""), v) for k, v in sorted(gp.items(), key=lambda kv: -kv[1])[:8]), "sum=%.3f" % sum(gp.values()))
 print(a.cfg, a.R, "nodes", c["nodes"], "evaluated", c["nodes_full_eval"], "cut", c["cut_cubes"], "nv", s["nv"], "nf", s["nf"],
       {k: round(v, 4) for k, v in t.items()})
+
+if a.flops:
+    kw2 = dict(kw); kw2["count_flops"] = 1; kw2.pop("kernel_times", None)
+    lib.build_geometry_device(sj, shapes.mc_settings(a.R, half, **kw2)); lib.finish_geometry()
+    fl = lib.last_kernel_flops()
+    nf = max(lib.last_slab()["nf"], 1)
+    print("flops:", " ".join("%s=%.3gG(%.0f/face%s)" % (k.split("(")[0].replace("k_", ""), v / 1e9, v / nf, (", %.1f TF/s" % (v / (kt[k][0] * 1e-3) / 1e12)) if kt and k in kt and kt[k][0] > 0 else "")
+                             for k, v in sorted(fl.items(), key=lambda kv: -kv[1]) if v > 0))
