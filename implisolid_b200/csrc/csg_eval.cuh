@@ -47,6 +47,13 @@ namespace isd {
 #define ISD_LIST_FIRST(list, n) do {} while (0)
 #define ISD_LIST_ENTRY(list, n, k) const uint32_t e = (list)[k]
 #endif
+// A list entry carries the opcode of the instruction it points at (bits 24-28) and XFORM's SAVE flag (bit 29), so the list
+// interpreters do not fetch the 16-byte instruction header; only METABALLS keeps something there (its ball count).
+#define ISD_ENTRY_DECODE(prog, e, pc)                                                         \
+    const uint32_t op = ((e) >> LE_OPC_SHIFT) & LE_OPC_MASK;                                  \
+    const bool save = ((e) & LE_SAVE) != 0;                                                   \
+    W4 hdr = W4{0u, 0u, 0u, 0u};                                                              \
+    if (op == OP_METABALLS) hdr = (prog).load4(pc)
 struct SdfGridView {          // HEAD-literal cube (cube.hpp:65-72): table lives in global memory
     const float* v;
     int nx, ny, nz;
@@ -458,14 +465,12 @@ ISD_HD void eval_values_list2(const Prog& prog, const SdfGridView& sdf, const Li
             }
             continue;
         }
-        const W4 hdr = prog.load4(pc);
-        const uint32_t word = hdr.x;
-        const uint32_t op = word & OP_MASK;
+        ISD_ENTRY_DECODE(prog, e, pc);
         Mat12<Prog> M;
         M.load(prog, pc + 4);
         pc += kInstrWords;
         if (op == OP_XFORM) {
-            if (word & OP_FLAG_SAVE) {
+            if (save) {
 #pragma unroll
                 for (int p = 0; p < NP; ++p) { fs[fp][0][p] = cx[p]; fs[fp][1][p] = cy[p]; fs[fp][2][p] = cz[p]; }
                 ++fp;
@@ -718,7 +723,7 @@ ISD_HD void eval_values(const Prog& prog, const SdfGridView& sdf, const Live& li
 template <class Live>
 ISD_HD uint32_t spec_entry(const W4& it, const Live& live) {
     if (!live(it.y)) return 0u;
-    if (!(it.x & IT_CLOSING)) return (it.x & IT_PC_MASK) | LE_VALID;
+    if (!(it.x & IT_CLOSING)) return (it.x & (IT_PC_MASK | (LE_OPC_MASK << LE_OPC_SHIFT) | LE_SAVE)) | LE_VALID;
     const bool la = live(it.z), lb = live(it.w);
     const uint32_t op = (it.x >> IT_OP_SHIFT) & 3u;
     uint32_t e = (it.x & (IT_PC_MASK | IT_CLOSING | IT_RESTORE | IT_SWAPPED)) | (op << LE_OP_SHIFT);      // same bit positions as LE_*
@@ -733,7 +738,7 @@ ISD_HD uint32_t spec_entry(const W4& it, const Live& live) {
 template <class Live>
 ISD_HD uint32_t spec_entry_gradient(const W4& it, const Live& live) {
     if (!live(it.y)) return 0u;
-    if (!(it.x & IT_CLOSING)) return (it.x & IT_PC_MASK) | LE_VALID;
+    if (!(it.x & IT_CLOSING)) return (it.x & (IT_PC_MASK | (LE_OPC_MASK << LE_OPC_SHIFT) | LE_SAVE)) | LE_VALID;
     const bool la = live(it.z), lb = live(it.w);
     const uint32_t op = (it.x >> IT_OP_SHIFT) & 3u;
     uint32_t e = (it.x & (IT_PC_MASK | IT_CLOSING | IT_RESTORE | IT_SWAPPED)) | (op << LE_OP_SHIFT);
@@ -786,14 +791,12 @@ ISD_HD void eval_values_list(const Prog& prog, const SdfGridView& sdf, const Lis
             }
             continue;
         }
-        const W4 hdr = prog.load4(pc);
-        const uint32_t word = hdr.x;
-        const uint32_t op = word & OP_MASK;
+        ISD_ENTRY_DECODE(prog, e, pc);
         Mat12<Prog> M;
         M.load(prog, pc + 4);
         pc += kInstrWords;
         if (op == OP_XFORM) {
-            if (word & OP_FLAG_SAVE) {
+            if (save) {
 #pragma unroll
                 for (int p = 0; p < P; ++p) { fs[fp][0][p] = cx[p]; fs[fp][1][p] = cy[p]; fs[fp][2][p] = cz[p]; }
                 ++fp;
@@ -1011,11 +1014,9 @@ ISD_HD void eval_value_gradient_list(const Prog& prog, const SdfGridView& sdf, c
             if (e & LE_RESTORE) { --fp; cx = fs[fp][0]; cy = fs[fp][1]; cz = fs[fp][2]; }
             continue;
         }
-        const W4 hdr = prog.load4(pc);
-        const uint32_t word = hdr.x;
-        const uint32_t op = word & OP_MASK;
+        ISD_ENTRY_DECODE(prog, e, pc);
         if (op == OP_XFORM) {
-            if (word & OP_FLAG_SAVE) { fs[fp][0] = cx; fs[fp][1] = cy; fs[fp][2] = cz; ++fp; }
+            if (save) { fs[fp][0] = cx; fs[fp][1] = cy; fs[fp][2] = cz; ++fp; }
             float x, y, z;
             M.apply(cx, cy, cz, x, y, z);
             cx = x; cy = y; cz = z;
@@ -1113,11 +1114,9 @@ ISD_HD void eval_value_gradient_list2(const Prog& prog, const SdfGridView& sdf, 
             if (e & LE_RESTORE) { --fp; cx = fs[fp][0]; cy = fs[fp][1]; cz = fs[fp][2]; }
             continue;
         }
-        const W4 hdr = prog.load4(pc);
-        const uint32_t word = hdr.x;
-        const uint32_t op = word & OP_MASK;
+        ISD_ENTRY_DECODE(prog, e, pc);
         if (op == OP_XFORM) {
-            if (word & OP_FLAG_SAVE) { fs[fp][0] = cx; fs[fp][1] = cy; fs[fp][2] = cz; ++fp; }
+            if (save) { fs[fp][0] = cx; fs[fp][1] = cy; fs[fp][2] = cz; ++fp; }
             F2 x, y, z;
             apply2(M, cx, cy, cz, x, y, z);
             cx = x; cy = y; cz = z;
@@ -1130,77 +1129,6 @@ ISD_HD void eval_value_gradient_list2(const Prog& prog, const SdfGridView& sdf, 
         ++sp;
     }
     f_out = tf; g0_out = t0; g1_out = t1; g2_out = t2;
-}
-
-// The same for NP pairs of points per thread (2 * NP points through one instruction stream): the list entry, the header and the
-// matrix are fetched and decoded once for all of them.  Per point the operations and their order are those of
-// eval_value_gradient_list2.
-template <int NP, class Prog, class List>
-ISD_HD void eval_value_gradient_listN(const Prog& prog, const SdfGridView& sdf, const List& list, int n_list, F2 (&cx)[NP], F2 (&cy)[NP], F2 (&cz)[NP],
-                                      F2 (&f_out)[NP], F2 (&g0_out)[NP], F2 (&g1_out)[NP], F2 (&g2_out)[NP]) {
-    F2 vs[kMaxValueStack][4][NP];
-    F2 fs[kMaxFrameStack][3][NP];
-    F2 tf[NP], t0[NP], t1[NP], t2[NP];
-#pragma unroll
-    for (int p = 0; p < NP; ++p) { tf[p] = splat(0.0f); t0[p] = splat(0.0f); t1[p] = splat(0.0f); t2[p] = splat(0.0f); }
-    int sp = 0, fp = 0;
-    for (int k = 0; k < n_list; ++k) {
-        const uint32_t e = list[k];
-        const int pc = (int)(e & IT_PC_MASK) * 4;
-        Mat12<Prog> M;
-        M.load(prog, pc + 4);
-        if (e & LE_CLOSING) {
-            const bool combine = (e & LE_COMBINE) != 0, negate = (e & LE_NEGATE) != 0;
-            const bool swapped = (e & LE_SWAPPED) != 0;
-            const uint32_t op = (e >> LE_OP_SHIFT) & 3u;
-            if (combine) --sp;
-#pragma unroll
-            for (int p = 0; p < NP; ++p) {
-                F2 r = tf[p], a0 = t0[p], a1 = t1[p], a2 = t2[p];
-                if (combine) {
-                    const F2 bf = vs[sp - 1][0][p], b0 = vs[sp - 1][1][p], b1 = vs[sp - 1][2][p], b2 = vs[sp - 1][3][p];
-                    csg_select_gradient(op, swapped, tf[p].x, bf.x, t0[p].x, t1[p].x, t2[p].x, b0.x, b1.x, b2.x, r.x, a0.x, a1.x, a2.x);
-                    csg_select_gradient(op, swapped, tf[p].y, bf.y, t0[p].y, t1[p].y, t2[p].y, b0.y, b1.y, b2.y, r.y, a0.y, a1.y, a2.y);
-                } else if (negate) {
-                    r = neg2(r); a0 = neg2(a0); a1 = neg2(a1); a2 = neg2(a2);
-                }
-                tf[p] = r;
-                back2(M, a0, a1, a2, t0[p], t1[p], t2[p]);
-            }
-            if (e & LE_RESTORE) {
-                --fp;
-#pragma unroll
-                for (int p = 0; p < NP; ++p) { cx[p] = fs[fp][0][p]; cy[p] = fs[fp][1][p]; cz[p] = fs[fp][2][p]; }
-            }
-            continue;
-        }
-        const W4 hdr = prog.load4(pc);
-        const uint32_t word = hdr.x;
-        const uint32_t op = word & OP_MASK;
-        if (op == OP_XFORM) {
-            if (word & OP_FLAG_SAVE) {
-#pragma unroll
-                for (int p = 0; p < NP; ++p) { fs[fp][0][p] = cx[p]; fs[fp][1][p] = cy[p]; fs[fp][2][p] = cz[p]; }
-                ++fp;
-            }
-#pragma unroll
-            for (int p = 0; p < NP; ++p) {
-                F2 x, y, z;
-                apply2(M, cx[p], cy[p], cz[p], x, y, z);
-                cx[p] = x; cy[p] = y; cz[p] = z;
-            }
-            continue;
-        }
-        if (sp > 0) {
-#pragma unroll
-            for (int p = 0; p < NP; ++p) { vs[sp - 1][0][p] = tf[p]; vs[sp - 1][1][p] = t0[p]; vs[sp - 1][2][p] = t1[p]; vs[sp - 1][3][p] = t2[p]; }
-        }
-#pragma unroll
-        for (int p = 0; p < NP; ++p) prim_value_gradient2(op, hdr, prog, pc + kInstrWords, M, sdf, cx[p], cy[p], cz[p], tf[p], t0[p], t1[p], t2[p]);
-        ++sp;
-    }
-#pragma unroll
-    for (int p = 0; p < NP; ++p) { f_out[p] = tf[p]; g0_out[p] = t0[p]; g1_out[p] = t1[p]; g2_out[p] = t2[p]; }
 }
 
 }  // namespace isd

@@ -126,7 +126,6 @@ struct Context {
     bool normals_valid = false, normals_host_valid = false;
     bool point_spec_on = false;             // the OB02 kernels may use K1's tile masks (c_point_spec describes the current program)
     int finish_split = 0;                   // "gpu":{"finish_split":..}: the pair path's projection finish; 0 one kernel, 1 bisect batches of 32 units + gradients, 2 bisect with lane refill + gradients
-    bool quad_kernels = false;              // "gpu":{"quad":1}: the gradient passes take four faces per thread
     bool pair_kernels = true;               // "gpu":{"pair":1}: with point lists, two centroids per thread through the f32x2 interpreters
     std::vector<uint32_t> last_program;     // the shape program of the last build (lazy normals re-upload it)
     isd_progress_fn progress_fn = nullptr;
@@ -837,10 +836,7 @@ void vertex_resampling_step(float c) {
     g.d_cen.reserve((size_t)nf * 3 * sizeof(float) + 16);
     g.d_nrm.reserve((size_t)nf * 3 * sizeof(float) + 16);
     g.d_w.reserve((size_t)nf * sizeof(float) + 16);
-    if (g.point_spec_on && g.pair_kernels && g.quad_kernels)
-        ISD_TIMED(KT_CENTROID_GRAD, k_centroid_gradients_quad<<<blocks_for((nf + 3) / 4, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf,
-                                                                                                                  g.d_cen.as<float>(), g.d_nrm.as<float>()));
-    else if (g.point_spec_on && g.pair_kernels)
+    if (g.point_spec_on && g.pair_kernels)
         ISD_TIMED(KT_CENTROID_GRAD, k_centroid_gradients_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf,
                                                                                                                   g.d_cen.as<float>(), g.d_nrm.as<float>()));
     else
@@ -1275,7 +1271,6 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
     for (int64_t& c : g.counters) c = 0;
     g.launches = 0;
     g.pair_kernels = s.pair != 0;
-    g.quad_kernels = s.quad != 0;
     g.finish_split = s.finish_split;
     g_kt.reset(s.kernel_times != 0);
     g_kt.start_counting(s.count_flops != 0);

@@ -749,75 +749,6 @@ ISD_PAIR_FN FG2 eval_fg_pair(SdfGridView sdf, float ax, float ay, float az, floa
     return r;
 }
 
-// Four points (two pairs) per thread: pair_slot's rule for all four — the list of the tile with the largest index on every axis,
-// provided no point's cell lies more than one cell below it.
-__device__ __forceinline__ int quad_slot(const PointSpec& ps, const float (&px)[4], const float (&py)[4], const float (&pz)[4]) {
-    if (!ps.enabled) return -1;
-    const float S = (float)ps.g.S, zlo = (float)ps.g.z0, zhi = (float)(ps.g.z0 + ps.g.nz);
-    int cmaxx = 0, cmaxy = 0, cmaxz = 0, cminx = 0x7fffffff, cminy = 0x7fffffff, cminz = 0x7fffffff;
-    bool inside = true;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        const float fx = (px[q] - ps.g.xmin) / ps.g.wx + 2.0f, fy = (py[q] - ps.g.ymin) / ps.g.wy + 2.0f, fz = (pz[q] - ps.g.zmin) / ps.g.wz + 2.0f;
-        inside = inside && (fx >= 0.0f && fy >= 0.0f && fz >= zlo) && (fx < S && fy < S && fz < zhi);      // also rejects NaN
-        const int cx = (int)fx, cy = (int)fy, cz = (int)fz - ps.g.z0;
-        cmaxx = max(cmaxx, cx); cmaxy = max(cmaxy, cy); cmaxz = max(cmaxz, cz);
-        cminx = min(cminx, cx); cminy = min(cminy, cy); cminz = min(cminz, cz);
-    }
-    if (!inside) return -1;
-    const int tx = cmaxx >> 3, ty = cmaxy >> 3, tz = cmaxz >> 3;
-    if (cminx < tx * 8 - 1 || cminy < ty * 8 - 1 || cminz < tz * 8 - 1) return -1;
-    const int row = tz * ps.g.ty + ty;
-    if (!((__ldg(ps.tile_bits + (size_t)row * ps.TW + (tx >> 5)) >> (tx & 31)) & 1u)) return -1;
-    return (int)__ldg(ps.tile_slot + (size_t)row * ps.g.tx + tx);
-}
-// f and grad f at four points: r[0] = points 0 and 1, r[1] = points 2 and 3
-ISD_PAIR_FN void eval_fg_quad(SdfGridView sdf, const float (&px)[4], const float (&py)[4], const float (&pz)[4], FG2 (&r)[2]) {
-    const int slot = quad_slot(c_point_spec, px, py, pz);
-    if (slot >= 0) {
-        const uint32_t* rec = c_point_spec.lists + ((size_t)slot * 2 + 1) * c_point_spec.stride;
-        F2 cx[2] = {F2{px[0], px[1]}, F2{px[2], px[3]}}, cy[2] = {F2{py[0], py[1]}, F2{py[2], py[3]}}, cz[2] = {F2{pz[0], pz[1]}, F2{pz[2], pz[3]}};
-        F2 f[2], g0[2], g1[2], g2[2];
-        eval_value_gradient_listN<2>(ConstProgram(), sdf, GlobalList{rec + 1}, (int)__ldg(rec), cx, cy, cz, f, g0, g1, g2);
-        if (c_count_flops) add_flops(4ull * list_flops(ConstProgram(), GlobalList{rec + 1}, (int)__ldg(rec), true));
-#pragma unroll
-        for (int h = 0; h < 2; ++h) { r[h].f = f[h]; r[h].g0 = g0[h]; r[h].g1 = g1[h]; r[h].g2 = g2[h]; }
-        return;
-    }
-    r[0] = eval_fg_pair(sdf, px[0], py[0], pz[0], px[1], py[1], pz[1]);
-    r[1] = eval_fg_pair(sdf, px[2], py[2], pz[2], px[3], py[3], pz[3]);
-}
-#ifndef ISD_QUAD_MINBLOCKS
-#define ISD_QUAD_MINBLOCKS 4
-#endif
-// k_centroid_gradients, faces 4t .. 4t+3 per thread ("gpu":{"quad":1})
-__global__ void __launch_bounds__(128, ISD_QUAD_MINBLOCKS) k_centroid_gradients_quad(SdfGridView sdf, const float* __restrict__ verts, const int* __restrict__ faces, int nf,
-                                                                                    float* __restrict__ cen, float* __restrict__ nrm) {
-    const int fa = (blockIdx.x * 128 + threadIdx.x) * 4;
-    if (fa >= nf) return;
-    float cx[4], cy[4], cz[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const int f = fa + k < nf ? fa + k : nf - 1;      // past the end: the last face again
-        const int f0 = faces[f * 3], f1 = faces[f * 3 + 1], f2 = faces[f * 3 + 2];
-        cx[k] = (verts[f0 * 3] + verts[f1 * 3] + verts[f2 * 3]) / 3.0f;
-        cy[k] = (verts[f0 * 3 + 1] + verts[f1 * 3 + 1] + verts[f2 * 3 + 1]) / 3.0f;
-        cz[k] = (verts[f0 * 3 + 2] + verts[f1 * 3 + 2] + verts[f2 * 3 + 2]) / 3.0f;
-        if (fa + k < nf) { cen[f * 3] = cx[k]; cen[f * 3 + 1] = cy[k]; cen[f * 3 + 2] = cz[k]; }
-    }
-    FG2 r[2];
-    eval_fg_quad(sdf, cx, cy, cz, r);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        if (fa + k >= nf) break;
-        const FG2& q = r[k >> 1];
-        const float g0 = (k & 1) ? q.g0.y : q.g0.x, g1 = (k & 1) ? q.g1.y : q.g1.x, g2 = (k & 1) ? q.g2.y : q.g2.x;
-        const float norm = norm2f(g0, g1, g2);
-        const int f = fa + k;
-        nrm[f * 3] = g0 / norm; nrm[f * 3 + 1] = g1 / norm; nrm[f * 3 + 2] = g2 / norm;
-    }
-}
-
 // k_centroid_gradients, faces 2t and 2t+1 per thread
 __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS_CG) k_centroid_gradients_pair(SdfGridView sdf, const float* __restrict__ verts, const int* __restrict__ faces, int nf,
                                                                  float* __restrict__ cen, float* __restrict__ nrm) {

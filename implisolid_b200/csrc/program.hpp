@@ -81,6 +81,7 @@ enum : uint32_t {
     LE_CLOSING = 1u << 16, LE_RESTORE = 1u << 17, LE_SWAPPED = 1u << 18, LE_OP_SHIFT = 19,
     LE_COMBINE = 1u << 21, LE_NEGATE = 1u << 22, LE_VALID = 1u << 31,
     LE_PASS = 1u << 23,       // gradient lists only: live closing instruction with one operand and nothing to do in value mode
+    LE_OPC_SHIFT = 24, LE_OPC_MASK = 31u, LE_SAVE = 1u << 29,      // opening instructions (in itab.x too): the opcode and XFORM's SAVE flag
 };
 constexpr int kMaxSpecNodes = 2048;       // tile specialisation: per-tile liveness mask of at most this many bits
 constexpr int kMaxPendingDepth = 64;      // liveness pass: pending-sibling stack held in one 64-bit register
@@ -505,7 +506,7 @@ private:
     void emit_node(const ShapeNode& n, bool preserve, Program& p, bool parent_identity = false) {
         p.num_nodes++;
         if (!n.is_csg()) {
-            put_itab(p, (uint32_t)(p.words.size() / 4), id_of(n), 0u, 0u);
+            put_itab(p, (uint32_t)(p.words.size() / 4) | ((uint32_t)n.op << LE_OPC_SHIFT), id_of(n), 0u, 0u);
             const size_t skip_at = put_header(p, (uint32_t)n.op | (id_of(n) << OP_ID_SHIFT), n.op == OP_METABALLS ? (uint32_t)(n.params.size() / 5) : 0u);
             put_matrix(p, n.minv);
             p.flops_per_point += 18;
@@ -547,7 +548,7 @@ private:
         const bool soft = preserve && parent_identity && is_identity(n.minv);
         const bool save = preserve && !soft;
         if (save && ++fs_ > p.frame_depth) p.frame_depth = fs_;
-        put_itab(p, (uint32_t)(p.words.size() / 4), id_of(n), 0u, 0u);
+        put_itab(p, (uint32_t)(p.words.size() / 4) | ((uint32_t)OP_XFORM << LE_OPC_SHIFT) | (save ? (uint32_t)LE_SAVE : 0u), id_of(n), 0u, 0u);
         const size_t skip_at = put_header(p, (uint32_t)OP_XFORM | (save ? (uint32_t)OP_FLAG_SAVE : 0u) | (id_of(n) << OP_ID_SHIFT), 0u);
         put_matrix(p, n.minv);
         p.flops_per_point += 18 + 1;
