@@ -10,8 +10,9 @@ C4, a left-deep chain of 32 transformed primitives (seed 1234), 1024^3, with the
 
 value     : voxels / s, device-resident (mesh stays in HBM), CUDA events on the library's stream, L2 flushed between steps.
 e2e       : the same through the reference-facing C API with host buffers: JSON strings in, get_v/get_f views out.
-roofline  : the kernel with the largest share of the step, timed by its own events inside the timed region
-            ("gpu":{"kernel_times":1}); FP32 operations come from an instrumented, untimed step ("gpu":{"count_flops":1}).
+roofline  : the kernel with the largest share of the step; every kernel is timed by its own pair of events in an instrumented
+            repeat of the timed steps ("gpu":{"kernel_times":1}: +5 % per step, so `value` comes from the plain steps);
+            FP32 operations come from an instrumented, untimed step ("gpu":{"count_flops":1}).
 cpu_baseline / --impl reference : the oracle restatement of the reference's CPU algorithm (the reference itself needs
             Boost/Eigen/Emscripten and cannot be built here), built -O3 -march=native, all host threads, on a bounded
             sample of the same workload: windows of cube layers spread evenly over the 1024^3 grid.

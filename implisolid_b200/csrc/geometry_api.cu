@@ -217,11 +217,12 @@ inline void launched() { g.launches++; }
 // Per-kernel device times ("gpu":{"kernel_times":1}; bench.py's roofline entries): a pair of events around every launch,
 // read after the build's last synchronisation.  Off by default: two event records per launch are a few per cent of a 0.4 ms step.
 enum { KT_SUPER_BOUNDS = 0, KT_TILE_BOUNDS, KT_EVAL_TILES, KT_CLASSIFY, KT_ROW_SCAN, KT_POINT_LISTS, KT_SEG_APPLY, KT_EMIT, KT_ADJACENCY, KT_FOF,
-       KT_CENTROID_GRAD, KT_FACE_WEIGHTS, KT_RESAMPLE, KT_FACE_PREPARE, KT_SEARCH, KT_FINISH, KT_LEFTOVERS, KT_QEM, KT_OTHER, KT_N };
-const char* const kKernelNames[KT_N] = {"k_super_bounds", "k_tile_bounds", "k_eval_tiles", "k_mc_classify_tiles", "k_row_scan", "k_build_point_lists",
-                                        "k_seg_apply", "k_mc_emit", "adjacency(k_vertex_degree+k_uscan+k_umbrella_fill+k_umbrella_sort)", "k_faces_of_faces",
-                                        "k_centroid_gradients", "k_face_weights", "k_resample", "k_face_prepare", "k_project_search", "k_project_finish",
-                                        "k_project_leftovers", "k_qem", "other(subdivision scan)"};
+       KT_CENTROID_GRAD, KT_FACE_WEIGHTS, KT_RESAMPLE, KT_FACE_PREPARE, KT_SEARCH, KT_FINISH, KT_LEFTOVERS, KT_QEM, KT_OTHER, KT_UNIT_GRAD, KT_N };
+// the names of the kernels a build actually launched under each id (the pair path and the finish's form change them)
+const char* g_kernel_names[KT_N] = {"k_super_bounds", "k_tile_bounds", "k_eval_tiles", "k_mc_classify_tiles", "k_row_scan", "k_build_point_lists",
+                                    "k_seg_apply", "k_mc_emit", "adjacency(k_vertex_degree+k_uscan+k_umbrella_fill+k_umbrella_sort)", "k_faces_of_faces",
+                                    "k_centroid_gradients", "k_face_weights", "k_resample", "k_face_prepare", "k_project_search", "k_project_finish",
+                                    "k_project_leftovers", "k_qem", "other(subdivision scan)", "k_unit_gradients_pair"};
 struct KernelTimes {
     bool on = false;
     std::vector<cudaEvent_t> pool;
@@ -836,6 +837,7 @@ void vertex_resampling_step(float c) {
     g.d_cen.reserve((size_t)nf * 3 * sizeof(float) + 16);
     g.d_nrm.reserve((size_t)nf * 3 * sizeof(float) + 16);
     g.d_w.reserve((size_t)nf * sizeof(float) + 16);
+    g_kernel_names[KT_CENTROID_GRAD] = (g.point_spec_on && g.pair_kernels) ? "k_centroid_gradients_pair" : "k_centroid_gradients";
     if (g.point_spec_on && g.pair_kernels)
         ISD_TIMED(KT_CENTROID_GRAD, k_centroid_gradients_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf,
                                                                                                                   g.d_cen.as<float>(), g.d_nrm.as<float>()));
@@ -1009,6 +1011,8 @@ void projection_step(bool enable_qem, bool exact_reduce, int repeat) {
     // the list of left-over centroids lives in the output array: k_project_finish only writes it once there are none left to list
     a.leftover = reinterpret_cast<int*>(g.d_proj.as<float>());
     const bool pairs = g.point_spec_on && g.pair_kernels;
+    g_kernel_names[KT_SEARCH] = pairs ? "k_project_search_pair" : "k_project_search";
+    g_kernel_names[KT_FINISH] = !pairs ? "k_project_finish" : g.finish_split == 2 ? "k_finish_bisect_refill" : g.finish_split == 1 ? "k_finish_bisect_units" : "k_project_finish_pair";
     if (pairs) ISD_TIMED(KT_SEARCH, k_project_search_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, a));
     else ISD_TIMED(KT_SEARCH, (g.point_spec_on ? k_project_search<true> : k_project_search<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a));
     // Phase B (direction types 2..6) is only needed when phase A left centroids over, which is rare and which only the device
@@ -1022,7 +1026,7 @@ void projection_step(bool enable_qem, bool exact_reduce, int repeat) {
                 ISD_TIMED(KT_FINISH, k_finish_bisect_refill<<<want < resident ? want : resident, 128, 0, g.stream>>>(g.sdf, pa));
             }
             else ISD_TIMED(KT_FINISH, k_finish_bisect_units<<<blocks_for((nf + 1) / 2, 4 * kFinishRange), 128, 0, g.stream>>>(g.sdf, pa));
-            ISD_TIMED(KT_FINISH, k_unit_gradients_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, pa.out, nf, pa.nrm_out,
+            ISD_TIMED(KT_UNIT_GRAD, k_unit_gradients_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, pa.out, nf, pa.nrm_out,
                                                                                                             pa.speculative ? pa.counters : nullptr, pa.state));
         } else if (pairs) {
             ISD_TIMED(KT_FINISH, k_project_finish_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, pa));
@@ -1637,7 +1641,7 @@ int isd_last_kernel_flops(double* out, int cap) {
     for (int i = 0; i < n; ++i) out[i] = g_kt.flops[i];
     return n;
 }
-const char* isd_kernel_name(int id) { return (id >= 0 && id < (int)KT_N) ? kKernelNames[id] : ""; }
+const char* isd_kernel_name(int id) { return (id >= 0 && id < (int)KT_N) ? g_kernel_names[id] : ""; }
 int isd_last_program_stats(double* out4) {
     for (int i = 0; i < 4; ++i) out4[i] = g.prog_stats[i];
     return 4;

@@ -296,23 +296,67 @@ __global__ void __launch_bounds__(kRowScanThreads) k_row_scan(McDesc m, McBuffer
 
 // One thread per segment of the work list: offsets become absolute, and the cut cubes go, in scan order, into cubes[]
 // as segment * 8 + position.
-__global__ void __launch_bounds__(256) k_seg_apply(McDesc m, McBuffers mb, unsigned long long* __restrict__ cubes) {
+//
+// Faces grouped by tile (`perm`, optional).  The OB02 kernels evaluate the tree at the faces' centroids through per-tile
+// instruction lists, two faces per thread; in face order (scan order: z, y, x) a warp's 64 faces lie in four or five tiles and its
+// lanes run as many different lists.  A segment's faces are one contiguous run of face indices, and a tile is 64 consecutive
+// segments = 64 consecutive threads here: the block adds up each tile's face count, one thread reserves the tile's (even) number
+// of slots with ONE atomic, and every segment writes its run of local face indices behind those of the tile's earlier segments.
+// perm then lists every face exactly once, tile by tile (tiles in no particular order — results are per face and do not depend
+// on it), padded with -1 to an even count per tile so that the pairs (2t, 2t + 1) the kernels take never straddle two tiles.
+struct PermArgs {
+    int* perm;                         // nullptr: not wanted
+    unsigned* cursor;                  // slots handed out so far (zeroed before the launch); the final value is perm's length
+    const unsigned* ghost_faces;       // triangles of the ghost layer (counted by the scan, not emitted), or nullptr
+};
+__global__ void __launch_bounds__(256) k_seg_apply(McDesc m, McBuffers mb, unsigned long long* __restrict__ cubes, PermArgs pa) {
+    __shared__ unsigned s_cnt[8];
+    __shared__ unsigned s_base[4];
     const long long n_seg = (long long)mb.counters[0] * 64;
-    for (long long seg = (long long)blockIdx.x * 256 + threadIdx.x; seg < n_seg; seg += (long long)gridDim.x * 256) {
-        const unsigned long long sb = mb.seg_bits[seg];
-        unsigned cut = planes_cut(sb);
-        if ((sb & 0xffffffffffull) == 0ull) continue;
-        const int t = (int)mb.list[seg >> 6], r = (int)(seg & 63);
-        const int ty = (t / m.g.tx) % m.g.ty, tzl = t / (m.g.tx * m.g.ty);
-        const int y = 8 * ty + (r & 7), z = m.g.z0 + 8 * tzl + (r >> 3);
-        const Triple base = mb.row_base[row_index(m, y, z)];
-        const uint2 rel = mb.seg_off[seg];
-        mb.seg_off[seg] = make_uint2(base.v + rel.x, base.f + rel.y);
-        unsigned long long slot = (unsigned long long)base.a + (sb >> 40);
-        while (cut) {
-            const int l = __ffs(cut) - 1;
-            cut &= cut - 1;
-            cubes[slot++] = (unsigned long long)seg * 8ull + (unsigned)l;
+    const unsigned ghost_f = (pa.perm != nullptr && pa.ghost_faces != nullptr) ? *pa.ghost_faces : 0u;
+    for (long long seg0 = (long long)blockIdx.x * 256; seg0 < n_seg; seg0 += (long long)gridDim.x * 256) {
+        const long long seg = seg0 + threadIdx.x;      // n_seg is a multiple of 64: a tile's segments are all in or all out
+        unsigned n_faces = 0u, face0 = 0u;
+        if (seg < n_seg) {
+            const unsigned long long sb = mb.seg_bits[seg];
+            unsigned cut = planes_cut(sb);
+            if ((sb & 0xffffffffffull) != 0ull) {
+                const int t = (int)mb.list[seg >> 6], r = (int)(seg & 63);
+                const int ty = (t / m.g.tx) % m.g.ty, tzl = t / (m.g.tx * m.g.ty);
+                const int y = 8 * ty + (r & 7), z = m.g.z0 + 8 * tzl + (r >> 3);
+                const Triple base = mb.row_base[row_index(m, y, z)];
+                const uint2 rel = mb.seg_off[seg];
+                mb.seg_off[seg] = make_uint2(base.v + rel.x, base.f + rel.y);
+                unsigned long long slot = (unsigned long long)base.a + (sb >> 40);
+                while (cut) {
+                    const int l = __ffs(cut) - 1;
+                    cut &= cut - 1;
+                    cubes[slot++] = (unsigned long long)seg * 8ull + (unsigned)l;
+                }
+                if (pa.perm != nullptr && z >= m.emit_z0) { n_faces = planes_t(sb, 0xffu); face0 = base.f + rel.y - ghost_f; }
+            }
+        }
+        if (pa.perm != nullptr) {      // uniform branch
+            const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, tile = w >> 1;      // a tile = two warps
+            unsigned inc = n_faces;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned o = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += o;
+            }
+            if (lane == 31) s_cnt[w] = inc;
+            __syncthreads();
+            const unsigned before = inc - n_faces + ((w & 1) ? s_cnt[w - 1] : 0u);
+            if ((threadIdx.x & 63) == 0) {
+                const unsigned total = s_cnt[2 * tile] + s_cnt[2 * tile + 1];
+                s_base[tile] = total ? atomicAdd(pa.cursor, (total + 1u) & ~1u) : 0u;
+            }
+            __syncthreads();
+            if (n_faces) {
+                int* dst = pa.perm + s_base[tile] + before;
+                for (unsigned j = 0; j < n_faces; ++j) dst[j] = (int)(face0 + j);
+            }
+            __syncthreads();
         }
     }
 }

@@ -433,7 +433,22 @@ __global__ void k_alpha_from_mean(const float* __restrict__ mean, AlphaList* __r
     make_alpha_list(*mean, 0.001f, *mean, 20, al);
 }
 
+// The order in which the pair kernels take the faces: face order (perm == nullptr: unit u = faces 2u, 2u + 1), or grouped by
+// tile (mc_kernels.cuh, k_seg_apply: perm lists every face once, each tile's run padded with -1 to an even length, so the two
+// members of a unit always come from one tile).  Results are per face and do not depend on the order.
+struct FaceOrder {
+    const int* perm;
+    const unsigned* len;      // perm's length (device; even)
+};
+__device__ __forceinline__ long long unit_count(const FaceOrder& fo, int n) { return fo.perm ? (long long)(*fo.len / 2u) : ((long long)n + 1) / 2; }
+// the two faces of unit u (u < unit_count): fa >= 0 always, fb = -1 when the unit has one member
+__device__ __forceinline__ void unit_faces(const FaceOrder& fo, long long u, int n, int& fa, int& fb) {
+    if (fo.perm) { fa = fo.perm[2 * u]; fb = fo.perm[2 * u + 1]; }
+    else { fa = (int)(2 * u); fb = 2 * u + 1 < (long long)n ? (int)(2 * u + 1) : -1; }
+}
+
 struct ProjectArgs {
+    FaceOrder order;
     const float* verts;
     const int* faces;
     const float* cen;        // centroids (input)
@@ -751,14 +766,16 @@ ISD_PAIR_FN FG2 eval_fg_pair(SdfGridView sdf, float ax, float ay, float az, floa
 
 // k_centroid_gradients, faces 2t and 2t+1 per thread
 __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS_CG) k_centroid_gradients_pair(SdfGridView sdf, const float* __restrict__ verts, const int* __restrict__ faces, int nf,
-                                                                 float* __restrict__ cen, float* __restrict__ nrm) {
-    const int fa = (blockIdx.x * 128 + threadIdx.x) * 2;
-    if (fa >= nf) return;
-    const bool two = fa + 1 < nf;
+                                                                 float* __restrict__ cen, float* __restrict__ nrm, FaceOrder order) {
+    const long long u = (long long)blockIdx.x * 128 + threadIdx.x;
+    if (u >= unit_count(order, nf)) return;
+    int fa, fb;
+    unit_faces(order, u, nf, fa, fb);
+    const bool two = fb >= 0;
     float c[2][3];
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
-        const int f = (k == 1 && two) ? fa + 1 : fa;      // an odd face count: the last thread evaluates its face twice
+        const int f = (k == 1 && two) ? fb : fa;      // a unit of one: the thread evaluates its face twice
         const int f0 = faces[f * 3], f1 = faces[f * 3 + 1], f2 = faces[f * 3 + 2];
 #pragma unroll
         for (int d = 0; d < 3; ++d) {
@@ -773,7 +790,7 @@ __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS_CG) k_centroid_gradien
     }
     if (two) {
         const float norm = norm2f(r.g0.y, r.g1.y, r.g2.y);
-        nrm[fa * 3 + 3] = r.g0.y / norm; nrm[fa * 3 + 4] = r.g1.y / norm; nrm[fa * 3 + 5] = r.g2.y / norm;
+        nrm[fb * 3] = r.g0.y / norm; nrm[fb * 3 + 1] = r.g1.y / norm; nrm[fb * 3 + 2] = r.g2.y / norm;
     }
 }
 
@@ -781,10 +798,12 @@ __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS_CG) k_centroid_gradien
 // trial points (direction type 0 over the whole alpha list, then type 1 over the short list), exactly as in the scalar kernel;
 // the two sequences advance in lockstep and a lane that has finished a phase rides along on its partner's point.
 __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_project_search_pair(SdfGridView sdf, ProjectArgs a) {
-    const int ia = (blockIdx.x * 128 + threadIdx.x) * 2;
-    if (ia >= a.n) return;
-    const bool two = ia + 1 < a.n;
-    const int idx[2] = {ia, two ? ia + 1 : ia};
+    const long long u = (long long)blockIdx.x * 128 + threadIdx.x;
+    if (u >= unit_count(a.order, a.n)) return;
+    int ia, ib;
+    unit_faces(a.order, u, a.n, ia, ib);
+    const bool two = ib >= 0;
+    const int idx[2] = {ia, two ? ib : ia};
     const float edge = a.al->avg_edge;
     const float* alphas = a.al->alpha;
     const int n_alpha_full = a.al->n_full, n_alpha_short = a.al->n_short;
@@ -880,11 +899,13 @@ __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_project_search_pair
 // k_project_finish, centroids 2t and 2t+1 per thread: the two bisections advance in lockstep, each with its own interval and
 // its own stopping test; a lane that has finished rides along on its partner's midpoint.
 __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_project_finish_pair(SdfGridView sdf, ProjectArgs a) {
-    const int ia = (blockIdx.x * 128 + threadIdx.x) * 2;
-    if (ia >= a.n) return;
+    const long long u = (long long)blockIdx.x * 128 + threadIdx.x;
+    if (u >= unit_count(a.order, a.n)) return;
     if (a.speculative && a.counters->c[10] != 0ull) return;
-    const bool two = ia + 1 < a.n;
-    const int idx[2] = {ia, two ? ia + 1 : ia};
+    int ia, ib;
+    unit_faces(a.order, u, a.n, ia, ib);
+    const bool two = ib >= 0;
+    const int idx[2] = {ia, two ? ib : ia};
     float o[2][3], x1[2][3], x2[2][3];
     bool zeros12[2], active[2];
 #pragma unroll
@@ -1093,13 +1114,14 @@ __global__ void __launch_bounds__(128, ISD_FINISH_REFILL_MINBLOCKS) k_finish_bis
     __shared__ int s_queue[4][128];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int* queue = s_queue[warp];
-    const long long n_units = ((long long)a.n + 1) / 2;
+    const long long n_units = unit_count(a.order, a.n);
     long long next = 0, last = 0;
     bool exhausted = false;
     int head = 0, waiting = 0;
     unsigned n_failed = 0u, n_bisect = 0u;
     int entry = -1, it = 0;      // this lane's unit (u << 2 | members that bisect), or -1: idle
     bool active[2] = {false, false};
+    int face[2] = {0, 0};        // the unit's faces
     float x1[2][3], x2[2][3];
 #pragma unroll
     for (int k = 0; k < 2; ++k)
@@ -1120,10 +1142,12 @@ __global__ void __launch_bounds__(128, ISD_FINISH_REFILL_MINBLOCKS) k_finish_bis
             const long long u = next + lane;
             int needs = 0;
             if (u < last) {
+                int uf[2];
+                unit_faces(a.order, u, a.n, uf[0], uf[1]);
 #pragma unroll
                 for (int k = 0; k < 2; ++k) {
-                    const long long i = 2 * u + k;
-                    if (i >= (long long)a.n) break;
+                    const long long i = uf[k];
+                    if (i < 0) break;
                     const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
                     const bool already = (a.state[i] & 1) != 0;
                     const float fc = a.fc[i];
@@ -1157,11 +1181,12 @@ __global__ void __launch_bounds__(128, ISD_FINISH_REFILL_MINBLOCKS) k_finish_bis
             if (r < waiting) {
                 entry = queue[(head + r) & 127];
                 it = 1;
+                unit_faces(a.order, entry >> 2, a.n, face[0], face[1]);
 #pragma unroll
                 for (int k = 0; k < 2; ++k) {
                     active[k] = ((entry >> k) & 1) != 0;
                     if (!active[k]) continue;
-                    const long long i = 2ll * (entry >> 2) + k;
+                    const long long i = face[k];
                     const float cx = a.cen[i * 3], cy = a.cen[i * 3 + 1], cz = a.cen[i * 3 + 2];
                     const float4 b = a.best[i];
                     x1[k][0] = cx; x1[k][1] = cy; x1[k][2] = cz; x2[k][0] = b.x; x2[k][1] = b.y; x2[k][2] = b.z;
@@ -1191,7 +1216,7 @@ __global__ void __launch_bounds__(128, ISD_FINISH_REFILL_MINBLOCKS) k_finish_bis
                 if (!active[k]) continue;
                 if (fabsf(v[k]) <= kRootTolerance || it >= kBisectionMaxIter) {
                     if (fabsf(v[k]) > kRootTolerance) atomicAdd(&a.counters->c[8], 1ull);
-                    const long long i = 2ll * (entry >> 2) + k;
+                    const long long i = face[k];
                     a.out[i * 3] = m[k][0]; a.out[i * 3 + 1] = m[k][1]; a.out[i * 3 + 2] = m[k][2];
                     active[k] = false;
                     continue;
@@ -1216,12 +1241,14 @@ __global__ void __launch_bounds__(128, ISD_FINISH_REFILL_MINBLOCKS) k_finish_bis
 // unit gradients at points 2t and 2t+1 (compute_centroid_gradient at the projected centroids, centroids_projection.cpp:1262)
 __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_unit_gradients_pair(SdfGridView sdf, const float* __restrict__ pts, int n, float* __restrict__ nrm,
                                                                                  const Ob02Counters* __restrict__ skip_if_leftovers,
-                                                                                 const unsigned char* __restrict__ state) {
-    const int ia = (blockIdx.x * 128 + threadIdx.x) * 2;
-    if (ia >= n) return;
+                                                                                 const unsigned char* __restrict__ state, FaceOrder order) {
+    const long long u = (long long)blockIdx.x * 128 + threadIdx.x;
+    if (u >= unit_count(order, n)) return;
     if (skip_if_leftovers != nullptr && skip_if_leftovers->c[10] != 0ull) return;
-    const bool two = ia + 1 < n;
-    const int ib = two ? ia + 1 : ia;
+    int ia, ib;
+    unit_faces(order, u, n, ia, ib);
+    const bool two = ib >= 0;
+    if (!two) ib = ia;
     if (state != nullptr && (state[ia] & 4) && (state[ib] & 4)) return;      // both written by the search (state bit 2, k_project_search)
     const FG2 r = eval_fg_pair(sdf, pts[ia * 3], pts[ia * 3 + 1], pts[ia * 3 + 2], pts[ib * 3], pts[ib * 3 + 1], pts[ib * 3 + 2]);
     {

@@ -1,5 +1,5 @@
 """profiles/rNN_traffic.json from an `ncu --set full` raw-page CSV: DRAM bytes (read + write) per kernel per step, under the
-names bench.py's kernel table uses (the pair kernels under their scalar names, the adjacency kernels summed).
+names bench.py's kernel table uses (the kernels' own names; the adjacency kernels summed).
 
   python tools/ncu_traffic_json.py gpurun_out/full.csv profiles/r02_traffic.json "workload text" "source text"
 """
@@ -18,7 +18,6 @@ for r in rows[2:]:
         continue
     name = re.sub(r"^void\s+", "", r[ix["Kernel Name"]])
     name = re.sub(r"<.*", "", name).split("(")[0].replace("isd::", "")
-    name = name[:-5] if name.endswith("_pair") else name
     if name in ADJ:
         name = "adjacency"
     def num(col):
