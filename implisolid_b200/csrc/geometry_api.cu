@@ -116,6 +116,9 @@ struct Context {
     DeviceBuffer d_cen, d_nrm, d_deg, d_uoff, d_uitems, d_cursor, d_fof, d_w, d_len3, d_best, d_fc, d_state, d_proj, d_pnrm, d_point_lists,
         d_noise, d_scal, d_counters, d_upartials;
     bool adjacency_valid = false, fof_valid_ = false;
+    DeviceBuffer d_perm;                    // faces grouped by tile for the pair kernels (mc_kernels.cuh k_seg_apply) + its length counter in front
+    bool perm_valid = false, want_perm = true;      // "gpu":{"perm":1}
+    long long perm_units_bound = 0;         // >= perm length / 2 (the length itself stays on the device)
     float average_edge = 0.f;
     bool alpha_ticket_zeroed = false;
     long long proj_n = 0;
@@ -669,7 +672,23 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     if (n_work > 0) {   // K3, second half: absolute segment offsets + the ordered list of cut cubes
         unsigned blocks = (unsigned)((n_seg + 255) / 256);
         if (blocks > (unsigned)g.sm_count * 32u) blocks = (unsigned)g.sm_count * 32u;
-        ISD_TIMED(KT_SEG_APPLY, k_seg_apply<<<blocks, 256, 0, g.stream>>>(m, mb, g.d_cubes.as<unsigned long long>()));
+        // faces grouped by tile, for the OB02 pair kernels: only when they will run on this very mesh (per-tile lists on, the
+        // local mesh is what K4 emits)
+        PermArgs pa{nullptr, nullptr, nullptr};
+        g.perm_valid = false;
+        const bool local_mesh = g.world == 1 || g.emulate || g.halo_mode;
+        if (g.want_perm && g.point_spec_on && g.pair_kernels && local_mesh && s.overall_repeats > 0 && (s.vresampl_iters > 0 || s.projection_enabled)) {
+            const size_t slots = (size_t)h[1] + (size_t)h[8] + 2;
+            g.d_perm.reserve(16 + slots * sizeof(int));
+            ISD_CUDA(cudaMemsetAsync(g.d_perm.ptr, 0, 16, g.stream));
+            ISD_CUDA(cudaMemsetAsync(g.d_perm.as<char>() + 16, 0xff, slots * sizeof(int), g.stream));
+            pa.cursor = g.d_perm.as<unsigned>();
+            pa.perm = reinterpret_cast<int*>(g.d_perm.as<char>() + 16);
+            pa.ghost_faces = m.ghost_rows > 0 ? g.d_totals.as<unsigned>() + 5 : nullptr;
+            g.perm_valid = true;
+            g.perm_units_bound = (long long)(slots / 2) + 1;
+        }
+        ISD_TIMED(KT_SEG_APPLY, k_seg_apply<<<blocks, 256, 0, g.stream>>>(m, mb, g.d_cubes.as<unsigned long long>(), pa));
     }
     ISD_CUDA(cudaEventRecord(g.ev[2], g.stream));
     const long long scan_v = h[0], scan_f = h[1];
@@ -777,6 +796,7 @@ void gather_mesh() {
     g.local_voff = 0; g.local_foff = 0;
     g.nv = gnv; g.nf = gnf;
     g.gathered = true;
+    g.perm_valid = false;
     g.host_valid = false;
 }
 
@@ -795,6 +815,13 @@ void exclusive_scan_u32(const unsigned* in, long long n, unsigned* out /* n + 1 
 }
 
 inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
+
+// the order in which the pair kernels take the faces (ob02_kernels.cuh FaceOrder) and the number of units to launch for
+FaceOrder face_order() {
+    if (!g.perm_valid) return FaceOrder{nullptr, nullptr};
+    return FaceOrder{reinterpret_cast<const int*>(g.d_perm.as<char>() + 16), g.d_perm.as<unsigned>()};
+}
+long long unit_launch_count(long long nf) { return g.perm_valid ? g.perm_units_bound : (nf + 1) / 2; }
 
 // umbrella CSR (always) and faces-of-faces (resampling only); the face list does not change between OB02 steps
 void build_adjacency(bool need_fof) {
@@ -839,8 +866,8 @@ void vertex_resampling_step(float c) {
     g.d_w.reserve((size_t)nf * sizeof(float) + 16);
     g_kernel_names[KT_CENTROID_GRAD] = (g.point_spec_on && g.pair_kernels) ? "k_centroid_gradients_pair" : "k_centroid_gradients";
     if (g.point_spec_on && g.pair_kernels)
-        ISD_TIMED(KT_CENTROID_GRAD, k_centroid_gradients_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf,
-                                                                                                                  g.d_cen.as<float>(), g.d_nrm.as<float>()));
+        ISD_TIMED(KT_CENTROID_GRAD, k_centroid_gradients_pair<<<blocks_for(unit_launch_count(nf), 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf,
+                                                                                                                  g.d_cen.as<float>(), g.d_nrm.as<float>(), face_order()));
     else
         ISD_TIMED(KT_CENTROID_GRAD, (g.point_spec_on ? k_centroid_gradients<true> : k_centroid_gradients<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, g.d_verts.as<float>(), g.d_faces.as<int>(), nf, g.d_cen.as<float>(),
                                                                    g.d_nrm.as<float>()));
@@ -1007,13 +1034,13 @@ void projection_step(bool enable_qem, bool exact_reduce, int repeat) {
     a.verts = g.d_verts.as<float>(); a.faces = g.d_faces.as<int>(); a.cen = g.d_cen.as<float>(); a.noise = nullptr;
     a.al = d_al; a.best = g.d_best.as<float4>(); a.fc = g.d_fc.as<float>(); a.state = g.d_state.as<unsigned char>();
     a.out = g.d_proj.as<float>(); a.nrm_out = g.d_pnrm.as<float>(); a.counters = g.d_counters.as<Ob02Counters>();
-    a.n = nf; a.speculative = 1;
+    a.n = nf; a.speculative = 1; a.order = face_order();
     // the list of left-over centroids lives in the output array: k_project_finish only writes it once there are none left to list
     a.leftover = reinterpret_cast<int*>(g.d_proj.as<float>());
     const bool pairs = g.point_spec_on && g.pair_kernels;
     g_kernel_names[KT_SEARCH] = pairs ? "k_project_search_pair" : "k_project_search";
     g_kernel_names[KT_FINISH] = !pairs ? "k_project_finish" : g.finish_split == 2 ? "k_finish_bisect_refill" : g.finish_split == 1 ? "k_finish_bisect_units" : "k_project_finish_pair";
-    if (pairs) ISD_TIMED(KT_SEARCH, k_project_search_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, a));
+    if (pairs) ISD_TIMED(KT_SEARCH, k_project_search_pair<<<blocks_for(unit_launch_count(nf), 128), 128, 0, g.stream>>>(g.sdf, a));
     else ISD_TIMED(KT_SEARCH, (g.point_spec_on ? k_project_search<true> : k_project_search<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a));
     // Phase B (direction types 2..6) is only needed when phase A left centroids over, which is rare and which only the device
     // knows: the rest of the step is launched right away and does nothing in that case (the kernels test the counter), so the
@@ -1022,14 +1049,14 @@ void projection_step(bool enable_qem, bool exact_reduce, int repeat) {
     auto finish_pass = [&](const ProjectArgs& pa) {
         if (pairs && g.finish_split) {
             if (g.finish_split == 2) {
-                const unsigned want = blocks_for((nf + 1) / 2, 4 * kRefillRange), resident = (unsigned)g.sm_count * ISD_FINISH_REFILL_MINBLOCKS;
+                const unsigned want = blocks_for(unit_launch_count(nf), 4 * kRefillRange), resident = (unsigned)g.sm_count * ISD_FINISH_REFILL_MINBLOCKS;
                 ISD_TIMED(KT_FINISH, k_finish_bisect_refill<<<want < resident ? want : resident, 128, 0, g.stream>>>(g.sdf, pa));
             }
             else ISD_TIMED(KT_FINISH, k_finish_bisect_units<<<blocks_for((nf + 1) / 2, 4 * kFinishRange), 128, 0, g.stream>>>(g.sdf, pa));
-            ISD_TIMED(KT_UNIT_GRAD, k_unit_gradients_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, pa.out, nf, pa.nrm_out,
-                                                                                                            pa.speculative ? pa.counters : nullptr, pa.state));
+            ISD_TIMED(KT_UNIT_GRAD, k_unit_gradients_pair<<<blocks_for(unit_launch_count(nf), 128), 128, 0, g.stream>>>(g.sdf, pa.out, nf, pa.nrm_out,
+                                                                                                            pa.speculative ? pa.counters : nullptr, pa.state, pa.order));
         } else if (pairs) {
-            ISD_TIMED(KT_FINISH, k_project_finish_pair<<<blocks_for((nf + 1) / 2, 128), 128, 0, g.stream>>>(g.sdf, pa));
+            ISD_TIMED(KT_FINISH, k_project_finish_pair<<<blocks_for(unit_launch_count(nf), 128), 128, 0, g.stream>>>(g.sdf, pa));
         } else {
             ISD_TIMED(KT_FINISH, (g.point_spec_on ? k_project_finish<true> : k_project_finish<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, pa));
         }
@@ -1173,7 +1200,7 @@ void subdivision_step(float amplitude) {
     std::swap(g.d_verts, g.d_verts2);
     std::swap(g.d_faces, g.d_faces2);
     g.nv = nv2; g.nf = nf2;
-    g.adjacency_valid = false; g.fof_valid_ = false;
+    g.adjacency_valid = false; g.fof_valid_ = false; g.perm_valid = false;
     g.host_valid = false;
     // randomize_verts draws 3*nv2 numbers whatever the amplitude
     const long long draws = nv2 * 3;
@@ -1230,7 +1257,7 @@ void export_own_slab() {
     }
     g.local_voff = g.own_v0; g.local_foff = g.own_f0;
     g.nv = own_nv; g.nf = own_nf;
-    g.adjacency_valid = false; g.fof_valid_ = false;      // they describe the local mesh, which is gone
+    g.adjacency_valid = false; g.fof_valid_ = false; g.perm_valid = false;      // they describe the local mesh, which is gone
     g.host_valid = false;
     g.slab[2] = voff; g.slab[3] = foff; g.slab[4] = own_nv; g.slab[5] = own_nf; g.slab[6] = gnv; g.slab[7] = gnf;
 }
@@ -1275,6 +1302,7 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
     for (int64_t& c : g.counters) c = 0;
     g.launches = 0;
     g.pair_kernels = s.pair != 0;
+    g.want_perm = s.perm != 0;
     g.finish_split = s.finish_split;
     g_kt.reset(s.kernel_times != 0);
     g_kt.start_counting(s.count_flops != 0);
@@ -1282,6 +1310,7 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
     g.faces_in_flight = false;
     g.adjacency_valid = false;
     g.fof_valid_ = false;
+    g.perm_valid = false;
     g.proj_n = 0;
     g.normals_valid = false;
     g.normals_host_valid = false;
@@ -1693,7 +1722,7 @@ static void load_mesh(const float* verts, int nv, const int* faces, int nf) {
     if (verts && nv) ISD_CUDA(cudaMemcpyAsync(g.d_verts.ptr, verts, (size_t)nv * 3 * sizeof(float), cudaMemcpyHostToDevice, g.stream));
     if (nf) ISD_CUDA(cudaMemcpyAsync(g.d_faces.ptr, faces, (size_t)nf * 3 * sizeof(int), cudaMemcpyHostToDevice, g.stream));
     g.nv = nv; g.nf = nf;
-    g.adjacency_valid = false; g.fof_valid_ = false; g.host_valid = false;
+    g.adjacency_valid = false; g.fof_valid_ = false; g.perm_valid = false; g.host_valid = false;
 }
 
 void isd_ob02_on_mesh(const char* shape_parameters_json, float* verts, int nv, const int* faces, int nf, int resample_iters, float c,
