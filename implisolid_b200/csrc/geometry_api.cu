@@ -1302,7 +1302,7 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
     for (int64_t& c : g.counters) c = 0;
     g.launches = 0;
     g.pair_kernels = s.pair != 0;
-    g.want_perm = s.perm != 0;
+    g.want_perm = s.perm > 0;      // -1 (auto) is decided once the program is known, below
     g.finish_split = s.finish_split;
     g_kt.reset(s.kernel_times != 0);
     g_kt.start_counting(s.count_flops != 0);
@@ -1320,6 +1320,7 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
     g.last_program = prog.words;
     g.prog_stats[0] = prog.flops_per_point; g.prog_stats[1] = prog.num_nodes; g.prog_stats[2] = (double)prog.words.size();
     g.prog_stats[3] = prog.value_depth;
+    if (s.perm < 0) g.want_perm = prog.num_nodes > 0 && prog.flops_per_point >= 40.0 * prog.num_nodes;
     g.keep_field = true;
     if (!g_ev_build_start) { ISD_CUDA(cudaEventCreate(&g_ev_build_start)); ISD_CUDA(cudaEventCreate(&g_ev_build_end)); }
     g_gather_spans.clear();
