@@ -540,8 +540,7 @@ def main():
             "sustained": {"ms_per_step": sustained_ms, "steps": extra, "l2": "not flushed, back to back"},
             "stage_ms": stages, "dominant_stage": dominant_stage, "roofline": roofline, "kernels": per_kernel, "roofline_mc_conventional": roof_mc,
             "counters": {"projection_by_type": e2e_counters["projection_by_type"], "projection_failed": e2e_counters["projection_failed"],
-                         "bisection_capped": e2e_counters["bisection_capped"], "bisected": e2e_counters["bisected"],
-                         "bisection_steps": e2e_counters["bisection_steps"], "bisection_max_steps": e2e_counters["bisection_max_steps"], "scope": "rank 0's slab + halo" if world > 1 else "whole mesh"},
+                         "bisection_capped": e2e_counters["bisection_capped"], "bisected": e2e_counters["bisected"], "scope": "rank 0's slab + halo" if world > 1 else "whole mesh"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},
             "gpu_launches": launches, "clocks": clocks, "other_configs": others,
             "speculation": {"timed_builds_speculative": bool(speculative_builds), "what": "a build of the spec the previous build had sizes its arrays and "

@@ -262,14 +262,13 @@ class GeometryLibrary:
         return dict(zip(TIMING_NAMES, [float(x) for x in buf]))
 
     def last_counters(self):
-        buf = np.zeros(20, dtype=np.int64)
-        self.lib.isd_last_counters(buf.ctypes.data, 20)
+        buf = np.zeros(18, dtype=np.int64)
+        self.lib.isd_last_counters(buf.ctypes.data, 18)
         return {"nodes": int(buf[0]), "cubes": int(buf[1]), "cut_cubes": int(buf[2]),
                 "projection_by_type": [int(x) for x in buf[3:10]], "projection_failed": int(buf[10]),
                 "bisection_capped": int(buf[11]), "bisected": int(buf[12]), "launches": int(buf[13]),
                 "field_bytes": int(buf[14]), "nodes_full_eval": int(buf[15]),
-                "speculative": int(buf[16]), "speculation_redone": int(buf[17]),
-                "bisection_steps": int(buf[18]), "bisection_max_steps": int(buf[19])}
+                "speculative": int(buf[16]), "speculation_redone": int(buf[17])}
 
     def spoil_speculation(self, what=1):
         self.lib.isd_debug_spoil_speculation(what)

@@ -1139,8 +1139,6 @@ void projection_step(bool enable_qem, bool exact_reduce, int repeat) {
     g.counters[10] += (int64_t)hc->c[7];
     g.counters[11] += (int64_t)hc->c[8];
     g.counters[12] += (int64_t)hc->c[9];
-    g.counters[18] += (int64_t)hc->c[12];
-    if ((int64_t)hc->c[13] > g.counters[19]) g.counters[19] = (int64_t)hc->c[13];
 }
 
 // ---- polygonize_step_3 ---------------------------------------------------------------------------------------------------
@@ -1414,10 +1412,6 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
             g.counters[10] += (int64_t)hc->c[7];
             g.counters[11] += (int64_t)hc->c[8];
             g.counters[12] += (int64_t)hc->c[9];
-            g.counters[18] += (int64_t)hc->c[12];
-            if ((int64_t)hc->c[13] > g.counters[19]) g.counters[19] = (int64_t)hc->c[13];
-    g.counters[18] += (int64_t)hc->c[12];
-    if ((int64_t)hc->c[13] > g.counters[19]) g.counters[19] = (int64_t)hc->c[13];
         }
         if (!g_deferred_slots.empty()) {
             g.average_edge = *reinterpret_cast<const float*>(g.h_small.as<char>() + 1024);
@@ -1658,7 +1652,7 @@ int isd_last_timings(float* out_ms, int cap) {
     return n;
 }
 int isd_last_counters(int64_t* out, int cap) {
-    int n = cap < 20 ? cap : 20;
+    int n = cap < 18 ? cap : 18;
     for (int i = 0; i < n; ++i) out[i] = g.counters[i];
     return n;
 }

@@ -52,9 +52,8 @@ __device__ inline void make_alpha_list(float initial_step_size, float min_step_s
 }
 
 // counters: [0..6] centroids resolved by direction type, [7] failed, [8] bisection capped, [9] bisected,
-// [10] centroids still unresolved after phase A, [11] range ticket of k_finish_bisect_refill, [12] bisection steps in all,
-// [13] the longest bisection (steps) — the last two from k_finish_bisect_refill only
-struct Ob02Counters { unsigned long long c[16]; };
+// [10] centroids still unresolved after phase A, [11] range ticket of k_finish_bisect_refill
+struct Ob02Counters { unsigned long long c[12]; };
 
 // one atomic per warp instead of one per thread: all counters are bumped by up to every thread of the grid
 __device__ __forceinline__ void count_if(bool pred, unsigned long long* ctr) {
@@ -202,29 +201,24 @@ __global__ void k_umbrella_sort(int nv, const unsigned* __restrict__ offsets, in
 // make_edge_lookup + build_faces_of_faces (mesh_algorithms.hpp:50-131).  The reference's map keeps, per undirected
 // edge, the first face that inserted it and the last face that found it; a face's neighbour across the edge is the
 // first one unless that is the face itself.  Both are read here from the (ascending) umbrella of one end vertex.
-// The faces that hold both a and b are the intersection of the two umbrellas, both ascending: a merge of two short contiguous
-// lists instead of a gather of every candidate's corners (one or two sectors per umbrella against one per candidate face).
 __global__ void k_faces_of_faces(const int* __restrict__ faces, int nf, const unsigned* __restrict__ offsets, const int* __restrict__ items,
                                  int* __restrict__ fof) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nf * 3) return;
     const int f = i / 3, j = i - f * 3;
     const int a = faces[f * 3 + j], b = faces[f * 3 + (j + 1) % 3];
-    int first = -1, last = -1, count = 0;
-    if (a != b) {      // a degenerate edge is nobody's (the reference's lookup finds consecutive corners only)
-        unsigned ka = offsets[a], kb = offsets[b];
-        const unsigned ea = offsets[a + 1], eb = offsets[b + 1];
-        while (ka < ea && kb < eb) {
-            const int ga = items[ka], gb = items[kb];
-            if (ga < gb) ++ka;
-            else if (gb < ga) ++kb;
-            else {      // a face listed twice in an umbrella (repeated vertex) is still one face
-                if (first < 0) first = ga;
-                last = ga;
-                ++count;
-                do { ++ka; } while (ka < ea && items[ka] == ga);
-                do { ++kb; } while (kb < eb && items[kb] == ga);
-            }
+    int first = -1, last = -1, count = 0, prev = -1;
+    for (unsigned k = offsets[a], e = offsets[a + 1]; k < e; ++k) {
+        const int g = items[k];
+        if (g == prev) continue;        // a face listed twice (repeated vertex) is still one face
+        prev = g;
+        const int g0 = faces[g * 3], g1 = faces[g * 3 + 1], g2 = faces[g * 3 + 2];
+        // does g have the undirected edge {a,b}?  (consecutive corners, cyclically — always true for a triangle holding both)
+        const bool has = (a != b) ? ((g0 == b) || (g1 == b) || (g2 == b)) : false;
+        if (has) {
+            if (first < 0) first = g;
+            last = g;
+            ++count;
         }
     }
     int r;
@@ -1124,7 +1118,7 @@ __global__ void __launch_bounds__(128, ISD_FINISH_REFILL_MINBLOCKS) k_finish_bis
     long long next = 0, last = 0;
     bool exhausted = false;
     int head = 0, waiting = 0;
-    unsigned n_failed = 0u, n_bisect = 0u, n_steps = 0u, max_steps = 0u;
+    unsigned n_failed = 0u, n_bisect = 0u;
     int entry = -1, it = 0;      // this lane's unit (u << 2 | members that bisect), or -1: idle
     bool active[2] = {false, false};
     int face[2] = {0, 0};        // the unit's faces
@@ -1225,8 +1219,6 @@ __global__ void __launch_bounds__(128, ISD_FINISH_REFILL_MINBLOCKS) k_finish_bis
                     const long long i = face[k];
                     a.out[i * 3] = m[k][0]; a.out[i * 3 + 1] = m[k][1]; a.out[i * 3 + 2] = m[k][2];
                     active[k] = false;
-                    n_steps += (unsigned)it;
-                    max_steps = max_steps > (unsigned)it ? max_steps : (unsigned)it;
                     continue;
                 }
                 if (v[k] > kRootTolerance) { x2[k][0] = m[k][0]; x2[k][1] = m[k][1]; x2[k][2] = m[k][2]; }
@@ -1240,15 +1232,10 @@ __global__ void __launch_bounds__(128, ISD_FINISH_REFILL_MINBLOCKS) k_finish_bis
     for (int d = 16; d > 0; d >>= 1) {
         n_failed += __shfl_xor_sync(0xffffffffu, n_failed, d);
         n_bisect += __shfl_xor_sync(0xffffffffu, n_bisect, d);
-        n_steps += __shfl_xor_sync(0xffffffffu, n_steps, d);
-        const unsigned o = __shfl_xor_sync(0xffffffffu, max_steps, d);
-        max_steps = max_steps > o ? max_steps : o;
     }
     if (lane == 0) {
         if (n_failed) atomicAdd(&a.counters->c[7], (unsigned long long)n_failed);
         if (n_bisect) atomicAdd(&a.counters->c[9], (unsigned long long)n_bisect);
-        if (n_steps) atomicAdd(&a.counters->c[12], (unsigned long long)n_steps);
-        if (max_steps) atomicMax(&a.counters->c[13], (unsigned long long)max_steps);
     }
 }
 // unit gradients at points 2t and 2t+1 (compute_centroid_gradient at the projected centroids, centroids_projection.cpp:1262)

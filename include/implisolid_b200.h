@@ -105,8 +105,7 @@ int isd_last_timings(float* out_ms, int cap);
  * [11]=bisection capped, [12]=bisected, [13]=kernel launches, [14]=field bytes, [15]=nodes
  * evaluated with the full program (others were proven off-surface and skipped), [16]=1 when the build
  * ran without waiting for the device in mid-step (sizes taken from the previous build of the same spec
- * and checked at the end, "gpu":{"speculate":1}), [17]=1 when such a build was dropped and done again,
- * [18]=bisection steps in all, [19]=steps of the longest bisection (both from the default finish kernel only). */
+ * and checked at the end, "gpu":{"speculate":1}), [17]=1 when such a build was dropped and done again. */
 int isd_last_counters(int64_t* out, int cap);
 /* Tests: what=0 forgets the previous build's counts (the next build waits for the device); what=1 makes the next
  * speculative build of the same spec assume a wrong left-over count, so that its end-of-build check fails and

@@ -62,7 +62,6 @@ if kt:
     print(" ".join("%s=%.3f" % (k.split("(")[0].replace("k_", ""), v[0]) for k, v in sorted(kt.items(), key=lambda kv: -kv[1][0])))
     gp = lib.last_kernel_gaps()
     print("gaps before:", " ".join("%s=%.3f" % (k.split("(")[0].replace("k_", ""), v) for k, v in sorted(gp.items(), key=lambda kv: -kv[1])[:8]), "sum=%.3f" % sum(gp.values()))
-print("bisected", c["bisected"], "steps", c["bisection_steps"], "longest", c["bisection_max_steps"], "failed", c["projection_failed"], "by type", c["projection_by_type"])
 print(a.cfg, a.R, "nodes", c["nodes"], "evaluated", c["nodes_full_eval"], "cut", c["cut_cubes"], "nv", s["nv"], "nf", s["nf"],
       {k: round(v, 4) for k, v in t.items()})
 
