@@ -129,6 +129,7 @@ struct Context {
     bool normals_valid = false, normals_host_valid = false;
     bool point_spec_on = false;             // the OB02 kernels may use K1's tile masks (c_point_spec describes the current program)
     int finish_split = 0;                   // "gpu":{"finish_split":..}: the pair path's projection finish; 0 one kernel, 1 bisect batches of 32 units + gradients, 2 bisect with lane refill + gradients
+    bool search_split = true;               // "gpu":{"search_split":1}: pair path, the search's trial points run in a lane-refill kernel of their own
     bool pair_kernels = true;               // "gpu":{"pair":1}: with point lists, two centroids per thread through the f32x2 interpreters
     std::vector<uint32_t> last_program;     // the shape program of the last build (lazy normals re-upload it)
     isd_progress_fn progress_fn = nullptr;
@@ -220,12 +221,12 @@ inline void launched() { g.launches++; }
 // Per-kernel device times ("gpu":{"kernel_times":1}; bench.py's roofline entries): a pair of events around every launch,
 // read after the build's last synchronisation.  Off by default: two event records per launch are a few per cent of a 0.4 ms step.
 enum { KT_SUPER_BOUNDS = 0, KT_TILE_BOUNDS, KT_EVAL_TILES, KT_CLASSIFY, KT_ROW_SCAN, KT_POINT_LISTS, KT_SEG_APPLY, KT_EMIT, KT_ADJACENCY, KT_FOF,
-       KT_CENTROID_GRAD, KT_FACE_WEIGHTS, KT_RESAMPLE, KT_FACE_PREPARE, KT_SEARCH, KT_FINISH, KT_LEFTOVERS, KT_QEM, KT_OTHER, KT_UNIT_GRAD, KT_N };
+       KT_CENTROID_GRAD, KT_FACE_WEIGHTS, KT_RESAMPLE, KT_FACE_PREPARE, KT_SEARCH, KT_FINISH, KT_LEFTOVERS, KT_QEM, KT_OTHER, KT_UNIT_GRAD, KT_TRIALS, KT_N };
 // the names of the kernels a build actually launched under each id (the pair path and the finish's form change them)
 const char* g_kernel_names[KT_N] = {"k_super_bounds", "k_tile_bounds", "k_eval_tiles", "k_mc_classify_tiles", "k_row_scan", "k_build_point_lists",
                                     "k_seg_apply", "k_mc_emit", "adjacency(k_vertex_degree+k_uscan+k_umbrella_fill+k_umbrella_sort)", "k_faces_of_faces",
                                     "k_centroid_gradients", "k_face_weights", "k_resample", "k_face_prepare", "k_project_search", "k_project_finish",
-                                    "k_project_leftovers", "k_qem", "other(subdivision scan)", "k_unit_gradients_pair"};
+                                    "k_project_leftovers", "k_qem", "other(subdivision scan)", "k_unit_gradients_pair", "k_search_trials_refill"};
 struct KernelTimes {
     bool on = false;
     std::vector<cudaEvent_t> pool;
@@ -1040,7 +1041,11 @@ void projection_step(bool enable_qem, bool exact_reduce, int repeat) {
     const bool pairs = g.point_spec_on && g.pair_kernels;
     g_kernel_names[KT_SEARCH] = pairs ? "k_project_search_pair" : "k_project_search";
     g_kernel_names[KT_FINISH] = !pairs ? "k_project_finish" : g.finish_split == 2 ? "k_finish_bisect_refill" : g.finish_split == 1 ? "k_finish_bisect_units" : "k_project_finish_pair";
-    if (pairs) ISD_TIMED(KT_SEARCH, k_project_search_pair<<<blocks_for(unit_launch_count(nf), 128), 128, 0, g.stream>>>(g.sdf, a));
+    if (pairs && g.search_split) {
+        ISD_TIMED(KT_SEARCH, k_project_search_pair<true><<<blocks_for(unit_launch_count(nf), 128), 128, 0, g.stream>>>(g.sdf, a));
+        const unsigned want = blocks_for(unit_launch_count(nf), 4 * kRefillRange), resident = (unsigned)g.sm_count * ISD_TRIALS_REFILL_MINBLOCKS;
+        ISD_TIMED(KT_TRIALS, k_search_trials_refill<<<want < resident ? want : resident, 128, 0, g.stream>>>(g.sdf, a));
+    } else if (pairs) ISD_TIMED(KT_SEARCH, k_project_search_pair<false><<<blocks_for(unit_launch_count(nf), 128), 128, 0, g.stream>>>(g.sdf, a));
     else ISD_TIMED(KT_SEARCH, (g.point_spec_on ? k_project_search<true> : k_project_search<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a));
     // Phase B (direction types 2..6) is only needed when phase A left centroids over, which is rare and which only the device
     // knows: the rest of the step is launched right away and does nothing in that case (the kernels test the counter), so the
@@ -1302,6 +1307,7 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
     for (int64_t& c : g.counters) c = 0;
     g.launches = 0;
     g.pair_kernels = s.pair != 0;
+    g.search_split = s.search_split != 0;
     g.want_perm = s.perm > 0;      // -1 (auto) is decided once the program is known, below
     g.finish_split = s.finish_split;
     g_kt.reset(s.kernel_times != 0);

@@ -52,8 +52,8 @@ __device__ inline void make_alpha_list(float initial_step_size, float min_step_s
 }
 
 // counters: [0..6] centroids resolved by direction type, [7] failed, [8] bisection capped, [9] bisected,
-// [10] centroids still unresolved after phase A, [11] range ticket of k_finish_bisect_refill
-struct Ob02Counters { unsigned long long c[12]; };
+// [10] centroids still unresolved after phase A, [11] range ticket of k_finish_bisect_refill, [12] of k_search_trials_refill
+struct Ob02Counters { unsigned long long c[16]; };
 
 // one atomic per warp instead of one per thread: all counters are bumped by up to every thread of the grid
 __device__ __forceinline__ void count_if(bool pred, unsigned long long* ctr) {
@@ -797,6 +797,9 @@ __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS_CG) k_centroid_gradien
 // k_project_search, centroids 2t and 2t+1 per thread.  Each centroid's result is the first sign change along its own sequence of
 // trial points (direction type 0 over the whole alpha list, then type 1 over the short list), exactly as in the scalar kernel;
 // the two sequences advance in lockstep and a lane that has finished a phase rides along on its partner's point.
+// TRIALS_LATER: the kernel stops after the gradient pass; a centroid that needs trial points is left pending (state 0, its search
+// direction and the sign of f in `best`) for k_search_trials_refill.
+template <bool TRIALS_LATER>
 __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_project_search_pair(SdfGridView sdf, ProjectArgs a) {
     const long long u = (long long)blockIdx.x * 128 + threadIdx.x;
     if (u >= unit_count(a.order, a.n)) return;
@@ -841,7 +844,8 @@ __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_project_search_pair
             }
         }
     }
-    for (int phase = 0; phase < 2; ++phase) {
+    const bool pending_mode = TRIALS_LATER && (n_alpha_full > 0 || n_alpha_short > 0);
+    for (int phase = 0; phase < 2 && !pending_mode; ++phase) {
         if (phase == 1) {
             if (ok[0] && ok[1]) break;
 #pragma unroll
@@ -875,13 +879,16 @@ __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_project_search_pair
         if (ok[k]) {
             a.best[idx[k]] = make_float4(best[k][0], best[k][1], best[k][2], best[k][3]);
             a.state[idx[k]] = settled[k] ? 5 : 1;
+        } else if (pending_mode) {
+            a.best[idx[k]] = make_float4(d[k][0], d[k][1], d[k][2], s_c[k]);
+            a.state[idx[k]] = 0;
         } else {
             a.state[idx[k]] = 2;
         }
     }
 #pragma unroll
     for (int k = 0; k < 2; ++k) {   // left-overs: one atomic per warp hands out list slots
-        const bool left = !ok[k] && (k == 0 || two);
+        const bool left = !ok[k] && !pending_mode && (k == 0 || two);
         const unsigned m = __ballot_sync(__activemask(), left);
         if (left) {
             const int leader = __ffs(m) - 1, lane = threadIdx.x & 31;
@@ -1096,13 +1103,148 @@ __global__ void __launch_bounds__(128, ISD_FINISH_UNITS_MINBLOCKS) k_finish_bise
         if (n_bisect) atomicAdd(&a.counters->c[9], (unsigned long long)n_bisect);
     }
 }
+// Trial points of the projection's search with LANE REFILL ("gpu":{"search_split":1}, default on the pair path).  After its
+// gradient pass k_project_search_pair walked the two centroids of a thread through their trial points in lockstep: a settled member
+// rode along, and a warp ran as long as its slowest lane (ncu, C4 1024^3: 13 of 32 lanes active in that part).  Here the pending
+// centroids are queued per warp exactly as in k_finish_bisect_refill below (persistent grid, ranges from a ticket, counters->c[12])
+// and a lane that has resolved its unit takes the next one.  Per centroid the sequence of trial points is the reference's:
+// direction type 0 over the whole alpha list, then the facet normal over the short list; the first sign change wins.
+constexpr int kRefillRange = 128;      // units per ticket (both lane-refill kernels)
+#ifndef ISD_TRIALS_REFILL_MINBLOCKS
+#define ISD_TRIALS_REFILL_MINBLOCKS 6
+#endif
+__global__ void __launch_bounds__(128, ISD_TRIALS_REFILL_MINBLOCKS) k_search_trials_refill(SdfGridView sdf, ProjectArgs a) {
+    __shared__ int s_queue[4][128];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int* queue = s_queue[warp];
+    const long long n_units = unit_count(a.order, a.n);
+    const float edge = a.al->avg_edge;
+    const float* alphas = a.al->alpha;
+    const int n_alpha_full = a.al->n_full, n_alpha_short = a.al->n_short;
+    long long next = 0, last = 0;
+    bool exhausted = false;
+    int head = 0, waiting = 0;
+    unsigned n_type0 = 0u, n_type1 = 0u;
+    int entry = -1;      // this lane's unit (u << 2 | members that search), or -1: idle
+    bool active[2] = {false, false};
+    int face[2] = {0, 0}, ai[2] = {0, 0}, phase[2] = {0, 0};
+    float c[2][3], d[2][3], s_c[2] = {0.0f, 0.0f};
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+#pragma unroll
+        for (int q = 0; q < 3; ++q) { c[k][q] = 0.0f; d[k][q] = 0.0f; }
+    for (;;) {
+        const unsigned idle = __ballot_sync(0xffffffffu, entry < 0);
+        const int n_idle = __popc(idle);
+        while (waiting < n_idle && !exhausted) {      // classify the next 32 units
+            if (next >= last) {      // draw another range
+                unsigned long long t = 0ull;
+                if (lane == 0) t = atomicAdd(&a.counters->c[12], 1ull);
+                t = __shfl_sync(0xffffffffu, t, 0);
+                next = (long long)t * kRefillRange;
+                last = next + kRefillRange < n_units ? next + kRefillRange : n_units;
+                if (next >= n_units) { exhausted = true; break; }
+            }
+            const long long u = next + lane;
+            int needs = 0;
+            if (u < last) {
+                int uf[2];
+                unit_faces(a.order, u, a.n, uf[0], uf[1]);
+#pragma unroll
+                for (int k = 0; k < 2; ++k)
+                    if (uf[k] >= 0 && a.state[uf[k]] == 0) needs |= 1 << k;
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, needs != 0);
+            if (needs) queue[(head + waiting + __popc(m & ((1u << lane) - 1u))) & 127] = (int)(u << 2) | needs;
+            waiting += __popc(m);
+            next += 32;
+            __syncwarp();
+        }
+        if (entry < 0) {      // idle lanes take the waiting units in lane order
+            const int r = __popc(idle & ((1u << lane) - 1u));
+            if (r < waiting) {
+                entry = queue[(head + r) & 127];
+                unit_faces(a.order, entry >> 2, a.n, face[0], face[1]);
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    active[k] = ((entry >> k) & 1) != 0;
+                    if (!active[k]) continue;
+                    const long long i = face[k];
+                    c[k][0] = a.cen[i * 3]; c[k][1] = a.cen[i * 3 + 1]; c[k][2] = a.cen[i * 3 + 2];
+                    const float4 b = a.best[i];
+                    d[k][0] = b.x; d[k][1] = b.y; d[k][2] = b.z; s_c[k] = b.w;
+                    ai[k] = 0; phase[k] = 0;
+                }
+            }
+        }
+        {
+            const int taken = waiting < n_idle ? waiting : n_idle;
+            head = (head + taken) & 127;
+            waiting -= taken;
+        }
+        __syncwarp();
+        if (__ballot_sync(0xffffffffu, entry >= 0) == 0u) break;      // no unit in flight, none waiting, range exhausted
+        if (entry >= 0) {
+            // a member at the end of a direction's alphas moves on: type 0 -> the facet normal (type 1) -> left over
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                if (!active[k]) continue;
+                if (phase[k] == 0 && ai[k] >= n_alpha_full) {
+                    phase[k] = 1; ai[k] = 0;
+                    facet_normal(a.verts, a.faces, face[k], d[k][0], d[k][1], d[k][2]);
+                }
+                if (phase[k] == 1 && ai[k] >= n_alpha_short) {
+                    a.state[face[k]] = 2;
+                    const unsigned long long slot = atomicAdd(&a.counters->c[10], 1ull);
+                    a.leftover[slot] = face[k];
+                    active[k] = false;
+                }
+            }
+            if (active[0] || active[1]) {      // one trial point per searching member
+                float p[2][3];
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    const float cc = edge * __ldg(alphas + (active[k] ? ai[k] : 0));          // (length_factor * alpha) * 4.0 / 4.0
+#pragma unroll
+                    for (int q = 0; q < 3; ++q) p[k][q] = c[k][q] + cc * d[k][q];
+                }
+                if (!active[0]) { p[0][0] = p[1][0]; p[0][1] = p[1][1]; p[0][2] = p[1][2]; }
+                if (!active[1]) { p[1][0] = p[0][0]; p[1][1] = p[0][1]; p[1][2] = p[0][2]; }
+                const F2 f = eval_f_pair(sdf, p[0][0], p[0][1], p[0][2], p[1][0], p[1][1], p[1][2]);
+                const float fv[2] = {f.x, f.y};
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    if (!active[k]) continue;
+                    if (sign_tol(fv[k]) * s_c[k] <= 0.0f) {
+                        a.best[face[k]] = make_float4(p[k][0], p[k][1], p[k][2], fv[k]);
+                        a.state[face[k]] = 1;
+                        if (phase[k] == 0) ++n_type0; else ++n_type1;
+                        active[k] = false;
+                    } else {
+                        ++ai[k];
+                    }
+                }
+            }
+            if (!active[0] && !active[1]) entry = -1;
+        }
+    }
+#pragma unroll
+    for (int dd = 16; dd > 0; dd >>= 1) {
+        n_type0 += __shfl_xor_sync(0xffffffffu, n_type0, dd);
+        n_type1 += __shfl_xor_sync(0xffffffffu, n_type1, dd);
+    }
+    if (lane == 0) {
+        if (n_type0) atomicAdd(&a.counters->c[0], (unsigned long long)n_type0);
+        if (n_type1) atomicAdd(&a.counters->c[1], (unsigned long long)n_type1);
+    }
+}
+
 // The same pass with LANE REFILL ("gpu":{"finish_split":2}).  In k_project_finish_pair a lane bisects for as long as the slowest
 // centroid of its warp (ncu, C4 1024^3: 13.7 of 32 lanes active in the bisection part); the batch form above fills all lanes at the
 // start of a batch but still runs every batch to its slowest member.  Here a lane that has finished its unit takes the next one
 // from the warp's queue at once, so every evaluation runs with (nearly) all lanes busy; the queue is topped up from the warp's
 // range of units, 32 classified at a time, whenever fewer units wait than lanes are idle.  Per centroid the sequence of
 // midpoints, tests and the iteration cap are those of k_project_finish.
-constexpr int kRefillRange = 128;      // units per ticket
 #ifndef ISD_FINISH_REFILL_MINBLOCKS
 #define ISD_FINISH_REFILL_MINBLOCKS 6
 #endif

@@ -48,6 +48,8 @@ struct McSettings {
     int perm;             // the pair kernels take the faces grouped by tile (a warp's lanes then run one instruction list) instead of in face
                           // order: 1 always, 0 never, -1 (default) when the tree's evaluations are heavy enough to pay for the scattered
                           // access (mean flops per tree node >= 40: metaball blends; measured C3 512^3 -11 %, C4 1024^3 +3.6 %)
+    int search_split;     // 1 (default): pair path only — the search's trial points run in a kernel of their own, lanes refilled from per-warp
+                          // queues (k_search_trials_refill); 0: in lockstep inside k_project_search_pair
     int speculate;        // 1 (default): a build of the spec the previous build had takes that build's counts (mesh size, cut cubes, left-over
                           // centroids) instead of waiting for the device in mid-step; the counts are checked when the build ends and a
                           // mismatch drops the result and builds again the waiting way; 0: always wait
@@ -121,6 +123,7 @@ inline McSettings parse_mc_settings(const char* json) {
     s.pair = d.get_int("gpu.pair", 1);
     s.finish_split = d.get_int("gpu.finish_split", 2);
     s.speculate = d.get_int("gpu.speculate", 1);
+    s.search_split = d.get_int("gpu.search_split", 1);
     s.perm = d.get_int("gpu.perm", -1);
     if (s.qem_enabled && !s.projection_enabled) {
         fprintf(stderr, "Invalid settings: QEM will not be applied if centroid projection is disabled\n");

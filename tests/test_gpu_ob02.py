@@ -161,8 +161,10 @@ def test_pair_kernels_change_nothing(gpu_lib, shape, R, half):
     one-centroid-per-thread kernels (pair 0), over two OB02 repeats."""
     sj = shape()
     out = []
-    for pair, split, perm in ((0, 0, 1), (1, 0, 1), (1, 1, 1), (1, 2, 1), (1, 2, 0), (1, 0, 0)):      # perm: faces taken grouped by tile / in face order
-        gpu_lib.build_geometry(sj, shapes.mc_settings(R, half, iters=2, c=1.0, projection=1, qem=1, repeats=2, point_spec=1, pair=pair, finish_split=split, perm=perm))
+    # perm: faces taken grouped by tile / in face order; ss: the search's trial points in their own lane-refill kernel / in lockstep
+    for pair, split, perm, ss in ((0, 0, 1, 1), (1, 0, 1, 1), (1, 1, 1, 0), (1, 2, 1, 1), (1, 2, 0, 1), (1, 0, 0, 0), (1, 2, 0, 0)):
+        gpu_lib.build_geometry(sj, shapes.mc_settings(R, half, iters=2, c=1.0, projection=1, qem=1, repeats=2, point_spec=1, pair=pair, finish_split=split, perm=perm,
+                                                      search_split=ss))
         v, f = gpu_lib.get_v(), gpu_lib.get_f()
         c, n = gpu_lib.projected_centroids()
         st = gpu_lib.last_counters()
