@@ -1342,6 +1342,12 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
         skip_ob02 = true;
     }
     if (any_ob02 && g.world > 1 && !g.emulate && !g.halo_mode) gather_mesh();      // OB02 runs on the stitched mesh, replicated
+    if (any_ob02 && (g.nv > 2147483647LL / 3 || g.nf > 2147483647LL / 3)) {
+        // the OB02, adjacency and subdivision kernels index corners as 3 * i in 32-bit integers
+        fprintf(stderr, "implisolid_b200: mesh too large for the OB02 stages on one GPU (%lld vertices, %lld faces; limit %lld): use more z-slabs\n",
+                g.nv, g.nf, 2147483647LL / 3);
+        abort();
+    }
     const bool faces_final = !(s.overall_repeats > 0 && s.subdiv_enabled) && !g.progress_fn;
     if (copy_out && any_ob02 && faces_final && !g.halo_mode) start_faces_copy();
     report_progress();                                             // mcc2.cpp:351
