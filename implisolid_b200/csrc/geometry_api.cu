@@ -129,6 +129,7 @@ struct Context {
     bool normals_valid = false, normals_host_valid = false;
     bool point_spec_on = false;             // the OB02 kernels may use K1's tile masks (c_point_spec describes the current program)
     int finish_split = 0;                   // "gpu":{"finish_split":..}: the pair path's projection finish; 0 one kernel, 1 bisect batches of 32 units + gradients, 2 bisect with lane refill + gradients
+    int refill_range = 0;                   // "gpu":{"refill_range":..}: units per ticket of the lane-refill kernels, 0 = by mesh size
     bool search_split = true;               // "gpu":{"search_split":1}: pair path, the search's trial points run in a lane-refill kernel of their own
     bool pair_kernels = true;               // "gpu":{"pair":1}: with point lists, two centroids per thread through the f32x2 interpreters
     std::vector<uint32_t> last_program;     // the shape program of the last build (lazy normals re-upload it)
@@ -1036,6 +1037,14 @@ void projection_step(bool enable_qem, bool exact_reduce, int repeat) {
     a.al = d_al; a.best = g.d_best.as<float4>(); a.fc = g.d_fc.as<float>(); a.state = g.d_state.as<unsigned char>();
     a.out = g.d_proj.as<float>(); a.nrm_out = g.d_pnrm.as<float>(); a.counters = g.d_counters.as<Ob02Counters>();
     a.n = nf; a.speculative = 1; a.order = face_order();
+    {   // units per ticket of the lane-refill kernels.  A ticket is a warp's serial work: where the projection is hard (C4's band of
+        // failing first directions) one range of 128 units kept a warp busy for a millisecond while the rest of a thin z-slab's grid
+        // had drained (k_search_trials_refill on an emulated 1/8 slab: 1.06 ms with 128, 0.30 ms with 32; whole mesh 0.222 / 0.205 /
+        // 0.213 ms with 128 / 64 / 32).  64, or 32 when the mesh cannot give every resident warp four tickets of 64.
+        const long long warps = (long long)g.sm_count * 6 * 4, per = unit_launch_count(nf) / (warps * 4);
+        a.range = per >= kRefillRange ? kRefillRange : 32;
+        if (g.refill_range > 0) a.range = (g.refill_range + 31) / 32 * 32;      // "gpu":{"refill_range":..}: A/B
+    }
     // the list of left-over centroids lives in the output array: k_project_finish only writes it once there are none left to list
     a.leftover = reinterpret_cast<int*>(g.d_proj.as<float>());
     const bool pairs = g.point_spec_on && g.pair_kernels;
@@ -1043,7 +1052,7 @@ void projection_step(bool enable_qem, bool exact_reduce, int repeat) {
     g_kernel_names[KT_FINISH] = !pairs ? "k_project_finish" : g.finish_split == 2 ? "k_finish_bisect_refill" : g.finish_split == 1 ? "k_finish_bisect_units" : "k_project_finish_pair";
     if (pairs && g.search_split) {
         ISD_TIMED(KT_SEARCH, k_project_search_pair<true><<<blocks_for(unit_launch_count(nf), 128), 128, 0, g.stream>>>(g.sdf, a));
-        const unsigned want = blocks_for(unit_launch_count(nf), 4 * kRefillRange), resident = (unsigned)g.sm_count * ISD_TRIALS_REFILL_MINBLOCKS;
+        const unsigned want = blocks_for(unit_launch_count(nf), 4 * a.range), resident = (unsigned)g.sm_count * ISD_TRIALS_REFILL_MINBLOCKS;
         ISD_TIMED(KT_TRIALS, k_search_trials_refill<<<want < resident ? want : resident, 128, 0, g.stream>>>(g.sdf, a));
     } else if (pairs) ISD_TIMED(KT_SEARCH, k_project_search_pair<false><<<blocks_for(unit_launch_count(nf), 128), 128, 0, g.stream>>>(g.sdf, a));
     else ISD_TIMED(KT_SEARCH, (g.point_spec_on ? k_project_search<true> : k_project_search<false>)<<<blocks_for(nf, 128), 128, 0, g.stream>>>(g.sdf, a));
@@ -1054,7 +1063,7 @@ void projection_step(bool enable_qem, bool exact_reduce, int repeat) {
     auto finish_pass = [&](const ProjectArgs& pa) {
         if (pairs && g.finish_split) {
             if (g.finish_split == 2) {
-                const unsigned want = blocks_for(unit_launch_count(nf), 4 * kRefillRange), resident = (unsigned)g.sm_count * ISD_FINISH_REFILL_MINBLOCKS;
+                const unsigned want = blocks_for(unit_launch_count(nf), 4 * pa.range), resident = (unsigned)g.sm_count * ISD_FINISH_REFILL_MINBLOCKS;
                 ISD_TIMED(KT_FINISH, k_finish_bisect_refill<<<want < resident ? want : resident, 128, 0, g.stream>>>(g.sdf, pa));
             }
             else ISD_TIMED(KT_FINISH, k_finish_bisect_units<<<blocks_for((nf + 1) / 2, 4 * kFinishRange), 128, 0, g.stream>>>(g.sdf, pa));
@@ -1308,6 +1317,7 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
     g.launches = 0;
     g.pair_kernels = s.pair != 0;
     g.search_split = s.search_split != 0;
+    g.refill_range = s.refill_range;
     g.want_perm = s.perm > 0;      // -1 (auto) is decided once the program is known, below
     g.finish_split = s.finish_split;
     g_kt.reset(s.kernel_times != 0);

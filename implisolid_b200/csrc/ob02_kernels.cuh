@@ -462,6 +462,7 @@ struct ProjectArgs {
     float* nrm_out;          // unit gradient at projected centroids
     Ob02Counters* counters;
     int n;
+    int range;               // lane-refill kernels: units per ticket (a multiple of 32; the host shrinks it for small meshes so that the grid fills the GPU)
     int speculative;         // k_project_finish: do nothing if phase A left centroids over (the host then runs phase B and calls again)
 };
 
@@ -1109,7 +1110,7 @@ __global__ void __launch_bounds__(128, ISD_FINISH_UNITS_MINBLOCKS) k_finish_bise
 // centroids are queued per warp exactly as in k_finish_bisect_refill below (persistent grid, ranges from a ticket, counters->c[12])
 // and a lane that has resolved its unit takes the next one.  Per centroid the sequence of trial points is the reference's:
 // direction type 0 over the whole alpha list, then the facet normal over the short list; the first sign change wins.
-constexpr int kRefillRange = 128;      // units per ticket (both lane-refill kernels)
+constexpr int kRefillRange = 64;       // units per ticket at most (both lane-refill kernels; ProjectArgs::range)
 #ifndef ISD_TRIALS_REFILL_MINBLOCKS
 #define ISD_TRIALS_REFILL_MINBLOCKS 6
 #endif
@@ -1141,8 +1142,8 @@ __global__ void __launch_bounds__(128, ISD_TRIALS_REFILL_MINBLOCKS) k_search_tri
                 unsigned long long t = 0ull;
                 if (lane == 0) t = atomicAdd(&a.counters->c[12], 1ull);
                 t = __shfl_sync(0xffffffffu, t, 0);
-                next = (long long)t * kRefillRange;
-                last = next + kRefillRange < n_units ? next + kRefillRange : n_units;
+                next = (long long)t * a.range;
+                last = next + a.range < n_units ? next + a.range : n_units;
                 if (next >= n_units) { exhausted = true; break; }
             }
             const long long u = next + lane;
@@ -1248,7 +1249,7 @@ __global__ void __launch_bounds__(128, ISD_TRIALS_REFILL_MINBLOCKS) k_search_tri
 #ifndef ISD_FINISH_REFILL_MINBLOCKS
 #define ISD_FINISH_REFILL_MINBLOCKS 6
 #endif
-// Persistent grid (one block per resident slot); a warp draws ranges of kRefillRange units from a ticket (counters->c[11], zeroed
+// Persistent grid (one block per resident slot); a warp draws ranges of ProjectArgs::range units (64, or 32 for small meshes) from a ticket (counters->c[11], zeroed
 // with the other counters at the start of the projection step) for as long as it has idle lanes, so lanes stay busy across range
 // boundaries and only the very end of the kernel runs with part of the lanes.
 __global__ void __launch_bounds__(128, ISD_FINISH_REFILL_MINBLOCKS) k_finish_bisect_refill(SdfGridView sdf, ProjectArgs a) {
@@ -1277,8 +1278,8 @@ __global__ void __launch_bounds__(128, ISD_FINISH_REFILL_MINBLOCKS) k_finish_bis
                 unsigned long long t = 0ull;
                 if (lane == 0) t = atomicAdd(&a.counters->c[11], 1ull);
                 t = __shfl_sync(0xffffffffu, t, 0);
-                next = (long long)t * kRefillRange;
-                last = next + kRefillRange < n_units ? next + kRefillRange : n_units;
+                next = (long long)t * a.range;
+                last = next + a.range < n_units ? next + a.range : n_units;
                 if (next >= n_units) { exhausted = true; break; }
             }
             const long long u = next + lane;
