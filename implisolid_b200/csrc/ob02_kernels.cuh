@@ -1194,11 +1194,17 @@ __global__ void __launch_bounds__(128, ISD_TRIALS_REFILL_MINBLOCKS) k_search_tri
                     phase[k] = 1; ai[k] = 0;
                     facet_normal(a.verts, a.faces, face[k], d[k][0], d[k][1], d[k][2]);
                 }
-                if (phase[k] == 1 && ai[k] >= n_alpha_short) {
-                    a.state[face[k]] = 2;
-                    const unsigned long long slot = atomicAdd(&a.counters->c[10], 1ull);
-                    a.leftover[slot] = face[k];
-                    active[k] = false;
+                const bool failed = phase[k] == 1 && ai[k] >= n_alpha_short;
+                if (failed) { a.state[face[k]] = 2; active[k] = false; }
+                {   // left over: one atomic per warp hands out the list slots of the lanes that fail in this step
+                    const unsigned fm = __ballot_sync(__activemask(), failed);
+                    if (failed) {
+                        const int leader = __ffs(fm) - 1;
+                        unsigned long long base = 0ull;
+                        if (lane == leader) base = atomicAdd(&a.counters->c[10], (unsigned long long)__popc(fm));
+                        base = __shfl_sync(fm, base, leader);
+                        a.leftover[base + __popc(fm & ((1u << lane) - 1u))] = face[k];
+                    }
                 }
             }
             if (active[0] || active[1]) {      // one trial point per searching member
