@@ -2,12 +2,9 @@
 # round 2, call v: why is the trials kernel slow on the upper half slab? (emulated rank 1/2)
 set -u
 O=gpurun_out; mkdir -p $O
-timeout 600 python -m pytest tests/test_gpu_ob02.py -m gpu -x -q 2>&1 | tail -2
 for extra in "refill_range=64" "refill_range=32" "search_split=0"; do
-  echo "== emulate 1/2 $extra"; python tools/one_step.py c4 1024 --ob02 --warm 3 --reps 3 --emulate 1/2 --gpu kernel_times=1 balance=1 $extra 2>&1 | grep -E "eval_tiles=" | cut -c1-330
+  echo "== emulate 1/2 $extra"; python tools/one_step.py c4 1024 --ob02 --warm 3 --reps 3 --emulate 1/2 --gpu kernel_times=1 balance=1 $extra 2>&1 | grep -E "eval_tiles=|rror" | cut -c1-330
 done
-echo "== whole"; python tools/one_step.py c4 1024 --ob02 --warm 3 --reps 30 2>&1 | grep -E "wall per build" | cut -c1-200
-python tools/one_step.py c4 1024 --ob02 --warm 3 --reps 5 --gpu kernel_times=1 2>&1 | grep -E "eval_tiles=" | cut -c1-330
 ncu --set full --clock-control none --profile-from-start off -k regex:"k_search_trials" -o $O/full_em12_v -f python tools/one_step.py c4 1024 --ob02 --emulate 1/2 --gpu balance=1 > $O/ncu_v.log 2>&1
 ncu -i $O/full_em12_v.ncu-rep --page raw --csv > $O/full_em12_v.csv 2>/dev/null
 python tools/ncu_full_summary.py $O/full_em12_v.csv $O/full_em12_v.txt | cut -c1-150

@@ -39,8 +39,15 @@ for kv in a.gpu:
 sj, mc = fn(), shapes.mc_settings(a.R, half, **kw)
 if a.emulate:
     r, w = (int(x) for x in a.emulate.split("/"))
+    voff = foff = 0      # global offsets of the slab = what the slabs below it hold (marching cubes only, same cuts)
+    kw_mc = {k: v for k, v in kw.items() if k not in ("iters", "c", "projection", "qem", "kernel_times")}
+    for below in range(r):
+        lib.lib.isd_dist_emulate(below, w)
+        lib.lib.isd_dist_set_offsets(0, 0)
+        lib.build_geometry_device(sj, shapes.mc_settings(a.R, half, **kw_mc)); lib.finish_geometry()
+        sl = lib.last_slab(); voff += sl["nv"]; foff += sl["nf"]
     lib.lib.isd_dist_emulate(r, w)
-    lib.lib.isd_dist_set_offsets(0, 0)
+    lib.lib.isd_dist_set_offsets(voff, foff)
     lib.lib.isd_dist_set_edge_total(95371408039445, 5212532)      # about C4 1024^3's mean edge 0.00142 x 3 x faces
 for _ in range(a.warm):
     lib.build_geometry_device(sj, mc)
