@@ -739,11 +739,11 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
     const long long store_v = g.halo_mode ? scan_v : (in_place ? gnv : nv), store_f = g.halo_mode ? scan_f - ghost_f : (in_place ? gnf : nf);
     g.d_verts.reserve((size_t)(store_v > 0 ? store_v : 1) * 3 * sizeof(float));
     g.d_faces.reserve((size_t)(store_f > 0 ? store_f : 1) * 3 * sizeof(int));
-    if (g.halo_mode && ghost_v > 0) ISD_CUDA(cudaMemsetAsync(g.d_verts.ptr, 0, (size_t)ghost_v * 3 * sizeof(float), g.stream));
     if (n_cubes > 0) {   // K4
         EmitArgs ea;
         ea.vbase = voff - ghost_v; ea.fbase = foff - ghost_f;
         ea.v_local0 = ghost_v; ea.f_local0 = ghost_f;
+        ea.ghost_vertices = g.halo_mode ? 1 : 0;
         if (g.halo_mode) { ea.vbase = 0; ea.fbase = 0; ea.v_local0 = 0; }      // local numbering = scan order, ghost vertices first
         unsigned blocks = (n_cubes + kEmitThreads - 1) / kEmitThreads;
         if (blocks > (unsigned)g.sm_count * 16u) blocks = (unsigned)g.sm_count * 16u;

@@ -378,6 +378,7 @@ struct EmitArgs {
     long long fbase;
     long long v_local0;  // scan offset of the first vertex this GPU stores (= ghost vertex count)
     long long f_local0;
+    int ghost_vertices;  // halo mode: the ghost layer's cubes write their vertices too (positions only; their faces belong to the slab below)
 };
 
 // first vertex (scan numbering) of the cube at (x, y, z): its segment's offset + the new vertices of the cubes before it
@@ -404,12 +405,19 @@ __global__ void __launch_bounds__(kEmitThreads) k_mc_emit(McDesc m, McBuffers mb
         const int t = (int)mb.list[seg >> 6];
         const int tx = t % m.g.tx, ty = (t / m.g.tx) % m.g.ty, tzl = t / (m.g.tx * m.g.ty);
         const int x = 8 * tx + l, y = 8 * ty + (r & 7), z = m.g.z0 + 8 * tzl + (r >> 3);
-        if (z < m.emit_z0) continue;          // ghost layer: counted here, emitted by the slab below
+        // Ghost layer: counted here, emitted by the slab below.  In halo mode its VERTICES are still written (the local mesh keeps
+        // them in its first slots): the lowest halo layer's faces hang on them, and although nothing the slab exports depends on
+        // those faces, the OB02 kernels evaluate the tree at their centroids — with the slots left at zero those were giant
+        // triangles to the origin whose every evaluation ran the whole tree outside the work-list tiles and failed every search
+        // direction (100 us per evaluation in a warp of its own: it dominated the sharded runs' projection).
+        const bool ghost = z < m.emit_z0;
+        if (ghost && !ea.ghost_vertices) continue;
         unsigned R[3][3];                     // sign rows (dy, dz) in {-1,0,1}^2: bit j <-> node x - 1 + j
 #pragma unroll
         for (int dz = 0; dz < 3; ++dz)
 #pragma unroll
-            for (int dy = 0; dy < 3; ++dy) R[dz][dy] = sign_bits4(sign_row(m, signs, y + dy - 1, z + dz - 1), x - 1);
+            for (int dy = 0; dy < 3; ++dy)      // a ghost cube only needs its own case code: the plane below it is not resident
+                R[dz][dy] = (ghost && dz == 0) ? 0u : sign_bits4(sign_row(m, signs, y + dy - 1, z + dz - 1), x - 1);
         // rows: 0 own (y,z)   1 B (y,z-1)   2 C (y-1,z)   3 A (y-1,z-1); the cube at x sits at bit position 1
         const int rdy[4] = {1, 1, 0, 0}, rdz[4] = {1, 0, 1, 0};
         unsigned code[4], codep[3];
@@ -456,7 +464,7 @@ __global__ void __launch_bounds__(kEmitThreads) k_mc_emit(McDesc m, McBuffers mb
                 }
             }
         }
-        if (nt == 0) continue;
+        if (nt == 0 || ghost) continue;
         // ---- vertex index of every cut edge (SURVEY Appendix A + first-appearance cube) --------------------------------
         long long ev[12];
 #pragma unroll

@@ -1126,6 +1126,9 @@ __global__ void __launch_bounds__(128, ISD_TRIALS_REFILL_MINBLOCKS) k_search_tri
     bool exhausted = false;
     int head = 0, waiting = 0;
     unsigned n_type0 = 0u, n_type1 = 0u;
+#ifdef ISD_TRIALS_DIAG
+    unsigned long long diag_steps = 0ull, diag_max_cyc = 0ull, diag_t0 = clock64();
+#endif
     int entry = -1;      // this lane's unit (u << 2 | members that search), or -1: idle
     bool active[2] = {false, false};
     int face[2] = {0, 0}, ai[2] = {0, 0}, phase[2] = {0, 0};
@@ -1217,8 +1220,14 @@ __global__ void __launch_bounds__(128, ISD_TRIALS_REFILL_MINBLOCKS) k_search_tri
                 }
                 if (!active[0]) { p[0][0] = p[1][0]; p[0][1] = p[1][1]; p[0][2] = p[1][2]; }
                 if (!active[1]) { p[1][0] = p[0][0]; p[1][1] = p[0][1]; p[1][2] = p[0][2]; }
+#ifdef ISD_TRIALS_DIAG
+                const unsigned long long diag_a = clock64();
+#endif
                 const F2 f = eval_f_pair(sdf, p[0][0], p[0][1], p[0][2], p[1][0], p[1][1], p[1][2]);
                 const float fv[2] = {f.x, f.y};
+#ifdef ISD_TRIALS_DIAG
+                { const unsigned long long dc = clock64() - diag_a; diag_max_cyc = dc > diag_max_cyc ? dc : diag_max_cyc; ++diag_steps; }
+#endif
 #pragma unroll
                 for (int k = 0; k < 2; ++k) {
                     if (!active[k]) continue;
@@ -1240,6 +1249,14 @@ __global__ void __launch_bounds__(128, ISD_TRIALS_REFILL_MINBLOCKS) k_search_tri
         n_type0 += __shfl_xor_sync(0xffffffffu, n_type0, dd);
         n_type1 += __shfl_xor_sync(0xffffffffu, n_type1, dd);
     }
+#ifdef ISD_TRIALS_DIAG
+    {      // diagnostic build only: the warps that lived longest
+        const unsigned long long life = clock64() - diag_t0;
+        if (lane == 0 && life > 600000ull)
+            printf("trials warp %d.%d: life %llu cyc, steps %llu, slowest step %llu cyc, last ticket start %lld of %lld units\n", (int)blockIdx.x, warp, life, diag_steps,
+                   diag_max_cyc, next, n_units);
+    }
+#endif
     if (lane == 0) {
         if (n_type0) atomicAdd(&a.counters->c[0], (unsigned long long)n_type0);
         if (n_type1) atomicAdd(&a.counters->c[1], (unsigned long long)n_type1);
