@@ -738,6 +738,9 @@ __device__ __forceinline__ int pair_slot(const PointSpec& ps, float ax, float ay
 #ifndef ISD_PAIR_MINBLOCKS_CG
 #define ISD_PAIR_MINBLOCKS_CG 7
 #endif
+#ifndef ISD_PAIR_MINBLOCKS_G      // the search's gradient pass (trials elsewhere) and the final unit gradients
+#define ISD_PAIR_MINBLOCKS_G 7      // 72 registers: 3.955 against 3.991 ms per C4 1024^3 build with 6 (80), 4.065 with 5 (96)
+#endif
 // f at two points / f and grad f at two points (.x = first point, .y = second)
 ISD_PAIR_FN F2 eval_f_pair(SdfGridView sdf, float ax, float ay, float az, float bx, float by, float bz) {
     const int slot = pair_slot(c_point_spec, ax, ay, az, bx, by, bz);
@@ -801,7 +804,7 @@ __global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS_CG) k_centroid_gradien
 // TRIALS_LATER: the kernel stops after the gradient pass; a centroid that needs trial points is left pending (state 0, its search
 // direction and the sign of f in `best`) for k_search_trials_refill.
 template <bool TRIALS_LATER>
-__global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_project_search_pair(SdfGridView sdf, ProjectArgs a) {
+__global__ void __launch_bounds__(128, TRIALS_LATER ? ISD_PAIR_MINBLOCKS_G : ISD_PAIR_MINBLOCKS) k_project_search_pair(SdfGridView sdf, ProjectArgs a) {
     const long long u = (long long)blockIdx.x * 128 + threadIdx.x;
     if (u >= unit_count(a.order, a.n)) return;
     int ia, ib;
@@ -1405,7 +1408,7 @@ __global__ void __launch_bounds__(128, ISD_FINISH_REFILL_MINBLOCKS) k_finish_bis
     }
 }
 // unit gradients at points 2t and 2t+1 (compute_centroid_gradient at the projected centroids, centroids_projection.cpp:1262)
-__global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS) k_unit_gradients_pair(SdfGridView sdf, const float* __restrict__ pts, int n, float* __restrict__ nrm,
+__global__ void __launch_bounds__(128, ISD_PAIR_MINBLOCKS_G) k_unit_gradients_pair(SdfGridView sdf, const float* __restrict__ pts, int n, float* __restrict__ nrm,
                                                                                  const Ob02Counters* __restrict__ skip_if_leftovers,
                                                                                  const unsigned char* __restrict__ state, FaceOrder order) {
     const long long u = (long long)blockIdx.x * 128 + threadIdx.x;
