@@ -429,9 +429,11 @@ void setup_grid(const McSettings& s, const ShapeCompiler::Program& prog) {
         !s.subdiv_enabled && !g.progress_fn) {
         // Dependency radius in cube layers: a resampling iteration moves a vertex from the centroids, normals and
         // neighbour-face curvatures of its umbrella (2 layers of input around it), projection + QEM from the faces around it
-        // (1 layer); one more layer because the lowest halo layer's faces hang on ghost vertices that are never written.
+        // (1 layer).  (Round 1 added one more layer because the lowest halo layer's faces hung on ghost vertices that were never
+        // written; k_mc_emit writes them now and tools/halo_check.py holds the stitched meshes bit-identical without that layer —
+        // and different with one layer less still.)
         const int per_repeat = 2 * s.vresampl_iters + ((s.projection_enabled && s.qem_enabled) ? 1 : 0);
-        g.halo = s.halo > 0 ? s.halo : s.overall_repeats * per_repeat + 1;
+        g.halo = s.halo > 0 ? s.halo : (s.overall_repeats * per_repeat > 1 ? s.overall_repeats * per_repeat : 1);
         g.halo_mode = true;
         zb = (zb - g.halo > 1) ? zb - g.halo : 1;
         ze = (ze + g.halo < S - 2) ? ze + g.halo : S - 2;

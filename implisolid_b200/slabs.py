@@ -75,12 +75,11 @@ def balanced_cuts(tile_hist, resolution, world):
 
 def halo_layers(overall_repeats, vresampl_iters, projection, qem, override=-1):
     """Cube layers a slab recomputes on each side in halo mode (csrc/geometry_api.cu: setup_grid): a
-    resampling iteration reads two layers around a vertex, projection + QEM one, and one more layer because the lowest
-    halo layer's faces hang on ghost vertices that are never written."""
+    resampling iteration reads two layers around a vertex, projection + QEM one; at least one."""
     if override > 0:
         return override
     per_repeat = 2 * vresampl_iters + (1 if (projection and qem) else 0)
-    return overall_repeats * per_repeat + 1
+    return max(1, overall_repeats * per_repeat)
 
 
 def halo_slab(resolution, rank, world, halo, cuts=None):

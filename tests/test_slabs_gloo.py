@@ -130,10 +130,10 @@ def test_balanced_cuts_equal_plain_partition_on_a_flat_histogram():
 
 
 def test_halo_radius_and_clamping():
-    assert slabs.halo_layers(1, 1, True, True) == 4
-    assert slabs.halo_layers(2, 1, True, True) == 7
+    assert slabs.halo_layers(1, 1, True, True) == 3
+    assert slabs.halo_layers(2, 1, True, True) == 6
     assert slabs.halo_layers(1, 0, True, False) == 1
-    assert slabs.halo_layers(3, 2, False, False) == 13
+    assert slabs.halo_layers(3, 2, False, False) == 12
     assert slabs.halo_layers(2, 1, True, True, override=5) == 5
     R, world = 64, 4
     S = R + 5
