@@ -82,6 +82,8 @@ EXT_SIGNATURES = {
                                 ctypes.c_float, ctypes.c_int, ctypes.c_int]),
     "isd_faces_of_faces": (None, [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
     "isd_umbrella": (None, [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]),
+    "isd_umbrella_noalloc": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
+    "isd_umbrella_noalloc_max_vertices": (ctypes.c_int, []),
     "isd_eval_points": (None, [ctypes.c_char_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p]),
     "isd_set_progress_callback": (None, [ctypes.c_void_p, ctypes.c_void_p]),
     "isd_get_n_ptr": (ctypes.c_void_p, []),

@@ -1779,6 +1779,77 @@ void isd_umbrella(const int* faces, int nf, int nv, int* offsets_nv1, int* items
     ISD_CUDA(cudaStreamSynchronize(g.stream));
 }
 
+// ---- isd_umbrella without any allocation (no counterpart in the reference) -------
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it): the umbrella CSR of
+// a mesh whose faces are already in device memory, written to device arrays the caller owns.  The scratch the kernels need —
+// per-vertex degree and fill cursor, the single-pass scan's block state — lives in ONE file-scope device array of fixed size
+// (4.2 MB, held by every GPU that loads the library until the process exits) instead of the grow-only buffers of build_adjacency().
+// In host code `s_noalloc_scratch` is only a stand-in for the symbol: its device address comes from cudaGetSymbolAddress, once per
+// device, with that device current.  Every call shares the array, so calls that overlap on the GPU (different streams, or graph
+// launches in flight together) race; what must start at zero is cleared by every call.
+constexpr int kNoAllocMaxVertices = 524288;      // stated maximum: meshes of up to 2^19 vertices
+constexpr size_t kNoAllocStateWords = 4 + 2 * (size_t)kUScanMaxBlocks;
+constexpr size_t kNoAllocScratchBytes = (2 * ((size_t)kNoAllocMaxVertices + 1) + kNoAllocStateWords) * sizeof(unsigned);
+}      // extern "C" (reopened below: the array has file scope and internal linkage)
+static __device__ __align__(256) unsigned char s_noalloc_scratch[kNoAllocScratchBytes];
+extern "C" {
+int isd_umbrella_noalloc(const int* d_faces, int nf, int nv, int* d_offsets_nv1, int* d_items_3nf, void* cuda_stream) {
+    if (!g.ready) {      // ensure_init() creates streams and pinned buffers: not something this entry point may do
+        fprintf(stderr, "implisolid_b200: isd_umbrella_noalloc: call isd_init() first (this entry point allocates nothing, not even the library's streams)\n");
+        return 2;
+    }
+    if (nv <= 0 || nf < 0 || d_offsets_nv1 == nullptr || (nf > 0 && (d_faces == nullptr || d_items_3nf == nullptr))) {
+        fprintf(stderr, "implisolid_b200: isd_umbrella_noalloc: bad arguments (nv %d, nf %d)\n", nv, nf);
+        return 1;
+    }
+    if (nv > kNoAllocMaxVertices || nf > 2147483647 / 3) {
+        fprintf(stderr, "implisolid_b200: isd_umbrella_noalloc: mesh too large for the fixed scratch array (%d vertices, limit %d; %d faces, limit %d): use "
+                        "isd_umbrella, which allocates\n", nv, kNoAllocMaxVertices, nf, 2147483647 / 3);
+        return 1;
+    }
+#define ISD_NOALLOC_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { \
+        fprintf(stderr, "implisolid_b200: isd_umbrella_noalloc: %s at line %d: %s\n", cudaGetErrorName(e__), __LINE__, cudaGetErrorString(e__)); return 3; } } while (0)
+    static unsigned char* scratch_of_device[64] = {nullptr};      // device address of s_noalloc_scratch, per device
+    int dev = 0;
+    ISD_NOALLOC_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { fprintf(stderr, "implisolid_b200: isd_umbrella_noalloc: device %d out of range\n", dev); return 1; }
+    if (scratch_of_device[dev] == nullptr) {
+        unsigned char* ptr = nullptr;
+        ISD_NOALLOC_CUDA(cudaGetSymbolAddress((void**)&ptr, s_noalloc_scratch));
+        scratch_of_device[dev] = ptr;
+    }
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
+    unsigned* deg = reinterpret_cast<unsigned*>(scratch_of_device[dev]);
+    unsigned* cursor = deg + (kNoAllocMaxVertices + 1);
+    unsigned* state = cursor + (kNoAllocMaxVertices + 1);
+    unsigned* offsets = reinterpret_cast<unsigned*>(d_offsets_nv1);
+    if (nf == 0) {
+        ISD_NOALLOC_CUDA(cudaMemsetAsync(offsets, 0, ((size_t)nv + 1) * sizeof(unsigned), st));
+        return 0;
+    }
+    // the array keeps the previous call's contents: degree, cursor and scan state start at zero
+    ISD_NOALLOC_CUDA(cudaMemsetAsync(deg, 0, ((size_t)nv + 1) * sizeof(unsigned), st));
+    ISD_NOALLOC_CUDA(cudaMemsetAsync(cursor, 0, ((size_t)nv + 1) * sizeof(unsigned), st));
+    ISD_NOALLOC_CUDA(cudaMemsetAsync(state, 0, kNoAllocStateWords * sizeof(unsigned), st));
+    const unsigned corner_blocks = (unsigned)(((long long)nf * 3 + 255) / 256);
+    k_vertex_degree<<<corner_blocks, 256, 0, st>>>(d_faces, nf, deg);
+    ISD_NOALLOC_CUDA(cudaGetLastError());
+    {   // exclusive_scan_u32's launch geometry
+        int blocks = (int)(((long long)nv + kUScanThreads * 4 - 1) / (kUScanThreads * 4));
+        if (blocks > kUScanMaxBlocks) blocks = kUScanMaxBlocks;
+        const long long per_block = (((long long)nv + blocks - 1) / blocks + kUScanThreads - 1) / kUScanThreads * kUScanThreads;
+        k_uscan<<<blocks, kUScanThreads, 0, st>>>(deg, (long long)nv, per_block, state, offsets);
+        ISD_NOALLOC_CUDA(cudaGetLastError());
+    }
+    k_umbrella_fill<<<corner_blocks, 256, 0, st>>>(d_faces, nf, offsets, cursor, d_items_3nf);
+    ISD_NOALLOC_CUDA(cudaGetLastError());
+    k_umbrella_sort<<<(unsigned)((nv + 127) / 128), 128, 0, st>>>(nv, offsets, d_items_3nf);
+    ISD_NOALLOC_CUDA(cudaGetLastError());
+#undef ISD_NOALLOC_CUDA
+    return 0;
+}
+int isd_umbrella_noalloc_max_vertices(void) { return kNoAllocMaxVertices; }
+
 void isd_eval_points(const char* shape_parameters_json, int ignore_root_matrix, const float* xyz, int64_t n, float* f_out, float* grad_out) {
     ensure_init();
     if (n <= 0) return;

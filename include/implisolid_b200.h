@@ -145,6 +145,15 @@ void isd_ob02_on_mesh(const char* shape_parameters_json, float* verts, int nv, c
 /* mesh adjacency as the OB02 stages see it (mesh_algorithms.hpp:50-209) */
 void isd_faces_of_faces(const int* faces, int nf, int nv, int* out_3nf);
 void isd_umbrella(const int* faces, int nf, int nv, int* offsets_nv1, int* items_3nf);
+/* isd_umbrella for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No
+ * counterpart in the reference.  All pointers are DEVICE pointers the caller owns
+ * (faces: 3*nf ints in; offsets: nv+1 ints out; items: 3*nf ints out); the work is enqueued on `cuda_stream` (a cudaStream_t, NULL =
+ * the library's stream) and NOT waited for.  The call allocates nothing: its scratch is one fixed 4.2 MB device array inside the
+ * library, so nv <= isd_umbrella_noalloc_max_vertices() (524288), every call shares that array and calls that overlap on the GPU
+ * race.  isd_init() must have been called.  Returns 0, or 1 bad arguments / mesh beyond the limit, 2 library not initialised,
+ * 3 CUDA error (each with a message on stderr). */
+int isd_umbrella_noalloc(const int* d_faces, int nf, int nv, int* d_offsets_nv1, int* d_items_3nf, void* cuda_stream);
+int isd_umbrella_noalloc_max_vertices(void);
 
 /* Points without the 50 000 cap of set_x: f and grad f at n host points (device kernel). */
 void isd_eval_points(const char* shape_parameters_json, int ignore_root_matrix, const float* xyz, int64_t n,
