@@ -46,6 +46,8 @@ def configs():
                        name="C2 cube-minus-cylinder (affine), %s, R=256, box +-0.8" % OB02_TEXT),
         "c3_512": dict(shape=shapes.c3_metaballs(), R=512, half=1.2,
                        name="C3 64-centre metaballs (Union of 16 meta_balls nodes), %s, R=512, box +-1.2" % OB02_TEXT),
+        "c3ii_512": dict(shape=shapes.c3_sum_blend(), R=512, half=1.2,
+                         name="C3(ii) one meta_balls node, 64 blobs summed (extension, not expressible in the reference), %s, R=512, box +-1.2" % OB02_TEXT),
         "c5_2048": dict(shape=shapes.c4_deep_chain(), R=2048, half=1.0,
                         name="C5 = the C4 shape at R=2048, %s, box +-1.0" % OB02_TEXT),
     }
@@ -456,7 +458,7 @@ def main():
     # ---- the other BASELINE configs, a few steps each ----
     others = {}
     if not args.no_other_configs:
-        plan = [("c5_2048", 5, 30)] if world > 1 else [("c2_256", 20, 3), ("c3_512", 10, 3), ("c5_2048", 3, 2)]
+        plan = [("c5_2048", 5, 30)] if world > 1 else [("c2_256", 20, 3), ("c3_512", 10, 3), ("c3ii_512", 10, 3), ("c5_2048", 3, 2)]
         for name, steps, warm in plan:
             c = cfgs[name]
             try:

@@ -367,6 +367,22 @@ private:
             float time = 0.1f;
             d.to_float(d.child(node, "time"), &time);
             std::unique_ptr<ShapeNode> n = leaf(OP_METABALLS, m);
+            // Extension (SURVEY §8(d) C3 variant (ii), not expressible in the reference, whose factory always builds four blobs
+            // from `time`): "balls": [x, y, z, strength, subtract, ...] gives the node's blobs explicitly — a single-node SUM blend
+            // of any number of centres, evaluated by the very loop of meta_balls_Rydgard.hpp:89-144.
+            const int balls = d.child(node, "balls");
+            if (balls >= 0) {
+                for (int c = d.first_child(balls); c >= 0; c = d.next(c)) {
+                    float v;
+                    if (!d.to_float(c, &v)) { fprintf(stderr, "implisolid_b200: bad \"balls\" entry\n"); abort(); }
+                    n->params.push_back(v);
+                }
+                if (n->params.empty() || n->params.size() % 5 != 0 || n->params.size() / 5 > 512) {
+                    fprintf(stderr, "implisolid_b200: \"balls\" needs 5 numbers per ball (x, y, z, strength, subtract), 1 to 512 balls\n");
+                    abort();
+                }
+                return n;
+            }
             metaball_centres(4, time, n->params);
             return n;
         }

@@ -73,6 +73,20 @@ def c3_metaballs():
     return json.dumps({"type": "Union", "matrix": EYE, "children": kids})
 
 
+def c3_sum_blend(n_balls=64, strength=0.2, subtract=0.75, seed=64):
+    """C3(ii), the perf variant of SURVEY §8(d): ONE meta_balls node whose 64 blobs are summed (the "balls" extension key — the
+    reference's factory always builds four blobs from `time`, so this spec is not expressible there; the oracle evaluates it with
+    the reference's own loop).  Centres default_rng(64).uniform(-0.5, 0.5); the reference removed the val > 0 clamp, so every ball
+    contributes -subtract/100 far away and `subtract` is scaled with the count (12 * 4 / 64 = 0.75); strength 0.2 gives an iso-surface
+    of area 5.2 inside [-0.63, 0.63]^3 (SURVEY asks for 5-8)."""
+    rng = np.random.default_rng(seed)
+    cen = rng.uniform(-0.5, 0.5, size=(n_balls, 3))
+    flat = []
+    for c in cen:
+        flat += [float(np.float32(c[0])), float(np.float32(c[1])), float(np.float32(c[2])), float(np.float32(strength)), float(np.float32(subtract))]
+    return json.dumps({"type": "meta_balls", "time": 0.1, "matrix": EYE, "balls": flat})
+
+
 def c4_deep_chain(n_prims=32, seed=1234):
     """C4: left-deep chain of n_prims transformed primitives, ops cycle [Union x3, Difference x1]."""
     rng = np.random.default_rng(seed)

@@ -328,6 +328,12 @@ struct meta_balls : implicit_function {
         }
         set_matrix(m);
     }
+    // extension ("balls" key; SURVEY §8(d) C3 variant (ii), oracle-only semantics: the reference's factory cannot express it):
+    // the blobs given explicitly, evaluated by the same loops
+    meta_balls(const REAL m[12], const std::vector<REAL>& flat5, REAL scale) {
+        for (size_t i = 0; i + 4 < flat5.size(); i += 5) balls.push_back(ball_t{flat5[i], flat5[i + 1], flat5[i + 2], flat5[i + 3], flat5[i + 4], scale});
+        set_matrix(m);
+    }
     void eval_implicit(const vects& x, scalars* f) const override {
         for (size_t i = 0; i < x.n(); i++) (*f)[i] = 0.0;
         const vects lx = prepare_inner_vectors(Minv, x);
@@ -748,6 +754,12 @@ inline const implicit_function* object_factory(Shape& S, const ojson::Node& node
     if (name == "meta_balls") {                                                          // :654-673
         matrix();
         REAL time = node.get_float("time", 0.1);
+        if (const ojson::Node* bl = node.child("balls")) {
+            std::vector<REAL> flat;
+            for (auto& kv : bl->kids) { float v = 0; if (!kv.second.as_float(&v)) { fprintf(stderr, "oracle: bad balls entry\n"); abort(); } flat.push_back(v); }
+            if (flat.empty() || flat.size() % 5 != 0) { fprintf(stderr, "oracle: balls needs 5 numbers per ball\n"); abort(); }
+            return S.keep(new meta_balls(m, flat, 1.0));
+        }
         return S.keep(new meta_balls(m, 4, time, 1.0));
     }
     if (name == "Union" || name == "Intersection" || name == "Difference") {

@@ -57,8 +57,9 @@ def test_field_cases_mesh_bit_exact(gpu_lib, oracle, name, shape, R, half):
 
 
 @pytest.mark.parametrize("name,shape,R,half", CASES + [("c2_r200", shapes.c2_cube_minus_cylinder, 200, 0.8), ("c4_r160", shapes.c4_deep_chain, 160, 1.0),
-                                                  ("c3_r120", shapes.c3_metaballs, 120, 1.2), ("moon_r130", shapes.demo_moon, 130, 1.0)],
-                         ids=[c[0] for c in CASES] + ["c2_r200", "c4_r160", "c3_r120", "moon_r130"])
+                                                  ("c3_r120", shapes.c3_metaballs, 120, 1.2), ("moon_r130", shapes.demo_moon, 130, 1.0),
+                                                  ("c3_sum_blend_r120", shapes.c3_sum_blend, 120, 1.2)],
+                         ids=[c[0] for c in CASES] + ["c2_r200", "c4_r160", "c3_r120", "moon_r130", "c3_sum_blend_r120"])
 def test_tile_pruning_changes_nothing(gpu_lib, name, shape, R, half):
     """Interval pruning (the default) must give the same mesh, bit for bit, as evaluating every node; and every tile
     it does evaluate holds the same field bits."""

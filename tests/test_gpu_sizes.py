@@ -63,7 +63,9 @@ def test_c2_256_both_cube_variants(gpu_lib, cube_mode):
 
 
 @pytest.mark.parametrize("name,shape,R,half", [("c2_256", shapes.c2_cube_minus_cylinder, 256, 0.8), ("c3_256", shapes.c3_metaballs, 256, 1.2),
-                                               ("c4_192", shapes.c4_deep_chain, 192, 1.0)])
+                                               ("c4_192", shapes.c4_deep_chain, 192, 1.0),
+                                               # C3 perf variant (ii) of SURVEY §8(d): one node, 64 blobs summed ("balls" extension)
+                                               ("c3_sum_blend_160", shapes.c3_sum_blend, 160, 1.2)])
 def test_full_pipeline_default_settings_at_size(gpu_lib, name, shape, R, half):
     o = load_oracle_mt()
     sj, mc = shape(), shapes.mc_settings(R, half, **OB02)

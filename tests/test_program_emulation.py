@@ -7,7 +7,7 @@ import pytest
 
 from implisolid_b200 import shapes
 
-SHAPES = ["c1_sphere", "c2_cube_minus_cylinder", "c3_metaballs", "c4_deep_chain", "demo_moon", "simple_cone", "bushy_tree",
+SHAPES = ["c1_sphere", "c2_cube_minus_cylinder", "c3_metaballs", "c3_sum_blend", "c4_deep_chain", "demo_moon", "simple_cone", "bushy_tree",
           # SURVEY §8 f-N1: torus / heart / mushroom go through double-precision powers (glibc pow in the oracle as in the
           # reference, multiplications and sqrt in the product); on these seeded points the results are bit-identical
           "n1_torus", "n1_heart", "n1_tetrahedron", "n1_mushroom", "n1_half_plane_cut", "n1_lid_slab", "n1_medley"]

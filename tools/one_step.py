@@ -13,7 +13,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import implisolid_b200
 from implisolid_b200 import shapes
 
-CFG = {"c1": (shapes.c1_sphere, 0.55), "c2": (shapes.c2_cube_minus_cylinder, 0.8), "c3": (shapes.c3_metaballs, 1.2),
+CFG = {"c1": (shapes.c1_sphere, 0.55), "c2": (shapes.c2_cube_minus_cylinder, 0.8), "c3": (shapes.c3_metaballs, 1.2), "c3ii": (shapes.c3_sum_blend, 1.2),
        "c4": (shapes.c4_deep_chain, 1.0)}
 
 ap = argparse.ArgumentParser()
