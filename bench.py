@@ -493,6 +493,7 @@ def main():
         "k_seg_apply": n_work_tiles * 64 * 24.0 + cut * 8.0,                 # segment record in, offsets out; 8 B per cut cube out
         "k_mc_emit": cut * 8.0 + 12.0 * (nv_local + nf_local) + 16.0 * nv_local,     # cube list in, vertices + faces out, <= 4 field values per vertex in
         "adjacency(k_vertex_degree+k_uscan+k_umbrella_fill+k_umbrella_sort)": 12.0 * nf_local * 5 + 8.0 * nv_local * 2,
+        "adjacency(k_mc_adjacency<0>+k_uscan+k_mc_adjacency<1>)": 24.0 * nf_local + 12.0 * nv_local + 16.0 * cut,      # items + faces-of-faces out, degree / offsets, cube list twice
         "k_faces_of_faces": 24.0 * nf_local,
         "k_face_weights": 40.0 * nf_local,
         "k_resample": 28.0 * nv_local + 20.0 * 3 * nf_local,

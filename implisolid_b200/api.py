@@ -75,6 +75,7 @@ EXT_SIGNATURES = {
     "isd_get_case_codes": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int64]),
     "isd_average_edge": (ctypes.c_float, []),
     "isd_get_projected_centroids": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int64]),
+    "isd_debug_adjacency": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
     "isd_get_centroid_normals": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int64]),
     "isd_set_sdf_grid": (None, [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_float, ctypes.c_float,
                                 ctypes.c_float, ctypes.c_void_p]),
@@ -325,6 +326,16 @@ class GeometryLibrary:
         if self.lib.isd_get_projected_centroids(c.ctypes.data, c.size) or self.lib.isd_get_centroid_normals(nr.ctypes.data, nr.size):
             raise RuntimeError("no projection in the last build")
         return c, nr
+
+    def debug_adjacency(self, nv, nf, fof=True):
+        """(umbrella offsets, umbrella items, faces-of-faces or None) the last build's OB02 stages used."""
+        off = np.empty(nv + 1, dtype=np.int32)
+        items = np.empty(nf * 3, dtype=np.int32)
+        ff = np.empty(nf * 3, dtype=np.int32) if fof else None
+        rc = self.lib.isd_debug_adjacency(off.ctypes.data, items.ctypes.data, ff.ctypes.data if fof else None)
+        if rc:
+            raise RuntimeError("no adjacency tables from the last build (%d)" % rc)
+        return off, items, ff
 
     def average_edge(self):
         return float(self.lib.isd_average_edge())

@@ -22,6 +22,7 @@
 #include "device_util.hpp"
 #include "field_kernel.cuh"
 #include "mc_kernels.cuh"
+#include "mc_adjacency.cuh"
 #include "ob02_kernels.cuh"
 #include "subdiv_kernels.cuh"
 #include "settings.hpp"
@@ -116,6 +117,9 @@ struct Context {
     DeviceBuffer d_cen, d_nrm, d_deg, d_uoff, d_uitems, d_cursor, d_fof, d_w, d_len3, d_best, d_fc, d_state, d_proj, d_pnrm, d_point_lists,
         d_noise, d_scal, d_counters, d_upartials;
     bool adjacency_valid = false, fof_valid_ = false;
+    // adjacency from the marching-cubes topology (mc_adjacency.cuh): what K2-K4 left behind, valid while the mesh is K4's own
+    McDesc topo_m{}; McBuffers topo_mb{}; EmitArgs topo_ea{};
+    bool topo_valid = false, want_topo = true;      // "gpu":{"mc_adjacency":1}
     DeviceBuffer d_perm;                    // faces grouped by tile for the pair kernels (mc_kernels.cuh k_seg_apply) + its length counter in front
     bool perm_valid = false, want_perm = true;      // "gpu":{"perm":1}
     long long perm_units_bound = 0;         // >= perm length / 2 (the length itself stays on the device)
@@ -212,6 +216,14 @@ void ensure_init(int device = -1) {
     ISD_CUDA(cudaMemcpyToSymbol(d_case_info, info, sizeof(info)));
     ISD_CUDA(cudaMemcpyToSymbol(d_tri_table, ISD_MC_TRI, sizeof(ISD_MC_TRI)));
     ISD_CUDA(cudaMemcpyToSymbol(d_edge_mask, ISD_MC_EDGE_MASK, sizeof(ISD_MC_EDGE_MASK)));
+    {   // which triangles of a case use which local edge (mc_adjacency.cuh), from the reference's own triangle table
+        static uint8_t edge_tris[256 * 12];
+        memset(edge_tris, 0, sizeof(edge_tris));
+        for (int c = 0; c < 256; ++c)
+            for (int t = 0; t < (int)ISD_MC_NTRI[c]; ++t)
+                for (int k = 0; k < 3; ++k) edge_tris[c * 12 + ISD_MC_TRI[c * 16 + 3 * t + k]] |= (uint8_t)(1u << t);
+        ISD_CUDA(cudaMemcpyToSymbol(d_edge_tris, edge_tris, sizeof(edge_tris)));
+    }
     g.h_small.reserve(4096);
     g.ready = true;
 }
@@ -760,6 +772,12 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         g.own_f0 -= ghost_f; g.own_f1 -= ghost_f;
     }
     g.gathered = false;
+    g.topo_valid = false;
+    if (n_cubes > 0 && (g.world == 1 || g.halo_mode)) {      // the local mesh is what K4 emitted, numbered in scan order
+        g.topo_m = m; g.topo_mb = mb;
+        g.topo_ea.vbase = 0; g.topo_ea.fbase = 0; g.topo_ea.v_local0 = 0; g.topo_ea.f_local0 = g.halo_mode ? ghost_f : 0; g.topo_ea.ghost_vertices = 0;
+        g.topo_valid = true;
+    }
     g.slab[0] = g.own_zb; g.slab[1] = g.own_ze; g.slab[2] = voff; g.slab[3] = foff;
     g.slab[4] = nv; g.slab[5] = nf; g.slab[6] = gnv; g.slab[7] = gnf;
     g.counters[0] = (int64_t)gd.S * gd.S * gd.nz;
@@ -801,6 +819,7 @@ void gather_mesh() {
     g.nv = gnv; g.nf = gnf;
     g.gathered = true;
     g.perm_valid = false;
+    g.topo_valid = false;
     g.host_valid = false;
 }
 
@@ -830,7 +849,28 @@ long long unit_launch_count(long long nf) { return g.perm_valid ? g.perm_units_b
 // umbrella CSR (always) and faces-of-faces (resampling only); the face list does not change between OB02 steps
 void build_adjacency(bool need_fof) {
     const int nv = (int)g.nv, nf = (int)g.nf;
+    if (!g.adjacency_valid && g.topo_valid && g.want_topo && nf > 0) {
+        // the mesh is K4's own: umbrellas (and faces-of-faces) straight from the case codes — two passes over the cut cubes and one scan
+        g.d_deg.reserve((size_t)(nv + 1) * sizeof(unsigned));
+        g.d_uoff.reserve((size_t)(nv + 2) * sizeof(unsigned));
+        g.d_uitems.reserve((size_t)nf * 3 * sizeof(int) + 16);
+        if (need_fof) g.d_fof.reserve((size_t)nf * 3 * sizeof(int) + 16);
+        g_kernel_names[KT_ADJACENCY] = "adjacency(k_mc_adjacency<0>+k_uscan+k_mc_adjacency<1>)";
+        const unsigned n_cubes = (unsigned)g.counters[2];
+        unsigned blocks = (n_cubes + 127) / 128;
+        if (blocks > (unsigned)g.sm_count * 16u) blocks = (unsigned)g.sm_count * 16u;
+        const unsigned* n_ptr = g.d_totals.as<unsigned>() + 2;
+        ISD_TIMED(KT_ADJACENCY, k_mc_adjacency<false><<<blocks, 128, 0, g.stream>>>(g.topo_m, g.topo_mb, g.topo_ea, g.d_signs.as<uint32_t>(), g.d_cubes.as<unsigned long long>(),
+                                                                                   n_ptr, g.d_deg.as<unsigned>(), nullptr, nullptr, nullptr));
+        exclusive_scan_u32(g.d_deg.as<unsigned>(), nv, g.d_uoff.as<unsigned>());
+        ISD_TIMED(KT_ADJACENCY, k_mc_adjacency<true><<<blocks, 128, 0, g.stream>>>(g.topo_m, g.topo_mb, g.topo_ea, g.d_signs.as<uint32_t>(), g.d_cubes.as<unsigned long long>(),
+                                                                                  n_ptr, nullptr, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(),
+                                                                                  need_fof ? g.d_fof.as<int>() : nullptr));
+        g.adjacency_valid = true;
+        g.fof_valid_ = need_fof;
+    }
     if (!g.adjacency_valid) {
+        g_kernel_names[KT_ADJACENCY] = "adjacency(k_vertex_degree+k_uscan+k_umbrella_fill+k_umbrella_sort)";
         g.d_deg.reserve((size_t)(nv + 1) * sizeof(unsigned));
         g.d_cursor.reserve((size_t)(nv + 1) * sizeof(unsigned));
         g.d_uoff.reserve((size_t)(nv + 2) * sizeof(unsigned));
@@ -1216,7 +1256,7 @@ void subdivision_step(float amplitude) {
     std::swap(g.d_verts, g.d_verts2);
     std::swap(g.d_faces, g.d_faces2);
     g.nv = nv2; g.nf = nf2;
-    g.adjacency_valid = false; g.fof_valid_ = false; g.perm_valid = false;
+    g.adjacency_valid = false; g.fof_valid_ = false; g.perm_valid = false; g.topo_valid = false;
     g.host_valid = false;
     // randomize_verts draws 3*nv2 numbers whatever the amplitude
     const long long draws = nv2 * 3;
@@ -1273,7 +1313,7 @@ void export_own_slab() {
     }
     g.local_voff = g.own_v0; g.local_foff = g.own_f0;
     g.nv = own_nv; g.nf = own_nf;
-    g.adjacency_valid = false; g.fof_valid_ = false; g.perm_valid = false;      // they describe the local mesh, which is gone
+    g.adjacency_valid = false; g.fof_valid_ = false; g.perm_valid = false; g.topo_valid = false;      // they describe the local mesh, which is gone
     g.host_valid = false;
     g.slab[2] = voff; g.slab[3] = foff; g.slab[4] = own_nv; g.slab[5] = own_nf; g.slab[6] = gnv; g.slab[7] = gnf;
 }
@@ -1320,6 +1360,7 @@ bool build_once(const char* shape_json, const McSettings& s, bool copy_out) {
     g.pair_kernels = s.pair != 0;
     g.search_split = s.search_split != 0;
     g.refill_range = s.refill_range;
+    g.want_topo = s.mc_adjacency != 0;
     g.want_perm = s.perm > 0;      // -1 (auto) is decided once the program is known, below
     g.finish_split = s.finish_split;
     g_kt.reset(s.kernel_times != 0);
@@ -1725,6 +1766,17 @@ int isd_get_projected_centroids(float* out, int64_t count) {
     ISD_CUDA(cudaStreamSynchronize(g.stream));
     return 0;
 }
+int isd_debug_adjacency(int* offsets_nv1, int* items_3nf, int* fof_3nf) {
+    if (!g.ready || !g.adjacency_valid || g.nf == 0) return 1;
+    ISD_CUDA(cudaMemcpyAsync(offsets_nv1, g.d_uoff.ptr, (size_t)(g.nv + 1) * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
+    ISD_CUDA(cudaMemcpyAsync(items_3nf, g.d_uitems.ptr, (size_t)g.nf * 3 * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
+    if (fof_3nf) {
+        if (!g.fof_valid_) return 2;
+        ISD_CUDA(cudaMemcpyAsync(fof_3nf, g.d_fof.ptr, (size_t)g.nf * 3 * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
+    }
+    ISD_CUDA(cudaStreamSynchronize(g.stream));
+    return 0;
+}
 int isd_get_centroid_normals(float* out, int64_t count) {
     if (!g.ready || g.proj_n == 0 || count != g.proj_n * 3) return 1;
     ISD_CUDA(cudaMemcpyAsync(out, g.d_pnrm.ptr, (size_t)count * sizeof(float), cudaMemcpyDeviceToHost, g.stream));
@@ -1747,7 +1799,7 @@ static void load_mesh(const float* verts, int nv, const int* faces, int nf) {
     if (verts && nv) ISD_CUDA(cudaMemcpyAsync(g.d_verts.ptr, verts, (size_t)nv * 3 * sizeof(float), cudaMemcpyHostToDevice, g.stream));
     if (nf) ISD_CUDA(cudaMemcpyAsync(g.d_faces.ptr, faces, (size_t)nf * 3 * sizeof(int), cudaMemcpyHostToDevice, g.stream));
     g.nv = nv; g.nf = nf;
-    g.adjacency_valid = false; g.fof_valid_ = false; g.perm_valid = false; g.host_valid = false;
+    g.adjacency_valid = false; g.fof_valid_ = false; g.perm_valid = false; g.topo_valid = false; g.host_valid = false;
 }
 
 void isd_ob02_on_mesh(const char* shape_parameters_json, float* verts, int nv, const int* faces, int nf, int resample_iters, float c,

@@ -51,6 +51,8 @@ struct McSettings {
     int search_split;     // 1 (default): pair path only — the search's trial points run in a kernel of their own, lanes refilled from per-warp
                           // queues (k_search_trials_refill); 0: in lockstep inside k_project_search_pair
     int refill_range;     // units per ticket of the lane-refill kernels; 0 (default): 128, fewer (>= 32) for meshes too small to fill the GPU
+    int mc_adjacency;     // 1 (default): umbrellas and faces-of-faces of the mesh K4 emitted come straight from the cube case codes
+                          // (mc_adjacency.cuh); 0: from the face list, as for any other mesh (same tables, bit for bit)
     int speculate;        // 1 (default): a build of the spec the previous build had takes that build's counts (mesh size, cut cubes, left-over
                           // centroids) instead of waiting for the device in mid-step; the counts are checked when the build ends and a
                           // mismatch drops the result and builds again the waiting way; 0: always wait
@@ -124,6 +126,7 @@ inline McSettings parse_mc_settings(const char* json) {
     s.pair = d.get_int("gpu.pair", 1);
     s.finish_split = d.get_int("gpu.finish_split", 2);
     s.speculate = d.get_int("gpu.speculate", 1);
+    s.mc_adjacency = d.get_int("gpu.mc_adjacency", 1);
     s.refill_range = d.get_int("gpu.refill_range", 0);
     s.search_split = d.get_int("gpu.search_split", 1);
     s.perm = d.get_int("gpu.perm", -1);

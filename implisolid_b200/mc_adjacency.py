@@ -1,6 +1,6 @@
-"""Umbrella (faces around every vertex) of a marching-cubes mesh straight from the cube case codes — host-side mirror of a
-kernel planned for the next round, kept here so the construction is pinned by a CPU test before it is
-written in CUDA.
+"""Umbrella (faces around every vertex) and faces-of-faces of a marching-cubes mesh straight from the cube case codes — host-side
+mirror of csrc/mc_adjacency.cuh (k_mc_adjacency), kept so that the construction and its tables are pinned by a CPU test
+against the oracle (tests/test_mc_adjacency.py); the kernel itself is held to the generic kernels on the GPU.
 
 The reference builds the umbrella from the finished face list (mesh_algorithms.hpp:178-209: faces around a vertex in
 ascending face index).  For a mesh that comes from marching cubes none of that is needed: a vertex sits on one grid edge,
@@ -63,3 +63,50 @@ def umbrella_from_cases(cases):
                         items.append(int(fbase[cube]) + t)
             offsets.append(len(items))
     return np.array(offsets, dtype=np.int64), np.array(items, dtype=np.int64)
+
+
+# cube faces: 0 -x, 1 +x, 2 -y, 3 +y, 4 -z, 5 +z (mc_adjacency.cuh d_edge_faces / d_across)
+_EDGE_FACES = [{2, 4}, {1, 4}, {3, 4}, {0, 4}, {2, 5}, {1, 5}, {3, 5}, {0, 5}, {0, 2}, {1, 2}, {1, 3}, {0, 3}]
+_ACROSS = {0: {3: 1, 7: 5, 8: 9, 11: 10}, 1: {1: 3, 5: 7, 9: 8, 10: 11}, 2: {0: 2, 4: 6, 8: 11, 9: 10},
+           3: {2: 0, 6: 4, 10: 9, 11: 8}, 4: {0: 4, 1: 5, 2: 6, 3: 7}, 5: {4: 0, 5: 1, 6: 2, 7: 3}}
+_STEP = {0: (-1, 0, 0), 1: (1, 0, 0), 2: (0, -1, 0), 3: (0, 1, 0), 4: (0, 0, -1), 5: (0, 0, 1)}
+
+
+def faces_of_faces_from_cases(cases):
+    """The face across every side of every face (build_faces_of_faces, mesh_algorithms.hpp:50-131) from the case codes alone: the
+    faces that hold both end vertices of a side are triangles of the face's own cube and — when both grid edges lie on one cube
+    face — of the neighbour across it; fewer than two -> 0, else the first in face order unless that is the face itself, then
+    the last.  Returns an (nf, 3) array."""
+    tri, ntri, _ = load_tables()
+    cases = np.asarray(cases, dtype=np.int64)
+    nz, ny, nx = cases.shape
+    flat = cases.reshape(-1)
+    fbase = np.concatenate([[0], np.cumsum(ntri[flat])])
+    out = np.zeros((int(fbase[-1]), 3), dtype=np.int64)
+
+    def holders(cube, ea, eb):
+        row = tri[flat[cube]]
+        return [int(fbase[cube]) + t for t in range(int(ntri[flat[cube]])) if ea in row[3 * t:3 * t + 3] and eb in row[3 * t:3 * t + 3]]
+
+    for c in np.nonzero(ntri[flat])[0]:
+        z, r = divmod(int(c), ny * nx)
+        y, x = divmod(r, nx)
+        row = tri[flat[c]]
+        for t in range(int(ntri[flat[c]])):
+            f = int(fbase[c]) + t
+            for j in range(3):
+                ea, eb = int(row[3 * t + j]), int(row[3 * t + (j + 1) % 3])
+                if ea == eb:
+                    continue
+                found = holders(c, ea, eb)
+                common = _EDGE_FACES[ea] & _EDGE_FACES[eb]
+                if common:
+                    d = min(common)
+                    dx, dy, dz = _STEP[d]
+                    xx, yy, zz = x + dx, y + dy, z + dz
+                    if 0 <= xx < nx and 0 <= yy < ny and 0 <= zz < nz:
+                        found += holders((zz * ny + yy) * nx + xx, _ACROSS[d][ea], _ACROSS[d][eb])
+                if len(found) > 1:
+                    found.sort()
+                    out[f, j] = found[0] if found[0] != f else found[-1]
+    return out

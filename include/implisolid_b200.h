@@ -132,6 +132,9 @@ int isd_get_field(float* out, int64_t count);  /* S^3 floats, x fastest (marchin
 int isd_get_case_codes(uint8_t* out, int64_t count); /* (S-3)^3 cube codes in scan order z,y,x (marching_cubes.hpp:1041-1057) */
 float isd_average_edge(void);                         /* mean edge length used by the last projection */
 int isd_get_projected_centroids(float* out, int64_t count); /* 3*Nf floats of the last projection */
+/* Debug (parity tests): the adjacency tables the last build's OB02 stages used, for the mesh they were built on (before any
+ * subdivision): umbrella CSR (nv+1 offsets, 3*nf items) and, if fof_3nf != NULL and it was built, faces-of-faces.  0 on success. */
+int isd_debug_adjacency(int* offsets_nv1, int* items_3nf, int* fof_3nf);
 int isd_get_centroid_normals(float* out, int64_t count);
 
 /* HEAD-literal `cube` (cube.hpp:65-72,215-270): the SDF table it interpolates, supplied by the

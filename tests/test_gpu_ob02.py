@@ -9,6 +9,7 @@ import numpy as np
 import pytest
 
 from implisolid_b200 import shapes
+from tests.oracle_lib import load_oracle
 
 pytestmark = pytest.mark.gpu
 
@@ -177,3 +178,52 @@ def test_pair_kernels_change_nothing(gpu_lib, shape, R, half):
         assert np.array_equal(c0.view(np.uint32), c1.view(np.uint32)) and np.array_equal(n0.view(np.uint32), n1.view(np.uint32))
         for k in ("projection_by_type", "projection_failed", "bisection_capped", "bisected"):
             assert s0[k] == s1[k], (k, s0[k], s1[k])
+
+
+@pytest.mark.parametrize("shape,R,half", [(shapes.c4_deep_chain, 96, 1.0), (shapes.bushy_tree, 80, 0.9), (shapes.c3_metaballs, 64, 1.2),
+                                          (shapes.n1_medley, 72, 0.9), (shapes.c2_cube_minus_cylinder, 100, 0.8), (shapes.demo_moon, 90, 0.6),
+                                          (lambda: shapes.random_tree(9), 48, 1.0), (shapes.c1_sphere, 21, 0.55)],
+                         ids=["c4", "bushy", "c3", "medley", "c2", "moon", "random9", "sphere"])
+def test_mc_adjacency_equals_generic(gpu_lib, shape, R, half):
+    """Umbrellas and faces-of-faces straight from the cube case codes (csrc/mc_adjacency.cuh, the default for the mesh K4 emits)
+    against the generic kernels that build them from the face list ("gpu":{"mc_adjacency":0}) and against the oracle's tables:
+    identical arrays, hence identical OB02 results bit for bit."""
+    sj = shape()
+    out = []
+    for topo in (1, 0):
+        gpu_lib.build_geometry(sj, shapes.mc_settings(R, half, iters=1, c=1.0, projection=1, qem=1, mc_adjacency=topo))
+        v, f = gpu_lib.get_v(), gpu_lib.get_f()
+        off, items, fof = gpu_lib.debug_adjacency(v.shape[0], f.shape[0])
+        gpu_lib.finish_geometry()
+        out.append((v, f, off, items, fof))
+    (v1, f1, off1, it1, fof1), (v0, f0, off0, it0, fof0) = out
+    assert np.array_equal(f1, f0)
+    assert np.array_equal(off1, off0) and np.array_equal(it1, it0)
+    assert np.array_equal(fof1, fof0)
+    assert np.array_equal(v1.view(np.uint32), v0.view(np.uint32))
+    o = load_oracle()
+    ooff, oitems = o.umbrella(f1, v1.shape[0])
+    assert np.array_equal(off1, ooff) and np.array_equal(it1, oitems)
+    assert np.array_equal(fof1.reshape(-1, 3), o.faces_of_faces(f1))
+
+
+@pytest.mark.parametrize("world", [2, 5])
+def test_mc_adjacency_equals_generic_on_halo_slabs(gpu_lib, world):
+    """The same on emulated z-slabs in halo mode, where the local mesh has a ghost layer (vertices, no faces) below and ends at
+    the slab's top: every rank's exported slab keeps its bits."""
+    sj = shapes.c4_deep_chain()
+    L = gpu_lib.lib
+    try:
+        for r in range(world):
+            res = []
+            for topo in (1, 0):
+                L.isd_dist_emulate(r, world)
+                L.isd_dist_set_offsets(0, 0)
+                L.isd_dist_set_edge_total(3 << 40, 40000)
+                gpu_lib.build_geometry(sj, shapes.mc_settings(72, 1.0, iters=1, c=1.0, projection=1, qem=1, mc_adjacency=topo))
+                res.append((gpu_lib.get_v(), gpu_lib.get_f()))
+                gpu_lib.finish_geometry()
+            assert np.array_equal(res[0][1], res[1][1])
+            assert np.array_equal(res[0][0].view(np.uint32), res[1][0].view(np.uint32))
+    finally:
+        L.isd_dist_emulate(0, 1)
