@@ -11,7 +11,7 @@ import sys
 rows = list(csv.reader(open(sys.argv[1])))
 hdr = rows[0]
 ix = {n: i for i, n in enumerate(hdr)}
-ADJ = ("k_vertex_degree", "k_uscan", "k_umbrella_fill", "k_umbrella_sort")
+ADJ = ("k_vertex_degree", "k_uscan", "k_umbrella_fill", "k_umbrella_sort", "k_mc_adjacency")
 out = {}
 for r in rows[2:]:
     if len(r) < len(hdr):
