@@ -759,8 +759,7 @@ void run_marching_cubes(const McSettings& s, const ShapeCompiler::Program& prog)
         ea.v_local0 = ghost_v; ea.f_local0 = ghost_f;
         ea.ghost_vertices = g.halo_mode ? 1 : 0;
         if (g.halo_mode) { ea.vbase = 0; ea.fbase = 0; ea.v_local0 = 0; }      // local numbering = scan order, ghost vertices first
-        unsigned blocks = (n_cubes + kEmitThreads - 1) / kEmitThreads;
-        if (blocks > (unsigned)g.sm_count * 16u) blocks = (unsigned)g.sm_count * 16u;
+        const unsigned blocks = (n_cubes + kEmitThreads - 1) / kEmitThreads;      // one thread per cut cube (a cap of 16 blocks per SM measured 3 % slower)
         ISD_TIMED(KT_EMIT, k_mc_emit<<<blocks, kEmitThreads, 0, g.stream>>>(m, mb, ea, g.d_field.as<float>(), g.d_signs.as<uint32_t>(),
                                                          g.d_cubes.as<unsigned long long>(), g.d_totals.as<unsigned>() + 2,
                                                          g.d_verts.as<float>() + g.local_voff * 3, g.d_faces.as<int>() + g.local_foff * 3));
@@ -857,13 +856,13 @@ void build_adjacency(bool need_fof) {
         if (need_fof) g.d_fof.reserve((size_t)nf * 3 * sizeof(int) + 16);
         g_kernel_names[KT_ADJACENCY] = "adjacency(k_mc_adjacency<0>+k_uscan+k_mc_adjacency<1>)";
         const unsigned n_cubes = (unsigned)g.counters[2];
-        unsigned blocks = (n_cubes + 127) / 128;
-        if (blocks > (unsigned)g.sm_count * 16u) blocks = (unsigned)g.sm_count * 16u;
+        // one thread per cut cube, no grid-stride cap: measured 0.343 against 0.394 ms at C4 1024^3 with the grid capped at 16 blocks per SM
+        const unsigned blocks = (n_cubes + kAdjThreads - 1) / kAdjThreads;
         const unsigned* n_ptr = g.d_totals.as<unsigned>() + 2;
-        ISD_TIMED(KT_ADJACENCY, k_mc_adjacency<false><<<blocks, 128, 0, g.stream>>>(g.topo_m, g.topo_mb, g.topo_ea, g.d_signs.as<uint32_t>(), g.d_cubes.as<unsigned long long>(),
+        ISD_TIMED(KT_ADJACENCY, k_mc_adjacency<false><<<blocks, kAdjThreads, 0, g.stream>>>(g.topo_m, g.topo_mb, g.topo_ea, g.d_signs.as<uint32_t>(), g.d_cubes.as<unsigned long long>(),
                                                                                    n_ptr, g.d_deg.as<unsigned>(), nullptr, nullptr, nullptr));
         exclusive_scan_u32(g.d_deg.as<unsigned>(), nv, g.d_uoff.as<unsigned>());
-        ISD_TIMED(KT_ADJACENCY, k_mc_adjacency<true><<<blocks, 128, 0, g.stream>>>(g.topo_m, g.topo_mb, g.topo_ea, g.d_signs.as<uint32_t>(), g.d_cubes.as<unsigned long long>(),
+        ISD_TIMED(KT_ADJACENCY, k_mc_adjacency<true><<<blocks, kAdjThreads, 0, g.stream>>>(g.topo_m, g.topo_mb, g.topo_ea, g.d_signs.as<uint32_t>(), g.d_cubes.as<unsigned long long>(),
                                                                                   n_ptr, nullptr, g.d_uoff.as<unsigned>(), g.d_uitems.as<int>(),
                                                                                   need_fof ? g.d_fof.as<int>() : nullptr));
         g.adjacency_valid = true;

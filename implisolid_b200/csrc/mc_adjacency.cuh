@@ -57,14 +57,18 @@ __device__ int8_t d_across[6][12] = {
     {4, 5, 6, 7, -1, -1, -1, -1, -1, -1, -1, -1},       // -z: 0->4 1->5 2->6 3->7
     {-1, -1, -1, -1, 0, 1, 2, 3, -1, -1, -1, -1}};      // +z: 4->0 5->1 6->2 7->3
 
+#ifndef ISD_ADJ_THREADS
+#define ISD_ADJ_THREADS 128
+#endif
+constexpr int kAdjThreads = ISD_ADJ_THREADS;
 template <bool FILL>
-__global__ void __launch_bounds__(128) k_mc_adjacency(McDesc m, McBuffers mb, EmitArgs ea, const uint32_t* __restrict__ signs,
+__global__ void __launch_bounds__(kAdjThreads) k_mc_adjacency(McDesc m, McBuffers mb, EmitArgs ea, const uint32_t* __restrict__ signs,
                                                       const unsigned long long* __restrict__ cubes, const unsigned* __restrict__ n_cubes_ptr,
                                                       unsigned* __restrict__ deg, const unsigned* __restrict__ offsets, int* __restrict__ items,
                                                       int* __restrict__ fof) {
     const unsigned n_cubes = *n_cubes_ptr;
     const int plane_lo = m.g.z0, plane_hi = m.g.z0 + m.g.nz - 1;      // resident node planes
-    for (unsigned i = blockIdx.x * 128 + threadIdx.x; i < n_cubes; i += gridDim.x * 128) {
+    for (unsigned i = blockIdx.x * kAdjThreads + threadIdx.x; i < n_cubes; i += gridDim.x * kAdjThreads) {
         const unsigned long long id = cubes[i];
         const long long seg = (long long)(id >> 3);
         const int l = (int)(id & 7ull), r = (int)(seg & 63);
